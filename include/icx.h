@@ -1,0 +1,272 @@
+/*
+ * icx.h -- C ABI of intercession-b200: the physics tick and the world-line
+ * record / replay / divergence scan of meta-engineer/Intercession, on B200.
+ *
+ * Every entry point is `extern "C"`, takes plain pointers and sizes, returns an
+ * int status (never throws / aborts across the boundary) and replaces the
+ * reference interface cited next to it (paths relative to the reference
+ * repository root).  The reference-side binding is shown in INTEGRATION.md.
+ *
+ * Threading: an IcxWorld is single-thread-affine (one CUDA stream); distinct
+ * worlds are independent.  No CPU fallback exists: without a CUDA device
+ * icx_world_create() fails with ICX_E_CUDA.
+ */
+#ifndef ICX_H
+#define ICX_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ICX_ABI_VERSION 1
+
+/* ---- status codes (reference: C++ exceptions, SURVEY 8b "Errors") ---- */
+#define ICX_OK           0
+#define ICX_E_INVALID    1   /* bad argument / bad call order                */
+#define ICX_E_CUDA       2   /* CUDA runtime error (see icx_last_error)      */
+#define ICX_E_CAPACITY   3   /* a fixed-capacity device buffer overflowed    */
+#define ICX_E_NOMEM      4
+#define ICX_E_STATE      5   /* object is in the wrong state for this call   */
+
+/* ---- enums mirroring source/physics/collider.h:18-37 ---- */
+#define ICX_COLLIDER_NONE   0
+#define ICX_COLLIDER_BOX    1
+#define ICX_COLLIDER_SPHERE 2
+#define ICX_COLLIDER_RAY    3
+
+#define ICX_COLLISION_NOOP   0
+#define ICX_COLLISION_RIGID  1
+#define ICX_COLLISION_SPRING 2
+#define ICX_COLLISION_FORCE  3
+
+/* ---- TimestreamState, source/spacetime/timestream_state.h:11-18 ---- */
+#define ICX_TS_MERGED        0
+#define ICX_TS_FORKED        1
+#define ICX_TS_FORKING       2
+#define ICX_TS_SUPERPOSITION 3
+#define ICX_TS_GHOST         4
+
+/*
+ * Entity id.  The reference packs a uint16 as 4b timeslice | 8b genesis | 4b
+ * causal chain-link (source/ecs/ecs_types.h:16-58), which caps a cosmos at 255
+ * hosted entities.  Here the same three fields live in a uint32:
+ * 4b timeslice [31:28] | 24b genesis [27:4] | 4b chain-link [3:0].
+ * A reference id `e` maps to ((e & 0xF000) << 16) | (e & 0x0FFF).
+ */
+typedef uint32_t IcxEntity;
+#define ICX_NULL_ENTITY        0xFFFFFFFFu
+#define ICX_NULL_TIMESLICE     14u          /* ecs_types.h: NULL_TIMESLICEID       */
+#define ICX_NULL_CHAINLINK     15u          /* ecs_types.h: NULL_CAUSALCHAINLINK   */
+#define ICX_COLLIDERS_PER_ENTITY 2          /* source/physics/collider_component.h:9 */
+
+/* ---- AoS component layouts, byte-identical to the reference structs ---- */
+
+/* source/physics/transform_component.h:14-20 (40 B; quaternion stored w,x,y,z) */
+typedef struct IcxTransform {
+    float origin[3];
+    float orientation[4];   /* w, x, y, z */
+    float scale[3];
+} IcxTransform;
+
+/* source/physics/physics_component.h:24-55 (108 B) */
+typedef struct IcxPhysics {
+    float   velocity[3];
+    float   acceleration[3];
+    float   angularVelocity[3];
+    float   angularAcceleration[3];
+    float   linearDrag;
+    float   angularDrag;
+    float   collisionLinearDrag;
+    float   collisionAngularDrag;
+    float   mass;                   /* 0 == INFINITE_MASS */
+    uint8_t lockOrigin;      uint8_t _pad0[3];
+    float   lockedOrigin[3];
+    uint8_t lockOrientation; uint8_t _pad1[3];
+    float   lockedOrientation[4];   /* w, x, y, z */
+    uint8_t isAsleep;        uint8_t _pad2[3];
+} IcxPhysics;
+
+/* source/physics/collider.h:42-92 (84 B) */
+typedef struct IcxCollider {
+    int32_t colliderType;           /* ICX_COLLIDER_*  */
+    int32_t collisionType;          /* ICX_COLLISION_* */
+    uint8_t isActive;
+    uint8_t useBehaviorsResponse;
+    uint8_t _pad0[2];
+    IcxTransform localTransform;
+    uint8_t inheritOrientation;
+    uint8_t influenceOrientation;
+    uint8_t _pad1[2];
+    float   minParametricValue;
+    float   staticFriction;
+    float   dynamicFriction;
+    float   restitution;
+    float   stiffness;
+    float   damping;
+    float   restLength;
+} IcxCollider;
+
+/* source/physics/collider_component.h:11-14 (168 B) */
+typedef struct IcxColliderComponent {
+    IcxCollider colliders[ICX_COLLIDERS_PER_ENTITY];
+} IcxColliderComponent;
+
+/*
+ * One narrowphase hit, in the values the reference hands to
+ * I_BehaviorsDrivetrain::on_collision (collision_physics_relay.h:114-155):
+ * i.e. AFTER the response procedure adjusted collisionPoint.  Records are
+ * returned in the reference's pair order (lexicographic on collider packets).
+ * flags: bit0 = a physics response ran, bit1/bit2 = collider A/B has
+ * useBehaviorsResponse (the adapter calls on_collision for those).
+ */
+typedef struct IcxContact {
+    IcxEntity entityA;
+    IcxEntity entityB;
+    uint8_t   slotA;
+    uint8_t   slotB;
+    uint16_t  flags;
+    float     point[3];
+    float     normal[3];
+    float     depth;
+    uint32_t  packetA;      /* collider packet indices (submission order) */
+    uint32_t  packetB;
+} IcxContact;
+
+#define ICX_CONTACT_RESPONDED   0x1u
+#define ICX_CONTACT_BEHAVIORS_A 0x2u
+#define ICX_CONTACT_BEHAVIORS_B 0x4u
+
+/* events::cosmos::TIMESTREAM_INTERCEPTION_params, source/events/event_types.h:133-139 */
+typedef struct IcxInterception {
+    IcxEntity agent;
+    IcxEntity recipient;
+} IcxInterception;
+
+/* A broadphase candidate: collider packet indices, a < b. */
+typedef struct IcxPair {
+    uint32_t a;
+    uint32_t b;
+} IcxPair;
+
+#define ICX_F_SPHERE_SPHERE   0x1u  /* wire the reference's unwired sphere_sphere_intersect
+                                       (collision_procedures.cpp:380-423); default off = parity
+                                       with the dispatch table collision_procedures.h:411-417 */
+#define ICX_F_NO_GRAVITY      0x2u  /* skip the hard-coded gravity (euler_physics_relay.h:32)  */
+
+typedef struct IcxConfig {
+    uint32_t struct_size;           /* = sizeof(IcxConfig)                                      */
+    int32_t  device;                /* CUDA device ordinal                                      */
+    uint32_t max_entities;
+    uint32_t host_timeslice;        /* Cosmos::get_host_id(); ICX_NULL_TIMESLICE = parallel     */
+    uint32_t flags;                 /* ICX_F_*                                                  */
+    float    gravity[3];            /* default (0,-10,0), euler_physics_relay.h:32              */
+    float    broadphase_margin;     /* AABB inflation; 0 = default 0.05                         */
+    float    cell_size;             /* uniform-grid cell; 0 = chosen at upload                  */
+    uint32_t max_neighbors;         /* candidate list capacity per collider; 0 = default 24     */
+    uint32_t max_large;             /* colliders larger than a cell; 0 = default 1024           */
+    uint32_t max_contacts;          /* contact / interception ring; 0 = 2 * max_entities        */
+    uint32_t worldline_stride;      /* 0 = one world; else entities [k*stride,(k+1)*stride) form
+                                       independent world-line k (pairs never cross world-lines) */
+} IcxConfig;
+
+typedef struct IcxStats {
+    uint64_t ticks;
+    uint32_t n_entities;
+    uint32_t n_packets;             /* active colliders submitted this tick                     */
+    uint32_t n_large;
+    uint32_t n_candidates;          /* broadphase pairs of the last tick                        */
+    uint32_t n_contacts;
+    uint32_t n_interceptions;
+    uint32_t n_rounds;              /* dependency rounds of the ordered resolve                 */
+    uint32_t n_retries;             /* ticks re-run with a larger margin / capacity (cumulative)*/
+    float    margin;                /* margin in force                                          */
+    float    cell_size;
+    uint32_t max_neighbors;
+    uint32_t _reserved;
+} IcxStats;
+
+typedef struct IcxWorld IcxWorld;
+typedef struct IcxTimeline IcxTimeline;
+
+/* ---- library ---- */
+int         icx_abi_version(void);
+int         icx_device_count(void);             /* 0 when no CUDA device is usable */
+const char* icx_status_string(int status);
+void        icx_config_default(IcxConfig* cfg);
+
+/* ---- world lifetime (replaces PhysicsDynamo ctor/dtor, physics_dynamo.cpp:7-21) ---- */
+int         icx_world_create(const IcxConfig* cfg, IcxWorld** out);
+void        icx_world_destroy(IcxWorld* w);
+const char* icx_last_error(const IcxWorld* w);
+
+/*
+ * Upload = PhysicsSynchro::update + ColliderSynchro::update
+ * (physics_synchro.cpp:12-36, collider_synchro.cpp:11-43): entities in ascending
+ * submission order; entity i has transform[i], optional physics (has_physics[i],
+ * NULL = all have one; collision_physics_relay.h:84-106 skips the response
+ * otherwise), optional collider component (colliders NULL = none), timestream
+ * state (Cosmos::get_timestream_state, cosmos.cpp:175-178; NULL = merged, 0).
+ */
+int icx_bodies_upload(IcxWorld* w, uint32_t n_entities,
+                      const IcxEntity* entity,
+                      const IcxTransform* transform,
+                      const IcxPhysics* physics,
+                      const uint8_t* has_physics,
+                      const IcxColliderComponent* colliders,
+                      const uint8_t* tstate,
+                      const uint16_t* tstate_coherency);
+
+/* Write device state back into the caller's AoS arrays (any pointer may be NULL). */
+int icx_bodies_download(IcxWorld* w, uint32_t n_entities,
+                        IcxTransform* transform,
+                        IcxPhysics* physics,
+                        IcxColliderComponent* colliders,
+                        uint8_t* tstate,
+                        uint16_t* tstate_coherency);
+
+/* Host-side edits between ticks (behaviours, replay): overwrite `count` entities
+ * listed in `index` (indices into the upload order) from the given AoS arrays,
+ * which are indexed by position in `index`.  NULL arrays are left untouched. */
+int icx_bodies_update(IcxWorld* w, uint32_t count, const uint32_t* index,
+                      const IcxTransform* transform,
+                      const IcxPhysics* physics,
+                      const IcxColliderComponent* colliders);
+
+/* Cosmos::get/set_coherency (cosmos.cpp:136-147) */
+int icx_coherency_set(IcxWorld* w, uint16_t coherency);
+int icx_coherency_get(IcxWorld* w, uint16_t* coherency);
+
+/*
+ * One tick = PhysicsDynamo::run_relays(dt) (physics_dynamo.cpp:38-46):
+ * EulerPhysicsRelay::engage then CollisionPhysicsRelay::engage, followed by
+ * Cosmos::increment_coherency (i_cosmos_context.cpp:64).  Asynchronous on the
+ * world's stream; icx_sync() waits and reports deferred errors.
+ */
+int icx_step(IcxWorld* w, double dt);
+int icx_step_n(IcxWorld* w, double dt, uint32_t n_ticks);
+int icx_sync(IcxWorld* w);
+
+/* Individual relays, for per-stage parity tests (A_PhysicsRelay::engage). */
+int icx_euler_engage(IcxWorld* w, double dt);       /* euler_physics_relay.h:21-97     */
+int icx_collision_engage(IcxWorld* w);              /* collision_physics_relay.h:24-231 */
+
+/* Results of the last tick.  *n receives the total available even if > cap. */
+int icx_pairs_fetch(IcxWorld* w, IcxPair* out, size_t cap, size_t* n);
+int icx_contacts_fetch(IcxWorld* w, IcxContact* out, size_t cap, size_t* n);
+int icx_interceptions_fetch(IcxWorld* w, IcxInterception* out, size_t cap, size_t* n);
+int icx_stats_fetch(IcxWorld* w, IcxStats* out);
+
+/* Device-timed duration (ms) of the last icx_step/icx_step_n, CUDA events on
+ * the world's stream. */
+int icx_last_step_ms(IcxWorld* w, float* ms);
+
+/* CUDA stream of the world as a void* (cudaStream_t), for callers that time it. */
+void* icx_world_stream(IcxWorld* w);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ICX_H */

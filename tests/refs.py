@@ -1,0 +1,102 @@
+"""Loaders for the CHECKERS (test infrastructure): oracle/_ref/libicx_ref.so = the reference's
+own sources compiled headlessly, oracle/libicx_oracle.so = the CPU restatement."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from intercession_b200 import abi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_PATH = os.path.join(ROOT, "oracle", "_ref", "libicx_ref.so")
+ORACLE_PATH = os.path.join(ROOT, "oracle", "libicx_oracle.so")
+
+_vp, _u32, _sz, _dbl = C.c_void_p, C.c_uint32, C.c_size_t, C.c_double
+_psz = C.POINTER(C.c_size_t)
+_pd = C.POINTER(C.c_double)
+
+
+def _collide_sig():
+    return (C.c_int, [_u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_uint16, _u32, _u32, _u32,
+                      _vp, _sz, _vp, _sz, _psz, _vp, _sz, _psz, _pd])
+
+
+REF_SIGS = {
+    "icxref_verbatim_run": (C.c_int, [_u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.POINTER(C.c_uint16),
+                                      _u32, _dbl, _u32, _vp, _sz, _psz, _vp, _sz, _psz, _pd]),
+    "icxref_euler": (C.c_int, [_u32, _vp, _vp, _vp, _dbl, _pd]),
+    "icxref_collide": _collide_sig(),
+    "icxref_intersect": (C.c_int, [_vp, _vp, _vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp]),
+    "icxref_response": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+}
+
+
+def _load(path, sigs):
+    if not os.path.exists(path):
+        return None
+    lib = C.CDLL(path)
+    for name, (res, args) in sigs.items():
+        fn = getattr(lib, name)
+        fn.restype, fn.argtypes = res, args
+    return lib
+
+
+_ref = None
+
+
+def ref():
+    global _ref
+    if _ref is None:
+        _ref = _load(REF_PATH, REF_SIGS)
+    return _ref
+
+
+def narrow16(ids32):
+    """IcxEntity -> reference uint16 id (genesis must fit 8 bits)."""
+    ids32 = np.asarray(ids32, np.uint32)
+    g = (ids32 >> 4) & 0xFFFFFF
+    assert (g < 255).all()
+    return (((ids32 >> 28) << 12) | (g << 4) | (ids32 & 0xF)).astype(np.uint16)
+
+
+def verbatim_run(scene, n_ticks=1, dt=1.0 / 45, host=0, coherency=0, cap=1 << 16, ids16=None):
+    """Run the reference objects (Cosmos + PhysicsDynamo) on a copy of `scene`."""
+    s = scene.copy()
+    ids = narrow16(s.ids) if ids16 is None else np.asarray(ids16, np.uint16)
+    hits = np.zeros(cap, abi.contact_dt)
+    ints = np.zeros(cap, abi.interception_dt)
+    nh, ni, sec = C.c_size_t(0), C.c_size_t(0), C.c_double(0)
+    coh = C.c_uint16(coherency)
+    has_col = np.ascontiguousarray(s.C["colliders"]["isActive"].any(axis=1).astype(np.uint8))
+    rc = ref().icxref_verbatim_run(s.n, abi.ptr(ids), abi.ptr(s.T), abi.ptr(s.P), abi.ptr(s.hasP),
+                                   abi.ptr(s.C), abi.ptr(has_col), abi.ptr(s.tstate), abi.ptr(s.tcoh),
+                                   C.byref(coh), host, dt, n_ticks, abi.ptr(hits), cap, C.byref(nh),
+                                   abi.ptr(ints), cap, C.byref(ni), C.byref(sec))
+    assert rc == 0, rc
+    s["hits"], s["ints"], s["seconds"], s["coherency"] = hits[:nh.value], ints[:ni.value], sec.value, coh.value
+    return s
+
+
+def procedures_tick(lib, prefix, scene, dt=1.0 / 45, host=0, coherency=0, flags=0, stride=0, cand=None,
+                    cap=None, euler=True, collide=True):
+    """One tick through `<prefix>_euler` + `<prefix>_collide` (reference procedures or the oracle)."""
+    s = scene.copy()
+    cap = cap or max(4 * s.n, 1024)
+    hits = np.zeros(cap, abi.contact_dt)
+    ints = np.zeros(cap, abi.interception_dt)
+    nh, ni, sec1, sec2 = C.c_size_t(0), C.c_size_t(0), C.c_double(0), C.c_double(0)
+    if euler:
+        rc = getattr(lib, prefix + "_euler")(s.n, abi.ptr(s.T), abi.ptr(s.P), abi.ptr(s.hasP), dt, C.byref(sec1))
+        assert rc == 0
+    if collide:
+        if cand is not None:
+            cand = np.ascontiguousarray(cand, abi.pair_dt)
+        rc = getattr(lib, prefix + "_collide")(
+            s.n, abi.ptr(s.ids), abi.ptr(s.T), abi.ptr(s.P), abi.ptr(s.hasP), abi.ptr(s.C),
+            abi.ptr(s.tstate), abi.ptr(s.tcoh), coherency, host, flags, stride,
+            abi.ptr(cand), 0 if cand is None else len(cand),
+            abi.ptr(hits), cap, C.byref(nh), abi.ptr(ints), cap, C.byref(ni), C.byref(sec2))
+        assert rc == 0, rc
+    assert nh.value <= cap and ni.value <= cap
+    s["hits"], s["ints"], s["seconds"] = hits[:nh.value], ints[:ni.value], sec1.value + sec2.value
+    return s
