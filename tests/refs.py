@@ -41,7 +41,44 @@ def _load(path, sigs):
     return lib
 
 
+ORACLE_SIGS = {
+    "icxo_euler": REF_SIGS["icxref_euler"],
+    "icxo_collide": _collide_sig(),
+    "icxo_intersect": REF_SIGS["icxref_intersect"],
+    "icxo_response": REF_SIGS["icxref_response"],
+    "icxo_aabbs": (C.c_int, [_u32, _vp, _vp, C.c_float, _vp, _sz, _psz]),
+    "icxo_pairs": (C.c_int, [_u32, _vp, _vp, C.c_float, _u32, _u32, C.c_int, _vp, _sz, _psz]),
+}
+
 _ref = None
+_oracle = None
+
+
+def oracle():
+    global _oracle
+    if _oracle is None:
+        _oracle = _load(ORACLE_PATH, ORACLE_SIGS)
+    return _oracle
+
+
+def oracle_pairs(scene, margin, flags=0, stride=0, method=1, cap=None):
+    """Broadphase candidate list per the oracle's definition (method 0 = brute force)."""
+    cap = cap or max(64 * scene.n, 4096)
+    out = np.zeros(cap, abi.pair_dt)
+    n = C.c_size_t(0)
+    Cc = scene.C.copy()
+    rc = oracle().icxo_pairs(scene.n, abi.ptr(scene.T), abi.ptr(Cc), margin, flags, stride, method,
+                             abi.ptr(out), cap, C.byref(n))
+    assert rc == 0 and n.value <= cap, (rc, n.value, cap)
+    return out[:n.value]
+
+
+def oracle_aabbs(scene, margin):
+    out = np.zeros((2 * scene.n, 6), np.float32)
+    n = C.c_size_t(0)
+    Cc = scene.C.copy()
+    oracle().icxo_aabbs(scene.n, abi.ptr(scene.T), abi.ptr(Cc), margin, abi.ptr(out), len(out), C.byref(n))
+    return out[:n.value]
 
 
 def ref():
