@@ -23,6 +23,12 @@ extern "C" {
 
 #define ICX_ABI_VERSION 1
 
+#if defined(__GNUC__)
+#define ICX_API __attribute__((visibility("default")))
+#else
+#define ICX_API
+#endif
+
 /* ---- status codes (reference: C++ exceptions, SURVEY 8b "Errors") ---- */
 #define ICX_OK           0
 #define ICX_E_INVALID    1   /* bad argument / bad call order                */
@@ -192,15 +198,15 @@ typedef struct IcxWorld IcxWorld;
 typedef struct IcxTimeline IcxTimeline;
 
 /* ---- library ---- */
-int         icx_abi_version(void);
-int         icx_device_count(void);             /* 0 when no CUDA device is usable */
-const char* icx_status_string(int status);
-void        icx_config_default(IcxConfig* cfg);
+ICX_API int         icx_abi_version(void);
+ICX_API int         icx_device_count(void);             /* 0 when no CUDA device is usable */
+ICX_API const char* icx_status_string(int status);
+ICX_API void        icx_config_default(IcxConfig* cfg);
 
 /* ---- world lifetime (replaces PhysicsDynamo ctor/dtor, physics_dynamo.cpp:7-21) ---- */
-int         icx_world_create(const IcxConfig* cfg, IcxWorld** out);
-void        icx_world_destroy(IcxWorld* w);
-const char* icx_last_error(const IcxWorld* w);
+ICX_API int         icx_world_create(const IcxConfig* cfg, IcxWorld** out);
+ICX_API void        icx_world_destroy(IcxWorld* w);
+ICX_API const char* icx_last_error(const IcxWorld* w);
 
 /*
  * Upload = PhysicsSynchro::update + ColliderSynchro::update
@@ -210,7 +216,7 @@ const char* icx_last_error(const IcxWorld* w);
  * otherwise), optional collider component (colliders NULL = none), timestream
  * state (Cosmos::get_timestream_state, cosmos.cpp:175-178; NULL = merged, 0).
  */
-int icx_bodies_upload(IcxWorld* w, uint32_t n_entities,
+ICX_API int icx_bodies_upload(IcxWorld* w, uint32_t n_entities,
                       const IcxEntity* entity,
                       const IcxTransform* transform,
                       const IcxPhysics* physics,
@@ -220,7 +226,7 @@ int icx_bodies_upload(IcxWorld* w, uint32_t n_entities,
                       const uint16_t* tstate_coherency);
 
 /* Write device state back into the caller's AoS arrays (any pointer may be NULL). */
-int icx_bodies_download(IcxWorld* w, uint32_t n_entities,
+ICX_API int icx_bodies_download(IcxWorld* w, uint32_t n_entities,
                         IcxTransform* transform,
                         IcxPhysics* physics,
                         IcxColliderComponent* colliders,
@@ -230,14 +236,14 @@ int icx_bodies_download(IcxWorld* w, uint32_t n_entities,
 /* Host-side edits between ticks (behaviours, replay): overwrite `count` entities
  * listed in `index` (indices into the upload order) from the given AoS arrays,
  * which are indexed by position in `index`.  NULL arrays are left untouched. */
-int icx_bodies_update(IcxWorld* w, uint32_t count, const uint32_t* index,
+ICX_API int icx_bodies_update(IcxWorld* w, uint32_t count, const uint32_t* index,
                       const IcxTransform* transform,
                       const IcxPhysics* physics,
                       const IcxColliderComponent* colliders);
 
 /* Cosmos::get/set_coherency (cosmos.cpp:136-147) */
-int icx_coherency_set(IcxWorld* w, uint16_t coherency);
-int icx_coherency_get(IcxWorld* w, uint16_t* coherency);
+ICX_API int icx_coherency_set(IcxWorld* w, uint16_t coherency);
+ICX_API int icx_coherency_get(IcxWorld* w, uint16_t* coherency);
 
 /*
  * One tick = PhysicsDynamo::run_relays(dt) (physics_dynamo.cpp:38-46):
@@ -245,26 +251,26 @@ int icx_coherency_get(IcxWorld* w, uint16_t* coherency);
  * Cosmos::increment_coherency (i_cosmos_context.cpp:64).  Asynchronous on the
  * world's stream; icx_sync() waits and reports deferred errors.
  */
-int icx_step(IcxWorld* w, double dt);
-int icx_step_n(IcxWorld* w, double dt, uint32_t n_ticks);
-int icx_sync(IcxWorld* w);
+ICX_API int icx_step(IcxWorld* w, double dt);
+ICX_API int icx_step_n(IcxWorld* w, double dt, uint32_t n_ticks);
+ICX_API int icx_sync(IcxWorld* w);
 
 /* Individual relays, for per-stage parity tests (A_PhysicsRelay::engage). */
-int icx_euler_engage(IcxWorld* w, double dt);       /* euler_physics_relay.h:21-97     */
-int icx_collision_engage(IcxWorld* w);              /* collision_physics_relay.h:24-231 */
+ICX_API int icx_euler_engage(IcxWorld* w, double dt);       /* euler_physics_relay.h:21-97     */
+ICX_API int icx_collision_engage(IcxWorld* w);              /* collision_physics_relay.h:24-231 */
 
 /* Results of the last tick.  *n receives the total available even if > cap. */
-int icx_pairs_fetch(IcxWorld* w, IcxPair* out, size_t cap, size_t* n);
-int icx_contacts_fetch(IcxWorld* w, IcxContact* out, size_t cap, size_t* n);
-int icx_interceptions_fetch(IcxWorld* w, IcxInterception* out, size_t cap, size_t* n);
-int icx_stats_fetch(IcxWorld* w, IcxStats* out);
+ICX_API int icx_pairs_fetch(IcxWorld* w, IcxPair* out, size_t cap, size_t* n);
+ICX_API int icx_contacts_fetch(IcxWorld* w, IcxContact* out, size_t cap, size_t* n);
+ICX_API int icx_interceptions_fetch(IcxWorld* w, IcxInterception* out, size_t cap, size_t* n);
+ICX_API int icx_stats_fetch(IcxWorld* w, IcxStats* out);
 
 /* Device-timed duration (ms) of the last icx_step/icx_step_n, CUDA events on
  * the world's stream. */
-int icx_last_step_ms(IcxWorld* w, float* ms);
+ICX_API int icx_last_step_ms(IcxWorld* w, float* ms);
 
 /* CUDA stream of the world as a void* (cudaStream_t), for callers that time it. */
-void* icx_world_stream(IcxWorld* w);
+ICX_API void* icx_world_stream(IcxWorld* w);
 
 #ifdef __cplusplus
 }

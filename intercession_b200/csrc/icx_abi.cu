@@ -1,0 +1,473 @@
+// C ABI of include/icx.h: world lifetime, AoS import/export, the tick driver.
+// No CPU fallback: every compute entry point needs a CUDA device.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include "icx_host.h"
+
+using namespace icx;
+
+namespace {
+
+#define CK(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { return fail_cuda(w, _e, #call); } } while (0)
+
+int fail(IcxWorld* w, int code, const std::string& msg) { if (w) w->error = msg; return code; }
+int fail_cuda(IcxWorld* w, cudaError_t e, const char* what)
+{
+    if (w) w->error = std::string(what) + ": " + cudaGetErrorString(e);
+    return ICX_E_CUDA;
+}
+
+template <typename T> cudaError_t alloc(IcxWorld* w, T*& p, size_t count)
+{
+    DeviceBuffer b; cudaError_t e = b.ensure(std::max<size_t>(count, 1) * sizeof(T));
+    if (e != cudaSuccess) return e;
+    w->pool.push_back(b); p = static_cast<T*>(b.ptr);
+    return cudaSuccess;
+}
+
+cudaError_t alloc_state(IcxWorld* w, EntityState& s, size_t n)
+{
+    cudaError_t e;
+    if ((e = alloc(w, s.pos, n))) return e;  if ((e = alloc(w, s.rot, n))) return e;
+    if ((e = alloc(w, s.vel, n))) return e;  if ((e = alloc(w, s.acc, n))) return e;
+    if ((e = alloc(w, s.angvel, n))) return e;  if ((e = alloc(w, s.angacc, n))) return e;
+    return alloc(w, s.ts, n);
+}
+
+uint32_t next_pow2(uint32_t v) { uint32_t p = 1; while (p < v) p <<= 1; return p; }
+
+int allocate(IcxWorld* w)
+{
+    DeviceWorld& W = w->W;
+    const size_t ne = w->cap_entities, np = w->cap_packets;
+    CK(alloc_state(w, W.in, ne)); CK(alloc_state(w, W.out, ne));
+    CK(alloc(w, W.prm0, ne)); CK(alloc(w, W.prm1, ne)); CK(alloc(w, W.locked_pos, ne)); CK(alloc(w, W.locked_rot, ne));
+    CK(alloc(w, W.entity_id, ne)); CK(alloc(w, W.first_packet, ne)); CK(alloc(w, W.pos0, ne));
+    CK(alloc(w, W.pk_entity, np)); CK(alloc(w, W.pk_lpos, np)); CK(alloc(w, W.pk_lrot, np)); CK(alloc(w, W.pk_lscale, np));
+    CK(alloc(w, W.pk_mat0, np)); CK(alloc(w, W.pk_damping, np)); CK(alloc(w, W.pk_minparam, np));
+    CK(alloc(w, W.pk_d, np * 6)); CK(alloc(w, W.pk_lo, np)); CK(alloc(w, W.pk_hi, np)); CK(alloc(w, W.pk_cell, np));
+    W.n_buckets = std::max<uint32_t>(next_pow2((uint32_t)std::min<size_t>(2 * np, 1u << 24)), 1024u);
+    CK(alloc(w, W.cell_count, (size_t)W.n_buckets + 4)); CK(alloc(w, W.cell_fill, (size_t)W.n_buckets));
+    CK(alloc(w, W.scan_partial, 4096 + 8));
+    CK(alloc(w, W.s_lo, np)); CK(alloc(w, W.s_hi, np)); CK(alloc(w, W.pos_of, np));
+    CK(alloc(w, W.large_list, W.max_large));
+    CK(alloc(w, W.nbr, np * (size_t)W.max_neighbors)); CK(alloc(w, W.nbr_count, np));
+    CK(alloc(w, W.head[0], ne)); CK(alloc(w, W.head[1], ne));
+    CK(alloc(w, W.active[0], ne)); CK(alloc(w, W.active[1], ne)); CK(alloc(w, W.ent_active, ne));
+    CK(alloc(w, W.contacts, W.max_contacts)); CK(alloc(w, W.intercepts, W.max_contacts)); CK(alloc(w, W.intercept_key, W.max_contacts));
+    CK(alloc(w, W.counters, CTR_TOTAL)); CK(alloc(w, W.flags, 4));
+    CK(cudaMemset(W.counters, 0, CTR_TOTAL * sizeof(uint32_t))); CK(cudaMemset(W.flags, 0, 16));
+    CK(cudaMallocHost((void**)&w->h_counters, CTR_TOTAL * sizeof(uint32_t)));
+    CK(cudaMallocHost((void**)&w->h_flags, 16));
+    return ICX_OK;
+}
+
+// grow a single pooled array (used by the retry path)
+template <typename T> int regrow(IcxWorld* w, T*& p, size_t count)
+{
+    for (auto& b : w->pool) if (b.ptr == p) { b.release(); CK(b.ensure(count * sizeof(T))); p = static_cast<T*>(b.ptr); return ICX_OK; }
+    return fail(w, ICX_E_STATE, "regrow: buffer not in pool");
+}
+
+Mirror mirror_of(IcxWorld* w)
+{
+    Mirror m;
+    m.ids = (uint32_t*)w->mir_ids.ptr; m.T = (IcxTransform*)w->mir_T.ptr; m.P = (IcxPhysics*)w->mir_P.ptr;
+    m.C = (IcxColliderComponent*)w->mir_C.ptr; m.hasP = (uint8_t*)w->mir_hasP.ptr;
+    return m;
+}
+
+void set_cell(IcxWorld* w, float cell) { w->W.cell_size = cell; w->W.inv_cell = 1.0f / cell; }
+
+// One tick attempt on the stream: integrate+prep, grid, rounds.  Returns the raised RF_* flags.
+int run_tick_once(IcxWorld* w, double dt, int do_euler, int do_collide, uint32_t* raised)
+{
+    DeviceWorld& W = w->W;
+    cudaStream_t st = w->stream;
+    CK(cudaMemsetAsync(W.counters, 0, CTR_TOTAL * sizeof(uint32_t), st));
+    CK(cudaMemsetAsync(W.flags, 0, 16, st));
+    CK(cudaMemsetAsync(W.cell_count, 0, ((size_t)W.n_buckets + 4) * sizeof(uint32_t), st));
+    CK(cudaMemsetAsync(W.cell_fill, 0, (size_t)W.n_buckets * sizeof(uint32_t), st));
+    launch_integrate_prep(W, dt, do_euler, st);
+    uint32_t rounds = 0;
+    *raised = 0;
+    if (do_collide && W.n_packets) {
+        launch_grid(W, st);
+        uint32_t n_threads = W.n_entities;
+        uint32_t ctr_in = CTR_ACTIVE0;
+        int parity = 0;
+        const uint32_t BATCH = 8;
+        bool done = false;
+        while (!done) {
+            if (rounds + BATCH > CTR_MAX_ROUNDS) return fail(w, ICX_E_CAPACITY, "resolve: dependency chain longer than CTR_MAX_ROUNDS");
+            const uint32_t first = rounds;
+            for (uint32_t b = 0; b < BATCH; b++) {
+                const uint32_t ctr_out = CTR_ROUND_BASE + rounds;
+                launch_resolve_round(W, parity, ctr_in, ctr_out, n_threads, st);
+                ctr_in = ctr_out; parity ^= 1; rounds++;
+            }
+            CK(cudaMemcpyAsync(w->h_counters, W.counters, (CTR_ROUND_BASE + rounds) * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+            CK(cudaMemcpyAsync(w->h_flags, W.flags, 16, cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            for (uint32_t r = first; r < rounds; r++)
+                if (w->h_counters[CTR_ROUND_BASE + r] == 0) { done = true; rounds = r + 1; break; }
+            if (w->h_flags[0]) done = true;
+            n_threads = std::min(n_threads, w->h_counters[CTR_ROUND_BASE + rounds - 1]);
+            if (!done && n_threads == 0) done = true;
+        }
+    } else {
+        CK(cudaMemcpyAsync(w->h_counters, W.counters, CTR_ROUND_BASE * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(w->h_flags, W.flags, 16, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+    }
+    CK(cudaGetLastError());
+    *raised = w->h_flags[0];
+    w->stats.n_rounds = rounds;
+    return ICX_OK;
+}
+
+int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_coherency)
+{
+    DeviceWorld& W = w->W;
+    for (int attempt = 0; attempt < 24; attempt++) {
+        uint32_t raised = 0;
+        int rc = run_tick_once(w, dt, do_euler, do_collide, &raised);
+        if (rc != ICX_OK) return rc;
+        if (!do_collide) raised &= ~(RF_CELL_TOO_SMALL | RF_LARGE_OVERFLOW);
+        if (raised == 0) {
+            std::swap(W.in, W.out);
+            if (advance_coherency) W.coherency = (uint16_t)(W.coherency + 1);
+            w->stats.ticks++;
+            w->stats.n_large = std::min(w->h_counters[CTR_LARGE], W.max_large);
+            w->stats.n_candidates = w->h_counters[CTR_CANDIDATES];
+            w->stats.n_contacts = w->h_counters[CTR_CONTACTS];
+            w->stats.n_interceptions = w->h_counters[CTR_INTERCEPTS];
+            w->stats.margin = W.margin; w->stats.cell_size = W.cell_size; w->stats.max_neighbors = W.max_neighbors;
+            w->have_results = do_collide != 0;
+            return ICX_OK;
+        }
+        // `in` is untouched: adjust the capacity / margin that was exceeded and run the tick again
+        w->stats.n_retries++;
+        if (raised & RF_CLIP_OVERFLOW) return fail(w, ICX_E_CAPACITY, "clipped manifold exceeded ICX_MAXV");
+        if (raised & RF_NEIGHBOR_OVERFLOW) {
+            if (W.max_neighbors >= 96) return fail(w, ICX_E_CAPACITY, "candidate list exceeded 96 neighbours per collider");
+            W.max_neighbors = std::min<uint32_t>(W.max_neighbors * 2, 96);
+            rc = regrow(w, W.nbr, (size_t)w->cap_packets * W.max_neighbors); if (rc) return rc;
+        }
+        if (raised & RF_MARGIN_VIOLATED) {
+            const float old = W.margin;
+            W.margin = old * 2.0f;
+            if (W.margin > 1.0e6f) return fail(w, ICX_E_CAPACITY, "broadphase margin diverged");
+            set_cell(w, W.cell_size + 2.0f * (W.margin - old));
+        }
+        if (raised & RF_CELL_TOO_SMALL) {
+            float need; std::memcpy(&need, &w->h_counters[CTR_ROUND_BASE - 1], 4);
+            set_cell(w, std::max(need, W.cell_size) * 1.05f);
+        }
+        if (raised & RF_CONTACT_OVERFLOW) {
+            W.max_contacts *= 2;
+            rc = regrow(w, W.contacts, W.max_contacts); if (rc) return rc;
+            rc = regrow(w, W.intercepts, W.max_contacts); if (rc) return rc;
+            rc = regrow(w, W.intercept_key, W.max_contacts); if (rc) return rc;
+        }
+        if (raised & RF_LARGE_OVERFLOW) {
+            W.max_large *= 2;
+            rc = regrow(w, W.large_list, W.max_large); if (rc) return rc;
+        }
+    }
+    return fail(w, ICX_E_CAPACITY, "tick did not converge after 24 capacity/margin retries");
+}
+
+} // namespace
+
+extern "C" {
+
+int icx_abi_version(void) { return ICX_ABI_VERSION; }
+
+int icx_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+const char* icx_status_string(int status)
+{
+    switch (status) {
+    case ICX_OK: return "ok";
+    case ICX_E_INVALID: return "invalid argument";
+    case ICX_E_CUDA: return "CUDA error";
+    case ICX_E_CAPACITY: return "capacity exceeded";
+    case ICX_E_NOMEM: return "out of memory";
+    case ICX_E_STATE: return "wrong state for this call";
+    default: return "unknown status";
+    }
+}
+
+void icx_config_default(IcxConfig* cfg)
+{
+    if (!cfg) return;
+    std::memset(cfg, 0, sizeof(*cfg));
+    cfg->struct_size = sizeof(IcxConfig);
+    cfg->max_entities = 1u << 16;
+    cfg->host_timeslice = 0;
+    cfg->gravity[0] = 0.0f; cfg->gravity[1] = -10.0f; cfg->gravity[2] = 0.0f;     // euler_physics_relay.h:32
+}
+
+int icx_world_create(const IcxConfig* cfg, IcxWorld** out)
+{
+    if (!cfg || !out || cfg->struct_size != sizeof(IcxConfig) || cfg->max_entities == 0 || cfg->max_entities > (1u << 27))
+        return ICX_E_INVALID;
+    *out = nullptr;
+    if (icx_device_count() <= cfg->device) return ICX_E_CUDA;      // no CPU fallback
+    IcxWorld* w = new (std::nothrow) IcxWorld();
+    if (!w) return ICX_E_NOMEM;
+    w->cfg = *cfg; w->device = cfg->device;
+    std::memset(&w->W, 0, sizeof(w->W)); std::memset(&w->stats, 0, sizeof(w->stats));
+    int rc = ICX_OK;
+    do {
+        if (cudaSetDevice(w->device) != cudaSuccess) { rc = ICX_E_CUDA; break; }
+        if (cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking) != cudaSuccess) { rc = ICX_E_CUDA; break; }
+        cudaEventCreate(&w->ev0); cudaEventCreate(&w->ev1);
+        DeviceWorld& W = w->W;
+        w->cap_entities = cfg->max_entities; w->cap_packets = 2 * cfg->max_entities;
+        W.margin = cfg->broadphase_margin > 0 ? cfg->broadphase_margin : 0.05f;
+        set_cell(w, cfg->cell_size > 0 ? cfg->cell_size : 1.0f);
+        W.max_neighbors = cfg->max_neighbors ? std::min<uint32_t>(cfg->max_neighbors, 96) : 24;
+        W.max_large = cfg->max_large ? cfg->max_large : 1024;
+        W.max_contacts = cfg->max_contacts ? cfg->max_contacts : std::max<uint32_t>(2 * cfg->max_entities, 1024);
+        W.gx = (cfg->flags & ICX_F_NO_GRAVITY) ? 0.0f : cfg->gravity[0];
+        W.gy = (cfg->flags & ICX_F_NO_GRAVITY) ? 0.0f : cfg->gravity[1];
+        W.gz = (cfg->flags & ICX_F_NO_GRAVITY) ? 0.0f : cfg->gravity[2];
+        W.host_timeslice = cfg->host_timeslice; W.cfg_flags = cfg->flags; W.worldline_stride = cfg->worldline_stride;
+        rc = allocate(w);
+    } while (0);
+    if (rc != ICX_OK) { icx_world_destroy(w); return rc; }
+    *out = w;
+    return ICX_OK;
+}
+
+void icx_world_destroy(IcxWorld* w)
+{
+    if (!w) return;
+    cudaSetDevice(w->device);
+    if (w->stream) cudaStreamSynchronize(w->stream);
+    for (auto& b : w->pool) b.release();
+    DeviceBuffer* extra[] = {&w->mir_ids, &w->mir_T, &w->mir_P, &w->mir_C, &w->mir_hasP, &w->st_ts, &w->st_tc, &w->st_index, &w->st_T, &w->st_P, &w->st_C};
+    for (auto* b : extra) b->release();
+    if (w->h_counters) cudaFreeHost(w->h_counters);
+    if (w->h_flags) cudaFreeHost(w->h_flags);
+    if (w->ev0) cudaEventDestroy(w->ev0);
+    if (w->ev1) cudaEventDestroy(w->ev1);
+    if (w->stream) cudaStreamDestroy(w->stream);
+    delete w;
+}
+
+const char* icx_last_error(const IcxWorld* w) { return w ? w->error.c_str() : "null world"; }
+
+int icx_bodies_upload(IcxWorld* w, uint32_t n, const IcxEntity* entity, const IcxTransform* T, const IcxPhysics* P,
+                      const uint8_t* has_physics, const IcxColliderComponent* C, const uint8_t* tstate, const uint16_t* tcoh)
+{
+    if (!w) return ICX_E_INVALID;
+    if (!entity || !T || n > w->cap_entities) return fail(w, ICX_E_INVALID, "upload: null ids/transforms or n > max_entities");
+    cudaSetDevice(w->device);
+    DeviceWorld& W = w->W;
+    cudaStream_t st = w->stream;
+    // packet structure = ColliderSynchro::update's submission order (collider_synchro.cpp:28-42)
+    std::vector<uint32_t> first(n);
+    w->active_mask.assign(n, 0);
+    uint32_t np = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        uint32_t cnt = 0;
+        if (C) for (int s = 0; s < ICX_COLLIDERS_PER_ENTITY; s++) if (C[i].colliders[s].isActive) { cnt++; w->active_mask[i] |= (uint8_t)(1u << s); }
+        first[i] = np | (cnt << 30);
+        np += cnt;
+    }
+    if (np > w->cap_packets || np >= (1u << 28)) return fail(w, ICX_E_CAPACITY, "upload: too many active colliders");
+    CK(w->mir_ids.ensure((size_t)w->cap_entities * 4)); CK(w->mir_T.ensure((size_t)w->cap_entities * sizeof(IcxTransform)));
+    CK(w->mir_hasP.ensure(w->cap_entities));
+    if (P) CK(w->mir_P.ensure((size_t)w->cap_entities * sizeof(IcxPhysics)));
+    if (C) CK(w->mir_C.ensure((size_t)w->cap_entities * sizeof(IcxColliderComponent)));
+    CK(w->st_ts.ensure(w->cap_entities)); CK(w->st_tc.ensure((size_t)w->cap_entities * 2));
+    w->have_P = P != nullptr; w->have_C = C != nullptr;
+    CK(cudaMemcpyAsync(w->mir_ids.ptr, entity, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(w->mir_T.ptr, T, (size_t)n * sizeof(IcxTransform), cudaMemcpyHostToDevice, st));
+    if (P) CK(cudaMemcpyAsync(w->mir_P.ptr, P, (size_t)n * sizeof(IcxPhysics), cudaMemcpyHostToDevice, st));
+    if (C) CK(cudaMemcpyAsync(w->mir_C.ptr, C, (size_t)n * sizeof(IcxColliderComponent), cudaMemcpyHostToDevice, st));
+    if (has_physics) CK(cudaMemcpyAsync(w->mir_hasP.ptr, has_physics, n, cudaMemcpyHostToDevice, st));
+    if (tstate) CK(cudaMemcpyAsync(w->st_ts.ptr, tstate, n, cudaMemcpyHostToDevice, st));
+    if (tcoh) CK(cudaMemcpyAsync(w->st_tc.ptr, tcoh, (size_t)n * 2, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(W.first_packet, first.data(), (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    CK(cudaMemsetAsync(W.counters, 0, CTR_ROUND_BASE * sizeof(uint32_t), st));
+    W.n_entities = n; W.n_packets = np; w->n_entities = n; w->n_packets = np;
+    Mirror M = mirror_of(w);
+    if (!P) M.P = nullptr;
+    launch_import_kernel(W, M, nullptr, M.ids, M.T, M.P, C ? M.C : nullptr,
+                         has_physics ? M.hasP : nullptr, tstate ? (const uint8_t*)w->st_ts.ptr : nullptr,
+                         tcoh ? (const uint16_t*)w->st_tc.ptr : nullptr, n, 1, C ? 1 : 0, st);
+    CK(cudaMemcpyAsync(w->h_counters, W.counters, CTR_ROUND_BASE * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));          // `first` and the caller's arrays may be released after return
+    CK(cudaGetLastError());
+    if (!(w->cfg.cell_size > 0)) {
+        float ext; std::memcpy(&ext, &w->h_counters[CTR_ROUND_BASE - 2], 4);
+        if (!(ext > 0)) ext = 1.0f;
+        set_cell(w, (ext + 2.0f * W.margin) * 1.02f);
+    }
+    w->stats.n_entities = n; w->stats.n_packets = np;
+    w->have_results = false;
+    return ICX_OK;
+}
+
+int icx_bodies_download(IcxWorld* w, uint32_t n, IcxTransform* T, IcxPhysics* P, IcxColliderComponent* C, uint8_t* tstate, uint16_t* tcoh)
+{
+    if (!w) return ICX_E_INVALID;
+    if (n != w->n_entities) return fail(w, ICX_E_INVALID, "download: n differs from the uploaded entity count");
+    if ((P && !w->have_P) || (C && !w->have_C)) return fail(w, ICX_E_STATE, "download: component was never uploaded");
+    cudaSetDevice(w->device);
+    cudaStream_t st = w->stream;
+    launch_export_kernel(w->W, mirror_of(w), T != nullptr, P != nullptr, C != nullptr,
+                         tstate ? (uint8_t*)w->st_ts.ptr : nullptr, tcoh ? (uint16_t*)w->st_tc.ptr : nullptr, n, st);
+    if (T) CK(cudaMemcpyAsync(T, w->mir_T.ptr, (size_t)n * sizeof(IcxTransform), cudaMemcpyDeviceToHost, st));
+    if (P) CK(cudaMemcpyAsync(P, w->mir_P.ptr, (size_t)n * sizeof(IcxPhysics), cudaMemcpyDeviceToHost, st));
+    if (C) CK(cudaMemcpyAsync(C, w->mir_C.ptr, (size_t)n * sizeof(IcxColliderComponent), cudaMemcpyDeviceToHost, st));
+    if (tstate) CK(cudaMemcpyAsync(tstate, w->st_ts.ptr, n, cudaMemcpyDeviceToHost, st));
+    if (tcoh) CK(cudaMemcpyAsync(tcoh, w->st_tc.ptr, (size_t)n * 2, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    return ICX_OK;
+}
+
+int icx_bodies_update(IcxWorld* w, uint32_t count, const uint32_t* index, const IcxTransform* T, const IcxPhysics* P, const IcxColliderComponent* C)
+{
+    if (!w) return ICX_E_INVALID;
+    if (!index && count) return fail(w, ICX_E_INVALID, "update: null index");
+    if ((P && !w->have_P) || (C && !w->have_C)) return fail(w, ICX_E_STATE, "update: component was never uploaded");
+    if (!count) return ICX_OK;
+    for (uint32_t i = 0; i < count; i++) {
+        if (index[i] >= w->n_entities) return fail(w, ICX_E_INVALID, "update: index out of range");
+        if (C) {
+            uint8_t m = 0;
+            for (int s = 0; s < ICX_COLLIDERS_PER_ENTITY; s++) if (C[i].colliders[s].isActive) m |= (uint8_t)(1u << s);
+            if (m != w->active_mask[index[i]]) return fail(w, ICX_E_STATE, "update: collider activation changed; call icx_bodies_upload");
+        }
+    }
+    cudaSetDevice(w->device);
+    cudaStream_t st = w->stream;
+    CK(w->st_index.ensure((size_t)count * 4));
+    CK(cudaMemcpyAsync(w->st_index.ptr, index, (size_t)count * 4, cudaMemcpyHostToDevice, st));
+    if (T) { CK(w->st_T.ensure((size_t)count * sizeof(IcxTransform))); CK(cudaMemcpyAsync(w->st_T.ptr, T, (size_t)count * sizeof(IcxTransform), cudaMemcpyHostToDevice, st)); }
+    if (P) { CK(w->st_P.ensure((size_t)count * sizeof(IcxPhysics))); CK(cudaMemcpyAsync(w->st_P.ptr, P, (size_t)count * sizeof(IcxPhysics), cudaMemcpyHostToDevice, st)); }
+    if (C) { CK(w->st_C.ensure((size_t)count * sizeof(IcxColliderComponent))); CK(cudaMemcpyAsync(w->st_C.ptr, C, (size_t)count * sizeof(IcxColliderComponent), cudaMemcpyHostToDevice, st)); }
+    Mirror M = mirror_of(w);
+    if (!w->have_P) M.P = nullptr;
+    launch_import_kernel(w->W, M, (const uint32_t*)w->st_index.ptr, nullptr, T ? (const IcxTransform*)w->st_T.ptr : nullptr,
+                         P ? (const IcxPhysics*)w->st_P.ptr : nullptr, C ? (const IcxColliderComponent*)w->st_C.ptr : nullptr,
+                         nullptr, nullptr, nullptr, count, 0, w->have_C ? 1 : 0, st);
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    return ICX_OK;
+}
+
+int icx_coherency_set(IcxWorld* w, uint16_t c) { if (!w) return ICX_E_INVALID; w->W.coherency = c; return ICX_OK; }
+int icx_coherency_get(IcxWorld* w, uint16_t* c) { if (!w || !c) return ICX_E_INVALID; *c = w->W.coherency; return ICX_OK; }
+
+static int timed_ticks(IcxWorld* w, double dt, uint32_t n_ticks, int do_euler, int do_collide, bool advance)
+{
+    if (!w) return ICX_E_INVALID;
+    cudaSetDevice(w->device);
+    cudaEventRecord(w->ev0, w->stream);
+    for (uint32_t t = 0; t < n_ticks; t++) { int rc = run_tick(w, dt, do_euler, do_collide, advance); if (rc != ICX_OK) return rc; }
+    cudaEventRecord(w->ev1, w->stream);
+    cudaEventSynchronize(w->ev1);
+    cudaEventElapsedTime(&w->last_ms, w->ev0, w->ev1);
+    return ICX_OK;
+}
+
+int icx_step(IcxWorld* w, double dt) { return timed_ticks(w, dt, 1, 1, 1, true); }
+int icx_step_n(IcxWorld* w, double dt, uint32_t n_ticks) { return timed_ticks(w, dt, n_ticks, 1, 1, true); }
+int icx_euler_engage(IcxWorld* w, double dt) { return timed_ticks(w, dt, 1, 1, 0, false); }
+int icx_collision_engage(IcxWorld* w) { return timed_ticks(w, 0.0, 1, 0, 1, false); }
+
+int icx_sync(IcxWorld* w)
+{
+    if (!w) return ICX_E_INVALID;
+    cudaSetDevice(w->device);
+    CK(cudaStreamSynchronize(w->stream));
+    CK(cudaGetLastError());
+    return ICX_OK;
+}
+
+int icx_last_step_ms(IcxWorld* w, float* ms) { if (!w || !ms) return ICX_E_INVALID; *ms = w->last_ms; return ICX_OK; }
+void* icx_world_stream(IcxWorld* w) { return w ? (void*)w->stream : nullptr; }
+
+int icx_stats_fetch(IcxWorld* w, IcxStats* out) { if (!w || !out) return ICX_E_INVALID; *out = w->stats; return ICX_OK; }
+
+int icx_contacts_fetch(IcxWorld* w, IcxContact* out, size_t cap, size_t* n)
+{
+    if (!w || !n) return ICX_E_INVALID;
+    if (!w->have_results) { *n = 0; return ICX_OK; }
+    const size_t total = w->stats.n_contacts;
+    *n = total;
+    if (!out || !total) return ICX_OK;
+    cudaSetDevice(w->device);
+    std::vector<IcxContact> tmp(total);
+    CK(cudaMemcpyAsync(tmp.data(), w->W.contacts, total * sizeof(IcxContact), cudaMemcpyDeviceToHost, w->stream));
+    CK(cudaStreamSynchronize(w->stream));
+    // the rounds emit hits out of order; the reference's order is lexicographic on the packet pair
+    std::sort(tmp.begin(), tmp.end(), [](const IcxContact& a, const IcxContact& b) {
+        return a.packetA < b.packetA || (a.packetA == b.packetA && a.packetB < b.packetB); });
+    std::memcpy(out, tmp.data(), std::min(cap, total) * sizeof(IcxContact));
+    return ICX_OK;
+}
+
+int icx_interceptions_fetch(IcxWorld* w, IcxInterception* out, size_t cap, size_t* n)
+{
+    if (!w || !n) return ICX_E_INVALID;
+    if (!w->have_results) { *n = 0; return ICX_OK; }
+    const size_t total = w->stats.n_interceptions;
+    *n = total;
+    if (!out || !total) return ICX_OK;
+    cudaSetDevice(w->device);
+    std::vector<IcxInterception> ev(total); std::vector<uint2> key(total);
+    CK(cudaMemcpyAsync(ev.data(), w->W.intercepts, total * sizeof(IcxInterception), cudaMemcpyDeviceToHost, w->stream));
+    CK(cudaMemcpyAsync(key.data(), w->W.intercept_key, total * sizeof(uint2), cudaMemcpyDeviceToHost, w->stream));
+    CK(cudaStreamSynchronize(w->stream));
+    std::vector<uint32_t> order(total);
+    for (size_t i = 0; i < total; i++) order[i] = (uint32_t)i;
+    std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
+        return key[a].x < key[b].x || (key[a].x == key[b].x && key[a].y < key[b].y); });
+    for (size_t i = 0; i < std::min(cap, total); i++) out[i] = ev[order[i]];
+    return ICX_OK;
+}
+
+int icx_pairs_fetch(IcxWorld* w, IcxPair* out, size_t cap, size_t* n)
+{
+    if (!w || !n) return ICX_E_INVALID;
+    if (!w->have_results) { *n = 0; return ICX_OK; }
+    cudaSetDevice(w->device);
+    const DeviceWorld& W = w->W;
+    const uint32_t np = W.n_packets;
+    std::vector<uint32_t> pos_of(np), cnt(np), nbr((size_t)np * W.max_neighbors);
+    CK(cudaMemcpyAsync(pos_of.data(), W.pos_of, (size_t)np * 4, cudaMemcpyDeviceToHost, w->stream));
+    CK(cudaMemcpyAsync(cnt.data(), W.nbr_count, (size_t)np * 4, cudaMemcpyDeviceToHost, w->stream));
+    CK(cudaMemcpyAsync(nbr.data(), W.nbr, nbr.size() * 4, cudaMemcpyDeviceToHost, w->stream));
+    CK(cudaStreamSynchronize(w->stream));
+    std::vector<uint64_t> keys;
+    for (uint32_t p = 0; p < np; p++) {
+        const uint32_t col = pos_of[p];
+        if (col == 0xFFFFFFFFu) continue;
+        for (uint32_t i = 0; i < cnt[col]; i++) {
+            const uint32_t o = nbr[(size_t)i * np + col] & ICX_NB_INDEX_MASK;
+            keys.push_back(((uint64_t)std::min(p, o) << 32) | std::max(p, o));
+        }
+    }
+    std::sort(keys.begin(), keys.end());
+    keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
+    *n = keys.size();
+    if (out) for (size_t i = 0; i < std::min(cap, keys.size()); i++) { out[i].a = (uint32_t)(keys[i] >> 32); out[i].b = (uint32_t)keys[i]; }
+    return ICX_OK;
+}
+
+} // extern "C"

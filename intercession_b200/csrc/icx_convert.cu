@@ -1,0 +1,173 @@
+// AoS <-> SoA boundary kernels.  The caller's arrays are the reference's own component structs
+// (TransformComponent 40 B, PhysicsComponent 108 B, ColliderComponent 168 B); a device-resident
+// AoS mirror keeps their constant fields so a download can hand back complete structs.
+#include "icx_world.cuh"
+#include "icx_host.h"
+#include "icx_math.cuh"
+
+namespace icx {
+
+// immutable <=> nothing CollisionPhysicsRelay::engage does can change the entity:
+// non-temporal (no interception), no ray collider (minParametricValue), and either no
+// PhysicsComponent (responses are skipped, relay :84-106) or infinite mass with an angular
+// velocity the response cannot touch.
+__device__ __forceinline__ bool is_immutable(uint32_t id, bool hasP, const IcxPhysics* P, const IcxColliderComponent* C)
+{
+    if ((id & 0xFu) != ICX_NULL_CHAINLINK) return false;
+    bool influence = false;
+    if (C) for (int s = 0; s < ICX_COLLIDERS_PER_ENTITY; s++) {
+        const IcxCollider& c = C->colliders[s];
+        if (!c.isActive) continue;
+        if (c.colliderType == ICX_COLLIDER_RAY) return false;
+        influence |= c.influenceOrientation != 0;
+    }
+    if (!hasP) return true;
+    if (P->mass != 0.0f) return false;
+    return P->lockOrientation || !influence;
+}
+
+// One thread per listed entity.  src_* (optional) are compact arrays indexed by i and are first
+// copied into the mirror at e = index ? index[i] : i; the SoA parts fed by each given array are
+// then rebuilt.  full != 0: every SoA part is rebuilt (first upload).
+__global__ void __launch_bounds__(128) k_import(DeviceWorld W, Mirror M, const uint32_t* __restrict__ index,
+                                                const uint32_t* src_ids, const IcxTransform* src_T, const IcxPhysics* src_P,
+                                                const IcxColliderComponent* src_C, const uint8_t* src_hasP,
+                                                const uint8_t* src_ts, const uint16_t* src_tc,
+                                                uint32_t count, int full, int have_C)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const uint32_t e = index ? index[i] : i;
+    if (src_ids && src_ids != M.ids) M.ids[e] = src_ids[i];
+    if (src_T && src_T != M.T) M.T[e] = src_T[i];
+    if (src_P && src_P != M.P) M.P[e] = src_P[i];
+    if (src_C && src_C != M.C) M.C[e] = src_C[i];
+    if (full) M.hasP[e] = src_hasP ? src_hasP[i] : (uint8_t)(M.P != nullptr);
+    const bool hasP = M.hasP[e] != 0;
+    const uint32_t id = M.ids[e];
+    const IcxPhysics* P = hasP ? &M.P[e] : nullptr;
+    const IcxColliderComponent* C = have_C ? &M.C[e] : nullptr;
+
+    if (full) {
+        W.entity_id[e] = id;
+        const uint32_t st = src_ts ? src_ts[i] : 0u, tc = src_tc ? src_tc[i] : 0u;
+        W.in.ts[e] = st | (tc << 16);
+    }
+    if (full || src_T) {
+        const IcxTransform& t = M.T[e];
+        W.in.pos[e] = make_float4(t.origin[0], t.origin[1], t.origin[2], 0.0f);
+        W.in.rot[e] = make_float4(t.orientation[0], t.orientation[1], t.orientation[2], t.orientation[3]);
+    }
+    if (full || src_P) {
+        if (hasP) {
+            W.in.vel[e] = make_float4(P->velocity[0], P->velocity[1], P->velocity[2], 0.0f);
+            W.in.acc[e] = make_float4(P->acceleration[0], P->acceleration[1], P->acceleration[2], 0.0f);
+            W.in.angvel[e] = make_float4(P->angularVelocity[0], P->angularVelocity[1], P->angularVelocity[2], 0.0f);
+            W.in.angacc[e] = make_float4(P->angularAcceleration[0], P->angularAcceleration[1], P->angularAcceleration[2], 0.0f);
+            W.locked_pos[e] = make_float4(P->lockedOrigin[0], P->lockedOrigin[1], P->lockedOrigin[2], 0.0f);
+            W.locked_rot[e] = make_float4(P->lockedOrientation[0], P->lockedOrientation[1], P->lockedOrientation[2], P->lockedOrientation[3]);
+        } else {
+            const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            W.in.vel[e] = z; W.in.acc[e] = z; W.in.angvel[e] = z; W.in.angacc[e] = z;
+        }
+    }
+    // constants that mix several components are always refreshed
+    {
+        const IcxTransform& t = M.T[e];
+        W.prm0[e] = make_float4(t.scale[0], t.scale[1], t.scale[2], hasP ? P->mass : 0.0f);
+        uint32_t ef = 0;
+        if (hasP) {
+            ef |= EF_HAS_PHYSICS;
+            if (P->lockOrigin) ef |= EF_LOCK_ORIGIN;
+            if (P->lockOrientation) ef |= EF_LOCK_ORIENTATION;
+            if (P->isAsleep) ef |= EF_ASLEEP;
+        }
+        if (is_immutable(id, hasP, P, C)) ef |= EF_IMMUTABLE;
+        W.prm1[e] = make_float4(hasP ? P->linearDrag : 0.0f, hasP ? P->angularDrag : 0.0f,
+                                hasP ? P->collisionAngularDrag : 0.0f, __uint_as_float(ef));
+        // colliders
+        const uint32_t fp = W.first_packet[e];
+        const uint32_t npk = fp >> 30, p0 = fp & 0x3FFFFFFFu;
+        if (C && npk && (full || src_C || src_T)) {
+            uint32_t k = 0;
+            for (int s = 0; s < ICX_COLLIDERS_PER_ENTITY; s++) {
+                const IcxCollider& c = C->colliders[s];
+                if (!c.isActive) continue;
+                const uint32_t p = p0 + k; k++;
+                uint32_t bits = ((uint32_t)c.colliderType & PF_TYPE_MASK) | (((uint32_t)c.collisionType & 3u) << PF_CTYPE_SHIFT);
+                if (c.useBehaviorsResponse) bits |= PF_BEHAVIORS;
+                if (c.inheritOrientation) bits |= PF_INHERIT_ORIENT;
+                if (c.influenceOrientation) bits |= PF_INFLUENCE_ORIENT;
+                if (s == 1) bits |= PF_SLOT;
+                const IcxTransform& l = c.localTransform;
+                W.pk_entity[p] = e;
+                W.pk_lpos[p] = make_float4(l.origin[0], l.origin[1], l.origin[2], __uint_as_float(bits));
+                W.pk_lrot[p] = make_float4(l.orientation[0], l.orientation[1], l.orientation[2], l.orientation[3]);
+                W.pk_lscale[p] = make_float4(l.scale[0], l.scale[1], l.scale[2], c.restLength);
+                W.pk_mat0[p] = make_float4(c.staticFriction, c.dynamicFriction, c.restitution, c.stiffness);
+                W.pk_damping[p] = c.damping;
+                W.pk_minparam[p] = c.minParametricValue;
+                // rotation-invariant extent estimate of mutable colliders -> initial grid cell size
+                if (!(ef & EF_IMMUTABLE) && c.colliderType != ICX_COLLIDER_NONE) {
+                    const float sx = fabsf(t.scale[0] * l.scale[0]), sy = fabsf(t.scale[1] * l.scale[1]), sz = fabsf(t.scale[2] * l.scale[2]);
+                    float ext;
+                    if (c.colliderType == ICX_COLLIDER_SPHERE) ext = 1.7320509f * sx;
+                    else if (c.colliderType == ICX_COLLIDER_RAY) ext = sz * 1.000001f;
+                    else ext = sqrtf(sx * sx + sy * sy + sz * sz);
+                    if (ext == ext) atomicMax((int*)&W.counters[CTR_ROUND_BASE - 2], __float_as_int(ext));
+                }
+            }
+        }
+    }
+}
+
+// Patch the mutable fields of the mirror from the current state, then the host copies it out.
+__global__ void __launch_bounds__(128) k_export(DeviceWorld W, Mirror M, int have_T, int have_P, int have_C,
+                                                uint8_t* ts_out, uint16_t* tc_out, uint32_t n)
+{
+    const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    if (have_T) {
+        const float4 p = W.in.pos[e], r = W.in.rot[e];
+        IcxTransform& t = M.T[e];
+        t.origin[0] = p.x; t.origin[1] = p.y; t.origin[2] = p.z;
+        t.orientation[0] = r.x; t.orientation[1] = r.y; t.orientation[2] = r.z; t.orientation[3] = r.w;
+    }
+    if (have_P && M.hasP[e]) {
+        const float4 v = W.in.vel[e], a = W.in.acc[e], w = W.in.angvel[e], al = W.in.angacc[e];
+        IcxPhysics& P = M.P[e];
+        P.velocity[0] = v.x; P.velocity[1] = v.y; P.velocity[2] = v.z;
+        P.acceleration[0] = a.x; P.acceleration[1] = a.y; P.acceleration[2] = a.z;
+        P.angularVelocity[0] = w.x; P.angularVelocity[1] = w.y; P.angularVelocity[2] = w.z;
+        P.angularAcceleration[0] = al.x; P.angularAcceleration[1] = al.y; P.angularAcceleration[2] = al.z;
+    }
+    if (have_C) {
+        const uint32_t fp = W.first_packet[e];
+        const uint32_t npk = fp >> 30, p0 = fp & 0x3FFFFFFFu;
+        uint32_t k = 0;
+        for (int s = 0; s < ICX_COLLIDERS_PER_ENTITY && k < npk; s++) {
+            IcxCollider& c = M.C[e].colliders[s];
+            if (!c.isActive) continue;
+            c.minParametricValue = W.pk_minparam[p0 + k]; k++;
+        }
+    }
+    const uint32_t ts = W.in.ts[e];
+    if (ts_out) ts_out[e] = (uint8_t)(ts & 0xFFu);
+    if (tc_out) tc_out[e] = (uint16_t)(ts >> 16);
+}
+
+void launch_import_kernel(const DeviceWorld& W, Mirror M, const uint32_t* index, const uint32_t* ids, const IcxTransform* T,
+                          const IcxPhysics* P, const IcxColliderComponent* C, const uint8_t* hasP, const uint8_t* ts,
+                          const uint16_t* tc, uint32_t count, int full, int have_C, cudaStream_t st)
+{
+    if (!count) return;
+    k_import<<<(count + 127) / 128, 128, 0, st>>>(W, M, index, ids, T, P, C, hasP, ts, tc, count, full, have_C);
+}
+void launch_export_kernel(const DeviceWorld& W, Mirror M, int have_T, int have_P, int have_C, uint8_t* ts, uint16_t* tc,
+                          uint32_t n, cudaStream_t st)
+{
+    if (!n) return;
+    k_export<<<(n + 127) / 128, 128, 0, st>>>(W, M, have_T, have_P, have_C, ts, tc, n);
+}
+
+} // namespace icx

@@ -1,0 +1,56 @@
+// Host-side world object behind the C ABI (include/icx.h).  Not part of the ABI.
+#pragma once
+#include <cuda_runtime.h>
+#include <string>
+#include <vector>
+#include "icx_world.cuh"
+
+namespace icx {
+
+// launchers implemented in the .cu translation units
+void launch_integrate_prep(const DeviceWorld& W, double dt, int do_euler, cudaStream_t st);
+void launch_grid(const DeviceWorld& W, cudaStream_t st);
+void launch_resolve_round(const DeviceWorld& W, int parity, uint32_t ctr_in, uint32_t ctr_out, uint32_t n_threads, cudaStream_t st);
+struct Mirror { uint32_t* ids; IcxTransform* T; IcxPhysics* P; IcxColliderComponent* C; uint8_t* hasP; };
+void launch_import_kernel(const DeviceWorld& W, Mirror M, const uint32_t* index, const uint32_t* ids, const IcxTransform* T,
+                          const IcxPhysics* P, const IcxColliderComponent* C, const uint8_t* hasP, const uint8_t* ts,
+                          const uint16_t* tc, uint32_t count, int full, int have_C, cudaStream_t st);
+void launch_export_kernel(const DeviceWorld& W, Mirror M, int have_T, int have_P, int have_C, uint8_t* ts, uint16_t* tc,
+                          uint32_t n, cudaStream_t st);
+
+struct DeviceBuffer {
+    void* ptr = nullptr; size_t bytes = 0;
+    cudaError_t ensure(size_t n) {
+        if (n <= bytes) return cudaSuccess;
+        if (ptr) cudaFree(ptr);
+        ptr = nullptr; bytes = 0;
+        cudaError_t e = cudaMalloc(&ptr, n);
+        if (e == cudaSuccess) bytes = n;
+        return e;
+    }
+    void release() { if (ptr) cudaFree(ptr); ptr = nullptr; bytes = 0; }
+};
+
+} // namespace icx
+
+struct IcxWorld {
+    IcxConfig cfg;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    icx::DeviceWorld W;                 // device pointers + parameters (in/out already oriented)
+    std::vector<icx::DeviceBuffer> pool;
+    uint32_t cap_entities = 0, cap_packets = 0;
+    uint32_t n_entities = 0, n_packets = 0;
+    std::vector<uint8_t> active_mask;   // per entity: bit s = collider slot s active (packet structure)
+    // staging (device) for AoS import/export, pinned host mirror for counters
+    icx::DeviceBuffer mir_ids, mir_T, mir_P, mir_C, mir_hasP;       // device AoS mirror
+    icx::DeviceBuffer st_ts, st_tc, st_index, st_T, st_P, st_C;      // staging for tstate and partial updates
+    bool have_P = false, have_C = false;
+    uint32_t* h_counters = nullptr;     // pinned
+    uint32_t* h_flags = nullptr;        // pinned
+    IcxStats stats;
+    float last_ms = 0.0f;
+    std::string error;
+    bool have_results = false;
+};

@@ -1,0 +1,114 @@
+// Device-resident world state (SoA) and the parameter block every kernel receives by value.
+// Layout rationale: DESIGN.md "Data layout in HBM".  All per-entity / per-packet arrays are
+// float4/uint4-granular so each thread moves 128-bit words and a warp moves 512 contiguous bytes.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/icx.h"
+
+namespace icx {
+
+// entity flag bits (EntityConst::flags)
+enum : uint32_t {
+    EF_HAS_PHYSICS      = 1u << 0,
+    EF_LOCK_ORIGIN      = 1u << 1,
+    EF_LOCK_ORIENTATION = 1u << 2,
+    EF_ASLEEP           = 1u << 3,
+    EF_IMMUTABLE        = 1u << 4,   // no collision response can change it (see is_immutable)
+    EF_HAS_RAY          = 1u << 5,
+};
+// packet flag bits (packed in PacketDerived::bits together with the two type enums)
+enum : uint32_t {
+    PF_TYPE_MASK        = 0x3u,          // ICX_COLLIDER_*
+    PF_CTYPE_SHIFT      = 2,             // ICX_COLLISION_* in bits 2..3
+    PF_BEHAVIORS        = 1u << 4,
+    PF_INHERIT_ORIENT   = 1u << 5,
+    PF_INFLUENCE_ORIENT = 1u << 6,
+    PF_LARGE            = 1u << 7,
+    PF_IMMUTABLE        = 1u << 8,
+    PF_SLOT             = 1u << 9,
+};
+
+// neighbour-list entry: other packet index in the low 28 bits, then
+#define ICX_NB_INDEX_MASK 0x0FFFFFFFu
+#define ICX_NB_IMMUTABLE  0x10000000u     // other packet's entity is immutable
+#define ICX_NB_LARGE      0x20000000u     // other packet is in the large-collider list
+
+// error / retry flags raised by kernels (World::d_flags)
+enum : uint32_t {
+    RF_NEIGHBOR_OVERFLOW = 1u << 0,   // a candidate list exceeded max_neighbors
+    RF_MARGIN_VIOLATED   = 1u << 1,   // static resolution moved a body further than the margin
+    RF_CELL_TOO_SMALL    = 1u << 2,   // a mutable collider is larger than a grid cell
+    RF_CONTACT_OVERFLOW  = 1u << 3,
+    RF_LARGE_OVERFLOW    = 1u << 4,
+    RF_CLIP_OVERFLOW     = 1u << 5,
+};
+
+// mutable entity state: one buffer is the tick input, the other the tick output
+struct EntityState {
+    float4* pos;     // origin.xyz, -
+    float4* rot;     // orientation w,x,y,z
+    float4* vel;     // velocity.xyz, -
+    float4* acc;     // acceleration.xyz, -
+    float4* angvel;  // angularVelocity.xyz, -
+    float4* angacc;  // angularAcceleration.xyz, -
+    uint32_t* ts;    // timestream state (low 8 bits) | coherency stamp << 16   (cosmos.h:247)
+};
+
+struct DeviceWorld {
+    uint32_t n_entities, n_packets;
+    EntityState in, out;            // Euler reads `in`, writes `out`; the collision pass mutates `out`
+    // per-entity constants
+    float4* prm0;                   // scale.xyz, mass
+    float4* prm1;                   // linearDrag, angularDrag, collisionAngularDrag, bits(flags)
+    float4* locked_pos;             // lockedOrigin.xyz
+    float4* locked_rot;             // lockedOrientation wxyz
+    uint32_t* entity_id;            // IcxEntity
+    uint32_t* first_packet;         // packet index of the entity's first active collider | count << 30
+    float4* pos0;                   // origin right after integration (margin check)
+    // per-packet constants (uploaded AoS -> SoA)
+    uint32_t* pk_entity;            // entity index
+    float4* pk_lpos;                // localTransform.origin.xyz, bits
+    float4* pk_lrot;                // localTransform.orientation wxyz
+    float4* pk_lscale;              // localTransform.scale.xyz, restLength
+    float4* pk_mat0;                // staticFriction, dynamicFriction, restitution, stiffness
+    float* pk_damping;
+    float* pk_minparam;             // Collider::minParametricValue (mutable, reset to 1 every tick)
+    // per-packet, derived every tick by the prep kernel
+    float4* pk_d;                   // 6 x float4 per packet, contiguous (96 B): d[p * 6 + k]
+                                    //   k=0..2: composite linear column k .xyz, base[k]
+                                    //   k=3..5: inverse linear column .xyz, inertia diag [k-3]
+    float4* pk_lo;                  // inflated bound lo.xyz, -
+    float4* pk_hi;                  // inflated bound hi.xyz, -
+    uint32_t* pk_cell;              // hashed grid bucket (or 0xFFFFFFFF for large / inert)
+    // grid
+    uint32_t n_buckets;             // power of two
+    uint32_t* cell_count;           // [n_buckets + 1] -> exclusive scan in place = cell_start
+    uint32_t* cell_fill;
+    uint32_t* scan_partial;
+    float4* s_lo;                   // sorted by bucket: lo.xyz, asfloat(packet | flags)
+    float4* s_hi;                   // hi.xyz, asfloat(entity index)
+    uint32_t* pos_of;               // packet -> sorted position (list owner column)
+    uint32_t* large_list;           // packets larger than a cell (immutable only)
+    // candidate lists, column-major: nbr[i * n_packets + column]
+    uint32_t* nbr; uint32_t* nbr_count; uint32_t max_neighbors;
+    // ordered resolve
+    uint32_t* head[2];              // per entity: consumed entries of slot-0 list | slot-1 list << 16
+    uint32_t* active[2];            // entity work lists
+    uint32_t* ent_active;           // dedupe flag while building active[0]
+    // outputs
+    IcxContact* contacts; IcxInterception* intercepts; uint2* intercept_key; uint32_t max_contacts;
+    // counters, one cache line each would be nicer; they are cold
+    uint32_t* counters;             // see CTR_*
+    uint32_t* flags;                // RF_*
+    // parameters
+    float margin, cell_size, inv_cell;
+    float gx, gy, gz;
+    uint32_t host_timeslice, cfg_flags, worldline_stride, max_large;
+    uint16_t coherency;
+};
+
+enum { CTR_LARGE = 0, CTR_ACTIVE0 = 1, CTR_CONTACTS = 2, CTR_INTERCEPTS = 3, CTR_CANDIDATES = 4,
+       CTR_ROUND_BASE = 8, CTR_MAX_ROUNDS = 4096, CTR_TOTAL = CTR_ROUND_BASE + CTR_MAX_ROUNDS + 8 };
+
+} // namespace icx

@@ -1,0 +1,127 @@
+"""Thin Python driver over the C ABI (include/icx.h) for tests and bench.py.
+
+Mirrors the reference's PhysicsDynamo call sequence (source/physics/physics_dynamo.cpp:23-53):
+upload == the synchros' submit(), step == run_relays(dt) (+ Cosmos::increment_coherency),
+download == the in-place component mutation the reference performs.  The production host side
+is C++ (intercession_b200/host/physics_dynamo.hpp); this class exists so Python tests read
+like the reference's tick.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import abi
+
+
+class IcxError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"icx status {code}: {msg}")
+        self.code = code
+
+
+class World:
+    def __init__(self, max_entities, host_timeslice=0, flags=0, margin=0.0, cell_size=0.0, max_neighbors=0,
+                 worldline_stride=0, device=0, max_contacts=0, gravity=None):
+        self.lib = abi.load()
+        cfg = abi.IcxConfig()
+        self.lib.icx_config_default(C.byref(cfg))
+        cfg.device = device
+        cfg.max_entities = max(int(max_entities), 1)
+        cfg.host_timeslice = host_timeslice
+        cfg.flags = flags
+        cfg.broadphase_margin = margin
+        cfg.cell_size = cell_size
+        cfg.max_neighbors = max_neighbors
+        cfg.worldline_stride = worldline_stride
+        cfg.max_contacts = max_contacts
+        if gravity is not None:
+            cfg.gravity[:] = gravity
+        self.handle = C.c_void_p()
+        rc = self.lib.icx_world_create(C.byref(cfg), C.byref(self.handle))
+        if rc != abi.OK:
+            raise IcxError(rc, self.lib.icx_status_string(rc).decode() + " (icx_world_create; is a CUDA device present?)")
+        self.n = 0
+
+    def close(self):
+        if self.handle:
+            self.lib.icx_world_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _ck(self, rc):
+        if rc != abi.OK:
+            raise IcxError(rc, self.lib.icx_last_error(self.handle).decode())
+
+    # ---- PhysicsSynchro / ColliderSynchro -> submit ----
+    def upload(self, s):
+        self.n = s.n
+        self._ck(self.lib.icx_bodies_upload(self.handle, s.n, abi.ptr(s.ids), abi.ptr(s.T), abi.ptr(s.P),
+                                            abi.ptr(s.hasP), abi.ptr(s.C), abi.ptr(s.tstate), abi.ptr(s.tcoh)))
+
+    def download(self, like):
+        out = like.copy()
+        self._ck(self.lib.icx_bodies_download(self.handle, out.n, abi.ptr(out.T), abi.ptr(out.P), abi.ptr(out.C),
+                                              abi.ptr(out.tstate), abi.ptr(out.tcoh)))
+        return out
+
+    def download_into(self, T=None, P=None, Cc=None, tstate=None, tcoh=None):
+        self._ck(self.lib.icx_bodies_download(self.handle, self.n, abi.ptr(T), abi.ptr(P), abi.ptr(Cc),
+                                              abi.ptr(tstate), abi.ptr(tcoh)))
+
+    def update(self, index, T=None, P=None, Cc=None):
+        index = np.ascontiguousarray(index, np.uint32)
+        self._ck(self.lib.icx_bodies_update(self.handle, len(index), abi.ptr(index), abi.ptr(T), abi.ptr(P), abi.ptr(Cc)))
+
+    # ---- PhysicsDynamo::run_relays ----
+    def step(self, dt=1.0 / 45, n=1):
+        self._ck(self.lib.icx_step_n(self.handle, dt, n) if n != 1 else self.lib.icx_step(self.handle, dt))
+
+    def euler_engage(self, dt=1.0 / 45):
+        self._ck(self.lib.icx_euler_engage(self.handle, dt))
+
+    def collision_engage(self):
+        self._ck(self.lib.icx_collision_engage(self.handle))
+
+    def sync(self):
+        self._ck(self.lib.icx_sync(self.handle))
+
+    def set_coherency(self, c):
+        self._ck(self.lib.icx_coherency_set(self.handle, c))
+
+    def coherency(self):
+        c = C.c_uint16(0)
+        self._ck(self.lib.icx_coherency_get(self.handle, C.byref(c)))
+        return c.value
+
+    # ---- results of the last tick ----
+    def _fetch(self, fn, dt):
+        n = C.c_size_t(0)
+        self._ck(fn(self.handle, None, 0, C.byref(n)))
+        out = np.zeros(n.value, dt)
+        if n.value:
+            self._ck(fn(self.handle, abi.ptr(out), n.value, C.byref(n)))
+        return out
+
+    def contacts(self):
+        return self._fetch(self.lib.icx_contacts_fetch, abi.contact_dt)
+
+    def interceptions(self):
+        return self._fetch(self.lib.icx_interceptions_fetch, abi.interception_dt)
+
+    def pairs(self):
+        return self._fetch(self.lib.icx_pairs_fetch, abi.pair_dt)
+
+    def stats(self):
+        st = abi.IcxStats()
+        self._ck(self.lib.icx_stats_fetch(self.handle, C.byref(st)))
+        return st
+
+    def last_step_ms(self):
+        ms = C.c_float(0)
+        self._ck(self.lib.icx_last_step_ms(self.handle, C.byref(ms)))
+        return ms.value
