@@ -152,8 +152,8 @@ int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_
         w->stats.n_retries++;
         if (raised & RF_CLIP_OVERFLOW) return fail(w, ICX_E_CAPACITY, "clipped manifold exceeded ICX_MAXV");
         if (raised & RF_NEIGHBOR_OVERFLOW) {
-            if (W.max_neighbors >= 96) return fail(w, ICX_E_CAPACITY, "candidate list exceeded 96 neighbours per collider");
-            W.max_neighbors = std::min<uint32_t>(W.max_neighbors * 2, 96);
+            if (W.max_neighbors >= 192) return fail(w, ICX_E_CAPACITY, "candidate list exceeded 192 neighbours per collider");
+            W.max_neighbors = std::min<uint32_t>(W.max_neighbors * 2, 192);
             rc = regrow(w, W.nbr, (size_t)w->cap_packets * W.max_neighbors); if (rc) return rc;
         }
         if (raised & RF_MARGIN_VIOLATED) {
@@ -235,7 +235,7 @@ int icx_world_create(const IcxConfig* cfg, IcxWorld** out)
         w->cap_entities = cfg->max_entities; w->cap_packets = 2 * cfg->max_entities;
         W.margin = cfg->broadphase_margin > 0 ? cfg->broadphase_margin : 0.05f;
         set_cell(w, cfg->cell_size > 0 ? cfg->cell_size : 1.0f);
-        W.max_neighbors = cfg->max_neighbors ? std::min<uint32_t>(cfg->max_neighbors, 96) : 24;
+        W.max_neighbors = cfg->max_neighbors ? std::min<uint32_t>(cfg->max_neighbors, 192) : 24;
         W.max_large = cfg->max_large ? cfg->max_large : 1024;
         W.max_contacts = cfg->max_contacts ? cfg->max_contacts : std::max<uint32_t>(2 * cfg->max_entities, 1024);
         W.gx = (cfg->flags & ICX_F_NO_GRAVITY) ? 0.0f : cfg->gravity[0];

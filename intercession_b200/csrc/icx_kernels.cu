@@ -249,7 +249,7 @@ __global__ void __launch_bounds__(256) k_scatter(DeviceWorld W)
 // bounds overlap, sorted ascending by packet index (= the order the reference's pair loop
 // meets them, collision_physics_relay.h:29-37).
 // ---------------------------------------------------------------------------------------
-#define ICX_KMAX 96
+#define ICX_KMAX 192
 
 __device__ __forceinline__ bool overlap(float4 alo, float4 ahi, float4 blo, float4 bhi) {
     return alo.x <= bhi.x && blo.x <= ahi.x && alo.y <= bhi.y && blo.y <= ahi.y && alo.z <= bhi.z && blo.z <= ahi.z;

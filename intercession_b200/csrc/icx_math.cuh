@@ -15,7 +15,8 @@ struct Q4 { float w, x, y, z; };
 struct M3 { V3 c[3]; };          // column-major
 struct M4 { V3 c[3]; V3 t; };    // affine [c0 c1 c2 | t]
 
-#define ICX_DI __device__ __forceinline__
+#define ICX_DI __host__ __device__ __forceinline__
+#define ICX_DN static __host__ __device__ __noinline__
 
 ICX_DI V3 v3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
 ICX_DI V3 v3(float4 f) { return v3(f.x, f.y, f.z); }

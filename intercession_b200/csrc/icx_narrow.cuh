@@ -86,7 +86,7 @@ ICX_DI bool intersect_ray_plane(V3 orig, V3 dir, V3 planeOrig, V3 planeNormal, f
     return false;
 }
 // pseudo_clip_polyhedra, collision_procedures.h:163-313
-static __device__ __noinline__ void pseudo_clip_polyhedra(const V3* clipper, int nc, V3* clippee, int& ne, V3 axis) {
+ICX_DN void pseudo_clip_polyhedra(const V3* clipper, int nc, V3* clippee, int& ne, V3 axis) {
     V3 centre = v3(0.0f, 0.0f, 0.0f);
     for (int i = 0; i < nc; i++) centre = centre + clipper[i];
     centre = centre / (float)nc;
@@ -138,7 +138,7 @@ ICX_DI V3 sat_axis(const M3& nA, const M3& nB, int a) {
 }
 
 // box_box_intersect, collision_procedures.cpp:14-231
-static __device__ __noinline__ bool box_box_intersect(const Shape& A, const Shape& B, Hit& h) {
+ICX_DN bool box_box_intersect(const Shape& A, const Shape& B, Hit& h) {
     const M3 nA = transpose(A.inv), nB = transpose(B.inv);      // :41-44
     V3 cA[8], cB[8];
     box_corners(A.M, cA); box_corners(B.M, cB);
@@ -183,7 +183,7 @@ static __device__ __noinline__ bool box_box_intersect(const Shape& A, const Shap
 }
 
 // sphere_box_intersect, collision_procedures.cpp:266-378 (A sphere, B box)
-static __device__ __noinline__ bool sphere_box_intersect(const Shape& A, const Shape& B, Hit& h) {
+ICX_DN bool sphere_box_intersect(const Shape& A, const Shape& B, Hit& h) {
     const M3 nA = transpose(A.inv), nB = transpose(B.inv);
     V3 cB[8]; box_corners(B.M, cB);
     const V3 sO = xform(A.M, 0.0f, 0.0f, 0.0f);
@@ -219,7 +219,7 @@ ICX_DI bool sphere_sphere_intersect(const Shape& A, float rA, const Shape& B, fl
 }
 
 // ray_box_intersect, collision_procedures.cpp:442-590 (A ray, B box); minParam = A.collider.minParametricValue
-static __device__ __noinline__ bool ray_box_intersect(const Shape& A, V3 entityOriginA, const Shape& B, V3 entityOriginB,
+ICX_DN bool ray_box_intersect(const Shape& A, V3 entityOriginA, const Shape& B, V3 entityOriginB,
                                                float& minParam, Hit& h) {
     const M3 nB = transpose(B.inv);
     V3 cB[8]; box_corners(B.M, cB);

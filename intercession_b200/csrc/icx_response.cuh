@@ -42,7 +42,7 @@ ICX_DI float impulse_denominator(float invMassA, float invMassB, const M3& imA, 
 }
 
 // rigid_rigid_response, .cpp:636-874.  Mutates origin/vel/angvel of both sides and h.point.
-static __device__ __noinline__ void rigid_rigid_response(Side& A, Side& B, Hit& h) {
+ICX_DN void rigid_rigid_response(Side& A, Side& B, Hit& h) {
     if (A.mass == 0 && B.mass == 0) return;                                         // :649
     float invMassA = 0, invMassB = 0;
     if (A.mass != 0) invMassA = 1.0f / A.mass;
@@ -79,7 +79,7 @@ static __device__ __noinline__ void rigid_rigid_response(Side& A, Side& B, Hit& 
 }
 
 // spring_rigid_response, .cpp:876-1053 (A is the spring).  Mutates acc/angacc/vel/angvel and h.point.
-static __device__ __noinline__ void spring_rigid_response(Side& A, Side& B, Hit& h) {
+ICX_DN void spring_rigid_response(Side& A, Side& B, Hit& h) {
     if (A.mass == 0 && B.mass == 0) return;
     float invMassA = 0, invMassB = 0;
     if (A.mass != 0) invMassA = 1.0f / A.mass;

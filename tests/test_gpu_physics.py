@@ -16,9 +16,9 @@ def oracle_tick(s, **kw):
 
 
 def dense(n, seed, **kw):
-    side = 2.0 + 0.95 * round(n ** (1 / 3) + 1)
+    side = 2.0 + 1.1 * round(n ** (1 / 3) + 1)
     kw.setdefault("kinds", ("sphere", "box", "aabb"))
-    return scenes.arena(n, seed=seed, fill_side=side, spacing=0.9, jitter=0.2, **kw)
+    return scenes.arena(n, seed=seed, fill_side=side, spacing=1.05, jitter=0.25, **kw)
 
 
 def lockstep_collision(s, host=0, flags=0, stride=0, coherency=0, margin=0.0, check_pairs=True):
