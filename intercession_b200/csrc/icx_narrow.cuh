@@ -56,24 +56,31 @@ ICX_DI Interval project_sphere(V3 o, float radius, V3 axis) {
     Interval r; r.x = op - rp; r.y = op + rp; return r;
 }
 
-// build_contact_manifold, :106-160
+// build_contact_manifold, :106-160.  The reference pushes a vertex when it is within
+// MANIFOLD_DEPTH of the RUNNING maximum, then re-filters against the final maximum walking the
+// kept vertices backwards; `kept` is that first filter as a bitmask (no dynamically indexed
+// temporaries).
 ICX_DI int build_contact_manifold(const M4& m, V3 axis, V3* dest) {
-    float coeffs[8]; V3 verts[8]; int nAll = 0;
+    float coeffs[8]; V3 verts[8];
+    uint32_t kept = 0;
     float maxCoeff = -INFINITY;
     float dx = -1.0f, dy = -1.0f, dz = -1.0f;
 #pragma unroll
     for (int o = 0; o < 8; o++) {
-        V3 vertex = xform(m, ICX_UNIT_RADIUS * dx, ICX_UNIT_RADIUS * dy, ICX_UNIT_RADIUS * dz);
-        float coeff = dot(vertex, axis);
+        const V3 vertex = xform(m, ICX_UNIT_RADIUS * dx, ICX_UNIT_RADIUS * dy, ICX_UNIT_RADIUS * dz);
+        const float coeff = dot(vertex, axis);
         maxCoeff = coeff > maxCoeff ? coeff : maxCoeff;
-        if (coeff >= maxCoeff - ICX_MANIFOLD_DEPTH) { coeffs[nAll] = coeff; verts[nAll] = vertex; nAll++; }
-        // order {0,1,0,2,0,1,0,2}
+        if (coeff >= maxCoeff - ICX_MANIFOLD_DEPTH) kept |= 1u << o;
+        coeffs[o] = coeff; verts[o] = vertex;
+        // winding order {0,1,0,2,0,1,0,2}: which dimension flips after vertex o
         if ((o & 1) == 0) dx = dx < 0.0f ? 1.0f : -1.0f;
         else if ((o & 3) == 1) dy = dy < 0.0f ? 1.0f : -1.0f;
         else dz = dz < 0.0f ? 1.0f : -1.0f;
     }
     int n = 0;
-    for (int i = nAll - 1; i >= 0; i--) if (coeffs[i] >= maxCoeff - ICX_MANIFOLD_DEPTH) dest[n++] = verts[i];
+#pragma unroll
+    for (int o = 7; o >= 0; o--)
+        if ((kept >> o & 1u) && coeffs[o] >= maxCoeff - ICX_MANIFOLD_DEPTH) dest[n++] = verts[o];
     return n;
 }
 // glm::intersectRayPlane, gtx/intersect.inl:6-26

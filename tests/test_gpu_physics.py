@@ -83,10 +83,14 @@ def test_collision_lockstep_interceptions(built, host):
 
 
 def test_collision_case_study_ray_spring(built):
-    s = scenes.case_study(push=True)
-    s.T["origin"][3] = (12, -1.2, 0)       # legs (ray spring) reaching the floor
-    exp, _ = lockstep_collision(s)
-    assert len(exp.hits) >= 2
+    n_hits = 0
+    for y in (-3.5, -3.0, -1.0):            # box+legs on the floor / legs (ray spring) only / box on the ball
+        s = scenes.case_study(push=True)
+        s.T["origin"][3] = (12, y, 0)
+        s.P["velocity"][3] = (0.3, -1.0, 0.2)
+        exp, _ = lockstep_collision(s)
+        n_hits += len(exp.hits)
+    assert n_hits >= 4
 
 
 def test_collision_worldline_batch(built):
