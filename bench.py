@@ -1,0 +1,286 @@
+#!/usr/bin/env python
+"""bench.py -- collider-steps/s of the physics tick on the 1 M mixed-collider scene (BASELINE.json).
+
+One step = one tick (PhysicsDynamo::run_relays: Euler + collision pass) over one scene.
+  value      whole-job collider-steps/s with the scene resident in HBM (CUDA events on the world's
+             stream around exactly K ticks, max over ranks)
+  e2e        the same through the C ABI with HOST buffers every step: icx_bodies_upload (pinned AoS
+             components in) + icx_step + icx_bodies_download (T, P out) + icx_contacts_fetch
+  roofline   algorithmic bytes (308 B/collider + 8 B/pair + 48 B/contact) over the
+             measured tick, against the measured HBM copy bandwidth; per-kernel shares alongside
+  cpu_baseline  the reference's own procedures (oracle/_ref) ticking a bounded sample on the host
+
+--gpus N > 1: a single scene does not shard (the reference's pair loop is sequential), so each rank
+ticks its own replica of the scene (weak scaling, no data-path collective); the only NCCL traffic
+is the gather of per-rank timings / stats.
+--impl reference: the reference CPU code on the host cores (see cpu_reference()).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+DT = 1.0 / 45
+METRIC = "collider-steps/sec at 1M bodies"
+UNIT = "collider-steps/s"
+B_PER_COLLIDER, B_PER_PAIR, B_PER_CONTACT = 308, 8, 48
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def build_scene(name, n, seed_offset=0):
+    from intercession_b200 import scenes
+    if name == "config3":
+        return scenes.config3(n, seed=20261105 + seed_offset)
+    if name == "config2":
+        return scenes.config2(n, seed=20261104 + seed_offset)
+    raise SystemExit(f"unknown workload {name}")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.stop, self.t = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self.stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([x.strip() for x in out.strip().split(",")])
+            except Exception:
+                pass
+            self.stop.wait(0.2)
+
+    def __enter__(self):
+        self.t = threading.Thread(target=self._run, daemon=True)
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.t.join(timeout=6)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def pinned_like(arr):
+    """Copy a numpy (structured) array into page-locked host memory (torch owns the allocation)."""
+    import torch
+    t = torch.empty(arr.nbytes, dtype=torch.uint8, pin_memory=True)
+    v = t.numpy().view(arr.dtype).reshape(arr.shape)
+    v[...] = arr
+    return v, t
+
+
+def cpu_reference(scene_name, n_sample, ticks, threads, seed_offset=0):
+    """Reference CPU tick on a bounded sample: the reference's own EulerPhysicsRelay + intersect/response
+    procedures (oracle/_ref, unmodified sources) in the reference's pair order behind the oracle-side
+    cull -- the verbatim all-pairs loop is O(N^2) (~47 h per tick at 1 M).  The reference
+    tick is single-threaded by construction; `threads` independent sample scenes run in parallel."""
+    import refs
+    lib = refs.ref()
+    kind = "reference"
+    if lib is None:
+        lib, kind = refs.oracle(), "port"
+    prefix = "icxref" if kind == "reference" else "icxo"
+    scenes_ = [build_scene(scene_name, n_sample, seed_offset + 100 + k) for k in range(threads)]
+    done = [0] * threads
+
+    def work(k):
+        s = scenes_[k]
+        for _ in range(ticks):
+            e = refs.procedures_tick(lib, prefix, s, collide=False)
+            cand = refs.oracle_pairs(e, 0.05)
+            s = refs.procedures_tick(lib, prefix, e, euler=False, cand=cand, cap=4 * s.n)
+            done[k] += s.n - s["n_walls"]
+    t0 = time.perf_counter()
+    ths = [threading.Thread(target=work, args=(k,)) for k in range(threads)]
+    [t.start() for t in ths]
+    [t.join() for t in ths]
+    sec = time.perf_counter() - t0
+    return sum(done) / sec, sec, kind
+
+
+def run_reference_arm(a, rank, world_size):
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    threads = max(1, min(cores, 32))
+    n_sample = min(a.bodies, 32768)
+    # warm-up
+    for _ in range(min(a.warmup, 1)):
+        cpu_reference(a.workload, n_sample, 1, threads)
+    t0 = time.perf_counter()
+    v, sec, kind = cpu_reference(a.workload, n_sample, a.steps, threads)
+    sample = (f"{threads} independent {n_sample}-body samples of {a.workload} (same recipe), {a.steps} ticks each: reference "
+              f"EulerPhysicsRelay + intersect/response procedures in reference pair order behind the oracle-side cull; "
+              f"the verbatim all-pairs tick is O(N^2)")
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": 1e3 * sec / max(a.steps, 1), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{a.workload}: {a.bodies} mixed sphere/AABB/OBB colliders in a closed arena (CPU sample {n_sample} x {threads})"},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="config3")
+    ap.add_argument("--bodies", type=int, default=1048576)
+    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--no-cpu", action="store_true")
+    a = ap.parse_args()
+    a.warmup = max(a.warmup, 3) if a.impl == "ours" else a.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if a.impl == "reference":
+        run_reference_arm(a, rank, world_size)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from intercession_b200 import world as icxworld
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- there is no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world_size > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    s = build_scene(a.workload, a.bodies, seed_offset=rank)
+    n_colliders = int(s.C["colliders"]["isActive"].sum())
+    w = icxworld.World(s.n, device=local_rank)
+    w.upload(s)
+    w.step(DT, a.warmup)
+    w.profile(True)
+    launches0 = w.phases()[2]
+    barrier()
+    with ClockSampler(local_rank) as clk:
+        w.step(DT, a.steps)
+        ms = w.last_step_ms()
+        barrier()
+    phases, pticks, launches1 = w.phases()
+    st = w.stats()
+    w.profile(False)
+    ms_t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world_size > 1:
+        dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
+    ms_max = float(ms_t.item())
+    value = world_size * n_colliders * a.steps / (ms_max * 1e-3)
+
+    # ---- roofline: algorithmic bytes of the tick over its measured duration ----
+    peak, peak_src = measured_peak()
+    alg_bytes = B_PER_COLLIDER * n_colliders + B_PER_PAIR * st.n_candidates + B_PER_CONTACT * st.n_contacts
+    tick_ms = ms / a.steps
+    achieved = alg_bytes / (tick_ms * 1e-3) / 1e9
+    per_kernel = {}
+    kernel_bytes = {"integrate_prep": B_PER_COLLIDER * n_colliders, "grid_sort": 0, "pairs": B_PER_PAIR * st.n_candidates,
+                    "resolve": B_PER_CONTACT * st.n_contacts}
+    for k, v in phases.items():
+        kms = v / max(pticks, 1)
+        per_kernel[k] = {"ms": round(kms, 4), "share": round(v / max(sum(phases.values()), 1e-9), 3),
+                         "alg_GBps": round(kernel_bytes[k] / max(kms * 1e-3, 1e-12) / 1e9, 1)}
+    dom = max(phases, key=phases.get)
+    roofline = {"bound": "hbm", "kernel": "tick (all kernels; dominant phase: %s)" % dom, "achieved": round(achieved, 2),
+                "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": None,
+                "algorithmic_bytes_per_tick": alg_bytes, "phases": per_kernel}
+
+    # ---- e2e: host AoS in / out through the C ABI every step ----
+    ids, _k0 = pinned_like(s.ids)
+    T, _k1 = pinned_like(s.T)
+    P, _k2 = pinned_like(s.P)
+    Cc, _k3 = pinned_like(s.C)
+    hasP, _k4 = pinned_like(s.hasP)
+    ts, _k5 = pinned_like(s.tstate)
+    tc, _k6 = pinned_like(s.tcoh)
+    from intercession_b200.scenes import Scene
+    hs = Scene(ids=ids, T=T, P=P, hasP=hasP, C=Cc, tstate=ts, tcoh=tc)
+    n_contacts = 0
+    for it in range(2 + a.e2e_steps):
+        if it == 2:
+            barrier()
+            t0 = time.perf_counter()
+        w.upload(hs)
+        w.step(DT)
+        w.download_into(T=T, P=P)
+        n_contacts = len(w.contacts())
+    barrier()
+    e2e_sec = time.perf_counter() - t0
+    e2e_t = torch.tensor([e2e_sec], dtype=torch.float64, device="cuda")
+    if world_size > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_val = world_size * n_colliders * a.e2e_steps / float(e2e_t.item())
+    h2d = ids.nbytes + T.nbytes + P.nbytes + Cc.nbytes + hasP.nbytes + ts.nbytes + tc.nbytes + 4 * s.n
+    d2h = T.nbytes + P.nbytes + n_contacts * 48
+    w.close()
+
+    cpu = None
+    if rank == 0 and not a.no_cpu:
+        cores = os.cpu_count() or 1
+        threads = max(1, min(cores, 32))
+        n_sample = min(a.bodies, 32768)
+        v1, sec1, kind = cpu_reference(a.workload, n_sample, 1, threads)
+        ticks = int(max(1, min(20, a.cpu_seconds / max(sec1, 1e-3))))
+        v, sec, kind = cpu_reference(a.workload, n_sample, ticks, threads)
+        cpu = {"value": v, "unit": UNIT, "cores": threads, "kind": kind,
+               "sample": f"{threads} independent {n_sample}-body samples of {a.workload}, {ticks} ticks each ({sec:.1f} s): reference "
+                         f"procedures (oracle/_ref) in reference pair order behind the oracle-side cull; verbatim all-pairs tick is O(N^2)"}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world_size, "steps": a.steps, "warmup": a.warmup,
+                "ms_per_step": ms_max / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic",
+                "config": {"workload": f"{a.workload}: {a.bodies} mixed sphere/AABB/OBB colliders + 6 walls in a closed arena, "
+                                       f"one scene replica per GPU, gravity on, dt=1/45",
+                           "l2": "inputs larger than L2 (per-tick state and derived arrays > 126 MB)" if a.bodies >= 400000 else "inputs fit L2 (reduced size)",
+                           "colliders_per_gpu": n_colliders, "candidate_pairs": st.n_candidates, "contacts": st.n_contacts,
+                           "resolve_rounds": st.n_rounds, "retries": st.n_retries, "margin": st.margin},
+                "clocks": clk.summary(), "roofline": roofline,
+                "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+                "gpu_launches": int(launches1 - launches0),
+                "cpu_baseline": cpu}
+        print(json.dumps(line), flush=True)
+    if world_size > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

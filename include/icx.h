@@ -269,6 +269,12 @@ ICX_API int icx_stats_fetch(IcxWorld* w, IcxStats* out);
  * the world's stream. */
 ICX_API int icx_last_step_ms(IcxWorld* w, float* ms);
 
+/* Per-phase device timing of icx_step* (CUDA events on the world's stream, accumulated since
+ * enabled): ms4 = {integrate+prep, grid sort, candidate lists, ordered resolve}; n_launches =
+ * kernels launched by this world since creation.  Costs four extra event records per tick. */
+ICX_API int icx_profile_enable(IcxWorld* w, int on);
+ICX_API int icx_phase_ms(IcxWorld* w, double* ms4, uint64_t* n_ticks, uint64_t* n_launches);
+
 /* CUDA stream of the world as a void* (cudaStream_t), for callers that time it. */
 ICX_API void* icx_world_stream(IcxWorld* w);
 

@@ -90,11 +90,19 @@ int run_tick_once(IcxWorld* w, double dt, int do_euler, int do_collide, uint32_t
     CK(cudaMemsetAsync(W.flags, 0, 16, st));
     CK(cudaMemsetAsync(W.cell_count, 0, ((size_t)W.n_buckets + 4) * sizeof(uint32_t), st));
     CK(cudaMemsetAsync(W.cell_fill, 0, (size_t)W.n_buckets * sizeof(uint32_t), st));
+    const bool prof = w->profile && do_collide && W.n_packets;
+    if (prof) cudaEventRecord(w->pev[0], st);
     launch_integrate_prep(W, dt, do_euler, st);
+    w->launches += 1;
+    if (prof) cudaEventRecord(w->pev[1], st);
     uint32_t rounds = 0;
     *raised = 0;
     if (do_collide && W.n_packets) {
         launch_grid(W, st);
+        if (prof) cudaEventRecord(w->pev[2], st);
+        launch_pairs(W, st);
+        if (prof) cudaEventRecord(w->pev[3], st);
+        w->launches += 5;
         uint32_t n_threads = W.n_entities;
         uint32_t ctr_in = CTR_ACTIVE0;
         int parity = 0;
@@ -107,7 +115,9 @@ int run_tick_once(IcxWorld* w, double dt, int do_euler, int do_collide, uint32_t
                 const uint32_t ctr_out = CTR_ROUND_BASE + rounds;
                 launch_resolve_round(W, parity, ctr_in, ctr_out, n_threads, st);
                 ctr_in = ctr_out; parity ^= 1; rounds++;
+                if (n_threads) w->launches += 1;
             }
+            if (prof) cudaEventRecord(w->pev[4], st);
             CK(cudaMemcpyAsync(w->h_counters, W.counters, (CTR_ROUND_BASE + rounds) * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
             CK(cudaMemcpyAsync(w->h_flags, W.flags, 16, cudaMemcpyDeviceToHost, st));
             CK(cudaStreamSynchronize(st));
@@ -125,6 +135,10 @@ int run_tick_once(IcxWorld* w, double dt, int do_euler, int do_collide, uint32_t
     CK(cudaGetLastError());
     *raised = w->h_flags[0];
     w->stats.n_rounds = rounds;
+    if (prof) {
+        for (int k = 0; k < 4; k++) { float ms = 0; cudaEventElapsedTime(&ms, w->pev[k], w->pev[k + 1]); w->phase_ms[k] += ms; }
+        w->phase_ticks++;
+    }
     return ICX_OK;
 }
 
@@ -261,6 +275,7 @@ void icx_world_destroy(IcxWorld* w)
     if (w->h_flags) cudaFreeHost(w->h_flags);
     if (w->ev0) cudaEventDestroy(w->ev0);
     if (w->ev1) cudaEventDestroy(w->ev1);
+    for (auto& e : w->pev) if (e) cudaEventDestroy(e);
     if (w->stream) cudaStreamDestroy(w->stream);
     delete w;
 }
@@ -401,6 +416,26 @@ int icx_sync(IcxWorld* w)
 
 int icx_last_step_ms(IcxWorld* w, float* ms) { if (!w || !ms) return ICX_E_INVALID; *ms = w->last_ms; return ICX_OK; }
 void* icx_world_stream(IcxWorld* w) { return w ? (void*)w->stream : nullptr; }
+
+int icx_profile_enable(IcxWorld* w, int on)
+{
+    if (!w) return ICX_E_INVALID;
+    cudaSetDevice(w->device);
+    if (on && !w->pev[0]) for (auto& e : w->pev) cudaEventCreate(&e);
+    w->profile = on != 0;
+    for (auto& m : w->phase_ms) m = 0;
+    w->phase_ticks = 0;
+    return ICX_OK;
+}
+
+int icx_phase_ms(IcxWorld* w, double* ms4, uint64_t* n_ticks, uint64_t* n_launches)
+{
+    if (!w) return ICX_E_INVALID;
+    if (ms4) for (int k = 0; k < 4; k++) ms4[k] = w->phase_ms[k];
+    if (n_ticks) *n_ticks = w->phase_ticks;
+    if (n_launches) *n_launches = w->launches;
+    return ICX_OK;
+}
 
 int icx_stats_fetch(IcxWorld* w, IcxStats* out) { if (!w || !out) return ICX_E_INVALID; *out = w->stats; return ICX_OK; }
 

@@ -9,7 +9,8 @@ namespace icx {
 
 // launchers implemented in the .cu translation units
 void launch_integrate_prep(const DeviceWorld& W, double dt, int do_euler, cudaStream_t st);
-void launch_grid(const DeviceWorld& W, cudaStream_t st);
+void launch_grid(const DeviceWorld& W, cudaStream_t st);      // 4 kernels: scan x3 + scatter
+void launch_pairs(const DeviceWorld& W, cudaStream_t st);
 void launch_resolve_round(const DeviceWorld& W, int parity, uint32_t ctr_in, uint32_t ctr_out, uint32_t n_threads, cudaStream_t st);
 struct Mirror { uint32_t* ids; IcxTransform* T; IcxPhysics* P; IcxColliderComponent* C; uint8_t* hasP; };
 void launch_import_kernel(const DeviceWorld& W, Mirror M, const uint32_t* index, const uint32_t* ids, const IcxTransform* T,
@@ -51,6 +52,12 @@ struct IcxWorld {
     uint32_t* h_flags = nullptr;        // pinned
     IcxStats stats;
     float last_ms = 0.0f;
+    // optional per-phase device timing (icx_profile_enable): integrate_prep | grid sort | pairs | resolve
+    bool profile = false;
+    cudaEvent_t pev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    double phase_ms[4] = {0, 0, 0, 0};
+    uint64_t phase_ticks = 0;
+    uint64_t launches = 0;              // kernels launched by icx_step* since creation
     std::string error;
     bool have_results = false;
 };

@@ -361,6 +361,11 @@ void launch_grid(const DeviceWorld& W, cudaStream_t st)
     k_scan_partials<<<1, SCAN_TPB, 0, st>>>(W.scan_partial, n_part);
     k_scan_add<<<(nb + 1 + 255) / 256, 256, 0, st>>>(W.cell_count, W.scan_partial, nb, n_part);
     k_scatter<<<(W.n_packets + 255) / 256, 256, 0, st>>>(W);
+}
+
+void launch_pairs(const DeviceWorld& W, cudaStream_t st)
+{
+    if (W.n_packets == 0) return;
     k_pairs<<<(W.n_packets + 127) / 128, 128, 0, st>>>(W);
 }
 

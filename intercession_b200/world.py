@@ -125,3 +125,14 @@ class World:
         ms = C.c_float(0)
         self._ck(self.lib.icx_last_step_ms(self.handle, C.byref(ms)))
         return ms.value
+
+    def profile(self, on=True):
+        self._ck(self.lib.icx_profile_enable(self.handle, 1 if on else 0))
+
+    def phases(self):
+        """({phase: accumulated ms}, ticks profiled, kernels launched since creation)."""
+        ms = (C.c_double * 4)()
+        nt, nl = C.c_uint64(0), C.c_uint64(0)
+        self._ck(self.lib.icx_phase_ms(self.handle, ms, C.byref(nt), C.byref(nl)))
+        names = ("integrate_prep", "grid_sort", "pairs", "resolve")
+        return dict(zip(names, list(ms))), nt.value, nl.value
