@@ -115,7 +115,7 @@ def cpu_reference(scene_name, n_sample, ticks, threads, seed_offset=0):
         s = scenes_[k]
         for _ in range(ticks):
             e = refs.procedures_tick(lib, prefix, s, collide=False)
-            cand = refs.oracle_pairs(e, 0.05)
+            cand = refs.oracle_pairs(e, 0.25)
             s = refs.procedures_tick(lib, prefix, e, euler=False, cand=cand, cap=4 * s.n)
             done[k] += s.n - s["n_walls"]
     t0 = time.perf_counter()
