@@ -213,7 +213,7 @@ def main():
     achieved = alg_bytes / (tick_ms * 1e-3) / 1e9
     per_kernel = {}
     kernel_bytes = {"integrate_prep": B_PER_COLLIDER * n_colliders, "grid_sort": 0, "pairs": B_PER_PAIR * st.n_candidates,
-                    "resolve": B_PER_CONTACT * st.n_contacts}
+                    "narrow": 0, "resolve": B_PER_CONTACT * st.n_contacts}
     for k, v in phases.items():
         kms = v / max(pticks, 1)
         per_kernel[k] = {"ms": round(kms, 4), "share": round(v / max(sum(phases.values()), 1e-9), 3),
@@ -272,7 +272,8 @@ def main():
                                        f"one scene replica per GPU, gravity on, dt=1/45",
                            "l2": "inputs larger than L2 (per-tick state and derived arrays > 126 MB)" if a.bodies >= 400000 else "inputs fit L2 (reduced size)",
                            "colliders_per_gpu": n_colliders, "candidate_pairs": st.n_candidates, "contacts": st.n_contacts,
-                           "resolve_rounds": st.n_rounds, "retries": st.n_retries, "margin": st.margin},
+                           "dirty_bodies": st.n_dirty,
+                           "resolve_rounds": st.n_rounds, "resolve_attempts": st.n_attempts, "retries": st.n_retries, "margin": st.margin},
                 "clocks": clk.summary(), "roofline": roofline,
                 "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
                 "gpu_launches": int(launches1 - launches0),

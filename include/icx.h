@@ -171,11 +171,12 @@ typedef struct IcxConfig {
     float    gravity[3];            /* default (0,-10,0), euler_physics_relay.h:32              */
     float    broadphase_margin;     /* AABB inflation; 0 = default 0.05                         */
     float    cell_size;             /* uniform-grid cell; 0 = chosen at upload                  */
-    uint32_t max_neighbors;         /* candidate list capacity per collider; 0 = default 24     */
+    uint32_t max_neighbors;         /* candidate list capacity per dirty collider; 0 = 24 (grows) */
     uint32_t max_large;             /* colliders larger than a cell; 0 = default 1024           */
     uint32_t max_contacts;          /* contact / interception ring; 0 = 2 * max_entities        */
     uint32_t worldline_stride;      /* 0 = one world; else entities [k*stride,(k+1)*stride) form
                                        independent world-line k (pairs never cross world-lines) */
+    uint32_t max_pairs;             /* broadphase pair list capacity; 0 = 8 * max_entities (grows)    */
 } IcxConfig;
 
 typedef struct IcxStats {
@@ -186,11 +187,13 @@ typedef struct IcxStats {
     uint32_t n_candidates;          /* broadphase pairs of the last tick                        */
     uint32_t n_contacts;
     uint32_t n_interceptions;
-    uint32_t n_rounds;              /* dependency rounds of the ordered resolve                 */
+    uint32_t n_rounds;              /* dependency rounds of the ordered resolve (last attempt)  */
     uint32_t n_retries;             /* ticks re-run with a larger margin / capacity (cumulative)*/
     float    margin;                /* margin in force                                          */
     float    cell_size;
     uint32_t max_neighbors;
+    uint32_t n_dirty;               /* bodies touched by a hit: the only ones resolved in order  */
+    uint32_t n_attempts;            /* ordered-resolve attempts (1 + times the dirty set grew)   */
     uint32_t _reserved;
 } IcxStats;
 
@@ -270,10 +273,12 @@ ICX_API int icx_stats_fetch(IcxWorld* w, IcxStats* out);
 ICX_API int icx_last_step_ms(IcxWorld* w, float* ms);
 
 /* Per-phase device timing of icx_step* (CUDA events on the world's stream, accumulated since
- * enabled): ms4 = {integrate+prep, grid sort, candidate lists, ordered resolve}; n_launches =
- * kernels launched by this world since creation.  Costs four extra event records per tick. */
+ * enabled): ms[ICX_N_PHASES] = {integrate+prep, grid sort, pair generation, speculative narrowphase,
+ * ordered resolve}; n_launches = kernels launched by this world since creation.  Costs six extra
+ * event records per tick. */
+#define ICX_N_PHASES 5
 ICX_API int icx_profile_enable(IcxWorld* w, int on);
-ICX_API int icx_phase_ms(IcxWorld* w, double* ms4, uint64_t* n_ticks, uint64_t* n_launches);
+ICX_API int icx_phase_ms(IcxWorld* w, double* ms, uint64_t* n_ticks, uint64_t* n_launches);
 
 /* CUDA stream of the world as a void* (cudaStream_t), for callers that time it. */
 ICX_API void* icx_world_stream(IcxWorld* w);

@@ -112,7 +112,7 @@ class IcxConfig(C.Structure):
                 ("host_timeslice", C.c_uint32), ("flags", C.c_uint32), ("gravity", C.c_float * 3),
                 ("broadphase_margin", C.c_float), ("cell_size", C.c_float),
                 ("max_neighbors", C.c_uint32), ("max_large", C.c_uint32), ("max_contacts", C.c_uint32),
-                ("worldline_stride", C.c_uint32)]
+                ("worldline_stride", C.c_uint32), ("max_pairs", C.c_uint32)]
 
 
 class IcxStats(C.Structure):
@@ -120,7 +120,7 @@ class IcxStats(C.Structure):
                 ("n_large", C.c_uint32), ("n_candidates", C.c_uint32), ("n_contacts", C.c_uint32),
                 ("n_interceptions", C.c_uint32), ("n_rounds", C.c_uint32), ("n_retries", C.c_uint32),
                 ("margin", C.c_float), ("cell_size", C.c_float), ("max_neighbors", C.c_uint32),
-                ("_reserved", C.c_uint32)]
+                ("n_dirty", C.c_uint32), ("n_attempts", C.c_uint32), ("_reserved", C.c_uint32)]
 
 
 _vp, _u32, _sz = C.c_void_p, C.c_uint32, C.c_size_t

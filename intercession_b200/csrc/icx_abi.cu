@@ -51,14 +51,18 @@ int allocate(IcxWorld* w)
     W.n_buckets = std::max<uint32_t>(next_pow2((uint32_t)std::min<size_t>(2 * np, 1u << 24)), 1024u);
     CK(alloc(w, W.cell_count, (size_t)W.n_buckets + 4)); CK(alloc(w, W.cell_fill, (size_t)W.n_buckets));
     CK(alloc(w, W.scan_partial, 4096 + 8));
-    CK(alloc(w, W.s_lo, np)); CK(alloc(w, W.s_hi, np)); CK(alloc(w, W.pos_of, np));
+    CK(alloc(w, W.s_lo, np)); CK(alloc(w, W.s_hi, np));
     CK(alloc(w, W.large_list, W.max_large));
-    CK(alloc(w, W.nbr, np * (size_t)W.max_neighbors)); CK(alloc(w, W.nbr_count, np));
+    CK(alloc(w, W.pairs, W.max_pairs)); CK(alloc(w, W.static_pairs, W.max_static));
+    CK(alloc(w, W.dirty_slot, ne)); CK(alloc(w, W.dirty_list, ne));
+    CK(alloc(w, W.nbr, 2 * ne * (size_t)W.max_neighbors)); CK(alloc(w, W.nbr_count, 2 * ne));
     CK(alloc(w, W.head[0], ne)); CK(alloc(w, W.head[1], ne));
-    CK(alloc(w, W.active[0], ne)); CK(alloc(w, W.active[1], ne)); CK(alloc(w, W.ent_active, ne));
+    CK(alloc(w, W.active[0], ne)); CK(alloc(w, W.active[1], ne));
     CK(alloc(w, W.contacts, W.max_contacts)); CK(alloc(w, W.intercepts, W.max_contacts)); CK(alloc(w, W.intercept_key, W.max_contacts));
     CK(alloc(w, W.counters, CTR_TOTAL)); CK(alloc(w, W.flags, 4));
     CK(cudaMemset(W.counters, 0, CTR_TOTAL * sizeof(uint32_t))); CK(cudaMemset(W.flags, 0, 16));
+    w->resolve_blocks = resolve_grid_blocks(w->device);
+    if (w->resolve_blocks <= 0) return fail(w, ICX_E_CUDA, "k_resolve cannot be made resident");
     CK(cudaMallocHost((void**)&w->h_counters, CTR_TOTAL * sizeof(uint32_t)));
     CK(cudaMallocHost((void**)&w->h_flags, 16));
     return ICX_OK;
@@ -81,7 +85,8 @@ Mirror mirror_of(IcxWorld* w)
 
 void set_cell(IcxWorld* w, float cell) { w->W.cell_size = cell; w->W.inv_cell = 1.0f / cell; }
 
-// One tick attempt on the stream: integrate+prep, grid, rounds.  Returns the raised RF_* flags.
+// One tick attempt on the stream: integrate+prep, grid, pairs, speculative narrowphase, ordered
+// resolve of the dirty bodies.  One host sync per tick (the counters / retry flags).
 int run_tick_once(IcxWorld* w, double dt, int do_euler, int do_collide, uint32_t* raised)
 {
     DeviceWorld& W = w->W;
@@ -95,48 +100,26 @@ int run_tick_once(IcxWorld* w, double dt, int do_euler, int do_collide, uint32_t
     launch_integrate_prep(W, dt, do_euler, st);
     w->launches += 1;
     if (prof) cudaEventRecord(w->pev[1], st);
-    uint32_t rounds = 0;
     *raised = 0;
     if (do_collide && W.n_packets) {
         launch_grid(W, st);
         if (prof) cudaEventRecord(w->pev[2], st);
         launch_pairs(W, st);
         if (prof) cudaEventRecord(w->pev[3], st);
-        w->launches += 5;
-        uint32_t n_threads = W.n_entities;
-        uint32_t ctr_in = CTR_ACTIVE0;
-        int parity = 0;
-        const uint32_t BATCH = 8;
-        bool done = false;
-        while (!done) {
-            if (rounds + BATCH > CTR_MAX_ROUNDS) return fail(w, ICX_E_CAPACITY, "resolve: dependency chain longer than CTR_MAX_ROUNDS");
-            const uint32_t first = rounds;
-            for (uint32_t b = 0; b < BATCH; b++) {
-                const uint32_t ctr_out = CTR_ROUND_BASE + rounds;
-                launch_resolve_round(W, parity, ctr_in, ctr_out, n_threads, st);
-                ctr_in = ctr_out; parity ^= 1; rounds++;
-                if (n_threads) w->launches += 1;
-            }
-            if (prof) cudaEventRecord(w->pev[4], st);
-            CK(cudaMemcpyAsync(w->h_counters, W.counters, (CTR_ROUND_BASE + rounds) * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-            CK(cudaMemcpyAsync(w->h_flags, W.flags, 16, cudaMemcpyDeviceToHost, st));
-            CK(cudaStreamSynchronize(st));
-            for (uint32_t r = first; r < rounds; r++)
-                if (w->h_counters[CTR_ROUND_BASE + r] == 0) { done = true; rounds = r + 1; break; }
-            if (w->h_flags[0]) done = true;
-            n_threads = std::min(n_threads, w->h_counters[CTR_ROUND_BASE + rounds - 1]);
-            if (!done && n_threads == 0) done = true;
-        }
-    } else {
-        CK(cudaMemcpyAsync(w->h_counters, W.counters, CTR_ROUND_BASE * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(w->h_flags, W.flags, 16, cudaMemcpyDeviceToHost, st));
-        CK(cudaStreamSynchronize(st));
+        launch_narrow(W, w->resolve_blocks * 2, st);
+        if (prof) cudaEventRecord(w->pev[4], st);
+        CK(launch_resolve(W, dt, do_euler, w->resolve_blocks, st));
+        w->launches += 7;
+        if (prof) cudaEventRecord(w->pev[5], st);
     }
+    CK(cudaMemcpyAsync(w->h_counters, W.counters, CTR_TOTAL * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(w->h_flags, W.flags, 16, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
     CK(cudaGetLastError());
     *raised = w->h_flags[0];
-    w->stats.n_rounds = rounds;
+    w->stats.n_rounds = w->h_counters[CTR_ROUNDS];
     if (prof) {
-        for (int k = 0; k < 4; k++) { float ms = 0; cudaEventElapsedTime(&ms, w->pev[k], w->pev[k + 1]); w->phase_ms[k] += ms; }
+        for (int k = 0; k < ICX_N_PHASES; k++) { float ms = 0; cudaEventElapsedTime(&ms, w->pev[k], w->pev[k + 1]); w->phase_ms[k] += ms; }
         w->phase_ticks++;
     }
     return ICX_OK;
@@ -158,6 +141,7 @@ int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_
             w->stats.n_candidates = w->h_counters[CTR_CANDIDATES];
             w->stats.n_contacts = w->h_counters[CTR_CONTACTS];
             w->stats.n_interceptions = w->h_counters[CTR_INTERCEPTS];
+            w->stats.n_dirty = w->h_counters[CTR_DIRTY]; w->stats.n_attempts = w->h_counters[CTR_ATTEMPTS] + 1;
             w->stats.margin = W.margin; w->stats.cell_size = W.cell_size; w->stats.max_neighbors = W.max_neighbors;
             w->have_results = do_collide != 0;
             return ICX_OK;
@@ -166,9 +150,19 @@ int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_
         w->stats.n_retries++;
         if (raised & RF_CLIP_OVERFLOW) return fail(w, ICX_E_CAPACITY, "clipped manifold exceeded ICX_MAXV");
         if (raised & RF_NEIGHBOR_OVERFLOW) {
-            if (W.max_neighbors >= 192) return fail(w, ICX_E_CAPACITY, "candidate list exceeded 192 neighbours per collider");
-            W.max_neighbors = std::min<uint32_t>(W.max_neighbors * 2, 192);
-            rc = regrow(w, W.nbr, (size_t)w->cap_packets * W.max_neighbors); if (rc) return rc;
+            if (W.max_neighbors >= 4096) return fail(w, ICX_E_CAPACITY, "candidate list exceeded 4096 neighbours per collider");
+            W.max_neighbors = std::min<uint32_t>(W.max_neighbors * 2, 4096);
+            rc = regrow(w, W.nbr, 2 * (size_t)w->cap_entities * W.max_neighbors); if (rc) return rc;
+        }
+        if (raised & RF_PAIR_OVERFLOW) {
+            if (w->h_counters[CTR_CANDIDATES] > W.max_pairs) {
+                W.max_pairs = std::max<uint32_t>(W.max_pairs * 2, w->h_counters[CTR_CANDIDATES] + w->h_counters[CTR_CANDIDATES] / 4);
+                rc = regrow(w, W.pairs, W.max_pairs); if (rc) return rc;
+            }
+            if (w->h_counters[CTR_STATIC] > W.max_static) {
+                W.max_static = w->h_counters[CTR_STATIC] * 2;
+                rc = regrow(w, W.static_pairs, W.max_static); if (rc) return rc;
+            }
         }
         if (raised & RF_MARGIN_VIOLATED) {
             const float old = W.margin;
@@ -177,7 +171,7 @@ int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_
             set_cell(w, W.cell_size + 2.0f * (W.margin - old));
         }
         if (raised & RF_CELL_TOO_SMALL) {
-            float need; std::memcpy(&need, &w->h_counters[CTR_ROUND_BASE - 1], 4);
+            float need; std::memcpy(&need, &w->h_counters[CTR_NEED_CELL], 4);
             set_cell(w, std::max(need, W.cell_size) * 1.05f);
         }
         if (raised & RF_CONTACT_OVERFLOW) {
@@ -190,6 +184,7 @@ int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_
             W.max_large *= 2;
             rc = regrow(w, W.large_list, W.max_large); if (rc) return rc;
         }
+        if (raised == RF_ROUNDS_EXCEEDED) return fail(w, ICX_E_CAPACITY, "resolve: dependency chain longer than ICX_MAX_ROUNDS");
     }
     return fail(w, ICX_E_CAPACITY, "tick did not converge after 24 capacity/margin retries");
 }
@@ -249,7 +244,9 @@ int icx_world_create(const IcxConfig* cfg, IcxWorld** out)
         w->cap_entities = cfg->max_entities; w->cap_packets = 2 * cfg->max_entities;
         W.margin = cfg->broadphase_margin > 0 ? cfg->broadphase_margin : 0.05f;
         set_cell(w, cfg->cell_size > 0 ? cfg->cell_size : 1.0f);
-        W.max_neighbors = cfg->max_neighbors ? std::min<uint32_t>(cfg->max_neighbors, 192) : 24;
+        W.max_neighbors = cfg->max_neighbors ? std::min<uint32_t>(cfg->max_neighbors, 4096) : 24;
+        W.max_pairs = cfg->max_pairs ? cfg->max_pairs : std::max<uint32_t>(8 * cfg->max_entities, 4096);
+        W.max_static = 4096;
         W.max_large = cfg->max_large ? cfg->max_large : 1024;
         W.max_contacts = cfg->max_contacts ? cfg->max_contacts : std::max<uint32_t>(2 * cfg->max_entities, 1024);
         W.gx = (cfg->flags & ICX_F_NO_GRAVITY) ? 0.0f : cfg->gravity[0];
@@ -315,18 +312,18 @@ int icx_bodies_upload(IcxWorld* w, uint32_t n, const IcxEntity* entity, const Ic
     if (tstate) CK(cudaMemcpyAsync(w->st_ts.ptr, tstate, n, cudaMemcpyHostToDevice, st));
     if (tcoh) CK(cudaMemcpyAsync(w->st_tc.ptr, tcoh, (size_t)n * 2, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(W.first_packet, first.data(), (size_t)n * 4, cudaMemcpyHostToDevice, st));
-    CK(cudaMemsetAsync(W.counters, 0, CTR_ROUND_BASE * sizeof(uint32_t), st));
+    CK(cudaMemsetAsync(W.counters, 0, CTR_TOTAL * sizeof(uint32_t), st));
     W.n_entities = n; W.n_packets = np; w->n_entities = n; w->n_packets = np;
     Mirror M = mirror_of(w);
     if (!P) M.P = nullptr;
     launch_import_kernel(W, M, nullptr, M.ids, M.T, M.P, C ? M.C : nullptr,
                          has_physics ? M.hasP : nullptr, tstate ? (const uint8_t*)w->st_ts.ptr : nullptr,
                          tcoh ? (const uint16_t*)w->st_tc.ptr : nullptr, n, 1, C ? 1 : 0, st);
-    CK(cudaMemcpyAsync(w->h_counters, W.counters, CTR_ROUND_BASE * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(w->h_counters, W.counters, CTR_TOTAL * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));          // `first` and the caller's arrays may be released after return
     CK(cudaGetLastError());
     if (!(w->cfg.cell_size > 0)) {
-        float ext; std::memcpy(&ext, &w->h_counters[CTR_ROUND_BASE - 2], 4);
+        float ext; std::memcpy(&ext, &w->h_counters[CTR_EXTENT], 4);
         if (!(ext > 0)) ext = 1.0f;
         set_cell(w, (ext + 2.0f * W.margin) * 1.02f);
     }
@@ -428,10 +425,10 @@ int icx_profile_enable(IcxWorld* w, int on)
     return ICX_OK;
 }
 
-int icx_phase_ms(IcxWorld* w, double* ms4, uint64_t* n_ticks, uint64_t* n_launches)
+int icx_phase_ms(IcxWorld* w, double* ms, uint64_t* n_ticks, uint64_t* n_launches)
 {
     if (!w) return ICX_E_INVALID;
-    if (ms4) for (int k = 0; k < 4; k++) ms4[k] = w->phase_ms[k];
+    if (ms) for (int k = 0; k < ICX_N_PHASES; k++) ms[k] = w->phase_ms[k];
     if (n_ticks) *n_ticks = w->phase_ticks;
     if (n_launches) *n_launches = w->launches;
     return ICX_OK;
@@ -482,26 +479,17 @@ int icx_pairs_fetch(IcxWorld* w, IcxPair* out, size_t cap, size_t* n)
     if (!w || !n) return ICX_E_INVALID;
     if (!w->have_results) { *n = 0; return ICX_OK; }
     cudaSetDevice(w->device);
-    const DeviceWorld& W = w->W;
-    const uint32_t np = W.n_packets;
-    std::vector<uint32_t> pos_of(np), cnt(np), nbr((size_t)np * W.max_neighbors);
-    CK(cudaMemcpyAsync(pos_of.data(), W.pos_of, (size_t)np * 4, cudaMemcpyDeviceToHost, w->stream));
-    CK(cudaMemcpyAsync(cnt.data(), W.nbr_count, (size_t)np * 4, cudaMemcpyDeviceToHost, w->stream));
-    CK(cudaMemcpyAsync(nbr.data(), W.nbr, nbr.size() * 4, cudaMemcpyDeviceToHost, w->stream));
+    const size_t total = w->stats.n_candidates;
+    *n = total;
+    if (!out || !total) return ICX_OK;
+    std::vector<uint2> raw(total);
+    CK(cudaMemcpyAsync(raw.data(), w->W.pairs, total * sizeof(uint2), cudaMemcpyDeviceToHost, w->stream));
     CK(cudaStreamSynchronize(w->stream));
-    std::vector<uint64_t> keys;
-    for (uint32_t p = 0; p < np; p++) {
-        const uint32_t col = pos_of[p];
-        if (col == 0xFFFFFFFFu) continue;
-        for (uint32_t i = 0; i < cnt[col]; i++) {
-            const uint32_t o = nbr[(size_t)i * np + col] & ICX_NB_INDEX_MASK;
-            keys.push_back(((uint64_t)std::min(p, o) << 32) | std::max(p, o));
-        }
-    }
+    // the generator emits pairs in block order; canonical order is lexicographic on (a, b)
+    std::vector<uint64_t> keys(total);
+    for (size_t i = 0; i < total; i++) keys[i] = ((uint64_t)raw[i].x << 32) | (raw[i].y & ICX_NB_INDEX_MASK);
     std::sort(keys.begin(), keys.end());
-    keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
-    *n = keys.size();
-    if (out) for (size_t i = 0; i < std::min(cap, keys.size()); i++) { out[i].a = (uint32_t)(keys[i] >> 32); out[i].b = (uint32_t)keys[i]; }
+    for (size_t i = 0; i < std::min(cap, total); i++) { out[i].a = (uint32_t)(keys[i] >> 32); out[i].b = (uint32_t)keys[i]; }
     return ICX_OK;
 }
 

@@ -114,7 +114,7 @@ __global__ void __launch_bounds__(128) k_import(DeviceWorld W, Mirror M, const u
                     if (c.colliderType == ICX_COLLIDER_SPHERE) ext = 1.7320509f * sx;
                     else if (c.colliderType == ICX_COLLIDER_RAY) ext = sz * 1.000001f;
                     else ext = sqrtf(sx * sx + sy * sy + sz * sz);
-                    if (ext == ext) atomicMax((int*)&W.counters[CTR_ROUND_BASE - 2], __float_as_int(ext));
+                    if (ext == ext) atomicMax((int*)&W.counters[CTR_EXTENT], __float_as_int(ext));
                 }
             }
         }

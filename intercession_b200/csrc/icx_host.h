@@ -11,7 +11,9 @@ namespace icx {
 void launch_integrate_prep(const DeviceWorld& W, double dt, int do_euler, cudaStream_t st);
 void launch_grid(const DeviceWorld& W, cudaStream_t st);      // 4 kernels: scan x3 + scatter
 void launch_pairs(const DeviceWorld& W, cudaStream_t st);
-void launch_resolve_round(const DeviceWorld& W, int parity, uint32_t ctr_in, uint32_t ctr_out, uint32_t n_threads, cudaStream_t st);
+void launch_narrow(const DeviceWorld& W, int blocks, cudaStream_t st);
+int resolve_grid_blocks(int device);                          // co-resident blocks of the persistent resolve kernel
+cudaError_t launch_resolve(const DeviceWorld& W, double dt, int do_euler, int blocks, cudaStream_t st);
 struct Mirror { uint32_t* ids; IcxTransform* T; IcxPhysics* P; IcxColliderComponent* C; uint8_t* hasP; };
 void launch_import_kernel(const DeviceWorld& W, Mirror M, const uint32_t* index, const uint32_t* ids, const IcxTransform* T,
                           const IcxPhysics* P, const IcxColliderComponent* C, const uint8_t* hasP, const uint8_t* ts,
@@ -54,10 +56,11 @@ struct IcxWorld {
     float last_ms = 0.0f;
     // optional per-phase device timing (icx_profile_enable): integrate_prep | grid sort | pairs | resolve
     bool profile = false;
-    cudaEvent_t pev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
-    double phase_ms[4] = {0, 0, 0, 0};
+    cudaEvent_t pev[ICX_N_PHASES + 1] = {};
+    double phase_ms[ICX_N_PHASES] = {};
     uint64_t phase_ticks = 0;
     uint64_t launches = 0;              // kernels launched by icx_step* since creation
+    int resolve_blocks = 0;
     std::string error;
     bool have_results = false;
 };

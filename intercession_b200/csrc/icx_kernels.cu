@@ -1,31 +1,22 @@
-// Hand-written sm_100a kernels of the physics tick.  One tick =
+// Hand-written sm_100a kernels of the physics tick, part 1 (part 2: icx_resolve.cu).  One tick =
 //   k_integrate_prep   Euler step (euler_physics_relay.h:21-97) fused with per-collider
 //                      composite-transform / bound / grid-bucket derivation
 //   k_scan_*           exclusive scan of the bucket histogram (counting sort)
 //   k_scatter          packets -> bucket-sorted bound array
-//   k_pairs            uniform-grid candidate lists (the broadphase the reference lacks)
-//   k_resolve_round    narrowphase + response + interception, replayed in the reference's
-//                      sequential pair order by a dependency-round schedule
+//   k_pairs            uniform-grid pair generator (the broadphase the reference lacks): flat,
+//                      block-staged, compacted list of candidate pairs
+//   k_narrow           speculative narrowphase of every candidate on the post-integration state;
+//                      marks the bodies that are hit ("dirty")
+//   k_resolve          narrowphase + response + interception for the dirty bodies only, replayed
+//                      in the reference's sequential pair order (DESIGN.md "Ordered resolve")
 // All kernels are HBM / latency bound FP32 CUDA-core work; there is no dense contraction,
 // hence no tensor cores.
 #include "icx_world.cuh"
 #include "icx_math.cuh"
+#include "icx_device.cuh"
 #define ICX_UNIT_RADIUS 0.5f
 
 namespace icx {
-
-__device__ __forceinline__ uint32_t hash_cell(int cx, int cy, int cz, uint32_t wl, uint32_t mask) {
-    uint32_t h = (uint32_t)cx * 73856093u ^ (uint32_t)cy * 19349663u ^ (uint32_t)cz * 83492791u ^ wl * 2654435761u;
-    h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
-    return h & mask;
-}
-
-__device__ __forceinline__ bool can_intersect(int a, int b, uint32_t cfg_flags) {
-    // non-null entries of intersectProcedures, collision_procedures.h:411-417
-    if (a == ICX_COLLIDER_BOX) return b != ICX_COLLIDER_NONE;
-    if (b == ICX_COLLIDER_BOX) return a != ICX_COLLIDER_NONE;
-    return (cfg_flags & ICX_F_SPHERE_SPHERE) && a == ICX_COLLIDER_SPHERE && b == ICX_COLLIDER_SPHERE;
-}
 
 // ---------------------------------------------------------------------------------------
 // K1: Euler integration + per-packet derivation.  One thread per entity.
@@ -36,42 +27,13 @@ __global__ void __launch_bounds__(256) k_integrate_prep(DeviceWorld W, double de
     if (e >= W.n_entities) return;
     const float4 p1 = W.prm1[e];
     const uint32_t ef = __float_as_uint(p1.w);
-    float4 pos = W.in.pos[e], rot = W.in.rot[e], vel = W.in.vel[e], acc = W.in.acc[e];
-    float4 av = W.in.angvel[e], aa = W.in.angacc[e];
-
-    if (do_euler && (ef & EF_HAS_PHYSICS) && !(ef & EF_ASLEEP)) {
-        // EulerPhysicsRelay::engage, euler_physics_relay.h:25-95
-        V3 org = v3(pos), v = v3(vel), a = v3(acc), w = v3(av), al = v3(aa);
-        Q4 q; q.w = rot.x; q.x = rot.y; q.y = rot.z; q.z = rot.w;
-        a = a + v3(W.gx, W.gy, W.gz);                                               // :32
-        if (ef & EF_LOCK_ORIGIN) { v = v3(0.0f, 0.0f, 0.0f); a = v3(0.0f, 0.0f, 0.0f); org = v3(W.locked_pos[e]); }   // :36-46
-        if (ef & EF_LOCK_ORIENTATION) {                                             // :47-57
-            w = v3(0.0f, 0.0f, 0.0f); al = v3(0.0f, 0.0f, 0.0f);
-            float4 lq = W.locked_rot[e]; q.w = lq.x; q.x = lq.y; q.y = lq.z; q.z = lq.w;
-        }
-        const float halfDt = (float)(deltaTime / 2.0f);                             // :62 double divide, then narrowed
-        const float dt = (float)deltaTime;
-#pragma unroll
-        for (int half = 0; half < 2; half++) {
-            org = org + v * halfDt;                                                 // :62 / :80
-            float angularSpeed = length(w);
-            if (angularSpeed != 0.0f) q = qmul(angle_axis(angularSpeed * halfDt, w / angularSpeed), q);   // :65-70
-            if (half == 0) { v = v + a * dt; w = w + al * dt; }                     // :74-75
-        }
-        a = v3(0.0f, 0.0f, 0.0f); al = v3(0.0f, 0.0f, 0.0f);                         // :90-91
-        v = v * (float)(1.0f - p1.x * deltaTime);                                   // :94 evaluated in double, narrowed by glm's *=
-        w = w * (float)(1.0f - p1.y * deltaTime);                                   // :95
-        pos = make_float4(org.x, org.y, org.z, 0.0f);
-        rot = make_float4(q.w, q.x, q.y, q.z);
-        vel = make_float4(v.x, v.y, v.z, 0.0f); acc = make_float4(a.x, a.y, a.z, 0.0f);
-        av = make_float4(w.x, w.y, w.z, 0.0f); aa = make_float4(al.x, al.y, al.z, 0.0f);
-    }
-    W.out.pos[e] = pos; W.out.rot[e] = rot; W.out.vel[e] = vel; W.out.acc[e] = acc;
-    W.out.angvel[e] = av; W.out.angacc[e] = aa;
+    const EntityRegs r = euler_entity(W, e, ef, p1, deltaTime, do_euler);
+    const float4 pos = r.pos, rot = r.rot;
+    W.out.pos[e] = r.pos; W.out.rot[e] = r.rot; W.out.vel[e] = r.vel; W.out.acc[e] = r.acc;
+    W.out.angvel[e] = r.av; W.out.angacc[e] = r.aa;
     W.out.ts[e] = W.in.ts[e];
-    W.pos0[e] = pos;
-    W.head[0][e] = 0u;
-    W.ent_active[e] = 0u;
+    W.pos0[e] = r.pos;
+    W.dirty_slot[e] = ICX_NONE;
 
     // ---- per-collider derivation (ColliderSynchro::update + what every later pair test needs) ----
     const uint32_t fp = W.first_packet[e];
@@ -143,11 +105,11 @@ __global__ void __launch_bounds__(256) k_integrate_prep(DeviceWorld W, double de
                     cell = 0xFFFFFFFEu;     // large
                 } else {
                     atomicOr(W.flags, RF_CELL_TOO_SMALL);
-                    atomicMax((int*)&W.counters[CTR_ROUND_BASE - 1], __float_as_int(ext));   // needed cell size (positive floats order as ints)
+                    atomicMax((int*)&W.counters[CTR_NEED_CELL], __float_as_int(ext));   // needed cell size (positive floats order as ints)
                 }
             } else {
-                const float cxf = (lo.x + hi.x) * 0.5f, cyf = (lo.y + hi.y) * 0.5f, czf = (lo.z + hi.z) * 0.5f;
-                cell = hash_cell((int)floorf(cxf * W.inv_cell), (int)floorf(cyf * W.inv_cell), (int)floorf(czf * W.inv_cell), wl, W.n_buckets - 1);
+                cell = bucket_of(cell_coord(lo.x, hi.x, W.inv_cell), cell_coord(lo.y, hi.y, W.inv_cell),
+                                 cell_coord(lo.z, hi.z, W.inv_cell), wl, W.n_buckets);
                 atomicAdd(&W.cell_count[cell], 1u);
             }
         }
@@ -231,7 +193,7 @@ __global__ void __launch_bounds__(256) k_scatter(DeviceWorld W)
     const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= W.n_packets) return;
     const uint32_t cell = W.pk_cell[p];
-    if (cell >= 0xFFFFFFFEu) { if (cell == 0xFFFFFFFFu) W.pos_of[p] = 0xFFFFFFFFu; return; }   // large columns are assigned by k_pairs_large
+    if (cell >= 0xFFFFFFFEu) return;                    // inert, or in the large-collider list
     const uint32_t pos = W.cell_count[cell] + atomicAdd(&W.cell_fill[cell], 1u);
     const uint32_t e = W.pk_entity[p];
     const uint32_t bits = __float_as_uint(W.pk_lpos[p].w);
@@ -240,110 +202,105 @@ __global__ void __launch_bounds__(256) k_scatter(DeviceWorld W)
     const uint32_t tag = p | ((bits & PF_TYPE_MASK) << 28) | ((ef & EF_IMMUTABLE) ? 0x40000000u : 0u);
     W.s_lo[pos] = make_float4(lo.x, lo.y, lo.z, __uint_as_float(tag));
     W.s_hi[pos] = make_float4(hi.x, hi.y, hi.z, __uint_as_float(e));
-    W.pos_of[p] = pos;
 }
 
 // ---------------------------------------------------------------------------------------
-// K4: candidate lists.  One thread per bucket-sorted packet: visit the 27 neighbouring buckets
-// (deduplicated after hashing) plus the large-collider list, keep partners whose inflated
-// bounds overlap, sorted ascending by packet index (= the order the reference's pair loop
-// meets them, collision_physics_relay.h:29-37).
+// K4: uniform-grid pair generator.  One thread per bucket-sorted packet (then one per large
+// collider): walk the 27 surrounding cells as 9-18 contiguous ranges, keep partners whose inflated
+// bounds overlap, emit each unordered pair once (from its lower sorted position).  Pairs are
+// appended warp-aggregated to a shared-memory stage and flushed with one global atomic per block,
+// so the list is written in coalesced runs.  Entry = (lower packet, higher packet | flags).
 // ---------------------------------------------------------------------------------------
-#define ICX_KMAX 192
+#define PAIRS_TPB 256
+#define PAIRS_STAGE 3072
 
-__device__ __forceinline__ bool overlap(float4 alo, float4 ahi, float4 blo, float4 bhi) {
-    return alo.x <= bhi.x && blo.x <= ahi.x && alo.y <= bhi.y && blo.y <= ahi.y && alo.z <= bhi.z && blo.z <= ahi.z;
+struct PairStage { uint2 buf[PAIRS_STAGE]; uint32_t count, base; };
+
+__device__ __forceinline__ void emit_pair(const DeviceWorld& W, PairStage& S, uint32_t a, uint32_t b, uint32_t flags)
+{
+    const uint2 entry = make_uint2(min(a, b), max(a, b) | flags);
+    const uint32_t m = __activemask(), lane = threadIdx.x & 31u;
+    const int leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if ((int)lane == leader) base = atomicAdd(&S.count, (uint32_t)__popc(m));
+    base = __shfl_sync(m, base, leader);
+    const uint32_t idx = base + __popc(m & ((1u << lane) - 1u));
+    if (idx < PAIRS_STAGE) { S.buf[idx] = entry; return; }
+    const uint32_t g = atomicAdd(&W.counters[CTR_CANDIDATES], 1u);      // stage full (very dense block): straight to global
+    if (g < W.max_pairs) W.pairs[g] = entry; else atomicOr(W.flags, RF_PAIR_OVERFLOW);
 }
 
-__device__ __forceinline__ void list_insert(uint32_t* list, uint32_t& cnt, uint32_t cap, uint32_t entry, bool& overflow)
-{
-    if (cnt >= cap) { overflow = true; return; }
-    uint32_t i = cnt;
-    const uint32_t key = entry & ICX_NB_INDEX_MASK;
-    while (i > 0 && (list[i - 1] & ICX_NB_INDEX_MASK) > key) { list[i] = list[i - 1]; i--; }
-    list[i] = entry; cnt++;
+// un-inflated bounds overlap (with 10 % of the margin kept as slack against rounding): only then can
+// the narrowphase report a hit on the post-integration state (DESIGN.md "Broadphase bound")
+__device__ __forceinline__ bool tight_le(float a, float b, float m2) {
+    const float s = m2 - 2.0e-6f * (fabsf(a) + fabsf(b));
+    return a + fmaxf(s, 0.0f) <= b;
+}
+__device__ __forceinline__ bool tight_overlap(float4 alo, float4 ahi, float4 blo, float4 bhi, float margin) {
+    const float m2 = 1.8f * margin;
+    return tight_le(alo.x, bhi.x, m2) && tight_le(blo.x, ahi.x, m2) && tight_le(alo.y, bhi.y, m2) && tight_le(blo.y, ahi.y, m2) &&
+           tight_le(alo.z, bhi.z, m2) && tight_le(blo.z, ahi.z, m2);
 }
 
-__global__ void __launch_bounds__(128) k_pairs(DeviceWorld W)
+__global__ void __launch_bounds__(PAIRS_TPB) k_pairs(DeviceWorld W)
 {
+    __shared__ PairStage S;
+    if (threadIdx.x == 0) S.count = 0;
+    __syncthreads();
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t n_grid = W.cell_count[W.n_buckets];
     const uint32_t n_large = min(W.counters[CTR_LARGE], W.max_large);
-    if (t >= n_grid + n_large) return;
-    uint32_t list[ICX_KMAX];
-    uint32_t cnt = 0; bool overflow = false;
-    const uint32_t cap = W.max_neighbors;
-    uint32_t p, e; int type; bool immut; float4 lo, hi;
-    if (t < n_grid) {
-        lo = W.s_lo[t]; hi = W.s_hi[t];
-        const uint32_t tag = __float_as_uint(lo.w);
-        p = tag & ICX_NB_INDEX_MASK; type = (tag >> 28) & 3; immut = (tag & 0x40000000u) != 0;
-        e = __float_as_uint(hi.w);
-    } else {
-        p = W.large_list[t - n_grid];
-        lo = W.pk_lo[p]; hi = W.pk_hi[p];
-        e = W.pk_entity[p]; type = __float_as_uint(W.pk_lpos[p].w) & PF_TYPE_MASK; immut = true;
-        W.pos_of[p] = t;
-    }
-    const uint32_t wl = W.worldline_stride ? e / W.worldline_stride : 0u;
-
-    if (t < n_grid) {
-        const float cxf = (lo.x + hi.x) * 0.5f, cyf = (lo.y + hi.y) * 0.5f, czf = (lo.z + hi.z) * 0.5f;
-        const int cx = (int)floorf(cxf * W.inv_cell), cy = (int)floorf(cyf * W.inv_cell), cz = (int)floorf(czf * W.inv_cell);
-        uint32_t seen[27]; int n_seen = 0;
-        for (int dz = -1; dz <= 1; dz++) for (int dy = -1; dy <= 1; dy++) for (int dx = -1; dx <= 1; dx++) {
-            const uint32_t hsh = hash_cell(cx + dx, cy + dy, cz + dz, wl, W.n_buckets - 1);
-            bool dup = false;
-            for (int s = 0; s < n_seen; s++) dup |= (seen[s] == hsh);
-            if (dup) continue;
-            seen[n_seen++] = hsh;
-            const uint32_t beg = W.cell_count[hsh], end = W.cell_count[hsh + 1];
-            for (uint32_t j = beg; j < end; j++) {
-                if (j == t) continue;
-                const float4 blo = W.s_lo[j], bhi = W.s_hi[j];
-                const uint32_t btag = __float_as_uint(blo.w);
-                const uint32_t be = __float_as_uint(bhi.w);
-                if (be == e) continue;                                               // same entity, relay :51
-                const bool bimmut = (btag & 0x40000000u) != 0;
-                if (immut && !bimmut) continue;         // an immutable body never drives a pair with a mutable one
-                if (W.worldline_stride && be / W.worldline_stride != wl) continue;
-                if (!can_intersect(type, (btag >> 28) & 3, W.cfg_flags)) continue;
-                if (!overlap(lo, hi, blo, bhi)) continue;
-                list_insert(list, cnt, cap, (btag & ICX_NB_INDEX_MASK) | (bimmut ? ICX_NB_IMMUTABLE : 0u), overflow);
-            }
+    if (t < n_grid + n_large) {
+        uint32_t p, e; int type; bool immut; float4 lo, hi;
+        if (t < n_grid) {
+            lo = W.s_lo[t]; hi = W.s_hi[t];
+            const uint32_t tag = __float_as_uint(lo.w);
+            p = tag & ICX_NB_INDEX_MASK; type = (tag >> 28) & 3; immut = (tag & 0x40000000u) != 0;
+            e = __float_as_uint(hi.w);
+        } else {
+            p = W.large_list[t - n_grid];
+            lo = W.pk_lo[p]; hi = W.pk_hi[p];
+            e = W.pk_entity[p]; type = __float_as_uint(W.pk_lpos[p].w) & PF_TYPE_MASK; immut = true;
+        }
+        const uint32_t wl = W.worldline_stride ? e / W.worldline_stride : 0u;
+        if (t < n_grid) {
+            for_each_neighbor(W, cell_coord(lo.x, hi.x, W.inv_cell), cell_coord(lo.y, hi.y, W.inv_cell), cell_coord(lo.z, hi.z, W.inv_cell), wl,
+                [&](uint32_t j) {
+                    if (j <= t) return;                                             // each pair once, from its lower sorted position
+                    const float4 blo = W.s_lo[j], bhi = W.s_hi[j];
+                    if (!overlap(lo, hi, blo, bhi)) return;
+                    const uint32_t btag = __float_as_uint(blo.w), be = __float_as_uint(bhi.w);
+                    if (be == e) return;                                            // same entity, relay :51
+                    if (W.worldline_stride && be / W.worldline_stride != wl) return;
+                    if (!can_intersect(type, (btag >> 28) & 3, W.cfg_flags)) return;
+                    const bool bimmut = (btag & 0x40000000u) != 0;
+                    emit_pair(W, S, p, btag & ICX_NB_INDEX_MASK,
+                              (tight_overlap(lo, hi, blo, bhi, W.margin) ? ICX_PAIR_TIGHT : 0u) | ((immut && bimmut) ? ICX_PAIR_STATIC : 0u));
+                });
+        }
+        // large colliders (all immutable): every grid packet tests them; large ones test the later large ones
+        for (uint32_t k = (t < n_grid ? 0u : t - n_grid + 1u); k < n_large; k++) {
+            const uint32_t q = W.large_list[k];
+            const uint32_t qe = W.pk_entity[q];
+            if (qe == e) continue;
+            if (W.worldline_stride && qe / W.worldline_stride != wl) continue;
+            const int qtype = __float_as_uint(W.pk_lpos[q].w) & PF_TYPE_MASK;
+            if (!can_intersect(type, qtype, W.cfg_flags)) continue;
+            const float4 qlo = W.pk_lo[q], qhi = W.pk_hi[q];
+            if (!overlap(lo, hi, qlo, qhi)) continue;
+            emit_pair(W, S, p, q, (tight_overlap(lo, hi, qlo, qhi, W.margin) ? ICX_PAIR_TIGHT : 0u) | (immut ? ICX_PAIR_STATIC : 0u));
         }
     }
-    // large colliders (all immutable): everyone tests them; large ones test only each other
-    for (uint32_t k = 0; k < n_large; k++) {
-        const uint32_t q = W.large_list[k];
-        if (q == p) continue;
-        const uint32_t qe = W.pk_entity[q];
-        if (qe == e) continue;
-        if (W.worldline_stride && qe / W.worldline_stride != wl) continue;
-        const int qtype = __float_as_uint(W.pk_lpos[q].w) & PF_TYPE_MASK;
-        if (!can_intersect(type, qtype, W.cfg_flags)) continue;
-        if (!overlap(lo, hi, W.pk_lo[q], W.pk_hi[q])) continue;
-        list_insert(list, cnt, cap, q | ICX_NB_IMMUTABLE | ICX_NB_LARGE, overflow);
-    }
-    if (overflow) atomicOr(W.flags, RF_NEIGHBOR_OVERFLOW);
-    W.nbr_count[t] = cnt;
-    uint32_t upper = 0;
-    for (uint32_t i = 0; i < cnt; i++) {
-        W.nbr[(size_t)i * W.n_packets + t] = list[i];
-        // count each pair once: from its lower packet, or from the driving side of an immutable pair
-        const uint32_t o = list[i] & ICX_NB_INDEX_MASK;
-        const bool oimm = (list[i] & ICX_NB_IMMUTABLE) != 0;
-        if (!immut && oimm) upper++;                    // only I list it
-        else if (immut && oimm) { const bool olarge = (list[i] & ICX_NB_LARGE) != 0, ilarge = t >= n_grid;
-                                  if (ilarge == olarge ? p < o : !ilarge) upper++; }
-        else if (o > p) upper++;
-    }
-    if (upper) atomicAdd(&W.counters[CTR_CANDIDATES], upper);
-    if (cnt > 0 && atomicExch(&W.ent_active[e], 1u) == 0u) {
-        const uint32_t idx = atomicAdd(&W.counters[CTR_ACTIVE0], 1u);
-        W.active[0][idx] = e;
+    __syncthreads();
+    const uint32_t n = min(S.count, (uint32_t)PAIRS_STAGE);
+    if (threadIdx.x == 0 && n) S.base = atomicAdd(&W.counters[CTR_CANDIDATES], n);
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
+        const uint32_t g = S.base + i;
+        if (g < W.max_pairs) W.pairs[g] = S.buf[i]; else atomicOr(W.flags, RF_PAIR_OVERFLOW);
     }
 }
+
 
 // ---- launchers ------------------------------------------------------------------------
 void launch_integrate_prep(const DeviceWorld& W, double dt, int do_euler, cudaStream_t st)
@@ -366,7 +323,7 @@ void launch_grid(const DeviceWorld& W, cudaStream_t st)
 void launch_pairs(const DeviceWorld& W, cudaStream_t st)
 {
     if (W.n_packets == 0) return;
-    k_pairs<<<(W.n_packets + 127) / 128, 128, 0, st>>>(W);
+    k_pairs<<<(W.n_packets + PAIRS_TPB - 1) / PAIRS_TPB, PAIRS_TPB, 0, st>>>(W);
 }
 
 } // namespace icx

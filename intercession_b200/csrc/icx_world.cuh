@@ -29,10 +29,17 @@ enum : uint32_t {
     PF_SLOT             = 1u << 9,
 };
 
-// neighbour-list entry: other packet index in the low 28 bits, then
+// neighbour-list entry of a dirty body: other packet index in the low 28 bits, then
 #define ICX_NB_INDEX_MASK 0x0FFFFFFFu
-#define ICX_NB_IMMUTABLE  0x10000000u     // other packet's entity is immutable
-#define ICX_NB_LARGE      0x20000000u     // other packet is in the large-collider list
+#define ICX_NB_IMMUTABLE  0x10000000u     // other packet's entity is immutable (never written, no ordering)
+// flat broadphase pair entry (uint2: x = lower packet, y = higher packet | flags)
+#define ICX_PAIR_TIGHT    0x80000000u     // un-inflated bounds overlap too: the narrowphase can hit
+#define ICX_PAIR_STATIC   0x40000000u     // both bodies immutable
+#define ICX_NONE          0xFFFFFFFFu
+// grid: 2^ICX_XB x-adjacent cells of one (y,z,world-line) row share a hashed block of buckets, so
+// the 3 x-neighbours of a cell are one contiguous range of the bucket-sorted array
+#define ICX_XB 4
+#define ICX_XMASK ((1 << ICX_XB) - 1)
 
 // error / retry flags raised by kernels (World::d_flags)
 enum : uint32_t {
@@ -42,6 +49,8 @@ enum : uint32_t {
     RF_CONTACT_OVERFLOW  = 1u << 3,
     RF_LARGE_OVERFLOW    = 1u << 4,
     RF_CLIP_OVERFLOW     = 1u << 5,
+    RF_PAIR_OVERFLOW     = 1u << 6,   // the flat pair list / static-pair list exceeded its capacity
+    RF_ROUNDS_EXCEEDED   = 1u << 7,
 };
 
 // mutable entity state: one buffer is the tick input, the other the tick output
@@ -86,16 +95,20 @@ struct DeviceWorld {
     uint32_t* cell_count;           // [n_buckets + 1] -> exclusive scan in place = cell_start
     uint32_t* cell_fill;
     uint32_t* scan_partial;
-    float4* s_lo;                   // sorted by bucket: lo.xyz, asfloat(packet | flags)
+    float4* s_lo;                   // sorted by bucket: lo.xyz, asfloat(packet | type << 28 | immutable << 30)
     float4* s_hi;                   // hi.xyz, asfloat(entity index)
-    uint32_t* pos_of;               // packet -> sorted position (list owner column)
     uint32_t* large_list;           // packets larger than a cell (immutable only)
-    // candidate lists, column-major: nbr[i * n_packets + column]
-    uint32_t* nbr; uint32_t* nbr_count; uint32_t max_neighbors;
-    // ordered resolve
-    uint32_t* head[2];              // per entity: consumed entries of slot-0 list | slot-1 list << 16
-    uint32_t* active[2];            // entity work lists
-    uint32_t* ent_active;           // dedupe flag while building active[0]
+    // flat candidate pair list (the broadphase output, icx_pairs_fetch)
+    uint2* pairs; uint32_t max_pairs;
+    uint2* static_pairs; uint32_t max_static;    // hits between two immutable bodies (contact records only)
+    // bodies touched by at least one hit ("dirty"): only these need the reference's sequential order
+    uint32_t* dirty_slot;           // per entity: index into dirty_list, ICX_NONE = clean
+    uint32_t* dirty_list;           // entity indices, arbitrary order
+    uint32_t* nbr;                  // sorted candidate lists of dirty bodies: nbr[(slot * 2 + k) * max_neighbors + i]
+    uint32_t* nbr_count;            // [slot * 2 + k]
+    uint32_t max_neighbors;
+    uint32_t* head[2];              // per dirty slot: consumed entries of the slot-0 list | slot-1 list << 16
+    uint32_t* active[2];            // dirty-slot work lists of the dependency rounds
     // outputs
     IcxContact* contacts; IcxInterception* intercepts; uint2* intercept_key; uint32_t max_contacts;
     // counters, one cache line each would be nicer; they are cold
@@ -108,7 +121,14 @@ struct DeviceWorld {
     uint16_t coherency;
 };
 
-enum { CTR_LARGE = 0, CTR_ACTIVE0 = 1, CTR_CONTACTS = 2, CTR_INTERCEPTS = 3, CTR_CANDIDATES = 4,
-       CTR_ROUND_BASE = 8, CTR_MAX_ROUNDS = 4096, CTR_TOTAL = CTR_ROUND_BASE + CTR_MAX_ROUNDS + 8 };
+enum { CTR_LARGE = 0, CTR_DIRTY = 1, CTR_CONTACTS = 2, CTR_INTERCEPTS = 3, CTR_CANDIDATES = 4, CTR_STATIC = 5,
+       CTR_LISTED = 6,          // dirty bodies whose candidate lists are built
+       CTR_ROUNDS = 7, CTR_ATTEMPTS = 8, CTR_NEW_DIRTY = 9, CTR_TIGHT = 10,
+       CTR_NEED_CELL = 11,      // float bits: cell size a too-large mutable collider needs
+       CTR_EXTENT = 12,         // float bits: largest collider extent seen at import
+       CTR_ACTIVE = 13,         // 3 rotating work-list counters: CTR_ACTIVE + (round % 3)
+       CTR_BARRIER = 16,        // 2 words: arrival count, generation
+       CTR_TOTAL = 32 };
+#define ICX_MAX_ROUNDS 65535u
 
 } // namespace icx

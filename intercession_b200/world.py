@@ -131,8 +131,8 @@ class World:
 
     def phases(self):
         """({phase: accumulated ms}, ticks profiled, kernels launched since creation)."""
-        ms = (C.c_double * 4)()
+        ms = (C.c_double * 5)()
         nt, nl = C.c_uint64(0), C.c_uint64(0)
         self._ck(self.lib.icx_phase_ms(self.handle, ms, C.byref(nt), C.byref(nl)))
-        names = ("integrate_prep", "grid_sort", "pairs", "resolve")
+        names = ("integrate_prep", "grid_sort", "pairs", "narrow", "resolve")
         return dict(zip(names, list(ms))), nt.value, nl.value

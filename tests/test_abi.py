@@ -59,7 +59,7 @@ def test_struct_layouts_match_reference_components():
     assert [f[k][1] for k in ("colliderType", "collisionType", "isActive", "useBehaviorsResponse", "localTransform",
                               "inheritOrientation", "influenceOrientation", "minParametricValue", "staticFriction",
                               "dynamicFriction", "restitution", "stiffness", "damping", "restLength")] == [0, 4, 8, 9, 12, 52, 53, 56, 60, 64, 68, 72, 76, 80]
-    assert C.sizeof(abi.IcxConfig) == 56 and C.sizeof(abi.IcxStats) == 56
+    assert C.sizeof(abi.IcxConfig) == 60 and C.sizeof(abi.IcxStats) == 64
 
 
 def test_entity_id_helpers():
