@@ -280,6 +280,11 @@ ICX_API int icx_last_step_ms(IcxWorld* w, float* ms);
 ICX_API int icx_profile_enable(IcxWorld* w, int on);
 ICX_API int icx_phase_ms(IcxWorld* w, double* ms, uint64_t* n_ticks, uint64_t* n_launches);
 
+/* Device-side timeline of the last ordered resolve (pairs of {globaltimer ns, tag}); tags:
+ * 0 start, 0x1nnnn lists built / bodies reset (nnnn = dirty bodies), 0x2.... barrier passed,
+ * 0x3nnnn round finished (nnnn = bodies active in it), 0x4.... end.  enable != 0 turns recording on. */
+ICX_API int icx_debug_trace(IcxWorld* w, int enable, uint64_t* out, size_t cap, size_t* n);
+
 /* CUDA stream of the world as a void* (cudaStream_t), for callers that time it. */
 ICX_API void* icx_world_stream(IcxWorld* w);
 

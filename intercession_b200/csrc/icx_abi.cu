@@ -53,7 +53,7 @@ int allocate(IcxWorld* w)
     CK(alloc(w, W.scan_partial, 4096 + 8));
     CK(alloc(w, W.s_lo, np)); CK(alloc(w, W.s_hi, np));
     CK(alloc(w, W.large_list, W.max_large));
-    CK(alloc(w, W.pairs, W.max_pairs)); CK(alloc(w, W.static_pairs, W.max_static));
+    CK(alloc(w, W.pairs, W.max_pairs)); CK(alloc(w, W.tight, W.max_pairs)); CK(alloc(w, W.static_pairs, W.max_static));
     CK(alloc(w, W.dirty_slot, ne)); CK(alloc(w, W.dirty_list, ne));
     CK(alloc(w, W.nbr, 2 * ne * (size_t)W.max_neighbors)); CK(alloc(w, W.nbr_count, 2 * ne));
     CK(alloc(w, W.head[0], ne)); CK(alloc(w, W.head[1], ne));
@@ -61,6 +61,7 @@ int allocate(IcxWorld* w)
     CK(alloc(w, W.contacts, W.max_contacts)); CK(alloc(w, W.intercepts, W.max_contacts)); CK(alloc(w, W.intercept_key, W.max_contacts));
     CK(alloc(w, W.counters, CTR_TOTAL)); CK(alloc(w, W.flags, 4));
     CK(cudaMemset(W.counters, 0, CTR_TOTAL * sizeof(uint32_t))); CK(cudaMemset(W.flags, 0, 16));
+    W.trace = nullptr;
     w->resolve_blocks = resolve_grid_blocks(w->device);
     if (w->resolve_blocks <= 0) return fail(w, ICX_E_CUDA, "k_resolve cannot be made resident");
     CK(cudaMallocHost((void**)&w->h_counters, CTR_TOTAL * sizeof(uint32_t)));
@@ -158,6 +159,7 @@ int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_
             if (w->h_counters[CTR_CANDIDATES] > W.max_pairs) {
                 W.max_pairs = std::max<uint32_t>(W.max_pairs * 2, w->h_counters[CTR_CANDIDATES] + w->h_counters[CTR_CANDIDATES] / 4);
                 rc = regrow(w, W.pairs, W.max_pairs); if (rc) return rc;
+                rc = regrow(w, W.tight, W.max_pairs); if (rc) return rc;
             }
             if (w->h_counters[CTR_STATIC] > W.max_static) {
                 W.max_static = w->h_counters[CTR_STATIC] * 2;
@@ -431,6 +433,24 @@ int icx_phase_ms(IcxWorld* w, double* ms, uint64_t* n_ticks, uint64_t* n_launche
     if (ms) for (int k = 0; k < ICX_N_PHASES; k++) ms[k] = w->phase_ms[k];
     if (n_ticks) *n_ticks = w->phase_ticks;
     if (n_launches) *n_launches = w->launches;
+    return ICX_OK;
+}
+
+int icx_debug_trace(IcxWorld* w, int enable, uint64_t* out, size_t cap, size_t* n)
+{
+    if (!w) return ICX_E_INVALID;
+    cudaSetDevice(w->device);
+    if (enable && !w->W.trace) { CK(alloc(w, w->W.trace, ICX_TRACE_CAP)); CK(cudaMemset(w->W.trace, 0, ICX_TRACE_CAP * 8)); }
+    if (n) *n = 0;
+    if (out && w->W.trace) {
+        std::vector<unsigned long long> tmp(ICX_TRACE_CAP);
+        CK(cudaMemcpyAsync(tmp.data(), w->W.trace, ICX_TRACE_CAP * 8, cudaMemcpyDeviceToHost, w->stream));
+        CK(cudaStreamSynchronize(w->stream));
+        const size_t used = std::min<size_t>(tmp[0], ICX_TRACE_CAP);
+        for (size_t i = 2; i < used && i - 2 < cap; i++) out[i - 2] = tmp[i];
+        if (n) *n = used >= 2 ? used - 2 : 0;
+    }
+    if (!enable) w->W.trace = nullptr;       // stays allocated in the pool
     return ICX_OK;
 }
 

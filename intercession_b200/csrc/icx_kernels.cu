@@ -212,22 +212,35 @@ __global__ void __launch_bounds__(256) k_scatter(DeviceWorld W)
 // so the list is written in coalesced runs.  Entry = (lower packet, higher packet | flags).
 // ---------------------------------------------------------------------------------------
 #define PAIRS_TPB 256
-#define PAIRS_STAGE 3072
+#define STAGE_TIGHT 1024
+#define STAGE_LOOSE 2048
 
-struct PairStage { uint2 buf[PAIRS_STAGE]; uint32_t count, base; };
+struct PairStage { uint2 tight[STAGE_TIGHT]; uint2 loose[STAGE_LOOSE]; uint32_t n_tight, n_loose, base_all, base_tight; };
 
-__device__ __forceinline__ void emit_pair(const DeviceWorld& W, PairStage& S, uint32_t a, uint32_t b, uint32_t flags)
+__device__ __forceinline__ void put_global(const DeviceWorld& W, uint2 entry, bool tight)
 {
-    const uint2 entry = make_uint2(min(a, b), max(a, b) | flags);
-    const uint32_t m = __activemask(), lane = threadIdx.x & 31u;
-    const int leader = __ffs(m) - 1;
-    uint32_t base = 0;
-    if ((int)lane == leader) base = atomicAdd(&S.count, (uint32_t)__popc(m));
-    base = __shfl_sync(m, base, leader);
-    const uint32_t idx = base + __popc(m & ((1u << lane) - 1u));
-    if (idx < PAIRS_STAGE) { S.buf[idx] = entry; return; }
-    const uint32_t g = atomicAdd(&W.counters[CTR_CANDIDATES], 1u);      // stage full (very dense block): straight to global
+    const uint32_t g = atomicAdd(&W.counters[CTR_CANDIDATES], 1u);
     if (g < W.max_pairs) W.pairs[g] = entry; else atomicOr(W.flags, RF_PAIR_OVERFLOW);
+    if (tight) {
+        const uint32_t q = atomicAdd(&W.counters[CTR_TIGHT], 1u);
+        if (q < W.max_pairs) W.tight[q] = entry; else atomicOr(W.flags, RF_PAIR_OVERFLOW);
+    }
+}
+
+// warp-aggregated append to the block's shared-memory stage (tight and loose pairs separately)
+__device__ __forceinline__ void emit_pair(const DeviceWorld& W, PairStage& S, uint32_t a, uint32_t b, bool tight, uint32_t flags)
+{
+    const uint2 entry = make_uint2(min(a, b), max(a, b) | flags | (tight ? ICX_PAIR_TIGHT : 0u));
+    const uint32_t m = __activemask(), lane = threadIdx.x & 31u;
+    const uint32_t mt = __ballot_sync(m, tight);
+    const uint32_t grp = tight ? mt : (m & ~mt);
+    const int leader = __ffs(grp) - 1;
+    uint32_t base = 0;
+    if ((int)lane == leader) base = atomicAdd(tight ? &S.n_tight : &S.n_loose, (uint32_t)__popc(grp));
+    base = __shfl_sync(grp, base, leader);
+    const uint32_t idx = base + __popc(grp & ((1u << lane) - 1u));
+    if (tight) { if (idx < STAGE_TIGHT) S.tight[idx] = entry; else put_global(W, entry, true); }
+    else { if (idx < STAGE_LOOSE) S.loose[idx] = entry; else put_global(W, entry, false); }
 }
 
 // un-inflated bounds overlap (with 10 % of the margin kept as slack against rounding): only then can
@@ -245,7 +258,7 @@ __device__ __forceinline__ bool tight_overlap(float4 alo, float4 ahi, float4 blo
 __global__ void __launch_bounds__(PAIRS_TPB) k_pairs(DeviceWorld W)
 {
     __shared__ PairStage S;
-    if (threadIdx.x == 0) S.count = 0;
+    if (threadIdx.x == 0) { S.n_tight = 0; S.n_loose = 0; }
     __syncthreads();
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t n_grid = W.cell_count[W.n_buckets];
@@ -264,19 +277,40 @@ __global__ void __launch_bounds__(PAIRS_TPB) k_pairs(DeviceWorld W)
         }
         const uint32_t wl = W.worldline_stride ? e / W.worldline_stride : 0u;
         if (t < n_grid) {
-            for_each_neighbor(W, cell_coord(lo.x, hi.x, W.inv_cell), cell_coord(lo.y, hi.y, W.inv_cell), cell_coord(lo.z, hi.z, W.inv_cell), wl,
-                [&](uint32_t j) {
-                    if (j <= t) return;                                             // each pair once, from its lower sorted position
-                    const float4 blo = W.s_lo[j], bhi = W.s_hi[j];
-                    if (!overlap(lo, hi, blo, bhi)) return;
-                    const uint32_t btag = __float_as_uint(blo.w), be = __float_as_uint(bhi.w);
-                    if (be == e) return;                                            // same entity, relay :51
-                    if (W.worldline_stride && be / W.worldline_stride != wl) return;
-                    if (!can_intersect(type, (btag >> 28) & 3, W.cfg_flags)) return;
-                    const bool bimmut = (btag & 0x40000000u) != 0;
-                    emit_pair(W, S, p, btag & ICX_NB_INDEX_MASK,
-                              (tight_overlap(lo, hi, blo, bhi, W.margin) ? ICX_PAIR_TIGHT : 0u) | ((immut && bimmut) ? ICX_PAIR_STATIC : 0u));
-                });
+            // forward half of the 27-cell neighbourhood: rows (dz, dy) >= (0, 0); a pair is emitted by
+            // the packet whose cell comes first in (z, y, x) order, ties by sorted position
+            const int cx = cell_coord(lo.x, hi.x, W.inv_cell), cy = cell_coord(lo.y, hi.y, W.inv_cell), cz = cell_coord(lo.z, hi.z, W.inv_cell);
+            const int xb0 = (cx - 1) >> ICX_XB, xb1 = (cx + 1) >> ICX_XB;
+            uint32_t seen[10]; int n_seen = 0;
+#pragma unroll 1
+            for (int r = 4; r < 9; r++) {
+                const int dy = r % 3 - 1, dz = r / 3 - 1;
+                for (int xb = xb0; xb <= xb1; xb++) {
+                    const uint32_t block = row_block(xb, cy + dy, cz + dz, wl, W.n_buckets);
+                    const uint32_t key = block * 2u + (uint32_t)(xb - xb0);
+                    bool dup = false;
+                    for (int q = 0; q < n_seen; q++) dup |= (seen[q] == key);
+                    if (dup) continue;
+                    seen[n_seen++] = key;
+                    const int x_lo = max(cx - 1, xb << ICX_XB), x_hi = min(cx + 1, (xb << ICX_XB) + ICX_XMASK);
+                    const uint32_t beg = W.cell_count[(block << ICX_XB) | (uint32_t)(x_lo & ICX_XMASK)];
+                    const uint32_t end = W.cell_count[((block << ICX_XB) | (uint32_t)(x_hi & ICX_XMASK)) + 1u];
+                    for (uint32_t j = beg; j < end; j++) {
+                        if (j == t) continue;
+                        const float4 blo = W.s_lo[j], bhi = W.s_hi[j];
+                        if (!overlap(lo, hi, blo, bhi)) continue;
+                        const uint32_t btag = __float_as_uint(blo.w), be = __float_as_uint(bhi.w);
+                        if (be == e) continue;                                      // same entity, relay :51
+                        if (W.worldline_stride && be / W.worldline_stride != wl) continue;
+                        if (!can_intersect(type, (btag >> 28) & 3, W.cfg_flags)) continue;
+                        const int bx = cell_coord(blo.x, bhi.x, W.inv_cell), by = cell_coord(blo.y, bhi.y, W.inv_cell), bz = cell_coord(blo.z, bhi.z, W.inv_cell);
+                        const bool mine = bz != cz ? bz > cz : (by != cy ? by > cy : (bx != cx ? bx > cx : j > t));
+                        if (!mine) continue;
+                        const bool bimmut = (btag & 0x40000000u) != 0;
+                        emit_pair(W, S, p, btag & ICX_NB_INDEX_MASK, tight_overlap(lo, hi, blo, bhi, W.margin), (immut && bimmut) ? ICX_PAIR_STATIC : 0u);
+                    }
+                }
+            }
         }
         // large colliders (all immutable): every grid packet tests them; large ones test the later large ones
         for (uint32_t k = (t < n_grid ? 0u : t - n_grid + 1u); k < n_large; k++) {
@@ -288,19 +322,23 @@ __global__ void __launch_bounds__(PAIRS_TPB) k_pairs(DeviceWorld W)
             if (!can_intersect(type, qtype, W.cfg_flags)) continue;
             const float4 qlo = W.pk_lo[q], qhi = W.pk_hi[q];
             if (!overlap(lo, hi, qlo, qhi)) continue;
-            emit_pair(W, S, p, q, (tight_overlap(lo, hi, qlo, qhi, W.margin) ? ICX_PAIR_TIGHT : 0u) | (immut ? ICX_PAIR_STATIC : 0u));
+            emit_pair(W, S, p, q, tight_overlap(lo, hi, qlo, qhi, W.margin), immut ? ICX_PAIR_STATIC : 0u);
         }
     }
     __syncthreads();
-    const uint32_t n = min(S.count, (uint32_t)PAIRS_STAGE);
-    if (threadIdx.x == 0 && n) S.base = atomicAdd(&W.counters[CTR_CANDIDATES], n);
+    const uint32_t nt = min(S.n_tight, (uint32_t)STAGE_TIGHT), nl = min(S.n_loose, (uint32_t)STAGE_LOOSE);
+    if (threadIdx.x == 0) {
+        if (nt + nl) S.base_all = atomicAdd(&W.counters[CTR_CANDIDATES], nt + nl);
+        if (nt) S.base_tight = atomicAdd(&W.counters[CTR_TIGHT], nt);
+    }
     __syncthreads();
-    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
-        const uint32_t g = S.base + i;
-        if (g < W.max_pairs) W.pairs[g] = S.buf[i]; else atomicOr(W.flags, RF_PAIR_OVERFLOW);
+    for (uint32_t i = threadIdx.x; i < nt + nl; i += blockDim.x) {
+        const uint2 entry = i < nt ? S.tight[i] : S.loose[i - nt];
+        const uint32_t g = S.base_all + i;
+        if (g < W.max_pairs) W.pairs[g] = entry; else atomicOr(W.flags, RF_PAIR_OVERFLOW);
+        if (i < nt) { const uint32_t q = S.base_tight + i; if (q < W.max_pairs) W.tight[q] = entry; else atomicOr(W.flags, RF_PAIR_OVERFLOW); }
     }
 }
-
 
 // ---- launchers ------------------------------------------------------------------------
 void launch_integrate_prep(const DeviceWorld& W, double dt, int do_euler, cudaStream_t st)

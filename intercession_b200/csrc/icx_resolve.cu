@@ -73,6 +73,60 @@ __device__ __forceinline__ Shape load_shape(const float4* d, V3 origin, int type
 
 __device__ __forceinline__ bool divergent(uint32_t s) { return s == ICX_TS_FORKING || s == ICX_TS_FORKED; }   // timestream_state.h:41-44
 
+// Conservative, cheap stand-in for the 15-axis SAT of box_box / sphere_box_intersect
+// (collision_procedures.cpp:41-120): false only if some axis separates the two shapes by clearly
+// more than rounding noise, in which case the reference's own (normalised, differently rounded)
+// test on that axis reports penetration <= 0 as well.  True means "may hit": the exact procedure
+// decides.  Used to pick the dirty set and to skip exact tests; never to produce a result.
+// slack > 0 also keeps pairs closer than slack (world units): the speculative pass uses it to
+// pre-mark bodies a neighbour may be pushed into, which saves replay restarts.
+// Penetration on axis L is rA(L) + rB(L) - |(cA - cB).L| and its sign does not depend on |L|.
+__device__ __forceinline__ float box_radius(V3 c0, V3 c1, V3 c2, V3 L) { return 0.5f * (fabsf(dot(c0, L)) + fabsf(dot(c1, L)) + fabsf(dot(c2, L))); }
+
+__device__ __forceinline__ bool sat_may_hit(const float4* __restrict__ dA, const float4* __restrict__ dB, V3 posA, V3 posB, int tA, int tB, float slack)
+{
+    const float4 a0 = dA[0], a1 = dA[1], a2 = dA[2], a3 = dA[3], a4 = dA[4], a5 = dA[5];
+    const float4 b0 = dB[0], b1 = dB[1], b2 = dB[2], b3 = dB[3], b4 = dB[4], b5 = dB[5];
+    const V3 A0 = v3(a0), A1 = v3(a1), A2 = v3(a2), B0 = v3(b0), B1 = v3(b1), B2 = v3(b2);
+    const V3 cA = v3(a0.w, a1.w, a2.w) + posA, cB = v3(b0.w, b1.w, b2.w) + posB;
+    const V3 d = cA - cB;
+    const float cmag = fabsf(cA.x) + fabsf(cA.y) + fabsf(cA.z) + fabsf(cB.x) + fabsf(cB.y) + fabsf(cB.z);
+    const float sphA = tA == ICX_COLLIDER_SPHERE ? 0.5f * sqrtf(dot(A0, A0)) : -1.0f;       // project_sphere radius, :97
+    const float sphB = tB == ICX_COLLIDER_SPHERE ? 0.5f * sqrtf(dot(B0, B0)) : -1.0f;
+    // face normals: rows of the inverse linear part (columns of its transpose), :41-52
+    V3 n[6];
+    n[0] = v3(a3.x, a4.x, a5.x); n[1] = v3(a3.y, a4.y, a5.y); n[2] = v3(a3.z, a4.z, a5.z);
+    n[3] = v3(b3.x, b4.x, b5.x); n[4] = v3(b3.y, b4.y, b5.y); n[5] = v3(b3.z, b4.z, b5.z);
+#pragma unroll
+    for (int a = 0; a < 15; a++) {
+        V3 L; float rel = 1.0e-4f;
+        if (a < 6) L = n[a];
+        else {
+            const V3 x = n[(a - 6) / 3], y = n[3 + (a - 6) % 3];
+            L = cross(x, y);
+            // nearly parallel normals: the direction of the cross product is noise, the axis proves nothing
+            if (dot(L, L) < 1.0e-4f * dot(x, x) * dot(y, y)) continue;
+            rel = 1.0e-3f;
+        }
+        const float l1 = fabsf(L.x) + fabsf(L.y) + fabsf(L.z);
+        const float rA = sphA >= 0.0f ? sphA * sqrtf(dot(L, L)) : box_radius(A0, A1, A2, L);
+        const float rB = sphB >= 0.0f ? sphB * sqrtf(dot(L, L)) : box_radius(B0, B1, B2, L);
+        const float s = rA + rB, dist = fabsf(dot(d, L));
+        if (dist > s + rel * (s + dist) + (4.0e-6f * cmag + slack) * l1) return false;
+    }
+    return true;
+}
+__device__ __forceinline__ bool is_sat_pair(int tA, int tB) {
+    return (tA == ICX_COLLIDER_BOX && (tB == ICX_COLLIDER_BOX || tB == ICX_COLLIDER_SPHERE)) || (tA == ICX_COLLIDER_SPHERE && tB == ICX_COLLIDER_BOX);
+}
+// current-state filter for packets pa, pb: false = the exact procedure cannot report a hit
+__device__ __forceinline__ bool may_hit(const DeviceWorld& W, uint32_t pa, uint32_t pb, float slack)
+{
+    const int tA = __float_as_uint(W.pk_lpos[pa].w) & PF_TYPE_MASK, tB = __float_as_uint(W.pk_lpos[pb].w) & PF_TYPE_MASK;
+    if (!is_sat_pair(tA, tB)) return true;
+    return sat_may_hit(W.pk_d + (size_t)pa * 6, W.pk_d + (size_t)pb * 6, v3(W.out.pos[W.pk_entity[pa]]), v3(W.out.pos[W.pk_entity[pb]]), tA, tB, slack);
+}
+
 // intersectProcedures[tA][tB], collision_procedures.h:411-417, for packets pa < pb on the current
 // state.  mpA / mpB: Collider::minParametricValue of a ray side, updated on a hit.
 static __device__ __noinline__ bool pair_intersect(const DeviceWorld& W, uint32_t pa, uint32_t pb, uint32_t ea, uint32_t eb,
@@ -104,7 +158,7 @@ static __device__ __noinline__ bool pair_intersect(const DeviceWorld& W, uint32_
 // One iteration of the reference's inner loop body (collision_physics_relay.h:39-228) for packets
 // pa < pb.  n_dirty: bodies with dirty_slot < n_dirty may be written; a hit on any other mutable
 // body aborts the attempt (see file header).
-static __device__ __noinline__ void process_pair(const DeviceWorld& W, uint32_t pa, uint32_t pb, uint32_t n_dirty)
+static __device__ __noinline__ void process_pair(const DeviceWorld& W, uint32_t pa, uint32_t pb, uint32_t n_dirty, uint32_t ctr_new)
 {
     const uint32_t ea = W.pk_entity[pa], eb = W.pk_entity[pb];
     const float4 lposA = W.pk_lpos[pa], lposB = W.pk_lpos[pb];
@@ -122,7 +176,7 @@ static __device__ __noinline__ void process_pair(const DeviceWorld& W, uint32_t 
         if (cleanA || cleanB) {                     // the dirty set was too small: grow it, write nothing
             if (cleanA) mark_dirty(W, ea);
             if (cleanB) mark_dirty(W, eb);
-            atomicAdd(&W.counters[CTR_NEW_DIRTY], 1u);
+            atomicAdd(&W.counters[ctr_new], 1u);
             return;
         }
     }
@@ -241,21 +295,26 @@ static __device__ __noinline__ void process_pair(const DeviceWorld& W, uint32_t 
 
 // ---------------------------------------------------------------------------------------
 // K5: speculative narrowphase.  One thread per candidate pair whose un-inflated bounds overlap:
-// test on the post-integration state, write nothing but the dirty marks.  Hits between two
+// a conservative separating-axis filter (exact procedure for ray / sphere-sphere pairs) on the
+// post-integration state; writes nothing but the dirty marks -- the exact, ordered evaluation of
+// every pair that may hit happens in k_resolve.  Hits between two
 // immutable bodies change nothing and need no order; they are queued for their contact record.
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) k_narrow(DeviceWorld W)
 {
-    const uint32_t n = min(W.counters[CTR_CANDIDATES], W.max_pairs);
+    const uint32_t n = min(W.counters[CTR_TIGHT], W.max_pairs);
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const uint2 pr = W.pairs[i];
-    if (!(pr.y & ICX_PAIR_TIGHT)) continue;
+    const uint2 pr = W.tight[i];
     const uint32_t pa = pr.x, pb = pr.y & ICX_NB_INDEX_MASK;
     const uint32_t ea = W.pk_entity[pa], eb = W.pk_entity[pb];
     const int tA = __float_as_uint(W.pk_lpos[pa].w) & PF_TYPE_MASK, tB = __float_as_uint(W.pk_lpos[pb].w) & PF_TYPE_MASK;
-    V3 baseA, baseB; Shape A, B; Hit h;
-    float mpA = 1.0f, mpB = 1.0f;               // Collider::reset value; a ray that hits is dirty and replayed in order
-    if (!pair_intersect(W, pa, pb, ea, eb, tA, tB, v3(W.out.pos[ea]), v3(W.out.pos[eb]), A, B, baseA, baseB, mpA, mpB, h)) continue;
+    if (is_sat_pair(tA, tB)) {
+        if (!sat_may_hit(W.pk_d + (size_t)pa * 6, W.pk_d + (size_t)pb * 6, v3(W.out.pos[ea]), v3(W.out.pos[eb]), tA, tB, 0.25f * W.margin)) continue;
+    } else {
+        V3 baseA, baseB; Shape A, B; Hit h;
+        float mpA = 1.0f, mpB = 1.0f;           // Collider::reset value; a ray that hits is dirty and replayed in order
+        if (!pair_intersect(W, pa, pb, ea, eb, tA, tB, v3(W.out.pos[ea]), v3(W.out.pos[eb]), A, B, baseA, baseB, mpA, mpB, h)) continue;
+    }
     if (pr.y & ICX_PAIR_STATIC) {
         const uint32_t k = atomicAdd(&W.counters[CTR_STATIC], 1u);
         if (k < W.max_static) W.static_pairs[k] = make_uint2(pa, pb); else atomicOr(W.flags, RF_PAIR_OVERFLOW);
@@ -266,56 +325,97 @@ __global__ void __launch_bounds__(128) k_narrow(DeviceWorld W)
     }
 }
 
-// Sorted candidate lists of one dirty body (both collider slots): every packet of another entity
-// whose inflated bound overlaps, ascending by packet index = the order the reference's pair loop
-// meets them (collision_physics_relay.h:29-37).
-__device__ __forceinline__ void list_insert(uint32_t* list, uint32_t& cnt, uint32_t cap, uint32_t entry, bool& overflow)
+// Sorted candidate lists of one dirty body (both collider slots), built by ONE WARP: every packet
+// of another entity whose inflated bound overlaps, ascending by packet index = the order the
+// reference's pair loop meets them (collision_physics_relay.h:29-37).  Lanes 0..17 resolve the
+// 9 rows x 2 bucket ranges around the body's cell, the candidates of all ranges are then tested
+// 32 at a time, and the survivors are ranked by counting (keys are distinct packet indices).
+__device__ __forceinline__ void build_lists_warp(const DeviceWorld& W, uint32_t slot)
 {
-    if (cnt >= cap) { overflow = true; return; }
-    uint32_t i = cnt;
-    const uint32_t key = entry & ICX_NB_INDEX_MASK;
-    while (i > 0 && (list[i - 1] & ICX_NB_INDEX_MASK) > key) { list[i] = list[i - 1]; i--; }
-    list[i] = entry; cnt++;
-}
-
-static __device__ __noinline__ void build_lists(const DeviceWorld& W, uint32_t slot)
-{
+    const uint32_t FULL = 0xFFFFFFFFu, lane = threadIdx.x & 31u;
     const uint32_t e = W.dirty_list[slot];
     const uint32_t fp = W.first_packet[e];
     const uint32_t npk = fp >> 30, p0 = fp & 0x3FFFFFFFu;
     const uint32_t wl = W.worldline_stride ? e / W.worldline_stride : 0u;
     const uint32_t n_large = min(W.counters[CTR_LARGE], W.max_large);
-    bool overflow = false;
+    const uint32_t cap = W.max_neighbors;
     for (uint32_t k = 0; k < 2u; k++) {
-        uint32_t* list = W.nbr + (size_t)(slot * 2u + k) * W.max_neighbors;
-        uint32_t cnt = 0;
+        uint32_t* list = W.nbr + (size_t)(slot * 2u + k) * cap;
+        uint32_t cnt = 0;                                   // warp-uniform
         if (k < npk && W.pk_cell[p0 + k] < 0xFFFFFFFEu) {
             const uint32_t p = p0 + k;
             const float4 lo = W.pk_lo[p], hi = W.pk_hi[p];
             const int type = __float_as_uint(W.pk_lpos[p].w) & PF_TYPE_MASK;
-            for_each_neighbor(W, cell_coord(lo.x, hi.x, W.inv_cell), cell_coord(lo.y, hi.y, W.inv_cell), cell_coord(lo.z, hi.z, W.inv_cell), wl,
-                [&](uint32_t j) {
-                    const float4 blo = W.s_lo[j], bhi = W.s_hi[j];
-                    if (!overlap(lo, hi, blo, bhi)) return;
-                    const uint32_t btag = __float_as_uint(blo.w), be = __float_as_uint(bhi.w);
-                    if (be == e) return;
-                    if (W.worldline_stride && be / W.worldline_stride != wl) return;
-                    if (!can_intersect(type, (btag >> 28) & 3, W.cfg_flags)) return;
-                    list_insert(list, cnt, W.max_neighbors, (btag & ICX_NB_INDEX_MASK) | ((btag & 0x40000000u) ? ICX_NB_IMMUTABLE : 0u), overflow);
-                });
-            for (uint32_t q = 0; q < n_large; q++) {
-                const uint32_t o = W.large_list[q];
-                const uint32_t oe = W.pk_entity[o];
-                if (oe == e) continue;
-                if (W.worldline_stride && oe / W.worldline_stride != wl) continue;
-                if (!can_intersect(type, (int)(__float_as_uint(W.pk_lpos[o].w) & PF_TYPE_MASK), W.cfg_flags)) continue;
-                if (!overlap(lo, hi, W.pk_lo[o], W.pk_hi[o])) continue;
-                list_insert(list, cnt, W.max_neighbors, o | ICX_NB_IMMUTABLE, overflow);
+            const int cx = cell_coord(lo.x, hi.x, W.inv_cell), cy = cell_coord(lo.y, hi.y, W.inv_cell), cz = cell_coord(lo.z, hi.z, W.inv_cell);
+            // ---- ranges ----
+            uint32_t beg = 0, len = 0;
+            {
+                const int r = (int)(lane >> 1), part = (int)(lane & 1u);
+                const int xb0 = (cx - 1) >> ICX_XB, xb1 = (cx + 1) >> ICX_XB, xb = xb0 + part;
+                const bool valid = lane < 18u && xb <= xb1;
+                uint32_t key = 0xFFFFFF00u + lane, block = 0;
+                if (valid) { block = row_block(xb, cy + (r % 3 - 1), cz + (r / 3 - 1), wl, W.n_buckets); key = block * 2u + (uint32_t)part; }
+                const uint32_t same = __match_any_sync(FULL, key);
+                if (valid && (uint32_t)(__ffs(same) - 1) == lane) {         // first lane of a duplicated range keeps it
+                    const int x_lo = max(cx - 1, xb << ICX_XB), x_hi = min(cx + 1, (xb << ICX_XB) + ICX_XMASK);
+                    beg = W.cell_count[(block << ICX_XB) | (uint32_t)(x_lo & ICX_XMASK)];
+                    len = W.cell_count[((block << ICX_XB) | (uint32_t)(x_hi & ICX_XMASK)) + 1u] - beg;
+                }
             }
+            uint32_t off = len;                              // inclusive scan -> exclusive offsets
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(FULL, off, o); if (lane >= (uint32_t)o) off += y; }
+            const uint32_t total = __shfl_sync(FULL, off, 31) + n_large;
+            off -= len;
+            const uint32_t n_grid_cand = total - n_large;
+            // ---- candidates, 32 at a time (grid ranges first, then the large-collider list) ----
+            for (uint32_t base = 0; base < total; base += 32u) {
+                const uint32_t idx = base + lane;
+                uint32_t j = ICX_NONE;
+#pragma unroll
+                for (int r = 0; r < 18; r++) {
+                    const uint32_t ro = __shfl_sync(FULL, off, r), rl = __shfl_sync(FULL, len, r), rb = __shfl_sync(FULL, beg, r);
+                    if (idx >= ro && idx < ro + rl) j = rb + (idx - ro);
+                }
+                uint32_t entry = 0; bool pass = false;
+                if (j != ICX_NONE) {
+                    const float4 blo = W.s_lo[j], bhi = W.s_hi[j];
+                    const uint32_t btag = __float_as_uint(blo.w), be = __float_as_uint(bhi.w);
+                    pass = overlap(lo, hi, blo, bhi) && be != e && (!W.worldline_stride || be / W.worldline_stride == wl) &&
+                           can_intersect(type, (btag >> 28) & 3, W.cfg_flags);
+                    entry = (btag & ICX_NB_INDEX_MASK) | ((btag & 0x40000000u) ? ICX_NB_IMMUTABLE : 0u);
+                } else if (idx >= n_grid_cand && idx < total) {
+                    const uint32_t o = W.large_list[idx - n_grid_cand];
+                    const uint32_t oe = W.pk_entity[o];
+                    pass = oe != e && (!W.worldline_stride || oe / W.worldline_stride == wl) &&
+                           can_intersect(type, (int)(__float_as_uint(W.pk_lpos[o].w) & PF_TYPE_MASK), W.cfg_flags) &&
+                           overlap(lo, hi, W.pk_lo[o], W.pk_hi[o]);
+                    entry = o | ICX_NB_IMMUTABLE;
+                }
+                const uint32_t m = __ballot_sync(FULL, pass);
+                if (pass) { const uint32_t at = cnt + __popc(m & ((1u << lane) - 1u)); if (at < cap) list[at] = entry; }
+                cnt += __popc(m);
+            }
+            __syncwarp();
+            if (cnt > cap) { if (lane == 0) atomicOr(W.flags, RF_NEIGHBOR_OVERFLOW); cnt = cap; }
+            // ---- sort ascending by packet index ----
+            if (cnt <= 32u) {
+                const uint32_t mine = lane < cnt ? list[lane] : 0xFFFFFFFFu;
+                uint32_t rank = 0;
+                for (uint32_t q = 0; q < cnt; q++) { const uint32_t other = __shfl_sync(FULL, mine, q); rank += ((other & ICX_NB_INDEX_MASK) < (mine & ICX_NB_INDEX_MASK)) ? 1u : 0u; }
+                __syncwarp();
+                if (lane < cnt) list[rank] = mine;
+            } else if (lane == 0) {
+                for (uint32_t i = 1; i < cnt; i++) {
+                    const uint32_t v = list[i]; uint32_t q = i;
+                    while (q > 0 && (list[q - 1] & ICX_NB_INDEX_MASK) > (v & ICX_NB_INDEX_MASK)) { list[q] = list[q - 1]; q--; }
+                    list[q] = v;
+                }
+            }
+            __syncwarp();
         }
-        W.nbr_count[slot * 2u + k] = cnt;
+        if (lane == 0) W.nbr_count[slot * 2u + k] = cnt;
     }
-    if (overflow) atomicOr(W.flags, RF_NEIGHBOR_OVERFLOW);
 }
 
 // Put a dirty body back to its post-integration state (bit-identical recomputation from the tick input).
@@ -330,87 +430,125 @@ static __device__ __noinline__ void restore_body(const DeviceWorld& W, uint32_t 
     for (uint32_t k = 0; k < (fp >> 30); k++) W.pk_minparam[(fp & 0x3FFFFFFFu) + k] = 1.0f;
 }
 
-// One dependency round for dirty slot s.
-__device__ __forceinline__ void round_step(const DeviceWorld& W, uint32_t s, uint32_t n_dirty, int parity, uint32_t ctr_out)
+// One dependency round for the dirty slot of each lane (s == ICX_NONE: idle lane).  The warp
+// alternates between a divergent, cheap phase -- every lane walks its cursor past the entries the
+// separating-axis filter rejects, up to the next pair that needs the exact procedure -- and a
+// converged phase in which all such lanes run the exact narrowphase + response together.
+__device__ __forceinline__ void round_step_warp(const DeviceWorld& W, uint32_t s, uint32_t n_dirty, int parity, uint32_t ctr_out, uint32_t ctr_new)
 {
+    const uint32_t FULL = 0xFFFFFFFFu;
     const uint32_t* __restrict__ hin = W.head[parity];
     uint32_t* __restrict__ hout = W.head[parity ^ 1];
-    const uint32_t e = W.dirty_list[s];
-    const Cursor c = load_cursor(W, s, e);
-    uint32_t hw = hin[s];
-    bool first = true;
+    bool done = s == ICX_NONE, handed_over = false, first = true;
+    Cursor c = {}; uint32_t hw = 0;
+    if (!done) { c = load_cursor(W, s, W.dirty_list[s]); hw = hin[s]; }
     for (;;) {
-        uint32_t k, entry;
-        if (!cursor_head(c, hw, k, entry)) break;
-        const uint32_t p = c.p0 + k;
-        const uint32_t o = entry & ICX_NB_INDEX_MASK;
-        uint32_t eo = 0, so = ICX_NONE;
-        if (!(entry & ICX_NB_IMMUTABLE)) { eo = W.pk_entity[o]; so = W.dirty_slot[eo]; }
-        if (so >= n_dirty) {                        // immutable or clean partner: no ordering, never written
-            process_pair(W, min(p, o), max(p, o), n_dirty);
-            hw = cursor_advance(hw, k); first = false;
-            continue;
+        bool have = false, two = false, partner_pending = false;
+        uint32_t pa = 0, pb = 0, k = 0, so = ICX_NONE, hwo2 = 0;
+        while (!done) {
+            uint32_t entry;
+            if (!cursor_head(c, hw, k, entry)) { done = true; break; }
+            const uint32_t p = c.p0 + k, o = entry & ICX_NB_INDEX_MASK;
+            uint32_t eo = 0; so = ICX_NONE;
+            if (!(entry & ICX_NB_IMMUTABLE)) { eo = W.pk_entity[o]; so = W.dirty_slot[eo]; }
+            pa = min(p, o); pb = max(p, o);
+            if (so >= n_dirty) {                        // immutable or clean partner: no ordering, never written
+                if (may_hit(W, pa, pb, 0.0f)) { have = true; two = false; break; }
+                hw = cursor_advance(hw, k); first = false;
+                continue;
+            }
+            if (!first) { done = true; break; }         // a two-sided pair must be at my cursor at round start
+            const Cursor co = load_cursor(W, so, eo);
+            const uint32_t hwo = hin[so];
+            uint32_t ko, entryo;
+            if (!cursor_head(co, hwo, ko, entryo)) { done = true; break; }                      // cannot happen for consistent lists
+            if (co.p0 + ko != o || (entryo & ICX_NB_INDEX_MASK) != p) { done = true; break; }    // partner is not ready: wait
+            if (p > o) { done = true; handed_over = true; break; }  // I am the B side: the A lane advances and re-queues me
+            hwo2 = cursor_advance(hwo, ko); partner_pending = cursor_pending(co, hwo2);
+            if (may_hit(W, pa, pb, 0.0f)) { have = true; two = true; break; }
+            hw = cursor_advance(hw, k); first = false;  // certain miss: consume it on both sides
+            hout[so] = hwo2;
+            if (partner_pending) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = so;
         }
-        if (!first) break;                          // a two-sided pair must be at my cursor at round start
-        const Cursor co = load_cursor(W, so, eo);
-        const uint32_t hwo = hin[so];
-        uint32_t ko, entryo;
-        if (!cursor_head(co, hwo, ko, entryo)) break;           // cannot happen for a consistent list
-        if (co.p0 + ko != o || (entryo & ICX_NB_INDEX_MASK) != p) break;    // partner is not ready: wait
-        if (p > o) return;                          // I am the B side: the A thread advances and re-queues me
-        process_pair(W, p, o, n_dirty);
-        hw = cursor_advance(hw, k); first = false;
-        const uint32_t hwo2 = cursor_advance(hwo, ko);
-        hout[so] = hwo2;
-        if (cursor_pending(co, hwo2)) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = so;
+        if (!__any_sync(FULL, have)) break;
+        if (have) {
+            process_pair(W, pa, pb, n_dirty, ctr_new);
+            hw = cursor_advance(hw, k); first = false;
+            if (two) {
+                hout[so] = hwo2;
+                if (partner_pending) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = so;
+            }
+        }
+        __syncwarp();
     }
-    hout[s] = hw;
-    if (cursor_pending(c, hw)) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = s;
+    if (s != ICX_NONE && !handed_over) {
+        hout[s] = hw;
+        if (cursor_pending(c, hw)) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = s;
+    }
 }
 
 // ---------------------------------------------------------------------------------------
 // K6: ordered resolve of the dirty bodies.  Persistent cooperative kernel (grid-wide barriers
 // between dependency rounds, no host round trips); see the file header.
 // ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void trace_mark(const DeviceWorld& W, uint32_t& n, uint32_t tag)
+{
+    if (!W.trace || n + 2 > ICX_TRACE_CAP) return;
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    W.trace[n++] = t; W.trace[n++] = tag;
+}
+
 __global__ void __launch_bounds__(128) k_resolve(DeviceWorld W, double dt, int do_euler)
 {
+    uint32_t tn = 2;        // trace[0] = number of words used
     cg::grid_group grid = cg::this_grid();
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
     volatile uint32_t* ctr = W.counters;
     uint32_t attempts = 0, rounds = 0;
+    if (tid == 0) trace_mark(W, tn, 0u);
     for (;;) {
         const uint32_t n_dirty = ctr[CTR_DIRTY], n_listed = ctr[CTR_LISTED], n_static = min(ctr[CTR_STATIC], W.max_static);
-        for (uint32_t s = n_listed + tid; s < n_dirty; s += nth) build_lists(W, s);
+        for (uint32_t s = n_listed + (tid >> 5); s < n_dirty; s += (nth >> 5)) build_lists_warp(W, s);
         for (uint32_t s = tid; s < n_dirty; s += nth) {
             if (attempts > 0 && s < n_listed) restore_body(W, W.dirty_list[s], dt, do_euler);
             W.head[0][s] = 0u; W.active[0][s] = s;
         }
+        if (tid == 0) trace_mark(W, tn, 0x10000u | n_dirty);
         grid.sync();
+        if (tid == 0) trace_mark(W, tn, 0x20000u);
         if (*(volatile uint32_t*)W.flags & RF_NEIGHBOR_OVERFLOW) break;     // lists are incomplete: the host grows them and re-runs the tick
         if (tid == 0) {
-            ctr[CTR_LISTED] = n_dirty; ctr[CTR_CONTACTS] = 0; ctr[CTR_INTERCEPTS] = 0; ctr[CTR_NEW_DIRTY] = 0;
+            ctr[CTR_LISTED] = n_dirty; ctr[CTR_CONTACTS] = 0; ctr[CTR_INTERCEPTS] = 0;
+            ctr[CTR_NEWD] = 0; ctr[CTR_NEWD + 1] = 0; ctr[CTR_NEWD + 2] = 0;
             ctr[CTR_ACTIVE] = n_dirty; ctr[CTR_ACTIVE + 1] = 0; ctr[CTR_ACTIVE + 2] = 0;
             __threadfence();
         }
         grid.sync();
-        for (uint32_t i = tid; i < n_static; i += nth) { const uint2 pr = W.static_pairs[i]; process_pair(W, pr.x, pr.y, n_dirty); }
+        for (uint32_t i = tid; i < n_static; i += nth) { const uint2 pr = W.static_pairs[i]; process_pair(W, pr.x, pr.y, n_dirty, CTR_NEWD); }
+        __syncwarp();
         int parity = 0;
         rounds = 0;
         for (;;) {
             const uint32_t n_act = ctr[CTR_ACTIVE + rounds % 3u];
-            if (n_act == 0u) break;
+            const uint32_t grew = rounds ? ctr[CTR_NEWD + (rounds + 2u) % 3u] : 0u;    // written in the previous round only
+            if (n_act == 0u || grew != 0u) break;       // done, or the dirty set grew: restart at once
             if (rounds >= ICX_MAX_ROUNDS) { if (tid == 0) atomicOr(W.flags, RF_ROUNDS_EXCEEDED); break; }
-            if (tid == 0) ctr[CTR_ACTIVE + (rounds + 2u) % 3u] = 0u;
-            for (uint32_t i = tid; i < n_act; i += nth) round_step(W, W.active[parity][i], n_dirty, parity, CTR_ACTIVE + (rounds + 1u) % 3u);
+            if (tid == 0) { ctr[CTR_ACTIVE + (rounds + 2u) % 3u] = 0u; ctr[CTR_NEWD + (rounds + 1u) % 3u] = 0u; }
+            for (uint32_t base = tid & ~31u; base < n_act; base += nth) {       // warp-uniform trip count
+                const uint32_t i = base + (tid & 31u);
+                round_step_warp(W, i < n_act ? W.active[parity][i] : ICX_NONE, n_dirty, parity, CTR_ACTIVE + (rounds + 1u) % 3u, CTR_NEWD + rounds % 3u);
+            }
             grid.sync();
+            if (tid == 0) trace_mark(W, tn, 0x30000u | min(n_act, 0xFFFFu));
             rounds++; parity ^= 1;
         }
         grid.sync();
-        if (ctr[CTR_NEW_DIRTY] == 0u || (*(volatile uint32_t*)W.flags & RF_ROUNDS_EXCEEDED)) break;
+        if (ctr[CTR_DIRTY] == n_dirty || (*(volatile uint32_t*)W.flags & RF_ROUNDS_EXCEEDED)) break;
         attempts++;
-        grid.sync();                                // everyone has read CTR_NEW_DIRTY before the next attempt resets it
+        grid.sync();
     }
-    if (tid == 0) { ctr[CTR_ROUNDS] = rounds; ctr[CTR_ATTEMPTS] = attempts; }
+    if (tid == 0) { ctr[CTR_ROUNDS] = rounds; ctr[CTR_ATTEMPTS] = attempts; trace_mark(W, tn, 0x40000u); if (W.trace) W.trace[0] = tn; }
 }
 
 void launch_narrow(const DeviceWorld& W, int blocks, cudaStream_t st)

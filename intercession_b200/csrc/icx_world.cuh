@@ -100,6 +100,7 @@ struct DeviceWorld {
     uint32_t* large_list;           // packets larger than a cell (immutable only)
     // flat candidate pair list (the broadphase output, icx_pairs_fetch)
     uint2* pairs; uint32_t max_pairs;
+    uint2* tight;                   // the subset with ICX_PAIR_TIGHT (input of the speculative narrowphase)
     uint2* static_pairs; uint32_t max_static;    // hits between two immutable bodies (contact records only)
     // bodies touched by at least one hit ("dirty"): only these need the reference's sequential order
     uint32_t* dirty_slot;           // per entity: index into dirty_list, ICX_NONE = clean
@@ -114,6 +115,7 @@ struct DeviceWorld {
     // counters, one cache line each would be nicer; they are cold
     uint32_t* counters;             // see CTR_*
     uint32_t* flags;                // RF_*
+    unsigned long long* trace;      // optional device timeline of k_resolve (globaltimer ns), ICX_TRACE_CAP entries; may be null
     // parameters
     float margin, cell_size, inv_cell;
     float gx, gy, gz;
@@ -127,8 +129,9 @@ enum { CTR_LARGE = 0, CTR_DIRTY = 1, CTR_CONTACTS = 2, CTR_INTERCEPTS = 3, CTR_C
        CTR_NEED_CELL = 11,      // float bits: cell size a too-large mutable collider needs
        CTR_EXTENT = 12,         // float bits: largest collider extent seen at import
        CTR_ACTIVE = 13,         // 3 rotating work-list counters: CTR_ACTIVE + (round % 3)
-       CTR_BARRIER = 16,        // 2 words: arrival count, generation
+       CTR_NEWD = 20,           // 3 rotating per-round counts of bodies that turned dirty during the replay
        CTR_TOTAL = 32 };
 #define ICX_MAX_ROUNDS 65535u
+#define ICX_TRACE_CAP 512
 
 } // namespace icx

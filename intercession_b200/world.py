@@ -136,3 +136,11 @@ class World:
         self._ck(self.lib.icx_phase_ms(self.handle, ms, C.byref(nt), C.byref(nl)))
         names = ("integrate_prep", "grid_sort", "pairs", "narrow", "resolve")
         return dict(zip(names, list(ms))), nt.value, nl.value
+
+    def trace(self, enable=True):
+        """Device timeline of the last ordered resolve: list of (ns since its start, tag)."""
+        buf = np.zeros(512, np.uint64)
+        n = C.c_size_t(0)
+        self._ck(self.lib.icx_debug_trace(self.handle, 1 if enable else 0, abi.ptr(buf), len(buf), C.byref(n)))
+        v = buf[:n.value].reshape(-1, 2)
+        return [(int(t - v[0, 0]), int(tag)) for t, tag in v] if len(v) else []

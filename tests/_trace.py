@@ -1,0 +1,12 @@
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from intercession_b200 import scenes, world
+s = scenes.config3(int(sys.argv[1]) if len(sys.argv) > 1 else 1048576)
+w = world.World(s.n); w.upload(s); w.step(1/45, 4); w.trace(True)
+for k in range(2):
+    w.step(1/45); st = w.stats()
+    print("tick", k, "dirty", st.n_dirty, "rounds", st.n_rounds, "attempts", st.n_attempts, "contacts", st.n_contacts, "ms", w.last_step_ms())
+    prev = 0
+    for t, tag in w.trace(True):
+        print(f"  {t/1e3:9.1f} us (+{(t-prev)/1e3:7.1f})  tag {tag>>16:x} arg {tag&0xffff}")
+        prev = t
