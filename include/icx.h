@@ -285,6 +285,9 @@ ICX_API int icx_phase_ms(IcxWorld* w, double* ms, uint64_t* n_ticks, uint64_t* n
  * 0x3nnnn round finished (nnnn = bodies active in it), 0x4.... end.  enable != 0 turns recording on. */
 ICX_API int icx_debug_trace(IcxWorld* w, int enable, uint64_t* out, size_t cap, size_t* n);
 
+/* Raw device counters of the last tick (32 words; diagnostic, layout not stable). */
+ICX_API int icx_debug_counters(IcxWorld* w, uint32_t* out32);
+
 /* CUDA stream of the world as a void* (cudaStream_t), for callers that time it. */
 ICX_API void* icx_world_stream(IcxWorld* w);
 

@@ -152,6 +152,7 @@ SIGNATURES = {
     "icx_last_step_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
     "icx_world_stream": (_vp, [_vp]),
     "icx_profile_enable": (C.c_int, [_vp, C.c_int]),
+    "icx_debug_counters": (C.c_int, [_vp, _vp]),
     "icx_debug_trace": (C.c_int, [_vp, C.c_int, _vp, _sz, _psz]),
     "icx_phase_ms": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
 }

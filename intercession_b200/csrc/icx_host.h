@@ -60,7 +60,7 @@ struct IcxWorld {
     double phase_ms[ICX_N_PHASES] = {};
     uint64_t phase_ticks = 0;
     uint64_t launches = 0;              // kernels launched by icx_step* since creation
-    int resolve_blocks = 0;
+    int resolve_blocks = 0, narrow_blocks = 0;
     std::string error;
     bool have_results = false;
 };

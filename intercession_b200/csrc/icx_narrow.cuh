@@ -144,23 +144,30 @@ ICX_DI V3 sat_axis(const M3& nA, const M3& nB, int a) {
     return cross(ai, bj);
 }
 
-// box_box_intersect, collision_procedures.cpp:14-231
-ICX_DN bool box_box_intersect(const Shape& A, const Shape& B, Hit& h) {
-    const M3 nA = transpose(A.inv), nB = transpose(B.inv);      // :41-44
-    V3 cA[8], cB[8];
-    box_corners(A.M, cA); box_corners(B.M, cB);
-    V3 minN = v3(0.0f, 0.0f, 0.0f); float minD = INFINITY;
-    for (int a = 0; a < 15; a++) {
-        V3 axis = normalize(sat_axis(nA, nB, a));
-        if (isnan(axis.x)) continue;                                                // :82
-        Interval iA = project_corners(cA, axis), iB = project_corners(cB, axis);
-        float pen; bool flip = false;
-        if ((iA.x + iA.y) / 2.0f > (iB.x + iB.y) / 2.0f) pen = iB.y - iA.x;         // :95-98
-        else { pen = iA.y - iB.x; flip = true; }
-        if (pen <= 0) return false;                                                 // :107
-        if (pen < minD) { minD = pen; minN = flip ? -axis : axis; }                 // :113-117
-    }
-    h.normal = minN; h.depth = minD;
+// One SAT axis of box_box / sphere_box_intersect (collision_procedures.cpp:76-118): the serial
+// procedures below loop over a = 0..14, the warp-cooperative ones (icx_resolve.cu) give one axis to
+// each lane; both run exactly this arithmetic.
+struct AxisResult { V3 axis; float pen; bool flip, skip; };
+
+ICX_DI AxisResult sat_axis_result(V3 axis, Interval iA, Interval iB) {
+    AxisResult r; r.axis = axis; r.skip = false; r.flip = false;
+    if ((iA.x + iA.y) / 2.0f > (iB.x + iB.y) / 2.0f) r.pen = iB.y - iA.x;           // :95-98
+    else { r.pen = iA.y - iB.x; r.flip = true; }
+    return r;
+}
+ICX_DI AxisResult box_box_axis(const M3& nA, const M3& nB, const V3* cA, const V3* cB, int a) {
+    const V3 axis = normalize(sat_axis(nA, nB, a));
+    if (isnan(axis.x)) { AxisResult r; r.axis = axis; r.pen = 0.0f; r.flip = false; r.skip = true; return r; }   // :82
+    return sat_axis_result(axis, project_corners(cA, axis), project_corners(cB, axis));
+}
+ICX_DI AxisResult sphere_box_axis(const M3& nA, const M3& nB, V3 sO, float projRadius, const V3* cB, int a) {
+    const V3 axis = normalize(sat_axis(nA, nB, a));
+    if (isnan(axis.x)) { AxisResult r; r.axis = axis; r.pen = 0.0f; r.flip = false; r.skip = true; return r; }
+    return sat_axis_result(axis, project_sphere(sO, projRadius, axis), project_corners(cB, axis));
+}
+
+// box_box_intersect after the axis loop, collision_procedures.cpp:120-231 (h.normal / h.depth are set)
+ICX_DN bool box_box_finish(const Shape& A, const Shape& B, Hit& h) {
     V3 mA[8], mB[ICX_MAXV];
     int nMA = build_contact_manifold(A.M, -h.normal, mA);                           // :128-132
     int nMB = build_contact_manifold(B.M, h.normal, mB);
@@ -189,6 +196,29 @@ ICX_DN bool box_box_intersect(const Shape& A, const Shape& B, Hit& h) {
     return true;
 }
 
+// box_box_intersect, collision_procedures.cpp:14-231
+ICX_DN bool box_box_intersect(const Shape& A, const Shape& B, Hit& h) {
+    const M3 nA = transpose(A.inv), nB = transpose(B.inv);      // :41-44
+    V3 cA[8], cB[8];
+    box_corners(A.M, cA); box_corners(B.M, cB);
+    V3 minN = v3(0.0f, 0.0f, 0.0f); float minD = INFINITY;
+    for (int a = 0; a < 15; a++) {
+        const AxisResult r = box_box_axis(nA, nB, cA, cB, a);
+        if (r.skip) continue;
+        if (r.pen <= 0) return false;                                               // :107
+        if (r.pen < minD) { minD = r.pen; minN = r.flip ? -r.axis : r.axis; }       // :113-117
+    }
+    h.normal = minN; h.depth = minD;
+    return box_box_finish(A, B, h);
+}
+
+// sphere_box_intersect after the axis loop, collision_procedures.cpp:362-378
+ICX_DI bool sphere_box_finish(V3 sO, V3 sS, Hit& h) {
+    const float radius = length(sS);                                                // :367-368 (reference quirk: includes translation)
+    h.point = sO - (h.normal * radius) + (h.normal * h.depth);                      // :370-373
+    return true;
+}
+
 // sphere_box_intersect, collision_procedures.cpp:266-378 (A sphere, B box)
 ICX_DN bool sphere_box_intersect(const Shape& A, const Shape& B, Hit& h) {
     const M3 nA = transpose(A.inv), nB = transpose(B.inv);
@@ -198,19 +228,13 @@ ICX_DN bool sphere_box_intersect(const Shape& A, const Shape& B, Hit& h) {
     const float projRadius = length(sS - sO);                                       // project_sphere :97
     V3 minN = v3(0.0f, 0.0f, 0.0f); float minD = INFINITY;
     for (int a = 0; a < 15; a++) {
-        V3 axis = normalize(sat_axis(nA, nB, a));
-        if (isnan(axis.x)) continue;
-        Interval iA = project_sphere(sO, projRadius, axis), iB = project_corners(cB, axis);
-        float pen; bool flip = false;
-        if ((iA.x + iA.y) / 2.0f > (iB.x + iB.y) / 2.0f) pen = iB.y - iA.x;
-        else { pen = iA.y - iB.x; flip = true; }
-        if (pen <= 0) return false;
-        if (pen < minD) { minD = pen; minN = flip ? -axis : axis; }
+        const AxisResult r = sphere_box_axis(nA, nB, sO, projRadius, cB, a);
+        if (r.skip) continue;
+        if (r.pen <= 0) return false;
+        if (r.pen < minD) { minD = r.pen; minN = r.flip ? -r.axis : r.axis; }
     }
     h.normal = minN; h.depth = minD;
-    const float radius = length(sS);                                                // :367-368 (reference quirk: includes translation)
-    h.point = sO - (h.normal * radius) + (h.normal * h.depth);                      // :370-373
-    return true;
+    return sphere_box_finish(sO, sS, h);
 }
 
 // sphere_sphere_intersect, collision_procedures.cpp:380-423 (opt-in, ICX_F_SPHERE_SPHERE)

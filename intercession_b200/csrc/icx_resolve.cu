@@ -155,33 +155,163 @@ static __device__ __noinline__ bool pair_intersect(const DeviceWorld& W, uint32_
     return hit;
 }
 
+// ---- warp-cooperative exact procedures ---------------------------------------------------
+// The exact narrowphase + response of ONE pair is a single thread's worth of serial FP32 work
+// (~6 K instructions): on a GPU that is pure latency.  The ordered resolve therefore gives every
+// pair a whole warp.  All 32 lanes hold the same operands and execute the same instructions
+// ("uniform" code: loads broadcast, results identical in every lane), except for the 15-axis SAT
+// loop, where lane a evaluates axis a with exactly the arithmetic of the serial loop and the warp
+// then reproduces the loop's decisions: any axis with penetration <= 0 -> no hit, otherwise the
+// FIRST axis attaining the strict minimum.  Only lane 0 writes to memory.
+struct SatPick { V3 normal; float depth; bool separated; };
+
+__device__ __forceinline__ SatPick sat_pick_warp(const AxisResult r, bool have)
+{
+    const uint32_t FULL = 0xFFFFFFFFu, lane = threadIdx.x & 31u;
+    SatPick p;
+    p.separated = __any_sync(FULL, have && !r.skip && r.pen <= 0) != 0;            // :107 (any axis, order irrelevant)
+    const bool cand = have && !r.skip && r.pen < INFINITY;                         // `pen < minD` can only ever hold for these
+    float key = cand ? r.pen : INFINITY; uint32_t idx = lane;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ok = __shfl_xor_sync(FULL, key, o); const uint32_t oi = __shfl_xor_sync(FULL, idx, o);
+        if (ok < key || (ok == key && oi < idx)) { key = ok; idx = oi; }
+    }
+    const V3 n = r.flip ? -r.axis : r.axis;                                          // :113-117
+    p.normal = v3(__shfl_sync(FULL, n.x, idx), __shfl_sync(FULL, n.y, idx), __shfl_sync(FULL, n.z, idx));
+    p.depth = key;
+    if (!(key < INFINITY)) p.normal = v3(0.0f, 0.0f, 0.0f);
+    return p;
+}
+
+// the 15-axis loop of box_box_intersect (X, Y boxes) or sphere_box_intersect (X sphere, Y box), one axis per lane
+__device__ __forceinline__ SatPick sat_warp(const Shape& X, const Shape& Y, bool x_is_sphere)
+{
+    const int lane = threadIdx.x & 31;
+    const M3 nX = transpose(X.inv), nY = transpose(Y.inv);
+    V3 cX[8], cY[8];
+    box_corners(Y.M, cY);
+    const V3 sO = xform(X.M, 0.0f, 0.0f, 0.0f);
+    const float projRadius = length(xform(X.M, ICX_UNIT_RADIUS, 0.0f, 0.0f) - sO);
+    if (!x_is_sphere) box_corners(X.M, cX);
+    AxisResult r; r.axis = v3(0.0f, 0.0f, 0.0f); r.pen = 0.0f; r.flip = false; r.skip = true;
+    if (lane < 15) r = x_is_sphere ? sphere_box_axis(nX, nY, sO, projRadius, cY, lane) : box_box_axis(nX, nY, cX, cY, lane);
+    return sat_pick_warp(r, lane < 15);
+}
+
+// everything one side of a pair contributes, fetched in ONE batch of independent loads
+struct SideData { float4 pos, vel, angvel, acc, angacc, prm0, prm1, mat0, lscale, pos0, d[6]; float damping, minparam; uint32_t slot, ts, id; };
+
+__device__ __forceinline__ SideData load_side(const DeviceWorld& W, uint32_t p, uint32_t e)
+{
+    SideData s;
+    s.pos = W.out.pos[e]; s.vel = W.out.vel[e]; s.angvel = W.out.angvel[e]; s.acc = W.out.acc[e]; s.angacc = W.out.angacc[e];
+    s.prm0 = W.prm0[e]; s.prm1 = W.prm1[e]; s.pos0 = W.pos0[e]; s.slot = W.dirty_slot[e]; s.ts = W.out.ts[e]; s.id = W.entity_id[e];
+    s.mat0 = W.pk_mat0[p]; s.lscale = W.pk_lscale[p]; s.damping = W.pk_damping[p]; s.minparam = W.pk_minparam[p];
+    const float4* d = W.pk_d + (size_t)p * 6;
+#pragma unroll
+    for (int k = 0; k < 6; k++) s.d[k] = d[k];
+    return s;
+}
+__device__ __forceinline__ Shape shape_of(const SideData& s, int type, V3& base)
+{
+    Shape sh;
+    sh.M.c[0] = v3(s.d[0]); sh.M.c[1] = v3(s.d[1]); sh.M.c[2] = v3(s.d[2]);
+    base = v3(s.d[0].w, s.d[1].w, s.d[2].w);
+    sh.M.t = base + (v3(s.pos) + v3(0.0f, 0.0f, 0.0f));
+    sh.inv.c[0] = v3(s.d[3]); sh.inv.c[1] = v3(s.d[4]); sh.inv.c[2] = v3(s.d[5]);
+    sh.type = type;
+    return sh;
+}
+__device__ __forceinline__ Side side_of(const SideData& s, const Shape& sh, V3 base, uint32_t bits)
+{
+    Side S;
+    S.origin = v3(s.pos); S.vel = v3(s.vel); S.angvel = v3(s.angvel); S.acc = v3(s.acc); S.angacc = v3(s.angacc);
+    S.mass = s.prm0.w; S.colAngDrag = s.prm1.z;
+    S.L = mat3_of(sh.M); S.base = base; S.inv = sh.inv; S.inertia = v3(s.d[3].w, s.d[4].w, s.d[5].w);
+    S.staticFriction = s.mat0.x; S.dynamicFriction = s.mat0.y; S.restitution = s.mat0.z; S.stiffness = s.mat0.w;
+    S.damping = s.damping; S.restLength = s.lscale.w;
+    S.influenceOrientation = (bits & PF_INFLUENCE_ORIENT) != 0;
+    return S;
+}
+__device__ __forceinline__ void store_side(const DeviceWorld& W, uint32_t e, const Side& S, const SideData& s, bool rr)
+{
+    W.out.vel[e] = make_float4(S.vel.x, S.vel.y, S.vel.z, 0.0f);
+    W.out.angvel[e] = make_float4(S.angvel.x, S.angvel.y, S.angvel.z, 0.0f);
+    if (rr) {
+        W.out.pos[e] = make_float4(S.origin.x, S.origin.y, S.origin.z, 0.0f);
+        const float lim = W.margin * 0.98f;
+        if (!(fabsf(S.origin.x - s.pos0.x) <= lim && fabsf(S.origin.y - s.pos0.y) <= lim && fabsf(S.origin.z - s.pos0.z) <= lim))
+            atomicOr(W.flags, RF_MARGIN_VIOLATED);
+    } else {
+        W.out.acc[e] = make_float4(S.acc.x, S.acc.y, S.acc.z, 0.0f);
+        W.out.angacc[e] = make_float4(S.angacc.x, S.angacc.y, S.angacc.z, 0.0f);
+    }
+}
+
 // One iteration of the reference's inner loop body (collision_physics_relay.h:39-228) for packets
-// pa < pb.  n_dirty: bodies with dirty_slot < n_dirty may be written; a hit on any other mutable
-// body aborts the attempt (see file header).
+// pa < pb, executed by a whole warp (all lanes pass the same arguments).  n_dirty: bodies with
+// dirty_slot < n_dirty may be written; a hit on any other mutable body aborts the attempt (see the
+// file header).
 static __device__ __noinline__ void process_pair(const DeviceWorld& W, uint32_t pa, uint32_t pb, uint32_t n_dirty, uint32_t ctr_new)
 {
+    const bool writer = (threadIdx.x & 31u) == 0u;
     const uint32_t ea = W.pk_entity[pa], eb = W.pk_entity[pb];
-    const float4 lposA = W.pk_lpos[pa], lposB = W.pk_lpos[pb];
-    const uint32_t bitsA = __float_as_uint(lposA.w), bitsB = __float_as_uint(lposB.w);
+    const uint32_t bitsA = __float_as_uint(W.pk_lpos[pa].w), bitsB = __float_as_uint(W.pk_lpos[pb].w);
     const int tA = bitsA & PF_TYPE_MASK, tB = bitsB & PF_TYPE_MASK;
-    const float4 posA4 = W.out.pos[ea], posB4 = W.out.pos[eb];
-    V3 baseA, baseB; Shape A, B; Hit h;
-    float mpA = (tA == ICX_COLLIDER_RAY) ? W.pk_minparam[pa] : 1.0f, mpB = (tB == ICX_COLLIDER_RAY) ? W.pk_minparam[pb] : 1.0f;
-    const bool hit = pair_intersect(W, pa, pb, ea, eb, tA, tB, v3(posA4), v3(posB4), A, B, baseA, baseB, mpA, mpB, h);
+    const SideData a = load_side(W, pa, ea), b = load_side(W, pb, eb);
+    V3 baseA, baseB;
+    const Shape A = shape_of(a, tA, baseA), B = shape_of(b, tB, baseB);
+    const V3 posA = v3(a.pos), posB = v3(b.pos);
+    float mpA = (tA == ICX_COLLIDER_RAY) ? a.minparam : 1.0f, mpB = (tB == ICX_COLLIDER_RAY) ? b.minparam : 1.0f;
+
+    // ***** intersection: intersectProcedures[tA][tB], collision_procedures.h:411-417 *****
+    // SAT axis loop by the whole warp; everything after it is serial work with dynamically indexed
+    // scratch arrays: lane 0 alone continues, so that only ONE stack frame per warp is live in L1
+    Hit h; h.point = v3(0.0f, 0.0f, 0.0f); h.normal = v3(0.0f, 0.0f, 0.0f); h.depth = 0.0f;
+    SatPick pick; pick.separated = true; pick.normal = h.normal; pick.depth = 0.0f;
+    const bool bb = tA == ICX_COLLIDER_BOX && tB == ICX_COLLIDER_BOX, sb = tA == ICX_COLLIDER_SPHERE && tB == ICX_COLLIDER_BOX,
+               bs = tA == ICX_COLLIDER_BOX && tB == ICX_COLLIDER_SPHERE;
+    if (bb) pick = sat_warp(A, B, false);
+    else if (sb) pick = sat_warp(A, B, true);
+    else if (bs) pick = sat_warp(B, A, true);
+    if (!writer) return;
+    bool hit = false;
+    if (bb) {
+        if (!pick.separated) { h.normal = pick.normal; h.depth = pick.depth; hit = box_box_finish(A, B, h); }
+    } else if (sb) {
+        if (!pick.separated) { h.normal = pick.normal; h.depth = pick.depth; hit = sphere_box_finish(xform(A.M, 0.0f, 0.0f, 0.0f), xform(A.M, ICX_UNIT_RADIUS, 0.0f, 0.0f), h); }
+    } else if (bs) {                                                                // box_sphere_intersect, .cpp:233-247
+        if (!pick.separated) {
+            h.normal = pick.normal; h.depth = pick.depth; hit = sphere_box_finish(xform(B.M, 0.0f, 0.0f, 0.0f), xform(B.M, ICX_UNIT_RADIUS, 0.0f, 0.0f), h);
+            h.normal = h.normal * -1.0f; h.point = h.point + (h.normal * h.depth);
+        }
+    } else if (tA == ICX_COLLIDER_RAY && tB == ICX_COLLIDER_BOX) {
+        hit = ray_box_intersect(A, posA, B, posB, mpA, h);
+    } else if (tA == ICX_COLLIDER_BOX && tB == ICX_COLLIDER_RAY) {                  // box_ray_intersect, .cpp:249-263
+        hit = ray_box_intersect(B, posB, A, posA, mpB, h);
+        if (hit) { h.normal = h.normal * -1.0f; h.point = h.point + (h.normal * h.depth); }
+    } else if ((W.cfg_flags & ICX_F_SPHERE_SPHERE) && tA == ICX_COLLIDER_SPHERE && tB == ICX_COLLIDER_SPHERE) {
+        hit = sphere_sphere_intersect(A, ICX_UNIT_RADIUS * a.lscale.x * a.prm0.x, B, ICX_UNIT_RADIUS * b.lscale.x * b.prm0.x, h);   // .cpp:403-404
+    }
     if (!hit) return;
-    const uint32_t efA = __float_as_uint(W.prm1[ea].w), efB = __float_as_uint(W.prm1[eb].w);
+    const uint32_t efA = __float_as_uint(a.prm1.w), efB = __float_as_uint(b.prm1.w);
     {
-        const bool cleanA = !(efA & EF_IMMUTABLE) && W.dirty_slot[ea] >= n_dirty;
-        const bool cleanB = !(efB & EF_IMMUTABLE) && W.dirty_slot[eb] >= n_dirty;
+        const bool cleanA = !(efA & EF_IMMUTABLE) && a.slot >= n_dirty;
+        const bool cleanB = !(efB & EF_IMMUTABLE) && b.slot >= n_dirty;
         if (cleanA || cleanB) {                     // the dirty set was too small: grow it, write nothing
-            if (cleanA) mark_dirty(W, ea);
-            if (cleanB) mark_dirty(W, eb);
-            atomicAdd(&W.counters[ctr_new], 1u);
+            if (writer) {
+                if (cleanA) mark_dirty(W, ea);
+                if (cleanB) mark_dirty(W, eb);
+                atomicAdd(&W.counters[ctr_new], 1u);
+            }
             return;
         }
     }
-    if (tA == ICX_COLLIDER_RAY) W.pk_minparam[pa] = mpA;
-    if (tB == ICX_COLLIDER_RAY) W.pk_minparam[pb] = mpB;
+    if (writer) {
+        if (tA == ICX_COLLIDER_RAY) W.pk_minparam[pa] = mpA;
+        if (tB == ICX_COLLIDER_RAY) W.pk_minparam[pb] = mpB;
+    }
 
     // ***** physics response, :82-107 *****
     const uint32_t ctA = (bitsA >> PF_CTYPE_SHIFT) & 3u, ctB = (bitsB >> PF_CTYPE_SHIFT) & 3u;
@@ -192,59 +322,16 @@ static __device__ __noinline__ void process_pair(const DeviceWorld& W, uint32_t 
         const bool sr = ctA == ICX_COLLISION_SPRING && ctB == ICX_COLLISION_RIGID;
         const bool rs = ctA == ICX_COLLISION_RIGID && ctB == ICX_COLLISION_SPRING;
         if (rr || sr || rs) {                                                       // other table entries are null_response
-            Side SA, SB;
-            {
-                const float4 v = W.out.vel[ea], w = W.out.angvel[ea], p0 = W.prm0[ea], p1 = W.prm1[ea], m0 = W.pk_mat0[pa];
-                SA.origin = v3(posA4); SA.vel = v3(v); SA.angvel = v3(w); SA.mass = p0.w; SA.colAngDrag = p1.z;
-                SA.L = mat3_of(A.M); SA.base = baseA; SA.inv = A.inv;
-                const float4* d = W.pk_d + (size_t)pa * 6; SA.inertia = v3(d[3].w, d[4].w, d[5].w);
-                SA.staticFriction = m0.x; SA.dynamicFriction = m0.y; SA.restitution = m0.z; SA.stiffness = m0.w;
-                SA.damping = W.pk_damping[pa]; SA.restLength = W.pk_lscale[pa].w;
-                SA.influenceOrientation = (bitsA & PF_INFLUENCE_ORIENT) != 0;
-                if (!rr) { SA.acc = v3(W.out.acc[ea]); SA.angacc = v3(W.out.angacc[ea]); }
-            }
-            {
-                const float4 v = W.out.vel[eb], w = W.out.angvel[eb], p0 = W.prm0[eb], p1 = W.prm1[eb], m0 = W.pk_mat0[pb];
-                SB.origin = v3(posB4); SB.vel = v3(v); SB.angvel = v3(w); SB.mass = p0.w; SB.colAngDrag = p1.z;
-                SB.L = mat3_of(B.M); SB.base = baseB; SB.inv = B.inv;
-                const float4* d = W.pk_d + (size_t)pb * 6; SB.inertia = v3(d[3].w, d[4].w, d[5].w);
-                SB.staticFriction = m0.x; SB.dynamicFriction = m0.y; SB.restitution = m0.z; SB.stiffness = m0.w;
-                SB.damping = W.pk_damping[pb]; SB.restLength = W.pk_lscale[pb].w;
-                SB.influenceOrientation = (bitsB & PF_INFLUENCE_ORIENT) != 0;
-                if (!rr) { SB.acc = v3(W.out.acc[eb]); SB.angacc = v3(W.out.angacc[eb]); }
-            }
+            Side SA = side_of(a, A, baseA, bitsA), SB = side_of(b, B, baseB, bitsB);
             if (rr) rigid_rigid_response(SA, SB, h);
             else if (sr) spring_rigid_response(SA, SB, h);
             else {                                                                  // rigid_spring_response, .cpp:1055-1065
                 Hit inv; inv.normal = -h.normal; inv.point = h.point - (h.normal * h.depth); inv.depth = h.depth;
                 spring_rigid_response(SB, SA, inv);
             }
-            const float lim = W.margin * 0.98f;
-            if (!(efA & EF_IMMUTABLE)) {
-                W.out.vel[ea] = make_float4(SA.vel.x, SA.vel.y, SA.vel.z, 0.0f);
-                W.out.angvel[ea] = make_float4(SA.angvel.x, SA.angvel.y, SA.angvel.z, 0.0f);
-                if (rr) {
-                    W.out.pos[ea] = make_float4(SA.origin.x, SA.origin.y, SA.origin.z, 0.0f);
-                    const float4 o0 = W.pos0[ea];
-                    if (!(fabsf(SA.origin.x - o0.x) <= lim && fabsf(SA.origin.y - o0.y) <= lim && fabsf(SA.origin.z - o0.z) <= lim))
-                        atomicOr(W.flags, RF_MARGIN_VIOLATED);
-                } else {
-                    W.out.acc[ea] = make_float4(SA.acc.x, SA.acc.y, SA.acc.z, 0.0f);
-                    W.out.angacc[ea] = make_float4(SA.angacc.x, SA.angacc.y, SA.angacc.z, 0.0f);
-                }
-            }
-            if (!(efB & EF_IMMUTABLE)) {
-                W.out.vel[eb] = make_float4(SB.vel.x, SB.vel.y, SB.vel.z, 0.0f);
-                W.out.angvel[eb] = make_float4(SB.angvel.x, SB.angvel.y, SB.angvel.z, 0.0f);
-                if (rr) {
-                    W.out.pos[eb] = make_float4(SB.origin.x, SB.origin.y, SB.origin.z, 0.0f);
-                    const float4 o0 = W.pos0[eb];
-                    if (!(fabsf(SB.origin.x - o0.x) <= lim && fabsf(SB.origin.y - o0.y) <= lim && fabsf(SB.origin.z - o0.z) <= lim))
-                        atomicOr(W.flags, RF_MARGIN_VIOLATED);
-                } else {
-                    W.out.acc[eb] = make_float4(SB.acc.x, SB.acc.y, SB.acc.z, 0.0f);
-                    W.out.angacc[eb] = make_float4(SB.angacc.x, SB.angacc.y, SB.angacc.z, 0.0f);
-                }
+            if (writer) {
+                if (!(efA & EF_IMMUTABLE)) store_side(W, ea, SA, a, rr);
+                if (!(efB & EF_IMMUTABLE)) store_side(W, eb, SB, b, rr);
             }
         }
     }
@@ -252,7 +339,7 @@ static __device__ __noinline__ void process_pair(const DeviceWorld& W, uint32_t 
     // ***** behaviours response :114-155 -> contact record, replayed by the host adapter *****
     if (bitsA & PF_BEHAVIORS) cflags |= ICX_CONTACT_BEHAVIORS_A;
     if (bitsB & PF_BEHAVIORS) cflags |= ICX_CONTACT_BEHAVIORS_B;
-    const uint32_t idA = W.entity_id[ea], idB = W.entity_id[eb];
+    const uint32_t idA = a.id, idB = b.id;
     {
         const uint32_t ci = atomicAdd(&W.counters[CTR_CONTACTS], 1u);
         if (ci < W.max_contacts) {
@@ -269,8 +356,7 @@ static __device__ __noinline__ void process_pair(const DeviceWorld& W, uint32_t 
     // ***** timestream response :157-228 *****
     const uint32_t thisLink = idA & 0xFu, otherLink = idB & 0xFu;                   // derive_causal_chain_link, ecs_types.h:92-95
     if (thisLink == ICX_NULL_CHAINLINK || otherLink == ICX_NULL_CHAINLINK) return;  // :185-188
-    const uint32_t tsA = W.out.ts[ea], tsB = W.out.ts[eb];
-    const bool dA = divergent(tsA & 0xFFu), dB = divergent(tsB & 0xFFu);
+    const bool dA = divergent(a.ts & 0xFFu), dB = divergent(b.ts & 0xFFu);
     if (!(((thisLink == 0) != (otherLink == 0))
           || (thisLink != 0 && otherLink != 0 && (dA != dB))
           || (thisLink != otherLink && (!dA || !dB) && W.host_timeslice == ICX_NULL_TIMESLICE)))
@@ -309,7 +395,13 @@ __global__ void __launch_bounds__(128) k_narrow(DeviceWorld W)
     const uint32_t ea = W.pk_entity[pa], eb = W.pk_entity[pb];
     const int tA = __float_as_uint(W.pk_lpos[pa].w) & PF_TYPE_MASK, tB = __float_as_uint(W.pk_lpos[pb].w) & PF_TYPE_MASK;
     if (is_sat_pair(tA, tB)) {
-        if (!sat_may_hit(W.pk_d + (size_t)pa * 6, W.pk_d + (size_t)pb * 6, v3(W.out.pos[ea]), v3(W.out.pos[eb]), tA, tB, 0.25f * W.margin)) continue;
+        const V3 oa = v3(W.out.pos[ea]), ob = v3(W.out.pos[eb]);
+        if (!sat_may_hit(W.pk_d + (size_t)pa * 6, W.pk_d + (size_t)pb * 6, oa, ob, tA, tB, 0.25f * W.margin)) continue;
+        if (!sat_may_hit(W.pk_d + (size_t)pa * 6, W.pk_d + (size_t)pb * 6, oa, ob, tA, tB, 0.0f)) {
+            // close but apart: if one of the two turns out to be hit (and pushed), the other is replayed in order too
+            if (!(pr.y & ICX_PAIR_STATIC)) { const uint32_t q = atomicAdd(&W.counters[CTR_NEAR], 1u); if (q < W.max_pairs) W.near[q] = make_uint2(ea, eb); }
+            continue;
+        }
     } else {
         V3 baseA, baseB; Shape A, B; Hit h;
         float mpA = 1.0f, mpB = 1.0f;           // Collider::reset value; a ray that hits is dirty and replayed in order
@@ -430,60 +522,96 @@ static __device__ __noinline__ void restore_body(const DeviceWorld& W, uint32_t 
     for (uint32_t k = 0; k < (fp >> 30); k++) W.pk_minparam[(fp & 0x3FFFFFFFu) + k] = 1.0f;
 }
 
-// One dependency round for the dirty slot of each lane (s == ICX_NONE: idle lane).  The warp
-// alternates between a divergent, cheap phase -- every lane walks its cursor past the entries the
-// separating-axis filter rejects, up to the next pair that needs the exact procedure -- and a
-// converged phase in which all such lanes run the exact narrowphase + response together.
-__device__ __forceinline__ void round_step_warp(const DeviceWorld& W, uint32_t s, uint32_t n_dirty, int parity, uint32_t ctr_out, uint32_t ctr_new)
+// ---- dependency rounds -----------------------------------------------------------------
+// A dirty body's cursor always rests on an entry that needs attention: a one-sided pair (clean or
+// immutable partner) the filter could not reject, or a two-sided pair (dirty partner).  One round =
+//   select   (one lane per active body)  one-sided pair -> work item; two-sided pair -> ready iff
+//            the partner's cursor rests on the same pair (both read the round-start cursors); the
+//            lower packet's lane then either consumes a certain miss or queues a work item
+//   execute  (one WARP per work item, so the divergent exact code never serialises 32 bodies)
+//            exact narrowphase + response, then both cursors advance past the one-sided pairs the
+//            filter rejects against the bodies' new state
+// separated by grid barriers.  Cursors are double buffered (head[parity]); each active body has
+// exactly one writer per round.
+
+// advance past leading one-sided entries the filter rejects (own state is final for this round,
+// the partners are never written)
+__device__ __forceinline__ uint32_t skip_rejects(const DeviceWorld& W, const Cursor& c, uint32_t hw, uint32_t n_dirty)
 {
-    const uint32_t FULL = 0xFFFFFFFFu;
-    const uint32_t* __restrict__ hin = W.head[parity];
-    uint32_t* __restrict__ hout = W.head[parity ^ 1];
-    bool done = s == ICX_NONE, handed_over = false, first = true;
-    Cursor c = {}; uint32_t hw = 0;
-    if (!done) { c = load_cursor(W, s, W.dirty_list[s]); hw = hin[s]; }
     for (;;) {
-        bool have = false, two = false, partner_pending = false;
-        uint32_t pa = 0, pb = 0, k = 0, so = ICX_NONE, hwo2 = 0;
-        while (!done) {
-            uint32_t entry;
-            if (!cursor_head(c, hw, k, entry)) { done = true; break; }
-            const uint32_t p = c.p0 + k, o = entry & ICX_NB_INDEX_MASK;
-            uint32_t eo = 0; so = ICX_NONE;
-            if (!(entry & ICX_NB_IMMUTABLE)) { eo = W.pk_entity[o]; so = W.dirty_slot[eo]; }
-            pa = min(p, o); pb = max(p, o);
-            if (so >= n_dirty) {                        // immutable or clean partner: no ordering, never written
-                if (may_hit(W, pa, pb, 0.0f)) { have = true; two = false; break; }
-                hw = cursor_advance(hw, k); first = false;
-                continue;
-            }
-            if (!first) { done = true; break; }         // a two-sided pair must be at my cursor at round start
-            const Cursor co = load_cursor(W, so, eo);
-            const uint32_t hwo = hin[so];
-            uint32_t ko, entryo;
-            if (!cursor_head(co, hwo, ko, entryo)) { done = true; break; }                      // cannot happen for consistent lists
-            if (co.p0 + ko != o || (entryo & ICX_NB_INDEX_MASK) != p) { done = true; break; }    // partner is not ready: wait
-            if (p > o) { done = true; handed_over = true; break; }  // I am the B side: the A lane advances and re-queues me
-            hwo2 = cursor_advance(hwo, ko); partner_pending = cursor_pending(co, hwo2);
-            if (may_hit(W, pa, pb, 0.0f)) { have = true; two = true; break; }
-            hw = cursor_advance(hw, k); first = false;  // certain miss: consume it on both sides
-            hout[so] = hwo2;
-            if (partner_pending) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = so;
-        }
-        if (!__any_sync(FULL, have)) break;
-        if (have) {
-            process_pair(W, pa, pb, n_dirty, ctr_new);
-            hw = cursor_advance(hw, k); first = false;
-            if (two) {
-                hout[so] = hwo2;
-                if (partner_pending) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = so;
-            }
-        }
-        __syncwarp();
+        uint32_t k, entry;
+        if (!cursor_head(c, hw, k, entry)) return hw;
+        const uint32_t p = c.p0 + k, o = entry & ICX_NB_INDEX_MASK;
+        if (!(entry & ICX_NB_IMMUTABLE) && W.dirty_slot[W.pk_entity[o]] < n_dirty) return hw;     // two-sided
+        if (may_hit(W, min(p, o), max(p, o), 0.0f)) return hw;
+        hw = cursor_advance(hw, k);
     }
-    if (s != ICX_NONE && !handed_over) {
-        hout[s] = hw;
-        if (cursor_pending(c, hw)) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = s;
+}
+
+__device__ __forceinline__ void settle(const DeviceWorld& W, uint32_t s, const Cursor& c, uint32_t hw, uint32_t n_dirty, int parity, uint32_t ctr_out)
+{
+    hw = skip_rejects(W, c, hw, n_dirty);
+    W.head[parity ^ 1][s] = hw;
+    if (cursor_pending(c, hw)) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = s;
+}
+
+__device__ __forceinline__ void round_select(const DeviceWorld& W, uint32_t s, uint32_t n_dirty, int parity, uint32_t ctr_out, uint32_t ctr_items)
+{
+    const uint32_t* __restrict__ hin = W.head[parity];
+    const uint32_t e = W.dirty_list[s];
+    const Cursor c = load_cursor(W, s, e);
+    const uint32_t hw = hin[s];
+    uint32_t k, entry;
+    if (!cursor_head(c, hw, k, entry)) return;                                      // (not queued when nothing is pending)
+    const uint32_t p = c.p0 + k, o = entry & ICX_NB_INDEX_MASK;
+    uint32_t eo = 0, so = ICX_NONE;
+    if (!(entry & ICX_NB_IMMUTABLE)) { eo = W.pk_entity[o]; so = W.dirty_slot[eo]; }
+    if (so >= n_dirty) {                                                            // one-sided, not rejected by the filter
+        W.items[atomicAdd(&W.counters[ctr_items], 1u)] = make_uint4(min(p, o), max(p, o), s, ICX_NONE);
+        return;
+    }
+    const Cursor co = load_cursor(W, so, eo);
+    const uint32_t hwo = hin[so];
+    uint32_t ko, entryo;
+    const bool ready = cursor_head(co, hwo, ko, entryo) && co.p0 + ko == o && (entryo & ICX_NB_INDEX_MASK) == p;
+    if (!ready) {                                                                   // wait: carry my cursor over
+        W.head[parity ^ 1][s] = hw;
+        W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = s;
+        return;
+    }
+    if (p > o) return;                                                              // the lower packet's lane acts for both
+    if (may_hit(W, p, o, 0.0f)) { W.items[atomicAdd(&W.counters[ctr_items], 1u)] = make_uint4(p, o, s, so); return; }
+    settle(W, s, c, cursor_advance(hw, k), n_dirty, parity, ctr_out);               // certain miss: consumed on both sides
+    settle(W, so, co, cursor_advance(hwo, ko), n_dirty, parity, ctr_out);
+}
+
+__device__ __forceinline__ void round_execute(const DeviceWorld& W, uint4 item, uint32_t n_dirty, int parity, uint32_t ctr_out, uint32_t ctr_new)
+{
+    process_pair(W, item.x, item.y, n_dirty, ctr_new);             // whole warp
+    __syncwarp();
+    // Advance the cursor(s).  One-sided pairs that follow need no partner: the warp runs them at once
+    // instead of spending a round on each (all lanes walk the cursor redundantly, lane 0 writes).
+    for (int side = 0; side < 2; side++) {
+        const uint32_t s = side ? item.w : item.z;
+        if (s == ICX_NONE) continue;
+        const Cursor c = load_cursor(W, s, W.dirty_list[s]);
+        uint32_t k, entry;
+        uint32_t hw = W.head[parity][s];
+        cursor_head(c, hw, k, entry);                                               // the entry just executed
+        hw = cursor_advance(hw, k);
+        for (;;) {
+            hw = skip_rejects(W, c, hw, n_dirty);
+            if (!cursor_head(c, hw, k, entry)) break;
+            const uint32_t p = c.p0 + k, o = entry & ICX_NB_INDEX_MASK;
+            if (!(entry & ICX_NB_IMMUTABLE) && W.dirty_slot[W.pk_entity[o]] < n_dirty) break;     // two-sided: next round
+            process_pair(W, min(p, o), max(p, o), n_dirty, ctr_new);
+            __syncwarp();
+            hw = cursor_advance(hw, k);
+        }
+        if ((threadIdx.x & 31u) == 0u) {
+            W.head[parity ^ 1][s] = hw;
+            if (cursor_pending(c, hw)) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = s;
+        }
     }
 }
 
@@ -499,7 +627,8 @@ __device__ __forceinline__ void trace_mark(const DeviceWorld& W, uint32_t& n, ui
     W.trace[n++] = t; W.trace[n++] = tag;
 }
 
-__global__ void __launch_bounds__(128) k_resolve(DeviceWorld W, double dt, int do_euler)
+#define RESOLVE_TPB 384
+__global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(DeviceWorld W, double dt, int do_euler)
 {
     uint32_t tn = 2;        // trace[0] = number of words used
     cg::grid_group grid = cg::this_grid();
@@ -507,26 +636,42 @@ __global__ void __launch_bounds__(128) k_resolve(DeviceWorld W, double dt, int d
     volatile uint32_t* ctr = W.counters;
     uint32_t attempts = 0, rounds = 0;
     if (tid == 0) trace_mark(W, tn, 0u);
+    {   // one ring around the speculatively hit bodies: neighbours they may be pushed into
+        const uint32_t n_hit = ctr[CTR_DIRTY], n_near = min(ctr[CTR_NEAR], W.max_pairs);
+        grid.sync();
+        for (uint32_t i = tid; i < n_near; i += nth) {
+            const uint2 pr = W.near[i];
+            const bool da = W.dirty_slot[pr.x] < n_hit, db = W.dirty_slot[pr.y] < n_hit;
+            if (da != db) {
+                const uint32_t other = da ? pr.y : pr.x;
+                if (!(__float_as_uint(W.prm1[other].w) & EF_IMMUTABLE)) mark_dirty(W, other);
+            }
+        }
+        grid.sync();
+    }
     for (;;) {
         const uint32_t n_dirty = ctr[CTR_DIRTY], n_listed = ctr[CTR_LISTED], n_static = min(ctr[CTR_STATIC], W.max_static);
         for (uint32_t s = n_listed + (tid >> 5); s < n_dirty; s += (nth >> 5)) build_lists_warp(W, s);
-        for (uint32_t s = tid; s < n_dirty; s += nth) {
+        for (uint32_t s = tid; s < n_dirty; s += nth)
             if (attempts > 0 && s < n_listed) restore_body(W, W.dirty_list[s], dt, do_euler);
-            W.head[0][s] = 0u; W.active[0][s] = s;
-        }
-        if (tid == 0) trace_mark(W, tn, 0x10000u | n_dirty);
+        if (tid == 0) trace_mark(W, tn, 0x10000u | min(n_dirty, 0xFFFFu));
         grid.sync();
         if (tid == 0) trace_mark(W, tn, 0x20000u);
         if (*(volatile uint32_t*)W.flags & RF_NEIGHBOR_OVERFLOW) break;     // lists are incomplete: the host grows them and re-runs the tick
         if (tid == 0) {
             ctr[CTR_LISTED] = n_dirty; ctr[CTR_CONTACTS] = 0; ctr[CTR_INTERCEPTS] = 0;
             ctr[CTR_NEWD] = 0; ctr[CTR_NEWD + 1] = 0; ctr[CTR_NEWD + 2] = 0;
-            ctr[CTR_ACTIVE] = n_dirty; ctr[CTR_ACTIVE + 1] = 0; ctr[CTR_ACTIVE + 2] = 0;
+            ctr[CTR_ACTIVE] = 0; ctr[CTR_ACTIVE + 1] = 0; ctr[CTR_ACTIVE + 2] = 0;
+            ctr[CTR_ITEMS] = 0; ctr[CTR_ITEMS + 1] = 0;
             __threadfence();
         }
         grid.sync();
-        for (uint32_t i = tid; i < n_static; i += nth) { const uint2 pr = W.static_pairs[i]; process_pair(W, pr.x, pr.y, n_dirty, CTR_NEWD); }
-        __syncwarp();
+        // static pairs (contact records only), then every body's cursor to its first entry of interest
+        for (uint32_t i = tid >> 5; i < n_static; i += nth >> 5) { const uint2 pr = W.static_pairs[i]; process_pair(W, pr.x, pr.y, n_dirty, CTR_NEWD); }
+        for (uint32_t s = tid; s < n_dirty; s += nth)
+            settle(W, s, load_cursor(W, s, W.dirty_list[s]), 0u, n_dirty, 1, CTR_ACTIVE);     // writes head[0] / active[0]
+        grid.sync();
+        if (tid == 0) trace_mark(W, tn, 0x50000u);
         int parity = 0;
         rounds = 0;
         for (;;) {
@@ -534,13 +679,15 @@ __global__ void __launch_bounds__(128) k_resolve(DeviceWorld W, double dt, int d
             const uint32_t grew = rounds ? ctr[CTR_NEWD + (rounds + 2u) % 3u] : 0u;    // written in the previous round only
             if (n_act == 0u || grew != 0u) break;       // done, or the dirty set grew: restart at once
             if (rounds >= ICX_MAX_ROUNDS) { if (tid == 0) atomicOr(W.flags, RF_ROUNDS_EXCEEDED); break; }
-            if (tid == 0) { ctr[CTR_ACTIVE + (rounds + 2u) % 3u] = 0u; ctr[CTR_NEWD + (rounds + 1u) % 3u] = 0u; }
-            for (uint32_t base = tid & ~31u; base < n_act; base += nth) {       // warp-uniform trip count
-                const uint32_t i = base + (tid & 31u);
-                round_step_warp(W, i < n_act ? W.active[parity][i] : ICX_NONE, n_dirty, parity, CTR_ACTIVE + (rounds + 1u) % 3u, CTR_NEWD + rounds % 3u);
-            }
+            const uint32_t ctr_out = CTR_ACTIVE + (rounds + 1u) % 3u, ctr_items = CTR_ITEMS + (rounds & 1u);
+            if (tid == 0) { ctr[CTR_ACTIVE + (rounds + 2u) % 3u] = 0u; ctr[CTR_NEWD + (rounds + 1u) % 3u] = 0u; ctr[CTR_ITEMS + ((rounds + 1u) & 1u)] = 0u; }
+            for (uint32_t i = tid; i < n_act; i += nth) round_select(W, W.active[parity][i], n_dirty, parity, ctr_out, ctr_items);
             grid.sync();
-            if (tid == 0) trace_mark(W, tn, 0x30000u | min(n_act, 0xFFFFu));
+            const uint32_t n_items = ctr[ctr_items];
+            for (uint32_t i = tid >> 5; i < n_items; i += nth >> 5)
+                round_execute(W, W.items[i], n_dirty, parity, ctr_out, CTR_NEWD + rounds % 3u);
+            grid.sync();
+            if (tid == 0) trace_mark(W, tn, 0x30000u | min(n_items, 0xFFFFu));
             rounds++; parity ^= 1;
         }
         grid.sync();
@@ -559,7 +706,7 @@ void launch_narrow(const DeviceWorld& W, int blocks, cudaStream_t st)
 int resolve_grid_blocks(int device)
 {
     int per_sm = 0, sms = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_resolve, 128, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_resolve, RESOLVE_TPB, 0);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     return per_sm * sms;
 }
@@ -568,7 +715,7 @@ cudaError_t launch_resolve(const DeviceWorld& W, double dt, int do_euler, int bl
 {
     DeviceWorld Wc = W;
     void* args[] = {&Wc, &dt, &do_euler};
-    return cudaLaunchCooperativeKernel((const void*)k_resolve, dim3(blocks), dim3(128), args, 0, st);
+    return cudaLaunchCooperativeKernel((const void*)k_resolve, dim3(blocks), dim3(RESOLVE_TPB), args, 0, st);
 }
 
 } // namespace icx

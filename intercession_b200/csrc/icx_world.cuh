@@ -100,6 +100,7 @@ struct DeviceWorld {
     uint32_t* large_list;           // packets larger than a cell (immutable only)
     // flat candidate pair list (the broadphase output, icx_pairs_fetch)
     uint2* pairs; uint32_t max_pairs;
+    uint2* near;                    // entity pairs that are close but apart on the post-integration state
     uint2* tight;                   // the subset with ICX_PAIR_TIGHT (input of the speculative narrowphase)
     uint2* static_pairs; uint32_t max_static;    // hits between two immutable bodies (contact records only)
     // bodies touched by at least one hit ("dirty"): only these need the reference's sequential order
@@ -110,6 +111,7 @@ struct DeviceWorld {
     uint32_t max_neighbors;
     uint32_t* head[2];              // per dirty slot: consumed entries of the slot-0 list | slot-1 list << 16
     uint32_t* active[2];            // dirty-slot work lists of the dependency rounds
+    uint4* items;                   // per round: pairs that need the exact procedure {pa, pb, slot a, slot b | ICX_NONE}
     // outputs
     IcxContact* contacts; IcxInterception* intercepts; uint2* intercept_key; uint32_t max_contacts;
     // counters, one cache line each would be nicer; they are cold
@@ -125,12 +127,14 @@ struct DeviceWorld {
 
 enum { CTR_LARGE = 0, CTR_DIRTY = 1, CTR_CONTACTS = 2, CTR_INTERCEPTS = 3, CTR_CANDIDATES = 4, CTR_STATIC = 5,
        CTR_LISTED = 6,          // dirty bodies whose candidate lists are built
-       CTR_ROUNDS = 7, CTR_ATTEMPTS = 8, CTR_NEW_DIRTY = 9, CTR_TIGHT = 10,
+       CTR_ROUNDS = 7, CTR_ATTEMPTS = 8, CTR_NEAR = 9, CTR_TIGHT = 10,
        CTR_NEED_CELL = 11,      // float bits: cell size a too-large mutable collider needs
        CTR_EXTENT = 12,         // float bits: largest collider extent seen at import
        CTR_ACTIVE = 13,         // 3 rotating work-list counters: CTR_ACTIVE + (round % 3)
+       CTR_ITEMS = 18,          // 2 alternating work-item counters
        CTR_NEWD = 20,           // 3 rotating per-round counts of bodies that turned dirty during the replay
-       CTR_TOTAL = 32 };
+       CTR_PROF = 32,           // ICX_PROFILE_PAIR builds: cycle accumulators
+       CTR_TOTAL = 48 };
 #define ICX_MAX_ROUNDS 65535u
 #define ICX_TRACE_CAP 512
 

@@ -1,4 +1,5 @@
-import sys, os
+import sys, os, ctypes
+import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from intercession_b200 import scenes, world
 s = scenes.config3(int(sys.argv[1]) if len(sys.argv) > 1 else 1048576)
@@ -6,6 +7,10 @@ w = world.World(s.n); w.upload(s); w.step(1/45, 4); w.trace(True)
 for k in range(2):
     w.step(1/45); st = w.stats()
     print("tick", k, "dirty", st.n_dirty, "rounds", st.n_rounds, "attempts", st.n_attempts, "contacts", st.n_contacts, "ms", w.last_step_ms())
+    cn = np.zeros(48, np.uint32); w.lib.icx_debug_counters(w.handle, cn.ctypes.data_as(ctypes.c_void_p)); pr = cn[32:]
+    if pr[0]:
+        print("  exact pairs", pr[0], "load wait", pr[1]/pr[0], "intersect", pr[2]/pr[0], "| responses", pr[3], "response+clean", pr[4]/max(pr[3],1),
+              "| box finishes", pr[5], "cycles", pr[6]/max(pr[5],1))
     prev = 0
     for t, tag in w.trace(True):
         print(f"  {t/1e3:9.1f} us (+{(t-prev)/1e3:7.1f})  tag {tag>>16:x} arg {tag&0xffff}")
