@@ -291,6 +291,54 @@ ICX_API int icx_debug_counters(IcxWorld* w, uint32_t* out32);
 /* CUDA stream of the world as a void* (cudaStream_t), for callers that time it. */
 ICX_API void* icx_world_stream(IcxWorld* w);
 
+/* ==== world-line record / replay / divergence scan ========================================
+ * The dense ENTITY_UPDATE stream between adjacent timeslices (EntityTimestreamMap,
+ * source/networking/entity_timestream_map.h:43-230) as a device-resident ring of SoA snapshots:
+ * slot = coherency % depth_ticks.  Entities are matched by upload index (the reference matches by
+ * id with the causal chain-link incremented on the way into the past, server_network_dynamo.cpp:673).
+ * create / remove / jump events stay on the host TimelineApi queues. */
+#define ICX_REPLAY_SERVER   0   /* ServerNetworkDynamo::run_relays phase 2, server_network_dynamo.cpp:377-421  */
+#define ICX_REPLAY_PARALLEL 1   /* ParallelNetworkDynamo::run_relays,     parallel_network_dynamo.cpp:51-89 */
+
+ICX_API int  icx_timeline_create(int device, uint32_t depth_ticks, uint32_t n_max, IcxTimeline** out);
+ICX_API void icx_timeline_destroy(IcxTimeline* tl);
+ICX_API const char* icx_timeline_last_error(const IcxTimeline* tl);
+
+/* Record = serialise every entity at `coherency` and push it (TimelineApi::push_past_timestream,
+ * server_network_dynamo.cpp:642-679; push_timestream_at_breakpoint rewrites the same slot,
+ * parallel_network_dynamo.cpp:369-385).  Asynchronous on the world's stream. */
+ICX_API int icx_record(IcxWorld* w, IcxTimeline* tl, uint16_t coherency);
+ICX_API int icx_record_at_breakpoint(IcxWorld* w, IcxTimeline* tl, uint16_t coherency);
+
+/* Breakpoint of the timestreams (TsBreakpointQueue::set_breakpoint_at_begin / remove_breakpoint,
+ * source/networking/ts_breakpoint_queue.h:107-121, set by link_timestreams when a parallel cosmos is
+ * linked): records present when it is set, and later plain records, lie BEHIND it -- ICX_REPLAY_SERVER
+ * cannot pop them, ICX_REPLAY_PARALLEL pops only them; icx_record_at_breakpoint inserts in front of it. */
+ICX_API int icx_breakpoint_set(IcxTimeline* tl);
+ICX_API int icx_breakpoint_clear(IcxTimeline* tl);
+
+/* Replay = pop the record stamped `coherency` (pop_future_timestream / pop_timestream_at_breakpoint)
+ * and apply it: ICX_REPLAY_SERVER overwrites transform + physics of every entity that is not
+ * forking / forked; ICX_REPLAY_PARALLEL only consumes it (a parallel cosmos takes upstream
+ * components only, of which the physics path has none).  *applied = 1 if a record was applied. */
+ICX_API int icx_replay(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, int mode, int* applied);
+
+/* Divergence scan: live origins against the record stamped `coherency`, with the reference's
+ * congruence predicate length2(a - b) <= 2.0f (TimejumpConditions::operator==,
+ * source/spacetime/timejump_conditions.h:21-25).  Per world-line k (cfg.worldline_stride, or one):
+ * flags[k] = any body incongruent, incongruent[k] = how many, score[k] = sum of min(length2, 2^20)
+ * accumulated in 48.16 fixed point (the score is this build's definition, the flag is the
+ * reference's).  The record may cover the whole world or one world-line (a base history shared by
+ * all candidates).  Synchronous. */
+ICX_API int icx_divergence_scan(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, uint32_t n_worldlines,
+                        uint8_t* flags, uint32_t* incongruent, double* score);
+
+/* Fork ageing (server_network_dynamo.cpp:13-15, :681-705): forking -> forked after 13 ticks;
+ * *resolution_needed = some entity has been forked for >= 13 ticks (parallel_notify_divergence). */
+ICX_API int icx_fork_age(IcxWorld* w, uint32_t* n_promoted, int* resolution_needed);
+
+ICX_API int icx_timeline_slot_info(const IcxTimeline* tl, uint16_t coherency, int* valid, uint32_t* n_recorded);
+
 #ifdef __cplusplus
 }
 #endif

@@ -55,6 +55,7 @@ NULL_TIMESLICE, NULL_CHAINLINK, NULL_ENTITY = 14, 15, 0xFFFFFFFF
 F_SPHERE_SPHERE, F_NO_GRAVITY = 1, 2
 CONTACT_RESPONDED, CONTACT_BEHAVIORS_A, CONTACT_BEHAVIORS_B = 1, 2, 4
 OK, E_INVALID, E_CUDA, E_CAPACITY, E_NOMEM, E_STATE = 0, 1, 2, 3, 4, 5
+REPLAY_SERVER, REPLAY_PARALLEL = 0, 1
 
 
 def compose_entity(timeslice, genesis, link):
@@ -152,6 +153,17 @@ SIGNATURES = {
     "icx_last_step_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
     "icx_world_stream": (_vp, [_vp]),
     "icx_profile_enable": (C.c_int, [_vp, C.c_int]),
+    "icx_timeline_create": (C.c_int, [C.c_int, _u32, _u32, C.POINTER(_vp)]),
+    "icx_timeline_destroy": (None, [_vp]),
+    "icx_timeline_last_error": (C.c_char_p, [_vp]),
+    "icx_record": (C.c_int, [_vp, _vp, C.c_uint16]),
+    "icx_record_at_breakpoint": (C.c_int, [_vp, _vp, C.c_uint16]),
+    "icx_breakpoint_set": (C.c_int, [_vp]),
+    "icx_breakpoint_clear": (C.c_int, [_vp]),
+    "icx_replay": (C.c_int, [_vp, _vp, C.c_uint16, C.c_int, C.POINTER(C.c_int)]),
+    "icx_divergence_scan": (C.c_int, [_vp, _vp, C.c_uint16, _u32, _vp, _vp, _vp]),
+    "icx_fork_age": (C.c_int, [_vp, C.POINTER(_u32), C.POINTER(C.c_int)]),
+    "icx_timeline_slot_info": (C.c_int, [_vp, C.c_uint16, C.POINTER(C.c_int), C.POINTER(_u32)]),
     "icx_debug_counters": (C.c_int, [_vp, _vp]),
     "icx_debug_trace": (C.c_int, [_vp, C.c_int, _vp, _sz, _psz]),
     "icx_phase_ms": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),

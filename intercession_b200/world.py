@@ -144,3 +144,62 @@ class World:
         self._ck(self.lib.icx_debug_trace(self.handle, 1 if enable else 0, abi.ptr(buf), len(buf), C.byref(n)))
         v = buf[:n.value].reshape(-1, 2)
         return [(int(t - v[0, 0]), int(tag)) for t, tag in v] if len(v) else []
+
+    # ---- TimelineApi hooks ----
+    def record(self, tl, coherency=None, at_breakpoint=False):
+        fn = self.lib.icx_record_at_breakpoint if at_breakpoint else self.lib.icx_record
+        self._ck_tl(tl, fn(self.handle, tl.handle, self.coherency() if coherency is None else coherency))
+
+    def replay(self, tl, coherency=None, mode=abi.REPLAY_SERVER):
+        applied = C.c_int(0)
+        self._ck_tl(tl, self.lib.icx_replay(self.handle, tl.handle, self.coherency() if coherency is None else coherency, mode, C.byref(applied)))
+        return bool(applied.value)
+
+    def divergence_scan(self, tl, coherency, n_worldlines=1):
+        flags = np.zeros(n_worldlines, np.uint8)
+        count = np.zeros(n_worldlines, np.uint32)
+        score = np.zeros(n_worldlines, np.float64)
+        self._ck_tl(tl, self.lib.icx_divergence_scan(self.handle, tl.handle, coherency, n_worldlines, abi.ptr(flags), abi.ptr(count), abi.ptr(score)))
+        return flags, count, score
+
+    def fork_age(self):
+        n, need = C.c_uint32(0), C.c_int(0)
+        self._ck(self.lib.icx_fork_age(self.handle, C.byref(n), C.byref(need)))
+        return n.value, bool(need.value)
+
+    def _ck_tl(self, tl, rc):
+        if rc != abi.OK:
+            raise IcxError(rc, (self.lib.icx_timeline_last_error(tl.handle) or self.lib.icx_last_error(self.handle)).decode())
+
+
+class Timeline:
+    """Device snapshot ring behind the TimelineApi record / replay hooks (include/icx.h)."""
+
+    def __init__(self, depth_ticks, n_max, device=0):
+        self.lib = abi.load()
+        self.handle = C.c_void_p()
+        rc = self.lib.icx_timeline_create(device, depth_ticks, n_max, C.byref(self.handle))
+        if rc != abi.OK:
+            raise IcxError(rc, self.lib.icx_status_string(rc).decode() + " (icx_timeline_create)")
+
+    def set_breakpoint(self):
+        self.lib.icx_breakpoint_set(self.handle)
+
+    def clear_breakpoint(self):
+        self.lib.icx_breakpoint_clear(self.handle)
+
+    def slot_info(self, coherency):
+        v, n = C.c_int(0), C.c_uint32(0)
+        self.lib.icx_timeline_slot_info(self.handle, coherency, C.byref(v), C.byref(n))
+        return bool(v.value), n.value
+
+    def close(self):
+        if self.handle:
+            self.lib.icx_timeline_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()

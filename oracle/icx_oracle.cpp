@@ -19,6 +19,8 @@
 #include <chrono>
 #include <cmath>
 #include <cstring>
+#include <list>
+#include <map>
 #include <vector>
 #include <algorithm>
 #include <thread>
@@ -846,6 +848,147 @@ int icxo_pairs(uint32_t n, const IcxTransform* T, IcxColliderComponent* C, float
     }
     if (n_pairs) *n_pairs = pairs.size();
     for (size_t k = 0; k < pairs.size() && k < cap; k++) out[k] = pairs[k];
+    return 0;
+}
+
+} // extern "C"
+
+// ---------------------------------------------------------------------------
+// World-line record / replay / divergence scan
+// ---------------------------------------------------------------------------
+namespace {
+
+// cyclic coherency compare, source/events/message.h:179-183
+inline bool coherency_ge(uint16_t a, uint16_t b) { return (a >= b && a - b <= 32768) || (a <= b && b - a > 32768); }
+
+struct Record { uint16_t coherency; IcxEntity entity; IcxTransform T; IcxPhysics P; };
+
+// TsBreakpointQueue, source/networking/ts_breakpoint_queue.h:16-193: a FIFO whose pop_front stops at a
+// movable breakpoint; the parallel context pops AT the breakpoint and inserts BEFORE it.
+struct Stream {
+    std::list<Record> list; std::list<Record>::iterator bp; bool active;
+    Stream() : bp(list.end()), active(false) {}
+    void push_back(const Record& r) { list.push_back(r); if (active && bp == list.end()) --bp; }       // :44-52
+    bool pop_front(Record& d) {                                                                       // :53-64
+        if (list.empty()) return false;
+        if (active && bp == list.begin()) return false;
+        d = list.front(); list.pop_front(); return true;
+    }
+    void set_breakpoint() { bp = list.begin(); active = true; }                                       // :107-112
+    void remove_breakpoint() { bp = list.end(); active = false; }                                     // :113-118
+    bool push_at_breakpoint(const Record& r) { if (!active) return false; list.insert(bp, r); return true; }   // :130-141
+    bool pop_at_breakpoint(Record& d) {                                                               // :143-156
+        if (list.empty() || !active || bp == list.end()) return false;
+        d = *bp; bp = list.erase(bp); return true;
+    }
+    bool available() const { return !(list.empty() || bp == list.begin()); }                          // :158-164 (bp == end when inactive & non-empty)
+    bool available_at_breakpoint() const { return bp != list.end(); }                                 // :165-171
+};
+
+// EntityTimestreamMap, source/networking/entity_timestream_map.h:43-230
+struct Timeline {
+    std::map<IcxEntity, Stream> streams; bool breakpoints = false;
+    Stream& at(IcxEntity e) {
+        auto it = streams.find(e);
+        if (it == streams.end()) { it = streams.emplace(e, Stream()).first; it->second.bp = it->second.list.end(); if (breakpoints) it->second.set_breakpoint(); }   // :63-67
+        return it->second;
+    }
+};
+
+inline IcxEntity inc_link(IcxEntity e) { return (e & 0xFu) + 1u >= 15u ? e : e + 1u; }   // increment_causal_chain_link, ecs_types.h:122-137
+
+} // namespace
+
+extern "C" {
+
+void* icxo_tl_create(void) { return new Timeline(); }
+void icxo_tl_destroy(void* h) { delete static_cast<Timeline*>(h); }
+void icxo_tl_breakpoint(void* h, int set)                                                             // entity_timestream_map.h:181-199
+{
+    Timeline* tl = static_cast<Timeline*>(h);
+    for (auto& kv : tl->streams) { if (set) kv.second.set_breakpoint(); else kv.second.remove_breakpoint(); }
+    tl->breakpoints = set != 0;
+}
+
+// server_network_dynamo.cpp:642-679 (link_inc = 1) / parallel_network_dynamo.cpp:369-385 (at_breakpoint = 1)
+int icxo_tl_record(void* h, uint32_t n, const IcxEntity* ids, const IcxTransform* T, const IcxPhysics* P,
+                   uint16_t coherency, int at_breakpoint, int link_inc)
+{
+    Timeline* tl = static_cast<Timeline*>(h);
+    for (uint32_t i = 0; i < n; i++) {
+        Record r; r.coherency = coherency; r.entity = link_inc ? inc_link(ids[i]) : ids[i]; r.T = T[i]; r.P = P[i];
+        Stream& s = tl->at(r.entity);
+        if (at_breakpoint) s.push_at_breakpoint(r); else s.push_back(r);
+    }
+    return 0;
+}
+
+// server_network_dynamo.cpp:377-421 / parallel_network_dynamo.cpp:51-89
+int icxo_tl_replay(void* h, uint32_t n, const IcxEntity* ids, IcxTransform* T, IcxPhysics* P, const uint8_t* tstate,
+                   uint16_t now, int mode)
+{
+    Timeline* tl = static_cast<Timeline*>(h);
+    int applied = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        auto it = tl->streams.find(ids[i]);
+        if (it == tl->streams.end()) continue;
+        Stream& s = it->second;
+        Record r;
+        for (;;) {
+            bool got;
+            if (mode == ICX_REPLAY_PARALLEL) got = s.available_at_breakpoint() && coherency_ge(now, s.bp->coherency) && s.pop_at_breakpoint(r);   // :141-149, :214-221
+            else got = s.available() && coherency_ge(now, s.list.front().coherency) && s.pop_front(r);                                              // :130-139, :205-212
+            if (!got) break;
+            if (mode == ICX_REPLAY_SERVER && r.coherency < now) continue;           // stale, :391
+            if (mode == ICX_REPLAY_PARALLEL) continue;                              // upstream components only
+            if (!divergent(tstate ? tstate[i] : 0)) { T[i] = r.T; P[i] = r.P; applied++; }
+        }
+    }
+    return applied;
+}
+
+// TimejumpConditions::operator==, source/spacetime/timejump_conditions.h:21-25
+int icxo_congruent(uint32_t n, const IcxTransform* live, const IcxTransform* rec, uint8_t* out)
+{
+    for (uint32_t i = 0; i < n; i++) out[i] = length2(ld3(live[i].origin) - ld3(rec[i].origin)) <= 2.0f ? 1 : 0;
+    return 0;
+}
+int icxo_coherency_ge(uint16_t a, uint16_t b) { return coherency_ge(a, b) ? 1 : 0; }
+
+// Per world-line reduction of the congruence predicate (the build's densification):
+// rec holds n_rec transforms; body i is compared with rec[i % n_rec].  score = sum of
+// min(length2, 2^20) in 48.16 fixed point, returned as a double.
+int icxo_divergence_scan(uint32_t n, const IcxTransform* live, uint32_t n_rec, const IcxTransform* rec, uint32_t stride,
+                         uint8_t* flags, uint32_t* incongruent, double* score)
+{
+    const uint32_t nw = stride ? (n + stride - 1) / stride : 1;
+    std::vector<uint64_t> acc(nw, 0); std::vector<uint32_t> cnt(nw, 0);
+    for (uint32_t i = 0; i < n; i++) {
+        const float len2 = length2(ld3(live[i].origin) - ld3(rec[i % n_rec].origin));
+        const uint32_t w = stride ? i / stride : 0;
+        if (!(len2 <= 2.0f)) cnt[w]++;
+        const float c = (len2 <= 1048576.0f) ? len2 : 1048576.0f;
+        acc[w] += (uint64_t)(c * 65536.0f);
+    }
+    for (uint32_t w = 0; w < nw; w++) {
+        if (flags) flags[w] = cnt[w] ? 1 : 0;
+        if (incongruent) incongruent[w] = cnt[w];
+        if (score) score[w] = (double)acc[w] / 65536.0;
+    }
+    return 0;
+}
+
+// Fork ageing, server_network_dynamo.cpp:13-15, :681-705
+int icxo_fork_age(uint32_t n, uint8_t* tstate, uint16_t* tcoh, uint16_t coherency, uint32_t* n_promoted, int* resolution_needed)
+{
+    uint32_t promoted = 0; int need = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        const uint8_t state = tstate[i]; const uint16_t since = tcoh[i];
+        if (state == ICX_TS_FORKING && since + 13 <= coherency) { tstate[i] = ICX_TS_FORKED; tcoh[i] = coherency; promoted++; }
+        if (state == ICX_TS_FORKED && since + 13 <= coherency) need = 1;
+    }
+    if (n_promoted) *n_promoted = promoted;
+    if (resolution_needed) *resolution_needed = need;
     return 0;
 }
 

@@ -1,5 +1,121 @@
 // TEST INFRASTRUCTURE -- not product code (see ref_harness.cpp header).
-// Reference timestream containers (EntityTimestreamMap / TsBreakpointQueue /
-// Message / coherency compare), header-only in the reference, driven headlessly.
+//
+// The reference's own timestream containers and predicates, driven headlessly:
+//   EntityTimestreamMap / TsBreakpointQueue   source/networking/entity_timestream_map.h, ts_breakpoint_queue.h
+//   Message<EventId> (LIFO byte stack)        source/events/message.h
+//   coherency_greater_or_equal                source/events/message.h:179-183
+//   is_divergent                              source/spacetime/timestream_state.h:41-44
+//   TimejumpConditions::operator==            source/spacetime/timejump_conditions.h:21-25
+// The dynamo code that calls them (ServerNetworkDynamo / ParallelNetworkDynamo::run_relays) does not
+// compile here (asio is not vendored), so the record / replay loops below restate
+//   record : server_network_dynamo.cpp:642-679   parallel_network_dynamo.cpp:369-385
+//   replay : server_network_dynamo.cpp:377-421   parallel_network_dynamo.cpp:51-89
+//   ageing : server_network_dynamo.cpp:13-15, :681-705
+// around the REAL containers, with the entity's components serialised into a real EventMessage in
+// the reference's order (descending component type so that they pop ascending,
+// ecs/component_registry.h:238-253: Transform first registered, then Physics).
 #include "../../include/icx.h"
-extern "C" int icxref_timeline_placeholder(void) { return 0; }
+
+#include "events/event_types.h"
+#include "events/message.h"
+#include "networking/entity_timestream_map.h"
+#include "physics/transform_component.h"
+#include "physics/physics_component.h"
+#include "spacetime/timestream_state.h"
+// timejump_conditions.h pulls in Cosmos only for helpers that are not used here
+#include "core/cosmos.h"
+#include "spacetime/timejump_conditions.h"
+
+#include <memory>
+
+using namespace pleep;
+
+namespace {
+
+struct RefTimeline {
+    EntityTimestreamMap map;
+};
+
+inline Entity narrow(IcxEntity e) { return (Entity)(((e >> 28) << 12) | (((e >> 4) & 0xFFu) << 4) | (e & 0xFu)); }
+
+} // namespace
+
+extern "C" {
+
+void* icxref_tl_create(void) { return new RefTimeline(); }
+void icxref_tl_destroy(void* h) { delete static_cast<RefTimeline*>(h); }
+
+// link_timestreams -> set breakpoints on every stream (entity_timestream_map.h:168-199)
+void icxref_tl_breakpoint(void* h, int set)
+{
+    RefTimeline* tl = static_cast<RefTimeline*>(h);
+    if (set) tl->map.set_breakpoints(); else tl->map.remove_breakpoints();
+}
+
+// Record every entity at `coherency`.  link_inc: the server increments the causal chain-link of the
+// id it pushes into the past (server_network_dynamo.cpp:673); entities are keyed by that id.
+int icxref_tl_record(void* h, uint32_t n, const IcxEntity* ids, const IcxTransform* T, const IcxPhysics* P,
+                     uint16_t coherency, int at_breakpoint, int link_inc)
+{
+    RefTimeline* tl = static_cast<RefTimeline*>(h);
+    for (uint32_t i = 0; i < n; i++) {
+        EventMessage msg(events::cosmos::ENTITY_UPDATE, coherency);
+        // serialize_entity_components: highest component type first
+        msg << *reinterpret_cast<const PhysicsComponent*>(&P[i]);
+        msg << *reinterpret_cast<const TransformComponent*>(&T[i]);
+        Entity e = narrow(ids[i]);
+        if (link_inc) increment_causal_chain_link(e);
+        events::cosmos::ENTITY_UPDATE_params info = { e, Signature(0x3), ComponentCategory::all };
+        msg << info;
+        if (at_breakpoint) tl->map.push_to_timestream_at_breakpoint(e, msg);
+        else tl->map.push_to_timestream(e, msg);
+    }
+    return 0;
+}
+
+// Replay at `now`.  ids are the RECEIVING cosmos' ids (already carrying the incremented link).
+// mode ICX_REPLAY_SERVER: pop_from_timestream, drop stale, apply to non-divergent entities.
+// mode ICX_REPLAY_PARALLEL: pop_from_timestream_at_breakpoint, upstream components only (= none here).
+// Returns the number of entities whose components were overwritten.
+int icxref_tl_replay(void* h, uint32_t n, const IcxEntity* ids, IcxTransform* T, IcxPhysics* P, const uint8_t* tstate,
+                     uint16_t now, int mode)
+{
+    RefTimeline* tl = static_cast<RefTimeline*>(h);
+    int applied = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        const Entity e = narrow(ids[i]);
+        EventMessage evnt(1);
+        for (;;) {
+            const bool got = mode == ICX_REPLAY_PARALLEL ? tl->map.pop_from_timestream_at_breakpoint(e, now, evnt)
+                                                         : tl->map.pop_from_timestream(e, now, evnt);
+            if (!got) break;
+            if (mode == ICX_REPLAY_SERVER && evnt.header.coherency < now) continue;         // :391
+            events::cosmos::ENTITY_UPDATE_params info;
+            evnt >> info;
+            if (mode == ICX_REPLAY_PARALLEL) continue;                                      // upstream only: nothing of ours
+            if (!is_divergent((TimestreamState)(tstate ? tstate[i] : 0))) {                 // :408-412
+                TransformComponent t; PhysicsComponent p;
+                evnt >> t; evnt >> p;                                                       // ascending component type
+                T[i] = *reinterpret_cast<IcxTransform*>(&t);
+                P[i] = *reinterpret_cast<IcxPhysics*>(&p);
+                applied++;
+            }
+        }
+    }
+    return applied;
+}
+
+// Congruence of live vs recorded origins with the reference's own operator==.
+int icxref_congruent(uint32_t n, const IcxTransform* live, const IcxTransform* rec, uint8_t* out)
+{
+    for (uint32_t i = 0; i < n; i++) {
+        TimejumpConditions a{0, glm::vec3(live[i].origin[0], live[i].origin[1], live[i].origin[2])};
+        TimejumpConditions b{0, glm::vec3(rec[i].origin[0], rec[i].origin[1], rec[i].origin[2])};
+        out[i] = (a == b) ? 1 : 0;
+    }
+    return 0;
+}
+
+int icxref_coherency_ge(uint16_t a, uint16_t b) { return coherency_greater_or_equal(a, b) ? 1 : 0; }
+
+} // extern "C"

@@ -137,3 +137,58 @@ def procedures_tick(lib, prefix, scene, dt=1.0 / 45, host=0, coherency=0, flags=
     assert nh.value <= cap and ni.value <= cap
     s["hits"], s["ints"], s["seconds"] = hits[:nh.value], ints[:ni.value], sec1.value + sec2.value
     return s
+
+
+# ---- timeline checkers (oracle/ref/ref_timeline.cpp: the reference's real containers; oracle: restatement) ----
+_TL_SIGS = {
+    "{p}_tl_create": (_vp, []),
+    "{p}_tl_destroy": (None, [_vp]),
+    "{p}_tl_breakpoint": (None, [_vp, C.c_int]),
+    "{p}_tl_record": (C.c_int, [_vp, _u32, _vp, _vp, _vp, C.c_uint16, C.c_int, C.c_int]),
+    "{p}_tl_replay": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp, C.c_uint16, C.c_int]),
+    "{p}_congruent": (C.c_int, [_u32, _vp, _vp, _vp]),
+    "{p}_coherency_ge": (C.c_int, [C.c_uint16, C.c_uint16]),
+}
+REF_SIGS.update({k.format(p="icxref"): v for k, v in _TL_SIGS.items()})
+ORACLE_SIGS.update({k.format(p="icxo"): v for k, v in _TL_SIGS.items()})
+ORACLE_SIGS["icxo_divergence_scan"] = (C.c_int, [_u32, _vp, _u32, _vp, _u32, _vp, _vp, _vp])
+ORACLE_SIGS["icxo_fork_age"] = (C.c_int, [_u32, _vp, _vp, C.c_uint16, C.POINTER(_u32), C.POINTER(C.c_int)])
+
+
+class CpuTimeline:
+    """EntityTimestreamMap driven through `<prefix>_tl_*` (reference containers or the oracle)."""
+
+    def __init__(self, lib, prefix):
+        self.lib, self.p = lib, prefix
+        self.h = getattr(lib, prefix + "_tl_create")()
+
+    def close(self):
+        getattr(self.lib, self.p + "_tl_destroy")(self.h)
+
+    def breakpoint(self, on):
+        getattr(self.lib, self.p + "_tl_breakpoint")(self.h, 1 if on else 0)
+
+    def record(self, s, coherency, at_breakpoint=False, link_inc=True):
+        getattr(self.lib, self.p + "_tl_record")(self.h, s.n, abi.ptr(s.ids), abi.ptr(s.T), abi.ptr(s.P), coherency,
+                                                 1 if at_breakpoint else 0, 1 if link_inc else 0)
+
+    def replay(self, s, now, mode=0):
+        """Returns (scene after replay, entities overwritten)."""
+        out = s.copy()
+        n = getattr(self.lib, self.p + "_tl_replay")(self.h, out.n, abi.ptr(out.ids), abi.ptr(out.T), abi.ptr(out.P),
+                                                     abi.ptr(out.tstate), now, mode)
+        return out, n
+
+
+def oracle_scan(live, rec, stride=0):
+    nw = (live.n + stride - 1) // stride if stride else 1
+    flags, cnt, score = np.zeros(nw, np.uint8), np.zeros(nw, np.uint32), np.zeros(nw, np.float64)
+    oracle().icxo_divergence_scan(live.n, abi.ptr(live.T), rec.n, abi.ptr(rec.T), stride, abi.ptr(flags), abi.ptr(cnt), abi.ptr(score))
+    return flags, cnt, score
+
+
+def oracle_fork_age(s, coherency):
+    out = s.copy()
+    n, need = C.c_uint32(0), C.c_int(0)
+    oracle().icxo_fork_age(out.n, abi.ptr(out.tstate), abi.ptr(out.tcoh), coherency, C.byref(n), C.byref(need))
+    return out, n.value, bool(need.value)
