@@ -126,6 +126,67 @@ def cpu_reference(scene_name, n_sample, ticks, threads, seed_offset=0):
     return sum(done) / sec, sec, kind
 
 
+def worldline_batch_bench(n_worldlines, per, ticks, rank, world_size, local_rank, barrier):
+    """BASELINE.json configs[3]: independent world-line candidates x `per` bodies, sharded round-robin over
+    the ranks (strong scaling, no data-path collective).  Per tick and rank: replay (parallel mode:
+    consume) + physics tick + record + divergence scan against the shared base history; then ONE
+    gather of {flag, incongruent, score} per world-line (NCCL over NVLink when world_size > 1)."""
+    import torch
+    import torch.distributed as dist
+    from intercession_b200 import abi, scenes, shard, world as icxworld
+    mine = shard.worldlines_of_rank(n_worldlines, rank, world_size)
+    full_local = scenes.worldline_batch(len(mine), per, seed=20261106, perturb=False)
+    for k, wl in enumerate(mine):                 # candidate w perturbs body (w mod per), seed + 1 + w  (same as scenes.worldline_batch)
+        r = np.random.default_rng(20261106 + 1 + int(wl))
+        full_local.P["velocity"][k * per + (int(wl) % per)] += r.uniform(-2, 2, 3).astype(np.float32)
+    base = full_local.base
+    hist_depth = ticks + 2
+    wb = icxworld.World(base.n, host_timeslice=abi.NULL_TIMESLICE, device=local_rank)
+    tl_base = icxworld.Timeline(hist_depth, per, device=local_rank)
+    wb.upload(base)
+    for t in range(ticks):                        # the base history every candidate is compared with (replicated, read-only)
+        wb.step(DT)
+        wb.record(tl_base, t + 1)
+    wb.close()
+    wc = icxworld.World(full_local.n, worldline_stride=per, host_timeslice=abi.NULL_TIMESLICE, device=local_rank)
+    tl_new = icxworld.Timeline(2, full_local.n, device=local_rank)
+    wc.upload(full_local)
+    dev = torch.device("cuda", local_rank) if world_size > 1 else None
+    z = np.zeros(len(mine))
+    shard.gather_results(z, z, z, n_worldlines, rank, world_size, device=dev)      # warm the communicator up (untimed)
+    barrier()
+    t0 = time.perf_counter()
+    dev_ms = 0.0
+    flags = cnt = score = None
+    any_flag = np.zeros(len(mine), np.uint8)
+    for t in range(ticks):
+        wc.replay(tl_new, t, mode=abi.REPLAY_PARALLEL)
+        wc.step(DT)
+        dev_ms += wc.last_step_ms()
+        wc.record(tl_new, t + 1)
+        flags, cnt, score = wc.divergence_scan(tl_base, t + 1, len(mine))
+        any_flag |= flags
+    gflags, gcnt, gscore = shard.gather_results(any_flag, cnt, score, n_worldlines, rank, world_size, device=dev)
+    barrier()
+    sec = time.perf_counter() - t0
+    st = wc.stats()
+    wc.close(); tl_new.close(); tl_base.close()
+    sec_t = torch.tensor([sec], dtype=torch.float64, device="cuda")
+    if world_size > 1:
+        dist.all_reduce(sec_t, op=dist.ReduceOp.MAX)
+    sec = float(sec_t.item())
+    bodies = n_worldlines * per
+    return {"workload": f"config4: {n_worldlines} world-line candidates x {per} bodies, {ticks} ticks of replay + tick + record + divergence scan, "
+                        f"sharded round-robin over {world_size} GPU(s), base history replicated",
+            "scaling": "strong", "n_gpus": world_size, "ticks": ticks, "seconds": round(sec, 4),
+            "worldline_ticks_per_s": n_worldlines * ticks / sec, "collider_steps_per_s": bodies * ticks / sec,
+            "physics_tick_ms_rank0": round(dev_ms / ticks, 4), "dirty_bodies_rank0": st.n_dirty, "contacts_rank0": st.n_contacts,
+            "divergent_worldlines": int(gflags.sum()), "most_congruent": shard.most_congruent(gflags, gscore),
+            "gather": {"collective": "all_gather_into_tensor (NCCL)" if world_size > 1 else "none (1 rank)",
+                       "bytes_per_rank": 24 * ((n_worldlines + world_size - 1) // world_size)},
+            "algorithmic_bytes_per_body_tick": {"record": 200, "scan": 26}}
+
+
 def run_reference_arm(a, rank, world_size):
     if rank != 0:
         return
@@ -160,6 +221,9 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--worldlines", type=int, default=4096, help="config-4 world-line candidates (0 = skip that section)")
+    ap.add_argument("--worldline-bodies", type=int, default=1024)
+    ap.add_argument("--worldline-ticks", type=int, default=8)
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3) if a.impl == "ours" else a.warmup
 
@@ -252,6 +316,10 @@ def main():
     d2h = T.nbytes + P.nbytes + n_contacts * 48
     w.close()
 
+    wlb = None
+    if a.worldlines > 0:
+        wlb = worldline_batch_bench(a.worldlines, a.worldline_bodies, a.worldline_ticks, rank, world_size, local_rank, barrier)
+
     cpu = None
     if rank == 0 and not a.no_cpu:
         cores = os.cpu_count() or 1
@@ -277,6 +345,7 @@ def main():
                 "clocks": clk.summary(), "roofline": roofline,
                 "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
                 "gpu_launches": int(launches1 - launches0),
+                "worldline_batch": wlb,
                 "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if world_size > 1:
