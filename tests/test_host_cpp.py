@@ -1,0 +1,52 @@
+"""The host-side C++ mirror of the reference's operator interface (intercession_b200/host/*.hpp):
+compiles as plain C++17 against the C ABI, fails loudly without a GPU, and -- on the GPU box --
+reproduces the case-study golden fixture through submit / run_relays / reset_relays."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SRC = os.path.join(ROOT, "tests", "host", "test_host_dynamo.cpp")
+EXE = os.path.join(ROOT, "build", "test_host_dynamo")
+
+
+@pytest.fixture(scope="module")
+def exe(built):
+    libdir = os.path.join(ROOT, "intercession_b200")
+    os.makedirs(os.path.dirname(EXE), exist_ok=True)
+    subprocess.run(["g++", "-std=c++17", "-O1", "-Wall", "-Wextra", "-Werror", SRC, "-o", EXE, "-L", libdir, "-licx",
+                    f"-Wl,-rpath,{libdir}"], check=True)
+    return EXE
+
+
+def test_host_mirror_compiles_and_refuses_without_gpu(exe):
+    from intercession_b200 import abi
+    if abi.load().icx_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    r = subprocess.run([exe, "3"], capture_output=True, text=True)
+    assert r.returncode == 2 and "no CPU fallback" in r.stdout
+
+
+@pytest.mark.gpu
+def test_host_mirror_reproduces_case_study(exe):
+    r = subprocess.run([exe, "100"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    g = np.load(os.path.join(ROOT, "tests", "golden", "verbatim_case_study.npz"))
+    seen = 0
+    for line in r.stdout.splitlines():
+        w = line.split()
+        if w[0] == "tick":
+            t = int(w[1])
+            eT, eP = g[f"push1_t{t}_T"], g[f"push1_t{t}_P"]
+            assert np.abs(np.array(w[3:6], np.float32) - eT["origin"][2]).max() < 1e-4, line
+            assert np.abs(np.array(w[7:10], np.float32) - eT["origin"][3]).max() < 1e-4, line
+            assert np.abs(np.array(w[11:14], np.float32) - eP["velocity"][3]).max() < 1e-4, line
+            seen += 1
+        elif w[0] == "callbacks":
+            assert int(w[1]) > 10 and int(w[3]) == 0          # the legs' ray collider asks for on_collision; nobody is forked
+            assert abs(float(w[6])) > 0.9                     # ground normal is +-y
+            assert int(w[-1]) == 1
+            seen += 1
+    assert seen == 4
