@@ -1,6 +1,7 @@
+"""Device-side timeline of the ordered resolve (icx_debug_trace) on the 1 M scene: prints per-round times."""
 import sys, os, ctypes
 import numpy as np
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))  # repo root
 from intercession_b200 import scenes, world
 s = scenes.config3(int(sys.argv[1]) if len(sys.argv) > 1 else 1048576)
 w = world.World(s.n); w.upload(s); w.step(1/45, 4); w.trace(True)
