@@ -283,8 +283,14 @@ def main():
         per_kernel[k] = {"ms": round(kms, 4), "share": round(v / max(sum(phases.values()), 1e-9), 3),
                          "alg_GBps": round(kernel_bytes[k] / max(kms * 1e-3, 1e-12) / 1e9, 1)}
     dom = max(phases, key=phases.get)
+    traffic, traffic_src = None, None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp) and a.workload == "config3" and a.bodies == 1048576:
+        tj = json.load(open(tp))
+        traffic, traffic_src = tj["tick_dram_bytes"], tj["source"]
     roofline = {"bound": "hbm", "kernel": "tick (all kernels; dominant phase: %s)" % dom, "achieved": round(achieved, 2),
-                "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": None,
+                "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": traffic,
+                "traffic_source": traffic_src,
                 "algorithmic_bytes_per_tick": alg_bytes, "phases": per_kernel}
 
     # ---- e2e: host AoS in / out through the C ABI every step ----
