@@ -53,7 +53,7 @@ int allocate(IcxWorld* w)
     CK(alloc(w, W.scan_partial, 4096 + 8));
     CK(alloc(w, W.s_lo, np)); CK(alloc(w, W.s_hi, np));
     CK(alloc(w, W.large_list, W.max_large));
-    CK(alloc(w, W.pairs, W.max_pairs)); CK(alloc(w, W.tight, W.max_pairs)); CK(alloc(w, W.near, W.max_pairs)); CK(alloc(w, W.static_pairs, W.max_static));
+    CK(alloc(w, W.pairs, W.max_pairs)); CK(alloc(w, W.tight, W.max_pairs)); CK(alloc(w, W.near, W.max_pairs)); CK(alloc(w, W.push, ne)); CK(alloc(w, W.static_pairs, W.max_static));
     CK(alloc(w, W.dirty_slot, ne)); CK(alloc(w, W.dirty_list, ne));
     CK(alloc(w, W.nbr, 2 * ne * (size_t)W.max_neighbors)); CK(alloc(w, W.nbr_count, 2 * ne));
     CK(alloc(w, W.head[0], ne)); CK(alloc(w, W.head[1], ne));

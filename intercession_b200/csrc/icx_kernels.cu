@@ -34,6 +34,7 @@ __global__ void __launch_bounds__(256) k_integrate_prep(DeviceWorld W, double de
     W.out.ts[e] = W.in.ts[e];
     W.pos0[e] = r.pos;
     W.dirty_slot[e] = ICX_NONE;
+    W.push[e] = 0.0f;
 
     // ---- per-collider derivation (ColliderSynchro::update + what every later pair test needs) ----
     const uint32_t fp = W.first_packet[e];

@@ -116,6 +116,51 @@ __device__ __forceinline__ bool sat_may_hit(const float4* __restrict__ dA, const
     }
     return true;
 }
+// Same filter, but it also measures: returns true ("may hit") with `value` = an upper bound of the
+// penetration depth the exact procedure can report (how far static resolution may push the two
+// bodies), or false with `value` = a lower bound of the gap between the shapes (how far a body
+// would have to be pushed before the exact procedure could report a hit).  A gap above `far`
+// returns at once.  Used only to PREDICT which bodies the ordered replay will touch.
+__device__ __forceinline__ bool sat_measure(const float4* __restrict__ dA, const float4* __restrict__ dB, V3 posA, V3 posB, int tA, int tB,
+                                            float far, float& value)
+{
+    const float4 a0 = dA[0], a1 = dA[1], a2 = dA[2], a3 = dA[3], a4 = dA[4], a5 = dA[5];
+    const float4 b0 = dB[0], b1 = dB[1], b2 = dB[2], b3 = dB[3], b4 = dB[4], b5 = dB[5];
+    const V3 A0 = v3(a0), A1 = v3(a1), A2 = v3(a2), B0 = v3(b0), B1 = v3(b1), B2 = v3(b2);
+    const V3 cA = v3(a0.w, a1.w, a2.w) + posA, cB = v3(b0.w, b1.w, b2.w) + posB;
+    const V3 d = cA - cB;
+    const float cmag = fabsf(cA.x) + fabsf(cA.y) + fabsf(cA.z) + fabsf(cB.x) + fabsf(cB.y) + fabsf(cB.z);
+    const float sphA = tA == ICX_COLLIDER_SPHERE ? 0.5f * sqrtf(dot(A0, A0)) : -1.0f;
+    const float sphB = tB == ICX_COLLIDER_SPHERE ? 0.5f * sqrtf(dot(B0, B0)) : -1.0f;
+    V3 n[6];
+    n[0] = v3(a3.x, a4.x, a5.x); n[1] = v3(a3.y, a4.y, a5.y); n[2] = v3(a3.z, a4.z, a5.z);
+    n[3] = v3(b3.x, b4.x, b5.x); n[4] = v3(b3.y, b4.y, b5.y); n[5] = v3(b3.z, b4.z, b5.z);
+    float minpen = INFINITY, maxsep = 0.0f; bool separated = false;
+#pragma unroll
+    for (int a = 0; a < 15; a++) {
+        V3 L; float rel = 1.0e-4f;
+        if (a < 6) L = n[a];
+        else {
+            const V3 x = n[(a - 6) / 3], y = n[3 + (a - 6) % 3];
+            L = cross(x, y);
+            if (dot(L, L) < 1.0e-4f * dot(x, x) * dot(y, y)) continue;
+            rel = 1.0e-3f;
+        }
+        const float l2 = dot(L, L), len = sqrtf(l2), l1 = fabsf(L.x) + fabsf(L.y) + fabsf(L.z);
+        const float rA = sphA >= 0.0f ? sphA * len : box_radius(A0, A1, A2, L);
+        const float rB = sphB >= 0.0f ? sphB * len : box_radius(B0, B1, B2, L);
+        const float s = rA + rB, dist = fabsf(dot(d, L));
+        const float tol = rel * (s + dist) + 4.0e-6f * cmag * l1;
+        if (dist > s + tol) {
+            separated = true;
+            maxsep = fmaxf(maxsep, (dist - s - tol) / len);
+            if (maxsep > far) { value = maxsep; return false; }
+        } else minpen = fminf(minpen, (s - dist + tol) / len);
+    }
+    value = separated ? maxsep : (minpen < INFINITY ? minpen : 0.0f);
+    return !separated;
+}
+
 __device__ __forceinline__ bool is_sat_pair(int tA, int tB) {
     return (tA == ICX_COLLIDER_BOX && (tB == ICX_COLLIDER_BOX || tB == ICX_COLLIDER_SPHERE)) || (tA == ICX_COLLIDER_SPHERE && tB == ICX_COLLIDER_BOX);
 }
@@ -394,26 +439,26 @@ __global__ void __launch_bounds__(128) k_narrow(DeviceWorld W)
     const uint32_t pa = pr.x, pb = pr.y & ICX_NB_INDEX_MASK;
     const uint32_t ea = W.pk_entity[pa], eb = W.pk_entity[pb];
     const int tA = __float_as_uint(W.pk_lpos[pa].w) & PF_TYPE_MASK, tB = __float_as_uint(W.pk_lpos[pb].w) & PF_TYPE_MASK;
+    float depth = 0.0f;
     if (is_sat_pair(tA, tB)) {
-        const V3 oa = v3(W.out.pos[ea]), ob = v3(W.out.pos[eb]);
-        if (!sat_may_hit(W.pk_d + (size_t)pa * 6, W.pk_d + (size_t)pb * 6, oa, ob, tA, tB, 0.25f * W.margin)) continue;
-        if (!sat_may_hit(W.pk_d + (size_t)pa * 6, W.pk_d + (size_t)pb * 6, oa, ob, tA, tB, 0.0f)) {
-            // close but apart: if one of the two turns out to be hit (and pushed), the other is replayed in order too
-            if (!(pr.y & ICX_PAIR_STATIC)) { const uint32_t q = atomicAdd(&W.counters[CTR_NEAR], 1u); if (q < W.max_pairs) W.near[q] = make_uint2(ea, eb); }
-            continue;
-        }
+        float value;
+        if (!sat_measure(W.pk_d + (size_t)pa * 6, W.pk_d + (size_t)pb * 6, v3(W.out.pos[ea]), v3(W.out.pos[eb]), tA, tB, 0.0f, value)) continue;
+        depth = value;
     } else {
         V3 baseA, baseB; Shape A, B; Hit h;
         float mpA = 1.0f, mpB = 1.0f;           // Collider::reset value; a ray that hits is dirty and replayed in order
         if (!pair_intersect(W, pa, pb, ea, eb, tA, tB, v3(W.out.pos[ea]), v3(W.out.pos[eb]), A, B, baseA, baseB, mpA, mpB, h)) continue;
+        depth = (tA == ICX_COLLIDER_RAY || tB == ICX_COLLIDER_RAY) ? 0.0f : h.depth;      // springs do not push
     }
     if (pr.y & ICX_PAIR_STATIC) {
         const uint32_t k = atomicAdd(&W.counters[CTR_STATIC], 1u);
         if (k < W.max_static) W.static_pairs[k] = make_uint2(pa, pb); else atomicOr(W.flags, RF_PAIR_OVERFLOW);
         continue;
     }
-    if (!(__float_as_uint(W.prm1[ea].w) & EF_IMMUTABLE)) mark_dirty(W, ea);
-    if (!(__float_as_uint(W.prm1[eb].w) & EF_IMMUTABLE)) mark_dirty(W, eb);
+    // predicted push of each body = sum of the depths of its contacts; touching bodies pass pushes on
+    const bool ma = !(__float_as_uint(W.prm1[ea].w) & EF_IMMUTABLE), mb = !(__float_as_uint(W.prm1[eb].w) & EF_IMMUTABLE);
+    if (ma) { mark_dirty(W, ea); atomicAdd(&W.push[ea], depth); }
+    if (mb) { mark_dirty(W, eb); atomicAdd(&W.push[eb], depth); }
     }
 }
 
@@ -636,17 +681,46 @@ __global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(DeviceWorld W, double d
     volatile uint32_t* ctr = W.counters;
     uint32_t attempts = 0, rounds = 0;
     if (tid == 0) trace_mark(W, tn, 0u);
-    {   // one ring around the speculatively hit bodies: neighbours they may be pushed into
-        const uint32_t n_hit = ctr[CTR_DIRTY], n_near = min(ctr[CTR_NEAR], W.max_pairs);
-        grid.sync();
-        for (uint32_t i = tid; i < n_near; i += nth) {
-            const uint2 pr = W.near[i];
-            const bool da = W.dirty_slot[pr.x] < n_hit, db = W.dirty_slot[pr.y] < n_hit;
-            if (da != db) {
-                const uint32_t other = da ? pr.y : pr.x;
-                if (!(__float_as_uint(W.prm1[other].w) & EF_IMMUTABLE)) mark_dirty(W, other);
+    {   // Predict which clean bodies the replay will reach: a body that static resolution may push by up to
+        // push[a] (sum of the depths of its speculative contacts) reaches the candidates whose gap is smaller;
+        // those are replayed in order too and inherit the remainder of the push.  One warp per dirty body walks
+        // its candidate list, at most three generations.  Only a prediction: a body it misses triggers the
+        // restart further down.
+        uint32_t done = 0;
+        for (int sweep = 0; sweep < 3; sweep++) {
+            const uint32_t n_dirty = ctr[CTR_DIRTY];
+            if (n_dirty == done) break;                         // uniform: read after a grid barrier
+            for (uint32_t sl = done + (tid >> 5); sl < n_dirty; sl += (nth >> 5)) build_lists_warp(W, sl);
+            grid.sync();
+            for (uint32_t sl = done + (tid >> 5); sl < n_dirty; sl += (nth >> 5)) {
+                const uint32_t e = W.dirty_list[sl];
+                const float pa = *(volatile float*)&W.push[e];
+                if (!(pa > 0.0f)) continue;
+                const uint32_t p0 = W.first_packet[e] & 0x3FFFFFFFu;
+                const uint32_t n0 = W.nbr_count[sl * 2u], n1 = W.nbr_count[sl * 2u + 1u];
+                for (uint32_t i = tid & 31u; i < n0 + n1; i += 32u) {
+                    const uint32_t k = i < n0 ? 0u : 1u;
+                    const uint32_t entry = W.nbr[(size_t)(sl * 2u + k) * W.max_neighbors + (k ? i - n0 : i)];
+                    if (entry & ICX_NB_IMMUTABLE) continue;
+                    const uint32_t o = entry & ICX_NB_INDEX_MASK, eo = W.pk_entity[o];
+                    if (W.dirty_slot[eo] != ICX_NONE) continue;
+                    const uint32_t p = p0 + k;
+                    const int tP = __float_as_uint(W.pk_lpos[p].w) & PF_TYPE_MASK, tO = __float_as_uint(W.pk_lpos[o].w) & PF_TYPE_MASK;
+                    if (!is_sat_pair(tP, tO)) continue;
+                    float value;
+                    const float reach = 1.5f * pa + 0.02f * W.margin;
+                    const bool touching = sat_measure(W.pk_d + (size_t)p * 6, W.pk_d + (size_t)o * 6, v3(W.out.pos[e]), v3(W.out.pos[eo]), tP, tO, reach, value);
+                    if (touching || value < reach) {
+                        mark_dirty(W, eo);
+                        const float inherit = touching ? pa : pa - value;
+                        if (inherit > 0.0f) atomicMax((int*)&W.push[eo], __float_as_int(inherit));
+                    }
+                }
             }
+            done = n_dirty;
+            grid.sync();
         }
+        if (tid == 0) ctr[CTR_LISTED] = done;
         grid.sync();
     }
     for (;;) {

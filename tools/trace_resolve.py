@@ -4,7 +4,7 @@ import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))  # repo root
 from intercession_b200 import scenes, world
 s = scenes.config3(int(sys.argv[1]) if len(sys.argv) > 1 else 1048576)
-w = world.World(s.n); w.upload(s); w.step(1/45, 4); w.trace(True)
+w = world.World(s.n); w.upload(s); w.step(1/45, int(sys.argv[2]) if len(sys.argv) > 2 else 4); w.trace(True)
 for k in range(2):
     w.step(1/45); st = w.stats()
     print("tick", k, "dirty", st.n_dirty, "rounds", st.n_rounds, "attempts", st.n_attempts, "contacts", st.n_contacts, "ms", w.last_step_ms())
