@@ -136,7 +136,7 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* t
     if (lane == 31) warp_sums[wid] = x;
     __syncthreads();
     if (wid == 0) {
-        uint32_t s = warp_sums[lane];
+        uint32_t s = lane < (blockDim.x >> 5) ? warp_sums[lane] : 0u;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xFFFFFFFFu, s, o); if (lane >= (uint32_t)o) s += y; }
         warp_sums[lane] = s;
@@ -206,43 +206,28 @@ __global__ void __launch_bounds__(256) k_scatter(DeviceWorld W)
 }
 
 // ---------------------------------------------------------------------------------------
-// K4: uniform-grid pair generator.  One thread per bucket-sorted packet (then one per large
-// collider): walk the 27 surrounding cells as 9-18 contiguous ranges, keep partners whose inflated
-// bounds overlap, emit each unordered pair once (from its lower sorted position).  Pairs are
-// appended warp-aggregated to a shared-memory stage and flushed with one global atomic per block,
-// so the list is written in coalesced runs.  Entry = (lower packet, higher packet | flags).
+// K4: uniform-grid pair generator.  Phase A (one thread per bucket-sorted packet) resolves the
+// forward half of the 27-cell neighbourhood into <= 10 contiguous ranges of the sorted array (all
+// table look-ups issued back to back) and stages them, with the packet's bound, in shared memory.
+// Phase B: every warp walks the candidates of its own 32 packets with 8 lanes per packet, four
+// packets at a time, so a packet's ~40 candidates cost ~5 warp iterations instead of 40 divergent
+// ones; partners whose inflated bounds overlap are kept and each unordered pair is emitted once
+// (from the packet whose cell comes first in (z, y, x) order, ties by sorted position).  Pairs are
+// staged per warp (ballot / popc, no atomics) and copied out in coalesced runs with one global
+// atomic per flush.  Entry = (lower packet, higher packet | flags).
 // ---------------------------------------------------------------------------------------
 #define PAIRS_TPB 256
-#define STAGE_TIGHT 1024
-#define STAGE_LOOSE 2048
+#define PAIRS_MAXR 10
+#define CAND_CAP 96                                 // 31 left over + 2 per lane per iteration
+#define WSTAGE 64                                   // per-warp stage capacity; flushed when more than WSTAGE - 32 entries are staged
 
-struct PairStage { uint2 tight[STAGE_TIGHT]; uint2 loose[STAGE_LOOSE]; uint32_t n_tight, n_loose, base_all, base_tight; };
-
-__device__ __forceinline__ void put_global(const DeviceWorld& W, uint2 entry, bool tight)
-{
-    const uint32_t g = atomicAdd(&W.counters[CTR_CANDIDATES], 1u);
-    if (g < W.max_pairs) W.pairs[g] = entry; else atomicOr(W.flags, RF_PAIR_OVERFLOW);
-    if (tight) {
-        const uint32_t q = atomicAdd(&W.counters[CTR_TIGHT], 1u);
-        if (q < W.max_pairs) W.tight[q] = entry; else atomicOr(W.flags, RF_PAIR_OVERFLOW);
-    }
-}
-
-// warp-aggregated append to the block's shared-memory stage (tight and loose pairs separately)
-__device__ __forceinline__ void emit_pair(const DeviceWorld& W, PairStage& S, uint32_t a, uint32_t b, bool tight, uint32_t flags)
-{
-    const uint2 entry = make_uint2(min(a, b), max(a, b) | flags | (tight ? ICX_PAIR_TIGHT : 0u));
-    const uint32_t m = __activemask(), lane = threadIdx.x & 31u;
-    const uint32_t mt = __ballot_sync(m, tight);
-    const uint32_t grp = tight ? mt : (m & ~mt);
-    const int leader = __ffs(grp) - 1;
-    uint32_t base = 0;
-    if ((int)lane == leader) base = atomicAdd(tight ? &S.n_tight : &S.n_loose, (uint32_t)__popc(grp));
-    base = __shfl_sync(grp, base, leader);
-    const uint32_t idx = base + __popc(grp & ((1u << lane) - 1u));
-    if (tight) { if (idx < STAGE_TIGHT) S.tight[idx] = entry; else put_global(W, entry, true); }
-    else { if (idx < STAGE_LOOSE) S.loose[idx] = entry; else put_global(W, entry, false); }
-}
+struct PairStage {
+    float4 lo[PAIRS_TPB], hi[PAIRS_TPB];            // own bounds (+ tag / entity in .w)
+    uint32_t rbeg[PAIRS_TPB][PAIRS_MAXR];           // range start in the sorted array
+    uint32_t rcum[PAIRS_TPB][PAIRS_MAXR];           // candidates of this packet up to the end of the range (inclusive scan)
+    uint2 tight[PAIRS_TPB / 32][WSTAGE], loose[PAIRS_TPB / 32][WSTAGE];
+    uint2 cand[PAIRS_TPB / 32][CAND_CAP];           // per warp: (packet slot in the block, sorted position of the partner) whose bounds overlap
+};
 
 // un-inflated bounds overlap (with 10 % of the margin kept as slack against rounding): only then can
 // the narrowphase report a hit on the post-integration state (DESIGN.md "Broadphase bound")
@@ -256,16 +241,56 @@ __device__ __forceinline__ bool tight_overlap(float4 alo, float4 ahi, float4 blo
            tight_le(alo.z, bhi.z, m2) && tight_le(blo.z, ahi.z, m2);
 }
 
-__global__ void __launch_bounds__(PAIRS_TPB) k_pairs(DeviceWorld W)
+// Per-warp pair stage: every lane of a converged warp calls with its verdict; entries are appended
+// by ballot / popc (no atomics) and the stage is copied out in one coalesced run with ONE global
+// atomic per list when it could overflow on the next call.
+struct WarpStage { uint32_t n_tight, n_loose; };     // warp-uniform registers
+
+__device__ __forceinline__ void warp_flush(const DeviceWorld& W, uint2* stage, uint32_t& n, uint32_t ctr, uint2* dst, uint2* dst2, uint32_t ctr2)
+{
+    const uint32_t FULL = 0xFFFFFFFFu, lane = threadIdx.x & 31u;
+    if (n == 0) return;
+    uint32_t base = 0, base2 = 0;
+    if (lane == 0) { base = atomicAdd(&W.counters[ctr], n); if (dst2) base2 = atomicAdd(&W.counters[ctr2], n); }
+    base = __shfl_sync(FULL, base, 0); base2 = __shfl_sync(FULL, base2, 0);
+    __syncwarp();
+    for (uint32_t i = lane; i < n; i += 32u) {
+        const uint2 entry = stage[i];
+        if (base + i < W.max_pairs) dst[base + i] = entry; else atomicOr(W.flags, RF_PAIR_OVERFLOW);
+        if (dst2) { if (base2 + i < W.max_pairs) dst2[base2 + i] = entry; else atomicOr(W.flags, RF_PAIR_OVERFLOW); }
+    }
+    __syncwarp();
+    n = 0;
+}
+
+__device__ __forceinline__ void warp_emit(const DeviceWorld& W, PairStage& S, WarpStage& ws, bool emit, bool tight, uint2 entry)
+{
+    const uint32_t FULL = 0xFFFFFFFFu, lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    const uint32_t mt = __ballot_sync(FULL, emit && tight), ml = __ballot_sync(FULL, emit && !tight);
+    const uint32_t below = (1u << lane) - 1u;
+    if (emit && tight) S.tight[wid][ws.n_tight + __popc(mt & below)] = entry;
+    if (emit && !tight) S.loose[wid][ws.n_loose + __popc(ml & below)] = entry;
+    ws.n_tight += __popc(mt); ws.n_loose += __popc(ml);
+    // tight pairs go to both lists (all candidates; narrowphase input)
+    if (ws.n_tight > WSTAGE - 32) warp_flush(W, S.tight[wid], ws.n_tight, CTR_CANDIDATES, W.pairs, W.tight, CTR_TIGHT);
+    if (ws.n_loose > WSTAGE - 32) warp_flush(W, S.loose[wid], ws.n_loose, CTR_CANDIDATES, W.pairs, nullptr, 0);
+}
+
+__global__ void __launch_bounds__(PAIRS_TPB, 4) k_pairs(DeviceWorld W)
 {
     __shared__ PairStage S;
-    if (threadIdx.x == 0) { S.n_tight = 0; S.n_loose = 0; }
-    __syncthreads();
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t tid = threadIdx.x;
+    const uint32_t t = blockIdx.x * blockDim.x + tid;
     const uint32_t n_grid = W.cell_count[W.n_buckets];
     const uint32_t n_large = min(W.counters[CTR_LARGE], W.max_large);
-    if (t < n_grid + n_large) {
-        uint32_t p, e; int type; bool immut; float4 lo, hi;
+    WarpStage ws; ws.n_tight = 0; ws.n_loose = 0;
+
+    // ---- phase A: own bound and the ranges of the forward half neighbourhood ----
+    uint32_t p = 0, e = 0; int type = 0; bool immut = false;
+    float4 lo = make_float4(0, 0, 0, 0), hi = lo;
+    uint32_t count = 0;
+    const bool have = t < n_grid + n_large;
+    if (have) {
         if (t < n_grid) {
             lo = W.s_lo[t]; hi = W.s_hi[t];
             const uint32_t tag = __float_as_uint(lo.w);
@@ -276,69 +301,141 @@ __global__ void __launch_bounds__(PAIRS_TPB) k_pairs(DeviceWorld W)
             lo = W.pk_lo[p]; hi = W.pk_hi[p];
             e = W.pk_entity[p]; type = __float_as_uint(W.pk_lpos[p].w) & PF_TYPE_MASK; immut = true;
         }
-        const uint32_t wl = W.worldline_stride ? e / W.worldline_stride : 0u;
-        if (t < n_grid) {
-            // forward half of the 27-cell neighbourhood: rows (dz, dy) >= (0, 0); a pair is emitted by
-            // the packet whose cell comes first in (z, y, x) order, ties by sorted position
-            const int cx = cell_coord(lo.x, hi.x, W.inv_cell), cy = cell_coord(lo.y, hi.y, W.inv_cell), cz = cell_coord(lo.z, hi.z, W.inv_cell);
-            const int xb0 = (cx - 1) >> ICX_XB, xb1 = (cx + 1) >> ICX_XB;
-            uint32_t seen[10]; int n_seen = 0;
-#pragma unroll 1
-            for (int r = 4; r < 9; r++) {
-                const int dy = r % 3 - 1, dz = r / 3 - 1;
-                for (int xb = xb0; xb <= xb1; xb++) {
+    }
+    const uint32_t wl = W.worldline_stride ? e / W.worldline_stride : 0u;
+    if (have && t < n_grid) {
+        // rows (dz, dy) >= (0, 0) of the 27-cell neighbourhood; the 3 x-neighbours of a row are one or two
+        // contiguous ranges of the sorted array (icx_world.cuh, ICX_XB).  All table look-ups are issued
+        // before any is used (independent loads), duplicates (hash collisions between rows) are dropped.
+        const int cx = cell_coord(lo.x, hi.x, W.inv_cell), cy = cell_coord(lo.y, hi.y, W.inv_cell), cz = cell_coord(lo.z, hi.z, W.inv_cell);
+        // A partner's bound overlaps mine only if its centre lies within my bound widened by its half extent
+        // (<= cell / 2): cells outside that box are skipped (slack: 0.1 % of a cell + rounding of the coordinates).
+        const float half = 0.5005f * W.cell_size;
+        const float sx = half + 4.0e-6f * fmaxf(fabsf(lo.x), fabsf(hi.x)), sy = half + 4.0e-6f * fmaxf(fabsf(lo.y), fabsf(hi.y)),
+                    sz = half + 4.0e-6f * fmaxf(fabsf(lo.z), fabsf(hi.z));
+        const int nx0 = max(cx - 1, (int)floorf((lo.x - sx) * W.inv_cell)), nx1 = min(cx + 1, (int)floorf((hi.x + sx) * W.inv_cell));
+        const int ny0 = max(cy - 1, (int)floorf((lo.y - sy) * W.inv_cell)), ny1 = min(cy + 1, (int)floorf((hi.y + sy) * W.inv_cell));
+        const int nz1 = min(cz + 1, (int)floorf((hi.z + sz) * W.inv_cell));
+        const int xb0 = nx0 >> ICX_XB, xb1 = nx1 >> ICX_XB;
+        uint32_t key[PAIRS_MAXR], beg[PAIRS_MAXR], end[PAIRS_MAXR];
+#pragma unroll
+        for (int r = 0; r < 5; r++) {
+            const int dy = (r + 4) % 3 - 1, dz = (r + 4) / 3 - 1;
+            const bool row_ok = cy + dy >= ny0 && cy + dy <= ny1 && cz + dz <= nz1;
+#pragma unroll
+            for (int part = 0; part < 2; part++) {
+                const int xb = xb0 + part, i = r * 2 + part;
+                key[i] = ICX_NONE; beg[i] = 0; end[i] = 0;
+                if (row_ok && xb <= xb1) {
                     const uint32_t block = row_block(xb, cy + dy, cz + dz, wl, W.n_buckets);
-                    const uint32_t key = block * 2u + (uint32_t)(xb - xb0);
-                    bool dup = false;
-                    for (int q = 0; q < n_seen; q++) dup |= (seen[q] == key);
-                    if (dup) continue;
-                    seen[n_seen++] = key;
-                    const int x_lo = max(cx - 1, xb << ICX_XB), x_hi = min(cx + 1, (xb << ICX_XB) + ICX_XMASK);
-                    const uint32_t beg = W.cell_count[(block << ICX_XB) | (uint32_t)(x_lo & ICX_XMASK)];
-                    const uint32_t end = W.cell_count[((block << ICX_XB) | (uint32_t)(x_hi & ICX_XMASK)) + 1u];
-                    for (uint32_t j = beg; j < end; j++) {
-                        if (j == t) continue;
-                        const float4 blo = W.s_lo[j], bhi = W.s_hi[j];
-                        if (!overlap(lo, hi, blo, bhi)) continue;
-                        const uint32_t btag = __float_as_uint(blo.w), be = __float_as_uint(bhi.w);
-                        if (be == e) continue;                                      // same entity, relay :51
-                        if (W.worldline_stride && be / W.worldline_stride != wl) continue;
-                        if (!can_intersect(type, (btag >> 28) & 3, W.cfg_flags)) continue;
-                        const int bx = cell_coord(blo.x, bhi.x, W.inv_cell), by = cell_coord(blo.y, bhi.y, W.inv_cell), bz = cell_coord(blo.z, bhi.z, W.inv_cell);
-                        const bool mine = bz != cz ? bz > cz : (by != cy ? by > cy : (bx != cx ? bx > cx : j > t));
-                        if (!mine) continue;
-                        const bool bimmut = (btag & 0x40000000u) != 0;
-                        emit_pair(W, S, p, btag & ICX_NB_INDEX_MASK, tight_overlap(lo, hi, blo, bhi, W.margin), (immut && bimmut) ? ICX_PAIR_STATIC : 0u);
-                    }
+                    key[i] = block * 2u + (uint32_t)part;
+                    const int x_lo = max(nx0, xb << ICX_XB), x_hi = min(nx1, (xb << ICX_XB) + ICX_XMASK);
+                    beg[i] = W.cell_count[(block << ICX_XB) | (uint32_t)(x_lo & ICX_XMASK)];
+                    end[i] = W.cell_count[((block << ICX_XB) | (uint32_t)(x_hi & ICX_XMASK)) + 1u];
                 }
             }
         }
-        // large colliders (all immutable): every grid packet tests them; large ones test the later large ones
-        for (uint32_t k = (t < n_grid ? 0u : t - n_grid + 1u); k < n_large; k++) {
-            const uint32_t q = W.large_list[k];
-            const uint32_t qe = W.pk_entity[q];
-            if (qe == e) continue;
-            if (W.worldline_stride && qe / W.worldline_stride != wl) continue;
-            const int qtype = __float_as_uint(W.pk_lpos[q].w) & PF_TYPE_MASK;
-            if (!can_intersect(type, qtype, W.cfg_flags)) continue;
-            const float4 qlo = W.pk_lo[q], qhi = W.pk_hi[q];
-            if (!overlap(lo, hi, qlo, qhi)) continue;
-            emit_pair(W, S, p, q, tight_overlap(lo, hi, qlo, qhi, W.margin), immut ? ICX_PAIR_STATIC : 0u);
+        int n_r = 0;
+#pragma unroll
+        for (int i = 0; i < PAIRS_MAXR; i++) {
+            bool keep = key[i] != ICX_NONE && end[i] > beg[i];
+#pragma unroll
+            for (int q = 0; q < i; q++) keep = keep && key[q] != key[i];
+            if (keep) { count += end[i] - beg[i]; S.rbeg[tid][n_r] = beg[i]; S.rcum[tid][n_r] = count; n_r++; }
         }
     }
-    __syncthreads();
-    const uint32_t nt = min(S.n_tight, (uint32_t)STAGE_TIGHT), nl = min(S.n_loose, (uint32_t)STAGE_LOOSE);
-    if (threadIdx.x == 0) {
-        if (nt + nl) S.base_all = atomicAdd(&W.counters[CTR_CANDIDATES], nt + nl);
-        if (nt) S.base_tight = atomicAdd(&W.counters[CTR_TIGHT], nt);
+    S.lo[tid] = lo; S.hi[tid] = make_float4(hi.x, hi.y, hi.z, __uint_as_float(e));
+    __syncwarp();
+
+    // ---- phase B: 8 lanes per packet, 4 packets of this warp at a time, 2 candidates per lane and iteration ----
+    // Only ~8 % of the candidates overlap; what follows the overlap test (emission rule, tight test,
+    // staging) would run with 1-3 active lanes per iteration, so overlapping candidates are queued per
+    // warp and finished 32 at a time with all lanes busy.
+    const uint32_t FULL = 0xFFFFFFFFu, lane = tid & 31u, sub = lane & 7u, grp = lane >> 3, wid = tid >> 5;
+    const uint32_t wbase = tid & ~31u, tb0 = blockIdx.x * blockDim.x;
+    uint32_t n_cand = 0;                                                                // warp-uniform
+    auto finish = [&](uint32_t first, uint32_t n) {                                     // queue entries [first, first + n), n <= 32
+        bool emit = false, tight = false; uint2 entry = make_uint2(0, 0);
+        if (lane < n) {
+            const uint2 cq = S.cand[wid][first + lane];
+            const uint32_t q = cq.x, j = cq.y, tq = tb0 + q;
+            const float4 alo = S.lo[q], ahi = S.hi[q];
+            const float4 blo = W.s_lo[j], bhi = W.s_hi[j];
+            const uint32_t atag = __float_as_uint(alo.w), ae = __float_as_uint(ahi.w);
+            const uint32_t btag = __float_as_uint(blo.w), be = __float_as_uint(bhi.w);
+            bool ok = be != ae;                                                         // same entity, relay :51
+            if (W.worldline_stride) ok = ok && (be / W.worldline_stride == ae / W.worldline_stride);
+            ok = ok && can_intersect((atag >> 28) & 3, (btag >> 28) & 3, W.cfg_flags);
+            if (ok) {
+                const int ax = cell_coord(alo.x, ahi.x, W.inv_cell), ay = cell_coord(alo.y, ahi.y, W.inv_cell), az = cell_coord(alo.z, ahi.z, W.inv_cell);
+                const int bx = cell_coord(blo.x, bhi.x, W.inv_cell), by = cell_coord(blo.y, bhi.y, W.inv_cell), bz = cell_coord(blo.z, bhi.z, W.inv_cell);
+                emit = bz != az ? bz > az : (by != ay ? by > ay : (bx != ax ? bx > ax : j > tq));
+                const uint32_t a = atag & ICX_NB_INDEX_MASK, b = btag & ICX_NB_INDEX_MASK;
+                tight = tight_overlap(alo, ahi, blo, bhi, W.margin);
+                const bool stat = (atag & 0x40000000u) && (btag & 0x40000000u);
+                entry = make_uint2(min(a, b), max(a, b) | (stat ? ICX_PAIR_STATIC : 0u) | (tight ? ICX_PAIR_TIGHT : 0u));
+            }
+        }
+        warp_emit(W, S, ws, emit, tight, entry);
+        __syncwarp();
+    };
+#pragma unroll 1
+    for (uint32_t round = 0; round < 8u; round++) {
+        const uint32_t ql = round * 4u + grp, q = wbase + ql;                          // packet of this lane group
+        const uint32_t cnt = __shfl_sync(FULL, count, ql);
+        uint32_t mx = max(cnt, __shfl_xor_sync(FULL, cnt, 8)); mx = max(mx, __shfl_xor_sync(FULL, mx, 16));
+        if (mx == 0u) continue;
+        const float4 alo = S.lo[q], ahi = S.hi[q];
+        const uint32_t tq = tb0 + q;
+        int k = 0; uint32_t kbase = 0, kend = cnt ? S.rcum[q][0] : 0u;                  // current range: candidates [kbase, kend)
+        for (uint32_t rb = 0; rb < mx; rb += 16u) {                                     // warp-uniform trip count
+            uint32_t j[2]; bool pass[2];
+#pragma unroll
+            for (int u = 0; u < 2; u++) {
+                const uint32_t r = rb + u * 8u + sub;
+                j[u] = ICX_NONE;
+                if (r < cnt) {
+                    while (r >= kend) { k++; kbase = kend; kend = S.rcum[q][k]; }
+                    j[u] = S.rbeg[q][k] + (r - kbase);
+                    if (j[u] == tq) j[u] = ICX_NONE;
+                }
+            }
+            float4 blo[2], bhi[2];
+#pragma unroll
+            for (int u = 0; u < 2; u++) if (j[u] != ICX_NONE) { blo[u] = W.s_lo[j[u]]; bhi[u] = W.s_hi[j[u]]; }
+#pragma unroll
+            for (int u = 0; u < 2; u++) {
+                pass[u] = j[u] != ICX_NONE && overlap(alo, ahi, blo[u], bhi[u]);
+                const uint32_t m = __ballot_sync(FULL, pass[u]);
+                if (pass[u]) S.cand[wid][n_cand + __popc(m & ((1u << lane) - 1u))] = make_uint2(q, j[u]);
+                n_cand += __popc(m);
+            }
+            __syncwarp();
+            while (n_cand >= 32u) { n_cand -= 32u; finish(n_cand, 32u); }
+        }
     }
-    __syncthreads();
-    for (uint32_t i = threadIdx.x; i < nt + nl; i += blockDim.x) {
-        const uint2 entry = i < nt ? S.tight[i] : S.loose[i - nt];
-        const uint32_t g = S.base_all + i;
-        if (g < W.max_pairs) W.pairs[g] = entry; else atomicOr(W.flags, RF_PAIR_OVERFLOW);
-        if (i < nt) { const uint32_t q = S.base_tight + i; if (q < W.max_pairs) W.tight[q] = entry; else atomicOr(W.flags, RF_PAIR_OVERFLOW); }
+    __syncwarp();
+    if (n_cand) finish(0u, n_cand);
+
+    // ---- large colliders (all immutable): every grid packet tests them; large ones test the later large ones ----
+    for (uint32_t k = 0; k < n_large; k++) {
+        bool emit = false, tight = false; uint2 entry = make_uint2(0, 0);
+        if (have && k >= (t < n_grid ? 0u : t - n_grid + 1u)) {
+            const uint32_t q = W.large_list[k];
+            const uint32_t qe = W.pk_entity[q];
+            const int qtype = __float_as_uint(W.pk_lpos[q].w) & PF_TYPE_MASK;
+            if (qe != e && (!W.worldline_stride || qe / W.worldline_stride == wl) && can_intersect(type, qtype, W.cfg_flags)) {
+                const float4 qlo = W.pk_lo[q], qhi = W.pk_hi[q];
+                if (overlap(lo, hi, qlo, qhi)) {
+                    emit = true; tight = tight_overlap(lo, hi, qlo, qhi, W.margin);
+                    entry = make_uint2(min(p, q), max(p, q) | (immut ? ICX_PAIR_STATIC : 0u) | (tight ? ICX_PAIR_TIGHT : 0u));
+                }
+            }
+        }
+        warp_emit(W, S, ws, emit, tight, entry);
     }
+    warp_flush(W, S.tight[tid >> 5], ws.n_tight, CTR_CANDIDATES, W.pairs, W.tight, CTR_TIGHT);
+    warp_flush(W, S.loose[tid >> 5], ws.n_loose, CTR_CANDIDATES, W.pairs, nullptr, 0);
 }
 
 // ---- launchers ------------------------------------------------------------------------

@@ -25,6 +25,11 @@ namespace cg = cooperative_groups;
 
 namespace icx {
 
+#ifdef ICX_PROFILE_PAIR
+#define PROF_ADD(k, v) do { if ((threadIdx.x & 31u) == 0u) atomicAdd(&W.counters[CTR_PROF + (k)], (uint32_t)(v)); } while (0)
+#else
+#define PROF_ADD(k, v) do { } while (0)
+#endif
 struct Cursor { uint32_t p0, npk, n0, n1; const uint32_t* l0; const uint32_t* l1; };
 
 __device__ __forceinline__ Cursor load_cursor(const DeviceWorld& W, uint32_t slot, uint32_t e)
@@ -301,6 +306,9 @@ __device__ __forceinline__ void store_side(const DeviceWorld& W, uint32_t e, con
 static __device__ __noinline__ void process_pair(const DeviceWorld& W, uint32_t pa, uint32_t pb, uint32_t n_dirty, uint32_t ctr_new)
 {
     const bool writer = (threadIdx.x & 31u) == 0u;
+#ifdef ICX_PROFILE_PAIR
+    const long long tp0 = clock64();
+#endif
     const uint32_t ea = W.pk_entity[pa], eb = W.pk_entity[pb];
     const uint32_t bitsA = __float_as_uint(W.pk_lpos[pa].w), bitsB = __float_as_uint(W.pk_lpos[pb].w);
     const int tA = bitsA & PF_TYPE_MASK, tB = bitsB & PF_TYPE_MASK;
@@ -320,6 +328,9 @@ static __device__ __noinline__ void process_pair(const DeviceWorld& W, uint32_t 
     if (bb) pick = sat_warp(A, B, false);
     else if (sb) pick = sat_warp(A, B, true);
     else if (bs) pick = sat_warp(B, A, true);
+#ifdef ICX_PROFILE_PAIR
+    if (writer) { atomicAdd(&W.counters[CTR_PROF + 5], (uint32_t)((clock64() - tp0) >> 4)); atomicAdd(&W.counters[CTR_PROF + 6], pick.separated ? 0u : 1u); }
+#endif
     if (!writer) return;
     bool hit = false;
     if (bb) {
@@ -579,25 +590,60 @@ static __device__ __noinline__ void restore_body(const DeviceWorld& W, uint32_t 
 // separated by grid barriers.  Cursors are double buffered (head[parity]); each active body has
 // exactly one writer per round.
 
-// advance past leading one-sided entries the filter rejects (own state is final for this round,
-// the partners are never written)
-__device__ __forceinline__ uint32_t skip_rejects(const DeviceWorld& W, const Cursor& c, uint32_t hw, uint32_t n_dirty)
+// Advance a body's cursor past the leading one-sided entries the filter rejects (own state is
+// final until the body's next exact pair, the partners are never written).  Done by a whole WARP
+// (all lanes pass the same arguments, the result is uniform): the
+// upcoming entries of both lists are classified in parallel, one entry per lane -- every filter
+// evaluation is a chain of dependent loads, which a single thread would pay for entry after
+// entry -- and the merged queue order is then replayed over the 32 precomputed verdicts.
+__device__ __forceinline__ uint32_t skip_rejects_warp(const DeviceWorld& W, const Cursor& c, uint32_t hw, uint32_t n_dirty)
 {
+    const uint32_t FULL = 0xFFFFFFFFu, lane = threadIdx.x & 31u;
     for (;;) {
-        uint32_t k, entry;
-        if (!cursor_head(c, hw, k, entry)) return hw;
-        const uint32_t p = c.p0 + k, o = entry & ICX_NB_INDEX_MASK;
-        if (!(entry & ICX_NB_IMMUTABLE) && W.dirty_slot[W.pk_entity[o]] < n_dirty) return hw;     // two-sided
-        if (may_hit(W, min(p, o), max(p, o), 0.0f)) return hw;
-        hw = cursor_advance(hw, k);
+        const uint32_t h0 = hw & 0xFFFFu, h1 = hw >> 16;
+        const uint32_t rem0 = h0 < c.n0 ? c.n0 - h0 : 0u, rem1 = h1 < c.n1 ? c.n1 - h1 : 0u;
+        if (rem0 + rem1 == 0u) return hw;
+        const uint32_t w0 = rem1 == 0u ? 32u : (rem0 == 0u ? 0u : 16u);        // lanes [0, w0) look at list 0, the rest at list 1
+        const uint32_t k = lane < w0 ? 0u : 1u, idx = k ? lane - w0 : lane;
+        const bool valid = idx < (k ? rem1 : rem0);
+        uint32_t entry = 0; bool stop = false;
+        if (valid) {
+            PROF_ADD(3, 1);
+            entry = k ? c.l1[h1 + idx] : c.l0[h0 + idx];
+            const uint32_t p = c.p0 + k, o = entry & ICX_NB_INDEX_MASK;
+            stop = (!(entry & ICX_NB_IMMUTABLE) && W.dirty_slot[W.pk_entity[o]] < n_dirty) || may_hit(W, min(p, o), max(p, o), 0.0f);
+        }
+        const uint32_t stops = __ballot_sync(FULL, stop);
+        // replay the merged order (cursor_head) over the chunk
+        uint32_t a0 = 0, a1 = 0; bool boundary = false;
+        for (;;) {
+            const bool has0 = a0 < rem0, has1 = a1 < rem1;
+            if (!has0 && !has1) break;
+            if ((has0 && a0 >= w0) || (has1 && a1 >= 32u - w0)) { boundary = true; break; }
+            const uint32_t ea = __shfl_sync(FULL, entry, has0 ? a0 : 0u), eb = __shfl_sync(FULL, entry, has1 ? w0 + a1 : 0u);
+            uint32_t pick;
+            if (has0 && has1) {
+                const uint32_t ao = ea & ICX_NB_INDEX_MASK, bo = eb & ICX_NB_INDEX_MASK;
+                const bool alow = ao < c.p0, blow = bo < c.p0;
+                if (alow || blow) pick = (alow && blow) ? (bo < ao ? 1u : 0u) : (alow ? 0u : 1u);
+                else pick = 0u;
+            } else pick = has0 ? 0u : 1u;
+            if (stops >> (pick ? w0 + a1 : a0) & 1u) break;
+            if (pick) a1++; else a0++;
+        }
+        hw = (h0 + a0) | ((h1 + a1) << 16);
+        if (!boundary) return hw;
     }
 }
 
-__device__ __forceinline__ void settle(const DeviceWorld& W, uint32_t s, const Cursor& c, uint32_t hw, uint32_t n_dirty, int parity, uint32_t ctr_out)
+// warp version of settle: lane 0 publishes the cursor
+__device__ __forceinline__ void settle_warp(const DeviceWorld& W, uint32_t s, const Cursor& c, uint32_t hw, uint32_t n_dirty, int parity, uint32_t ctr_out)
 {
-    hw = skip_rejects(W, c, hw, n_dirty);
-    W.head[parity ^ 1][s] = hw;
-    if (cursor_pending(c, hw)) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = s;
+    hw = skip_rejects_warp(W, c, hw, n_dirty);
+    if ((threadIdx.x & 31u) == 0u) {
+        W.head[parity ^ 1][s] = hw;
+        if (cursor_pending(c, hw)) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = s;
+    }
 }
 
 __device__ __forceinline__ void round_select(const DeviceWorld& W, uint32_t s, uint32_t n_dirty, int parity, uint32_t ctr_out, uint32_t ctr_items)
@@ -625,15 +671,21 @@ __device__ __forceinline__ void round_select(const DeviceWorld& W, uint32_t s, u
         return;
     }
     if (p > o) return;                                                              // the lower packet's lane acts for both
-    if (may_hit(W, p, o, 0.0f)) { W.items[atomicAdd(&W.counters[ctr_items], 1u)] = make_uint4(p, o, s, so); return; }
-    settle(W, s, c, cursor_advance(hw, k), n_dirty, parity, ctr_out);               // certain miss: consumed on both sides
-    settle(W, so, co, cursor_advance(hwo, ko), n_dirty, parity, ctr_out);
+    // a certain miss is consumed on both sides without the exact procedure; the cursor walk that follows is a warp's job either way
+    W.items[atomicAdd(&W.counters[ctr_items], 1u)] = make_uint4(p, may_hit(W, p, o, 0.0f) ? o : (o | ICX_ITEM_MISS), s, so);
 }
 
 __device__ __forceinline__ void round_execute(const DeviceWorld& W, uint4 item, uint32_t n_dirty, int parity, uint32_t ctr_out, uint32_t ctr_new)
 {
-    process_pair(W, item.x, item.y, n_dirty, ctr_new);             // whole warp
+#ifdef ICX_PROFILE_PAIR
+    const long long t0 = clock64();
+#endif
+    if (!(item.y & ICX_ITEM_MISS)) process_pair(W, item.x, item.y, n_dirty, ctr_new);             // whole warp
     __syncwarp();
+#ifdef ICX_PROFILE_PAIR
+    const long long t1 = clock64();
+    PROF_ADD(0, 1); PROF_ADD(1, (t1 - t0) >> 4);
+#endif
     // Advance the cursor(s).  One-sided pairs that follow need no partner: the warp runs them at once
     // instead of spending a round on each (all lanes walk the cursor redundantly, lane 0 writes).
     for (int side = 0; side < 2; side++) {
@@ -645,10 +697,11 @@ __device__ __forceinline__ void round_execute(const DeviceWorld& W, uint4 item, 
         cursor_head(c, hw, k, entry);                                               // the entry just executed
         hw = cursor_advance(hw, k);
         for (;;) {
-            hw = skip_rejects(W, c, hw, n_dirty);
+            hw = skip_rejects_warp(W, c, hw, n_dirty);
             if (!cursor_head(c, hw, k, entry)) break;
             const uint32_t p = c.p0 + k, o = entry & ICX_NB_INDEX_MASK;
             if (!(entry & ICX_NB_IMMUTABLE) && W.dirty_slot[W.pk_entity[o]] < n_dirty) break;     // two-sided: next round
+            PROF_ADD(4, 1);
             process_pair(W, min(p, o), max(p, o), n_dirty, ctr_new);
             __syncwarp();
             hw = cursor_advance(hw, k);
@@ -658,6 +711,9 @@ __device__ __forceinline__ void round_execute(const DeviceWorld& W, uint4 item, 
             if (cursor_pending(c, hw)) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = s;
         }
     }
+#ifdef ICX_PROFILE_PAIR
+    PROF_ADD(2, (clock64() - t1) >> 4);
+#endif
 }
 
 // ---------------------------------------------------------------------------------------
@@ -742,8 +798,8 @@ __global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(DeviceWorld W, double d
         grid.sync();
         // static pairs (contact records only), then every body's cursor to its first entry of interest
         for (uint32_t i = tid >> 5; i < n_static; i += nth >> 5) { const uint2 pr = W.static_pairs[i]; process_pair(W, pr.x, pr.y, n_dirty, CTR_NEWD); }
-        for (uint32_t s = tid; s < n_dirty; s += nth)
-            settle(W, s, load_cursor(W, s, W.dirty_list[s]), 0u, n_dirty, 1, CTR_ACTIVE);     // writes head[0] / active[0]
+        for (uint32_t s = tid >> 5; s < n_dirty; s += nth >> 5)
+            settle_warp(W, s, load_cursor(W, s, W.dirty_list[s]), 0u, n_dirty, 1, CTR_ACTIVE);     // writes head[0] / active[0]
         grid.sync();
         if (tid == 0) trace_mark(W, tn, 0x50000u);
         int parity = 0;

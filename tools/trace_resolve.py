@@ -10,8 +10,8 @@ for k in range(2):
     print("tick", k, "dirty", st.n_dirty, "rounds", st.n_rounds, "attempts", st.n_attempts, "contacts", st.n_contacts, "ms", w.last_step_ms())
     cn = np.zeros(48, np.uint32); w.lib.icx_debug_counters(w.handle, cn.ctypes.data_as(ctypes.c_void_p)); pr = cn[32:]
     if pr[0]:
-        print("  exact pairs", pr[0], "load wait", pr[1]/pr[0], "intersect", pr[2]/pr[0], "| responses", pr[3], "response+clean", pr[4]/max(pr[3],1),
-              "| box finishes", pr[5], "cycles", pr[6]/max(pr[5],1))
+        print("  items", pr[0], "cycles/first pair", 16*pr[1]/pr[0], "cycles/chain", 16*pr[2]/pr[0], "| filter calls", pr[3], "follow-up pairs", pr[4],
+              "| load+SAT cycles per exact pair", 16*pr[5]/max(pr[0]+pr[4],1), "not separated", pr[6])
     prev = 0
     for t, tag in w.trace(True):
         print(f"  {t/1e3:9.1f} us (+{(t-prev)/1e3:7.1f})  tag {tag>>16:x} arg {tag&0xffff}")
