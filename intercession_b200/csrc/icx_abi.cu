@@ -55,9 +55,9 @@ int allocate(IcxWorld* w)
     CK(alloc(w, W.large_list, W.max_large));
     CK(alloc(w, W.pairs, W.max_pairs)); CK(alloc(w, W.tight, W.max_pairs)); CK(alloc(w, W.near, W.max_pairs)); CK(alloc(w, W.push, ne)); CK(alloc(w, W.static_pairs, W.max_static));
     CK(alloc(w, W.dirty_slot, ne)); CK(alloc(w, W.dirty_list, ne));
-    CK(alloc(w, W.nbr, 2 * ne * (size_t)W.max_neighbors)); CK(alloc(w, W.nbr_count, 2 * ne));
+    CK(alloc(w, W.nbr, 2 * ne * (size_t)W.max_neighbors)); CK(alloc(w, W.nbr_count, 2 * ne)); CK(alloc(w, W.slot_info, ne));
     CK(alloc(w, W.head[0], ne)); CK(alloc(w, W.head[1], ne));
-    CK(alloc(w, W.active[0], ne)); CK(alloc(w, W.active[1], ne)); CK(alloc(w, W.items, ne));
+    CK(alloc(w, W.active[0], ne)); CK(alloc(w, W.active[1], ne)); CK(alloc(w, W.items, ne + W.max_static));
     CK(alloc(w, W.contacts, W.max_contacts)); CK(alloc(w, W.intercepts, W.max_contacts)); CK(alloc(w, W.intercept_key, W.max_contacts));
     CK(alloc(w, W.counters, CTR_TOTAL)); CK(alloc(w, W.flags, 4));
     CK(cudaMemset(W.counters, 0, CTR_TOTAL * sizeof(uint32_t))); CK(cudaMemset(W.flags, 0, 16));
@@ -166,6 +166,7 @@ int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_
             if (w->h_counters[CTR_STATIC] > W.max_static) {
                 W.max_static = w->h_counters[CTR_STATIC] * 2;
                 rc = regrow(w, W.static_pairs, W.max_static); if (rc) return rc;
+                rc = regrow(w, W.items, (size_t)w->cap_entities + W.max_static); if (rc) return rc;     // static pairs ride in the first round's item list
             }
         }
         if (raised & RF_MARGIN_VIOLATED) {

@@ -52,6 +52,18 @@ __device__ __forceinline__ bool overlap(float4 alo, float4 ahi, float4 blo, floa
     return alo.x <= bhi.x && blo.x <= ahi.x && alo.y <= bhi.y && blo.y <= ahi.y && alo.z <= bhi.z && blo.z <= ahi.z;
 }
 
+// un-inflated bounds overlap (with 10 % of the margin kept as slack against rounding): only then can
+// the narrowphase report a hit on the post-integration state (DESIGN.md "Broadphase bound")
+__device__ __forceinline__ bool tight_le(float a, float b, float m2) {
+    const float s = m2 - 2.0e-6f * (fabsf(a) + fabsf(b));
+    return a + fmaxf(s, 0.0f) <= b;
+}
+__device__ __forceinline__ bool tight_overlap(float4 alo, float4 ahi, float4 blo, float4 bhi, float margin) {
+    const float m2 = 1.8f * margin;
+    return tight_le(alo.x, bhi.x, m2) && tight_le(blo.x, ahi.x, m2) && tight_le(alo.y, bhi.y, m2) && tight_le(blo.y, ahi.y, m2) &&
+           tight_le(alo.z, bhi.z, m2) && tight_le(blo.z, ahi.z, m2);
+}
+
 struct EntityRegs { float4 pos, rot, vel, acc, av, aa; };
 
 // EulerPhysicsRelay::engage for one entity, euler_physics_relay.h:25-95.  Reads W.in, returns the

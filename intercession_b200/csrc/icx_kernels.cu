@@ -229,18 +229,6 @@ struct PairStage {
     uint2 cand[PAIRS_TPB / 32][CAND_CAP];           // per warp: (packet slot in the block, sorted position of the partner) whose bounds overlap
 };
 
-// un-inflated bounds overlap (with 10 % of the margin kept as slack against rounding): only then can
-// the narrowphase report a hit on the post-integration state (DESIGN.md "Broadphase bound")
-__device__ __forceinline__ bool tight_le(float a, float b, float m2) {
-    const float s = m2 - 2.0e-6f * (fabsf(a) + fabsf(b));
-    return a + fmaxf(s, 0.0f) <= b;
-}
-__device__ __forceinline__ bool tight_overlap(float4 alo, float4 ahi, float4 blo, float4 bhi, float margin) {
-    const float m2 = 1.8f * margin;
-    return tight_le(alo.x, bhi.x, m2) && tight_le(blo.x, ahi.x, m2) && tight_le(alo.y, bhi.y, m2) && tight_le(blo.y, ahi.y, m2) &&
-           tight_le(alo.z, bhi.z, m2) && tight_le(blo.z, ahi.z, m2);
-}
-
 // Per-warp pair stage: every lane of a converged warp calls with its verdict; entries are appended
 // by ballot / popc (no atomics) and the stage is copied out in one coalesced run with ONE global
 // atomic per list when it could overflow on the next call.

@@ -83,6 +83,29 @@ ICX_DI int build_contact_manifold(const M4& m, V3 axis, V3* dest) {
         if ((kept >> o & 1u) && coeffs[o] >= maxCoeff - ICX_MANIFOLD_DEPTH) dest[n++] = verts[o];
     return n;
 }
+// The same with rolled loops over caller-provided scratch (tmpv: 8 vertices, tmpc: 8 floats): the
+// ordered resolve runs this once per warp on cold code, where instruction fetch is the cost.
+ICX_DI int build_contact_manifold_s(const M4& m, V3 axis, V3* dest, V3* tmpv, float* tmpc) {
+    uint32_t kept = 0;
+    float maxCoeff = -INFINITY;
+    float dx = -1.0f, dy = -1.0f, dz = -1.0f;
+#pragma unroll 1
+    for (int o = 0; o < 8; o++) {
+        const V3 vertex = xform(m, ICX_UNIT_RADIUS * dx, ICX_UNIT_RADIUS * dy, ICX_UNIT_RADIUS * dz);
+        const float coeff = dot(vertex, axis);
+        maxCoeff = coeff > maxCoeff ? coeff : maxCoeff;
+        if (coeff >= maxCoeff - ICX_MANIFOLD_DEPTH) kept |= 1u << o;
+        tmpc[o] = coeff; tmpv[o] = vertex;
+        if ((o & 1) == 0) dx = dx < 0.0f ? 1.0f : -1.0f;
+        else if ((o & 3) == 1) dy = dy < 0.0f ? 1.0f : -1.0f;
+        else dz = dz < 0.0f ? 1.0f : -1.0f;
+    }
+    int n = 0;
+#pragma unroll 1
+    for (int o = 7; o >= 0; o--)
+        if ((kept >> o & 1u) && tmpc[o] >= maxCoeff - ICX_MANIFOLD_DEPTH) dest[n++] = tmpv[o];
+    return n;
+}
 // glm::intersectRayPlane, gtx/intersect.inl:6-26
 ICX_DI bool intersect_ray_plane(V3 orig, V3 dir, V3 planeOrig, V3 planeNormal, float& dist) {
     float d = dot(dir, planeNormal);
@@ -92,11 +115,15 @@ ICX_DI bool intersect_ray_plane(V3 orig, V3 dir, V3 planeOrig, V3 planeNormal, f
     }
     return false;
 }
-// pseudo_clip_polyhedra, collision_procedures.h:163-313
-ICX_DN void pseudo_clip_polyhedra(const V3* clipper, int nc, V3* clippee, int& ne, V3 axis) {
+// pseudo_clip_polyhedra, collision_procedures.h:163-313.  `clipped` = caller-provided scratch of
+// ICX_MAXV vertices: the ordered resolve hands in shared memory, because a single active lane
+// working on thread-local arrays touches one 128-byte line per word and thrashes L1.
+ICX_DI void pseudo_clip_polyhedra_s(const V3* clipper, int nc, V3* clippee, int& ne, V3 axis, V3* clipped) {
     V3 centre = v3(0.0f, 0.0f, 0.0f);
+#pragma unroll 1
     for (int i = 0; i < nc; i++) centre = centre + clipper[i];
     centre = centre / (float)nc;
+#pragma unroll 1
     for (int i = 0; i < nc; i++) {
         V3 tangent = cross(axis, clipper[(i + 1) % nc] - clipper[i]);
         if (length2(tangent) == 0.0f) continue;
@@ -105,9 +132,10 @@ ICX_DN void pseudo_clip_polyhedra(const V3* clipper, int nc, V3* clippee, int& n
         float insideCoeff = 0.0f;
         if (nc > 2) insideCoeff = pn.x * centre.x + pn.y * centre.y + pn.z * centre.z + pw;
         if (insideCoeff == 0.0f) insideCoeff = INFINITY;
-        V3 clipped[ICX_MAXV]; int nk = 0;
+        int nk = 0;
         float prevCoeff = -INFINITY;
         if (ne == 0) break;
+#pragma unroll 1
         for (int j = 0; j < ne + 1; j++) {
             if (ne == 2 && j >= 2) break;
             int J = j % ne;
@@ -128,9 +156,15 @@ ICX_DN void pseudo_clip_polyhedra(const V3* clipper, int nc, V3* clippee, int& n
             }
             if (currInside && j < ne) { if (nk < ICX_MAXV) clipped[nk++] = clippee[J]; }
         }
+#pragma unroll 1
         for (int k = 0; k < nk; k++) clippee[k] = clipped[k];
         ne = nk;
     }
+}
+
+ICX_DN void pseudo_clip_polyhedra(const V3* clipper, int nc, V3* clippee, int& ne, V3 axis) {
+    V3 clipped[ICX_MAXV];
+    pseudo_clip_polyhedra_s(clipper, nc, clippee, ne, axis, clipped);
 }
 
 // the 15 SAT axes of box_box / sphere_box, collision_procedures.cpp:41-67; a = 0..14
@@ -167,16 +201,17 @@ ICX_DI AxisResult sphere_box_axis(const M3& nA, const M3& nB, V3 sO, float projR
 }
 
 // box_box_intersect after the axis loop, collision_procedures.cpp:120-231 (h.normal / h.depth are set)
-ICX_DN bool box_box_finish(const Shape& A, const Shape& B, Hit& h) {
-    V3 mA[8], mB[ICX_MAXV];
-    int nMA = build_contact_manifold(A.M, -h.normal, mA);                           // :128-132
-    int nMB = build_contact_manifold(B.M, h.normal, mB);
+// mA (8), mB (ICX_MAXV), clipped (ICX_MAXV): caller-provided scratch, see pseudo_clip_polyhedra_s
+ICX_DI bool box_box_finish_s(const Shape& A, const Shape& B, Hit& h, V3* mA, V3* mB, V3* clipped) {
+    int nMA = build_contact_manifold_s(A.M, -h.normal, mA, clipped, (float*)(clipped + 8));      // :128-132 (clipped is free until the clip)
+    int nMB = build_contact_manifold_s(B.M, h.normal, mB, clipped, (float*)(clipped + 8));
     if (nMB == 0 || nMA == 0) return false;                                         // :135-139
     if (nMB == 1) { h.point = mB[0]; return true; }                                 // :140-146
     if (nMA == 1) { h.point = mA[0] + (h.normal * h.depth); return true; }          // :147-153
-    pseudo_clip_polyhedra(mA, nMA, mB, nMB, h.normal);                              // :159
+    pseudo_clip_polyhedra_s(mA, nMA, mB, nMB, h.normal, clipped);                   // :159
     if (nMB == 1) { h.point = mB[0]; return true; }                                 // :168-172
     float maxCoeff = -INFINITY; V3 origin = v3(0.0f, 0.0f, 0.0f); float contributors = 0.0f;   // :181-199
+#pragma unroll 1
     for (int i = 0; i < nMB; i++) {
         float vc = dot(mB[i], h.normal);
         if (vc > maxCoeff) { origin = mB[i]; contributors = 1.0f; maxCoeff = vc; }
@@ -185,6 +220,7 @@ ICX_DN bool box_box_finish(const Shape& A, const Shape& B, Hit& h) {
     origin = origin / contributors;                                                 // :203
     const float manifoldRange = 1.0f - ICX_MANIFOLD_MIN_WEIGHT;
     V3 pt = v3(0.0f, 0.0f, 0.0f);
+#pragma unroll 1
     for (int i = 0; i < nMB; i++) {                                                 // :210-221
         float vc = dot(mB[i], h.normal);
         V3 rel = mB[i] - origin;
@@ -194,6 +230,11 @@ ICX_DN bool box_box_finish(const Shape& A, const Shape& B, Hit& h) {
     pt = pt / (float)nMB;                                                           // :222
     h.point = pt + origin;
     return true;
+}
+
+ICX_DN bool box_box_finish(const Shape& A, const Shape& B, Hit& h) {
+    V3 mA[8], mB[ICX_MAXV], clipped[ICX_MAXV];
+    return box_box_finish_s(A, B, h, mA, mB, clipped);
 }
 
 // box_box_intersect, collision_procedures.cpp:14-231

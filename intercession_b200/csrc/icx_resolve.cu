@@ -30,35 +30,36 @@ namespace icx {
 #else
 #define PROF_ADD(k, v) do { } while (0)
 #endif
-struct Cursor { uint32_t p0, npk, n0, n1; const uint32_t* l0; const uint32_t* l1; };
+// list entry: x = other packet | ICX_NB_IMMUTABLE, y = its entity index (saves one dependent load per walk step)
+struct Cursor { uint32_t p0, npk, n0, n1, e; const uint2* l0; const uint2* l1; };
 
-__device__ __forceinline__ Cursor load_cursor(const DeviceWorld& W, uint32_t slot, uint32_t e)
+// slot_info[slot] = {first packet | count << 30, n0, n1, entity}: everything a walk needs in ONE load
+__device__ __forceinline__ Cursor make_cursor(const DeviceWorld& W, uint32_t slot, uint4 info)
 {
     Cursor c;
-    const uint32_t fp = W.first_packet[e];
-    c.npk = fp >> 30; c.p0 = fp & 0x3FFFFFFFu;
+    c.npk = info.x >> 30; c.p0 = info.x & 0x3FFFFFFFu; c.n0 = info.y; c.n1 = info.z; c.e = info.w;
     c.l0 = W.nbr + (size_t)(slot * 2u) * W.max_neighbors; c.l1 = c.l0 + W.max_neighbors;
-    c.n0 = W.nbr_count[slot * 2u]; c.n1 = W.nbr_count[slot * 2u + 1u];
     return c;
 }
+__device__ __forceinline__ Cursor load_cursor(const DeviceWorld& W, uint32_t slot) { return make_cursor(W, slot, W.slot_info[slot]); }
 // Next entry of the body's merged queue.  Order = the reference's lexicographic pair order seen
 // from this body: first pairs whose other packet precedes mine, by (other, my slot); then all
 // pairs of my slot-0 packet, then all of my slot-1 packet.
-__device__ __forceinline__ bool cursor_head(const Cursor& c, uint32_t hw, uint32_t& k, uint32_t& entry)
+__device__ __forceinline__ bool cursor_head(const Cursor& c, uint32_t hw, uint32_t& k, uint32_t& entry, uint32_t& eo)
 {
     const uint32_t h0 = hw & 0xFFFFu, h1 = hw >> 16;
     const bool has0 = h0 < c.n0, has1 = h1 < c.n1;
     if (!has0 && !has1) return false;
-    uint32_t a = 0, b = 0;
-    if (has0) a = c.l0[h0];
-    if (has1) b = c.l1[h1];
+    uint32_t a = 0, b = 0, ea = 0, eb = 0;
+    if (has0) { const uint2 v = c.l0[h0]; a = v.x; ea = v.y; }
+    if (has1) { const uint2 v = c.l1[h1]; b = v.x; eb = v.y; }
     if (has0 && has1) {
         const uint32_t ao = a & ICX_NB_INDEX_MASK, bo = b & ICX_NB_INDEX_MASK;
         const bool alow = ao < c.p0, blow = bo < c.p0;
         if (alow || blow) k = (alow && blow) ? (bo < ao ? 1u : 0u) : (alow ? 0u : 1u);
         else k = 0u;
     } else k = has0 ? 0u : 1u;
-    entry = k ? b : a;
+    entry = k ? b : a; eo = k ? eb : ea;
     return true;
 }
 __device__ __forceinline__ uint32_t cursor_advance(uint32_t hw, uint32_t k) { return k ? hw + 0x10000u : hw + 1u; }
@@ -170,11 +171,60 @@ __device__ __forceinline__ bool is_sat_pair(int tA, int tB) {
     return (tA == ICX_COLLIDER_BOX && (tB == ICX_COLLIDER_BOX || tB == ICX_COLLIDER_SPHERE)) || (tA == ICX_COLLIDER_SPHERE && tB == ICX_COLLIDER_BOX);
 }
 // current-state filter for packets pa, pb: false = the exact procedure cannot report a hit
-__device__ __forceinline__ bool may_hit(const DeviceWorld& W, uint32_t pa, uint32_t pb, float slack)
+// One copy (the unrolled 15-axis filter is ~18 KB of code).  The entities are passed in so that every
+// load is independent of the others: one memory round trip instead of three.
+static __device__ __noinline__ bool may_hit(const float4* __restrict__ pk_lpos, const float4* __restrict__ pk_d, const float4* __restrict__ pos,
+                                            uint32_t pa, uint32_t pb, uint32_t ea, uint32_t eb, float slack)
 {
-    const int tA = __float_as_uint(W.pk_lpos[pa].w) & PF_TYPE_MASK, tB = __float_as_uint(W.pk_lpos[pb].w) & PF_TYPE_MASK;
+    const float wA = pk_lpos[pa].w, wB = pk_lpos[pb].w;
+    const float4 posA = pos[ea], posB = pos[eb];
+    const int tA = __float_as_uint(wA) & PF_TYPE_MASK, tB = __float_as_uint(wB) & PF_TYPE_MASK;
     if (!is_sat_pair(tA, tB)) return true;
-    return sat_may_hit(W.pk_d + (size_t)pa * 6, W.pk_d + (size_t)pb * 6, v3(W.out.pos[W.pk_entity[pa]]), v3(W.out.pos[W.pk_entity[pb]]), tA, tB, slack);
+    return sat_may_hit(pk_d + (size_t)pa * 6, pk_d + (size_t)pb * 6, v3(posA), v3(posB), tA, tB, slack);
+}
+// packets p (entity e) and o (entity eo) in either order
+__device__ __forceinline__ bool may_hit_po(const DeviceWorld& W, uint32_t p, uint32_t e, uint32_t o, uint32_t eo) {
+    return p < o ? may_hit(W.pk_lpos, W.pk_d, W.out.pos, p, o, e, eo, 0.0f) : may_hit(W.pk_lpos, W.pk_d, W.out.pos, o, p, eo, e, 0.0f);
+}
+
+// The same filter by a whole warp for ONE pair (uniform arguments): lane a evaluates axis a, so the
+// verdict costs one axis of latency instead of fifteen.  Same arithmetic per axis as sat_may_hit.
+__device__ __forceinline__ bool may_hit_warp(const DeviceWorld& W, uint32_t pa, uint32_t pb, uint32_t ea, uint32_t eb)
+{
+    const uint32_t FULL = 0xFFFFFFFFu, lane = threadIdx.x & 31u;
+    const float wA = W.pk_lpos[pa].w, wB = W.pk_lpos[pb].w;
+    const float4 pA = W.out.pos[ea], pB = W.out.pos[eb];
+    const float4* __restrict__ dA = W.pk_d + (size_t)pa * 6; const float4* __restrict__ dB = W.pk_d + (size_t)pb * 6;
+    const float4 a0 = dA[0], a1 = dA[1], a2 = dA[2], a3 = dA[3], a4 = dA[4], a5 = dA[5];
+    const float4 b0 = dB[0], b1 = dB[1], b2 = dB[2], b3 = dB[3], b4 = dB[4], b5 = dB[5];
+    const int tA = __float_as_uint(wA) & PF_TYPE_MASK, tB = __float_as_uint(wB) & PF_TYPE_MASK;
+    if (!is_sat_pair(tA, tB)) return true;
+    const V3 A0 = v3(a0), A1 = v3(a1), A2 = v3(a2), B0 = v3(b0), B1 = v3(b1), B2 = v3(b2);
+    const V3 cA = v3(a0.w, a1.w, a2.w) + v3(pA), cB = v3(b0.w, b1.w, b2.w) + v3(pB);
+    const V3 d = cA - cB;
+    const float cmag = fabsf(cA.x) + fabsf(cA.y) + fabsf(cA.z) + fabsf(cB.x) + fabsf(cB.y) + fabsf(cB.z);
+    const float sphA = tA == ICX_COLLIDER_SPHERE ? 0.5f * sqrtf(dot(A0, A0)) : -1.0f;
+    const float sphB = tB == ICX_COLLIDER_SPHERE ? 0.5f * sqrtf(dot(B0, B0)) : -1.0f;
+    const V3 nA0 = v3(a3.x, a4.x, a5.x), nA1 = v3(a3.y, a4.y, a5.y), nA2 = v3(a3.z, a4.z, a5.z);
+    const V3 nB0 = v3(b3.x, b4.x, b5.x), nB1 = v3(b3.y, b4.y, b5.y), nB2 = v3(b3.z, b4.z, b5.z);
+    bool sep = false;
+    if (lane < 15u) {
+        V3 L; float rel = 1.0e-4f; bool skip = false;
+        if (lane < 6u) L = lane == 0u ? nA0 : lane == 1u ? nA1 : lane == 2u ? nA2 : lane == 3u ? nB0 : lane == 4u ? nB1 : nB2;
+        else {
+            const uint32_t i = (lane - 6u) / 3u, j = (lane - 6u) % 3u;
+            const V3 x = i == 0u ? nA0 : i == 1u ? nA1 : nA2, y = j == 0u ? nB0 : j == 1u ? nB1 : nB2;
+            L = cross(x, y);
+            skip = dot(L, L) < 1.0e-4f * dot(x, x) * dot(y, y);
+            rel = 1.0e-3f;
+        }
+        const float l1 = fabsf(L.x) + fabsf(L.y) + fabsf(L.z);
+        const float rA = sphA >= 0.0f ? sphA * sqrtf(dot(L, L)) : box_radius(A0, A1, A2, L);
+        const float rB = sphB >= 0.0f ? sphB * sqrtf(dot(L, L)) : box_radius(B0, B1, B2, L);
+        const float sum = rA + rB, dist = fabsf(dot(d, L));
+        sep = !skip && dist > sum + rel * (sum + dist) + (4.0e-6f * cmag) * l1;
+    }
+    return __any_sync(FULL, sep) == 0;
 }
 
 // intersectProcedures[tA][tB], collision_procedures.h:411-417, for packets pa < pb on the current
@@ -303,7 +353,7 @@ __device__ __forceinline__ void store_side(const DeviceWorld& W, uint32_t e, con
 // pa < pb, executed by a whole warp (all lanes pass the same arguments).  n_dirty: bodies with
 // dirty_slot < n_dirty may be written; a hit on any other mutable body aborts the attempt (see the
 // file header).
-static __device__ __noinline__ void process_pair(const DeviceWorld& W, uint32_t pa, uint32_t pb, uint32_t n_dirty, uint32_t ctr_new)
+__device__ __forceinline__ void process_pair(const DeviceWorld& W, uint32_t pa, uint32_t pb, uint32_t n_dirty, uint32_t ctr_new, V3* scratch)
 {
     const bool writer = (threadIdx.x & 31u) == 0u;
 #ifdef ICX_PROFILE_PAIR
@@ -325,16 +375,14 @@ static __device__ __noinline__ void process_pair(const DeviceWorld& W, uint32_t 
     SatPick pick; pick.separated = true; pick.normal = h.normal; pick.depth = 0.0f;
     const bool bb = tA == ICX_COLLIDER_BOX && tB == ICX_COLLIDER_BOX, sb = tA == ICX_COLLIDER_SPHERE && tB == ICX_COLLIDER_BOX,
                bs = tA == ICX_COLLIDER_BOX && tB == ICX_COLLIDER_SPHERE;
-    if (bb) pick = sat_warp(A, B, false);
-    else if (sb) pick = sat_warp(A, B, true);
-    else if (bs) pick = sat_warp(B, A, true);
+    if (bb || sb || bs) pick = sat_warp(bs ? B : A, bs ? A : B, !bb);               // one instantiation: the code has to stay small (instruction cache)
 #ifdef ICX_PROFILE_PAIR
     if (writer) { atomicAdd(&W.counters[CTR_PROF + 5], (uint32_t)((clock64() - tp0) >> 4)); atomicAdd(&W.counters[CTR_PROF + 6], pick.separated ? 0u : 1u); }
 #endif
     if (!writer) return;
     bool hit = false;
     if (bb) {
-        if (!pick.separated) { h.normal = pick.normal; h.depth = pick.depth; hit = box_box_finish(A, B, h); }
+        if (!pick.separated) { h.normal = pick.normal; h.depth = pick.depth; hit = box_box_finish_s(A, B, h, scratch, scratch + 8, scratch + 8 + ICX_MAXV); }
     } else if (sb) {
         if (!pick.separated) { h.normal = pick.normal; h.depth = pick.depth; hit = sphere_box_finish(xform(A.M, 0.0f, 0.0f, 0.0f), xform(A.M, ICX_UNIT_RADIUS, 0.0f, 0.0f), h); }
     } else if (bs) {                                                                // box_sphere_intersect, .cpp:233-247
@@ -351,6 +399,11 @@ static __device__ __noinline__ void process_pair(const DeviceWorld& W, uint32_t 
         hit = sphere_sphere_intersect(A, ICX_UNIT_RADIUS * a.lscale.x * a.prm0.x, B, ICX_UNIT_RADIUS * b.lscale.x * b.prm0.x, h);   // .cpp:403-404
     }
     if (!hit) return;
+#ifdef ICX_PROFILE_PAIR
+    const long long tp1 = clock64();
+    atomicAdd(&W.counters[CTR_PROF + 7], (uint32_t)((tp1 - tp0) >> 4)); atomicAdd(&W.counters[CTR_PROF + 8], 1u);
+    if (bb) { atomicAdd(&W.counters[CTR_PROF + 11], (uint32_t)((tp1 - tp0) >> 4)); atomicAdd(&W.counters[CTR_PROF + 12], 1u); }
+#endif
     const uint32_t efA = __float_as_uint(a.prm1.w), efB = __float_as_uint(b.prm1.w);
     {
         const bool cleanA = !(efA & EF_IMMUTABLE) && a.slot >= n_dirty;
@@ -379,11 +432,14 @@ static __device__ __noinline__ void process_pair(const DeviceWorld& W, uint32_t 
         const bool rs = ctA == ICX_COLLISION_RIGID && ctB == ICX_COLLISION_SPRING;
         if (rr || sr || rs) {                                                       // other table entries are null_response
             Side SA = side_of(a, A, baseA, bitsA), SB = side_of(b, B, baseB, bitsB);
-            if (rr) rigid_rigid_response(SA, SB, h);
-            else if (sr) spring_rigid_response(SA, SB, h);
-            else {                                                                  // rigid_spring_response, .cpp:1055-1065
-                Hit inv; inv.normal = -h.normal; inv.point = h.point - (h.normal * h.depth); inv.depth = h.depth;
-                spring_rigid_response(SB, SA, inv);
+            if (rr) rigid_rigid_response_i(SA, SB, h);
+            else {
+                if (rs) {                                                           // rigid_spring_response, .cpp:1055-1065: swapped sides, inverted contact
+                    const Side t = SA; SA = SB; SB = t;
+                    Hit inv; inv.normal = -h.normal; inv.point = h.point - (h.normal * h.depth); inv.depth = h.depth;
+                    spring_rigid_response_i(SA, SB, inv);
+                    const Side u = SA; SA = SB; SB = u;
+                } else spring_rigid_response_i(SA, SB, h);
             }
             if (writer) {
                 if (!(efA & EF_IMMUTABLE)) store_side(W, ea, SA, a, rr);
@@ -392,6 +448,10 @@ static __device__ __noinline__ void process_pair(const DeviceWorld& W, uint32_t 
         }
     }
 
+#ifdef ICX_PROFILE_PAIR
+    const long long tp2 = clock64();
+    atomicAdd(&W.counters[CTR_PROF + 9], (uint32_t)((tp2 - tp1) >> 4));
+#endif
     // ***** behaviours response :114-155 -> contact record, replayed by the host adapter *****
     if (bitsA & PF_BEHAVIORS) cflags |= ICX_CONTACT_BEHAVIORS_A;
     if (bitsB & PF_BEHAVIORS) cflags |= ICX_CONTACT_BEHAVIORS_B;
@@ -442,7 +502,7 @@ static __device__ __noinline__ void process_pair(const DeviceWorld& W, uint32_t 
 // every pair that may hit happens in k_resolve.  Hits between two
 // immutable bodies change nothing and need no order; they are queued for their contact record.
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_narrow(DeviceWorld W)
+__global__ void __launch_bounds__(128) k_narrow(const __grid_constant__ DeviceWorld W)
 {
     const uint32_t n = min(W.counters[CTR_TIGHT], W.max_pairs);
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -478,7 +538,7 @@ __global__ void __launch_bounds__(128) k_narrow(DeviceWorld W)
 // reference's pair loop meets them (collision_physics_relay.h:29-37).  Lanes 0..17 resolve the
 // 9 rows x 2 bucket ranges around the body's cell, the candidates of all ranges are then tested
 // 32 at a time, and the survivors are ranked by counting (keys are distinct packet indices).
-__device__ __forceinline__ void build_lists_warp(const DeviceWorld& W, uint32_t slot)
+static __device__ __noinline__ void build_lists_warp(const DeviceWorld& W, uint32_t slot)
 {
     const uint32_t FULL = 0xFFFFFFFFu, lane = threadIdx.x & 31u;
     const uint32_t e = W.dirty_list[slot];
@@ -487,8 +547,9 @@ __device__ __forceinline__ void build_lists_warp(const DeviceWorld& W, uint32_t 
     const uint32_t wl = W.worldline_stride ? e / W.worldline_stride : 0u;
     const uint32_t n_large = min(W.counters[CTR_LARGE], W.max_large);
     const uint32_t cap = W.max_neighbors;
+    uint32_t cnt0 = 0, cnt1 = 0;
     for (uint32_t k = 0; k < 2u; k++) {
-        uint32_t* list = W.nbr + (size_t)(slot * 2u + k) * cap;
+        uint2* list = W.nbr + (size_t)(slot * 2u + k) * cap;
         uint32_t cnt = 0;                                   // warp-uniform
         if (k < npk && W.pk_cell[p0 + k] < 0xFFFFFFFEu) {
             const uint32_t p = p0 + k;
@@ -525,20 +586,20 @@ __device__ __forceinline__ void build_lists_warp(const DeviceWorld& W, uint32_t 
                     const uint32_t ro = __shfl_sync(FULL, off, r), rl = __shfl_sync(FULL, len, r), rb = __shfl_sync(FULL, beg, r);
                     if (idx >= ro && idx < ro + rl) j = rb + (idx - ro);
                 }
-                uint32_t entry = 0; bool pass = false;
+                uint2 entry = make_uint2(0u, 0u); bool pass = false;
                 if (j != ICX_NONE) {
                     const float4 blo = W.s_lo[j], bhi = W.s_hi[j];
                     const uint32_t btag = __float_as_uint(blo.w), be = __float_as_uint(bhi.w);
                     pass = overlap(lo, hi, blo, bhi) && be != e && (!W.worldline_stride || be / W.worldline_stride == wl) &&
                            can_intersect(type, (btag >> 28) & 3, W.cfg_flags);
-                    entry = (btag & ICX_NB_INDEX_MASK) | ((btag & 0x40000000u) ? ICX_NB_IMMUTABLE : 0u);
+                    entry = make_uint2((btag & ICX_NB_INDEX_MASK) | ((btag & 0x40000000u) ? ICX_NB_IMMUTABLE : 0u), be);
                 } else if (idx >= n_grid_cand && idx < total) {
                     const uint32_t o = W.large_list[idx - n_grid_cand];
                     const uint32_t oe = W.pk_entity[o];
                     pass = oe != e && (!W.worldline_stride || oe / W.worldline_stride == wl) &&
                            can_intersect(type, (int)(__float_as_uint(W.pk_lpos[o].w) & PF_TYPE_MASK), W.cfg_flags) &&
                            overlap(lo, hi, W.pk_lo[o], W.pk_hi[o]);
-                    entry = o | ICX_NB_IMMUTABLE;
+                    entry = make_uint2(o | ICX_NB_IMMUTABLE, oe);
                 }
                 const uint32_t m = __ballot_sync(FULL, pass);
                 if (pass) { const uint32_t at = cnt + __popc(m & ((1u << lane) - 1u)); if (at < cap) list[at] = entry; }
@@ -548,22 +609,24 @@ __device__ __forceinline__ void build_lists_warp(const DeviceWorld& W, uint32_t 
             if (cnt > cap) { if (lane == 0) atomicOr(W.flags, RF_NEIGHBOR_OVERFLOW); cnt = cap; }
             // ---- sort ascending by packet index ----
             if (cnt <= 32u) {
-                const uint32_t mine = lane < cnt ? list[lane] : 0xFFFFFFFFu;
+                const uint2 mine = lane < cnt ? list[lane] : make_uint2(0xFFFFFFFFu, 0u);
                 uint32_t rank = 0;
-                for (uint32_t q = 0; q < cnt; q++) { const uint32_t other = __shfl_sync(FULL, mine, q); rank += ((other & ICX_NB_INDEX_MASK) < (mine & ICX_NB_INDEX_MASK)) ? 1u : 0u; }
+                for (uint32_t q = 0; q < cnt; q++) { const uint32_t other = __shfl_sync(FULL, mine.x, q); rank += ((other & ICX_NB_INDEX_MASK) < (mine.x & ICX_NB_INDEX_MASK)) ? 1u : 0u; }
                 __syncwarp();
                 if (lane < cnt) list[rank] = mine;
             } else if (lane == 0) {
                 for (uint32_t i = 1; i < cnt; i++) {
-                    const uint32_t v = list[i]; uint32_t q = i;
-                    while (q > 0 && (list[q - 1] & ICX_NB_INDEX_MASK) > (v & ICX_NB_INDEX_MASK)) { list[q] = list[q - 1]; q--; }
+                    const uint2 v = list[i]; uint32_t q = i;
+                    while (q > 0 && (list[q - 1].x & ICX_NB_INDEX_MASK) > (v.x & ICX_NB_INDEX_MASK)) { list[q] = list[q - 1]; q--; }
                     list[q] = v;
                 }
             }
             __syncwarp();
         }
         if (lane == 0) W.nbr_count[slot * 2u + k] = cnt;
+        if (k == 0u) cnt0 = cnt; else cnt1 = cnt;
     }
+    if (lane == 0) W.slot_info[slot] = make_uint4(fp, cnt0, cnt1, e);
 }
 
 // Put a dirty body back to its post-integration state (bit-identical recomputation from the tick input).
@@ -590,15 +653,21 @@ static __device__ __noinline__ void restore_body(const DeviceWorld& W, uint32_t 
 // separated by grid barriers.  Cursors are double buffered (head[parity]); each active body has
 // exactly one writer per round.
 
-// Advance a body's cursor past the leading one-sided entries the filter rejects (own state is
-// final until the body's next exact pair, the partners are never written).  Done by a whole WARP
-// (all lanes pass the same arguments, the result is uniform): the
-// upcoming entries of both lists are classified in parallel, one entry per lane -- every filter
-// evaluation is a chain of dependent loads, which a single thread would pay for entry after
-// entry -- and the merged queue order is then replayed over the 32 precomputed verdicts.
-__device__ __forceinline__ uint32_t skip_rejects_warp(const DeviceWorld& W, const Cursor& c, uint32_t hw, uint32_t n_dirty)
+// Advance a body's cursor past the leading one-sided entries that cannot hit on the current state
+// (own state is final until the body's next exact pair, one-sided partners are never written).
+// Done by a whole WARP (uniform arguments and result).  Pass 1, one entry per lane: two-sided
+// entries (dirty partner) stop the walk; of the others only those whose un-inflated bounds overlap
+// -- mine translated by what static resolution moved me so far -- are candidates (the test that
+// defines ICX_PAIR_TIGHT).  Pass 2 replays the merged queue order over the 32 verdicts and gives
+// each candidate it meets to the warp-cooperative SAT filter.  kind: 0 = queue exhausted,
+// 1 = rests on a two-sided entry, 2 = rests on a one-sided pair to execute (list k_out, packet o_out).
+__device__ __forceinline__ uint32_t skip_rejects_warp(const DeviceWorld& W, const Cursor& c, uint32_t hw, uint32_t n_dirty,
+                                                      int& kind, uint32_t& k_out, uint32_t& o_out)
 {
     const uint32_t FULL = 0xFFFFFFFFu, lane = threadIdx.x & 31u;
+    const float4 pe = W.out.pos[c.e], pe0 = W.pos0[c.e];
+    const float dx = pe.x - pe0.x, dy = pe.y - pe0.y, dz = pe.z - pe0.z;
+    kind = 0; k_out = 0; o_out = 0;
     for (;;) {
         const uint32_t h0 = hw & 0xFFFFu, h1 = hw >> 16;
         const uint32_t rem0 = h0 < c.n0 ? c.n0 - h0 : 0u, rem1 = h1 < c.n1 ? c.n1 - h1 : 0u;
@@ -606,21 +675,27 @@ __device__ __forceinline__ uint32_t skip_rejects_warp(const DeviceWorld& W, cons
         const uint32_t w0 = rem1 == 0u ? 32u : (rem0 == 0u ? 0u : 16u);        // lanes [0, w0) look at list 0, the rest at list 1
         const uint32_t k = lane < w0 ? 0u : 1u, idx = k ? lane - w0 : lane;
         const bool valid = idx < (k ? rem1 : rem0);
-        uint32_t entry = 0; bool stop = false;
+        uint32_t entry = 0, ent = 0; bool two = false, cand = false;
         if (valid) {
             PROF_ADD(3, 1);
-            entry = k ? c.l1[h1 + idx] : c.l0[h0 + idx];
+            const uint2 en = k ? c.l1[h1 + idx] : c.l0[h0 + idx];
+            entry = en.x; ent = en.y;
             const uint32_t p = c.p0 + k, o = entry & ICX_NB_INDEX_MASK;
-            stop = (!(entry & ICX_NB_IMMUTABLE) && W.dirty_slot[W.pk_entity[o]] < n_dirty) || may_hit(W, min(p, o), max(p, o), 0.0f);
+            const uint32_t ds = (entry & ICX_NB_IMMUTABLE) ? ICX_NONE : W.dirty_slot[en.y];
+            float4 alo = W.pk_lo[p], ahi = W.pk_hi[p];
+            const float4 blo = W.pk_lo[o], bhi = W.pk_hi[o];
+            alo.x += dx; alo.y += dy; alo.z += dz; ahi.x += dx; ahi.y += dy; ahi.z += dz;
+            two = ds < n_dirty;
+            cand = !two && tight_overlap(alo, ahi, blo, bhi, W.margin);
         }
-        const uint32_t stops = __ballot_sync(FULL, stop);
-        // replay the merged order (cursor_head) over the chunk
+        const uint32_t twos = __ballot_sync(FULL, two), cands = __ballot_sync(FULL, cand);
         uint32_t a0 = 0, a1 = 0; bool boundary = false;
-        for (;;) {
+        for (;;) {                                                              // merged order (cursor_head) over the chunk
             const bool has0 = a0 < rem0, has1 = a1 < rem1;
             if (!has0 && !has1) break;
             if ((has0 && a0 >= w0) || (has1 && a1 >= 32u - w0)) { boundary = true; break; }
-            const uint32_t ea = __shfl_sync(FULL, entry, has0 ? a0 : 0u), eb = __shfl_sync(FULL, entry, has1 ? w0 + a1 : 0u);
+            const uint32_t la = has0 ? a0 : 0u, lb = has1 ? w0 + a1 : 0u;
+            const uint32_t ea = __shfl_sync(FULL, entry, la), eb = __shfl_sync(FULL, entry, lb);
             uint32_t pick;
             if (has0 && has1) {
                 const uint32_t ao = ea & ICX_NB_INDEX_MASK, bo = eb & ICX_NB_INDEX_MASK;
@@ -628,7 +703,13 @@ __device__ __forceinline__ uint32_t skip_rejects_warp(const DeviceWorld& W, cons
                 if (alow || blow) pick = (alow && blow) ? (bo < ao ? 1u : 0u) : (alow ? 0u : 1u);
                 else pick = 0u;
             } else pick = has0 ? 0u : 1u;
-            if (stops >> (pick ? w0 + a1 : a0) & 1u) break;
+            const uint32_t bit = pick ? lb : la;
+            if (twos >> bit & 1u) { kind = 1; break; }
+            if (cands >> bit & 1u) {
+                const uint32_t o = (pick ? eb : ea) & ICX_NB_INDEX_MASK, eo = __shfl_sync(FULL, ent, bit), p = c.p0 + pick;
+                const bool mh = p < o ? may_hit_warp(W, p, o, c.e, eo) : may_hit_warp(W, o, p, eo, c.e);
+                if (mh) { kind = 2; k_out = pick; o_out = o; break; }
+            }
             if (pick) a1++; else a0++;
         }
         hw = (h0 + a0) | ((h1 + a1) << 16);
@@ -639,7 +720,8 @@ __device__ __forceinline__ uint32_t skip_rejects_warp(const DeviceWorld& W, cons
 // warp version of settle: lane 0 publishes the cursor
 __device__ __forceinline__ void settle_warp(const DeviceWorld& W, uint32_t s, const Cursor& c, uint32_t hw, uint32_t n_dirty, int parity, uint32_t ctr_out)
 {
-    hw = skip_rejects_warp(W, c, hw, n_dirty);
+    int kind; uint32_t kk, oo;
+    hw = skip_rejects_warp(W, c, hw, n_dirty, kind, kk, oo);
     if ((threadIdx.x & 31u) == 0u) {
         W.head[parity ^ 1][s] = hw;
         if (cursor_pending(c, hw)) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = s;
@@ -649,22 +731,21 @@ __device__ __forceinline__ void settle_warp(const DeviceWorld& W, uint32_t s, co
 __device__ __forceinline__ void round_select(const DeviceWorld& W, uint32_t s, uint32_t n_dirty, int parity, uint32_t ctr_out, uint32_t ctr_items)
 {
     const uint32_t* __restrict__ hin = W.head[parity];
-    const uint32_t e = W.dirty_list[s];
-    const Cursor c = load_cursor(W, s, e);
+    const Cursor c = load_cursor(W, s);
     const uint32_t hw = hin[s];
-    uint32_t k, entry;
-    if (!cursor_head(c, hw, k, entry)) return;                                      // (not queued when nothing is pending)
+    uint32_t k, entry, eo;
+    if (!cursor_head(c, hw, k, entry, eo)) return;                                  // (not queued when nothing is pending)
     const uint32_t p = c.p0 + k, o = entry & ICX_NB_INDEX_MASK;
-    uint32_t eo = 0, so = ICX_NONE;
-    if (!(entry & ICX_NB_IMMUTABLE)) { eo = W.pk_entity[o]; so = W.dirty_slot[eo]; }
+    uint32_t so = ICX_NONE;
+    if (!(entry & ICX_NB_IMMUTABLE)) so = W.dirty_slot[eo];
     if (so >= n_dirty) {                                                            // one-sided, not rejected by the filter
         W.items[atomicAdd(&W.counters[ctr_items], 1u)] = make_uint4(min(p, o), max(p, o), s, ICX_NONE);
         return;
     }
-    const Cursor co = load_cursor(W, so, eo);
+    const Cursor co = load_cursor(W, so);
     const uint32_t hwo = hin[so];
-    uint32_t ko, entryo;
-    const bool ready = cursor_head(co, hwo, ko, entryo) && co.p0 + ko == o && (entryo & ICX_NB_INDEX_MASK) == p;
+    uint32_t ko, entryo, eoo;
+    const bool ready = cursor_head(co, hwo, ko, entryo, eoo) && co.p0 + ko == o && (entryo & ICX_NB_INDEX_MASK) == p;
     if (!ready) {                                                                   // wait: carry my cursor over
         W.head[parity ^ 1][s] = hw;
         W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = s;
@@ -672,47 +753,73 @@ __device__ __forceinline__ void round_select(const DeviceWorld& W, uint32_t s, u
     }
     if (p > o) return;                                                              // the lower packet's lane acts for both
     // a certain miss is consumed on both sides without the exact procedure; the cursor walk that follows is a warp's job either way
-    W.items[atomicAdd(&W.counters[ctr_items], 1u)] = make_uint4(p, may_hit(W, p, o, 0.0f) ? o : (o | ICX_ITEM_MISS), s, so);
+    W.items[atomicAdd(&W.counters[ctr_items], 1u)] = make_uint4(p, may_hit(W.pk_lpos, W.pk_d, W.out.pos, p, o, c.e, eo, 0.0f) ? o : (o | ICX_ITEM_MISS), s, so);
 }
 
-__device__ __forceinline__ void round_execute(const DeviceWorld& W, uint4 item, uint32_t n_dirty, int parity, uint32_t ctr_out, uint32_t ctr_new)
+// One work item, by a whole warp: the exact pair (unless the filter already rejected it), then the
+// cursors of its one or two dirty bodies move on.  The cursor records of both bodies are requested
+// BEFORE the exact procedure and arrive while it runs.  One-sided pairs that follow need no
+// partner and are executed at once -- through the same process_pair call site: the procedure is
+// ~85 KB of code and must exist once.
+__device__ __forceinline__ void round_execute(const DeviceWorld& W, uint4 item, uint32_t n_dirty, int parity, uint32_t ctr_out, uint32_t ctr_new, V3* scratch)
 {
+    const uint32_t FULL = 0xFFFFFFFFu, lane = threadIdx.x & 31u;
 #ifdef ICX_PROFILE_PAIR
     const long long t0 = clock64();
+    long long t_pair = 0;
 #endif
-    if (!(item.y & ICX_ITEM_MISS)) process_pair(W, item.x, item.y, n_dirty, ctr_new);             // whole warp
-    __syncwarp();
+    const uint32_t my_s = lane == 0u ? item.z : (lane == 1u ? item.w : ICX_NONE);
+    uint4 my_info = make_uint4(0u, 0u, 0u, 0u); uint32_t my_hw = 0u;
+    if (my_s != ICX_NONE) { my_info = W.slot_info[my_s]; my_hw = W.head[parity][my_s]; }
+
+    uint32_t pa = item.x, pb = item.y & ~ICX_ITEM_MISS;
+    bool run = !(item.y & ICX_ITEM_MISS);
+    int side = 0; bool entered = false;                                             // body being walked; its cursor is loaded
+    Cursor c; uint32_t hw = 0, k_run = 0;
+    c.p0 = c.npk = c.n0 = c.n1 = c.e = 0; c.l0 = c.l1 = nullptr;
+    for (;;) {
+        if (run) {
 #ifdef ICX_PROFILE_PAIR
-    const long long t1 = clock64();
-    PROF_ADD(0, 1); PROF_ADD(1, (t1 - t0) >> 4);
+            const long long tq = clock64();
 #endif
-    // Advance the cursor(s).  One-sided pairs that follow need no partner: the warp runs them at once
-    // instead of spending a round on each (all lanes walk the cursor redundantly, lane 0 writes).
-    for (int side = 0; side < 2; side++) {
-        const uint32_t s = side ? item.w : item.z;
-        if (s == ICX_NONE) continue;
-        const Cursor c = load_cursor(W, s, W.dirty_list[s]);
-        uint32_t k, entry;
-        uint32_t hw = W.head[parity][s];
-        cursor_head(c, hw, k, entry);                                               // the entry just executed
-        hw = cursor_advance(hw, k);
-        for (;;) {
-            hw = skip_rejects_warp(W, c, hw, n_dirty);
-            if (!cursor_head(c, hw, k, entry)) break;
-            const uint32_t p = c.p0 + k, o = entry & ICX_NB_INDEX_MASK;
-            if (!(entry & ICX_NB_IMMUTABLE) && W.dirty_slot[W.pk_entity[o]] < n_dirty) break;     // two-sided: next round
-            PROF_ADD(4, 1);
-            process_pair(W, min(p, o), max(p, o), n_dirty, ctr_new);
+            process_pair(W, pa, pb, n_dirty, ctr_new, scratch);
             __syncwarp();
-            hw = cursor_advance(hw, k);
+#ifdef ICX_PROFILE_PAIR
+            t_pair += clock64() - tq;
+#endif
         }
-        if ((threadIdx.x & 31u) == 0u) {
-            W.head[parity ^ 1][s] = hw;
-            if (cursor_pending(c, hw)) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = s;
+        run = false;
+        for (; side < 2; side++) {
+            const uint32_t sb = side ? item.w : item.z;
+            if (sb == ICX_NONE) continue;
+            if (!entered) {                                                         // step over the entry just executed
+                uint4 info; info.x = __shfl_sync(FULL, my_info.x, side); info.y = __shfl_sync(FULL, my_info.y, side);
+                info.z = __shfl_sync(FULL, my_info.z, side); info.w = __shfl_sync(FULL, my_info.w, side);
+                c = make_cursor(W, sb, info);
+                hw = __shfl_sync(FULL, my_hw, side);
+                uint32_t k, entry, eo;
+                cursor_head(c, hw, k, entry, eo);
+                hw = cursor_advance(hw, k);
+                entered = true;
+            } else hw = cursor_advance(hw, k_run);                                  // a follow-up pair was executed
+            int kind; uint32_t kk, oo;
+            hw = skip_rejects_warp(W, c, hw, n_dirty, kind, kk, oo);
+            if (kind == 2) {                                                        // one-sided pair the filter keeps: run it now
+                PROF_ADD(4, 1);
+                const uint32_t p = c.p0 + kk;
+                k_run = kk; pa = min(p, oo); pb = max(p, oo); run = true;
+                break;
+            }
+            if (lane == 0u) {
+                W.head[parity ^ 1][sb] = hw;
+                if (cursor_pending(c, hw)) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = sb;
+            }
+            entered = false;
         }
+        if (!run) break;
     }
 #ifdef ICX_PROFILE_PAIR
-    PROF_ADD(2, (clock64() - t1) >> 4);
+    PROF_ADD(0, 1); PROF_ADD(1, t_pair >> 4); PROF_ADD(2, (clock64() - t0 - t_pair) >> 4);
 #endif
 }
 
@@ -729,8 +836,11 @@ __device__ __forceinline__ void trace_mark(const DeviceWorld& W, uint32_t& n, ui
 }
 
 #define RESOLVE_TPB 384
-__global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(DeviceWorld W, double dt, int do_euler)
+__global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(const __grid_constant__ DeviceWorld W, double dt, int do_euler)
 {
+    // per-warp scratch of the exact procedures (contact manifolds, clipping): see pseudo_clip_polyhedra_s
+    __shared__ V3 scratch_all[RESOLVE_TPB / 32][8 + 2 * ICX_MAXV];
+    V3* const scratch = scratch_all[threadIdx.x >> 5];
     uint32_t tn = 2;        // trace[0] = number of words used
     cg::grid_group grid = cg::this_grid();
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
@@ -756,9 +866,10 @@ __global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(DeviceWorld W, double d
                 const uint32_t n0 = W.nbr_count[sl * 2u], n1 = W.nbr_count[sl * 2u + 1u];
                 for (uint32_t i = tid & 31u; i < n0 + n1; i += 32u) {
                     const uint32_t k = i < n0 ? 0u : 1u;
-                    const uint32_t entry = W.nbr[(size_t)(sl * 2u + k) * W.max_neighbors + (k ? i - n0 : i)];
+                    const uint2 en = W.nbr[(size_t)(sl * 2u + k) * W.max_neighbors + (k ? i - n0 : i)];
+                    const uint32_t entry = en.x;
                     if (entry & ICX_NB_IMMUTABLE) continue;
-                    const uint32_t o = entry & ICX_NB_INDEX_MASK, eo = W.pk_entity[o];
+                    const uint32_t o = entry & ICX_NB_INDEX_MASK, eo = en.y;
                     if (W.dirty_slot[eo] != ICX_NONE) continue;
                     const uint32_t p = p0 + k;
                     const int tP = __float_as_uint(W.pk_lpos[p].w) & PF_TYPE_MASK, tO = __float_as_uint(W.pk_lpos[o].w) & PF_TYPE_MASK;
@@ -796,10 +907,10 @@ __global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(DeviceWorld W, double d
             __threadfence();
         }
         grid.sync();
-        // static pairs (contact records only), then every body's cursor to its first entry of interest
-        for (uint32_t i = tid >> 5; i < n_static; i += nth >> 5) { const uint2 pr = W.static_pairs[i]; process_pair(W, pr.x, pr.y, n_dirty, CTR_NEWD); }
+        // static pairs (contact records only) join the first round's work items; every body's cursor goes to its first entry of interest
+        for (uint32_t i = tid; i < n_static; i += nth) { const uint2 pr = W.static_pairs[i]; W.items[atomicAdd(&W.counters[CTR_ITEMS], 1u)] = make_uint4(pr.x, pr.y, ICX_NONE, ICX_NONE); }
         for (uint32_t s = tid >> 5; s < n_dirty; s += nth >> 5)
-            settle_warp(W, s, load_cursor(W, s, W.dirty_list[s]), 0u, n_dirty, 1, CTR_ACTIVE);     // writes head[0] / active[0]
+            settle_warp(W, s, load_cursor(W, s), 0u, n_dirty, 1, CTR_ACTIVE);     // writes head[0] / active[0]
         grid.sync();
         if (tid == 0) trace_mark(W, tn, 0x50000u);
         int parity = 0;
@@ -807,7 +918,7 @@ __global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(DeviceWorld W, double d
         for (;;) {
             const uint32_t n_act = ctr[CTR_ACTIVE + rounds % 3u];
             const uint32_t grew = rounds ? ctr[CTR_NEWD + (rounds + 2u) % 3u] : 0u;    // written in the previous round only
-            if (n_act == 0u || grew != 0u) break;       // done, or the dirty set grew: restart at once
+            if ((n_act == 0u && !(rounds == 0u && n_static)) || grew != 0u) break;       // done, or the dirty set grew: restart at once
             if (rounds >= ICX_MAX_ROUNDS) { if (tid == 0) atomicOr(W.flags, RF_ROUNDS_EXCEEDED); break; }
             const uint32_t ctr_out = CTR_ACTIVE + (rounds + 1u) % 3u, ctr_items = CTR_ITEMS + (rounds & 1u);
             if (tid == 0) { ctr[CTR_ACTIVE + (rounds + 2u) % 3u] = 0u; ctr[CTR_NEWD + (rounds + 1u) % 3u] = 0u; ctr[CTR_ITEMS + ((rounds + 1u) & 1u)] = 0u; }
@@ -815,7 +926,7 @@ __global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(DeviceWorld W, double d
             grid.sync();
             const uint32_t n_items = ctr[ctr_items];
             for (uint32_t i = tid >> 5; i < n_items; i += nth >> 5)
-                round_execute(W, W.items[i], n_dirty, parity, ctr_out, CTR_NEWD + rounds % 3u);
+                round_execute(W, W.items[i], n_dirty, parity, ctr_out, CTR_NEWD + rounds % 3u, scratch);
             grid.sync();
             if (tid == 0) trace_mark(W, tn, 0x30000u | min(n_items, 0xFFFFu));
             rounds++; parity ^= 1;

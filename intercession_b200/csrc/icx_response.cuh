@@ -42,7 +42,7 @@ ICX_DI float impulse_denominator(float invMassA, float invMassB, const M3& imA, 
 }
 
 // rigid_rigid_response, .cpp:636-874.  Mutates origin/vel/angvel of both sides and h.point.
-ICX_DN void rigid_rigid_response(Side& A, Side& B, Hit& h) {
+ICX_DI void rigid_rigid_response_i(Side& A, Side& B, Hit& h) {
     if (A.mass == 0 && B.mass == 0) return;                                         // :649
     float invMassA = 0, invMassB = 0;
     if (A.mass != 0) invMassA = 1.0f / A.mass;
@@ -79,7 +79,7 @@ ICX_DN void rigid_rigid_response(Side& A, Side& B, Hit& h) {
 }
 
 // spring_rigid_response, .cpp:876-1053 (A is the spring).  Mutates acc/angacc/vel/angvel and h.point.
-ICX_DN void spring_rigid_response(Side& A, Side& B, Hit& h) {
+ICX_DI void spring_rigid_response_i(Side& A, Side& B, Hit& h) {
     if (A.mass == 0 && B.mass == 0) return;
     float invMassA = 0, invMassB = 0;
     if (A.mass != 0) invMassA = 1.0f / A.mass;
@@ -114,5 +114,9 @@ ICX_DN void spring_rigid_response(Side& A, Side& B, Hit& h) {
     if (A.influenceOrientation) A.angvel = A.angvel * (1.0f - (A.colAngDrag * 2.0f));                         // :1044-1051
     if (B.influenceOrientation) B.angvel = B.angvel * (1.0f - (B.colAngDrag * 2.0f));
 }
+
+// out-of-line versions for the serial callers (speculative narrowphase, host checks)
+ICX_DN void rigid_rigid_response(Side& A, Side& B, Hit& h) { rigid_rigid_response_i(A, B, h); }
+ICX_DN void spring_rigid_response(Side& A, Side& B, Hit& h) { spring_rigid_response_i(A, B, h); }
 
 } // namespace icx

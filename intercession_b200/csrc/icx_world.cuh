@@ -108,8 +108,9 @@ struct DeviceWorld {
     // bodies touched by at least one hit ("dirty"): only these need the reference's sequential order
     uint32_t* dirty_slot;           // per entity: index into dirty_list, ICX_NONE = clean
     uint32_t* dirty_list;           // entity indices, arbitrary order
-    uint32_t* nbr;                  // sorted candidate lists of dirty bodies: nbr[(slot * 2 + k) * max_neighbors + i]
+    uint2* nbr;                     // sorted candidate lists of dirty bodies: nbr[(slot * 2 + k) * max_neighbors + i] = {other packet | flags, its entity}
     uint32_t* nbr_count;            // [slot * 2 + k]
+    uint4* slot_info;               // per dirty slot: {first packet | count << 30, n0, n1, entity}
     uint32_t max_neighbors;
     uint32_t* head[2];              // per dirty slot: consumed entries of the slot-0 list | slot-1 list << 16
     uint32_t* active[2];            // dirty-slot work lists of the dependency rounds

@@ -11,7 +11,9 @@ for k in range(2):
     cn = np.zeros(48, np.uint32); w.lib.icx_debug_counters(w.handle, cn.ctypes.data_as(ctypes.c_void_p)); pr = cn[32:]
     if pr[0]:
         print("  items", pr[0], "cycles/first pair", 16*pr[1]/pr[0], "cycles/chain", 16*pr[2]/pr[0], "| filter calls", pr[3], "follow-up pairs", pr[4],
-              "| load+SAT cycles per exact pair", 16*pr[5]/max(pr[0]+pr[4],1), "not separated", pr[6])
+              "| load+SAT cycles per exact pair", 16*pr[5]/max(pr[0]+pr[4],1), "not separated", pr[6],
+              "| hits", pr[8], "cycles to hit decided", 16*pr[7]/max(pr[8],1), "(box-box:", pr[12], 16*pr[11]/max(pr[12],1), ") response cycles", 16*pr[9]/max(pr[8],1),
+              "| rr response: first run", 16*pr[13]/max(pr[14],1), "second run", 16*pr[10]/max(pr[14],1), "n", pr[14])
     prev = 0
     for t, tag in w.trace(True):
         print(f"  {t/1e3:9.1f} us (+{(t-prev)/1e3:7.1f})  tag {tag>>16:x} arg {tag&0xffff}")
