@@ -244,6 +244,30 @@ ICX_API int icx_bodies_update(IcxWorld* w, uint32_t count, const uint32_t* index
                       const IcxPhysics* physics,
                       const IcxColliderComponent* colliders);
 
+/*
+ * ParallelCosmosContext::load_and_link (source/spacetime/parallel_cosmos_context.cpp:60-169):
+ * make `dst` a copy of `src` as the parallel cosmos sees it.  Every entity is copied with all its
+ * components except those with causal chain-link 0 and no future timestream (has_future[i] == 0;
+ * NULL = every entity has one, :110-116).  dst takes src's coherency (:91).  A FORKED entity stays
+ * forked in dst and is re-merged in src (:145-150); every other entity starts {merged, 0} in dst.
+ * The two worlds may live on different GPUs (peer copy).  dst keeps its own IcxConfig
+ * (host_timeslice = ICX_NULL_TIMESLICE for the parallel cosmos).  Linking the timestreams
+ * (:157) is the caller's icx_timeline_* handle sharing.
+ */
+ICX_API int icx_world_clone(IcxWorld* src, IcxWorld* dst, const uint8_t* has_future, uint32_t* n_cloned);
+
+/*
+ * ParallelCosmosContext::extract_entity_updates (:171-423, entity loop :206-272): write every
+ * temporal entity of the parallel world `par` back into `dst` under its id with the causal
+ * chain-link decremented (:212), all components (:252); the entity's timestream state follows if
+ * the decremented link is > 0 (:255) and is reset to merged when dst is timeslice 0 (:268-271).
+ * Skipped like the reference: non-temporal ids (link 15, :213) and ids created during the parallel
+ * run (timeslice 14, :223-229).  A link-0 id makes the reference throw (ecs_types.h:148):
+ * ICX_E_INVALID.  Ids absent from dst are counted in *n_missing and left to the host (the
+ * reference registers them, :241-245: entity lifecycle is host-side).
+ */
+ICX_API int icx_world_extract(IcxWorld* par, IcxWorld* dst, uint32_t* n_extracted, uint32_t* n_missing);
+
 /* Cosmos::get/set_coherency (cosmos.cpp:136-147) */
 ICX_API int icx_coherency_set(IcxWorld* w, uint16_t coherency);
 ICX_API int icx_coherency_get(IcxWorld* w, uint16_t* coherency);

@@ -163,6 +163,8 @@ SIGNATURES = {
     "icx_replay": (C.c_int, [_vp, _vp, C.c_uint16, C.c_int, C.POINTER(C.c_int)]),
     "icx_divergence_scan": (C.c_int, [_vp, _vp, C.c_uint16, _u32, _vp, _vp, _vp]),
     "icx_fork_age": (C.c_int, [_vp, C.POINTER(_u32), C.POINTER(C.c_int)]),
+    "icx_world_clone": (C.c_int, [_vp, _vp, _vp, C.POINTER(_u32)]),
+    "icx_world_extract": (C.c_int, [_vp, _vp, C.POINTER(_u32), C.POINTER(_u32)]),
     "icx_timeline_slot_info": (C.c_int, [_vp, C.c_uint16, C.POINTER(C.c_int), C.POINTER(_u32)]),
     "icx_debug_counters": (C.c_int, [_vp, _vp]),
     "icx_debug_trace": (C.c_int, [_vp, C.c_int, _vp, _sz, _psz]),

@@ -271,7 +271,8 @@ void icx_world_destroy(IcxWorld* w)
     cudaSetDevice(w->device);
     if (w->stream) cudaStreamSynchronize(w->stream);
     for (auto& b : w->pool) b.release();
-    DeviceBuffer* extra[] = {&w->mir_ids, &w->mir_T, &w->mir_P, &w->mir_C, &w->mir_hasP, &w->st_ts, &w->st_tc, &w->st_index, &w->st_T, &w->st_P, &w->st_C};
+    DeviceBuffer* extra[] = {&w->mir_ids, &w->mir_T, &w->mir_P, &w->mir_C, &w->mir_hasP, &w->st_ts, &w->st_tc, &w->st_index, &w->st_T, &w->st_P, &w->st_C,
+                             &w->cl_idx, &w->cl_ids, &w->cl_T, &w->cl_P, &w->cl_C, &w->cl_hasP, &w->cl_ts, &w->cl_tc};
     for (auto* b : extra) b->release();
     if (w->h_counters) cudaFreeHost(w->h_counters);
     if (w->h_flags) cudaFreeHost(w->h_flags);
@@ -295,6 +296,7 @@ int icx_bodies_upload(IcxWorld* w, uint32_t n, const IcxEntity* entity, const Ic
     // packet structure = ColliderSynchro::update's submission order (collider_synchro.cpp:28-42)
     std::vector<uint32_t> first(n);
     w->active_mask.assign(n, 0);
+    w->h_ids.assign(entity, entity + n);
     uint32_t np = 0;
     for (uint32_t i = 0; i < n; i++) {
         uint32_t cnt = 0;

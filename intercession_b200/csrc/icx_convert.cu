@@ -156,6 +156,56 @@ __global__ void __launch_bounds__(128) k_export(DeviceWorld W, Mirror M, int hav
     if (tc_out) tc_out[e] = (uint16_t)(ts >> 16);
 }
 
+// ---- ParallelCosmosContext::load_and_link / extract_entity_updates (a22) ------------------
+// Gather the AoS rows of the entities listed in idx (ascending source indices) into compact
+// staging arrays.  mode 0 = clone (parallel_cosmos_context.cpp:107-151): a FORKED source entity
+// carries its state over (stamped with the shared coherency) and is re-merged in the source
+// (:145-150); every other entity starts as {merged, 0} in the fresh cosmos.  mode 1 = extract
+// (:206-262): the state travels unchanged (the destination decides what to keep).
+__global__ void __launch_bounds__(128) k_gather_rows(DeviceWorld W, Mirror M, const uint32_t* __restrict__ idx, uint32_t count, int mode,
+                                                     uint32_t* o_ids, IcxTransform* o_T, IcxPhysics* o_P, IcxColliderComponent* o_C,
+                                                     uint8_t* o_hasP, uint8_t* o_ts, uint16_t* o_tc)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const uint32_t e = idx[i];
+    o_ids[i] = M.ids[e]; o_T[i] = M.T[e]; o_hasP[i] = M.hasP[e];
+    if (o_P) o_P[i] = M.P[e];
+    if (o_C) o_C[i] = M.C[e];
+    const uint32_t ts = W.in.ts[e], state = ts & 0xFFu;
+    if (mode == 0) {
+        if (state == ICX_TS_FORKED) {
+            o_ts[i] = ICX_TS_FORKED; o_tc[i] = W.coherency;
+            W.in.ts[e] = ICX_TS_MERGED | ((uint32_t)W.coherency << 16);             // set_timestream_state stamps the coherency, cosmos.cpp:162
+        } else { o_ts[i] = ICX_TS_MERGED; o_tc[i] = 0; }
+    } else { o_ts[i] = (uint8_t)state; o_tc[i] = (uint16_t)(ts >> 16); }
+}
+
+// extract, destination side (:255 and :268-271): entity index[i] takes the extracted state if its
+// chain-link is > 0; timeslice 0 re-merges every extracted entity.  Both stamp the coherency.
+__global__ void __launch_bounds__(128) k_extract_ts(DeviceWorld W, const uint32_t* __restrict__ index, const uint8_t* __restrict__ ts, uint32_t count)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const uint32_t e = index[i];
+    uint32_t cur = W.in.ts[e];
+    if ((W.entity_id[e] & 0xFu) > 0u) cur = (uint32_t)ts[i] | ((uint32_t)W.coherency << 16);
+    if (W.host_timeslice == 0u) cur = ICX_TS_MERGED | ((uint32_t)W.coherency << 16);
+    W.in.ts[e] = cur;
+}
+
+void launch_gather_rows(const DeviceWorld& W, Mirror M, const uint32_t* idx, uint32_t count, int mode, uint32_t* o_ids, IcxTransform* o_T,
+                        IcxPhysics* o_P, IcxColliderComponent* o_C, uint8_t* o_hasP, uint8_t* o_ts, uint16_t* o_tc, cudaStream_t st)
+{
+    if (!count) return;
+    k_gather_rows<<<(count + 127) / 128, 128, 0, st>>>(W, M, idx, count, mode, o_ids, o_T, o_P, o_C, o_hasP, o_ts, o_tc);
+}
+void launch_extract_ts(const DeviceWorld& W, const uint32_t* index, const uint8_t* ts, uint32_t count, cudaStream_t st)
+{
+    if (!count) return;
+    k_extract_ts<<<(count + 127) / 128, 128, 0, st>>>(W, index, ts, count);
+}
+
 void launch_import_kernel(const DeviceWorld& W, Mirror M, const uint32_t* index, const uint32_t* ids, const IcxTransform* T,
                           const IcxPhysics* P, const IcxColliderComponent* C, const uint8_t* hasP, const uint8_t* ts,
                           const uint16_t* tc, uint32_t count, int full, int have_C, cudaStream_t st)

@@ -21,6 +21,10 @@ void launch_import_kernel(const DeviceWorld& W, Mirror M, const uint32_t* index,
 void launch_export_kernel(const DeviceWorld& W, Mirror M, int have_T, int have_P, int have_C, uint8_t* ts, uint16_t* tc,
                           uint32_t n, cudaStream_t st);
 
+void launch_gather_rows(const DeviceWorld& W, Mirror M, const uint32_t* idx, uint32_t count, int mode, uint32_t* o_ids, IcxTransform* o_T,
+                        IcxPhysics* o_P, IcxColliderComponent* o_C, uint8_t* o_hasP, uint8_t* o_ts, uint16_t* o_tc, cudaStream_t st);
+void launch_extract_ts(const DeviceWorld& W, const uint32_t* index, const uint8_t* ts, uint32_t count, cudaStream_t st);
+
 struct DeviceBuffer {
     void* ptr = nullptr; size_t bytes = 0;
     cudaError_t ensure(size_t n) {
@@ -46,6 +50,8 @@ struct IcxWorld {
     uint32_t cap_entities = 0, cap_packets = 0;
     uint32_t n_entities = 0, n_packets = 0;
     std::vector<uint8_t> active_mask;   // per entity: bit s = collider slot s active (packet structure)
+    std::vector<uint32_t> h_ids;        // host copy of the entity ids (clone / extract bookkeeping)
+    icx::DeviceBuffer cl_idx, cl_ids, cl_T, cl_P, cl_C, cl_hasP, cl_ts, cl_tc;     // compact staging of clone / extract
     // staging (device) for AoS import/export, pinned host mirror for counters
     icx::DeviceBuffer mir_ids, mir_T, mir_P, mir_C, mir_hasP;       // device AoS mirror
     icx::DeviceBuffer st_ts, st_tc, st_index, st_T, st_P, st_C;      // staging for tstate and partial updates

@@ -167,6 +167,25 @@ class World:
         self._ck(self.lib.icx_fork_age(self.handle, C.byref(n), C.byref(need)))
         return n.value, bool(need.value)
 
+    # ---- ParallelCosmosContext::load_and_link / extract_entity_updates ----
+    def clone_into(self, dst, has_future=None):
+        """dst becomes the parallel-cosmos copy of this world; returns the number of entities copied."""
+        hf = None if has_future is None else np.ascontiguousarray(has_future, np.uint8)
+        n = C.c_uint32(0)
+        rc = self.lib.icx_world_clone(self.handle, dst.handle, abi.ptr(hf), C.byref(n))
+        if rc != abi.OK:
+            raise IcxError(rc, self.lib.icx_last_error(dst.handle).decode())
+        dst.n = n.value
+        return n.value
+
+    def extract_into(self, dst):
+        """Write this (parallel) world's temporal entities back into dst at chain-link - 1: (extracted, missing)."""
+        n, miss = C.c_uint32(0), C.c_uint32(0)
+        rc = self.lib.icx_world_extract(self.handle, dst.handle, C.byref(n), C.byref(miss))
+        if rc != abi.OK:
+            raise IcxError(rc, self.lib.icx_last_error(dst.handle).decode())
+        return n.value, miss.value
+
     def _ck_tl(self, tl, rc):
         if rc != abi.OK:
             raise IcxError(rc, (self.lib.icx_timeline_last_error(tl.handle) or self.lib.icx_last_error(self.handle)).decode())
