@@ -361,6 +361,16 @@ ICX_API int icx_divergence_scan(IcxWorld* w, IcxTimeline* tl, uint16_t coherency
  * *resolution_needed = some entity has been forked for >= 13 ticks (parallel_notify_divergence). */
 ICX_API int icx_fork_age(IcxWorld* w, uint32_t* n_promoted, int* resolution_needed);
 
+/* Snapshot transport between timeslices on different GPUs / processes (the future -> past ENTITY_UPDATE
+ * stream, server_network_dynamo.cpp:642-679): pack the slot stamped `coherency` into / restore it from a
+ * caller-owned DEVICE buffer of n * ICX_SNAPSHOT_BYTES bytes ([6][n] float4 state + [n] uint32 timestream
+ * word), e.g. the buffer a ncclSend / ncclRecv moves.  `stream` is a cudaStream_t (NULL = default stream);
+ * the copies are complete on return.  The recording world must be synchronised (icx_sync) before export. */
+#define ICX_SNAPSHOT_BYTES 100
+ICX_API int icx_timeline_slot_export(IcxTimeline* tl, uint16_t coherency, void* device_buffer, size_t capacity_bytes,
+                                     uint32_t* n_entities, void* stream);
+ICX_API int icx_timeline_slot_import(IcxTimeline* tl, uint16_t coherency, uint32_t n_entities, const void* device_buffer, void* stream);
+
 ICX_API int icx_timeline_slot_info(const IcxTimeline* tl, uint16_t coherency, int* valid, uint32_t* n_recorded);
 
 #ifdef __cplusplus

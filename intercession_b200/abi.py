@@ -56,6 +56,7 @@ F_SPHERE_SPHERE, F_NO_GRAVITY = 1, 2
 CONTACT_RESPONDED, CONTACT_BEHAVIORS_A, CONTACT_BEHAVIORS_B = 1, 2, 4
 OK, E_INVALID, E_CUDA, E_CAPACITY, E_NOMEM, E_STATE = 0, 1, 2, 3, 4, 5
 REPLAY_SERVER, REPLAY_PARALLEL = 0, 1
+SNAPSHOT_BYTES = 100
 
 
 def compose_entity(timeslice, genesis, link):
@@ -163,6 +164,8 @@ SIGNATURES = {
     "icx_replay": (C.c_int, [_vp, _vp, C.c_uint16, C.c_int, C.POINTER(C.c_int)]),
     "icx_divergence_scan": (C.c_int, [_vp, _vp, C.c_uint16, _u32, _vp, _vp, _vp]),
     "icx_fork_age": (C.c_int, [_vp, C.POINTER(_u32), C.POINTER(C.c_int)]),
+    "icx_timeline_slot_export": (C.c_int, [_vp, C.c_uint16, _vp, _sz, C.POINTER(_u32), _vp]),
+    "icx_timeline_slot_import": (C.c_int, [_vp, C.c_uint16, _u32, _vp, _vp]),
     "icx_world_clone": (C.c_int, [_vp, _vp, _vp, C.POINTER(_u32)]),
     "icx_world_extract": (C.c_int, [_vp, _vp, C.POINTER(_u32), C.POINTER(_u32)]),
     "icx_timeline_slot_info": (C.c_int, [_vp, C.c_uint16, C.POINTER(C.c_int), C.POINTER(_u32)]),

@@ -357,6 +357,48 @@ int icx_fork_age(IcxWorld* w, uint32_t* n_promoted, int* resolution_needed)
     return ICX_OK;
 }
 
+// The snapshot stream between adjacent timeslices (future -> past, server_network_dynamo.cpp:642-679
+// push_past_timestream) when the two timeslices live on different GPUs / processes: the slot stamped
+// `coherency` packed as [6][n] float4 + [n] uint32 = 100 B per entity in a caller-owned DEVICE buffer
+// (what a ncclSend / cudaMemcpyPeer moves), and its inverse on the receiving side, which lands in
+// the ring exactly like icx_record (push_back).  Copies run on `stream` (cudaStream_t, NULL = the
+// default stream) and are complete on return.
+int icx_timeline_slot_export(IcxTimeline* tl, uint16_t coherency, void* device_buffer, size_t capacity_bytes, uint32_t* n_out, void* stream)
+{
+    if (!tl || !device_buffer) return ICX_E_INVALID;
+    const int s = slot_of(tl, coherency);
+    if (!(tl->valid[s] && tl->stamp[s] == coherency)) { tl->error = "slot_export: no record with this coherency"; return ICX_E_STATE; }
+    const uint32_t n = tl->count[s];
+    if (n_out) *n_out = n;
+    if ((size_t)n * ICX_SNAPSHOT_BYTES > capacity_bytes) { tl->error = "slot_export: buffer too small"; return ICX_E_CAPACITY; }
+    if (!n) return ICX_OK;
+    cudaSetDevice(tl->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    TCK(cudaMemcpy2DAsync(device_buffer, (size_t)n * 16, tl->state + (size_t)s * 6 * tl->n_max, (size_t)tl->n_max * 16, (size_t)n * 16, 6,
+                          cudaMemcpyDeviceToDevice, st));
+    TCK(cudaMemcpyAsync((char*)device_buffer + (size_t)n * 96, tl->ts + (size_t)s * tl->n_max, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+    TCK(cudaStreamSynchronize(st));
+    return ICX_OK;
+}
+
+int icx_timeline_slot_import(IcxTimeline* tl, uint16_t coherency, uint32_t n, const void* device_buffer, void* stream)
+{
+    if (!tl || (!device_buffer && n)) return ICX_E_INVALID;
+    if (n > tl->n_max) { tl->error = "slot_import: more entities than the timeline holds"; return ICX_E_CAPACITY; }
+    const int s = slot_of(tl, coherency);
+    cudaSetDevice(tl->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n) {
+        TCK(cudaMemcpy2DAsync(tl->state + (size_t)s * 6 * tl->n_max, (size_t)tl->n_max * 16, device_buffer, (size_t)n * 16, (size_t)n * 16, 6,
+                              cudaMemcpyDeviceToDevice, st));
+        TCK(cudaMemcpyAsync(tl->ts + (size_t)s * tl->n_max, (const char*)device_buffer + (size_t)n * 96, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+        TCK(cudaStreamSynchronize(st));
+    }
+    tl->stamp[s] = coherency; tl->valid[s] = 1; tl->count[s] = n;
+    tl->behind[s] = tl->breakpoint_active ? 1 : 0;
+    return ICX_OK;
+}
+
 int icx_timeline_slot_info(const IcxTimeline* tl, uint16_t coherency, int* valid, uint32_t* n_recorded)
 {
     if (!tl) return ICX_E_INVALID;

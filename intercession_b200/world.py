@@ -207,6 +207,19 @@ class Timeline:
     def clear_breakpoint(self):
         self.lib.icx_breakpoint_clear(self.handle)
 
+    def export_slot(self, coherency, dev_ptr, capacity_bytes, stream=None):
+        """Pack the slot stamped `coherency` into the device buffer at dev_ptr (int); returns the entity count."""
+        n = C.c_uint32(0)
+        rc = self.lib.icx_timeline_slot_export(self.handle, coherency, C.c_void_p(dev_ptr), capacity_bytes, C.byref(n), C.c_void_p(stream or 0))
+        if rc != abi.OK:
+            raise IcxError(rc, self.lib.icx_timeline_last_error(self.handle).decode())
+        return n.value
+
+    def import_slot(self, coherency, n, dev_ptr, stream=None):
+        rc = self.lib.icx_timeline_slot_import(self.handle, coherency, n, C.c_void_p(dev_ptr), C.c_void_p(stream or 0))
+        if rc != abi.OK:
+            raise IcxError(rc, self.lib.icx_timeline_last_error(self.handle).decode())
+
     def slot_info(self, coherency):
         v, n = C.c_int(0), C.c_uint32(0)
         self.lib.icx_timeline_slot_info(self.handle, coherency, C.byref(v), C.byref(n))
