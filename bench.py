@@ -187,6 +187,58 @@ def worldline_batch_bench(n_worldlines, per, ticks, rank, world_size, local_rank
             "algorithmic_bytes_per_body_tick": {"record": 200, "scan": 26}}
 
 
+def timeslice_pipeline_bench(bodies, ticks, delay, rank, world_size, local_rank, barrier):
+    """BASELINE.json configs[4] (reduced: no time travellers, no parallel cosmos): one timeslice per rank, each
+    `delay` ticks behind its future neighbour; per wall tick and link ONE snapshot of 100 B per entity travels
+    future -> past (ncclSend / ncclRecv over NVLink between ranks; a device copy when world_size == 1, where two
+    timeslices share the GPU so that the path is exercised).  Per tick and timeslice: record + export, import,
+    replay of the record that came due, fork ageing, physics tick."""
+    import torch
+    import torch.distributed as dist
+    from intercession_b200 import abi, pipeline, scenes
+    n_ts = world_size if world_size > 1 else 2
+    base = scenes.arena(bodies, seed=20261107, kinds=("sphere", "box"), temporal=True)
+    mine = [rank] if world_size > 1 else list(range(n_ts))
+    slices = []
+    for k in mine:
+        sc = base.copy()
+        sc["ids"] = pipeline.past_ids(base.ids, k)
+        slices.append(pipeline.Timeslice(sc, k, n_ts, delay, device=local_rank))
+    warm = delay + 2
+    if world_size > 1:
+        pipeline.run_distributed(slices[0], warm, rank, n_ts, local_rank)
+    else:
+        links = [pipeline.LoopbackLink(base.n, local_rank) for _ in range(n_ts - 1)]
+        pipeline.run_local(slices, warm, links)
+    barrier()
+    t0 = time.perf_counter()
+    if world_size > 1:
+        sent = pipeline.run_distributed(slices[0], ticks, rank, n_ts, local_rank)
+    else:
+        pipeline.run_local(slices, ticks, links)
+        sent = (n_ts - 1) * ticks * base.n * abi.SNAPSHOT_BYTES
+    barrier()
+    sec = time.perf_counter() - t0
+    sec_t = torch.tensor([sec], dtype=torch.float64, device="cuda")
+    sent_t = torch.tensor([float(sent)], dtype=torch.float64, device="cuda")
+    rep_t = torch.tensor([float(min(ts.replayed for ts in slices if ts.rank > 0) if any(ts.rank > 0 for ts in slices) else 1e9)],
+                         dtype=torch.float64, device="cuda")
+    if world_size > 1:
+        dist.all_reduce(sec_t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(sent_t, op=dist.ReduceOp.SUM)
+        dist.all_reduce(rep_t, op=dist.ReduceOp.MIN)
+    sec = float(sec_t.item())
+    for ts in slices:
+        ts.close()
+    return {"workload": f"config5 (reduced): {n_ts} timeslices x {bodies} temporal bodies + 6 walls, delay {delay} ticks, {ticks} wall ticks; "
+                        f"no time travellers / parallel cosmos",
+            "n_timeslices": n_ts, "timeslices_per_gpu": len(mine), "ticks": ticks, "seconds": round(sec, 4),
+            "wall_ticks_per_s": ticks / sec, "collider_steps_per_s": n_ts * base.n * ticks / sec,
+            "snapshot_bytes_per_link_tick": base.n * abi.SNAPSHOT_BYTES, "snapshot_bytes_moved": int(sent_t.item()),
+            "transport": "ncclSend/ncclRecv (batch_isend_irecv)" if world_size > 1 else "device copy (one process, one GPU)",
+            "records_replayed_min": int(rep_t.item())}
+
+
 def run_reference_arm(a, rank, world_size):
     if rank != 0:
         return
@@ -224,6 +276,9 @@ def main():
     ap.add_argument("--worldlines", type=int, default=4096, help="config-4 world-line candidates (0 = skip that section)")
     ap.add_argument("--worldline-bodies", type=int, default=1024)
     ap.add_argument("--worldline-ticks", type=int, default=8)
+    ap.add_argument("--pipeline-bodies", type=int, default=100000, help="config-5 bodies per timeslice (0 = skip that section)")
+    ap.add_argument("--pipeline-ticks", type=int, default=12)
+    ap.add_argument("--pipeline-delay", type=int, default=5)
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3) if a.impl == "ours" else a.warmup
 
@@ -326,6 +381,10 @@ def main():
     if a.worldlines > 0:
         wlb = worldline_batch_bench(a.worldlines, a.worldline_bodies, a.worldline_ticks, rank, world_size, local_rank, barrier)
 
+    tsp = None
+    if a.pipeline_bodies > 0:
+        tsp = timeslice_pipeline_bench(a.pipeline_bodies, a.pipeline_ticks, a.pipeline_delay, rank, world_size, local_rank, barrier)
+
     cpu = None
     if rank == 0 and not a.no_cpu:
         cores = os.cpu_count() or 1
@@ -352,6 +411,7 @@ def main():
                 "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
                 "gpu_launches": int(launches1 - launches0),
                 "worldline_batch": wlb,
+                "timeslice_pipeline": tsp,
                 "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if world_size > 1:
