@@ -903,7 +903,7 @@ __global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(const __grid_constant__
             ctr[CTR_LISTED] = n_dirty; ctr[CTR_CONTACTS] = 0; ctr[CTR_INTERCEPTS] = 0;
             ctr[CTR_NEWD] = 0; ctr[CTR_NEWD + 1] = 0; ctr[CTR_NEWD + 2] = 0;
             ctr[CTR_ACTIVE] = 0; ctr[CTR_ACTIVE + 1] = 0; ctr[CTR_ACTIVE + 2] = 0;
-            ctr[CTR_ITEMS] = 0; ctr[CTR_ITEMS + 1] = 0;
+            ctr[CTR_ITEMS] = 0; ctr[CTR_ITEMS + 1] = 0; ctr[CTR_FETCH] = 0; ctr[CTR_FETCH + 1] = 0;
             __threadfence();
         }
         grid.sync();
@@ -921,12 +921,19 @@ __global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(const __grid_constant__
             if ((n_act == 0u && !(rounds == 0u && n_static)) || grew != 0u) break;       // done, or the dirty set grew: restart at once
             if (rounds >= ICX_MAX_ROUNDS) { if (tid == 0) atomicOr(W.flags, RF_ROUNDS_EXCEEDED); break; }
             const uint32_t ctr_out = CTR_ACTIVE + (rounds + 1u) % 3u, ctr_items = CTR_ITEMS + (rounds & 1u);
-            if (tid == 0) { ctr[CTR_ACTIVE + (rounds + 2u) % 3u] = 0u; ctr[CTR_NEWD + (rounds + 1u) % 3u] = 0u; ctr[CTR_ITEMS + ((rounds + 1u) & 1u)] = 0u; }
+            if (tid == 0) { ctr[CTR_ACTIVE + (rounds + 2u) % 3u] = 0u; ctr[CTR_NEWD + (rounds + 1u) % 3u] = 0u; ctr[CTR_ITEMS + ((rounds + 1u) & 1u)] = 0u;
+                            ctr[CTR_FETCH + ((rounds + 1u) & 1u)] = 0u; }
             for (uint32_t i = tid; i < n_act; i += nth) round_select(W, W.active[parity][i], n_dirty, parity, ctr_out, ctr_items);
             grid.sync();
             const uint32_t n_items = ctr[ctr_items];
-            for (uint32_t i = tid >> 5; i < n_items; i += nth >> 5)
+            // items differ 3x in cost (filter miss ... box-box hit with clipping): warps fetch them one by one
+            for (;;) {
+                uint32_t i = 0;
+                if ((tid & 31u) == 0u) i = atomicAdd(&W.counters[CTR_FETCH + (rounds & 1u)], 1u);
+                i = __shfl_sync(0xFFFFFFFFu, i, 0);
+                if (i >= n_items) break;
                 round_execute(W, W.items[i], n_dirty, parity, ctr_out, CTR_NEWD + rounds % 3u, scratch);
+            }
             grid.sync();
             if (tid == 0) trace_mark(W, tn, 0x30000u | min(n_items, 0xFFFFu));
             rounds++; parity ^= 1;

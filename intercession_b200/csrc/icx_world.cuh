@@ -136,6 +136,7 @@ enum { CTR_LARGE = 0, CTR_DIRTY = 1, CTR_CONTACTS = 2, CTR_INTERCEPTS = 3, CTR_C
        CTR_ACTIVE = 13,         // 3 rotating work-list counters: CTR_ACTIVE + (round % 3)
        CTR_ITEMS = 18,          // 2 alternating work-item counters
        CTR_NEWD = 20,           // 3 rotating per-round counts of bodies that turned dirty during the replay
+       CTR_FETCH = 23,          // 2 alternating work-item fetch counters
        CTR_PROF = 32,           // ICX_PROFILE_PAIR builds: cycle accumulators
        CTR_TOTAL = 48 };
 #define ICX_MAX_ROUNDS 65535u
