@@ -57,6 +57,25 @@ public:
         ck(icx_divergence_scan(cosmos.world(), m_tl, coherency, 1, &flag, incongruent, score));
         return flag == 0;
     }
+    // ParallelCosmosContext::load_and_link (parallel_cosmos_context.cpp:60-169): `parallel` becomes the copy of
+    // `source` the parallel cosmos simulates (entities with chain-link 0 and no future timestream are left out,
+    // forked entities carry their state and are re-merged in the source); returns the number of entities copied.
+    // The caller links the timestreams afterwards (link_timestreams), as the reference does (:157).
+    static uint32_t parallel_load_and_link(PhysicsDynamo& source, PhysicsDynamo& parallel, const uint8_t* has_future = nullptr)
+    {
+        uint32_t n = 0;
+        check(icx_world_clone(source.world(), parallel.world(), has_future, &n), parallel.world(), "icx_world_clone");
+        return n;
+    }
+    // ParallelCosmosContext::extract_entity_updates (:171-423): every temporal entity of `parallel` overwrites the
+    // entity of `destination` whose id has the chain-link decremented; *missing = ids the destination has to
+    // register first (:241-245).  Returns the number of entities written.
+    static uint32_t parallel_extract(PhysicsDynamo& parallel, PhysicsDynamo& destination, uint32_t* missing = nullptr)
+    {
+        uint32_t n = 0;
+        check(icx_world_extract(parallel.world(), destination.world(), &n, missing), destination.world(), "icx_world_extract");
+        return n;
+    }
     IcxTimeline* timeline() { return m_tl; }
 
 private:
