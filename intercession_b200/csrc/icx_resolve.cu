@@ -171,24 +171,8 @@ __device__ __forceinline__ bool is_sat_pair(int tA, int tB) {
     return (tA == ICX_COLLIDER_BOX && (tB == ICX_COLLIDER_BOX || tB == ICX_COLLIDER_SPHERE)) || (tA == ICX_COLLIDER_SPHERE && tB == ICX_COLLIDER_BOX);
 }
 // current-state filter for packets pa, pb: false = the exact procedure cannot report a hit
-// One copy (the unrolled 15-axis filter is ~18 KB of code).  The entities are passed in so that every
-// load is independent of the others: one memory round trip instead of three.
-static __device__ __noinline__ bool may_hit(const float4* __restrict__ pk_lpos, const float4* __restrict__ pk_d, const float4* __restrict__ pos,
-                                            uint32_t pa, uint32_t pb, uint32_t ea, uint32_t eb, float slack)
-{
-    const float wA = pk_lpos[pa].w, wB = pk_lpos[pb].w;
-    const float4 posA = pos[ea], posB = pos[eb];
-    const int tA = __float_as_uint(wA) & PF_TYPE_MASK, tB = __float_as_uint(wB) & PF_TYPE_MASK;
-    if (!is_sat_pair(tA, tB)) return true;
-    return sat_may_hit(pk_d + (size_t)pa * 6, pk_d + (size_t)pb * 6, v3(posA), v3(posB), tA, tB, slack);
-}
-// packets p (entity e) and o (entity eo) in either order
-__device__ __forceinline__ bool may_hit_po(const DeviceWorld& W, uint32_t p, uint32_t e, uint32_t o, uint32_t eo) {
-    return p < o ? may_hit(W.pk_lpos, W.pk_d, W.out.pos, p, o, e, eo, 0.0f) : may_hit(W.pk_lpos, W.pk_d, W.out.pos, o, p, eo, e, 0.0f);
-}
-
-// The same filter by a whole warp for ONE pair (uniform arguments): lane a evaluates axis a, so the
-// verdict costs one axis of latency instead of fifteen.  Same arithmetic per axis as sat_may_hit.
+// The current-state filter (sat_may_hit) by a whole warp for ONE pair (uniform arguments): lane a evaluates
+// axis a, so the verdict costs one axis of latency instead of fifteen.  Same arithmetic per axis.
 __device__ __forceinline__ bool may_hit_warp(const DeviceWorld& W, uint32_t pa, uint32_t pb, uint32_t ea, uint32_t eb)
 {
     const uint32_t FULL = 0xFFFFFFFFu, lane = threadIdx.x & 31u;
@@ -752,8 +736,9 @@ __device__ __forceinline__ void round_select(const DeviceWorld& W, uint32_t s, u
         return;
     }
     if (p > o) return;                                                              // the lower packet's lane acts for both
-    // a certain miss is consumed on both sides without the exact procedure; the cursor walk that follows is a warp's job either way
-    W.items[atomicAdd(&W.counters[ctr_items], 1u)] = make_uint4(p, may_hit(W.pk_lpos, W.pk_d, W.out.pos, p, o, c.e, eo, 0.0f) ? o : (o | ICX_ITEM_MISS), s, so);
+    // the SAT filter is the executing warp's job (one axis per lane instead of fifteen in a row on this lane):
+    // a pair it rejects is consumed on both sides without the exact procedure
+    W.items[atomicAdd(&W.counters[ctr_items], 1u)] = make_uint4(p, o | ICX_ITEM_CHECK, s, so);
 }
 
 // One work item, by a whole warp: the exact pair (unless the filter already rejected it), then the
@@ -772,8 +757,9 @@ __device__ __forceinline__ void round_execute(const DeviceWorld& W, uint4 item, 
     uint4 my_info = make_uint4(0u, 0u, 0u, 0u); uint32_t my_hw = 0u;
     if (my_s != ICX_NONE) { my_info = W.slot_info[my_s]; my_hw = W.head[parity][my_s]; }
 
-    uint32_t pa = item.x, pb = item.y & ~ICX_ITEM_MISS;
-    bool run = !(item.y & ICX_ITEM_MISS);
+    uint32_t pa = item.x, pb = item.y & ICX_NB_INDEX_MASK;
+    bool run = true;
+    if (item.y & ICX_ITEM_CHECK) run = may_hit_warp(W, pa, pb, W.pk_entity[pa], W.pk_entity[pb]);
     int side = 0; bool entered = false;                                             // body being walked; its cursor is loaded
     Cursor c; uint32_t hw = 0, k_run = 0;
     c.p0 = c.npk = c.n0 = c.n1 = c.e = 0; c.l0 = c.l1 = nullptr;

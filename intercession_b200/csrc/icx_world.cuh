@@ -36,7 +36,7 @@ enum : uint32_t {
 #define ICX_PAIR_TIGHT    0x80000000u     // un-inflated bounds overlap too: the narrowphase can hit
 #define ICX_PAIR_STATIC   0x40000000u     // both bodies immutable
 #define ICX_NONE          0xFFFFFFFFu
-#define ICX_ITEM_MISS     0x80000000u     // work item (uint4.y): the filter rejected the pair, only the cursors advance
+#define ICX_ITEM_CHECK    0x80000000u     // work item (uint4.y): two-sided pair, the SAT filter has not seen it yet
 // grid: 2^ICX_XB x-adjacent cells of one (y,z,world-line) row share a hashed block of buckets, so
 // the 3 x-neighbours of a cell are one contiguous range of the bucket-sorted array
 #define ICX_XB 4
