@@ -386,7 +386,7 @@ def main():
         tsp = timeslice_pipeline_bench(a.pipeline_bodies, a.pipeline_ticks, a.pipeline_delay, rank, world_size, local_rank, barrier)
 
     cpu = None
-    if rank == 0 and not a.no_cpu:
+    if rank == 0 and world_size == 1 and not a.no_cpu:          # reported at N = 1 only (the reference arm covers every N)
         cores = os.cpu_count() or 1
         threads = max(1, min(cores, 32))
         n_sample = min(a.bodies, 32768)

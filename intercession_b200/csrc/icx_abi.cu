@@ -196,6 +196,19 @@ int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_
 
 } // namespace
 
+int icx_host_masks(IcxWorld* w)
+{
+    if (w->masks_on_host) return ICX_OK;
+    w->active_mask.assign(w->n_entities, 0);
+    if (w->n_entities) {
+        cudaSetDevice(w->device);
+        CK(cudaMemcpyAsync(w->active_mask.data(), w->d_mask.ptr, w->n_entities, cudaMemcpyDeviceToHost, w->stream));
+        CK(cudaStreamSynchronize(w->stream));
+    }
+    w->masks_on_host = true;
+    return ICX_OK;
+}
+
 extern "C" {
 
 int icx_abi_version(void) { return ICX_ABI_VERSION; }
@@ -232,7 +245,7 @@ void icx_config_default(IcxConfig* cfg)
 
 int icx_world_create(const IcxConfig* cfg, IcxWorld** out)
 {
-    if (!cfg || !out || cfg->struct_size != sizeof(IcxConfig) || cfg->max_entities == 0 || cfg->max_entities > (1u << 27))
+    if (!cfg || !out || cfg->struct_size != sizeof(IcxConfig) || cfg->max_entities == 0 || cfg->max_entities > (1u << 24))      /* device scans are two-level: 4096 x 4096 */
         return ICX_E_INVALID;
     *out = nullptr;
     if (icx_device_count() <= cfg->device) return ICX_E_CUDA;      // no CPU fallback
@@ -272,7 +285,7 @@ void icx_world_destroy(IcxWorld* w)
     if (w->stream) cudaStreamSynchronize(w->stream);
     for (auto& b : w->pool) b.release();
     DeviceBuffer* extra[] = {&w->mir_ids, &w->mir_T, &w->mir_P, &w->mir_C, &w->mir_hasP, &w->st_ts, &w->st_tc, &w->st_index, &w->st_T, &w->st_P, &w->st_C,
-                             &w->cl_idx, &w->cl_ids, &w->cl_T, &w->cl_P, &w->cl_C, &w->cl_hasP, &w->cl_ts, &w->cl_tc};
+                             &w->d_mask, &w->st_scan, &w->cl_idx, &w->cl_ids, &w->cl_T, &w->cl_P, &w->cl_C, &w->cl_hasP, &w->cl_ts, &w->cl_tc};
     for (auto* b : extra) b->release();
     if (w->h_counters) cudaFreeHost(w->h_counters);
     if (w->h_flags) cudaFreeHost(w->h_flags);
@@ -293,18 +306,9 @@ int icx_bodies_upload(IcxWorld* w, uint32_t n, const IcxEntity* entity, const Ic
     cudaSetDevice(w->device);
     DeviceWorld& W = w->W;
     cudaStream_t st = w->stream;
-    // packet structure = ColliderSynchro::update's submission order (collider_synchro.cpp:28-42)
-    std::vector<uint32_t> first(n);
-    w->active_mask.assign(n, 0);
     w->h_ids.assign(entity, entity + n);
-    uint32_t np = 0;
-    for (uint32_t i = 0; i < n; i++) {
-        uint32_t cnt = 0;
-        if (C) for (int s = 0; s < ICX_COLLIDERS_PER_ENTITY; s++) if (C[i].colliders[s].isActive) { cnt++; w->active_mask[i] |= (uint8_t)(1u << s); }
-        first[i] = np | (cnt << 30);
-        np += cnt;
-    }
-    if (np > w->cap_packets || np >= (1u << 28)) return fail(w, ICX_E_CAPACITY, "upload: too many active colliders");
+    w->masks_on_host = false;
+    CK(w->d_mask.ensure(w->cap_entities)); CK(w->st_scan.ensure(((size_t)w->cap_entities + 4) * 4));
     CK(w->mir_ids.ensure((size_t)w->cap_entities * 4)); CK(w->mir_T.ensure((size_t)w->cap_entities * sizeof(IcxTransform)));
     CK(w->mir_hasP.ensure(w->cap_entities));
     if (P) CK(w->mir_P.ensure((size_t)w->cap_entities * sizeof(IcxPhysics)));
@@ -318,17 +322,23 @@ int icx_bodies_upload(IcxWorld* w, uint32_t n, const IcxEntity* entity, const Ic
     if (has_physics) CK(cudaMemcpyAsync(w->mir_hasP.ptr, has_physics, n, cudaMemcpyHostToDevice, st));
     if (tstate) CK(cudaMemcpyAsync(w->st_ts.ptr, tstate, n, cudaMemcpyHostToDevice, st));
     if (tcoh) CK(cudaMemcpyAsync(w->st_tc.ptr, tcoh, (size_t)n * 2, cudaMemcpyHostToDevice, st));
-    CK(cudaMemcpyAsync(W.first_packet, first.data(), (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    // packet structure (one packet per active collider, submission order) on the device, from the uploaded components
+    launch_packet_structure(C ? (const IcxColliderComponent*)w->mir_C.ptr : nullptr, n, (uint32_t*)w->st_scan.ptr, W.scan_partial,
+                            (uint8_t*)w->d_mask.ptr, W.first_packet, st);
     CK(cudaMemsetAsync(W.counters, 0, CTR_TOTAL * sizeof(uint32_t), st));
-    W.n_entities = n; W.n_packets = np; w->n_entities = n; w->n_packets = np;
+    W.n_entities = n; w->n_entities = n;
     Mirror M = mirror_of(w);
     if (!P) M.P = nullptr;
     launch_import_kernel(W, M, nullptr, M.ids, M.T, M.P, C ? M.C : nullptr,
                          has_physics ? M.hasP : nullptr, tstate ? (const uint8_t*)w->st_ts.ptr : nullptr,
                          tcoh ? (const uint16_t*)w->st_tc.ptr : nullptr, n, 1, C ? 1 : 0, st);
     CK(cudaMemcpyAsync(w->h_counters, W.counters, CTR_TOTAL * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));          // `first` and the caller's arrays may be released after return
+    CK(cudaMemcpyAsync(w->h_flags + 1, (uint32_t*)w->st_scan.ptr + n, 4, cudaMemcpyDeviceToHost, st));      // packet count
+    CK(cudaStreamSynchronize(st));          // the caller's arrays may be released after return
     CK(cudaGetLastError());
+    const uint32_t np = w->h_flags[1];
+    W.n_packets = np; w->n_packets = np;
+    if (np > w->cap_packets || np >= (1u << 28)) { W.n_entities = 0; W.n_packets = 0; w->n_entities = 0; w->n_packets = 0; return fail(w, ICX_E_CAPACITY, "upload: too many active colliders"); }
     if (!(w->cfg.cell_size > 0)) {
         float ext; std::memcpy(&ext, &w->h_counters[CTR_EXTENT], 4);
         if (!(ext > 0)) ext = 1.0f;
@@ -364,6 +374,7 @@ int icx_bodies_update(IcxWorld* w, uint32_t count, const uint32_t* index, const 
     if (!index && count) return fail(w, ICX_E_INVALID, "update: null index");
     if ((P && !w->have_P) || (C && !w->have_C)) return fail(w, ICX_E_STATE, "update: component was never uploaded");
     if (!count) return ICX_OK;
+    if (C) { int mrc = icx_host_masks(w); if (mrc != ICX_OK) return mrc; }
     for (uint32_t i = 0; i < count; i++) {
         if (index[i] >= w->n_entities) return fail(w, ICX_E_INVALID, "update: index out of range");
         if (C) {

@@ -70,6 +70,7 @@ int icx_world_clone(IcxWorld* src, IcxWorld* dst, const uint8_t* has_future, uin
     for (uint32_t i = 0; i < n; i++)
         if (!(has_future && !has_future[i] && (src->h_ids[i] & 0xFu) == 0u)) idx.push_back(i);
     const uint32_t nk = (uint32_t)idx.size();
+    { int mrc = icx_host_masks(src); if (mrc != ICX_OK) { dst->error = src->error; return mrc; } }
     if (nk > dst->cap_entities) return cfail(dst, ICX_E_CAPACITY, "clone: destination max_entities too small");
     std::vector<uint32_t> first(nk);
     dst->active_mask.resize(nk); dst->h_ids.resize(nk);
@@ -101,6 +102,9 @@ int icx_world_clone(IcxWorld* src, IcxWorld* dst, const uint8_t* has_future, uin
     CKW(dst, xcopy(dst, dst->st_ts.ptr, src, src->cl_ts.ptr, nk));
     CKW(dst, xcopy(dst, dst->st_tc.ptr, src, src->cl_tc.ptr, (size_t)nk * 2));
     if (nk) CKW(dst, cudaMemcpyAsync(W.first_packet, first.data(), (size_t)nk * 4, cudaMemcpyHostToDevice, st));
+    CKW(dst, dst->d_mask.ensure(cap));
+    if (nk) CKW(dst, cudaMemcpyAsync(dst->d_mask.ptr, dst->active_mask.data(), nk, cudaMemcpyHostToDevice, st));
+    dst->masks_on_host = true;
     CKW(dst, cudaMemsetAsync(W.counters, 0, CTR_TOTAL * sizeof(uint32_t), st));
     W.n_entities = nk; W.n_packets = np; dst->n_entities = nk; dst->n_packets = np;
     W.coherency = src->W.coherency;                                                 // :91 set_coherency(source)
@@ -129,6 +133,7 @@ int icx_world_extract(IcxWorld* par, IcxWorld* dst, uint32_t* n_extracted, uint3
     if (n_missing) *n_missing = 0;
     if (par->have_C && !dst->have_C) return cfail(dst, ICX_E_STATE, "extract: destination has no collider components");
     if (par->have_P && !dst->have_P) return cfail(dst, ICX_E_STATE, "extract: destination has no physics components");
+    { int mrc = icx_host_masks(par); if (mrc == ICX_OK) mrc = icx_host_masks(dst); if (mrc != ICX_OK) return cfail(dst, mrc, "extract: cannot read the collider activation masks"); }
     std::unordered_map<uint32_t, uint32_t> where;
     where.reserve(dst->h_ids.size() * 2);
     for (uint32_t j = 0; j < dst->n_entities; j++) where.emplace(dst->h_ids[j], j);

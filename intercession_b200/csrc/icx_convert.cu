@@ -156,6 +156,35 @@ __global__ void __launch_bounds__(128) k_export(DeviceWorld W, Mirror M, int hav
     if (tc_out) tc_out[e] = (uint16_t)(ts >> 16);
 }
 
+// ---- packet structure = ColliderSynchro::update's submission order (collider_synchro.cpp:28-42) ----
+// One packet per ACTIVE collider, entity by entity.  Computed on the device from the uploaded
+// components (count, exclusive scan, pack): walking 168 B per entity on the host costs more than the
+// PCIe transfer of the whole world.
+__global__ void __launch_bounds__(256) k_count_active(const IcxColliderComponent* __restrict__ C, uint32_t n, uint32_t* __restrict__ counts,
+                                                      uint8_t* __restrict__ mask)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t m = 0;
+    if (C) for (int s = 0; s < ICX_COLLIDERS_PER_ENTITY; s++) if (C[i].colliders[s].isActive) m |= 1u << s;
+    counts[i] = __popc(m); mask[i] = (uint8_t)m;
+}
+__global__ void __launch_bounds__(256) k_make_first(const uint32_t* __restrict__ offs, const uint8_t* __restrict__ mask, uint32_t n,
+                                                    uint32_t* __restrict__ first)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) first[i] = offs[i] | ((uint32_t)__popc((uint32_t)mask[i]) << 30);
+}
+void launch_exclusive_scan(uint32_t* data, uint32_t* partial, uint32_t n, cudaStream_t st);
+// scan_buf: n + 1 words (scan_buf[n] = number of packets afterwards)
+void launch_packet_structure(const IcxColliderComponent* C, uint32_t n, uint32_t* scan_buf, uint32_t* partial, uint8_t* mask, uint32_t* first,
+                             cudaStream_t st)
+{
+    if (n) k_count_active<<<(n + 255) / 256, 256, 0, st>>>(C, n, scan_buf, mask);
+    launch_exclusive_scan(scan_buf, partial, n, st);
+    if (n) k_make_first<<<(n + 255) / 256, 256, 0, st>>>(scan_buf, mask, n, first);
+}
+
 // ---- ParallelCosmosContext::load_and_link / extract_entity_updates (a22) ------------------
 // Gather the AoS rows of the entities listed in idx (ascending source indices) into compact
 // staging arrays.  mode 0 = clone (parallel_cosmos_context.cpp:107-151): a FORKED source entity

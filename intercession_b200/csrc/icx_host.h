@@ -25,6 +25,9 @@ void launch_gather_rows(const DeviceWorld& W, Mirror M, const uint32_t* idx, uin
                         IcxPhysics* o_P, IcxColliderComponent* o_C, uint8_t* o_hasP, uint8_t* o_ts, uint16_t* o_tc, cudaStream_t st);
 void launch_extract_ts(const DeviceWorld& W, const uint32_t* index, const uint8_t* ts, uint32_t count, cudaStream_t st);
 
+void launch_packet_structure(const IcxColliderComponent* C, uint32_t n, uint32_t* scan_buf, uint32_t* partial, uint8_t* mask, uint32_t* first,
+                             cudaStream_t st);
+
 struct DeviceBuffer {
     void* ptr = nullptr; size_t bytes = 0;
     cudaError_t ensure(size_t n) {
@@ -49,7 +52,9 @@ struct IcxWorld {
     std::vector<icx::DeviceBuffer> pool;
     uint32_t cap_entities = 0, cap_packets = 0;
     uint32_t n_entities = 0, n_packets = 0;
-    std::vector<uint8_t> active_mask;   // per entity: bit s = collider slot s active (packet structure)
+    std::vector<uint8_t> active_mask;   // per entity: bit s = collider slot s active (packet structure); see icx_host_masks()
+    bool masks_on_host = false;         // active_mask mirrors d_mask (fetched on demand: only update / clone / extract need it)
+    icx::DeviceBuffer d_mask, st_scan;  // device copy of active_mask; scan scratch of the packet-structure pass
     std::vector<uint32_t> h_ids;        // host copy of the entity ids (clone / extract bookkeeping)
     icx::DeviceBuffer cl_idx, cl_ids, cl_T, cl_P, cl_C, cl_hasP, cl_ts, cl_tc;     // compact staging of clone / extract
     // staging (device) for AoS import/export, pinned host mirror for counters
@@ -70,3 +75,6 @@ struct IcxWorld {
     std::string error;
     bool have_results = false;
 };
+
+// make w->active_mask valid (one small device-to-host copy after an upload); ICX_OK or ICX_E_CUDA
+int icx_host_masks(IcxWorld* w);

@@ -444,6 +444,17 @@ void launch_grid(const DeviceWorld& W, cudaStream_t st)
     k_scatter<<<(W.n_packets + 255) / 256, 256, 0, st>>>(W);
 }
 
+// exclusive scan of data[0..n) in place; data[n] receives the total (n <= 4096 * 4096)
+void launch_exclusive_scan(uint32_t* data, uint32_t* partial, uint32_t n, cudaStream_t st)
+{
+    const uint32_t n_part = (n + SCAN_EPB - 1) / SCAN_EPB;
+    if (n) {
+        k_scan_blocks<<<n_part, SCAN_TPB, 0, st>>>(data, partial, n);
+        k_scan_partials<<<1, SCAN_TPB, 0, st>>>(partial, n_part);
+    } else cudaMemsetAsync(partial, 0, 4, st);
+    k_scan_add<<<(n + 1 + 255) / 256, 256, 0, st>>>(data, partial, n, n_part);
+}
+
 void launch_pairs(const DeviceWorld& W, cudaStream_t st)
 {
     if (W.n_packets == 0) return;
