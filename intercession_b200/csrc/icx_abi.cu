@@ -53,7 +53,7 @@ int allocate(IcxWorld* w)
     CK(alloc(w, W.scan_partial, 4096 + 8));
     CK(alloc(w, W.s_lo, np)); CK(alloc(w, W.s_hi, np));
     CK(alloc(w, W.large_list, W.max_large));
-    CK(alloc(w, W.pairs, W.max_pairs)); CK(alloc(w, W.tight, W.max_pairs)); CK(alloc(w, W.near, W.max_pairs)); CK(alloc(w, W.push, ne)); CK(alloc(w, W.static_pairs, W.max_static));
+    CK(alloc(w, W.pairs, W.max_pairs)); CK(alloc(w, W.tight, W.max_pairs)); CK(alloc(w, W.push, ne)); CK(alloc(w, W.static_pairs, W.max_static));
     CK(alloc(w, W.dirty_slot, ne)); CK(alloc(w, W.dirty_list, ne));
     CK(alloc(w, W.nbr, 2 * ne * (size_t)W.max_neighbors)); CK(alloc(w, W.nbr_count, 2 * ne)); CK(alloc(w, W.slot_info, ne));
     CK(alloc(w, W.head[0], ne)); CK(alloc(w, W.head[1], ne));
@@ -62,9 +62,9 @@ int allocate(IcxWorld* w)
     CK(alloc(w, W.counters, CTR_TOTAL)); CK(alloc(w, W.flags, 4));
     CK(cudaMemset(W.counters, 0, CTR_TOTAL * sizeof(uint32_t))); CK(cudaMemset(W.flags, 0, 16));
     W.trace = nullptr;
-    w->resolve_blocks = resolve_grid_blocks(w->device);
+    w->resolve_blocks = resolve_grid_blocks(w->device, 1); w->prepare_blocks = resolve_grid_blocks(w->device, 0);
     { int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, w->device); w->narrow_blocks = sms * 8; }
-    if (w->resolve_blocks <= 0) return fail(w, ICX_E_CUDA, "k_resolve cannot be made resident");
+    if (w->resolve_blocks <= 0 || w->prepare_blocks <= 0) return fail(w, ICX_E_CUDA, "k_resolve cannot be made resident");
     CK(cudaMallocHost((void**)&w->h_counters, CTR_TOTAL * sizeof(uint32_t)));
     CK(cudaMallocHost((void**)&w->h_flags, 16));
     return ICX_OK;
@@ -110,8 +110,8 @@ int run_tick_once(IcxWorld* w, double dt, int do_euler, int do_collide, uint32_t
         if (prof) cudaEventRecord(w->pev[3], st);
         launch_narrow(W, w->narrow_blocks, st);
         if (prof) cudaEventRecord(w->pev[4], st);
-        CK(launch_resolve(W, dt, do_euler, w->resolve_blocks, st));
-        w->launches += 7;
+        CK(launch_resolve(W, dt, do_euler, w->prepare_blocks, w->resolve_blocks, st));
+        w->launches += 8;
         if (prof) cudaEventRecord(w->pev[5], st);
     }
     CK(cudaMemcpyAsync(w->h_counters, W.counters, CTR_TOTAL * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
@@ -161,7 +161,6 @@ int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_
                 W.max_pairs = std::max<uint32_t>(W.max_pairs * 2, w->h_counters[CTR_CANDIDATES] + w->h_counters[CTR_CANDIDATES] / 4);
                 rc = regrow(w, W.pairs, W.max_pairs); if (rc) return rc;
                 rc = regrow(w, W.tight, W.max_pairs); if (rc) return rc;
-                rc = regrow(w, W.near, W.max_pairs); if (rc) return rc;
             }
             if (w->h_counters[CTR_STATIC] > W.max_static) {
                 W.max_static = w->h_counters[CTR_STATIC] * 2;

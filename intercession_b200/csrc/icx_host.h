@@ -12,8 +12,8 @@ void launch_integrate_prep(const DeviceWorld& W, double dt, int do_euler, cudaSt
 void launch_grid(const DeviceWorld& W, cudaStream_t st);      // 4 kernels: scan x3 + scatter
 void launch_pairs(const DeviceWorld& W, cudaStream_t st);
 void launch_narrow(const DeviceWorld& W, int blocks, cudaStream_t st);
-int resolve_grid_blocks(int device);                          // co-resident blocks of the persistent resolve kernel
-cudaError_t launch_resolve(const DeviceWorld& W, double dt, int do_euler, int blocks, cudaStream_t st);
+int resolve_grid_blocks(int device, int phase);               // co-resident blocks of the persistent resolve kernels (0 = prepare, 1 = rounds)
+cudaError_t launch_resolve(const DeviceWorld& W, double dt, int do_euler, int prepare_blocks, int blocks, cudaStream_t st);
 struct Mirror { uint32_t* ids; IcxTransform* T; IcxPhysics* P; IcxColliderComponent* C; uint8_t* hasP; };
 void launch_import_kernel(const DeviceWorld& W, Mirror M, const uint32_t* index, const uint32_t* ids, const IcxTransform* T,
                           const IcxPhysics* P, const IcxColliderComponent* C, const uint8_t* hasP, const uint8_t* ts,
@@ -71,7 +71,7 @@ struct IcxWorld {
     double phase_ms[ICX_N_PHASES] = {};
     uint64_t phase_ticks = 0;
     uint64_t launches = 0;              // kernels launched by icx_step* since creation
-    int resolve_blocks = 0, narrow_blocks = 0;
+    int resolve_blocks = 0, prepare_blocks = 0, narrow_blocks = 0;
     std::string error;
     bool have_results = false;
 };

@@ -821,19 +821,24 @@ __device__ __forceinline__ void trace_mark(const DeviceWorld& W, uint32_t& n, ui
     W.trace[n++] = t; W.trace[n++] = tag;
 }
 
-#define RESOLVE_TPB 384
-__global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(const __grid_constant__ DeviceWorld W, double dt, int do_euler)
+// The work before the rounds (candidate lists, push prediction, first cursor positions) is throughput-bound
+// and light on registers; the rounds are latency-bound and want every register they can get (no spills in
+// the exact procedures).  So the first attempt is split over two cooperative launches with different shapes:
+// PHASE 0 = prepare (2 x 384 threads per SM), PHASE 1 = rounds (1 x 256 threads per SM, 251 registers) --
+// which also carries the whole loop for the rare restarts.
+#define RESOLVE_TPB 256
+#define PREPARE_TPB 384
+template <int PHASE>
+__device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, int do_euler, V3* scratch)
 {
-    // per-warp scratch of the exact procedures (contact manifolds, clipping): see pseudo_clip_polyhedra_s
-    __shared__ V3 scratch_all[RESOLVE_TPB / 32][8 + 2 * ICX_MAXV];
-    V3* const scratch = scratch_all[threadIdx.x >> 5];
     uint32_t tn = 2;        // trace[0] = number of words used
+    if (PHASE == 1 && W.trace) tn = (uint32_t)W.trace[0];
     cg::grid_group grid = cg::this_grid();
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
     volatile uint32_t* ctr = W.counters;
     uint32_t attempts = 0, rounds = 0;
-    if (tid == 0) trace_mark(W, tn, 0u);
-    {   // Predict which clean bodies the replay will reach: a body that static resolution may push by up to
+    if (PHASE != 1 && tid == 0) trace_mark(W, tn, 0u);
+    if (PHASE != 1) {   // Predict which clean bodies the replay will reach: a body that static resolution may push by up to
         // push[a] (sum of the depths of its speculative contacts) reaches the candidates whose gap is smaller;
         // those are replayed in order too and inherit the remainder of the push.  One warp per dirty body walks
         // its candidate list, at most three generations.  Only a prediction: a body it misses triggers the
@@ -878,6 +883,9 @@ __global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(const __grid_constant__
     }
     for (;;) {
         const uint32_t n_dirty = ctr[CTR_DIRTY], n_listed = ctr[CTR_LISTED], n_static = min(ctr[CTR_STATIC], W.max_static);
+        if (PHASE == 1 && attempts == 0) {                  // the prepare launch did all of this for the first attempt
+            if (*(volatile uint32_t*)W.flags & RF_NEIGHBOR_OVERFLOW) break;
+        } else {
         for (uint32_t s = n_listed + (tid >> 5); s < n_dirty; s += (nth >> 5)) build_lists_warp(W, s);
         for (uint32_t s = tid; s < n_dirty; s += nth)
             if (attempts > 0 && s < n_listed) restore_body(W, W.dirty_list[s], dt, do_euler);
@@ -899,6 +907,8 @@ __global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(const __grid_constant__
             settle_warp(W, s, load_cursor(W, s), 0u, n_dirty, 1, CTR_ACTIVE);     // writes head[0] / active[0]
         grid.sync();
         if (tid == 0) trace_mark(W, tn, 0x50000u);
+        }
+        if (PHASE == 0) { if (tid == 0 && W.trace) W.trace[0] = tn; return; }
         int parity = 0;
         rounds = 0;
         for (;;) {
@@ -932,23 +942,37 @@ __global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(const __grid_constant__
     if (tid == 0) { ctr[CTR_ROUNDS] = rounds; ctr[CTR_ATTEMPTS] = attempts; trace_mark(W, tn, 0x40000u); if (W.trace) W.trace[0] = tn; }
 }
 
+__global__ void __launch_bounds__(PREPARE_TPB, 2) k_resolve_prepare(const __grid_constant__ DeviceWorld W, double dt, int do_euler)
+{
+    resolve_body<0>(W, dt, do_euler, nullptr);
+}
+__global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(const __grid_constant__ DeviceWorld W, double dt, int do_euler)
+{
+    // per-warp scratch of the exact procedures (contact manifolds, clipping): see pseudo_clip_polyhedra_s
+    __shared__ V3 scratch_all[RESOLVE_TPB / 32][8 + 2 * ICX_MAXV];
+    resolve_body<1>(W, dt, do_euler, scratch_all[threadIdx.x >> 5]);
+}
+
 void launch_narrow(const DeviceWorld& W, int blocks, cudaStream_t st)
 {
     k_narrow<<<blocks, 128, 0, st>>>(W);
 }
 
-int resolve_grid_blocks(int device)
+int resolve_grid_blocks(int device, int phase)
 {
     int per_sm = 0, sms = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_resolve, RESOLVE_TPB, 0);
+    if (phase == 0) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_resolve_prepare, PREPARE_TPB, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_resolve, RESOLVE_TPB, 0);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     return per_sm * sms;
 }
 
-cudaError_t launch_resolve(const DeviceWorld& W, double dt, int do_euler, int blocks, cudaStream_t st)
+cudaError_t launch_resolve(const DeviceWorld& W, double dt, int do_euler, int prepare_blocks, int blocks, cudaStream_t st)
 {
     DeviceWorld Wc = W;
     void* args[] = {&Wc, &dt, &do_euler};
+    cudaError_t e = cudaLaunchCooperativeKernel((const void*)k_resolve_prepare, dim3(prepare_blocks), dim3(PREPARE_TPB), args, 0, st);
+    if (e != cudaSuccess) return e;
     return cudaLaunchCooperativeKernel((const void*)k_resolve, dim3(blocks), dim3(RESOLVE_TPB), args, 0, st);
 }
 

@@ -101,7 +101,6 @@ struct DeviceWorld {
     uint32_t* large_list;           // packets larger than a cell (immutable only)
     // flat candidate pair list (the broadphase output, icx_pairs_fetch)
     uint2* pairs; uint32_t max_pairs;
-    uint4* near;                    // {entity a, entity b, gap bits, -}: pairs that touch (gap 0) or are closer than the margin
     float* push;                    // per entity: predicted displacement by static resolution this tick
     uint2* tight;                   // the subset with ICX_PAIR_TIGHT (input of the speculative narrowphase)
     uint2* static_pairs; uint32_t max_static;    // hits between two immutable bodies (contact records only)
