@@ -59,8 +59,10 @@ class ClockSampler:
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index):
-        self.index, self.stop, self.t = index, threading.Event(), None
+    def __init__(self, index, poll=True):
+        # poll=False (ranks > 0 of a multi-GPU run): one sample on entry and one on exit instead of a polling
+        # thread -- eight processes polling NVML at once serialise on the driver and slow every rank's launches
+        self.index, self.stop, self.t, self.poll = index, threading.Event(), None, poll
         self.sm, self.mx, self.reasons = [], [], set()
         self.nvml = None
         try:
@@ -99,14 +101,26 @@ class ClockSampler:
                 pass
             self.stop.wait(0.02 if self.nvml else 0.25)
 
+    def _once(self):
+        try:
+            self._sample_nvml() if self.nvml else self._sample_smi()
+        except Exception:
+            pass
+
     def __enter__(self):
-        self.t = threading.Thread(target=self._run, daemon=True)
-        self.t.start()
+        if self.poll:
+            self.t = threading.Thread(target=self._run, daemon=True)
+            self.t.start()
+        else:
+            self._once()
         return self
 
     def __exit__(self, *a):
-        self.stop.set()
-        self.t.join(timeout=6)
+        if self.poll:
+            self.stop.set()
+            self.t.join(timeout=6)
+        else:
+            self._once()
 
     def summary(self):
         return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": max(self.mx) if self.mx else None,
@@ -253,10 +267,45 @@ def timeslice_pipeline_bench(bodies, ticks, delay, rank, world_size, local_rank,
         dist.all_reduce(sent_t, op=dist.ReduceOp.SUM)
         dist.all_reduce(rep_t, op=dist.ReduceOp.MIN)
     sec = float(sec_t.item())
+
+    # ---- one parallel-cosmos cycle: load_and_link from a past timeslice, re-simulate `delay` ticks up to its
+    # future neighbour's coherency, extract at chain-link - 1.  Rank 0 only, parallel cosmos on the same GPU (the peer-GPU
+    # copies are covered by tests/test_gpu_clone.py; the idle ranks' GPUs sit in the NCCL barrier meanwhile). ----
+    cycle = None
+    if rank == 0:
+        from intercession_b200 import world as icxworld
+        dst = slices[0]
+        if world_size == 1:
+            src_w, own_src = slices[1].w, False
+        else:
+            sc = base.copy(); sc["ids"] = pipeline.past_ids(base.ids, 1)
+            src_w, own_src = icxworld.World(sc.n, host_timeslice=1, device=local_rank), True
+            src_w.upload(sc); src_w.set_coherency(dst.w.coherency())
+        par = icxworld.World(base.n, host_timeslice=abi.NULL_TIMESLICE, device=local_rank)
+        best = None
+        for rep in range(3):
+            torch.cuda.synchronize()
+            c0 = time.perf_counter()
+            n_cl = src_w.clone_into(par); par.sync()
+            c1 = time.perf_counter()
+            par.step(pipeline.DT, delay); par.sync()
+            c2 = time.perf_counter()
+            n_ex, n_miss = par.extract_into(dst.w); dst.w.sync()
+            c3 = time.perf_counter()
+            cur = (c3 - c0, c1 - c0, c2 - c1, c3 - c2)
+            best = cur if best is None or cur[0] < best[0] else best
+        cycle = {"workload": f"load_and_link of {n_cl} entities -> {delay} re-simulated ticks -> extract at chain-link - 1 ({n_ex} written, {n_miss} missing); best of 3",
+                 "cycle_ms": round(best[0] * 1e3, 3), "clone_ms": round(best[1] * 1e3, 3), "run_ms": round(best[2] * 1e3, 3),
+                 "extract_ms": round(best[3] * 1e3, 3), "state_bytes_each_way": int(n_cl) * 316}
+        par.close()
+        if own_src:
+            src_w.close()
+    barrier()
     for ts in slices:
         ts.close()
     return {"workload": f"config5 (reduced): {n_ts} timeslices x {bodies} temporal bodies + 6 walls, delay {delay} ticks, {ticks} wall ticks; "
-                        f"no time travellers / parallel cosmos",
+                        f"no time travellers; one parallel-cosmos cycle timed separately",
+            "parallel_cycle": cycle,
             "n_timeslices": n_ts, "timeslices_per_gpu": len(mine), "ticks": ticks, "seconds": round(sec, 4),
             "wall_ticks_per_s": ticks / sec, "collider_steps_per_s": n_ts * base.n * ticks / sec,
             "snapshot_bytes_per_link_tick": base.n * abi.SNAPSHOT_BYTES, "snapshot_bytes_moved": int(sent_t.item()),
@@ -329,7 +378,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    s = build_scene(a.workload, a.bodies, seed_offset=rank)
+    s = build_scene(a.workload, a.bodies)             # every rank runs the SAME scene (BASELINE config 3 fixes the seed): true replicas
     n_colliders = int(s.C["colliders"]["isActive"].sum())
     w = icxworld.World(s.n, device=local_rank)
     w.upload(s)
@@ -337,7 +386,7 @@ def main():
     w.profile(True)
     launches0 = w.phases()[2]
     barrier()
-    with ClockSampler(local_rank) as clk:
+    with ClockSampler(local_rank, poll=(rank == 0)) as clk:
         w.step(DT, a.steps)
         ms = w.last_step_ms()
         barrier()
@@ -348,6 +397,14 @@ def main():
     if world_size > 1:
         dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
     ms_max = float(ms_t.item())
+    # per-rank view of the replicas
+    mine = torch.tensor([ms / a.steps, float(st.n_retries), float(st.n_attempts), float(min(clk.sm) if clk.sm else 0.0),
+                         float(len(clk.reasons - {"sw_power_cap"}))], dtype=torch.float64, device="cuda")
+    per_rank = [mine]
+    if world_size > 1:
+        per_rank = [torch.zeros_like(mine) for _ in range(world_size)]
+        dist.all_gather(per_rank, mine)
+    per_rank = [[round(float(x), 4) for x in t.tolist()] for t in per_rank]
     value = world_size * n_colliders * a.steps / (ms_max * 1e-3)
 
     # ---- roofline: algorithmic bytes of the tick over its measured duration ----
@@ -431,7 +488,9 @@ def main():
                            "l2": "inputs larger than L2 (per-tick state and derived arrays > 126 MB)" if a.bodies >= 400000 else "inputs fit L2 (reduced size)",
                            "colliders_per_gpu": n_colliders, "candidate_pairs": st.n_candidates, "contacts": st.n_contacts,
                            "dirty_bodies": st.n_dirty,
-                           "resolve_rounds": st.n_rounds, "resolve_attempts": st.n_attempts, "retries": st.n_retries, "margin": st.margin},
+                           "resolve_rounds": st.n_rounds, "resolve_attempts": st.n_attempts, "retries": st.n_retries, "margin": st.margin,
+                           "per_rank": {"columns": ["ms_per_step", "retries", "resolve_attempts_last_tick", "sm_mhz_min", "slowdown_reasons"],
+                                        "rows": per_rank}},
                 "clocks": clk.summary(), "roofline": roofline,
                 "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
                 "gpu_launches": int(launches1 - launches0),

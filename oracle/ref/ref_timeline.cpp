@@ -11,6 +11,9 @@
 //   record : server_network_dynamo.cpp:642-679   parallel_network_dynamo.cpp:369-385
 //   replay : server_network_dynamo.cpp:377-421   parallel_network_dynamo.cpp:51-89
 //   ageing : server_network_dynamo.cpp:13-15, :681-705
+//   jump bookkeeping (cached departures, paradox search, request classification):
+//            parallel_network_dynamo.cpp:155-161, :303-355, :488-593 -- the three containers are declared as in
+//            parallel_network_dynamo.h:54-65 and compared with the REAL TimejumpConditions::operator==
 // around the REAL containers, with the entity's components serialised into a real EventMessage in
 // the reference's order (descending component type so that they pop ascending,
 // ecs/component_registry.h:238-253: Transform first registered, then Physics).
@@ -27,6 +30,9 @@
 #include "spacetime/timejump_conditions.h"
 
 #include <memory>
+#include <unordered_map>
+#include <unordered_set>
+#include <vector>
 
 using namespace pleep;
 
@@ -117,5 +123,64 @@ int icxref_congruent(uint32_t n, const IcxTransform* live, const IcxTransform* r
 }
 
 int icxref_coherency_ge(uint16_t a, uint16_t b) { return coherency_greater_or_equal(a, b) ? 1 : 0; }
+
+// ---- jump bookkeeping of ParallelNetworkDynamo over the real TimejumpConditions ----
+struct RefJumps {
+    std::unordered_map<uint32_t, TimejumpConditions> m_jumpConditions;                       // keyed by the (wide) entity id
+    std::unordered_map<uint32_t, std::vector<TimejumpConditions>> m_jumpRevisionHistory;
+    std::unordered_set<uint32_t> m_resolvedTrips;
+};
+void* icxref_jumps_create(void) { return new RefJumps(); }
+void icxref_jumps_destroy(void* h) { delete static_cast<RefJumps*>(h); }
+void icxref_jumps_clear_departures(void* h) { static_cast<RefJumps*>(h)->m_jumpConditions.clear(); }      // :393
+
+// JUMP_DEPARTURE from the timestream, :155-161
+void icxref_jumps_departure(void* h, uint32_t entity, uint32_t tripId, const float* o)
+{
+    RefJumps& J = *static_cast<RefJumps*>(h);
+    J.m_jumpConditions.insert({ entity, TimejumpConditions{ tripId, glm::vec3(o[0], o[1], o[2]) } });
+}
+
+// JUMP_ARRIVAL, :303-355; returns 1 when the reference would log PARADOX DETECTED and send WORLDLINE_SHIFT
+int icxref_jumps_arrival(void* h, uint32_t tripId, const float* o)
+{
+    RefJumps& J = *static_cast<RefJumps*>(h);
+    TimejumpConditions newConditions{ 0, glm::vec3(o[0], o[1], o[2]) };
+    int paradox = 0;
+    if (!J.m_jumpRevisionHistory[tripId].empty() && !(newConditions == J.m_jumpRevisionHistory[tripId].back()))
+    {
+        for (TimejumpConditions& cond : J.m_jumpRevisionHistory[tripId])
+        {
+            if (newConditions == cond)
+            {
+                paradox = 1;
+                J.m_resolvedTrips.insert(tripId);
+                J.m_jumpRevisionHistory.erase(tripId);
+                break;
+            }
+        }
+    }
+    J.m_jumpRevisionHistory[tripId].push_back(newConditions);
+    return paradox;
+}
+
+// _jump_request_handler, :488-593; returns 0 missing / 1 equivalent / 2 resolved / 3 divergent
+int icxref_jumps_request(void* h, uint32_t entity, const float* o, uint32_t* tripOut)
+{
+    RefJumps& J = *static_cast<RefJumps*>(h);
+    TimejumpConditions newConditions{ 0, glm::vec3(o[0], o[1], o[2]) };
+    int kind;
+    if (J.m_jumpConditions.count(entity) < 1) { *tripOut = 91339; kind = 0; }
+    else if (newConditions == J.m_jumpConditions[entity]) { *tripOut = J.m_jumpConditions[entity].tripId; kind = 1; }
+    else if (J.m_resolvedTrips.count(J.m_jumpConditions[entity].tripId))
+    {
+        *tripOut = J.m_jumpConditions[entity].tripId;
+        J.m_resolvedTrips.erase(J.m_jumpConditions[entity].tripId);
+        kind = 2;
+    }
+    else { *tripOut = J.m_jumpConditions[entity].tripId; kind = 3; }
+    J.m_jumpConditions.erase(entity);
+    return kind;
+}
 
 } // extern "C"
