@@ -134,11 +134,27 @@ int icx_world_extract(IcxWorld* par, IcxWorld* dst, uint32_t* n_extracted, uint3
     if (par->have_C && !dst->have_C) return cfail(dst, ICX_E_STATE, "extract: destination has no collider components");
     if (par->have_P && !dst->have_P) return cfail(dst, ICX_E_STATE, "extract: destination has no physics components");
     { int mrc = icx_host_masks(par); if (mrc == ICX_OK) mrc = icx_host_masks(dst); if (mrc != ICX_OK) return cfail(dst, mrc, "extract: cannot read the collider activation masks"); }
+    // Both id lists are normally ascending (upload order = the reference's signature-map order, and a clone keeps it):
+    // then id - 1 is matched by one merge pass; otherwise through a hash map.
+    const bool merge = std::is_sorted(dst->h_ids.begin(), dst->h_ids.begin() + dst->n_entities) &&
+                       std::is_sorted(par->h_ids.begin(), par->h_ids.begin() + par->n_entities);
     std::unordered_map<uint32_t, uint32_t> where;
-    where.reserve(dst->h_ids.size() * 2);
-    for (uint32_t j = 0; j < dst->n_entities; j++) where.emplace(dst->h_ids[j], j);
+    if (!merge) {
+        where.reserve(dst->h_ids.size() * 2);
+        for (uint32_t j = 0; j < dst->n_entities; j++) where.emplace(dst->h_ids[j], j);
+    }
     std::vector<uint32_t> from, to;
-    uint32_t missing = 0;
+    from.reserve(par->n_entities); to.reserve(par->n_entities);
+    uint32_t missing = 0, cursor = 0;
+    const uint32_t NOT_FOUND = 0xFFFFFFFFu;
+    auto find_local = [&](uint32_t local) -> uint32_t {
+        if (merge) {
+            while (cursor < dst->n_entities && dst->h_ids[cursor] < local) cursor++;
+            return (cursor < dst->n_entities && dst->h_ids[cursor] == local) ? cursor : NOT_FOUND;
+        }
+        auto it = where.find(local);
+        return it == where.end() ? NOT_FOUND : it->second;
+    };
     for (uint32_t i = 0; i < par->n_entities; i++) {
         const uint32_t id = par->h_ids[i], link = id & 0xFu;
         if (link >= ICX_NULL_CHAINLINK) continue;                                   // decrement_causal_chain_link fails: non-temporal, :213-219
@@ -146,11 +162,11 @@ int icx_world_extract(IcxWorld* par, IcxWorld* dst, uint32_t* n_extracted, uint3
             return cfail(dst, ICX_E_INVALID, "extract: entity with causal chain-link 0 in the parallel world");
         if ((id >> 28) == ICX_NULL_TIMESLICE) continue;                             // created during the parallel run, :223-229
         const uint32_t local = id - 1u;                                             // chain-link - 1
-        auto it = where.find(local);
-        if (it == where.end()) { missing++; continue; }                             // :241-245 registers it: entity lifecycle stays on the host
-        if (par->active_mask[i] != dst->active_mask[it->second])
+        const uint32_t j = find_local(local);
+        if (j == NOT_FOUND) { missing++; continue; }                                // :241-245 registers it: entity lifecycle stays on the host
+        if (par->active_mask[i] != dst->active_mask[j])
             return cfail(dst, ICX_E_STATE, "extract: collider activation differs; re-upload the destination");
-        from.push_back(i); to.push_back(it->second);
+        from.push_back(i); to.push_back(j);
     }
     const uint32_t cnt = (uint32_t)from.size();
     if (n_missing) *n_missing = missing;
