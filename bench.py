@@ -226,6 +226,59 @@ def worldline_batch_bench(n_worldlines, per, ticks, rank, world_size, local_rank
             "algorithmic_bytes_per_body_tick": {"record": 200, "scan": 26}}
 
 
+def timeline_kernels_bench(w, n, peak, device, reps=24, depth=6):
+    """The world-line kernels on their own over the resident 1 M-entity world: record (k_record), replay (k_replay),
+    divergence scan (k_divergence_scan).  `us` = mean kernel duration from CUDA events on the world's stream
+    (icx_timeline_kernel_ms) over `reps` launches cycling through `depth` ring slots (depth x 100 B x n > L2);
+    `call_us` = host clock per ABI call over the same batch (record / replay are asynchronous launches; the scan returns its
+    reduction to the host, so its call includes one read-back and stream sync).
+    Algorithmic bytes per body: record / replay 100 B read + 100 B written (6 x float4 + state word), scan 26 B."""
+    from intercession_b200 import abi, world as icxworld
+    tl = icxworld.Timeline(depth, n, device=device)
+    tl.profile(True)
+    c0 = 1000
+
+    def run(fn, which, reps):
+        fn(0); w.sync()
+        kern = []
+        t0 = time.perf_counter()
+        for k in range(reps):
+            fn(k)
+        w.sync()
+        call = (time.perf_counter() - t0) / reps
+        for k in range(reps):                      # events hold the LAST launch only: time each launch on its own
+            fn(k)
+            kern.append(tl.kernel_ms(which))
+        return float(np.mean(kern)) * 1e-3, call
+
+    def entry(sec, call, nbytes, extra=None):
+        e = {"us": round(sec * 1e6, 2), "call_us": round(call * 1e6, 2), "alg_bytes": nbytes,
+             "alg_GBps": round(nbytes / sec / 1e9, 1), "frac": round(nbytes / sec / 1e9 / peak, 4)}
+        if extra:
+            e["note"] = extra
+        return e
+
+    out = {}
+    sec, call = run(lambda k: w.record(tl, (c0 + k % depth) & 0xFFFF), 0, reps)
+    out["record"] = entry(sec, call, 200 * n)
+    rec_call = call
+
+    def pair(k):                                   # a replay consumes its record (pop): re-record before each one
+        c = (c0 + k % depth) & 0xFFFF
+        w.record(tl, c)
+        assert w.replay(tl, c, abi.REPLAY_SERVER)
+    sec, call = run(pair, 1, reps)
+    out["replay"] = entry(sec, max(call - rec_call, 1e-9), 200 * n, "call_us = record + replay pair minus the record call")
+    for k in range(depth):
+        w.record(tl, (c0 + k) & 0xFFFF)
+    sec, call = run(lambda k: w.divergence_scan(tl, (c0 + k % depth) & 0xFFFF, 1), 2, reps)
+    out["divergence_scan"] = entry(sec, call, 26 * n, "call_us includes the result read-back and stream sync")
+    out["entities"] = n
+    out["timing"] = f"CUDA events per launch, mean of {reps}; {depth} ring slots of {100 * n / 1e6:.0f} MB (larger than L2)"
+    tl.close()
+    return out
+
+
 def timeslice_pipeline_bench(bodies, ticks, delay, rank, world_size, local_rank, barrier):
     """BASELINE.json configs[4] (reduced: no time travellers, no parallel cosmos): one timeslice per rank, each
     `delay` ticks behind its future neighbour; per wall tick and link ONE snapshot of 100 B per entity travels
@@ -347,6 +400,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-timeline", action="store_true", help="skip the record / replay / scan kernel timings")
     ap.add_argument("--worldlines", type=int, default=4096, help="config-4 world-line candidates (0 = skip that section)")
     ap.add_argument("--worldline-bodies", type=int, default=1024)
     ap.add_argument("--worldline-ticks", type=int, default=8)
@@ -457,6 +511,8 @@ def main():
     e2e_val = world_size * n_colliders * a.e2e_steps / float(e2e_t.item())
     h2d = ids.nbytes + T.nbytes + P.nbytes + Cc.nbytes + hasP.nbytes + ts.nbytes + tc.nbytes + 4 * s.n
     d2h = T.nbytes + P.nbytes + n_contacts * 48
+    tlk = timeline_kernels_bench(w, s.n, peak, local_rank) if (rank == 0 and not a.no_timeline) else None
+    barrier()
     w.close()
 
     wlb = None
@@ -494,6 +550,7 @@ def main():
                 "clocks": clk.summary(), "roofline": roofline,
                 "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
                 "gpu_launches": int(launches1 - launches0),
+                "timeline_kernels": tlk,
                 "worldline_batch": wlb,
                 "timeslice_pipeline": tsp,
                 "cpu_baseline": cpu}

@@ -328,6 +328,12 @@ ICX_API int  icx_timeline_create(int device, uint32_t depth_ticks, uint32_t n_ma
 ICX_API void icx_timeline_destroy(IcxTimeline* tl);
 ICX_API const char* icx_timeline_last_error(const IcxTimeline* tl);
 
+/* Measurement hook (no reference counterpart): CUDA events around the record / replay / divergence-scan kernel launches on
+ * the world's stream.  which: 0 = k_record, 1 = k_replay, 2 = k_divergence_scan; *ms = duration of the LAST such launch
+ * (waits for it).  ICX_E_STATE if that kernel has not run since profiling was switched on. */
+ICX_API int icx_timeline_profile(IcxTimeline* tl, int enable);
+ICX_API int icx_timeline_kernel_ms(IcxTimeline* tl, int which, float* ms);
+
 /* Record = serialise every entity at `coherency` and push it (TimelineApi::push_past_timestream,
  * server_network_dynamo.cpp:642-679; push_timestream_at_breakpoint rewrites the same slot,
  * parallel_network_dynamo.cpp:369-385).  Asynchronous on the world's stream. */

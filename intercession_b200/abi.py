@@ -157,6 +157,8 @@ SIGNATURES = {
     "icx_timeline_create": (C.c_int, [C.c_int, _u32, _u32, C.POINTER(_vp)]),
     "icx_timeline_destroy": (None, [_vp]),
     "icx_timeline_last_error": (C.c_char_p, [_vp]),
+    "icx_timeline_profile": (C.c_int, [_vp, C.c_int]),
+    "icx_timeline_kernel_ms": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_float)]),
     "icx_record": (C.c_int, [_vp, _vp, C.c_uint16]),
     "icx_record_at_breakpoint": (C.c_int, [_vp, _vp, C.c_uint16]),
     "icx_breakpoint_set": (C.c_int, [_vp]),

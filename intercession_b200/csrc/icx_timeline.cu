@@ -34,6 +34,10 @@ struct IcxTimeline {
     // scan outputs (device) + pinned host mirror
     unsigned long long* d_score = nullptr; uint32_t* d_count = nullptr; uint32_t cap_wl = 0;
     uint32_t* d_age = nullptr;          // [0] promoted, [1] resolution needed
+    // optional kernel timing (icx_timeline_profile): events around the last record / replay / scan launch
+    bool profile = false;
+    cudaEvent_t pev[3][2] = {};
+    bool pev_used[3] = {};
     std::string error;
 };
 
@@ -210,10 +214,31 @@ void icx_timeline_destroy(IcxTimeline* tl)
     if (tl->d_score) cudaFree(tl->d_score);
     if (tl->d_count) cudaFree(tl->d_count);
     if (tl->d_age) cudaFree(tl->d_age);
+    for (auto& pair : tl->pev) for (cudaEvent_t e : pair) if (e) cudaEventDestroy(e);
     delete tl;
 }
 
 const char* icx_timeline_last_error(const IcxTimeline* tl) { return tl ? tl->error.c_str() : "null timeline"; }
+
+int icx_timeline_profile(IcxTimeline* tl, int enable)
+{
+    if (!tl) return ICX_E_INVALID;
+    cudaSetDevice(tl->device);
+    if (enable && !tl->pev[0][0])
+        for (auto& pair : tl->pev) for (cudaEvent_t& e : pair) TCK(cudaEventCreate(&e));
+    tl->profile = enable != 0;
+    return ICX_OK;
+}
+
+int icx_timeline_kernel_ms(IcxTimeline* tl, int which, float* ms)
+{
+    if (!tl || !ms || which < 0 || which > 2) return ICX_E_INVALID;
+    if (!tl->pev_used[which]) { tl->error = "kernel_ms: that kernel has not run with profiling on"; return ICX_E_STATE; }
+    cudaSetDevice(tl->device);
+    TCK(cudaEventSynchronize(tl->pev[which][1]));
+    TCK(cudaEventElapsedTime(ms, tl->pev[which][0], tl->pev[which][1]));
+    return ICX_OK;
+}
 
 static int record_impl(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, bool at_breakpoint);
 int icx_record(IcxWorld* w, IcxTimeline* tl, uint16_t coherency) { return record_impl(w, tl, coherency, false); }
@@ -248,7 +273,9 @@ static int record_impl(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, bool at
     const uint32_t n = w->n_entities;
     if (n) {
         const int blocks = (int)std::min<uint32_t>((n + 255) / 256, 148 * 16);
+        if (tl->profile) cudaEventRecord(tl->pev[0][0], w->stream);
         k_record<<<blocks, 256, 0, w->stream>>>(w->W.in, tl->state + (size_t)s * 6 * tl->n_max, tl->ts + (size_t)s * tl->n_max, n, tl->n_max);
+        if (tl->profile) { cudaEventRecord(tl->pev[0][1], w->stream); tl->pev_used[0] = true; }
         TCK(cudaGetLastError());
         w->launches += 1;
     }
@@ -286,7 +313,9 @@ int icx_replay(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, int mode, int* 
     if (n_src != n && !(w->W.worldline_stride && n_src == w->W.worldline_stride)) { tl->error = "replay: record size matches neither the world nor one world-line"; return ICX_E_INVALID; }
     cudaSetDevice(w->device);
     const int blocks = (int)std::min<uint32_t>((n + 255) / 256, 148 * 16);
+    if (tl->profile) cudaEventRecord(tl->pev[1][0], w->stream);
     k_replay<<<blocks, 256, 0, w->stream>>>(w->W.in, tl->state + (size_t)s * 6 * tl->n_max, n, n_src, tl->n_max);
+    if (tl->profile) { cudaEventRecord(tl->pev[1][1], w->stream); tl->pev_used[1] = true; }
     TCK(cudaGetLastError());
     w->launches += 1;
     if (applied) *applied = 1;
@@ -318,7 +347,9 @@ int icx_divergence_scan(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, uint32
         if (!attr_set[w->device & 63]) { TCK(cudaFuncSetAttribute(k_divergence_scan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_set[w->device & 63] = true; }
         const uint32_t n_tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
         const int blocks = (int)std::min<uint32_t>(n_tiles, 148 * 2);
+        if (tl->profile) cudaEventRecord(tl->pev[2][0], st);
         k_divergence_scan<<<blocks, SCAN_TPB, smem, st>>>(w->W.in.pos, tl->state + (size_t)s * 6 * tl->n_max, n, n_snap, stride, tl->d_count, tl->d_score);
+        if (tl->profile) { cudaEventRecord(tl->pev[2][1], st); tl->pev_used[2] = true; }
         TCK(cudaGetLastError());
         w->launches += 1;
     }

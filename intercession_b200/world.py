@@ -220,6 +220,17 @@ class Timeline:
         if rc != abi.OK:
             raise IcxError(rc, self.lib.icx_timeline_last_error(self.handle).decode())
 
+    def profile(self, on=True):
+        self.lib.icx_timeline_profile(self.handle, 1 if on else 0)
+
+    def kernel_ms(self, which):
+        """Duration of the last k_record (0) / k_replay (1) / k_divergence_scan (2) launch, CUDA events on the world's stream."""
+        ms = C.c_float(0)
+        rc = self.lib.icx_timeline_kernel_ms(self.handle, which, C.byref(ms))
+        if rc != abi.OK:
+            raise IcxError(rc, self.lib.icx_timeline_last_error(self.handle).decode())
+        return ms.value
+
     def slot_info(self, coherency):
         v, n = C.c_int(0), C.c_uint32(0)
         self.lib.icx_timeline_slot_info(self.handle, coherency, C.byref(v), C.byref(n))
