@@ -198,12 +198,15 @@ def worldline_batch_bench(n_worldlines, per, ticks, rank, world_size, local_rank
     dev_ms = 0.0
     flags = cnt = score = None
     any_flag = np.zeros(len(mine), np.uint8)
+    tl_base.profile(True)
+    scan_ms = []
     for t in range(ticks):
         wc.replay(tl_new, t, mode=abi.REPLAY_PARALLEL)
         wc.step(DT)
         dev_ms += wc.last_step_ms()
         wc.record(tl_new, t + 1)
         flags, cnt, score = wc.divergence_scan(tl_base, t + 1, len(mine))
+        scan_ms.append(tl_base.kernel_ms(2))
         any_flag |= flags
     gflags, gcnt, gscore = shard.gather_results(any_flag, cnt, score, n_worldlines, rank, world_size, device=dev)
     barrier()
@@ -223,7 +226,12 @@ def worldline_batch_bench(n_worldlines, per, ticks, rank, world_size, local_rank
             "divergent_worldlines": int(gflags.sum()), "most_congruent": shard.most_congruent(gflags, gscore),
             "gather": {"collective": "all_gather_into_tensor (NCCL)" if world_size > 1 else "none (1 rank)",
                        "bytes_per_rank": 24 * ((n_worldlines + world_size - 1) // world_size)},
-            "algorithmic_bytes_per_body_tick": {"record": 200, "scan": 26}}
+            "algorithmic_bytes_per_body_tick": {"record": 200, "scan": 26},
+            # k_divergence_scan over this rank's candidates: 16 B of live position per body from HBM (the tick and the record
+            # ran in between, > L2); the 16 KB base record is shared by every world-line and stays in L2
+            "scan_kernel_rank0": {"us": round(float(np.mean(scan_ms)) * 1e3, 2), "bodies": int(full_local.n),
+                                  "alg_GBps": round(16.0 * full_local.n / (float(np.mean(scan_ms)) * 1e-3) / 1e9, 1),
+                                  "timing": "CUDA events per launch (icx_timeline_kernel_ms), mean over the ticks"}}
 
 
 def timeline_kernels_bench(w, n, peak, device, reps=24, depth=6):
@@ -277,6 +285,34 @@ def timeline_kernels_bench(w, n, peak, device, reps=24, depth=6):
     out["timing"] = f"CUDA events per launch, mean of {reps}; {depth} ring slots of {100 * n / 1e6:.0f} MB (larger than L2)"
     tl.close()
     return out
+
+
+def projectile_behaviors_bench(w, n, peak, reps=24):
+    """ProjectileBehaviors::on_fixed_update on the device (SURVEY 8(f) row 1) for one projectile per entity of the resident
+    world: mean kernel duration from CUDA events on the world's stream (icx_projectiles_kernel_ms).  Algorithmic bytes per
+    projectile: 40 B component row read + 8 B lifetime written + 4 B entity index + 16 B + 16 B scale/mass word read and
+    written = 84 B.  88 MB per launch at 1 M: below L2 capacity, so the rows are written
+    flushed out of L2 by a 256 MB read pass between launches."""
+    import torch
+    from intercession_b200 import abi
+    rng = np.random.default_rng(5)
+    p = np.zeros(n, abi.projectile_dt)
+    p["currLifetime"] = rng.uniform(0, 200, n); p["maxLifetime"] = 300.0; p["hz"] = rng.uniform(0.5, 4.0, n)
+    p["scaleMin"] = rng.uniform(0.3, 0.5, n); p["scaleMax"] = p["scaleMin"] + 0.1
+    w.projectiles_upload(np.arange(n, dtype=np.uint32), p)
+    flush = torch.zeros(256 << 18, dtype=torch.float32, device="cuda")
+    us = []
+    for k in range(reps + 3):
+        flush.sum(); torch.cuda.synchronize()              # a READ pass: the L2 is left full of clean lines (a fill would leave dirty ones to drain)
+        w.projectiles_fixed_update(1.0 / 60.0)
+        if k >= 3:
+            us.append(w.projectiles_kernel_ms() * 1e3)
+    sec = float(np.mean(us)) * 1e-6
+    nbytes = 84 * n
+    w.projectiles_upload(np.zeros(0, np.uint32), np.zeros(0, abi.projectile_dt))
+    return {"kernel": "k_projectile_update", "projectiles": n, "us": round(sec * 1e6, 2), "alg_bytes": nbytes,
+            "alg_GBps": round(nbytes / sec / 1e9, 1), "frac": round(nbytes / sec / 1e9 / peak, 4),
+            "timing": f"CUDA events per launch, mean of {reps}, L2 flushed (256 MB read pass) before each launch"}
 
 
 def timeslice_pipeline_bench(bodies, ticks, delay, rank, world_size, local_rank, barrier):
@@ -512,6 +548,7 @@ def main():
     h2d = ids.nbytes + T.nbytes + P.nbytes + Cc.nbytes + hasP.nbytes + ts.nbytes + tc.nbytes + 4 * s.n
     d2h = T.nbytes + P.nbytes + n_contacts * 48
     tlk = timeline_kernels_bench(w, s.n, peak, local_rank) if (rank == 0 and not a.no_timeline) else None
+    beh = projectile_behaviors_bench(w, s.n, peak) if (rank == 0 and not a.no_timeline) else None
     barrier()
     w.close()
 
@@ -551,6 +588,7 @@ def main():
                 "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
                 "gpu_launches": int(launches1 - launches0),
                 "timeline_kernels": tlk,
+                "behaviors": beh,
                 "worldline_batch": wlb,
                 "timeslice_pipeline": tsp,
                 "cpu_baseline": cpu}

@@ -315,6 +315,36 @@ ICX_API int icx_debug_counters(IcxWorld* w, uint32_t* out32);
 /* CUDA stream of the world as a void* (cudaStream_t), for callers that time it. */
 ICX_API void* icx_world_stream(IcxWorld* w);
 
+/* ==== behaviours on the device ======================================
+ * ProjectileBehaviors::on_fixed_update (source/behaviors/projectile_behaviors.h:17-54) is the
+ * per-tick host work between replay and physics for every projectile: it advances the lifetime,
+ * pulses TransformComponent::scale and condemns expired entities.  Run on the device it needs no
+ * per-tick icx_bodies_update of the scales.  IcxProjectile = ProjectileComponent
+ * (source/behaviors/projectile_component.h:8-16, 40 B, doubles). */
+typedef struct IcxProjectile {
+    double currLifetime;
+    double maxLifetime;
+    double hz;
+    double scaleMax;
+    double scaleMin;
+} IcxProjectile;
+
+/* Projectile i belongs to the entity at upload position index[i] (each entity at most once).
+ * Replaces any earlier set; n = 0 drops it.  Call again after icx_bodies_upload. */
+ICX_API int icx_projectiles_upload(IcxWorld* w, uint32_t n, const uint32_t* index, const IcxProjectile* proj);
+/* on_fixed_update(dt) for every uploaded projectile, asynchronously on the world's stream:
+ *   currLifetime += dt;  scale = vec3((float)(sin(currLifetime * hz) * (scaleMax - scaleMin) / 2 + (scaleMin + 1)));
+ *   currLifetime > maxLifetime -> condemned (Cosmos::condemn_entity, cosmos.h:339-345).
+ * The scale lands where the next tick and icx_bodies_download read it.  Condemned projectiles keep
+ * being reported until the caller removes them (entity lifecycle stays with the host ECS). */
+ICX_API int icx_projectiles_fixed_update(IcxWorld* w, double dt);
+/* Component state back to the host, projectile order of the upload. */
+ICX_API int icx_projectiles_download(IcxWorld* w, uint32_t n, IcxProjectile* out);
+/* Projectile numbers (positions in the uploaded set, ascending) condemned by the LAST update. */
+ICX_API int icx_projectiles_condemned(IcxWorld* w, uint32_t* out, size_t cap, size_t* n);
+/* Device-timed duration (ms) of the last icx_projectiles_fixed_update kernel (CUDA events). */
+ICX_API int icx_projectiles_kernel_ms(IcxWorld* w, float* ms);
+
 /* ==== world-line record / replay / divergence scan ========================================
  * The dense ENTITY_UPDATE stream between adjacent timeslices (EntityTimestreamMap,
  * source/networking/entity_timestream_map.h:43-230) as a device-resident ring of SoA snapshots:

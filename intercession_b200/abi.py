@@ -13,11 +13,14 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libicx.so")
+LIB_PATH = os.environ.get("ICX_LIB", os.path.join(_HERE, "libicx.so"))      # ICX_LIB: tuning variants (tools/), never a fallback
 
 # ---- numpy dtypes -----------------------------------------------------------
 transform_dt = np.dtype([("origin", "<f4", 3), ("orientation", "<f4", 4), ("scale", "<f4", 3)])
 assert transform_dt.itemsize == 40
+# ProjectileComponent, source/behaviors/projectile_component.h:8-16
+projectile_dt = np.dtype([("currLifetime", "<f8"), ("maxLifetime", "<f8"), ("hz", "<f8"), ("scaleMax", "<f8"), ("scaleMin", "<f8")])
+assert projectile_dt.itemsize == 40
 
 physics_dt = np.dtype({
     "names": ["velocity", "acceleration", "angularVelocity", "angularAcceleration",
@@ -174,6 +177,11 @@ SIGNATURES = {
     "icx_debug_counters": (C.c_int, [_vp, _vp]),
     "icx_debug_trace": (C.c_int, [_vp, C.c_int, _vp, _sz, _psz]),
     "icx_phase_ms": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "icx_projectiles_upload": (C.c_int, [_vp, _u32, _vp, _vp]),
+    "icx_projectiles_fixed_update": (C.c_int, [_vp, C.c_double]),
+    "icx_projectiles_download": (C.c_int, [_vp, _u32, _vp]),
+    "icx_projectiles_condemned": (C.c_int, [_vp, _vp, _sz, _psz]),
+    "icx_projectiles_kernel_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
 }
 
 _lib = None

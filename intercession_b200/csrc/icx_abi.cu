@@ -284,12 +284,15 @@ void icx_world_destroy(IcxWorld* w)
     if (w->stream) cudaStreamSynchronize(w->stream);
     for (auto& b : w->pool) b.release();
     DeviceBuffer* extra[] = {&w->mir_ids, &w->mir_T, &w->mir_P, &w->mir_C, &w->mir_hasP, &w->st_ts, &w->st_tc, &w->st_index, &w->st_T, &w->st_P, &w->st_C,
-                             &w->d_mask, &w->st_scan, &w->cl_idx, &w->cl_ids, &w->cl_T, &w->cl_P, &w->cl_C, &w->cl_hasP, &w->cl_ts, &w->cl_tc};
+                             &w->d_mask, &w->st_scan, &w->cl_idx, &w->cl_ids, &w->cl_T, &w->cl_P, &w->cl_C, &w->cl_hasP, &w->cl_ts, &w->cl_tc,
+                             &w->pj_proj, &w->pj_index, &w->pj_condemned, &w->pj_count};
     for (auto* b : extra) b->release();
     if (w->h_counters) cudaFreeHost(w->h_counters);
     if (w->h_flags) cudaFreeHost(w->h_flags);
     if (w->ev0) cudaEventDestroy(w->ev0);
     if (w->ev1) cudaEventDestroy(w->ev1);
+    if (w->pj_ev0) cudaEventDestroy(w->pj_ev0);
+    if (w->pj_ev1) cudaEventDestroy(w->pj_ev1);
     for (auto& e : w->pev) if (e) cudaEventDestroy(e);
     if (w->stream) cudaStreamDestroy(w->stream);
     delete w;
@@ -326,6 +329,7 @@ int icx_bodies_upload(IcxWorld* w, uint32_t n, const IcxEntity* entity, const Ic
                             (uint8_t*)w->d_mask.ptr, W.first_packet, st);
     CK(cudaMemsetAsync(W.counters, 0, CTR_TOTAL * sizeof(uint32_t), st));
     W.n_entities = n; w->n_entities = n;
+    w->n_projectiles = 0; w->pj_updated = false;     // projectile rows index the previous upload order
     Mirror M = mirror_of(w);
     if (!P) M.P = nullptr;
     launch_import_kernel(W, M, nullptr, M.ids, M.T, M.P, C ? M.C : nullptr,

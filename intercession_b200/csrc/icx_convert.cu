@@ -132,6 +132,8 @@ __global__ void __launch_bounds__(128) k_export(DeviceWorld W, Mirror M, int hav
         IcxTransform& t = M.T[e];
         t.origin[0] = p.x; t.origin[1] = p.y; t.origin[2] = p.z;
         t.orientation[0] = r.x; t.orientation[1] = r.y; t.orientation[2] = r.z; t.orientation[3] = r.w;
+        const float4 sm = W.prm0[e];                       // the scale is device state too (icx_projectiles_fixed_update pulses it)
+        t.scale[0] = sm.x; t.scale[1] = sm.y; t.scale[2] = sm.z;
     }
     if (have_P && M.hasP[e]) {
         const float4 v = W.in.vel[e], a = W.in.acc[e], w = W.in.angvel[e], al = W.in.angacc[e];

@@ -74,6 +74,11 @@ struct IcxWorld {
     int resolve_blocks = 0, prepare_blocks = 0, narrow_blocks = 0;
     std::string error;
     bool have_results = false;
+    // behaviours on the device (icx_behaviors.cu): ProjectileComponent rows, their entity rows, condemned list + count
+    icx::DeviceBuffer pj_proj, pj_index, pj_condemned, pj_count;
+    uint32_t n_projectiles = 0;
+    bool pj_updated = false;
+    cudaEvent_t pj_ev0 = nullptr, pj_ev1 = nullptr;
 };
 
 // make w->active_mask valid (one small device-to-host copy after an upload); ICX_OK or ICX_E_CUDA

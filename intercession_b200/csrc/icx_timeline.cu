@@ -88,8 +88,11 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
                  :: "r"(smem_addr(bar)), "r"(parity) : "memory");
 }
 
+#ifndef SCAN_TILE
 #define SCAN_TILE 1024          // bodies per stage: 2 x 16 KB
 #define SCAN_STAGES 3
+#define SCAN_CTAS 2             // persistent CTAs per SM
+#endif
 #define SCAN_TPB 256
 
 // TimejumpConditions::operator== (timejump_conditions.h:21-25): congruent <=> length2(a - b) <= 2.0f.
@@ -102,17 +105,30 @@ __global__ void __launch_bounds__(SCAN_TPB) k_divergence_scan(const float4* __re
     extern __shared__ __align__(128) unsigned char smem[];
     float4* s_live = reinterpret_cast<float4*>(smem);                                   // [STAGES][TILE]
     float4* s_snap = s_live + SCAN_STAGES * SCAN_TILE;
-    uint64_t* bar = reinterpret_cast<uint64_t*>(s_snap + SCAN_STAGES * SCAN_TILE);      // [STAGES]
+    uint64_t* bar = reinterpret_cast<uint64_t*>(s_snap + SCAN_STAGES * SCAN_TILE);      // [STAGES + 1]
     const uint32_t n_tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    // A base history shared by all world-lines (config 4: n_snap = one world-line) that fits the snapshot stages is
+    // loaded ONCE per CTA and stays resident: re-fetching the same 16 KB for every tile made all CTAs hammer the same
+    // few L2 slices, and the batch scan ran at half the speed of the single-world case.
+    const bool resident = n_snap != n && n_snap <= SCAN_STAGES * SCAN_TILE;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < SCAN_STAGES; s++) mbar_init(&bar[s], 1);
+        for (int s = 0; s <= SCAN_STAGES; s++) mbar_init(&bar[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+    if (resident && threadIdx.x == 0) {
+        mbar_expect_tx(&bar[SCAN_STAGES], n_snap * 16u);
+        bulk_load(s_snap, snap, n_snap * 16u, &bar[SCAN_STAGES]);
+    }
     // tile -> source range of the snapshot: the whole snapshot is addressed modulo n_snap (a base
     // history shared by all world-lines); SCAN_TILE divides n_snap or n_snap == n is required by the host
     auto issue = [&](uint32_t tile, int stage) {
         const uint32_t first = tile * SCAN_TILE, cnt = min((uint32_t)SCAN_TILE, n - first);
+        if (resident) {
+            mbar_expect_tx(&bar[stage], cnt * 16u);
+            bulk_load(s_live + stage * SCAN_TILE, live + first, cnt * 16u, &bar[stage]);
+            return;
+        }
         const uint32_t sfirst = n_snap == n ? first : first % n_snap;
         mbar_expect_tx(&bar[stage], cnt * 32u);
         bulk_load(s_live + stage * SCAN_TILE, live + first, cnt * 16u, &bar[stage]);
@@ -121,15 +137,34 @@ __global__ void __launch_bounds__(SCAN_TPB) k_divergence_scan(const float4* __re
     uint32_t my = 0;                                        // tiles this CTA has consumed
     if (threadIdx.x == 0)
         for (int s = 0; s < SCAN_STAGES - 1; s++) { const uint32_t t = blockIdx.x + s * gridDim.x; if (t < n_tiles) issue(t, s); }
+    // When a tile never straddles two world-lines (one world, or world-lines of whole tiles: the config-4 batch), every
+    // thread accumulates in registers and a warp reduces + publishes ONCE per world-line it has seen -- once per kernel for
+    // a single world.  Integer accumulation: the sums do not depend on the order, so both paths give the same bits.
+    const bool tile_uniform = stride == 0u || stride % SCAN_TILE == 0u;
+    const uint32_t FULL = 0xFFFFFFFFu;
+    uint32_t acc_bad = 0, acc_wl = 0xFFFFFFFFu; unsigned long long acc_q = 0;
+    auto publish = [&]() {                                  // warp-uniform call
+        if (acc_wl == 0xFFFFFFFFu) return;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { acc_bad += __shfl_xor_sync(FULL, acc_bad, o); acc_q += __shfl_xor_sync(FULL, acc_q, o); }
+        if ((threadIdx.x & 31u) == 0) { if (acc_bad) atomicAdd(&wl_count[acc_wl], acc_bad); if (acc_q) atomicAdd(&wl_score[acc_wl], acc_q); }
+        acc_bad = 0; acc_q = 0;
+    };
     for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, my++) {
         const int stage = my % SCAN_STAGES;
         if (threadIdx.x == 0) {                             // keep STAGES-1 tiles in flight
             const uint32_t t = tile + (SCAN_STAGES - 1) * gridDim.x;
             if (t < n_tiles) issue(t, (my + SCAN_STAGES - 1) % SCAN_STAGES);
         }
-        mbar_wait(&bar[stage], (my / SCAN_STAGES) & 1u);
         const uint32_t first = tile * SCAN_TILE, cnt = min((uint32_t)SCAN_TILE, n - first);
-        const float4* a = s_live + stage * SCAN_TILE; const float4* b = s_snap + stage * SCAN_TILE;
+        if (tile_uniform) {
+            const uint32_t wl_t = stride ? first / stride : 0u;
+            if (wl_t != acc_wl) { publish(); acc_wl = wl_t; }
+        }
+        if (resident && my == 0) mbar_wait(&bar[SCAN_STAGES], 0u);
+        mbar_wait(&bar[stage], (my / SCAN_STAGES) & 1u);
+        const float4* a = s_live + stage * SCAN_TILE;
+        const float4* b = resident ? s_snap + first % n_snap : s_snap + stage * SCAN_TILE;
 #pragma unroll
         for (uint32_t k = 0; k < SCAN_TILE / SCAN_TPB; k++) {
             const uint32_t i = k * SCAN_TPB + threadIdx.x;
@@ -141,10 +176,10 @@ __global__ void __launch_bounds__(SCAN_TPB) k_divergence_scan(const float4* __re
                 bad = (len2 <= 2.0f) ? 0u : 1u;
                 const float c = (len2 <= 1048576.0f) ? len2 : 1048576.0f;
                 q = __float2ull_rz(c * 65536.0f);
-                wl = stride ? (first + i) / stride : 0u;
+                if (!tile_uniform) wl = (first + i) / stride;
             }
-            // one atomic per warp when the whole warp is in one world-line (the usual case)
-            const uint32_t FULL = 0xFFFFFFFFu;
+            if (tile_uniform) { acc_bad += bad; acc_q += q; continue; }
+            // ragged world-lines: one atomic per warp when the whole warp is in one world-line
             const uint32_t wl0 = __shfl_sync(FULL, wl, 0);
             if (__all_sync(FULL, wl == wl0)) {
                 if (wl0 != 0xFFFFFFFFu) {
@@ -159,6 +194,7 @@ __global__ void __launch_bounds__(SCAN_TPB) k_divergence_scan(const float4* __re
         }
         __syncthreads();                                    // the stage may be refilled
     }
+    if (tile_uniform) publish();
 }
 
 // Fork ageing, server_network_dynamo.cpp:681-705 (thresholds :13-15).  The comparison is the
@@ -342,11 +378,11 @@ int icx_divergence_scan(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, uint32
     cudaStream_t st = w->stream;
     TCK(cudaMemsetAsync(tl->d_score, 0, (size_t)n_worldlines * 8, st)); TCK(cudaMemsetAsync(tl->d_count, 0, (size_t)n_worldlines * 4, st));
     if (n) {
-        const size_t smem = (size_t)2 * SCAN_STAGES * SCAN_TILE * sizeof(float4) + SCAN_STAGES * sizeof(uint64_t);
+        const size_t smem = (size_t)2 * SCAN_STAGES * SCAN_TILE * sizeof(float4) + (SCAN_STAGES + 1) * sizeof(uint64_t);
         static bool attr_set[64] = {};
         if (!attr_set[w->device & 63]) { TCK(cudaFuncSetAttribute(k_divergence_scan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_set[w->device & 63] = true; }
         const uint32_t n_tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
-        const int blocks = (int)std::min<uint32_t>(n_tiles, 148 * 2);
+        const int blocks = (int)std::min<uint32_t>(n_tiles, 148 * SCAN_CTAS);
         if (tl->profile) cudaEventRecord(tl->pev[2][0], st);
         k_divergence_scan<<<blocks, SCAN_TPB, smem, st>>>(w->W.in.pos, tl->state + (size_t)s * 6 * tl->n_max, n, n_snap, stride, tl->d_count, tl->d_score);
         if (tl->profile) { cudaEventRecord(tl->pev[2][1], st); tl->pev_used[2] = true; }

@@ -121,6 +121,33 @@ class World:
         self._ck(self.lib.icx_stats_fetch(self.handle, C.byref(st)))
         return st
 
+    # ---- ProjectileBehaviors::on_fixed_update on the device (behaviors/projectile_behaviors.h:17-54) ----
+    def projectiles_upload(self, index, proj):
+        index = np.ascontiguousarray(index, np.uint32)
+        proj = np.ascontiguousarray(proj, abi.projectile_dt)
+        assert len(index) == len(proj)
+        self._n_proj = len(proj)
+        self._ck(self.lib.icx_projectiles_upload(self.handle, len(proj), abi.ptr(index), abi.ptr(proj)))
+
+    def projectiles_fixed_update(self, dt):
+        self._ck(self.lib.icx_projectiles_fixed_update(self.handle, dt))
+
+    def projectiles_download(self):
+        out = np.zeros(self._n_proj, abi.projectile_dt)
+        self._ck(self.lib.icx_projectiles_download(self.handle, len(out), abi.ptr(out)))
+        return out
+
+    def projectiles_condemned(self):
+        out = np.zeros(max(self._n_proj, 1), np.uint32)
+        n = C.c_size_t(0)
+        self._ck(self.lib.icx_projectiles_condemned(self.handle, abi.ptr(out), len(out), C.byref(n)))
+        return out[:n.value]
+
+    def projectiles_kernel_ms(self):
+        ms = C.c_float(0)
+        self._ck(self.lib.icx_projectiles_kernel_ms(self.handle, C.byref(ms)))
+        return ms.value
+
     def last_step_ms(self):
         ms = C.c_float(0)
         self._ck(self.lib.icx_last_step_ms(self.handle, C.byref(ms)))

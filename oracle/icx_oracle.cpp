@@ -992,4 +992,24 @@ int icxo_fork_age(uint32_t n, uint8_t* tstate, uint16_t* tcoh, uint16_t coherenc
     return 0;
 }
 
+// ProjectileBehaviors::on_fixed_update, behaviors/projectile_behaviors.h:17-54, n_updates fixed steps.
+// T[i] is the transform of projectile i's entity.  A condemned entity is destroyed by the next
+// Cosmos::update (cosmos.cpp:29-36) and receives no further updates.
+int icxo_projectile_update(uint32_t n, double dt, uint32_t n_updates, IcxTransform* T, IcxProjectile* proj, uint8_t* condemned)
+{
+    for (uint32_t i = 0; i < n; i++) condemned[i] = 0;
+    for (uint32_t u = 0; u < n_updates; u++)
+        for (uint32_t i = 0; i < n; i++) {
+            if (condemned[i]) continue;
+            IcxProjectile& p = proj[i];
+            p.currLifetime += dt;                                                      // :33
+            const double s = std::sin(p.currLifetime * p.hz);                         // :35
+            const double amp = (p.scaleMax - p.scaleMin) / 2.0;                        // :38
+            const float sc = static_cast<float>(s * amp + (p.scaleMin + 1.0));         // :39
+            T[i].scale[0] = sc; T[i].scale[1] = sc; T[i].scale[2] = sc;
+            if (p.currLifetime > p.maxLifetime) condemned[i] = 1;                      // :41-44
+        }
+    return 0;
+}
+
 } // extern "C"

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstring>
 #include "../../intercession_b200/host/timeline_api.hpp"
+#include "../../intercession_b200/host/projectile_behaviors.hpp"
 
 using namespace icx_host;
 
@@ -84,6 +85,14 @@ int main(int argc, char** argv)
         const bool congruent = timeline.is_congruent(dynamo, (uint16_t)(ticks - 1));
         std::printf("callbacks %d interceptions %d ground_normal %.6g %.6g %.6g congruent %d\n", n_callbacks, n_interceptions,
                     last_ground[0], last_ground[1], last_ground[2], congruent ? 1 : 0);
+        // ProjectileBehaviors on the device: the "point" sphere (row 2) becomes a projectile about to expire
+        ProjectileBehaviors projectiles(dynamo.world());
+        ProjectileComponent pc{299.99, 300.0, 1.0, 2.0, 1.0};
+        projectiles.attach({2u}, {pc});
+        projectiles.on_fixed_update(1.0 / 60);
+        std::vector<ProjectileComponent> back;
+        projectiles.fetch(back);
+        std::printf("projectile life %.17g condemned %zu\n", back[0].currLifetime, projectiles.condemned().size());
     } catch (const std::exception& e) {
         std::printf("error: %s\n", e.what());
         return 2;

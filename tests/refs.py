@@ -28,6 +28,7 @@ REF_SIGS = {
     "icxref_collide": _collide_sig(),
     "icxref_intersect": (C.c_int, [_vp, _vp, _vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp]),
     "icxref_response": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "icxref_projectile_update": (C.c_int, [_u32, _dbl, _u32, _vp, _vp, _vp]),
 }
 
 
@@ -48,6 +49,7 @@ ORACLE_SIGS = {
     "icxo_response": REF_SIGS["icxref_response"],
     "icxo_aabbs": (C.c_int, [_u32, _vp, _vp, C.c_float, _vp, _sz, _psz]),
     "icxo_pairs": (C.c_int, [_u32, _vp, _vp, C.c_float, _u32, _u32, C.c_int, _vp, _sz, _psz]),
+    "icxo_projectile_update": REF_SIGS["icxref_projectile_update"],
 }
 
 _ref = None
@@ -192,3 +194,12 @@ def oracle_fork_age(s, coherency):
     n, need = C.c_uint32(0), C.c_int(0)
     oracle().icxo_fork_age(out.n, abi.ptr(out.tstate), abi.ptr(out.tcoh), coherency, C.byref(n), C.byref(need))
     return out, n.value, bool(need.value)
+
+
+def projectile_update(lib, prefix, T, proj, dt, n_updates=1):
+    """ProjectileBehaviors::on_fixed_update through a checker: returns (scale per projectile, components, condemned)."""
+    T, proj = T.copy(), proj.copy()
+    condemned = np.zeros(len(proj), np.uint8)
+    rc = getattr(lib, prefix + "_projectile_update")(len(proj), dt, n_updates, abi.ptr(T), abi.ptr(proj), abi.ptr(condemned))
+    assert rc == 0
+    return T["scale"].copy(), proj, condemned

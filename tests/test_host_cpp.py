@@ -49,4 +49,7 @@ def test_host_mirror_reproduces_case_study(exe):
             assert abs(float(w[6])) > 0.9                     # ground normal is +-y
             assert int(w[-1]) == 1
             seen += 1
-    assert seen == 4
+        elif w[0] == "projectile":                            # 299.99 + 1/60 > maxLifetime 300: condemned by the first update
+            assert float(w[2]) == 299.99 + 1.0 / 60 and int(w[4]) == 1
+            seen += 1
+    assert seen == 5
