@@ -264,7 +264,10 @@ __device__ __forceinline__ void warp_emit(const DeviceWorld& W, PairStage& S, Wa
     if (ws.n_loose > WSTAGE - 32) warp_flush(W, S.loose[wid], ws.n_loose, CTR_CANDIDATES, W.pairs, nullptr, 0);
 }
 
-__global__ void __launch_bounds__(PAIRS_TPB, 4) k_pairs(DeviceWorld W)
+#ifndef PAIRS_MINB
+#define PAIRS_MINB 4
+#endif
+__global__ void __launch_bounds__(PAIRS_TPB, PAIRS_MINB) k_pairs(DeviceWorld W)
 {
     __shared__ PairStage S;
     const uint32_t tid = threadIdx.x;
