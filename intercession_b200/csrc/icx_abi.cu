@@ -48,7 +48,8 @@ int allocate(IcxWorld* w)
     CK(alloc(w, W.pk_entity, np)); CK(alloc(w, W.pk_lpos, np)); CK(alloc(w, W.pk_lrot, np)); CK(alloc(w, W.pk_lscale, np));
     CK(alloc(w, W.pk_mat0, np)); CK(alloc(w, W.pk_damping, np)); CK(alloc(w, W.pk_minparam, np));
     CK(alloc(w, W.pk_d, np * 6)); CK(alloc(w, W.pk_lo, np)); CK(alloc(w, W.pk_hi, np)); CK(alloc(w, W.pk_cell, np));
-    W.n_buckets = std::max<uint32_t>(next_pow2((uint32_t)std::min<size_t>(2 * np, 1u << 24)), 1024u);
+    W.n_buckets = std::max<uint32_t>(next_pow2((uint32_t)std::min<size_t>(2 * np, 1u << 24)), 1024u);     // capacity; resized per upload
+    w->cap_buckets = W.n_buckets;
     CK(alloc(w, W.cell_count, (size_t)W.n_buckets + 4)); CK(alloc(w, W.cell_fill, (size_t)W.n_buckets));
     CK(alloc(w, W.scan_partial, 4096 + 8));
     CK(alloc(w, W.s_lo, np)); CK(alloc(w, W.s_hi, np));
@@ -342,6 +343,7 @@ int icx_bodies_upload(IcxWorld* w, uint32_t n, const IcxEntity* entity, const Ic
     const uint32_t np = w->h_flags[1];
     W.n_packets = np; w->n_packets = np;
     if (np > w->cap_packets || np >= (1u << 28)) { W.n_entities = 0; W.n_packets = 0; w->n_entities = 0; w->n_packets = 0; return fail(w, ICX_E_CAPACITY, "upload: too many active colliders"); }
+    icx_size_buckets(w);
     if (!(w->cfg.cell_size > 0)) {
         float ext; std::memcpy(&ext, &w->h_counters[CTR_EXTENT], 4);
         if (!(ext > 0)) ext = 1.0f;

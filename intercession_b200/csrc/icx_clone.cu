@@ -107,6 +107,7 @@ int icx_world_clone(IcxWorld* src, IcxWorld* dst, const uint8_t* has_future, uin
     dst->masks_on_host = true;
     CKW(dst, cudaMemsetAsync(W.counters, 0, CTR_TOTAL * sizeof(uint32_t), st));
     W.n_entities = nk; W.n_packets = np; dst->n_entities = nk; dst->n_packets = np;
+    icx_size_buckets(dst);
     W.coherency = src->W.coherency;                                                 // :91 set_coherency(source)
     Mirror M = mirror(dst);
     if (!dst->have_P) M.P = nullptr;

@@ -50,7 +50,7 @@ struct IcxWorld {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     icx::DeviceWorld W;                 // device pointers + parameters (in/out already oriented)
     std::vector<icx::DeviceBuffer> pool;
-    uint32_t cap_entities = 0, cap_packets = 0;
+    uint32_t cap_entities = 0, cap_packets = 0, cap_buckets = 0;
     uint32_t n_entities = 0, n_packets = 0;
     std::vector<uint8_t> active_mask;   // per entity: bit s = collider slot s active (packet structure); see icx_host_masks()
     bool masks_on_host = false;         // active_mask mirrors d_mask (fetched on demand: only update / clone / extract need it)
@@ -80,6 +80,18 @@ struct IcxWorld {
     bool pj_updated = false;
     cudaEvent_t pj_ev0 = nullptr, pj_ev1 = nullptr;
 };
+
+// Grid buckets for the colliders actually active: the table is allocated for the capacity (2 colliders per entity), but the
+// per-tick memsets and scans run over n_buckets, so a world with one collider per entity should not pay for twice that.
+#ifndef ICX_BUCKET_FACTOR
+#define ICX_BUCKET_FACTOR 2u
+#endif
+inline void icx_size_buckets(IcxWorld* w)
+{
+    uint32_t nb = 1024u;
+    while (nb < ICX_BUCKET_FACTOR * w->n_packets && nb < w->cap_buckets) nb <<= 1;
+    w->W.n_buckets = nb < w->cap_buckets ? nb : w->cap_buckets;
+}
 
 // make w->active_mask valid (one small device-to-host copy after an upload); ICX_OK or ICX_E_CUDA
 int icx_host_masks(IcxWorld* w);
