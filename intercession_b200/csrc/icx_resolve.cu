@@ -283,6 +283,27 @@ __device__ __forceinline__ SatPick sat_warp(const Shape& X, const Shape& Y, bool
     return sat_pick_warp(r, lane < 15);
 }
 
+// The same loop on ONE lane (lane-parallel items, see round_execute_lanes): the serial axis loop of box_box_intersect /
+// sphere_box_intersect itself, collision_procedures.cpp:76-118 -- same arithmetic per axis, first strict minimum.
+__device__ __forceinline__ SatPick sat_serial(const Shape& X, const Shape& Y, bool x_is_sphere)
+{
+    const M3 nX = transpose(X.inv), nY = transpose(Y.inv);
+    V3 cX[8], cY[8];
+    box_corners(Y.M, cY);
+    const V3 sO = xform(X.M, 0.0f, 0.0f, 0.0f);
+    const float projRadius = length(xform(X.M, ICX_UNIT_RADIUS, 0.0f, 0.0f) - sO);
+    if (!x_is_sphere) box_corners(X.M, cX);
+    SatPick p; p.separated = false; p.normal = v3(0.0f, 0.0f, 0.0f); p.depth = INFINITY;
+#pragma unroll 1
+    for (int a = 0; a < 15; a++) {
+        const AxisResult r = x_is_sphere ? sphere_box_axis(nX, nY, sO, projRadius, cY, a) : box_box_axis(nX, nY, cX, cY, a);
+        if (r.skip) continue;
+        if (r.pen <= 0) { p.separated = true; break; }                              // :107
+        if (r.pen < p.depth) { p.depth = r.pen; p.normal = r.flip ? -r.axis : r.axis; }   // :113-117
+    }
+    return p;
+}
+
 // everything one side of a pair contributes, fetched in ONE batch of independent loads
 struct SideData { float4 pos, vel, angvel, acc, angacc, prm0, prm1, mat0, lscale, pos0, d[6]; float damping, minparam; uint32_t slot, ts, id; };
 
@@ -337,9 +358,15 @@ __device__ __forceinline__ void store_side(const DeviceWorld& W, uint32_t e, con
 // pa < pb, executed by a whole warp (all lanes pass the same arguments).  n_dirty: bodies with
 // dirty_slot < n_dirty may be written; a hit on any other mutable body aborts the attempt (see the
 // file header).
-__device__ __forceinline__ void process_pair(const DeviceWorld& W, uint32_t pa, uint32_t pb, uint32_t n_dirty, uint32_t ctr_new, V3* scratch)
+// LANE = false: a whole warp runs ONE pair (all lanes pass the same arguments, lane 0 finishes and writes).
+// LANE = true: every lane with `active` runs ITS OWN pair from start to end -- the plain SIMT form; the serial work
+// that keeps 31 lanes idle in warp mode (manifold, clipping, response: ~35 k cycles) then runs for up to 32 pairs at once,
+// with thread-local scratch (all lanes active: local memory lines are fully used).
+template <bool LANE>
+__device__ __forceinline__ void process_pair(const DeviceWorld& W, uint32_t pa, uint32_t pb, uint32_t n_dirty, uint32_t ctr_new, V3* scratch, bool active = true)
 {
-    const bool writer = (threadIdx.x & 31u) == 0u;
+    if (LANE && !active) return;
+    const bool writer = LANE ? true : (threadIdx.x & 31u) == 0u;
 #ifdef ICX_PROFILE_PAIR
     const long long tp0 = clock64();
 #endif
@@ -359,14 +386,19 @@ __device__ __forceinline__ void process_pair(const DeviceWorld& W, uint32_t pa, 
     SatPick pick; pick.separated = true; pick.normal = h.normal; pick.depth = 0.0f;
     const bool bb = tA == ICX_COLLIDER_BOX && tB == ICX_COLLIDER_BOX, sb = tA == ICX_COLLIDER_SPHERE && tB == ICX_COLLIDER_BOX,
                bs = tA == ICX_COLLIDER_BOX && tB == ICX_COLLIDER_SPHERE;
-    if (bb || sb || bs) pick = sat_warp(bs ? B : A, bs ? A : B, !bb);               // one instantiation: the code has to stay small (instruction cache)
+    if (bb || sb || bs) pick = LANE ? sat_serial(bs ? B : A, bs ? A : B, !bb)
+                                    : sat_warp(bs ? B : A, bs ? A : B, !bb);        // one instantiation per mode: the code has to stay small (instruction cache)
 #ifdef ICX_PROFILE_PAIR
     if (writer) { atomicAdd(&W.counters[CTR_PROF + 5], (uint32_t)((clock64() - tp0) >> 4)); atomicAdd(&W.counters[CTR_PROF + 6], pick.separated ? 0u : 1u); }
 #endif
     if (!writer) return;
     bool hit = false;
     if (bb) {
-        if (!pick.separated) { h.normal = pick.normal; h.depth = pick.depth; hit = box_box_finish_s(A, B, h, scratch, scratch + 8, scratch + 8 + ICX_MAXV); }
+        if (!pick.separated) {
+            h.normal = pick.normal; h.depth = pick.depth;
+            if (LANE) hit = box_box_finish(A, B, h);
+            else hit = box_box_finish_s(A, B, h, scratch, scratch + 8, scratch + 8 + ICX_MAXV);
+        }
     } else if (sb) {
         if (!pick.separated) { h.normal = pick.normal; h.depth = pick.depth; hit = sphere_box_finish(xform(A.M, 0.0f, 0.0f, 0.0f), xform(A.M, ICX_UNIT_RADIUS, 0.0f, 0.0f), h); }
     } else if (bs) {                                                                // box_sphere_intersect, .cpp:233-247
@@ -746,7 +778,8 @@ __device__ __forceinline__ void round_select(const DeviceWorld& W, uint32_t s, u
 // BEFORE the exact procedure and arrive while it runs.  One-sided pairs that follow need no
 // partner and are executed at once -- through the same process_pair call site: the procedure is
 // ~85 KB of code and must exist once.
-__device__ __forceinline__ void round_execute(const DeviceWorld& W, uint4 item, uint32_t n_dirty, int parity, uint32_t ctr_out, uint32_t ctr_new, V3* scratch)
+__device__ __forceinline__ void round_execute(const DeviceWorld& W, uint4 item, uint32_t n_dirty, int parity, uint32_t ctr_out, uint32_t ctr_new, V3* scratch,
+                                              bool first_done = false)
 {
     const uint32_t FULL = 0xFFFFFFFFu, lane = threadIdx.x & 31u;
 #ifdef ICX_PROFILE_PAIR
@@ -758,8 +791,8 @@ __device__ __forceinline__ void round_execute(const DeviceWorld& W, uint4 item, 
     if (my_s != ICX_NONE) { my_info = W.slot_info[my_s]; my_hw = W.head[parity][my_s]; }
 
     uint32_t pa = item.x, pb = item.y & ICX_NB_INDEX_MASK;
-    bool run = true;
-    if (item.y & ICX_ITEM_CHECK) run = may_hit_warp(W, pa, pb, W.pk_entity[pa], W.pk_entity[pb]);
+    bool run = !first_done;                                                         // lane mode: the item's own pair has been executed already
+    if (run && (item.y & ICX_ITEM_CHECK)) run = may_hit_warp(W, pa, pb, W.pk_entity[pa], W.pk_entity[pb]);
     int side = 0; bool entered = false;                                             // body being walked; its cursor is loaded
     Cursor c; uint32_t hw = 0, k_run = 0;
     c.p0 = c.npk = c.n0 = c.n1 = c.e = 0; c.l0 = c.l1 = nullptr;
@@ -768,7 +801,7 @@ __device__ __forceinline__ void round_execute(const DeviceWorld& W, uint4 item, 
 #ifdef ICX_PROFILE_PAIR
             const long long tq = clock64();
 #endif
-            process_pair(W, pa, pb, n_dirty, ctr_new, scratch);
+            process_pair<false>(W, pa, pb, n_dirty, ctr_new, scratch);
             __syncwarp();
 #ifdef ICX_PROFILE_PAIR
             t_pair += clock64() - tq;
@@ -826,7 +859,12 @@ __device__ __forceinline__ void trace_mark(const DeviceWorld& W, uint32_t& n, ui
 // the exact procedures).  So the first attempt is split over two cooperative launches with different shapes:
 // PHASE 0 = prepare (2 x 384 threads per SM), PHASE 1 = rounds (1 x 256 threads per SM, 251 registers) --
 // which also carries the whole loop for the rare restarts.
+#ifndef ICX_LANE_MIN
+#define ICX_LANE_MIN 4u          // items per warp from which a round runs lane-parallel (break-even measured at ~4: the lane-parallel pass costs ~40 us flat, a warp-mode item ~19 us, a cursor walk ~9.5 us)
+#endif
+#ifndef RESOLVE_TPB
 #define RESOLVE_TPB 256
+#endif
 #define PREPARE_TPB 384
 template <int PHASE>
 __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, int do_euler, V3* scratch)
@@ -923,12 +961,28 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
             grid.sync();
             const uint32_t n_items = ctr[ctr_items];
             // items differ 3x in cost (filter miss ... box-box hit with clipping): warps fetch them one by one
+            // A fat round (more than ICX_LANE_MIN items per warp) is throughput-bound on the single finishing lane: there a warp
+            // takes a batch of items, runs their exact pairs lane-parallel (one item per lane; the items of a round touch
+            // disjoint bodies), then walks the cursors of the batch item by item as a warp.  Thin rounds keep one item per warp.
+            const uint32_t per_warp = (n_items + (nth >> 5) - 1u) / (nth >> 5);
+            const uint32_t batch = per_warp >= ICX_LANE_MIN ? min(per_warp, 32u) : 1u;
             for (;;) {
                 uint32_t i = 0;
-                if ((tid & 31u) == 0u) i = atomicAdd(&W.counters[CTR_FETCH + (rounds & 1u)], 1u);
+                if ((tid & 31u) == 0u) i = atomicAdd(&W.counters[CTR_FETCH + (rounds & 1u)], batch);
                 i = __shfl_sync(0xFFFFFFFFu, i, 0);
                 if (i >= n_items) break;
-                round_execute(W, W.items[i], n_dirty, parity, ctr_out, CTR_NEWD + rounds % 3u, scratch);
+                if (batch == 1u) { round_execute(W, W.items[i], n_dirty, parity, ctr_out, CTR_NEWD + rounds % 3u, scratch); continue; }
+                const uint32_t cnt = min(batch, n_items - i), lane = tid & 31u;
+                uint4 mine = make_uint4(0u, 0u, ICX_NONE, ICX_NONE);
+                if (lane < cnt) mine = W.items[i + lane];
+                process_pair<true>(W, mine.x, mine.y & ICX_NB_INDEX_MASK, n_dirty, CTR_NEWD + rounds % 3u, scratch, lane < cnt);
+                __syncwarp();
+                for (uint32_t j = 0; j < cnt; j++) {
+                    uint4 it;
+                    it.x = __shfl_sync(0xFFFFFFFFu, mine.x, j); it.y = __shfl_sync(0xFFFFFFFFu, mine.y, j);
+                    it.z = __shfl_sync(0xFFFFFFFFu, mine.z, j); it.w = __shfl_sync(0xFFFFFFFFu, mine.w, j);
+                    round_execute(W, it, n_dirty, parity, ctr_out, CTR_NEWD + rounds % 3u, scratch, true);
+                }
             }
             grid.sync();
             if (tid == 0) trace_mark(W, tn, 0x30000u | min(n_items, 0xFFFFu));
