@@ -744,6 +744,36 @@ __device__ __forceinline__ void settle_warp(const DeviceWorld& W, uint32_t s, co
     }
 }
 
+// The walk on ONE lane (lane-parallel items): the merged queue order is cursor_head's, the verdict per entry is the
+// warp version's -- two-sided entries stop the walk, one-sided ones need overlapping un-inflated bounds (mine translated
+// by what static resolution moved me) and the conservative filter, here sat_may_hit itself (same arithmetic per axis).
+__device__ __forceinline__ uint32_t skip_rejects_lane(const DeviceWorld& W, const Cursor& c, uint32_t hw, uint32_t n_dirty,
+                                                      int& kind, uint32_t& k_out, uint32_t& o_out)
+{
+    const float4 pe = W.out.pos[c.e], pe0 = W.pos0[c.e];
+    const float dx = pe.x - pe0.x, dy = pe.y - pe0.y, dz = pe.z - pe0.z;
+    kind = 0; k_out = 0; o_out = 0;
+#pragma unroll 1
+    for (;;) {
+        uint32_t k, entry, eo;
+        if (!cursor_head(c, hw, k, entry, eo)) return hw;
+        const uint32_t p = c.p0 + k, o = entry & ICX_NB_INDEX_MASK;
+        const uint32_t ds = (entry & ICX_NB_IMMUTABLE) ? ICX_NONE : W.dirty_slot[eo];
+        if (ds < n_dirty) { kind = 1; return hw; }
+        float4 alo = W.pk_lo[p], ahi = W.pk_hi[p];
+        const float4 blo = W.pk_lo[o], bhi = W.pk_hi[o];
+        alo.x += dx; alo.y += dy; alo.z += dz; ahi.x += dx; ahi.y += dy; ahi.z += dz;
+        if (tight_overlap(alo, ahi, blo, bhi, W.margin)) {
+            const uint32_t qa = min(p, o), qb = max(p, o), ea = p < o ? c.e : eo, eb = p < o ? eo : c.e;
+            const int tA = __float_as_uint(W.pk_lpos[qa].w) & PF_TYPE_MASK, tB = __float_as_uint(W.pk_lpos[qb].w) & PF_TYPE_MASK;
+            const bool mh = !is_sat_pair(tA, tB)
+                            || sat_may_hit(W.pk_d + (size_t)qa * 6, W.pk_d + (size_t)qb * 6, v3(W.out.pos[ea]), v3(W.out.pos[eb]), tA, tB, 0.0f);
+            if (mh) { kind = 2; k_out = k; o_out = o; return hw; }
+        }
+        hw = cursor_advance(hw, k);
+    }
+}
+
 __device__ __forceinline__ void round_select(const DeviceWorld& W, uint32_t s, uint32_t n_dirty, int parity, uint32_t ctr_out, uint32_t ctr_items)
 {
     const uint32_t* __restrict__ hin = W.head[parity];
@@ -840,6 +870,49 @@ __device__ __forceinline__ void round_execute(const DeviceWorld& W, uint4 item, 
 #ifdef ICX_PROFILE_PAIR
     PROF_ADD(0, 1); PROF_ADD(1, t_pair >> 4); PROF_ADD(2, (clock64() - t0 - t_pair) >> 4);
 #endif
+}
+
+// Up to 32 work items by one warp, one per lane, from the exact pair to the end of its cursor walks (the scalar form of
+// round_execute).  All lanes meet at ONE process_pair call site per iteration: a lane whose walk found a one-sided pair
+// to execute brings it to the next iteration, the others idle there.
+__device__ __forceinline__ void round_execute_lanes(const DeviceWorld& W, uint4 item, bool active, uint32_t n_dirty, int parity, uint32_t ctr_out, uint32_t ctr_new)
+{
+    const uint32_t FULL = 0xFFFFFFFFu;
+    uint32_t pa = item.x, pb = item.y & ICX_NB_INDEX_MASK;
+    bool run = active, done = !active, entered = false;
+    int side = 0;
+    Cursor c; uint32_t hw = 0, k_run = 0;
+    c.p0 = c.npk = c.n0 = c.n1 = c.e = 0; c.l0 = c.l1 = nullptr;
+#pragma unroll 1
+    while (__any_sync(FULL, !done)) {
+        process_pair<true>(W, pa, pb, n_dirty, ctr_new, nullptr, run && !done);
+        if (done) continue;
+        run = false;
+#pragma unroll 1
+        for (; side < 2; side++) {
+            const uint32_t sb = side ? item.w : item.z;
+            if (sb == ICX_NONE) continue;
+            if (!entered) {                                                         // step over the entry just executed
+                c = load_cursor(W, sb);
+                hw = W.head[parity][sb];
+                uint32_t k, entry, eo;
+                cursor_head(c, hw, k, entry, eo);
+                hw = cursor_advance(hw, k);
+                entered = true;
+            } else hw = cursor_advance(hw, k_run);                                  // a follow-up pair was executed
+            int kind; uint32_t kk, oo;
+            hw = skip_rejects_lane(W, c, hw, n_dirty, kind, kk, oo);
+            if (kind == 2) {                                                        // one-sided pair the filter keeps: next iteration
+                const uint32_t p = c.p0 + kk;
+                k_run = kk; pa = min(p, oo); pb = max(p, oo); run = true;
+                break;
+            }
+            W.head[parity ^ 1][sb] = hw;
+            if (cursor_pending(c, hw)) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = sb;
+            entered = false;
+        }
+        if (!run) done = true;
+    }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -962,8 +1035,8 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
             const uint32_t n_items = ctr[ctr_items];
             // items differ 3x in cost (filter miss ... box-box hit with clipping): warps fetch them one by one
             // A fat round (more than ICX_LANE_MIN items per warp) is throughput-bound on the single finishing lane: there a warp
-            // takes a batch of items, runs their exact pairs lane-parallel (one item per lane; the items of a round touch
-            // disjoint bodies), then walks the cursors of the batch item by item as a warp.  Thin rounds keep one item per warp.
+            // takes a batch of items and runs them lane-parallel, one item per lane from the exact pair to the end of its cursor
+            // walks (the items of a round touch disjoint bodies).  Thin rounds keep one item per warp.
             const uint32_t per_warp = (n_items + (nth >> 5) - 1u) / (nth >> 5);
             const uint32_t batch = per_warp >= ICX_LANE_MIN ? min(per_warp, 32u) : 1u;
             for (;;) {
@@ -975,14 +1048,8 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
                 const uint32_t cnt = min(batch, n_items - i), lane = tid & 31u;
                 uint4 mine = make_uint4(0u, 0u, ICX_NONE, ICX_NONE);
                 if (lane < cnt) mine = W.items[i + lane];
-                process_pair<true>(W, mine.x, mine.y & ICX_NB_INDEX_MASK, n_dirty, CTR_NEWD + rounds % 3u, scratch, lane < cnt);
+                round_execute_lanes(W, mine, lane < cnt, n_dirty, parity, ctr_out, CTR_NEWD + rounds % 3u);
                 __syncwarp();
-                for (uint32_t j = 0; j < cnt; j++) {
-                    uint4 it;
-                    it.x = __shfl_sync(0xFFFFFFFFu, mine.x, j); it.y = __shfl_sync(0xFFFFFFFFu, mine.y, j);
-                    it.z = __shfl_sync(0xFFFFFFFFu, mine.z, j); it.w = __shfl_sync(0xFFFFFFFFu, mine.w, j);
-                    round_execute(W, it, n_dirty, parity, ctr_out, CTR_NEWD + rounds % 3u, scratch, true);
-                }
             }
             grid.sync();
             if (tid == 0) trace_mark(W, tn, 0x30000u | min(n_items, 0xFFFFu));
