@@ -1014,8 +1014,13 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
         grid.sync();
         // static pairs (contact records only) join the first round's work items; every body's cursor goes to its first entry of interest
         for (uint32_t i = tid; i < n_static; i += nth) { const uint2 pr = W.static_pairs[i]; W.items[atomicAdd(&W.counters[CTR_ITEMS], 1u)] = make_uint4(pr.x, pr.y, ICX_NONE, ICX_NONE); }
-        for (uint32_t s = tid >> 5; s < n_dirty; s += nth >> 5)
-            settle_warp(W, s, load_cursor(W, s), 0u, n_dirty, 1, CTR_ACTIVE);     // writes head[0] / active[0]
+        for (uint32_t s = tid; s < n_dirty; s += nth) {                              // one lane per body (the walk is a chain of dependent loads:
+            const Cursor c = load_cursor(W, s);                                     // 32 bodies per warp hide it better than 32 entries of one body)
+            int kind; uint32_t kk, oo;
+            const uint32_t hw = skip_rejects_lane(W, c, 0u, n_dirty, kind, kk, oo);
+            W.head[0][s] = hw;
+            if (cursor_pending(c, hw)) W.active[0][atomicAdd(&W.counters[CTR_ACTIVE], 1u)] = s;   // writes head[0] / active[0]
+        }
         grid.sync();
         if (tid == 0) trace_mark(W, tn, 0x50000u);
         }
