@@ -161,6 +161,9 @@ typedef struct IcxPair {
                                        (collision_procedures.cpp:380-423); default off = parity
                                        with the dispatch table collision_procedures.h:411-417 */
 #define ICX_F_NO_GRAVITY      0x2u  /* skip the hard-coded gravity (euler_physics_relay.h:32)  */
+#define ICX_F_LANE_ROUNDS     0x4u  /* diagnostic: run EVERY dependency round of the ordered resolve
+                                       lane-parallel (one work item per lane; normally only rounds with
+                                       >= 4 items per warp do).  Results are identical either way. */
 
 typedef struct IcxConfig {
     uint32_t struct_size;           /* = sizeof(IcxConfig)                                      */

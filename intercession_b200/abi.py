@@ -55,7 +55,7 @@ COLLIDER_NONE, COLLIDER_BOX, COLLIDER_SPHERE, COLLIDER_RAY = 0, 1, 2, 3
 COLLISION_NOOP, COLLISION_RIGID, COLLISION_SPRING, COLLISION_FORCE = 0, 1, 2, 3
 TS_MERGED, TS_FORKED, TS_FORKING, TS_SUPERPOSITION, TS_GHOST = 0, 1, 2, 3, 4
 NULL_TIMESLICE, NULL_CHAINLINK, NULL_ENTITY = 14, 15, 0xFFFFFFFF
-F_SPHERE_SPHERE, F_NO_GRAVITY = 1, 2
+F_SPHERE_SPHERE, F_NO_GRAVITY, F_LANE_ROUNDS = 1, 2, 4
 CONTACT_RESPONDED, CONTACT_BEHAVIORS_A, CONTACT_BEHAVIORS_B = 1, 2, 4
 OK, E_INVALID, E_CUDA, E_CAPACITY, E_NOMEM, E_STATE = 0, 1, 2, 3, 4, 5
 REPLAY_SERVER, REPLAY_PARALLEL = 0, 1

@@ -1043,13 +1043,15 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
             // takes a batch of items and runs them lane-parallel, one item per lane from the exact pair to the end of its cursor
             // walks (the items of a round touch disjoint bodies).  Thin rounds keep one item per warp.
             const uint32_t per_warp = (n_items + (nth >> 5) - 1u) / (nth >> 5);
-            const uint32_t batch = per_warp >= ICX_LANE_MIN ? min(per_warp, 32u) : 1u;
+            const bool force_lanes = (W.cfg_flags & ICX_F_LANE_ROUNDS) != 0u;
+            const bool lane_mode = per_warp >= ICX_LANE_MIN || force_lanes;
+            const uint32_t batch = lane_mode ? (force_lanes ? 32u : min(per_warp, 32u)) : 1u;
             for (;;) {
                 uint32_t i = 0;
                 if ((tid & 31u) == 0u) i = atomicAdd(&W.counters[CTR_FETCH + (rounds & 1u)], batch);
                 i = __shfl_sync(0xFFFFFFFFu, i, 0);
                 if (i >= n_items) break;
-                if (batch == 1u) { round_execute(W, W.items[i], n_dirty, parity, ctr_out, CTR_NEWD + rounds % 3u, scratch); continue; }
+                if (!lane_mode) { round_execute(W, W.items[i], n_dirty, parity, ctr_out, CTR_NEWD + rounds % 3u, scratch); continue; }
                 const uint32_t cnt = min(batch, n_items - i), lane = tid & 31u;
                 uint4 mine = make_uint4(0u, 0u, ICX_NONE, ICX_NONE);
                 if (lane < cnt) mine = W.items[i + lane];
