@@ -938,7 +938,10 @@ __device__ __forceinline__ void trace_mark(const DeviceWorld& W, uint32_t& n, ui
 #ifndef RESOLVE_TPB
 #define RESOLVE_TPB 256
 #endif
+#ifndef PREPARE_TPB
 #define PREPARE_TPB 384
+#define PREPARE_MINB 2
+#endif
 template <int PHASE>
 __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, int do_euler, V3* scratch)
 {
@@ -960,6 +963,7 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
             if (n_dirty == done) break;                         // uniform: read after a grid barrier
             for (uint32_t sl = done + (tid >> 5); sl < n_dirty; sl += (nth >> 5)) build_lists_warp(W, sl);
             grid.sync();
+            if (tid == 0) trace_mark(W, tn, 0x60000u | min(n_dirty - done, 0xFFFFu));      // lists of this sweep's bodies built
             for (uint32_t sl = done + (tid >> 5); sl < n_dirty; sl += (nth >> 5)) {
                 const uint32_t e = W.dirty_list[sl];
                 const float pa = *(volatile float*)&W.push[e];
@@ -988,6 +992,7 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
             }
             done = n_dirty;
             grid.sync();
+            if (tid == 0) trace_mark(W, tn, 0x70000u | (uint32_t)sweep);                       // prediction sweep done
         }
         if (tid == 0) ctr[CTR_LISTED] = done;
         grid.sync();
@@ -1070,7 +1075,7 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
     if (tid == 0) { ctr[CTR_ROUNDS] = rounds; ctr[CTR_ATTEMPTS] = attempts; trace_mark(W, tn, 0x40000u); if (W.trace) W.trace[0] = tn; }
 }
 
-__global__ void __launch_bounds__(PREPARE_TPB, 2) k_resolve_prepare(const __grid_constant__ DeviceWorld W, double dt, int do_euler)
+__global__ void __launch_bounds__(PREPARE_TPB, PREPARE_MINB) k_resolve_prepare(const __grid_constant__ DeviceWorld W, double dt, int do_euler)
 {
     resolve_body<0>(W, dt, do_euler, nullptr);
 }
