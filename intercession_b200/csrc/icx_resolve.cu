@@ -663,9 +663,12 @@ static __device__ __noinline__ void restore_body(const DeviceWorld& W, uint32_t 
 //   select   (one lane per active body)  one-sided pair -> work item; two-sided pair -> ready iff
 //            the partner's cursor rests on the same pair (both read the round-start cursors); the
 //            lower packet's lane then either consumes a certain miss or queues a work item
-//   execute  (one WARP per work item, so the divergent exact code never serialises 32 bodies)
-//            exact narrowphase + response, then both cursors advance past the one-sided pairs the
-//            filter rejects against the bodies' new state
+//   execute  exact narrowphase + response, then both cursors advance past the one-sided pairs the
+//            filter rejects against the bodies' new state.  Thin rounds: one WARP per work item
+//            (warp-cooperative SAT and cursor walk, lane 0 finishes).  Fat rounds (>= ICX_LANE_MIN
+//            items per warp): one LANE per work item, 32 items per warp in plain SIMT form -- with
+//            one lane active a warp spends its time streaming the ~85 KB procedure through the
+//            instruction cache, which more warps per SM did not hide (measured)
 // separated by grid barriers.  Cursors are double buffered (head[parity]); each active body has
 // exactly one writer per round.
 
@@ -808,8 +811,7 @@ __device__ __forceinline__ void round_select(const DeviceWorld& W, uint32_t s, u
 // BEFORE the exact procedure and arrive while it runs.  One-sided pairs that follow need no
 // partner and are executed at once -- through the same process_pair call site: the procedure is
 // ~85 KB of code and must exist once.
-__device__ __forceinline__ void round_execute(const DeviceWorld& W, uint4 item, uint32_t n_dirty, int parity, uint32_t ctr_out, uint32_t ctr_new, V3* scratch,
-                                              bool first_done = false)
+__device__ __forceinline__ void round_execute(const DeviceWorld& W, uint4 item, uint32_t n_dirty, int parity, uint32_t ctr_out, uint32_t ctr_new, V3* scratch)
 {
     const uint32_t FULL = 0xFFFFFFFFu, lane = threadIdx.x & 31u;
 #ifdef ICX_PROFILE_PAIR
@@ -821,8 +823,8 @@ __device__ __forceinline__ void round_execute(const DeviceWorld& W, uint4 item, 
     if (my_s != ICX_NONE) { my_info = W.slot_info[my_s]; my_hw = W.head[parity][my_s]; }
 
     uint32_t pa = item.x, pb = item.y & ICX_NB_INDEX_MASK;
-    bool run = !first_done;                                                         // lane mode: the item's own pair has been executed already
-    if (run && (item.y & ICX_ITEM_CHECK)) run = may_hit_warp(W, pa, pb, W.pk_entity[pa], W.pk_entity[pb]);
+    bool run = true;
+    if (item.y & ICX_ITEM_CHECK) run = may_hit_warp(W, pa, pb, W.pk_entity[pa], W.pk_entity[pb]);
     int side = 0; bool entered = false;                                             // body being walked; its cursor is loaded
     Cursor c; uint32_t hw = 0, k_run = 0;
     c.p0 = c.npk = c.n0 = c.n1 = c.e = 0; c.l0 = c.l1 = nullptr;
