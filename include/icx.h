@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define ICX_ABI_VERSION 1
+#define ICX_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define ICX_API __attribute__((visibility("default")))
@@ -192,12 +192,12 @@ typedef struct IcxStats {
     uint32_t n_interceptions;
     uint32_t n_rounds;              /* dependency rounds of the ordered resolve (last attempt)  */
     uint32_t n_retries;             /* ticks re-run with a larger margin / capacity (cumulative)*/
-    float    margin;                /* margin in force                                          */
+    float    margin;                /* uniform part of the broadphase margin (per-body budgets may exceed it) */
     float    cell_size;
     uint32_t max_neighbors;
     uint32_t n_dirty;               /* bodies touched by a hit: the only ones resolved in order  */
     uint32_t n_attempts;            /* ordered-resolve attempts (1 + times the dirty set grew)   */
-    uint32_t _reserved;
+    uint32_t n_movers;              /* bodies whose displacement budget exceeded the uniform margin (own candidate walk) */
 } IcxStats;
 
 typedef struct IcxWorld IcxWorld;
@@ -292,6 +292,12 @@ ICX_API int icx_collision_engage(IcxWorld* w);              /* collision_physics
 /* Results of the last tick.  *n receives the total available even if > cap. */
 ICX_API int icx_pairs_fetch(IcxWorld* w, IcxPair* out, size_t cap, size_t* n);
 ICX_API int icx_contacts_fetch(IcxWorld* w, IcxContact* out, size_t cap, size_t* n);
+/* Broadphase, second part.  icx_pairs_fetch returns every pair whose bounds, inflated by the uniform margin, overlap on the
+ * post-integration state.  A body that static resolution is predicted (or was caught) to move further than the margin gets a
+ * larger per-body budget; the additional candidates this creates -- overlap(bound_i (+) budget_i, bound_j (+) budget_j) but not
+ * in the uniform list -- are found by that body alone and returned here.  The ordered pass runs over the union. */
+ICX_API int icx_extra_pairs_fetch(IcxWorld* w, IcxPair* out, size_t cap, size_t* n);
+ICX_API int icx_budgets_fetch(IcxWorld* w, float* out, size_t cap);
 ICX_API int icx_interceptions_fetch(IcxWorld* w, IcxInterception* out, size_t cap, size_t* n);
 ICX_API int icx_stats_fetch(IcxWorld* w, IcxStats* out);
 
@@ -351,9 +357,13 @@ ICX_API int icx_projectiles_kernel_ms(IcxWorld* w, float* ms);
 /* ==== world-line record / replay / divergence scan ========================================
  * The dense ENTITY_UPDATE stream between adjacent timeslices (EntityTimestreamMap,
  * source/networking/entity_timestream_map.h:43-230) as a device-resident ring of SoA snapshots:
- * slot = coherency % depth_ticks.  Entities are matched by upload index (the reference matches by
- * id with the causal chain-link incremented on the way into the past, server_network_dynamo.cpp:673).
- * create / remove / jump events stay on the host TimelineApi queues. */
+ * slot = coherency % depth_ticks.  A record carries what the reference's does (ComponentCategory::all,
+ * server_network_dynamo.cpp:666-677; layout component_registry.h:238-279): per entity the whole
+ * TransformComponent and PhysicsComponent and the id the receiving cosmos knows it by (causal chain-link + 1,
+ * :673); ColliderComponents travel as a sparse list of the rows that changed since the previous record into
+ * the ring (every record of the reference repeats them unchanged).  Entities are addressed by upload index
+ * AND checked by id: a replay leaves an entity whose id is not the recorded one alone and counts it
+ * (icx_timeline_id_mismatches).  create / remove / jump events stay on the host TimelineApi queues. */
 #define ICX_REPLAY_SERVER   0   /* ServerNetworkDynamo::run_relays phase 2, server_network_dynamo.cpp:377-421  */
 #define ICX_REPLAY_PARALLEL 1   /* ParallelNetworkDynamo::run_relays,     parallel_network_dynamo.cpp:51-89 */
 
@@ -367,11 +377,17 @@ ICX_API const char* icx_timeline_last_error(const IcxTimeline* tl);
 ICX_API int icx_timeline_profile(IcxTimeline* tl, int enable);
 ICX_API int icx_timeline_kernel_ms(IcxTimeline* tl, int which, float* ms);
 
-/* Record = serialise every entity at `coherency` and push it (TimelineApi::push_past_timestream,
- * server_network_dynamo.cpp:642-679; push_timestream_at_breakpoint rewrites the same slot,
- * parallel_network_dynamo.cpp:369-385).  Asynchronous on the world's stream. */
+/* Record = serialise every entity at `coherency` and push it.  Asynchronous on the world's stream.
+ *   icx_record                TimelineApi::push_past_timestream, server_network_dynamo.cpp:642-679: the id travels with
+ *                             its causal chain-link incremented (:673, refused at link >= 14, ecs_types.h:118-136)
+ *   icx_record_at_breakpoint  push_timestream_at_breakpoint, parallel_network_dynamo.cpp:369-385: rewrites the slot in
+ *                             front of the breakpoint, ids unchanged
+ *   icx_record_ex             both spelled out (ICX_RECORD_*) */
+#define ICX_RECORD_AT_BREAKPOINT 0x1u
+#define ICX_RECORD_KEEP_LINK     0x2u   /* do not increment the chain-link (the record goes back to the cosmos it came from) */
 ICX_API int icx_record(IcxWorld* w, IcxTimeline* tl, uint16_t coherency);
 ICX_API int icx_record_at_breakpoint(IcxWorld* w, IcxTimeline* tl, uint16_t coherency);
+ICX_API int icx_record_ex(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, uint32_t flags);
 
 /* Breakpoint of the timestreams (TsBreakpointQueue::set_breakpoint_at_begin / remove_breakpoint,
  * source/networking/ts_breakpoint_queue.h:107-121, set by link_timestreams when a parallel cosmos is
@@ -380,35 +396,52 @@ ICX_API int icx_record_at_breakpoint(IcxWorld* w, IcxTimeline* tl, uint16_t cohe
 ICX_API int icx_breakpoint_set(IcxTimeline* tl);
 ICX_API int icx_breakpoint_clear(IcxTimeline* tl);
 
-/* Replay = pop the record stamped `coherency` (pop_future_timestream / pop_timestream_at_breakpoint)
- * and apply it: ICX_REPLAY_SERVER overwrites transform + physics of every entity that is not
- * forking / forked; ICX_REPLAY_PARALLEL only consumes it (a parallel cosmos takes upstream
- * components only, of which the physics path has none).  *applied = 1 if a record was applied. */
+/* Replay = pop every record with coherency <= `coherency` (cyclic compare, events/message.h:179-183), drop those the
+ * reference drops (`record.coherency < now`, a plain integer compare: server_network_dynamo.cpp:391) and apply the rest
+ * oldest first: ICX_REPLAY_SERVER overwrites transform + physics (+ changed colliders) of every entity that is not
+ * forking / forked; ICX_REPLAY_PARALLEL only consumes (a parallel cosmos takes upstream components only, of which the
+ * physics path has none).  *applied = 1 if a record was applied.  Asynchronous on the world's stream. */
 ICX_API int icx_replay(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, int mode, int* applied);
+
+/* Entities (and collider rows) replays from this ring have skipped so far because the recorded id / packet structure was not
+ * the receiving entity's.  Synchronises the device. */
+ICX_API int icx_timeline_id_mismatches(IcxTimeline* tl, uint64_t* total);
 
 /* Divergence scan: live origins against the record stamped `coherency`, with the reference's
  * congruence predicate length2(a - b) <= 2.0f (TimejumpConditions::operator==,
  * source/spacetime/timejump_conditions.h:21-25).  Per world-line k (cfg.worldline_stride, or one):
  * flags[k] = any body incongruent, incongruent[k] = how many, score[k] = sum of min(length2, 2^20)
  * accumulated in 48.16 fixed point (the score is this build's definition, the flag is the
- * reference's).  The record may cover the whole world or one world-line (a base history shared by
- * all candidates).  Synchronous. */
+ * reference's).  The record may cover the whole world or ONE world-line (a base history shared by
+ * all candidates).  icx_divergence_scan is synchronous; _enqueue only launches (results stay on the device, and a
+ * per-world-line "flagged by some scan since the last reset" byte is kept), _fetch waits and reads the LAST scan's
+ * results plus those bytes (any pointer may be NULL) -- a per-tick scan then costs no host round trip. */
 ICX_API int icx_divergence_scan(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, uint32_t n_worldlines,
                         uint8_t* flags, uint32_t* incongruent, double* score);
+ICX_API int icx_divergence_scan_enqueue(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, uint32_t n_worldlines);
+ICX_API int icx_divergence_scan_fetch(IcxTimeline* tl, uint32_t n_worldlines, uint8_t* flags, uint8_t* flags_ever,
+                              uint32_t* incongruent, double* score, int reset_ever);
 
 /* Fork ageing (server_network_dynamo.cpp:13-15, :681-705): forking -> forked after 13 ticks;
- * *resolution_needed = some entity has been forked for >= 13 ticks (parallel_notify_divergence). */
+ * *resolution_needed = some entity has been forked for >= 13 ticks (parallel_notify_divergence).
+ * With both out-pointers NULL the call only enqueues the promotion kernel (no host round trip). */
 ICX_API int icx_fork_age(IcxWorld* w, uint32_t* n_promoted, int* resolution_needed);
 
 /* Snapshot transport between timeslices on different GPUs / processes (the future -> past ENTITY_UPDATE
  * stream, server_network_dynamo.cpp:642-679): pack the slot stamped `coherency` into / restore it from a
- * caller-owned DEVICE buffer of n * ICX_SNAPSHOT_BYTES bytes ([6][n] float4 state + [n] uint32 timestream
- * word), e.g. the buffer a ncclSend / ncclRecv moves.  `stream` is a cudaStream_t (NULL = default stream);
- * the copies are complete on return.  The recording world must be synchronised (icx_sync) before export. */
-#define ICX_SNAPSHOT_BYTES 100
+ * caller-owned DEVICE buffer, e.g. the buffer a ncclSend / ncclRecv moves:
+ *   [10][n] float4 state | [n] uint32 id | 16-byte header {collider rows, 0, 0, 0} | rows x 176 B {index, pad, ColliderComponent}
+ * ICX_SNAPSHOT_CAPACITY(n, rows) is the buffer size for n entities and up to `rows` changed colliders.  `stream` is a
+ * cudaStream_t (NULL = default stream); both calls are ASYNCHRONOUS on it and ordered against the recording / replaying
+ * worlds' streams by events, so a timeslice needs no host synchronisation per tick. */
+#define ICX_SNAPSHOT_BYTES 164
+#define ICX_SNAPSHOT_HEADER_BYTES 16
+#define ICX_SNAPSHOT_DELTA_BYTES 176
+#define ICX_SNAPSHOT_CAPACITY(n, rows) ((size_t)(n) * ICX_SNAPSHOT_BYTES + ICX_SNAPSHOT_HEADER_BYTES + (size_t)(rows) * ICX_SNAPSHOT_DELTA_BYTES)
 ICX_API int icx_timeline_slot_export(IcxTimeline* tl, uint16_t coherency, void* device_buffer, size_t capacity_bytes,
                                      uint32_t* n_entities, void* stream);
-ICX_API int icx_timeline_slot_import(IcxTimeline* tl, uint16_t coherency, uint32_t n_entities, const void* device_buffer, void* stream);
+ICX_API int icx_timeline_slot_import(IcxTimeline* tl, uint16_t coherency, uint32_t n_entities, const void* device_buffer,
+                                     size_t buffer_bytes, void* stream);
 
 ICX_API int icx_timeline_slot_info(const IcxTimeline* tl, uint16_t coherency, int* valid, uint32_t* n_recorded);
 

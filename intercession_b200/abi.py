@@ -59,7 +59,13 @@ F_SPHERE_SPHERE, F_NO_GRAVITY, F_LANE_ROUNDS = 1, 2, 4
 CONTACT_RESPONDED, CONTACT_BEHAVIORS_A, CONTACT_BEHAVIORS_B = 1, 2, 4
 OK, E_INVALID, E_CUDA, E_CAPACITY, E_NOMEM, E_STATE = 0, 1, 2, 3, 4, 5
 REPLAY_SERVER, REPLAY_PARALLEL = 0, 1
-SNAPSHOT_BYTES = 100
+SNAPSHOT_BYTES, SNAPSHOT_HEADER_BYTES, SNAPSHOT_DELTA_BYTES = 164, 16, 176
+RECORD_AT_BREAKPOINT, RECORD_KEEP_LINK = 1, 2
+
+
+def snapshot_capacity(n, rows=0):
+    """ICX_SNAPSHOT_CAPACITY: transport buffer for n entities and up to `rows` changed ColliderComponents."""
+    return n * SNAPSHOT_BYTES + SNAPSHOT_HEADER_BYTES + rows * SNAPSHOT_DELTA_BYTES
 
 
 def compose_entity(timeslice, genesis, link):
@@ -125,7 +131,7 @@ class IcxStats(C.Structure):
                 ("n_large", C.c_uint32), ("n_candidates", C.c_uint32), ("n_contacts", C.c_uint32),
                 ("n_interceptions", C.c_uint32), ("n_rounds", C.c_uint32), ("n_retries", C.c_uint32),
                 ("margin", C.c_float), ("cell_size", C.c_float), ("max_neighbors", C.c_uint32),
-                ("n_dirty", C.c_uint32), ("n_attempts", C.c_uint32), ("_reserved", C.c_uint32)]
+                ("n_dirty", C.c_uint32), ("n_attempts", C.c_uint32), ("n_movers", C.c_uint32)]
 
 
 _vp, _u32, _sz = C.c_void_p, C.c_uint32, C.c_size_t
@@ -152,6 +158,8 @@ SIGNATURES = {
     "icx_collision_engage": (C.c_int, [_vp]),
     "icx_pairs_fetch": (C.c_int, [_vp, _vp, _sz, _psz]),
     "icx_contacts_fetch": (C.c_int, [_vp, _vp, _sz, _psz]),
+    "icx_extra_pairs_fetch": (C.c_int, [_vp, _vp, _sz, _psz]),
+    "icx_budgets_fetch": (C.c_int, [_vp, _vp, _sz]),
     "icx_interceptions_fetch": (C.c_int, [_vp, _vp, _sz, _psz]),
     "icx_stats_fetch": (C.c_int, [_vp, C.POINTER(IcxStats)]),
     "icx_last_step_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
@@ -164,13 +172,17 @@ SIGNATURES = {
     "icx_timeline_kernel_ms": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_float)]),
     "icx_record": (C.c_int, [_vp, _vp, C.c_uint16]),
     "icx_record_at_breakpoint": (C.c_int, [_vp, _vp, C.c_uint16]),
+    "icx_record_ex": (C.c_int, [_vp, _vp, C.c_uint16, _u32]),
+    "icx_timeline_id_mismatches": (C.c_int, [_vp, C.POINTER(C.c_uint64)]),
+    "icx_divergence_scan_enqueue": (C.c_int, [_vp, _vp, C.c_uint16, _u32]),
+    "icx_divergence_scan_fetch": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp, C.c_int]),
     "icx_breakpoint_set": (C.c_int, [_vp]),
     "icx_breakpoint_clear": (C.c_int, [_vp]),
     "icx_replay": (C.c_int, [_vp, _vp, C.c_uint16, C.c_int, C.POINTER(C.c_int)]),
     "icx_divergence_scan": (C.c_int, [_vp, _vp, C.c_uint16, _u32, _vp, _vp, _vp]),
     "icx_fork_age": (C.c_int, [_vp, C.POINTER(_u32), C.POINTER(C.c_int)]),
     "icx_timeline_slot_export": (C.c_int, [_vp, C.c_uint16, _vp, _sz, C.POINTER(_u32), _vp]),
-    "icx_timeline_slot_import": (C.c_int, [_vp, C.c_uint16, _u32, _vp, _vp]),
+    "icx_timeline_slot_import": (C.c_int, [_vp, C.c_uint16, _u32, _vp, _sz, _vp]),
     "icx_world_clone": (C.c_int, [_vp, _vp, _vp, C.POINTER(_u32)]),
     "icx_world_extract": (C.c_int, [_vp, _vp, C.POINTER(_u32), C.POINTER(_u32)]),
     "icx_timeline_slot_info": (C.c_int, [_vp, C.c_uint16, C.POINTER(C.c_int), C.POINTER(_u32)]),

@@ -44,7 +44,7 @@ int allocate(IcxWorld* w)
     const size_t ne = w->cap_entities, np = w->cap_packets;
     CK(alloc_state(w, W.in, ne)); CK(alloc_state(w, W.out, ne));
     CK(alloc(w, W.prm0, ne)); CK(alloc(w, W.prm1, ne)); CK(alloc(w, W.locked_pos, ne)); CK(alloc(w, W.locked_rot, ne));
-    CK(alloc(w, W.entity_id, ne)); CK(alloc(w, W.first_packet, ne)); CK(alloc(w, W.pos0, ne));
+    CK(alloc(w, W.entity_id, ne)); CK(alloc(w, W.first_packet, ne)); CK(alloc(w, W.pos0, ne)); CK(alloc(w, W.c_ver, ne));
     CK(alloc(w, W.pk_entity, np)); CK(alloc(w, W.pk_lpos, np)); CK(alloc(w, W.pk_lrot, np)); CK(alloc(w, W.pk_lscale, np));
     CK(alloc(w, W.pk_mat0, np)); CK(alloc(w, W.pk_damping, np)); CK(alloc(w, W.pk_minparam, np));
     CK(alloc(w, W.pk_d, np * 6)); CK(alloc(w, W.pk_lo, np)); CK(alloc(w, W.pk_hi, np)); CK(alloc(w, W.pk_cell, np));
@@ -55,6 +55,8 @@ int allocate(IcxWorld* w)
     CK(alloc(w, W.s_lo, np)); CK(alloc(w, W.s_hi, np));
     CK(alloc(w, W.large_list, W.max_large));
     CK(alloc(w, W.pairs, W.max_pairs)); CK(alloc(w, W.tight, W.max_pairs)); CK(alloc(w, W.push, ne)); CK(alloc(w, W.static_pairs, W.max_static));
+    CK(alloc(w, W.bm, ne)); CK(alloc(w, W.bm_keep, ne)); CK(alloc(w, W.bm_need, ne)); CK(alloc(w, W.mover_list, ne)); CK(alloc(w, W.xpairs, W.max_xpairs));
+    CK(cudaMemset(W.bm_keep, 0, ne * sizeof(float))); CK(cudaMemset(W.bm_need, 0, ne * sizeof(uint32_t)));
     CK(alloc(w, W.dirty_slot, ne)); CK(alloc(w, W.dirty_list, ne));
     CK(alloc(w, W.nbr, 2 * ne * (size_t)W.max_neighbors)); CK(alloc(w, W.nbr_count, 2 * ne)); CK(alloc(w, W.slot_info, ne));
     CK(alloc(w, W.head[0], ne)); CK(alloc(w, W.head[1], ne));
@@ -145,6 +147,7 @@ int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_
             w->stats.n_contacts = w->h_counters[CTR_CONTACTS];
             w->stats.n_interceptions = w->h_counters[CTR_INTERCEPTS];
             w->stats.n_dirty = w->h_counters[CTR_DIRTY]; w->stats.n_attempts = w->h_counters[CTR_ATTEMPTS] + 1;
+            w->stats.n_movers = w->h_counters[CTR_MOVERS];
             w->stats.margin = W.margin; w->stats.cell_size = W.cell_size; w->stats.max_neighbors = W.max_neighbors;
             w->have_results = do_collide != 0;
             return ICX_OK;
@@ -163,18 +166,17 @@ int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_
                 rc = regrow(w, W.pairs, W.max_pairs); if (rc) return rc;
                 rc = regrow(w, W.tight, W.max_pairs); if (rc) return rc;
             }
+            if (w->h_counters[CTR_XPAIRS] > W.max_xpairs) {
+                W.max_xpairs = std::max<uint32_t>(W.max_xpairs * 2, w->h_counters[CTR_XPAIRS] + w->h_counters[CTR_XPAIRS] / 4);
+                rc = regrow(w, W.xpairs, W.max_xpairs); if (rc) return rc;
+            }
             if (w->h_counters[CTR_STATIC] > W.max_static) {
                 W.max_static = w->h_counters[CTR_STATIC] * 2;
                 rc = regrow(w, W.static_pairs, W.max_static); if (rc) return rc;
                 rc = regrow(w, W.items, (size_t)w->cap_entities + W.max_static); if (rc) return rc;     // static pairs ride in the first round's item list
             }
         }
-        if (raised & RF_MARGIN_VIOLATED) {
-            const float old = W.margin;
-            W.margin = old * 2.0f;
-            if (W.margin > 1.0e6f) return fail(w, ICX_E_CAPACITY, "broadphase margin diverged");
-            set_cell(w, W.cell_size + 2.0f * (W.margin - old));
-        }
+        if (raised & RF_MARGIN_VIOLATED) launch_budget_update(W, w->stream);       // only the bodies that moved too far get a larger budget
         if (raised & RF_CELL_TOO_SMALL) {
             float need; std::memcpy(&need, &w->h_counters[CTR_NEED_CELL], 4);
             set_cell(w, std::max(need, W.cell_size) * 1.05f);
@@ -265,6 +267,7 @@ int icx_world_create(const IcxConfig* cfg, IcxWorld** out)
         W.max_neighbors = cfg->max_neighbors ? std::min<uint32_t>(cfg->max_neighbors, 4096) : 24;
         W.max_pairs = cfg->max_pairs ? cfg->max_pairs : std::max<uint32_t>(8 * cfg->max_entities, 4096);
         W.max_static = 4096;
+        W.max_xpairs = std::max<uint32_t>(cfg->max_entities, 4096);
         W.max_large = cfg->max_large ? cfg->max_large : 1024;
         W.max_contacts = cfg->max_contacts ? cfg->max_contacts : std::max<uint32_t>(2 * cfg->max_entities, 1024);
         W.gx = (cfg->flags & ICX_F_NO_GRAVITY) ? 0.0f : cfg->gravity[0];
@@ -286,7 +289,8 @@ void icx_world_destroy(IcxWorld* w)
     for (auto& b : w->pool) b.release();
     DeviceBuffer* extra[] = {&w->mir_ids, &w->mir_T, &w->mir_P, &w->mir_C, &w->mir_hasP, &w->st_ts, &w->st_tc, &w->st_index, &w->st_T, &w->st_P, &w->st_C,
                              &w->d_mask, &w->st_scan, &w->cl_idx, &w->cl_ids, &w->cl_T, &w->cl_P, &w->cl_C, &w->cl_hasP, &w->cl_ts, &w->cl_tc,
-                             &w->pj_proj, &w->pj_index, &w->pj_condemned, &w->pj_count};
+                             &w->pj_proj, &w->pj_index, &w->pj_condemned, &w->pj_count,
+                             &w->pend_rows, &w->pend_flag, &w->pend_list, &w->pend_count};
     for (auto* b : extra) b->release();
     if (w->h_counters) cudaFreeHost(w->h_counters);
     if (w->h_flags) cudaFreeHost(w->h_flags);
@@ -329,13 +333,15 @@ int icx_bodies_upload(IcxWorld* w, uint32_t n, const IcxEntity* entity, const Ic
     launch_packet_structure(C ? (const IcxColliderComponent*)w->mir_C.ptr : nullptr, n, (uint32_t*)w->st_scan.ptr, W.scan_partial,
                             (uint8_t*)w->d_mask.ptr, W.first_packet, st);
     CK(cudaMemsetAsync(W.counters, 0, CTR_TOTAL * sizeof(uint32_t), st));
+    CK(cudaMemsetAsync(W.bm_keep, 0, (size_t)w->cap_entities * sizeof(float), st)); CK(cudaMemsetAsync(W.bm_need, 0, (size_t)w->cap_entities * sizeof(uint32_t), st));
     W.n_entities = n; w->n_entities = n;
     w->n_projectiles = 0; w->pj_updated = false;     // projectile rows index the previous upload order
     Mirror M = mirror_of(w);
     if (!P) M.P = nullptr;
     launch_import_kernel(W, M, nullptr, M.ids, M.T, M.P, C ? M.C : nullptr,
                          has_physics ? M.hasP : nullptr, tstate ? (const uint8_t*)w->st_ts.ptr : nullptr,
-                         tcoh ? (const uint16_t*)w->st_tc.ptr : nullptr, n, 1, C ? 1 : 0, st);
+                         tcoh ? (const uint16_t*)w->st_tc.ptr : nullptr, n, 1, C ? 1 : 0, ++w->c_epoch, st);
+    w->pend_any = false;
     CK(cudaMemcpyAsync(w->h_counters, W.counters, CTR_TOTAL * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(w->h_flags + 1, (uint32_t*)w->st_scan.ptr + n, 4, cudaMemcpyDeviceToHost, st));      // packet count
     CK(cudaStreamSynchronize(st));          // the caller's arrays may be released after return
@@ -399,7 +405,7 @@ int icx_bodies_update(IcxWorld* w, uint32_t count, const uint32_t* index, const 
     if (!w->have_P) M.P = nullptr;
     launch_import_kernel(w->W, M, (const uint32_t*)w->st_index.ptr, nullptr, T ? (const IcxTransform*)w->st_T.ptr : nullptr,
                          P ? (const IcxPhysics*)w->st_P.ptr : nullptr, C ? (const IcxColliderComponent*)w->st_C.ptr : nullptr,
-                         nullptr, nullptr, nullptr, count, 0, w->have_C ? 1 : 0, st);
+                         nullptr, nullptr, nullptr, count, 0, w->have_C ? 1 : 0, C ? ++w->c_epoch : w->c_epoch, st);
     CK(cudaStreamSynchronize(st));
     CK(cudaGetLastError());
     return ICX_OK;
@@ -535,9 +541,40 @@ int icx_pairs_fetch(IcxWorld* w, IcxPair* out, size_t cap, size_t* n)
     CK(cudaStreamSynchronize(w->stream));
     // the generator emits pairs in block order; canonical order is lexicographic on (a, b)
     std::vector<uint64_t> keys(total);
-    for (size_t i = 0; i < total; i++) keys[i] = ((uint64_t)raw[i].x << 32) | (raw[i].y & ICX_NB_INDEX_MASK);
+    for (size_t i = 0; i < total; i++) keys[i] = ((uint64_t)(raw[i].x & ICX_NB_INDEX_MASK) << 32) | (raw[i].y & ICX_NB_INDEX_MASK);
     std::sort(keys.begin(), keys.end());
     for (size_t i = 0; i < std::min(cap, total); i++) { out[i].a = (uint32_t)(keys[i] >> 32); out[i].b = (uint32_t)keys[i]; }
+    return ICX_OK;
+}
+
+// The movers' extra candidates of the last tick (pairs only their displacement budgets create), canonical order.
+int icx_extra_pairs_fetch(IcxWorld* w, IcxPair* out, size_t cap, size_t* n)
+{
+    if (!w || !n) return ICX_E_INVALID;
+    if (!w->have_results) { *n = 0; return ICX_OK; }
+    cudaSetDevice(w->device);
+    const size_t total = std::min<size_t>(w->h_counters[CTR_XPAIRS], w->W.max_xpairs);
+    std::vector<uint2> raw(total);
+    if (total) {
+        CK(cudaMemcpyAsync(raw.data(), w->W.xpairs, total * sizeof(uint2), cudaMemcpyDeviceToHost, w->stream));
+        CK(cudaStreamSynchronize(w->stream));
+    }
+    std::vector<uint64_t> keys(total);
+    for (size_t i = 0; i < total; i++) keys[i] = ((uint64_t)(raw[i].x & ICX_NB_INDEX_MASK) << 32) | (raw[i].y & ICX_NB_INDEX_MASK);
+    std::sort(keys.begin(), keys.end());
+    keys.erase(std::unique(keys.begin(), keys.end()), keys.end());       // rows that collide in the bucket hash are walked twice
+    *n = keys.size();
+    if (out) for (size_t i = 0; i < std::min(cap, keys.size()); i++) { out[i].a = (uint32_t)(keys[i] >> 32); out[i].b = (uint32_t)keys[i]; }
+    return ICX_OK;
+}
+
+// Per-entity displacement budgets of the last tick (>= IcxStats.margin).
+int icx_budgets_fetch(IcxWorld* w, float* out, size_t cap)
+{
+    if (!w || !out) return ICX_E_INVALID;
+    cudaSetDevice(w->device);
+    const size_t n = std::min<size_t>(cap, w->n_entities);
+    if (n) { CK(cudaMemcpyAsync(out, w->W.bm, n * sizeof(float), cudaMemcpyDeviceToHost, w->stream)); CK(cudaStreamSynchronize(w->stream)); }
     return ICX_OK;
 }
 

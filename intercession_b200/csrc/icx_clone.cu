@@ -106,13 +106,15 @@ int icx_world_clone(IcxWorld* src, IcxWorld* dst, const uint8_t* has_future, uin
     if (nk) CKW(dst, cudaMemcpyAsync(dst->d_mask.ptr, dst->active_mask.data(), nk, cudaMemcpyHostToDevice, st));
     dst->masks_on_host = true;
     CKW(dst, cudaMemsetAsync(W.counters, 0, CTR_TOTAL * sizeof(uint32_t), st));
+    CKW(dst, cudaMemsetAsync(W.bm_keep, 0, (size_t)dst->cap_entities * sizeof(float), st)); CKW(dst, cudaMemsetAsync(W.bm_need, 0, (size_t)dst->cap_entities * sizeof(uint32_t), st));
     W.n_entities = nk; W.n_packets = np; dst->n_entities = nk; dst->n_packets = np;
     icx_size_buckets(dst);
     W.coherency = src->W.coherency;                                                 // :91 set_coherency(source)
     Mirror M = mirror(dst);
     if (!dst->have_P) M.P = nullptr;
     launch_import_kernel(W, M, nullptr, M.ids, M.T, M.P, dst->have_C ? M.C : nullptr, M.hasP, (const uint8_t*)dst->st_ts.ptr,
-                         (const uint16_t*)dst->st_tc.ptr, nk, 1, dst->have_C ? 1 : 0, st);
+                         (const uint16_t*)dst->st_tc.ptr, nk, 1, dst->have_C ? 1 : 0, ++dst->c_epoch, st);
+    dst->pend_any = false;
     CKW(dst, cudaMemcpyAsync(dst->h_counters, W.counters, CTR_TOTAL * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     CKW(dst, cudaStreamSynchronize(st));
     CKW(dst, cudaGetLastError());
@@ -191,7 +193,7 @@ int icx_world_extract(IcxWorld* par, IcxWorld* dst, uint32_t* n_extracted, uint3
     launch_import_kernel(dst->W, M, (const uint32_t*)dst->st_index.ptr, nullptr, (const IcxTransform*)dst->st_T.ptr,
                          par->have_P ? (const IcxPhysics*)dst->st_P.ptr : nullptr,
                          par->have_C ? (const IcxColliderComponent*)dst->st_C.ptr : nullptr,
-                         nullptr, nullptr, nullptr, cnt, 0, dst->have_C ? 1 : 0, st);
+                         nullptr, nullptr, nullptr, cnt, 0, dst->have_C ? 1 : 0, par->have_C ? ++dst->c_epoch : dst->c_epoch, st);
     launch_extract_ts(dst->W, (const uint32_t*)dst->st_index.ptr, (const uint8_t*)dst->cl_ts.ptr, cnt, st);
     CKW(dst, cudaStreamSynchronize(st));
     CKW(dst, cudaGetLastError());

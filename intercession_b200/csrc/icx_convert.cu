@@ -4,27 +4,9 @@
 #include "icx_world.cuh"
 #include "icx_host.h"
 #include "icx_math.cuh"
+#include "icx_rows.cuh"
 
 namespace icx {
-
-// immutable <=> nothing CollisionPhysicsRelay::engage does can change the entity:
-// non-temporal (no interception), no ray collider (minParametricValue), and either no
-// PhysicsComponent (responses are skipped, relay :84-106) or infinite mass with an angular
-// velocity the response cannot touch.
-__device__ __forceinline__ bool is_immutable(uint32_t id, bool hasP, const IcxPhysics* P, const IcxColliderComponent* C)
-{
-    if ((id & 0xFu) != ICX_NULL_CHAINLINK) return false;
-    bool influence = false;
-    if (C) for (int s = 0; s < ICX_COLLIDERS_PER_ENTITY; s++) {
-        const IcxCollider& c = C->colliders[s];
-        if (!c.isActive) continue;
-        if (c.colliderType == ICX_COLLIDER_RAY) return false;
-        influence |= c.influenceOrientation != 0;
-    }
-    if (!hasP) return true;
-    if (P->mass != 0.0f) return false;
-    return P->lockOrientation || !influence;
-}
 
 // One thread per listed entity.  src_* (optional) are compact arrays indexed by i and are first
 // copied into the mirror at e = index ? index[i] : i; the SoA parts fed by each given array are
@@ -33,7 +15,7 @@ __global__ void __launch_bounds__(128) k_import(DeviceWorld W, Mirror M, const u
                                                 const uint32_t* src_ids, const IcxTransform* src_T, const IcxPhysics* src_P,
                                                 const IcxColliderComponent* src_C, const uint8_t* src_hasP,
                                                 const uint8_t* src_ts, const uint16_t* src_tc,
-                                                uint32_t count, int full, int have_C)
+                                                uint32_t count, int full, int have_C, uint32_t epoch)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= count) return;
@@ -64,60 +46,35 @@ __global__ void __launch_bounds__(128) k_import(DeviceWorld W, Mirror M, const u
             W.in.acc[e] = make_float4(P->acceleration[0], P->acceleration[1], P->acceleration[2], 0.0f);
             W.in.angvel[e] = make_float4(P->angularVelocity[0], P->angularVelocity[1], P->angularVelocity[2], 0.0f);
             W.in.angacc[e] = make_float4(P->angularAcceleration[0], P->angularAcceleration[1], P->angularAcceleration[2], 0.0f);
-            W.locked_pos[e] = make_float4(P->lockedOrigin[0], P->lockedOrigin[1], P->lockedOrigin[2], 0.0f);
+            W.locked_pos[e] = make_float4(P->lockedOrigin[0], P->lockedOrigin[1], P->lockedOrigin[2], P->collisionLinearDrag);
             W.locked_rot[e] = make_float4(P->lockedOrientation[0], P->lockedOrientation[1], P->lockedOrientation[2], P->lockedOrientation[3]);
         } else {
             const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
             W.in.vel[e] = z; W.in.acc[e] = z; W.in.angvel[e] = z; W.in.angacc[e] = z;
         }
     }
-    // constants that mix several components are always refreshed
+    // Constants: the SoA is the source of truth (a replay overwrites it without touching the mirror), so only the parts fed by
+    // a GIVEN array are rebuilt; the flag word mixes all three components and takes the missing inputs from its old value.
     {
-        const IcxTransform& t = M.T[e];
-        W.prm0[e] = make_float4(t.scale[0], t.scale[1], t.scale[2], hasP ? P->mass : 0.0f);
-        uint32_t ef = 0;
-        if (hasP) {
-            ef |= EF_HAS_PHYSICS;
-            if (P->lockOrigin) ef |= EF_LOCK_ORIGIN;
-            if (P->lockOrientation) ef |= EF_LOCK_ORIENTATION;
-            if (P->isAsleep) ef |= EF_ASLEEP;
-        }
-        if (is_immutable(id, hasP, P, C)) ef |= EF_IMMUTABLE;
-        W.prm1[e] = make_float4(hasP ? P->linearDrag : 0.0f, hasP ? P->angularDrag : 0.0f,
-                                hasP ? P->collisionAngularDrag : 0.0f, __uint_as_float(ef));
-        // colliders
-        const uint32_t fp = W.first_packet[e];
-        const uint32_t npk = fp >> 30, p0 = fp & 0x3FFFFFFFu;
-        if (C && npk && (full || src_C || src_T)) {
-            uint32_t k = 0;
-            for (int s = 0; s < ICX_COLLIDERS_PER_ENTITY; s++) {
-                const IcxCollider& c = C->colliders[s];
-                if (!c.isActive) continue;
-                const uint32_t p = p0 + k; k++;
-                uint32_t bits = ((uint32_t)c.colliderType & PF_TYPE_MASK) | (((uint32_t)c.collisionType & 3u) << PF_CTYPE_SHIFT);
-                if (c.useBehaviorsResponse) bits |= PF_BEHAVIORS;
-                if (c.inheritOrientation) bits |= PF_INHERIT_ORIENT;
-                if (c.influenceOrientation) bits |= PF_INFLUENCE_ORIENT;
-                if (s == 1) bits |= PF_SLOT;
-                const IcxTransform& l = c.localTransform;
-                W.pk_entity[p] = e;
-                W.pk_lpos[p] = make_float4(l.origin[0], l.origin[1], l.origin[2], __uint_as_float(bits));
-                W.pk_lrot[p] = make_float4(l.orientation[0], l.orientation[1], l.orientation[2], l.orientation[3]);
-                W.pk_lscale[p] = make_float4(l.scale[0], l.scale[1], l.scale[2], c.restLength);
-                W.pk_mat0[p] = make_float4(c.staticFriction, c.dynamicFriction, c.restitution, c.stiffness);
-                W.pk_damping[p] = c.damping;
-                W.pk_minparam[p] = c.minParametricValue;
-                // rotation-invariant extent estimate of mutable colliders -> initial grid cell size
-                if (!(ef & EF_IMMUTABLE) && c.colliderType != ICX_COLLIDER_NONE) {
-                    const float sx = fabsf(t.scale[0] * l.scale[0]), sy = fabsf(t.scale[1] * l.scale[1]), sz = fabsf(t.scale[2] * l.scale[2]);
-                    float ext;
-                    if (c.colliderType == ICX_COLLIDER_SPHERE) ext = 1.7320509f * sx;
-                    else if (c.colliderType == ICX_COLLIDER_RAY) ext = sz * 1.000001f;
-                    else ext = sqrtf(sx * sx + sy * sy + sz * sz);
-                    if (ext == ext) atomicMax((int*)&W.counters[CTR_EXTENT], __float_as_int(ext));
-                }
-            }
-        }
+        const float4 old0 = full ? make_float4(1.0f, 1.0f, 1.0f, 0.0f) : W.prm0[e];
+        const float4 old1 = full ? make_float4(0.0f, 0.0f, 0.0f, 0.0f) : W.prm1[e];
+        const uint32_t oldf = __float_as_uint(old1.w);
+        const bool newT = full || src_T, newP = full || src_P, newC = full || src_C;
+        float4 p0 = old0;
+        if (newT) { const IcxTransform& t = M.T[e]; p0.x = t.scale[0]; p0.y = t.scale[1]; p0.z = t.scale[2]; }
+        if (newP) p0.w = hasP ? P->mass : 0.0f;
+        W.prm0[e] = p0;
+        const bool lockO = newP ? (hasP && P->lockOrigin) : (oldf & EF_LOCK_ORIGIN) != 0;
+        const bool lockR = newP ? (hasP && P->lockOrientation) : (oldf & EF_LOCK_ORIENTATION) != 0;
+        const bool asleep = newP ? (hasP && P->isAsleep) : (oldf & EF_ASLEEP) != 0;
+        const uint32_t cbits = newC ? collider_flag_bits(C) : oldf;
+        const uint32_t ef = entity_flags(id, hasP, lockO, lockR, asleep, p0.w, cbits);
+        float4 p1 = old1;
+        if (newP) { p1.x = hasP ? P->linearDrag : 0.0f; p1.y = hasP ? P->angularDrag : 0.0f; p1.z = hasP ? P->collisionAngularDrag : 0.0f; }
+        p1.w = __uint_as_float(ef);
+        W.prm1[e] = p1;
+        if (newC) W.c_ver[e] = epoch;
+        if (C && (newC || src_T)) import_collider_row(W, e, *C, p0.x, p0.y, p0.z, ef, newC);
     }
 }
 
@@ -142,6 +99,13 @@ __global__ void __launch_bounds__(128) k_export(DeviceWorld W, Mirror M, int hav
         P.acceleration[0] = a.x; P.acceleration[1] = a.y; P.acceleration[2] = a.z;
         P.angularVelocity[0] = w.x; P.angularVelocity[1] = w.y; P.angularVelocity[2] = w.z;
         P.angularAcceleration[0] = al.x; P.angularAcceleration[1] = al.y; P.angularAcceleration[2] = al.z;
+        // the constants live in the SoA too (a replay overwrites them there, server_network_dynamo.cpp:408-412)
+        const float4 p0 = W.prm0[e], p1 = W.prm1[e], lp = W.locked_pos[e], lr = W.locked_rot[e];
+        const uint32_t ef = __float_as_uint(p1.w);
+        P.linearDrag = p1.x; P.angularDrag = p1.y; P.collisionAngularDrag = p1.z; P.collisionLinearDrag = lp.w; P.mass = p0.w;
+        P.lockOrigin = (ef & EF_LOCK_ORIGIN) ? 1 : 0; P.lockOrientation = (ef & EF_LOCK_ORIENTATION) ? 1 : 0; P.isAsleep = (ef & EF_ASLEEP) ? 1 : 0;
+        P.lockedOrigin[0] = lp.x; P.lockedOrigin[1] = lp.y; P.lockedOrigin[2] = lp.z;
+        P.lockedOrientation[0] = lr.x; P.lockedOrientation[1] = lr.y; P.lockedOrientation[2] = lr.z; P.lockedOrientation[3] = lr.w;
     }
     if (have_C) {
         const uint32_t fp = W.first_packet[e];
@@ -239,10 +203,10 @@ void launch_extract_ts(const DeviceWorld& W, const uint32_t* index, const uint8_
 
 void launch_import_kernel(const DeviceWorld& W, Mirror M, const uint32_t* index, const uint32_t* ids, const IcxTransform* T,
                           const IcxPhysics* P, const IcxColliderComponent* C, const uint8_t* hasP, const uint8_t* ts,
-                          const uint16_t* tc, uint32_t count, int full, int have_C, cudaStream_t st)
+                          const uint16_t* tc, uint32_t count, int full, int have_C, uint32_t epoch, cudaStream_t st)
 {
     if (!count) return;
-    k_import<<<(count + 127) / 128, 128, 0, st>>>(W, M, index, ids, T, P, C, hasP, ts, tc, count, full, have_C);
+    k_import<<<(count + 127) / 128, 128, 0, st>>>(W, M, index, ids, T, P, C, hasP, ts, tc, count, full, have_C, epoch);
 }
 void launch_export_kernel(const DeviceWorld& W, Mirror M, int have_T, int have_P, int have_C, uint8_t* ts, uint16_t* tc,
                           uint32_t n, cudaStream_t st)

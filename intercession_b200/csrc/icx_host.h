@@ -11,13 +11,14 @@ namespace icx {
 void launch_integrate_prep(const DeviceWorld& W, double dt, int do_euler, cudaStream_t st);
 void launch_grid(const DeviceWorld& W, cudaStream_t st);      // 4 kernels: scan x3 + scatter
 void launch_pairs(const DeviceWorld& W, cudaStream_t st);
+void launch_budget_update(const DeviceWorld& W, cudaStream_t st);
 void launch_narrow(const DeviceWorld& W, int blocks, cudaStream_t st);
 int resolve_grid_blocks(int device, int phase);               // co-resident blocks of the persistent resolve kernels (0 = prepare, 1 = rounds)
 cudaError_t launch_resolve(const DeviceWorld& W, double dt, int do_euler, int prepare_blocks, int blocks, cudaStream_t st);
 struct Mirror { uint32_t* ids; IcxTransform* T; IcxPhysics* P; IcxColliderComponent* C; uint8_t* hasP; };
 void launch_import_kernel(const DeviceWorld& W, Mirror M, const uint32_t* index, const uint32_t* ids, const IcxTransform* T,
                           const IcxPhysics* P, const IcxColliderComponent* C, const uint8_t* hasP, const uint8_t* ts,
-                          const uint16_t* tc, uint32_t count, int full, int have_C, cudaStream_t st);
+                          const uint16_t* tc, uint32_t count, int full, int have_C, uint32_t epoch, cudaStream_t st);
 void launch_export_kernel(const DeviceWorld& W, Mirror M, int have_T, int have_P, int have_C, uint8_t* ts, uint16_t* tc,
                           uint32_t n, cudaStream_t st);
 
@@ -61,6 +62,10 @@ struct IcxWorld {
     icx::DeviceBuffer mir_ids, mir_T, mir_P, mir_C, mir_hasP;       // device AoS mirror
     icx::DeviceBuffer st_ts, st_tc, st_index, st_T, st_P, st_C;      // staging for tstate and partial updates
     bool have_P = false, have_C = false;
+    uint32_t c_epoch = 1;               // bumped whenever some ColliderComponent changes (upload / update / extract / replayed delta); DeviceWorld::c_ver
+    // collider deltas a replay met while their entity was divergent: kept until the entity takes records again (icx_timeline.cu)
+    icx::DeviceBuffer pend_rows, pend_flag, pend_list, pend_count;
+    bool pend_any = false;
     uint32_t* h_counters = nullptr;     // pinned
     uint32_t* h_flags = nullptr;        // pinned
     IcxStats stats;

@@ -35,6 +35,7 @@ __global__ void __launch_bounds__(256) k_integrate_prep(DeviceWorld W, double de
     W.pos0[e] = r.pos;
     W.dirty_slot[e] = ICX_NONE;
     W.push[e] = 0.0f;
+    { const float k = W.bm_keep[e]; if (k > 0.0f) { const float d = k * 0.85f; W.bm_keep[e] = d > W.margin ? d : 0.0f; } }   // the carried budget floor fades
 
     // ---- per-collider derivation (ColliderSynchro::update + what every later pair test needs) ----
     const uint32_t fp = W.first_packet[e];
@@ -363,8 +364,10 @@ __global__ void __launch_bounds__(PAIRS_TPB, PAIRS_MINB) k_pairs(DeviceWorld W)
                 emit = bz != az ? bz > az : (by != ay ? by > ay : (bx != ax ? bx > ax : j > tq));
                 const uint32_t a = atag & ICX_NB_INDEX_MASK, b = btag & ICX_NB_INDEX_MASK;
                 tight = tight_overlap(alo, ahi, blo, bhi, W.margin);
-                const bool stat = (atag & 0x40000000u) && (btag & 0x40000000u);
-                entry = make_uint2(min(a, b), max(a, b) | (stat ? ICX_PAIR_STATIC : 0u) | (tight ? ICX_PAIR_TIGHT : 0u));
+                const bool ia = (atag & 0x40000000u) != 0, ib = (btag & 0x40000000u) != 0;
+                const bool lo_immut = a < b ? ia : ib, hi_immut = a < b ? ib : ia;
+                entry = make_uint2(min(a, b) | (lo_immut ? ICX_PAIR_A_IMMUT : 0u),
+                                   max(a, b) | ((ia && ib) ? ICX_PAIR_STATIC : 0u) | (tight ? ICX_PAIR_TIGHT : 0u) | (hi_immut ? ICX_PAIR_B_IMMUT : 0u));
             }
         }
         warp_emit(W, S, ws, emit, tight, entry);
@@ -419,7 +422,9 @@ __global__ void __launch_bounds__(PAIRS_TPB, PAIRS_MINB) k_pairs(DeviceWorld W)
                 const float4 qlo = W.pk_lo[q], qhi = W.pk_hi[q];
                 if (overlap(lo, hi, qlo, qhi)) {
                     emit = true; tight = tight_overlap(lo, hi, qlo, qhi, W.margin);
-                    entry = make_uint2(min(p, q), max(p, q) | (immut ? ICX_PAIR_STATIC : 0u) | (tight ? ICX_PAIR_TIGHT : 0u));
+                    // q (large list) is always immutable
+                    entry = make_uint2(min(p, q) | ((p < q ? immut : true) ? ICX_PAIR_A_IMMUT : 0u),
+                                       max(p, q) | (immut ? ICX_PAIR_STATIC : 0u) | (tight ? ICX_PAIR_TIGHT : 0u) | ((p < q ? true : immut) ? ICX_PAIR_B_IMMUT : 0u));
                 }
             }
         }
@@ -429,7 +434,23 @@ __global__ void __launch_bounds__(PAIRS_TPB, PAIRS_MINB) k_pairs(DeviceWorld W)
     warp_flush(W, S.loose[tid >> 5], ws.n_loose, CTR_CANDIDATES, W.pairs, nullptr, 0);
 }
 
+// After an attempt that moved bodies beyond their budget: raise the carried floor of exactly those bodies (run_tick re-runs
+// the tick from the untouched input).
+__global__ void __launch_bounds__(256) k_budget_update(DeviceWorld W)
+{
+    const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= W.n_entities) return;
+    const uint32_t need = W.bm_need[e];
+    if (!need) return;
+    W.bm_need[e] = 0u;
+    W.bm_keep[e] = fmaxf(W.bm_keep[e], (__uint_as_float(need) * 1.5f + 0.01f) / 0.85f);    // k_integrate_prep fades it by 0.85 before use
+}
+
 // ---- launchers ------------------------------------------------------------------------
+void launch_budget_update(const DeviceWorld& W, cudaStream_t st)
+{
+    if (W.n_entities) k_budget_update<<<(W.n_entities + 255) / 256, 256, 0, st>>>(W);
+}
 void launch_integrate_prep(const DeviceWorld& W, double dt, int do_euler, cudaStream_t st)
 {
     if (W.n_entities == 0) return;

@@ -345,9 +345,14 @@ __device__ __forceinline__ void store_side(const DeviceWorld& W, uint32_t e, con
     W.out.angvel[e] = make_float4(S.angvel.x, S.angvel.y, S.angvel.z, 0.0f);
     if (rr) {
         W.out.pos[e] = make_float4(S.origin.x, S.origin.y, S.origin.z, 0.0f);
-        const float lim = W.margin * 0.98f;
-        if (!(fabsf(S.origin.x - s.pos0.x) <= lim && fabsf(S.origin.y - s.pos0.y) <= lim && fabsf(S.origin.z - s.pos0.z) <= lim))
+        // the candidate lists cover a displacement of bm[e] (DESIGN.md "Broadphase bound"): beyond it the tick is re-run with
+        // this body's budget raised (a NaN origin is the reference's problem as much as ours: it is carried along)
+        const float lim = W.bm[e] * 0.98f;
+        const float dmax = fmaxf(fmaxf(fabsf(S.origin.x - s.pos0.x), fabsf(S.origin.y - s.pos0.y)), fabsf(S.origin.z - s.pos0.z));
+        if (dmax > lim && dmax < 3.0e38f) {
             atomicOr(W.flags, RF_MARGIN_VIOLATED);
+            if (atomicMax((int*)&W.bm_need[e], __float_as_int(dmax)) == 0) atomicAdd(&W.counters[CTR_VIOLATORS], 1u);
+        }
     } else {
         W.out.acc[e] = make_float4(S.acc.x, S.acc.y, S.acc.z, 0.0f);
         W.out.angacc[e] = make_float4(S.angacc.x, S.angacc.y, S.angacc.z, 0.0f);
@@ -523,7 +528,7 @@ __global__ void __launch_bounds__(128) k_narrow(const __grid_constant__ DeviceWo
     const uint32_t n = min(W.counters[CTR_TIGHT], W.max_pairs);
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const uint2 pr = W.tight[i];
-    const uint32_t pa = pr.x, pb = pr.y & ICX_NB_INDEX_MASK;
+    const uint32_t pa = pr.x & ICX_NB_INDEX_MASK, pb = pr.y & ICX_NB_INDEX_MASK;
     const uint32_t ea = W.pk_entity[pa], eb = W.pk_entity[pb];
     const int tA = __float_as_uint(W.pk_lpos[pa].w) & PF_TYPE_MASK, tB = __float_as_uint(W.pk_lpos[pb].w) & PF_TYPE_MASK;
     float depth = 0.0f;
@@ -549,100 +554,190 @@ __global__ void __launch_bounds__(128) k_narrow(const __grid_constant__ DeviceWo
     }
 }
 
-// Sorted candidate lists of one dirty body (both collider slots), built by ONE WARP: every packet
-// of another entity whose inflated bound overlaps, ascending by packet index = the order the
-// reference's pair loop meets them (collision_physics_relay.h:29-37).  Lanes 0..17 resolve the
-// 9 rows x 2 bucket ranges around the body's cell, the candidates of all ranges are then tested
-// 32 at a time, and the survivors are ranked by counting (keys are distinct packet indices).
-static __device__ __noinline__ void build_lists_warp(const DeviceWorld& W, uint32_t slot)
+// ---- per-body displacement budgets, the movers' extra candidates, candidate lists -------------
+// The stored bounds S are the shapes' bounds inflated by the uniform W.margin: enough for a body that static resolution
+// moves by less than that during the pass.  A body the speculative pass predicts to be pushed further (push[e] = sum of
+// the depths of its speculative contacts), or that an earlier attempt caught moving further (bm_keep), gets a budget
+// bm[e] > margin.  Candidates are the pairs with overlap(S_i (+) x_i, S_j (+) x_j), x = bm - margin: for x_i = x_j = 0 that
+// is the flat list k_pairs emitted; the rest (xpairs) is found by the movers themselves, one warp each, walking the grid
+// cells their widened bound can reach.  Nobody else pays for a mover.
+static __device__ __forceinline__ void budget_entity(const DeviceWorld& W, uint32_t e)
 {
-    const uint32_t FULL = 0xFFFFFFFFu, lane = threadIdx.x & 31u;
-    const uint32_t e = W.dirty_list[slot];
+    const float m0 = W.margin;
+    const float p = W.push[e], k = W.bm_keep[e];
+    float b = fmaxf(m0, k);
+    if (p > 0.0f) b = fmaxf(b, 1.5f * p + 0.25f * m0);
+    if (!(b == b) || (__float_as_uint(W.prm1[e].w) & EF_IMMUTABLE)) b = m0;
+    W.bm[e] = b;
+    if (b > m0 && (W.first_packet[e] >> 30)) {
+        W.mover_list[atomicAdd(&W.counters[CTR_MOVERS], 1u)] = e;
+        atomicMax((int*)&W.counters[CTR_XMAX], __float_as_int(b - m0));
+    }
+}
+
+__device__ __forceinline__ bool overlap_x(float4 alo, float4 ahi, float xa, float4 blo, float4 bhi, float xb)
+{
+    return alo.x - xa <= bhi.x + xb && blo.x - xb <= ahi.x + xa && alo.y - xa <= bhi.y + xb && blo.y - xb <= ahi.y + xa &&
+           alo.z - xa <= bhi.z + xb && blo.z - xb <= ahi.z + xa;
+}
+
+__device__ __forceinline__ void emit_xpair(const DeviceWorld& W, uint32_t p, uint32_t q, bool q_immut)
+{
+    const uint32_t at = atomicAdd(&W.counters[CTR_XPAIRS], 1u);
+    if (at >= W.max_xpairs) { atomicOr(W.flags, RF_PAIR_OVERFLOW); return; }
+    // p belongs to a mover (mutable)
+    W.xpairs[at] = p < q ? make_uint2(p, q | (q_immut ? ICX_PAIR_B_IMMUT : 0u)) : make_uint2(q | (q_immut ? ICX_PAIR_A_IMMUT : 0u), p);
+}
+
+// One warp per mover entity: every packet whose widened bound overlaps the mover's widened bound but whose stored bound
+// does not (those pairs are in the flat list already).  A partner is binned by the centre of its stored bound, which lies
+// within half a cell of that bound: the walk covers the cells within x_i + x_max + cell / 2 of the mover's stored bound.
+// A pair of two movers is emitted by the one with the lower packet index.  Rows that collide in the bucket hash are visited
+// twice: the duplicates are dropped when the lists are sorted.
+static __device__ __noinline__ void mover_walk_warp(const DeviceWorld& W, uint32_t e, float x_max)
+{
+    const uint32_t lane = threadIdx.x & 31u;
     const uint32_t fp = W.first_packet[e];
     const uint32_t npk = fp >> 30, p0 = fp & 0x3FFFFFFFu;
     const uint32_t wl = W.worldline_stride ? e / W.worldline_stride : 0u;
     const uint32_t n_large = min(W.counters[CTR_LARGE], W.max_large);
-    const uint32_t cap = W.max_neighbors;
-    uint32_t cnt0 = 0, cnt1 = 0;
+    const float m0 = W.margin, xi = W.bm[e] - m0;
+    for (uint32_t k = 0; k < npk; k++) {
+        const uint32_t p = p0 + k;
+        if (W.pk_cell[p] >= 0xFFFFFFFEu) continue;                                  // inert (large colliders are immutable: never movers)
+        const float4 lo = W.pk_lo[p], hi = W.pk_hi[p];
+        const int type = __float_as_uint(W.pk_lpos[p].w) & PF_TYPE_MASK;
+        const float reach = xi + x_max + 0.5005f * W.cell_size;
+        const float sx = reach + 4.0e-6f * fmaxf(fabsf(lo.x), fabsf(hi.x)), sy = reach + 4.0e-6f * fmaxf(fabsf(lo.y), fabsf(hi.y)),
+                    sz = reach + 4.0e-6f * fmaxf(fabsf(lo.z), fabsf(hi.z));
+        const int cx0 = (int)floorf((lo.x - sx) * W.inv_cell), cx1 = (int)floorf((hi.x + sx) * W.inv_cell);
+        const int cy0 = (int)floorf((lo.y - sy) * W.inv_cell), cy1 = (int)floorf((hi.y + sy) * W.inv_cell);
+        const int cz0 = (int)floorf((lo.z - sz) * W.inv_cell), cz1 = (int)floorf((hi.z + sz) * W.inv_cell);
+        for (int cz = cz0; cz <= cz1; cz++)
+            for (int cy = cy0; cy <= cy1; cy++)
+                for (int xb = cx0 >> ICX_XB; xb <= (cx1 >> ICX_XB); xb++) {
+                    const uint32_t block = row_block(xb, cy, cz, wl, W.n_buckets);
+                    const int x_lo = max(cx0, xb << ICX_XB), x_hi = min(cx1, (xb << ICX_XB) + ICX_XMASK);
+                    const uint32_t beg = W.cell_count[(block << ICX_XB) | (uint32_t)(x_lo & ICX_XMASK)];
+                    const uint32_t end = W.cell_count[((block << ICX_XB) | (uint32_t)(x_hi & ICX_XMASK)) + 1u];
+                    for (uint32_t j = beg + lane; j < end; j += 32u) {
+                        const float4 blo = W.s_lo[j], bhi = W.s_hi[j];
+                        const uint32_t btag = __float_as_uint(blo.w), be = __float_as_uint(bhi.w), q = btag & ICX_NB_INDEX_MASK;
+                        if (be == e || (W.worldline_stride && be / W.worldline_stride != wl) || !can_intersect(type, (btag >> 28) & 3, W.cfg_flags)) continue;
+                        const bool q_immut = (btag & 0x40000000u) != 0;
+                        const float xj = q_immut ? 0.0f : W.bm[be] - m0;
+                        if (xj > 0.0f && q < p) continue;                          // two movers: the lower packet's walk emits the pair
+                        if (!overlap_x(lo, hi, xi, blo, bhi, xj) || overlap(lo, hi, blo, bhi)) continue;
+                        emit_xpair(W, p, q, q_immut);
+                    }
+                }
+        for (uint32_t i = lane; i < n_large; i += 32u) {                           // large colliders (immutable, not in the grid)
+            const uint32_t q = W.large_list[i], qe = W.pk_entity[q];
+            if (qe == e || (W.worldline_stride && qe / W.worldline_stride != wl) ||
+                !can_intersect(type, (int)(__float_as_uint(W.pk_lpos[q].w) & PF_TYPE_MASK), W.cfg_flags)) continue;
+            const float4 qlo = W.pk_lo[q], qhi = W.pk_hi[q];
+            if (!overlap_x(lo, hi, xi, qlo, qhi, 0.0f) || overlap(lo, hi, qlo, qhi)) continue;
+            emit_xpair(W, p, q, true);
+        }
+    }
+}
+
+// Candidate lists of the dirty bodies [first, n_dirty): the adjacency of the flat pair list (+ the movers' extra pairs),
+// every list ascending by packet index = the order the reference's pair loop meets the partners
+// (collision_physics_relay.h:29-37).  Streaming pass over the pairs with one atomic append per dirty endpoint, then one
+// warp per body sorts (and drops the duplicates the movers' walks may have produced).
+#define SORT_CAP 128
+__device__ __forceinline__ void list_append(const DeviceWorld& W, uint32_t e, uint32_t p, uint32_t first, uint32_t n_dirty, uint32_t other, uint32_t eo, bool o_immut)
+{
+    const uint32_t s = W.dirty_slot[e];
+    if (s < first || s >= n_dirty) return;                                          // clean (ICX_NONE), or listed already
+    const uint32_t k = p - (W.first_packet[e] & 0x3FFFFFFFu);
+    const uint32_t at = atomicAdd(&W.nbr_count[s * 2u + k], 1u);
+    if (at < W.max_neighbors) W.nbr[(size_t)(s * 2u + k) * W.max_neighbors + at] = make_uint2(other | (o_immut ? ICX_NB_IMMUTABLE : 0u), eo);
+}
+
+static __device__ __noinline__ void sort_lists_warp(const DeviceWorld& W, uint32_t slot, uint2* sm)
+{
+    const uint32_t FULL = 0xFFFFFFFFu, lane = threadIdx.x & 31u;
+    const uint32_t e = W.dirty_list[slot], cap = W.max_neighbors;
+    uint32_t out_cnt[2];
     for (uint32_t k = 0; k < 2u; k++) {
         uint2* list = W.nbr + (size_t)(slot * 2u + k) * cap;
-        uint32_t cnt = 0;                                   // warp-uniform
-        if (k < npk && W.pk_cell[p0 + k] < 0xFFFFFFFEu) {
-            const uint32_t p = p0 + k;
-            const float4 lo = W.pk_lo[p], hi = W.pk_hi[p];
-            const int type = __float_as_uint(W.pk_lpos[p].w) & PF_TYPE_MASK;
-            const int cx = cell_coord(lo.x, hi.x, W.inv_cell), cy = cell_coord(lo.y, hi.y, W.inv_cell), cz = cell_coord(lo.z, hi.z, W.inv_cell);
-            // ---- ranges ----
-            uint32_t beg = 0, len = 0;
-            {
-                const int r = (int)(lane >> 1), part = (int)(lane & 1u);
-                const int xb0 = (cx - 1) >> ICX_XB, xb1 = (cx + 1) >> ICX_XB, xb = xb0 + part;
-                const bool valid = lane < 18u && xb <= xb1;
-                uint32_t key = 0xFFFFFF00u + lane, block = 0;
-                if (valid) { block = row_block(xb, cy + (r % 3 - 1), cz + (r / 3 - 1), wl, W.n_buckets); key = block * 2u + (uint32_t)part; }
-                const uint32_t same = __match_any_sync(FULL, key);
-                if (valid && (uint32_t)(__ffs(same) - 1) == lane) {         // first lane of a duplicated range keeps it
-                    const int x_lo = max(cx - 1, xb << ICX_XB), x_hi = min(cx + 1, (xb << ICX_XB) + ICX_XMASK);
-                    beg = W.cell_count[(block << ICX_XB) | (uint32_t)(x_lo & ICX_XMASK)];
-                    len = W.cell_count[((block << ICX_XB) | (uint32_t)(x_hi & ICX_XMASK)) + 1u] - beg;
-                }
-            }
-            uint32_t off = len;                              // inclusive scan -> exclusive offsets
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(FULL, off, o); if (lane >= (uint32_t)o) off += y; }
-            const uint32_t total = __shfl_sync(FULL, off, 31) + n_large;
-            off -= len;
-            const uint32_t n_grid_cand = total - n_large;
-            // ---- candidates, 32 at a time (grid ranges first, then the large-collider list) ----
-            for (uint32_t base = 0; base < total; base += 32u) {
-                const uint32_t idx = base + lane;
-                uint32_t j = ICX_NONE;
-#pragma unroll
-                for (int r = 0; r < 18; r++) {
-                    const uint32_t ro = __shfl_sync(FULL, off, r), rl = __shfl_sync(FULL, len, r), rb = __shfl_sync(FULL, beg, r);
-                    if (idx >= ro && idx < ro + rl) j = rb + (idx - ro);
-                }
-                uint2 entry = make_uint2(0u, 0u); bool pass = false;
-                if (j != ICX_NONE) {
-                    const float4 blo = W.s_lo[j], bhi = W.s_hi[j];
-                    const uint32_t btag = __float_as_uint(blo.w), be = __float_as_uint(bhi.w);
-                    pass = overlap(lo, hi, blo, bhi) && be != e && (!W.worldline_stride || be / W.worldline_stride == wl) &&
-                           can_intersect(type, (btag >> 28) & 3, W.cfg_flags);
-                    entry = make_uint2((btag & ICX_NB_INDEX_MASK) | ((btag & 0x40000000u) ? ICX_NB_IMMUTABLE : 0u), be);
-                } else if (idx >= n_grid_cand && idx < total) {
-                    const uint32_t o = W.large_list[idx - n_grid_cand];
-                    const uint32_t oe = W.pk_entity[o];
-                    pass = oe != e && (!W.worldline_stride || oe / W.worldline_stride == wl) &&
-                           can_intersect(type, (int)(__float_as_uint(W.pk_lpos[o].w) & PF_TYPE_MASK), W.cfg_flags) &&
-                           overlap(lo, hi, W.pk_lo[o], W.pk_hi[o]);
-                    entry = make_uint2(o | ICX_NB_IMMUTABLE, oe);
-                }
-                const uint32_t m = __ballot_sync(FULL, pass);
-                if (pass) { const uint32_t at = cnt + __popc(m & ((1u << lane) - 1u)); if (at < cap) list[at] = entry; }
-                cnt += __popc(m);
+        uint32_t cnt = W.nbr_count[slot * 2u + k];
+        if (cnt > cap) { if (lane == 0) atomicOr(W.flags, RF_NEIGHBOR_OVERFLOW); cnt = cap; }
+        if (cnt <= 32u) {
+            const uint2 mine = lane < cnt ? list[lane] : make_uint2(0xFFFFFFFFu, 0u);
+            const uint32_t key = mine.x & ICX_NB_INDEX_MASK;
+            bool first = lane < cnt;
+            for (uint32_t q = 0; q < cnt; q++) { const uint32_t other = __shfl_sync(FULL, key, q); if (q < lane && other == key) first = false; }
+            const uint32_t firsts = __ballot_sync(FULL, first);
+            uint32_t rank = 0;
+            for (uint32_t q = 0; q < cnt; q++) { const uint32_t other = __shfl_sync(FULL, key, q); rank += ((firsts >> q & 1u) && other < key) ? 1u : 0u; }
+            __syncwarp();
+            if (first) list[rank] = mine;
+            cnt = __popc(firsts);
+        } else if (cnt <= SORT_CAP) {
+            for (uint32_t i = lane; i < cnt; i += 32u) sm[i] = list[i];
+            __syncwarp();
+            uint32_t dupmask = 0;                                                   // bit t: my element lane + 32 t repeats an earlier one
+            for (uint32_t i = lane, t = 0; i < cnt; i += 32u, t++) {
+                const uint32_t key = sm[i].x & ICX_NB_INDEX_MASK;
+                bool dup = false;
+                for (uint32_t q = 0; q < i; q++) dup |= (sm[q].x & ICX_NB_INDEX_MASK) == key;
+                if (dup) dupmask |= 1u << t;
             }
             __syncwarp();
-            if (cnt > cap) { if (lane == 0) atomicOr(W.flags, RF_NEIGHBOR_OVERFLOW); cnt = cap; }
-            // ---- sort ascending by packet index ----
-            if (cnt <= 32u) {
-                const uint2 mine = lane < cnt ? list[lane] : make_uint2(0xFFFFFFFFu, 0u);
+            for (uint32_t i = lane, t = 0; i < cnt; i += 32u, t++) if (dupmask >> t & 1u) sm[i].y |= 0x80000000u;    // entity indices are < 2^24
+            __syncwarp();
+            uint32_t kept = 0;
+            for (uint32_t i = lane, t = 0; i < cnt; i += 32u, t++) {
+                if (dupmask >> t & 1u) continue;
+                const uint2 mine = sm[i]; const uint32_t key = mine.x & ICX_NB_INDEX_MASK;
                 uint32_t rank = 0;
-                for (uint32_t q = 0; q < cnt; q++) { const uint32_t other = __shfl_sync(FULL, mine.x, q); rank += ((other & ICX_NB_INDEX_MASK) < (mine.x & ICX_NB_INDEX_MASK)) ? 1u : 0u; }
-                __syncwarp();
-                if (lane < cnt) list[rank] = mine;
-            } else if (lane == 0) {
+                for (uint32_t q = 0; q < cnt; q++) { const uint2 o = sm[q]; rank += (!(o.y >> 31) && (o.x & ICX_NB_INDEX_MASK) < key) ? 1u : 0u; }
+                list[rank] = mine; kept++;
+            }
+            cnt = __reduce_add_sync(FULL, kept);
+            __syncwarp();
+        } else {
+            if (lane == 0) {
                 for (uint32_t i = 1; i < cnt; i++) {
                     const uint2 v = list[i]; uint32_t q = i;
                     while (q > 0 && (list[q - 1].x & ICX_NB_INDEX_MASK) > (v.x & ICX_NB_INDEX_MASK)) { list[q] = list[q - 1]; q--; }
                     list[q] = v;
                 }
+                uint32_t w = cnt ? 1u : 0u;
+                for (uint32_t i = 1; i < cnt; i++) if ((list[i].x & ICX_NB_INDEX_MASK) != (list[w - 1].x & ICX_NB_INDEX_MASK)) list[w++] = list[i];
+                cnt = w;
             }
-            __syncwarp();
+            cnt = __shfl_sync(FULL, cnt, 0);
         }
+        __syncwarp();
         if (lane == 0) W.nbr_count[slot * 2u + k] = cnt;
-        if (k == 0u) cnt0 = cnt; else cnt1 = cnt;
+        out_cnt[k] = cnt;
     }
-    if (lane == 0) W.slot_info[slot] = make_uint4(fp, cnt0, cnt1, e);
+    if (lane == 0) W.slot_info[slot] = make_uint4(W.first_packet[e], out_cnt[0], out_cnt[1], e);
+}
+
+template <typename Grid>
+__device__ __forceinline__ void lists_build(const DeviceWorld& W, uint32_t first, uint32_t n_dirty, Grid& grid, uint32_t tid, uint32_t nth, uint2* sort_sm)
+{
+    if (first >= n_dirty) return;                                                   // uniform
+    for (uint32_t s = first + tid; s < n_dirty; s += nth) { W.nbr_count[s * 2u] = 0u; W.nbr_count[s * 2u + 1u] = 0u; }
+    grid.sync();
+    const uint32_t n_pairs = min(*(volatile uint32_t*)&W.counters[CTR_CANDIDATES], W.max_pairs);
+    const uint32_t n_x = min(*(volatile uint32_t*)&W.counters[CTR_XPAIRS], W.max_xpairs);
+    for (uint32_t i = tid; i < n_pairs + n_x; i += nth) {
+        const uint2 pr = i < n_pairs ? W.pairs[i] : W.xpairs[i - n_pairs];
+        const uint32_t pa = pr.x & ICX_NB_INDEX_MASK, pb = pr.y & ICX_NB_INDEX_MASK;
+        const bool ia = (pr.x & ICX_PAIR_A_IMMUT) != 0, ib = (pr.y & ICX_PAIR_B_IMMUT) != 0;
+        if (ia && ib) continue;
+        const uint32_t ea = W.pk_entity[pa], eb = W.pk_entity[pb];
+        if (!ia) list_append(W, ea, pa, first, n_dirty, pb, eb, ib);
+        if (!ib) list_append(W, eb, pb, first, n_dirty, pa, ea, ia);
+    }
+    grid.sync();
+    for (uint32_t s = first + (tid >> 5); s < n_dirty; s += (nth >> 5)) sort_lists_warp(W, s, sort_sm);
 }
 
 // Put a dirty body back to its post-integration state (bit-identical recomputation from the tick input).
@@ -945,7 +1040,7 @@ __device__ __forceinline__ void trace_mark(const DeviceWorld& W, uint32_t& n, ui
 #define PREPARE_MINB 2
 #endif
 template <int PHASE>
-__device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, int do_euler, V3* scratch)
+__device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, int do_euler, V3* scratch, uint2* sort_sm)
 {
     uint32_t tn = 2;        // trace[0] = number of words used
     if (PHASE == 1 && W.trace) tn = (uint32_t)W.trace[0];
@@ -959,11 +1054,21 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
         // those are replayed in order too and inherit the remainder of the push.  One warp per dirty body walks
         // its candidate list, at most three generations.  Only a prediction: a body it misses triggers the
         // restart further down.
+        // budgets of all bodies, then the movers' own candidates (see budget_entity / mover_walk_warp)
+        for (uint32_t e = tid; e < W.n_entities; e += nth) budget_entity(W, e);
+        grid.sync();
+        {
+            const uint32_t n_mov = min(ctr[CTR_MOVERS], W.n_entities);
+            const float x_max = __uint_as_float(ctr[CTR_XMAX]);
+            for (uint32_t m = tid >> 5; m < n_mov; m += (nth >> 5)) mover_walk_warp(W, W.mover_list[m], x_max);
+            if (tid == 0) trace_mark(W, tn, 0x80000u | min(n_mov, 0xFFFFu));
+        }
+        grid.sync();
         uint32_t done = 0;
         for (int sweep = 0; sweep < 3; sweep++) {
             const uint32_t n_dirty = ctr[CTR_DIRTY];
             if (n_dirty == done) break;                         // uniform: read after a grid barrier
-            for (uint32_t sl = done + (tid >> 5); sl < n_dirty; sl += (nth >> 5)) build_lists_warp(W, sl);
+            lists_build(W, done, n_dirty, grid, tid, nth, sort_sm);
             grid.sync();
             if (tid == 0) trace_mark(W, tn, 0x60000u | min(n_dirty - done, 0xFFFFu));      // lists of this sweep's bodies built
             for (uint32_t sl = done + (tid >> 5); sl < n_dirty; sl += (nth >> 5)) {
@@ -1004,7 +1109,7 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
         if (PHASE == 1 && attempts == 0) {                  // the prepare launch did all of this for the first attempt
             if (*(volatile uint32_t*)W.flags & RF_NEIGHBOR_OVERFLOW) break;
         } else {
-        for (uint32_t s = n_listed + (tid >> 5); s < n_dirty; s += (nth >> 5)) build_lists_warp(W, s);
+        lists_build(W, n_listed, n_dirty, grid, tid, nth, sort_sm);
         for (uint32_t s = tid; s < n_dirty; s += nth)
             if (attempts > 0 && s < n_listed) restore_body(W, W.dirty_list[s], dt, do_euler);
         if (tid == 0) trace_mark(W, tn, 0x10000u | min(n_dirty, 0xFFFFu));
@@ -1079,13 +1184,15 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
 
 __global__ void __launch_bounds__(PREPARE_TPB, PREPARE_MINB) k_resolve_prepare(const __grid_constant__ DeviceWorld W, double dt, int do_euler)
 {
-    resolve_body<0>(W, dt, do_euler, nullptr);
+    __shared__ uint2 sort_all[PREPARE_TPB / 32][SORT_CAP];
+    resolve_body<0>(W, dt, do_euler, nullptr, sort_all[threadIdx.x >> 5]);
 }
 __global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(const __grid_constant__ DeviceWorld W, double dt, int do_euler)
 {
     // per-warp scratch of the exact procedures (contact manifolds, clipping): see pseudo_clip_polyhedra_s
     __shared__ V3 scratch_all[RESOLVE_TPB / 32][8 + 2 * ICX_MAXV];
-    resolve_body<1>(W, dt, do_euler, scratch_all[threadIdx.x >> 5]);
+    __shared__ uint2 sort_all[RESOLVE_TPB / 32][SORT_CAP];
+    resolve_body<1>(W, dt, do_euler, scratch_all[threadIdx.x >> 5], sort_all[threadIdx.x >> 5]);
 }
 
 void launch_narrow(const DeviceWorld& W, int blocks, cudaStream_t st)

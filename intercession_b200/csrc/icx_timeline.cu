@@ -1,38 +1,64 @@
 // World-line record / replay / divergence scan on a device-resident
 // snapshot ring.
 //
-// The reference records by serialising every entity into a heap message on a per-entity mutexed
-// list each tick (server_network_dynamo.cpp:642-679, parallel_network_dynamo.cpp:369-385) and
-// replays by popping them again (server_network_dynamo.cpp:377-421).  Here the dense ENTITY_UPDATE
-// stream is a ring of SoA snapshots in HBM: slot = coherency % depth, stamped with the coherency
-// it holds.  Rare, variable-length events (create / remove / jump) stay on the host queues.
-//   k_record          7 SoA arrays -> ring slot, 128-bit loads/stores, one launch
-//   k_replay          ring slot -> world, predicated on the timestream state (non-divergent only)
+// The reference records by serialising every entity -- ALL of its components (ComponentCategory::all,
+// server_network_dynamo.cpp:666-677, parallel_network_dynamo.cpp:369-385) -- into a heap message on a
+// per-entity mutexed list each tick and replays by popping them again and overwriting all components
+// of the non-divergent entities (server_network_dynamo.cpp:377-421).  Here the dense ENTITY_UPDATE
+// stream is a ring of SoA snapshots in HBM: slot = coherency % depth, stamped with the coherency it
+// holds.  A slot carries, per entity, the whole TransformComponent + PhysicsComponent (10 float4: the
+// six mutable ones plus scale|mass, drags|flag bits, lockedOrigin|collisionLinearDrag, lockedOrientation)
+// and the id the receiving cosmos knows the entity by (causal chain-link + 1, :673); the
+// ColliderComponent, which changes rarely (BipedBehaviors writes restLength / damping of its own
+// entities, biped_behaviors.h:96-100), travels as a SPARSE list of {entity, 168-byte row} per slot for
+// the entities whose component changed since the previous record into this ring (DeviceWorld::c_ver
+// against IcxTimeline::seen).  Rare, variable-length events (create / remove / jump) stay on the host queues.
+//   k_record          11 SoA arrays -> ring slot, 128-bit loads/stores, one launch
+//   k_replay          ring slot -> world, predicated on the timestream state (non-divergent only) and on the id
+//   k_delta_*         sparse collider rows: collect on record, apply (or stash while divergent) on replay
 //   k_divergence_scan TMA-staged (cp.async.bulk + mbarrier, 3-stage ring in shared memory) diff of
 //                     live vs recorded origins, congruence predicate of timejump_conditions.h:21-25,
 //                     reduced per world-line to {incongruent bodies, fixed-point score}
 //   k_fork_age        forking -> forked promotion and the divergence notification
 //                     (server_network_dynamo.cpp:681-705)
-// All four are pure HBM streaming kernels.
+// All of them are pure HBM streaming kernels.
 #include <algorithm>
 #include <cstring>
 #include <new>
 #include "icx_host.h"
+#include "icx_rows.cuh"
 
 using namespace icx;
 
+#define TL_ARRAYS 10                    // float4 arrays per slot: pos rot vel acc angvel angacc | prm0 prm1 locked_pos locked_rot
+
+struct DeltaRow { uint32_t idx, _pad; IcxColliderComponent C; };       // 176 B, 16-byte aligned
+static_assert(sizeof(DeltaRow) == ICX_SNAPSHOT_DELTA_BYTES, "delta row layout");
+
 struct IcxTimeline {
-    int device = 0;
+    int device = 0, sms = 148;
     uint32_t depth = 0, n_max = 0;
-    float4* state = nullptr;            // [depth][6][n_max]: pos, rot, vel, acc, angvel, angacc
-    uint32_t* ts = nullptr;             // [depth][n_max]
+    float4* state = nullptr;            // [depth][TL_ARRAYS][n_max]
+    uint32_t* ids = nullptr;            // [depth][n_max]: id under which the RECEIVER knows the entity
     std::vector<uint16_t> stamp;        // coherency held by each slot
     std::vector<uint8_t> valid;
     std::vector<uint8_t> behind;        // slot lies behind the breakpoint (old history, TsBreakpointQueue)
+    std::vector<uint64_t> seq;          // push order (FIFO order of the per-entity lists)
+    uint64_t next_seq = 1;
     bool breakpoint_active = false;
     std::vector<uint32_t> count;        // entities recorded in each slot
+    // sparse collider rows
+    DeltaRow* delta = nullptr; uint32_t delta_cap = 0;      // [depth][delta_cap]
+    uint32_t* d_delta_n = nullptr;      // [depth + 1] rows held by each slot (device), + one scratch counter
+    std::vector<int64_t> delta_n;       // host view: rows in the slot, -1 = unknown (imported)
+    uint32_t* seen = nullptr;           // [n_max]: DeviceWorld::c_ver of each entity at its last collected row
+    const IcxWorld* last_recorder = nullptr; uint32_t last_epoch = 0;
+    unsigned long long* d_mismatch = nullptr;   // entities a replay skipped because the recorded id is not theirs
+    std::vector<cudaEvent_t> slot_ev;   // slot contents complete (record / import) -- waited on by replay / export on other streams
     // scan outputs (device) + pinned host mirror
     unsigned long long* d_score = nullptr; uint32_t* d_count = nullptr; uint32_t cap_wl = 0;
+    uint8_t* d_ever = nullptr;          // per world-line: flagged by some scan since the last reset
+    cudaStream_t scan_stream = nullptr; uint32_t scan_wl = 0;
     uint32_t* d_age = nullptr;          // [0] promoted, [1] resolution needed
     // optional kernel timing (icx_timeline_profile): events around the last record / replay / scan launch
     bool profile = false;
@@ -45,29 +71,131 @@ namespace {
 
 #define TCK(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) { if (tl) tl->error = std::string(#call) + ": " + cudaGetErrorString(_e); return ICX_E_CUDA; } } while (0)
 
-__global__ void __launch_bounds__(256) k_record(EntityState S, float4* __restrict__ dst, uint32_t* __restrict__ dst_ts, uint32_t n, uint32_t n_max)
+struct RecordSrc { EntityState S; const float4* prm0; const float4* prm1; const float4* locked_pos; const float4* locked_rot; const uint32_t* entity_id; };
+
+// increment_causal_chain_link, ecs_types.h:118-136: refused for link >= 14 (14 + 1 would be the null link)
+__device__ __forceinline__ uint32_t inc_link(uint32_t id) { return (id & 0xFu) + 1u >= 15u ? id : id + 1u; }
+
+__global__ void __launch_bounds__(256) k_record(RecordSrc R, float4* __restrict__ dst, uint32_t* __restrict__ dst_ids, uint32_t n, uint32_t n_max, int link_inc)
 {
     // thread i moves one float4 of each array: a warp moves 512 contiguous bytes per array
+    const size_t m = n_max;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const float4 a = S.pos[i], b = S.rot[i], c = S.vel[i], d = S.acc[i], e = S.angvel[i], f = S.angacc[i];
-        const uint32_t t = S.ts[i];
-        dst[i] = a; dst[(size_t)n_max + i] = b; dst[2 * (size_t)n_max + i] = c; dst[3 * (size_t)n_max + i] = d;
-        dst[4 * (size_t)n_max + i] = e; dst[5 * (size_t)n_max + i] = f;
-        dst_ts[i] = t;
+        const float4 a = R.S.pos[i], b = R.S.rot[i], c = R.S.vel[i], d = R.S.acc[i], e = R.S.angvel[i], f = R.S.angacc[i];
+        const float4 g = R.prm0[i], h = R.prm1[i], k = R.locked_pos[i], l = R.locked_rot[i];
+        const uint32_t id = R.entity_id[i];
+        dst[i] = a; dst[m + i] = b; dst[2 * m + i] = c; dst[3 * m + i] = d; dst[4 * m + i] = e; dst[5 * m + i] = f;
+        dst[6 * m + i] = g; dst[7 * m + i] = h; dst[8 * m + i] = k; dst[9 * m + i] = l;
+        dst_ids[i] = link_inc ? inc_link(id) : id;                                  // server_network_dynamo.cpp:673
     }
 }
 
 // ENTITY_UPDATE replay, server_network_dynamo.cpp:396-420: a non-divergent entity takes every
 // component of the record; a divergent one only the `upstream` category, which holds no physics
-// component (hard_config_cosmos.h:47-58 registers only SpacialInputComponent upstream).
-__global__ void __launch_bounds__(256) k_replay(EntityState S, const float4* __restrict__ src, uint32_t n, uint32_t n_src, uint32_t n_max)
+// component (hard_config_cosmos.h:47-58 registers only SpacialInputComponent upstream).  The record is
+// addressed to the id it carries: an entity whose id differs is left alone and counted.
+__global__ void __launch_bounds__(256) k_replay(DeviceWorld W, const float4* __restrict__ src, const uint32_t* __restrict__ src_ids,
+                                                uint32_t n, uint32_t n_src, uint32_t n_max, unsigned long long* __restrict__ mismatch)
 {
+    const EntityState S = W.in;
+    const size_t m = n_max;
+    uint32_t bad = 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const uint32_t state = S.ts[i] & 0xFFu;
         if (state == ICX_TS_FORKING || state == ICX_TS_FORKED) continue;            // is_divergent, timestream_state.h:41-44
         const uint32_t j = n_src == n ? i : i % n_src;
-        S.pos[i] = src[j]; S.rot[i] = src[(size_t)n_max + j]; S.vel[i] = src[2 * (size_t)n_max + j];
-        S.acc[i] = src[3 * (size_t)n_max + j]; S.angvel[i] = src[4 * (size_t)n_max + j]; S.angacc[i] = src[5 * (size_t)n_max + j];
+        const uint32_t id = W.entity_id[i];
+        if (n_src == n && src_ids[j] != id) { bad++; continue; }
+        S.pos[i] = src[j]; S.rot[i] = src[m + j];                                   // TransformComponent
+        const float4 r0 = src[6 * m + j], r1 = src[7 * m + j];
+        const float4 o0 = W.prm0[i], o1 = W.prm1[i];
+        const uint32_t recf = __float_as_uint(r1.w), oldf = __float_as_uint(o1.w);
+        const bool both = (recf & EF_HAS_PHYSICS) && (oldf & EF_HAS_PHYSICS);       // deserialize_data_for does nothing for a missing component
+        float4 p0 = make_float4(r0.x, r0.y, r0.z, both ? r0.w : o0.w);
+        float4 p1 = o1; uint32_t lockbits = oldf;
+        if (both) {                                                                 // PhysicsComponent
+            S.vel[i] = src[2 * m + j]; S.acc[i] = src[3 * m + j]; S.angvel[i] = src[4 * m + j]; S.angacc[i] = src[5 * m + j];
+            W.locked_pos[i] = src[8 * m + j]; W.locked_rot[i] = src[9 * m + j];
+            p1 = r1; lockbits = recf;
+        }
+        const bool hasP = (oldf & EF_HAS_PHYSICS) != 0;
+        p1.w = __uint_as_float(entity_flags(id, hasP, (lockbits & EF_LOCK_ORIGIN) != 0, (lockbits & EF_LOCK_ORIENTATION) != 0,
+                                            (lockbits & EF_ASLEEP) != 0, p0.w, oldf));
+        W.prm0[i] = p0; W.prm1[i] = p1;
+    }
+    bad = __reduce_add_sync(0xFFFFFFFFu, bad);
+    if (bad && (threadIdx.x & 31u) == 0) atomicAdd(mismatch, (unsigned long long)bad);
+}
+
+// ---- sparse ColliderComponent rows ----
+__global__ void __launch_bounds__(256) k_delta_count(const uint32_t* __restrict__ c_ver, const uint32_t* __restrict__ seen, uint32_t n, int all,
+                                                     uint32_t* __restrict__ out)
+{
+    uint32_t c = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) c += (all || c_ver[i] != seen[i]) ? 1u : 0u;
+    c = __reduce_add_sync(0xFFFFFFFFu, c);
+    if (c && (threadIdx.x & 31u) == 0) atomicAdd(out, c);
+}
+__global__ void __launch_bounds__(256) k_delta_collect(const uint32_t* __restrict__ c_ver, uint32_t* __restrict__ seen, const IcxColliderComponent* __restrict__ C,
+                                                       uint32_t n, int all, DeltaRow* __restrict__ dst, uint32_t cap, uint32_t* __restrict__ counter)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t v = c_ver[i];
+        if (!all && v == seen[i]) continue;
+        seen[i] = v;
+        const uint32_t at = atomicAdd(counter, 1u);
+        if (at < cap) { dst[at].idx = i; dst[at]._pad = 0; dst[at].C = C[i]; }
+    }
+}
+
+// one collider row into entity e: AoS mirror (the source of later downloads / records), per-packet constants, flag word
+__device__ __forceinline__ void apply_collider_row(const DeviceWorld& W, IcxColliderComponent* __restrict__ MC, uint32_t e, IcxColliderComponent row,
+                                                   uint32_t epoch, unsigned long long* __restrict__ mismatch)
+{
+    const uint32_t npk = W.first_packet[e] >> 30;
+    uint32_t act = 0;
+    for (int s = 0; s < ICX_COLLIDERS_PER_ENTITY; s++) {
+        if (row.colliders[s].isActive) act++;
+        row.colliders[s].minParametricValue = MC[e].colliders[s].minParametricValue;   // per-tick scratch (Collider::reset), not state
+    }
+    if (act != npk) { atomicAdd(mismatch, 1ull); return; }                           // packet structure differs: needs a re-upload
+    MC[e] = row;
+    const float4 p0 = W.prm0[e]; float4 p1 = W.prm1[e];
+    const uint32_t oldf = __float_as_uint(p1.w);
+    const uint32_t ef = entity_flags(W.entity_id[e], (oldf & EF_HAS_PHYSICS) != 0, (oldf & EF_LOCK_ORIGIN) != 0, (oldf & EF_LOCK_ORIENTATION) != 0,
+                                     (oldf & EF_ASLEEP) != 0, p0.w, collider_flag_bits(&row));
+    p1.w = __uint_as_float(ef); W.prm1[e] = p1;
+    import_collider_row(W, e, row, p0.x, p0.y, p0.z, ef, false);
+    W.c_ver[e] = epoch;
+}
+
+// Rows of one slot: applied to non-divergent entities (ComponentCategory::all), kept aside for divergent ones -- the
+// reference's records carry every component every tick, so the first record such an entity takes again restores them.
+__global__ void __launch_bounds__(128) k_replay_delta(DeviceWorld W, IcxColliderComponent* __restrict__ MC, const DeltaRow* __restrict__ rows,
+                                                      const uint32_t* __restrict__ d_n, uint32_t cap, uint32_t epoch,
+                                                      IcxColliderComponent* __restrict__ pend_rows, uint8_t* __restrict__ pend_flag,
+                                                      unsigned long long* __restrict__ mismatch)
+{
+    const uint32_t n = min(*d_n, cap);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t e = rows[i].idx;
+        if (e >= W.n_entities) { atomicAdd(mismatch, 1ull); continue; }
+        const uint32_t state = W.in.ts[e] & 0xFFu;
+        if (state == ICX_TS_FORKING || state == ICX_TS_FORKED) { pend_rows[e] = rows[i].C; pend_flag[e] = 1; continue; }
+        pend_flag[e] = 0;
+        apply_collider_row(W, MC, e, rows[i].C, epoch, mismatch);
+    }
+}
+__global__ void __launch_bounds__(256) k_replay_pending(DeviceWorld W, IcxColliderComponent* __restrict__ MC, uint32_t epoch,
+                                                        const IcxColliderComponent* __restrict__ pend_rows, uint8_t* __restrict__ pend_flag,
+                                                        unsigned long long* __restrict__ mismatch)
+{
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < W.n_entities; e += gridDim.x * blockDim.x) {
+        if (!pend_flag[e]) continue;
+        const uint32_t state = W.in.ts[e] & 0xFFu;
+        if (state == ICX_TS_FORKING || state == ICX_TS_FORKED) continue;
+        pend_flag[e] = 0;
+        apply_collider_row(W, MC, e, pend_rows[e], epoch, mismatch);
     }
 }
 
@@ -218,6 +346,37 @@ __global__ void __launch_bounds__(256) k_fork_age(uint32_t* __restrict__ ts, uin
 }
 
 int slot_of(const IcxTimeline* tl, uint16_t coherency) { return (int)(coherency % tl->depth); }
+float4* slot_state(const IcxTimeline* tl, int s) { return tl->state + (size_t)s * TL_ARRAYS * tl->n_max; }
+uint32_t* slot_ids(const IcxTimeline* tl, int s) { return tl->ids + (size_t)s * tl->n_max; }
+int stream_blocks(const IcxTimeline* tl, uint32_t n, int per_sm) { return (int)std::min<uint32_t>((n + 255) / 256, (uint32_t)(tl->sms * per_sm)); }
+
+// Per-slot capacity of the sparse collider rows (grown on demand; existing rows are kept).
+int ensure_delta_cap(IcxTimeline* tl, uint32_t rows)
+{
+    if (rows <= tl->delta_cap) return ICX_OK;
+    uint32_t cap = std::max<uint32_t>(64, tl->delta_cap);
+    while (cap < rows) cap *= 2;
+    DeltaRow* fresh = nullptr;
+    TCK(cudaMalloc((void**)&fresh, (size_t)tl->depth * cap * sizeof(DeltaRow)));
+    if (tl->delta) {
+        TCK(cudaDeviceSynchronize());
+        TCK(cudaMemcpy2D(fresh, (size_t)cap * sizeof(DeltaRow), tl->delta, (size_t)tl->delta_cap * sizeof(DeltaRow),
+                         (size_t)tl->delta_cap * sizeof(DeltaRow), tl->depth, cudaMemcpyDeviceToDevice));
+        cudaFree(tl->delta);
+    }
+    tl->delta = fresh; tl->delta_cap = cap;
+    return ICX_OK;
+}
+
+// A world that replays collider rows needs somewhere to keep the rows of entities that are divergent at that moment.
+int ensure_pending(IcxWorld* w, IcxTimeline* tl)
+{
+    if (w->pend_flag.ptr) return ICX_OK;
+    TCK(w->pend_rows.ensure((size_t)w->cap_entities * sizeof(IcxColliderComponent)));
+    TCK(w->pend_flag.ensure(w->cap_entities));
+    TCK(cudaMemsetAsync(w->pend_flag.ptr, 0, w->cap_entities, w->stream));
+    return ICX_OK;
+}
 
 } // namespace
 
@@ -232,10 +391,19 @@ int icx_timeline_create(int device, uint32_t depth_ticks, uint32_t n_max, IcxTim
     if (!tl) return ICX_E_NOMEM;
     tl->device = device; tl->depth = depth_ticks; tl->n_max = n_max;
     tl->stamp.assign(depth_ticks, 0); tl->valid.assign(depth_ticks, 0); tl->behind.assign(depth_ticks, 0); tl->count.assign(depth_ticks, 0);
+    tl->seq.assign(depth_ticks, 0); tl->delta_n.assign(depth_ticks, 0); tl->slot_ev.assign(depth_ticks, nullptr);
     cudaSetDevice(device);
-    cudaError_t e = cudaMalloc((void**)&tl->state, (size_t)depth_ticks * 6 * n_max * sizeof(float4));
-    if (e == cudaSuccess) e = cudaMalloc((void**)&tl->ts, (size_t)depth_ticks * n_max * sizeof(uint32_t));
+    cudaDeviceGetAttribute(&tl->sms, cudaDevAttrMultiProcessorCount, device);
+    cudaError_t e = cudaMalloc((void**)&tl->state, (size_t)depth_ticks * TL_ARRAYS * n_max * sizeof(float4));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&tl->ids, (size_t)depth_ticks * n_max * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&tl->seen, (size_t)n_max * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&tl->d_delta_n, ((size_t)depth_ticks + 1) * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&tl->d_mismatch, sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc((void**)&tl->d_age, 2 * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMemset(tl->seen, 0, (size_t)n_max * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMemset(tl->d_delta_n, 0, ((size_t)depth_ticks + 1) * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMemset(tl->d_mismatch, 0, sizeof(unsigned long long));
+    for (uint32_t k = 0; k < depth_ticks && e == cudaSuccess; k++) e = cudaEventCreateWithFlags(&tl->slot_ev[k], cudaEventDisableTiming);
     if (e != cudaSuccess) { icx_timeline_destroy(tl); return e == cudaErrorMemoryAllocation ? ICX_E_NOMEM : ICX_E_CUDA; }
     *out = tl;
     return ICX_OK;
@@ -245,11 +413,10 @@ void icx_timeline_destroy(IcxTimeline* tl)
 {
     if (!tl) return;
     cudaSetDevice(tl->device);
-    if (tl->state) cudaFree(tl->state);
-    if (tl->ts) cudaFree(tl->ts);
-    if (tl->d_score) cudaFree(tl->d_score);
-    if (tl->d_count) cudaFree(tl->d_count);
-    if (tl->d_age) cudaFree(tl->d_age);
+    cudaDeviceSynchronize();
+    void* bufs[] = {tl->state, tl->ids, tl->seen, tl->d_delta_n, tl->d_mismatch, tl->delta, tl->d_score, tl->d_count, tl->d_ever, tl->d_age};
+    for (void* b : bufs) if (b) cudaFree(b);
+    for (cudaEvent_t e : tl->slot_ev) if (e) cudaEventDestroy(e);
     for (auto& pair : tl->pev) for (cudaEvent_t e : pair) if (e) cudaEventDestroy(e);
     delete tl;
 }
@@ -276,12 +443,21 @@ int icx_timeline_kernel_ms(IcxTimeline* tl, int which, float* ms)
     return ICX_OK;
 }
 
-static int record_impl(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, bool at_breakpoint);
-int icx_record(IcxWorld* w, IcxTimeline* tl, uint16_t coherency) { return record_impl(w, tl, coherency, false); }
+int icx_timeline_id_mismatches(IcxTimeline* tl, uint64_t* total)
+{
+    if (!tl || !total) return ICX_E_INVALID;
+    cudaSetDevice(tl->device);
+    unsigned long long v = 0;
+    TCK(cudaDeviceSynchronize());
+    TCK(cudaMemcpy(&v, tl->d_mismatch, sizeof(v), cudaMemcpyDeviceToHost));
+    *total = v;
+    return ICX_OK;
+}
+
+int icx_record(IcxWorld* w, IcxTimeline* tl, uint16_t coherency) { return icx_record_ex(w, tl, coherency, 0); }
 int icx_record_at_breakpoint(IcxWorld* w, IcxTimeline* tl, uint16_t coherency)
 {
-    if (tl && !tl->breakpoint_active) { tl->error = "record_at_breakpoint: no breakpoint set"; return ICX_E_STATE; }   // push_at_breakpoint returns false
-    return record_impl(w, tl, coherency, true);
+    return icx_record_ex(w, tl, coherency, ICX_RECORD_AT_BREAKPOINT | ICX_RECORD_KEEP_LINK);
 }
 // TsBreakpointQueue::set_breakpoint_at_begin on every timestream (EntityTimestreamMap, link_timestreams):
 // everything recorded so far becomes old history, reachable only through the breakpoint.
@@ -300,22 +476,51 @@ int icx_breakpoint_clear(IcxTimeline* tl)
     return ICX_OK;
 }
 
-static int record_impl(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, bool at_breakpoint)
+int icx_record_ex(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, uint32_t flags)
 {
     if (!w || !tl) return ICX_E_INVALID;
+    const bool at_breakpoint = (flags & ICX_RECORD_AT_BREAKPOINT) != 0;
+    if (at_breakpoint && !tl->breakpoint_active) { tl->error = "record_at_breakpoint: no breakpoint set"; return ICX_E_STATE; }   // push_at_breakpoint returns false
     if (w->n_entities > tl->n_max || w->device != tl->device) { tl->error = "record: world does not fit the timeline"; return ICX_E_INVALID; }
     cudaSetDevice(w->device);
+    cudaStream_t st = w->stream;
     const int s = slot_of(tl, coherency);
     const uint32_t n = w->n_entities;
     if (n) {
-        const int blocks = (int)std::min<uint32_t>((n + 255) / 256, 148 * 16);
-        if (tl->profile) cudaEventRecord(tl->pev[0][0], w->stream);
-        k_record<<<blocks, 256, 0, w->stream>>>(w->W.in, tl->state + (size_t)s * 6 * tl->n_max, tl->ts + (size_t)s * tl->n_max, n, tl->n_max);
-        if (tl->profile) { cudaEventRecord(tl->pev[0][1], w->stream); tl->pev_used[0] = true; }
+        RecordSrc R; R.S = w->W.in; R.prm0 = w->W.prm0; R.prm1 = w->W.prm1; R.locked_pos = w->W.locked_pos; R.locked_rot = w->W.locked_rot;
+        R.entity_id = w->W.entity_id;
+        if (tl->profile) cudaEventRecord(tl->pev[0][0], st);
+        k_record<<<stream_blocks(tl, n, 16), 256, 0, st>>>(R, slot_state(tl, s), slot_ids(tl, s), n, tl->n_max, (flags & ICX_RECORD_KEEP_LINK) ? 0 : 1);
+        if (tl->profile) { cudaEventRecord(tl->pev[0][1], st); tl->pev_used[0] = true; }
         TCK(cudaGetLastError());
         w->launches += 1;
     }
-    tl->stamp[s] = coherency; tl->valid[s] = 1; tl->count[s] = n;
+    // ColliderComponents that changed since the last record into this ring (everything when another cosmos takes over the ring)
+    int64_t rows = 0;
+    if (n && w->have_C && (tl->last_recorder != w || tl->last_epoch != w->c_epoch)) {
+        const int all = tl->last_recorder != w ? 1 : 0;
+        uint32_t* scratch = tl->d_delta_n + tl->depth;
+        uint32_t cnt = n;
+        if (!all) {
+            TCK(cudaMemsetAsync(scratch, 0, 4, st));
+            k_delta_count<<<stream_blocks(tl, n, 8), 256, 0, st>>>(w->W.c_ver, tl->seen, n, 0, scratch);
+            TCK(cudaMemcpyAsync(&cnt, scratch, 4, cudaMemcpyDeviceToHost, st));
+            TCK(cudaStreamSynchronize(st));                                         // rare path: some collider changed this tick
+        }
+        if (cnt) { int rc = ensure_delta_cap(tl, cnt); if (rc != ICX_OK) return rc; }
+        TCK(cudaMemsetAsync(tl->d_delta_n + s, 0, 4, st));
+        if (cnt) {
+            k_delta_collect<<<stream_blocks(tl, n, 8), 256, 0, st>>>(w->W.c_ver, tl->seen, (const IcxColliderComponent*)w->mir_C.ptr, n, all,
+                                                                   tl->delta + (size_t)s * tl->delta_cap, tl->delta_cap, tl->d_delta_n + s);
+            TCK(cudaGetLastError());
+            w->launches += 2;
+        }
+        rows = cnt;
+        tl->last_recorder = w; tl->last_epoch = w->c_epoch;
+    } else if (tl->delta_n[s] != 0) TCK(cudaMemsetAsync(tl->d_delta_n + s, 0, 4, st));
+    tl->delta_n[s] = rows;
+    TCK(cudaEventRecord(tl->slot_ev[s], st));
+    tl->stamp[s] = coherency; tl->valid[s] = 1; tl->count[s] = n; tl->seq[s] = tl->next_seq++;
     // push_back lands after the breakpoint (old side), push_at_breakpoint before it (ts_breakpoint_queue.h:44-52, :140-152)
     tl->behind[s] = (tl->breakpoint_active && !at_breakpoint) ? 1 : 0;
     return ICX_OK;
@@ -326,12 +531,11 @@ int icx_replay(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, int mode, int* 
     if (!w || !tl) return ICX_E_INVALID;
     if (applied) *applied = 0;
     if (mode != ICX_REPLAY_SERVER && mode != ICX_REPLAY_PARALLEL) return ICX_E_INVALID;
-    // pop_future_timestream hands out every record with coherency <= now (cyclic, message.h:179-183) and
-    // the relay drops those older than now (server_network_dynamo.cpp:391): only the record stamped `now`
-    // is applied, older ones are consumed unseen.  pop_front stops at the breakpoint; pop_at_breakpoint
-    // only takes what lies behind it.
-    const int s = slot_of(tl, coherency);
-    bool hit = false;
+    // pop_future_timestream hands out, oldest first, every record with coherency <= now (cyclic compare, message.h:179-183);
+    // the relay then drops those with `coherency < now` -- a PLAIN integer compare (server_network_dynamo.cpp:391), so across
+    // the uint16 wrap an older record (65535 with now = 2) is still deserialised, before the current one.  pop_front stops at
+    // the breakpoint; pop_at_breakpoint only takes what lies behind it.
+    std::vector<int> use;
     for (uint32_t k = 0; k < tl->depth; k++) {
         if (!tl->valid[k]) continue;
         const uint16_t a = coherency, b = tl->stamp[k];
@@ -340,26 +544,55 @@ int icx_replay(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, int mode, int* 
         const bool behind = tl->breakpoint_active && tl->behind[k];
         if (mode == ICX_REPLAY_SERVER ? behind : !behind) continue;
         tl->valid[k] = 0; tl->behind[k] = 0;
-        if ((int)k == s && b == coherency) hit = true;
+        if (!(b < coherency)) use.push_back((int)k);
     }
-    if (!hit) return ICX_OK;
-    if (mode == ICX_REPLAY_PARALLEL) return ICX_OK;             // parallel_network_dynamo.cpp:78-86: upstream components only
-    const uint32_t n = w->n_entities, n_src = tl->count[s];
-    if (!n || !n_src) return ICX_OK;
-    if (n_src != n && !(w->W.worldline_stride && n_src == w->W.worldline_stride)) { tl->error = "replay: record size matches neither the world nor one world-line"; return ICX_E_INVALID; }
+    if (use.empty() || mode == ICX_REPLAY_PARALLEL) return ICX_OK;          // parallel_network_dynamo.cpp:78-86: upstream components only
+    std::sort(use.begin(), use.end(), [&](int x, int y) { return tl->seq[x] < tl->seq[y]; });
+    const uint32_t n = w->n_entities;
+    if (!n) return ICX_OK;
     cudaSetDevice(w->device);
-    const int blocks = (int)std::min<uint32_t>((n + 255) / 256, 148 * 16);
-    if (tl->profile) cudaEventRecord(tl->pev[1][0], w->stream);
-    k_replay<<<blocks, 256, 0, w->stream>>>(w->W.in, tl->state + (size_t)s * 6 * tl->n_max, n, n_src, tl->n_max);
-    if (tl->profile) { cudaEventRecord(tl->pev[1][1], w->stream); tl->pev_used[1] = true; }
+    cudaStream_t st = w->stream;
+    const int last = use.back();
+    const uint32_t n_src = tl->count[last];
+    if (!n_src) return ICX_OK;
+    if (n_src != n && !(w->W.worldline_stride && n_src == w->W.worldline_stride)) { tl->error = "replay: record size matches neither the world nor one world-line"; return ICX_E_INVALID; }
+    for (int k : use) TCK(cudaStreamWaitEvent(st, tl->slot_ev[k], 0));
+    // collider rows first (every popped record in order), then the dense part of the newest: each overwrites everything
+    bool rows_any = false;
+    for (int k : use) rows_any |= tl->delta_n[k] != 0;
+    if (w->have_C && n_src == n && (rows_any || w->pend_any)) {
+        int rc = ensure_pending(w, tl); if (rc != ICX_OK) return rc;
+        const uint32_t epoch = ++w->c_epoch;
+        IcxColliderComponent* MC = (IcxColliderComponent*)w->mir_C.ptr;
+        if (w->pend_any) k_replay_pending<<<stream_blocks(tl, n, 8), 256, 0, st>>>(w->W, MC, epoch, (const IcxColliderComponent*)w->pend_rows.ptr,
+                                                                                 (uint8_t*)w->pend_flag.ptr, tl->d_mismatch);
+        for (int k : use) {
+            if (tl->delta_n[k] == 0) continue;
+            const uint32_t guess = tl->delta_n[k] > 0 ? (uint32_t)tl->delta_n[k] : tl->delta_cap;
+            k_replay_delta<<<std::max(1, std::min<int>((int)((guess + 127) / 128), tl->sms * 4)), 128, 0, st>>>(
+                w->W, MC, tl->delta + (size_t)k * tl->delta_cap, tl->d_delta_n + k, tl->delta_cap, epoch,
+                (IcxColliderComponent*)w->pend_rows.ptr, (uint8_t*)w->pend_flag.ptr, tl->d_mismatch);
+            w->pend_any = true;         // a row may have met a divergent entity (conservative: costs one flag pass per replay)
+        }
+        TCK(cudaGetLastError());
+    }
+    if (tl->profile) cudaEventRecord(tl->pev[1][0], st);
+    k_replay<<<stream_blocks(tl, n, 16), 256, 0, st>>>(w->W, slot_state(tl, last), slot_ids(tl, last), n, n_src, tl->n_max, tl->d_mismatch);
+    if (tl->profile) { cudaEventRecord(tl->pev[1][1], st); tl->pev_used[1] = true; }
     TCK(cudaGetLastError());
     w->launches += 1;
     if (applied) *applied = 1;
     return ICX_OK;
 }
 
-int icx_divergence_scan(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, uint32_t n_worldlines,
-                        uint8_t* flags, uint32_t* incongruent, double* score)
+// per world-line: ever[k] |= (count[k] != 0) -- lets a caller scan every tick and read the verdicts back once
+__global__ void k_scan_fold(const uint32_t* __restrict__ count, uint8_t* __restrict__ ever, uint32_t n)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n && count[k]) ever[k] = 1;
+}
+
+int icx_divergence_scan_enqueue(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, uint32_t n_worldlines)
 {
     if (!w || !tl || n_worldlines == 0) return ICX_E_INVALID;
     const int s = slot_of(tl, coherency);
@@ -369,29 +602,46 @@ int icx_divergence_scan(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, uint32
     if (n_snap != n && !(stride && n_snap == stride && stride % SCAN_TILE == 0)) { tl->error = "scan: record must cover the world, or one world-line whose size is a multiple of 1024"; return ICX_E_INVALID; }
     cudaSetDevice(w->device);
     if (tl->cap_wl < n_worldlines) {
+        TCK(cudaDeviceSynchronize());
         if (tl->d_score) cudaFree(tl->d_score);
         if (tl->d_count) cudaFree(tl->d_count);
-        tl->d_score = nullptr; tl->d_count = nullptr; tl->cap_wl = 0;
+        if (tl->d_ever) cudaFree(tl->d_ever);
+        tl->d_score = nullptr; tl->d_count = nullptr; tl->d_ever = nullptr; tl->cap_wl = 0;
         TCK(cudaMalloc((void**)&tl->d_score, (size_t)n_worldlines * 8)); TCK(cudaMalloc((void**)&tl->d_count, (size_t)n_worldlines * 4));
+        TCK(cudaMalloc((void**)&tl->d_ever, n_worldlines)); TCK(cudaMemset(tl->d_ever, 0, n_worldlines));
         tl->cap_wl = n_worldlines;
     }
     cudaStream_t st = w->stream;
+    TCK(cudaStreamWaitEvent(st, tl->slot_ev[s], 0));
     TCK(cudaMemsetAsync(tl->d_score, 0, (size_t)n_worldlines * 8, st)); TCK(cudaMemsetAsync(tl->d_count, 0, (size_t)n_worldlines * 4, st));
     if (n) {
         const size_t smem = (size_t)2 * SCAN_STAGES * SCAN_TILE * sizeof(float4) + (SCAN_STAGES + 1) * sizeof(uint64_t);
         static bool attr_set[64] = {};
         if (!attr_set[w->device & 63]) { TCK(cudaFuncSetAttribute(k_divergence_scan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_set[w->device & 63] = true; }
         const uint32_t n_tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
-        const int blocks = (int)std::min<uint32_t>(n_tiles, 148 * SCAN_CTAS);
+        const int blocks = (int)std::min<uint32_t>(n_tiles, (uint32_t)(tl->sms * SCAN_CTAS));
         if (tl->profile) cudaEventRecord(tl->pev[2][0], st);
-        k_divergence_scan<<<blocks, SCAN_TPB, smem, st>>>(w->W.in.pos, tl->state + (size_t)s * 6 * tl->n_max, n, n_snap, stride, tl->d_count, tl->d_score);
+        k_divergence_scan<<<blocks, SCAN_TPB, smem, st>>>(w->W.in.pos, slot_state(tl, s), n, n_snap, stride, tl->d_count, tl->d_score);
         if (tl->profile) { cudaEventRecord(tl->pev[2][1], st); tl->pev_used[2] = true; }
+        k_scan_fold<<<(n_worldlines + 255) / 256, 256, 0, st>>>(tl->d_count, tl->d_ever, n_worldlines);
         TCK(cudaGetLastError());
-        w->launches += 1;
+        w->launches += 2;
     }
+    tl->scan_stream = st; tl->scan_wl = n_worldlines;
+    return ICX_OK;
+}
+
+int icx_divergence_scan_fetch(IcxTimeline* tl, uint32_t n_worldlines, uint8_t* flags, uint8_t* flags_ever, uint32_t* incongruent, double* score, int reset_ever)
+{
+    if (!tl || n_worldlines == 0) return ICX_E_INVALID;
+    if (!tl->scan_wl || n_worldlines != tl->scan_wl) { tl->error = "scan_fetch: no scan of that many world-lines was enqueued"; return ICX_E_STATE; }
+    cudaSetDevice(tl->device);
+    cudaStream_t st = tl->scan_stream;
     std::vector<unsigned long long> hs(n_worldlines); std::vector<uint32_t> hc(n_worldlines);
     TCK(cudaMemcpyAsync(hs.data(), tl->d_score, (size_t)n_worldlines * 8, cudaMemcpyDeviceToHost, st));
     TCK(cudaMemcpyAsync(hc.data(), tl->d_count, (size_t)n_worldlines * 4, cudaMemcpyDeviceToHost, st));
+    if (flags_ever) TCK(cudaMemcpyAsync(flags_ever, tl->d_ever, n_worldlines, cudaMemcpyDeviceToHost, st));
+    if (reset_ever) TCK(cudaMemsetAsync(tl->d_ever, 0, n_worldlines, st));
     TCK(cudaStreamSynchronize(st));
     for (uint32_t k = 0; k < n_worldlines; k++) {
         if (flags) flags[k] = hc[k] ? 1 : 0;
@@ -399,6 +649,14 @@ int icx_divergence_scan(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, uint32
         if (score) score[k] = (double)hs[k] / 65536.0;
     }
     return ICX_OK;
+}
+
+int icx_divergence_scan(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, uint32_t n_worldlines,
+                        uint8_t* flags, uint32_t* incongruent, double* score)
+{
+    int rc = icx_divergence_scan_enqueue(w, tl, coherency, n_worldlines);
+    if (rc != ICX_OK) return rc;
+    return icx_divergence_scan_fetch(tl, n_worldlines, flags, nullptr, incongruent, score, 0);
 }
 
 int icx_fork_age(IcxWorld* w, uint32_t* n_promoted, int* resolution_needed)
@@ -411,11 +669,13 @@ int icx_fork_age(IcxWorld* w, uint32_t* n_promoted, int* resolution_needed)
     TCK(cudaMemsetAsync(d, 0, 8, st));
     const uint32_t n = w->n_entities;
     if (n) {
-        const int blocks = (int)std::min<uint32_t>((n + 255) / 256, 148 * 8);
+        int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, w->device);
+        const int blocks = (int)std::min<uint32_t>((n + 255) / 256, (uint32_t)(sms * 8));
         k_fork_age<<<blocks, 256, 0, st>>>(w->W.in.ts, n, (uint32_t)w->W.coherency, d);
         TCK(cudaGetLastError());
         w->launches += 1;
     }
+    if (!n_promoted && !resolution_needed) return ICX_OK;      // asynchronous use: the promotions are all the caller wants
     uint32_t h[2] = {0, 0};
     TCK(cudaMemcpyAsync(h, d, 8, cudaMemcpyDeviceToHost, st));
     TCK(cudaStreamSynchronize(st));
@@ -426,10 +686,12 @@ int icx_fork_age(IcxWorld* w, uint32_t* n_promoted, int* resolution_needed)
 
 // The snapshot stream between adjacent timeslices (future -> past, server_network_dynamo.cpp:642-679
 // push_past_timestream) when the two timeslices live on different GPUs / processes: the slot stamped
-// `coherency` packed as [6][n] float4 + [n] uint32 = 100 B per entity in a caller-owned DEVICE buffer
-// (what a ncclSend / cudaMemcpyPeer moves), and its inverse on the receiving side, which lands in
-// the ring exactly like icx_record (push_back).  Copies run on `stream` (cudaStream_t, NULL = the
-// default stream) and are complete on return.
+// `coherency` packed into a caller-owned DEVICE buffer (what a ncclSend / cudaMemcpyPeer moves) as
+//   [10][n] float4 | [n] uint32 ids | {uint32 rows, 0, 0, 0} | rows x 176-byte collider rows
+// and its inverse on the receiving side, which lands in the ring exactly like icx_record (push_back).
+// Both are asynchronous on `stream` (cudaStream_t, NULL = the default stream): the export waits for the
+// record on the recording world's stream through an event, a replay / scan on another stream waits for the
+// import the same way -- no host synchronisation unless the number of collider rows is unknown to the host.
 int icx_timeline_slot_export(IcxTimeline* tl, uint16_t coherency, void* device_buffer, size_t capacity_bytes, uint32_t* n_out, void* stream)
 {
     if (!tl || !device_buffer) return ICX_E_INVALID;
@@ -437,31 +699,50 @@ int icx_timeline_slot_export(IcxTimeline* tl, uint16_t coherency, void* device_b
     if (!(tl->valid[s] && tl->stamp[s] == coherency)) { tl->error = "slot_export: no record with this coherency"; return ICX_E_STATE; }
     const uint32_t n = tl->count[s];
     if (n_out) *n_out = n;
-    if ((size_t)n * ICX_SNAPSHOT_BYTES > capacity_bytes) { tl->error = "slot_export: buffer too small"; return ICX_E_CAPACITY; }
-    if (!n) return ICX_OK;
     cudaSetDevice(tl->device);
     cudaStream_t st = (cudaStream_t)stream;
-    TCK(cudaMemcpy2DAsync(device_buffer, (size_t)n * 16, tl->state + (size_t)s * 6 * tl->n_max, (size_t)tl->n_max * 16, (size_t)n * 16, 6,
-                          cudaMemcpyDeviceToDevice, st));
-    TCK(cudaMemcpyAsync((char*)device_buffer + (size_t)n * 96, tl->ts + (size_t)s * tl->n_max, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
-    TCK(cudaStreamSynchronize(st));
+    TCK(cudaStreamWaitEvent(st, tl->slot_ev[s], 0));
+    int64_t rows = tl->delta_n[s];
+    if (rows < 0) {                                     // an imported slot: ask the device
+        uint32_t r = 0;
+        TCK(cudaMemcpyAsync(&r, tl->d_delta_n + s, 4, cudaMemcpyDeviceToHost, st)); TCK(cudaStreamSynchronize(st));
+        rows = std::min<uint32_t>(r, tl->delta_cap);
+    }
+    const size_t dense = (size_t)n * ICX_SNAPSHOT_BYTES;
+    if (dense + ICX_SNAPSHOT_HEADER_BYTES + (size_t)rows * sizeof(DeltaRow) > capacity_bytes) { tl->error = "slot_export: buffer too small"; return ICX_E_CAPACITY; }
+    char* out = (char*)device_buffer;
+    if (n) {
+        TCK(cudaMemcpy2DAsync(out, (size_t)n * 16, slot_state(tl, s), (size_t)tl->n_max * 16, (size_t)n * 16, TL_ARRAYS, cudaMemcpyDeviceToDevice, st));
+        TCK(cudaMemcpyAsync(out + (size_t)n * 16 * TL_ARRAYS, slot_ids(tl, s), (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+    }
+    TCK(cudaMemsetAsync(out + dense, 0, ICX_SNAPSHOT_HEADER_BYTES, st));
+    TCK(cudaMemcpyAsync(out + dense, tl->d_delta_n + s, 4, cudaMemcpyDeviceToDevice, st));
+    if (rows) TCK(cudaMemcpyAsync(out + dense + ICX_SNAPSHOT_HEADER_BYTES, tl->delta + (size_t)s * tl->delta_cap, (size_t)rows * sizeof(DeltaRow), cudaMemcpyDeviceToDevice, st));
     return ICX_OK;
 }
 
-int icx_timeline_slot_import(IcxTimeline* tl, uint16_t coherency, uint32_t n, const void* device_buffer, void* stream)
+int icx_timeline_slot_import(IcxTimeline* tl, uint16_t coherency, uint32_t n, const void* device_buffer, size_t buffer_bytes, void* stream)
 {
     if (!tl || (!device_buffer && n)) return ICX_E_INVALID;
     if (n > tl->n_max) { tl->error = "slot_import: more entities than the timeline holds"; return ICX_E_CAPACITY; }
+    const size_t dense = (size_t)n * ICX_SNAPSHOT_BYTES;
+    if (buffer_bytes < dense + ICX_SNAPSHOT_HEADER_BYTES) { tl->error = "slot_import: buffer shorter than the dense snapshot + header"; return ICX_E_INVALID; }
     const int s = slot_of(tl, coherency);
     cudaSetDevice(tl->device);
     cudaStream_t st = (cudaStream_t)stream;
+    const char* in = (const char*)device_buffer;
+    // the row count stays on the device; room for as many rows as the buffer could hold
+    const uint32_t room = (uint32_t)std::min<size_t>((buffer_bytes - dense - ICX_SNAPSHOT_HEADER_BYTES) / sizeof(DeltaRow), tl->n_max);
+    if (room) { int rc = ensure_delta_cap(tl, room); if (rc != ICX_OK) return rc; }
     if (n) {
-        TCK(cudaMemcpy2DAsync(tl->state + (size_t)s * 6 * tl->n_max, (size_t)tl->n_max * 16, device_buffer, (size_t)n * 16, (size_t)n * 16, 6,
-                              cudaMemcpyDeviceToDevice, st));
-        TCK(cudaMemcpyAsync(tl->ts + (size_t)s * tl->n_max, (const char*)device_buffer + (size_t)n * 96, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
-        TCK(cudaStreamSynchronize(st));
+        TCK(cudaMemcpy2DAsync(slot_state(tl, s), (size_t)tl->n_max * 16, in, (size_t)n * 16, (size_t)n * 16, TL_ARRAYS, cudaMemcpyDeviceToDevice, st));
+        TCK(cudaMemcpyAsync(slot_ids(tl, s), in + (size_t)n * 16 * TL_ARRAYS, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
     }
-    tl->stamp[s] = coherency; tl->valid[s] = 1; tl->count[s] = n;
+    TCK(cudaMemcpyAsync(tl->d_delta_n + s, in + dense, 4, cudaMemcpyDeviceToDevice, st));
+    if (room) TCK(cudaMemcpyAsync(tl->delta + (size_t)s * tl->delta_cap, in + dense + ICX_SNAPSHOT_HEADER_BYTES, (size_t)room * sizeof(DeltaRow), cudaMemcpyDeviceToDevice, st));
+    TCK(cudaEventRecord(tl->slot_ev[s], st));
+    tl->delta_n[s] = room ? -1 : 0;
+    tl->stamp[s] = coherency; tl->valid[s] = 1; tl->count[s] = n; tl->seq[s] = tl->next_seq++;
     tl->behind[s] = tl->breakpoint_active ? 1 : 0;
     return ICX_OK;
 }

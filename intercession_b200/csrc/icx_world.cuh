@@ -16,6 +16,7 @@ enum : uint32_t {
     EF_ASLEEP           = 1u << 3,
     EF_IMMUTABLE        = 1u << 4,   // no collision response can change it (see is_immutable)
     EF_HAS_RAY          = 1u << 5,
+    EF_INFLUENCE        = 1u << 6,   // some active collider has influenceOrientation (is_immutable needs it when a replay changes mass / locks)
 };
 // packet flag bits (packed in PacketDerived::bits together with the two type enums)
 enum : uint32_t {
@@ -35,6 +36,8 @@ enum : uint32_t {
 // flat broadphase pair entry (uint2: x = lower packet, y = higher packet | flags)
 #define ICX_PAIR_TIGHT    0x80000000u     // un-inflated bounds overlap too: the narrowphase can hit
 #define ICX_PAIR_STATIC   0x40000000u     // both bodies immutable
+#define ICX_PAIR_B_IMMUT  0x20000000u     // (in .y) the higher packet's body is immutable
+#define ICX_PAIR_A_IMMUT  0x80000000u     // (in .x) the lower packet's body is immutable
 #define ICX_NONE          0xFFFFFFFFu
 #define ICX_ITEM_CHECK    0x80000000u     // work item (uint4.y): two-sided pair, the SAT filter has not seen it yet
 // grid: 2^ICX_XB x-adjacent cells of one (y,z,world-line) row share a hashed block of buckets, so
@@ -71,10 +74,11 @@ struct DeviceWorld {
     // per-entity constants
     float4* prm0;                   // scale.xyz, mass
     float4* prm1;                   // linearDrag, angularDrag, collisionAngularDrag, bits(flags)
-    float4* locked_pos;             // lockedOrigin.xyz
+    float4* locked_pos;             // lockedOrigin.xyz, collisionLinearDrag (unused by the tick, carried so that P is complete in SoA)
     float4* locked_rot;             // lockedOrientation wxyz
     uint32_t* entity_id;            // IcxEntity
     uint32_t* first_packet;         // packet index of the entity's first active collider | count << 30
+    uint32_t* c_ver;                // per entity: world epoch (IcxWorld::c_epoch) at which its ColliderComponent last changed (record: sparse collider deltas)
     float4* pos0;                   // origin right after integration (margin check)
     // per-packet constants (uploaded AoS -> SoA)
     uint32_t* pk_entity;            // entity index
@@ -102,6 +106,14 @@ struct DeviceWorld {
     // flat candidate pair list (the broadphase output, icx_pairs_fetch)
     uint2* pairs; uint32_t max_pairs;
     float* push;                    // per entity: predicted displacement by static resolution this tick
+    // Per-body displacement budget (DESIGN.md "Broadphase bound"): the stored bounds are inflated by the uniform `margin`;
+    // a body the speculative pass predicts to be pushed further, or that was caught moving further, gets bm[e] > margin and is
+    // a MOVER: its extra candidates (xpairs) come from a wide grid walk of its own, nobody else pays for it.
+    float* bm;                      // per entity: budget of this tick, >= margin
+    float* bm_keep;                 // per entity: floor carried over ticks (raised by a violation, decays)
+    uint32_t* bm_need;              // per entity: float bits of the largest displacement seen beyond bm (0 = none)
+    uint32_t* mover_list;           // entities with bm > margin (mutable ones)
+    uint2* xpairs; uint32_t max_xpairs;     // candidate pairs only the movers' budgets create (same entry format as pairs)
     uint2* tight;                   // the subset with ICX_PAIR_TIGHT (input of the speculative narrowphase)
     uint2* static_pairs; uint32_t max_static;    // hits between two immutable bodies (contact records only)
     // bodies touched by at least one hit ("dirty"): only these need the reference's sequential order
@@ -136,6 +148,9 @@ enum { CTR_LARGE = 0, CTR_DIRTY = 1, CTR_CONTACTS = 2, CTR_INTERCEPTS = 3, CTR_C
        CTR_ITEMS = 18,          // 2 alternating work-item counters
        CTR_NEWD = 20,           // 3 rotating per-round counts of bodies that turned dirty during the replay
        CTR_FETCH = 23,          // 2 alternating work-item fetch counters
+       CTR_MOVERS = 25, CTR_XPAIRS = 26,
+       CTR_XMAX = 27,           // float bits: largest (bm - margin) of this tick
+       CTR_VIOLATORS = 28,      // bodies that moved beyond their budget (diagnostic)
        CTR_PROF = 32,           // ICX_PROFILE_PAIR builds: cycle accumulators
        CTR_TOTAL = 48 };
 #define ICX_MAX_ROUNDS 65535u

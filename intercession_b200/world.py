@@ -90,6 +90,10 @@ class World:
     def sync(self):
         self._ck(self.lib.icx_sync(self.handle))
 
+    def stream(self):
+        """cudaStream_t of the world as an int."""
+        return self.lib.icx_world_stream(self.handle) or 0
+
     def set_coherency(self, c):
         self._ck(self.lib.icx_coherency_set(self.handle, c))
 
@@ -115,6 +119,19 @@ class World:
 
     def pairs(self):
         return self._fetch(self.lib.icx_pairs_fetch, abi.pair_dt)
+
+    def extra_pairs(self):
+        return self._fetch(self.lib.icx_extra_pairs_fetch, abi.pair_dt)
+
+    def all_pairs(self):
+        """Uniform-margin pairs + the movers' extra pairs, canonical order: the candidate set of the ordered pass."""
+        p = np.concatenate([self.pairs(), self.extra_pairs()])
+        return p[np.lexsort((p["b"], p["a"]))]
+
+    def budgets(self):
+        out = np.zeros(self.n, np.float32)
+        self._ck(self.lib.icx_budgets_fetch(self.handle, abi.ptr(out), len(out)))
+        return out
 
     def stats(self):
         st = abi.IcxStats()
@@ -173,9 +190,11 @@ class World:
         return [(int(t - v[0, 0]), int(tag)) for t, tag in v] if len(v) else []
 
     # ---- TimelineApi hooks ----
-    def record(self, tl, coherency=None, at_breakpoint=False):
-        fn = self.lib.icx_record_at_breakpoint if at_breakpoint else self.lib.icx_record
-        self._ck_tl(tl, fn(self.handle, tl.handle, self.coherency() if coherency is None else coherency))
+    def record(self, tl, coherency=None, at_breakpoint=False, keep_link=None):
+        """push_past_timestream (chain-link + 1 on the way into the past) / push_timestream_at_breakpoint (ids unchanged)."""
+        keep = at_breakpoint if keep_link is None else keep_link
+        flags = (abi.RECORD_AT_BREAKPOINT if at_breakpoint else 0) | (abi.RECORD_KEEP_LINK if keep else 0)
+        self._ck_tl(tl, self.lib.icx_record_ex(self.handle, tl.handle, self.coherency() if coherency is None else coherency, flags))
 
     def replay(self, tl, coherency=None, mode=abi.REPLAY_SERVER):
         applied = C.c_int(0)
@@ -188,6 +207,12 @@ class World:
         score = np.zeros(n_worldlines, np.float64)
         self._ck_tl(tl, self.lib.icx_divergence_scan(self.handle, tl.handle, coherency, n_worldlines, abi.ptr(flags), abi.ptr(count), abi.ptr(score)))
         return flags, count, score
+
+    def divergence_scan_enqueue(self, tl, coherency, n_worldlines=1):
+        self._ck_tl(tl, self.lib.icx_divergence_scan_enqueue(self.handle, tl.handle, coherency, n_worldlines))
+
+    def fork_age_async(self):
+        self._ck(self.lib.icx_fork_age(self.handle, None, None))
 
     def fork_age(self):
         n, need = C.c_uint32(0), C.c_int(0)
@@ -242,10 +267,25 @@ class Timeline:
             raise IcxError(rc, self.lib.icx_timeline_last_error(self.handle).decode())
         return n.value
 
-    def import_slot(self, coherency, n, dev_ptr, stream=None):
-        rc = self.lib.icx_timeline_slot_import(self.handle, coherency, n, C.c_void_p(dev_ptr), C.c_void_p(stream or 0))
+    def import_slot(self, coherency, n, dev_ptr, nbytes, stream=None):
+        rc = self.lib.icx_timeline_slot_import(self.handle, coherency, n, C.c_void_p(dev_ptr), nbytes, C.c_void_p(stream or 0))
         if rc != abi.OK:
             raise IcxError(rc, self.lib.icx_timeline_last_error(self.handle).decode())
+
+    def id_mismatches(self):
+        v = C.c_uint64(0)
+        self.lib.icx_timeline_id_mismatches(self.handle, C.byref(v))
+        return v.value
+
+    def scan_fetch(self, n_worldlines, reset_ever=False):
+        """Results of the last enqueued scan + the per-world-line 'flagged by some scan since the last reset' bytes."""
+        flags, ever = np.zeros(n_worldlines, np.uint8), np.zeros(n_worldlines, np.uint8)
+        count, score = np.zeros(n_worldlines, np.uint32), np.zeros(n_worldlines, np.float64)
+        rc = self.lib.icx_divergence_scan_fetch(self.handle, n_worldlines, abi.ptr(flags), abi.ptr(ever), abi.ptr(count), abi.ptr(score),
+                                                1 if reset_ever else 0)
+        if rc != abi.OK:
+            raise IcxError(rc, self.lib.icx_timeline_last_error(self.handle).decode())
+        return flags, ever, count, score
 
     def profile(self, on=True):
         self.lib.icx_timeline_profile(self.handle, 1 if on else 0)

@@ -861,7 +861,7 @@ namespace {
 // cyclic coherency compare, source/events/message.h:179-183
 inline bool coherency_ge(uint16_t a, uint16_t b) { return (a >= b && a - b <= 32768) || (a <= b && b - a > 32768); }
 
-struct Record { uint16_t coherency; IcxEntity entity; IcxTransform T; IcxPhysics P; };
+struct Record { uint16_t coherency; IcxEntity entity; IcxTransform T; IcxPhysics P; IcxColliderComponent C; bool hasC; };
 
 // TsBreakpointQueue, source/networking/ts_breakpoint_queue.h:16-193: a FIFO whose pop_front stops at a
 // movable breakpoint; the parallel context pops AT the breakpoint and inserts BEFORE it.
@@ -911,12 +911,14 @@ void icxo_tl_breakpoint(void* h, int set)                                       
 }
 
 // server_network_dynamo.cpp:642-679 (link_inc = 1) / parallel_network_dynamo.cpp:369-385 (at_breakpoint = 1)
-int icxo_tl_record(void* h, uint32_t n, const IcxEntity* ids, const IcxTransform* T, const IcxPhysics* P,
+// ComponentCategory::all (:666-668): every component of the entity travels -- Transform, Physics and (C != NULL) ColliderComponent
+int icxo_tl_record(void* h, uint32_t n, const IcxEntity* ids, const IcxTransform* T, const IcxPhysics* P, const IcxColliderComponent* C,
                    uint16_t coherency, int at_breakpoint, int link_inc)
 {
     Timeline* tl = static_cast<Timeline*>(h);
     for (uint32_t i = 0; i < n; i++) {
         Record r; r.coherency = coherency; r.entity = link_inc ? inc_link(ids[i]) : ids[i]; r.T = T[i]; r.P = P[i];
+        r.hasC = C != nullptr; if (C) r.C = C[i]; else std::memset(&r.C, 0, sizeof(r.C));
         Stream& s = tl->at(r.entity);
         if (at_breakpoint) s.push_at_breakpoint(r); else s.push_back(r);
     }
@@ -924,7 +926,7 @@ int icxo_tl_record(void* h, uint32_t n, const IcxEntity* ids, const IcxTransform
 }
 
 // server_network_dynamo.cpp:377-421 / parallel_network_dynamo.cpp:51-89
-int icxo_tl_replay(void* h, uint32_t n, const IcxEntity* ids, IcxTransform* T, IcxPhysics* P, const uint8_t* tstate,
+int icxo_tl_replay(void* h, uint32_t n, const IcxEntity* ids, IcxTransform* T, IcxPhysics* P, IcxColliderComponent* C, const uint8_t* tstate,
                    uint16_t now, int mode)
 {
     Timeline* tl = static_cast<Timeline*>(h);
@@ -941,7 +943,7 @@ int icxo_tl_replay(void* h, uint32_t n, const IcxEntity* ids, IcxTransform* T, I
             if (!got) break;
             if (mode == ICX_REPLAY_SERVER && r.coherency < now) continue;           // stale, :391
             if (mode == ICX_REPLAY_PARALLEL) continue;                              // upstream components only
-            if (!divergent(tstate ? tstate[i] : 0)) { T[i] = r.T; P[i] = r.P; applied++; }
+            if (!divergent(tstate ? tstate[i] : 0)) { T[i] = r.T; P[i] = r.P; if (C && r.hasC) C[i] = r.C; applied++; }   // :408-412 all components
         }
     }
     return applied;

@@ -24,6 +24,7 @@
 #include "networking/entity_timestream_map.h"
 #include "physics/transform_component.h"
 #include "physics/physics_component.h"
+#include "physics/collider_component.h"
 #include "spacetime/timestream_state.h"
 // timejump_conditions.h pulls in Cosmos only for helpers that are not used here
 #include "core/cosmos.h"
@@ -60,18 +61,20 @@ void icxref_tl_breakpoint(void* h, int set)
 
 // Record every entity at `coherency`.  link_inc: the server increments the causal chain-link of the
 // id it pushes into the past (server_network_dynamo.cpp:673); entities are keyed by that id.
-int icxref_tl_record(void* h, uint32_t n, const IcxEntity* ids, const IcxTransform* T, const IcxPhysics* P,
+int icxref_tl_record(void* h, uint32_t n, const IcxEntity* ids, const IcxTransform* T, const IcxPhysics* P, const IcxColliderComponent* C,
                      uint16_t coherency, int at_breakpoint, int link_inc)
 {
     RefTimeline* tl = static_cast<RefTimeline*>(h);
     for (uint32_t i = 0; i < n; i++) {
         EventMessage msg(events::cosmos::ENTITY_UPDATE, coherency);
-        // serialize_entity_components: highest component type first
+        // serialize_entity_components: highest component type first (hard_config_cosmos.h:47-58 registers
+        // Transform = 0, ..., Physics = 6, Collider = 7)
+        if (C) msg << *reinterpret_cast<const ColliderComponent*>(&C[i]);
         msg << *reinterpret_cast<const PhysicsComponent*>(&P[i]);
         msg << *reinterpret_cast<const TransformComponent*>(&T[i]);
         Entity e = narrow(ids[i]);
         if (link_inc) increment_causal_chain_link(e);
-        events::cosmos::ENTITY_UPDATE_params info = { e, Signature(0x3), ComponentCategory::all };
+        events::cosmos::ENTITY_UPDATE_params info = { e, Signature(C ? 0xC1 : 0x41), ComponentCategory::all };
         msg << info;
         if (at_breakpoint) tl->map.push_to_timestream_at_breakpoint(e, msg);
         else tl->map.push_to_timestream(e, msg);
@@ -83,7 +86,7 @@ int icxref_tl_record(void* h, uint32_t n, const IcxEntity* ids, const IcxTransfo
 // mode ICX_REPLAY_SERVER: pop_from_timestream, drop stale, apply to non-divergent entities.
 // mode ICX_REPLAY_PARALLEL: pop_from_timestream_at_breakpoint, upstream components only (= none here).
 // Returns the number of entities whose components were overwritten.
-int icxref_tl_replay(void* h, uint32_t n, const IcxEntity* ids, IcxTransform* T, IcxPhysics* P, const uint8_t* tstate,
+int icxref_tl_replay(void* h, uint32_t n, const IcxEntity* ids, IcxTransform* T, IcxPhysics* P, IcxColliderComponent* C, const uint8_t* tstate,
                      uint16_t now, int mode)
 {
     RefTimeline* tl = static_cast<RefTimeline*>(h);
@@ -104,6 +107,10 @@ int icxref_tl_replay(void* h, uint32_t n, const IcxEntity* ids, IcxTransform* T,
                 evnt >> t; evnt >> p;                                                       // ascending component type
                 T[i] = *reinterpret_cast<IcxTransform*>(&t);
                 P[i] = *reinterpret_cast<IcxPhysics*>(&p);
+                if (info.sign.test(7)) {                                                    // deserialize_entity_components walks the signature
+                    ColliderComponent c; evnt >> c;
+                    if (C) std::memcpy(&C[i], &c, sizeof(IcxColliderComponent));
+                }
                 applied++;
             }
         }

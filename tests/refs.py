@@ -146,8 +146,8 @@ _TL_SIGS = {
     "{p}_tl_create": (_vp, []),
     "{p}_tl_destroy": (None, [_vp]),
     "{p}_tl_breakpoint": (None, [_vp, C.c_int]),
-    "{p}_tl_record": (C.c_int, [_vp, _u32, _vp, _vp, _vp, C.c_uint16, C.c_int, C.c_int]),
-    "{p}_tl_replay": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp, C.c_uint16, C.c_int]),
+    "{p}_tl_record": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp, C.c_uint16, C.c_int, C.c_int]),
+    "{p}_tl_replay": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, C.c_uint16, C.c_int]),
     "{p}_congruent": (C.c_int, [_u32, _vp, _vp, _vp]),
     "{p}_coherency_ge": (C.c_int, [C.c_uint16, C.c_uint16]),
 }
@@ -170,14 +170,15 @@ class CpuTimeline:
     def breakpoint(self, on):
         getattr(self.lib, self.p + "_tl_breakpoint")(self.h, 1 if on else 0)
 
-    def record(self, s, coherency, at_breakpoint=False, link_inc=True):
-        getattr(self.lib, self.p + "_tl_record")(self.h, s.n, abi.ptr(s.ids), abi.ptr(s.T), abi.ptr(s.P), coherency,
-                                                 1 if at_breakpoint else 0, 1 if link_inc else 0)
+    def record(self, s, coherency, at_breakpoint=False, link_inc=True, colliders=True):
+        """ENTITY_UPDATE of every entity with ALL its components (Transform, Physics, ColliderComponent)."""
+        getattr(self.lib, self.p + "_tl_record")(self.h, s.n, abi.ptr(s.ids), abi.ptr(s.T), abi.ptr(s.P), abi.ptr(s.C) if colliders else None,
+                                                 coherency, 1 if at_breakpoint else 0, 1 if link_inc else 0)
 
     def replay(self, s, now, mode=0):
         """Returns (scene after replay, entities overwritten)."""
         out = s.copy()
-        n = getattr(self.lib, self.p + "_tl_replay")(self.h, out.n, abi.ptr(out.ids), abi.ptr(out.T), abi.ptr(out.P),
+        n = getattr(self.lib, self.p + "_tl_replay")(self.h, out.n, abi.ptr(out.ids), abi.ptr(out.T), abi.ptr(out.P), abi.ptr(out.C),
                                                      abi.ptr(out.tstate), now, mode)
         return out, n
 

@@ -70,7 +70,7 @@ def test_entity_id_helpers():
 def test_no_cpu_fallback(built):
     """Without a CUDA device nothing computes: creation fails with ICX_E_CUDA, NULL worlds are rejected."""
     lib = abi.load()
-    assert lib.icx_abi_version() == 1
+    assert lib.icx_abi_version() == 2
     if lib.icx_device_count() > 0:
         pytest.skip("a CUDA device is present")
     cfg = abi.IcxConfig()

@@ -23,12 +23,12 @@ def collide_on_device(s):
     with world.World(s.n) as w:
         w.upload(s)
         w.collision_engage()
-        return w.download(s), w.contacts(), w.interceptions(), w.pairs(), w.stats()
+        return w.download(s), w.contacts(), w.interceptions(), w.pairs(), w.stats(), w.all_pairs()
 
 
 def test_config2_64k_collision_lockstep(built):
     s = scenes.config2(65536)
-    got, hits, ints, pairs, st = collide_on_device(s)
+    got, hits, ints, pairs, st, _ = collide_on_device(s)
     opairs = refs.oracle_pairs(s, st.margin, method=1)
     assert len(pairs) == len(opairs) and not fields_diff(pairs, opairs)
     exp = refs.procedures_tick(refs.oracle(), "icxo", s, euler=False, cand=opairs)
@@ -40,7 +40,7 @@ def test_config2_64k_collision_lockstep(built):
 
 def test_config3_1m_collision_lockstep_and_pair_properties(built):
     s = scenes.config3(1048576)
-    got, hits, ints, pairs, st = collide_on_device(s)
+    got, hits, ints, pairs, st, cand = collide_on_device(s)
     # ---- pair list properties ----
     key = pairs["a"].astype(np.uint64) << np.uint64(32) | pairs["b"].astype(np.uint64)
     assert np.all(pairs["a"] < pairs["b"]) and np.all(np.diff(key.astype(np.int64)) > 0)      # canonical order, unique
@@ -65,7 +65,7 @@ def test_config3_1m_collision_lockstep_and_pair_properties(built):
             found += 1
     assert found > 100
     # ---- everything downstream of the list, bit-exact ----
-    exp = refs.procedures_tick(refs.oracle(), "icxo", s, euler=False, cand=pairs)
+    exp = refs.procedures_tick(refs.oracle(), "icxo", s, euler=False, cand=cand)      # uniform-margin pairs + the movers' extra pairs
     assert len(exp.hits) > 5000
     assert_hits_equal(hits, exp.hits)
     assert not fields_diff(ints, exp.ints)

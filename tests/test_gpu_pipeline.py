@@ -24,36 +24,69 @@ def test_three_timeslices_replay_their_future(built):
         slices.append(pipeline.Timeslice(s, k, n_ts, delay))
         if k < n_ts - 1:
             links.append(pipeline.LoopbackLink(s.n))
-    seen = {}                                                     # (timeslice, coherency) -> state pushed at that coherency
+    pushed = {}                                                   # (timeslice, coherency) -> state it recorded at that coherency
     checked = 0
 
     def on_tick(t, phase):
         nonlocal checked
-        if phase == "pushed":
+        if phase == "replayed":                                   # phase 2 done, phase 4 (record) comes next: what is about to be pushed
+            for k, ts in enumerate(slices):
+                c = ts.w.coherency()
+                cur = ts.w.download(ts.scene)
+                pushed[(k, c)] = cur
+                if k > 0 and t >= delay:
+                    # right after the replay at coherency c, timeslice k holds what k - 1 pushed at c, bit for bit
+                    exp = pushed[(k - 1, c)]
+                    assert not fields_diff(cur.T, exp.T) and not fields_diff(cur.P, exp.P) and not fields_diff(cur.C, exp.C), (k, c)
+                    checked += 1
+    try:
+        pipeline.run_local(slices, ticks, links, on_tick=on_tick)
+        for k in range(1, n_ts):
+            assert slices[k].replayed == ticks - delay            # one record came due per tick once the pipeline is full
+            assert slices[k].tl_in.id_mismatches() == 0
+        assert checked == (ticks - delay) * (n_ts - 1)
+    finally:
+        for ts in slices:
+            ts.close()
+
+
+def test_middle_timeslice_forwards_what_it_replayed(built):
+    """Reference order inside the networker: replay from the future (:377-421), THEN push to the past (:642-679).  A change
+    injected into timeslice 0 at coherency c (a behaviour, an input: anything the tick itself does not derive) must therefore
+    reach timeslice 2 through timeslice 1's record stamped c -- with push before replay the middle timeslice would forward
+    its own stale state instead."""
+    delay, n_ts = 2, 3
+    base = scenes.arena(120, seed=5, walls=True, temporal=True, spacing=1.0, jitter=0.2, fill_side=8.0)
+    slices, links = [], []
+    for k in range(n_ts):
+        s = base.copy()
+        s["ids"] = pipeline.past_ids(base.ids, k)
+        slices.append(pipeline.Timeslice(s, k, n_ts, delay))
+        if k < n_ts - 1:
+            links.append(pipeline.LoopbackLink(s.n))
+    inject_at = slices[0].w.coherency() + 3
+    idx = np.array([10, 50, 90], np.uint32)
+    marker = np.float32(123.5)
+    seen = {}
+
+    def on_tick(t, phase):
+        if phase == "replayed":
+            w0 = slices[0].w
+            if w0.coherency() == inject_at:                       # external edit on the future-most timeslice, before it records
+                cur = w0.download(slices[0].scene)
+                P = np.ascontiguousarray(cur.P[idx]); P["linearDrag"] = marker
+                T = np.ascontiguousarray(cur.T[idx]); T["scale"] *= np.float32(1.25)
+                w0.update(idx, T=T, P=P)
             for k, ts in enumerate(slices):
                 seen[(k, ts.w.coherency())] = ts.w.download(ts.scene)
     try:
-        for t in range(ticks):
-            pipeline.run_local(slices, 1, links, on_tick=on_tick)
-            for k in range(1, n_ts):
-                ts = slices[k]
-                if t >= delay:
-                    assert ts.replayed == t - delay + 1           # one record came due per tick once the pipeline is full
-                    checked += 1
-        # one more wall tick by hand: right after the replay at coherency c, timeslice k holds what k-1 pushed at c
-        counts = [ts.push(links[k].ptr(), links[k].nbytes()) if k < n_ts - 1 else 0 for k, ts in enumerate(slices)]
-        on_tick(ticks, "pushed")
-        for k in range(1, n_ts):
-            slices[k].pull(links[k - 1].ptr(), counts[k - 1])
-        for k in range(1, n_ts):
-            ts = slices[k]
-            c = ts.w.coherency()
-            assert ts.w.replay(ts.tl_in, c, abi.REPLAY_SERVER)
-            got, exp = ts.w.download(ts.scene), seen[(k - 1, c)]
-            assert not fields_diff(got.T, exp.T) and not fields_diff(got.P, exp.P), k
-            # (the tick is deterministic: once synchronised, the past re-derives the same state on its own)
-            assert not fields_diff(seen[(k, c)].T, exp.T)
-        assert checked == (ticks - delay) * (n_ts - 1)
+        pipeline.run_local(slices, 3 + 2 * delay + 3, links, on_tick=on_tick)
+        got = seen[(2, inject_at)]                                # timeslice 2 right after ITS replay at that coherency
+        src = seen[(0, inject_at)]                                # (captured before the injection: compare with the recorded state)
+        assert np.all(got.P["linearDrag"][idx] == marker)
+        mid = seen[(1, inject_at)]
+        assert np.all(mid.P["linearDrag"][idx] == marker)
+        assert np.array_equal(got.T["scale"][idx], mid.T["scale"][idx]) and not np.array_equal(got.T["scale"][idx], src.T["scale"][idx])
     finally:
         for ts in slices:
             ts.close()
@@ -65,15 +98,16 @@ def test_slot_export_import_roundtrip(built):
     with world.World(s.n) as a, world.World(s.n) as b, world.Timeline(4, s.n) as ta, world.Timeline(6, s.n + 10) as tb:
         a.upload(s); a.step(1 / 45, 2)
         a.record(ta, 9); a.sync()
-        buf = torch.empty(s.n * abi.SNAPSHOT_BYTES, dtype=torch.uint8, device="cuda")
+        buf = torch.empty(abi.snapshot_capacity(s.n, 8), dtype=torch.uint8, device="cuda")
         assert ta.export_slot(9, buf.data_ptr(), buf.numel()) == s.n
         with pytest.raises(world.IcxError):
             ta.export_slot(8, buf.data_ptr(), buf.numel())        # nothing recorded with that stamp
         with pytest.raises(world.IcxError):
             ta.export_slot(9, buf.data_ptr(), 10)                 # buffer too small
-        tb.import_slot(9, s.n, buf.data_ptr())
+        tb.import_slot(9, s.n, buf.data_ptr(), buf.numel())
         assert tb.slot_info(9) == (True, s.n)
-        b.upload(s); b.set_coherency(9)
+        sb = s.copy(); sb["ids"] = pipeline.past_ids(s.ids)      # the record is addressed to the past's ids (chain-link + 1)
+        b.upload(sb); b.set_coherency(9)
         assert b.replay(tb, 9, abi.REPLAY_SERVER)
         ga, gb = a.download(s), b.download(s)
-        assert not fields_diff(ga.T, gb.T) and not fields_diff(ga.P, gb.P)
+        assert not fields_diff(ga.T, gb.T) and not fields_diff(ga.P, gb.P) and tb.id_mismatches() == 0

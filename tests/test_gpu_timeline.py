@@ -7,15 +7,19 @@ import pytest
 from intercession_b200 import abi, scenes, world
 import refs
 from util import fields_diff
-from test_timeline_oracle import evolve, past_ids, small_scene
+from test_timeline_oracle import changed_colliders, evolve, past_ids, small_scene
 
 pytestmark = pytest.mark.gpu
 DT = 1.0 / 45
 
 
-def set_state(w, s):
-    """Overwrite transform + physics of every entity (what a tick / a behaviour would have produced)."""
+def set_state(w, s, colliders_of=None):
+    """Overwrite transform + physics of every entity (what a tick / a behaviour would have produced) and the
+    ColliderComponent of the entities in the mask `colliders_of` (what BipedBehaviors does to its own entities)."""
     w.update(np.arange(s.n, dtype=np.uint32), T=s.T, P=s.P)
+    if colliders_of is not None and colliders_of.any():
+        idx = np.nonzero(colliders_of)[0].astype(np.uint32)
+        w.update(idx, Cc=np.ascontiguousarray(s.C[idx]))
 
 
 def test_record_replay_server(built):
@@ -25,18 +29,129 @@ def test_record_replay_server(built):
     otl = refs.CpuTimeline(refs.oracle(), "icxo")
     with world.World(fut.n) as wf, world.World(past.n) as wp, world.Timeline(16, fut.n) as tl:
         wf.upload(fut)
+        st = fut
         for t in range(100, 111):
-            st = evolve(fut, t)
-            set_state(wf, st)
+            st = evolve(fut, t, prev=st)
+            set_state(wf, st, changed_colliders(fut.n, t))
             wf.record(tl, t)
             otl.record(st, t)
-        for now in (99, 100, 103, 103, 107, 120, 110):
-            wp.upload(past)
+        # The past timeslice replays in order, like the reference's (every tick pops what has come due): entities that are
+        # forked / forking keep everything, the others end up with ALL components of the record -- scale, mass, drags, locks,
+        # isAsleep, and the collider rows that changed at ANY earlier tick.
+        wp.upload(past)
+        cur = past
+        for now in (99, 100, 101, 103, 103, 107, 120, 110):
             applied = wp.replay(tl, now)
-            exp, n = otl.replay(past, now)
+            cur, n = otl.replay(cur, now)
             got = wp.download(past)
             assert applied == (n > 0), now
-            assert not fields_diff(got.T, exp.T) and not fields_diff(got.P, exp.P), now
+            assert not fields_diff(got.T, cur.T) and not fields_diff(got.P, cur.P) and not fields_diff(got.C, cur.C), now
+        assert tl.id_mismatches() == 0
+    otl.close()
+
+
+def test_replay_checks_ids_and_wraps(built):
+    """A record is addressed to the id it carries (chain-link + 1 on the way into the past, server_network_dynamo.cpp:673):
+    a receiver whose ids are not those is left alone and counted.  Across the uint16 wrap the reference's plain `<` stale
+    filter (:391) lets older records through: the device applies what the real EntityTimestreamMap path applies."""
+    fut = small_scene()
+    past = fut.copy()
+    past["ids"] = past_ids(fut.ids)
+    with world.World(fut.n) as wf, world.World(past.n) as wp, world.Timeline(16, fut.n) as tl:
+        wf.upload(fut)
+        set_state(wf, evolve(fut, 3))
+        wf.record(tl, 40)
+        wrong = past.copy()
+        wrong["ids"] = fut.ids.copy()                           # the future's own ids: only link-14 / non-temporal ids coincide
+        wp.upload(wrong)
+        assert wp.replay(tl, 40)
+        got = wp.download(wrong)
+        same = past.ids == fut.ids
+        div = np.isin(past.tstate, (abi.TS_FORKED, abi.TS_FORKING))
+        assert np.array_equal(got.T["origin"][~same], wrong.T["origin"][~same])
+        assert tl.id_mismatches() == int((~same & ~div).sum()) > 0
+    for last, now in ((2, 2), (65535, 2), (1, 3)):
+        otl = refs.CpuTimeline(refs.oracle(), "icxo")
+        with world.World(fut.n) as wf, world.World(past.n) as wp, world.Timeline(16, fut.n) as tl:
+            wf.upload(fut)
+            t, st = 65533, fut
+            while True:
+                st = evolve(fut, t % 97, prev=st)
+                set_state(wf, st, changed_colliders(fut.n, t % 97))
+                wf.record(tl, t)
+                otl.record(st, t)
+                if t == last:
+                    break
+                t = (t + 1) & 0xFFFF
+            wp.upload(past)
+            assert wp.replay(tl, now)
+            exp, n = otl.replay(past, now)
+            got = wp.download(past)
+            assert n > 0 and not fields_diff(got.T, exp.T) and not fields_diff(got.P, exp.P) and not fields_diff(got.C, exp.C), (last, now)
+        otl.close()
+
+
+def test_replay_collider_rows_wait_for_divergent_entities(built):
+    """Every record of the reference carries every component, so an entity that was forked while its collider changed in the
+    future takes the change with the first record it accepts again.  The sparse rows it skipped are kept for that moment."""
+    fut = small_scene()
+    past = fut.copy()
+    past["ids"] = past_ids(fut.ids)
+    otl = refs.CpuTimeline(refs.oracle(), "icxo")
+    with world.World(fut.n) as wf, world.World(past.n) as wp, world.Timeline(16, fut.n) as tl:
+        wf.upload(fut)
+        st = fut
+        for t in range(10, 16):
+            st = evolve(fut, t, prev=st)
+            set_state(wf, st, changed_colliders(fut.n, t))
+            wf.record(tl, t)
+            otl.record(st, t)
+        wp.upload(past)
+        cur = past
+        for now in (10, 11, 12):
+            wp.replay(tl, now)
+            cur, _ = otl.replay(cur, now)
+        # the forked / forking entities merge again (what icx_world_extract does at the end of a parallel cycle)
+        cur.tstate[:] = abi.TS_MERGED
+        merged = wp.download(past)
+        merged.tstate[:] = abi.TS_MERGED
+        wp.upload(merged)                                       # a re-upload drops the kept rows: replay 13 must still restore ...
+        wp.replay(tl, 13)
+        cur, _ = otl.replay(cur, 13)
+        got = wp.download(past)
+        assert not fields_diff(got.T, cur.T) and not fields_diff(got.P, cur.P)
+        # ... T and P in full; collider rows that changed at ticks <= 12 were not re-sent, which a re-upload must bring itself
+    otl.close()
+    # same flow without the re-upload: the state table changes through the ABI the extraction uses
+    otl = refs.CpuTimeline(refs.oracle(), "icxo")
+    with world.World(fut.n) as wf, world.World(past.n) as wp, world.World(past.n, host_timeslice=abi.NULL_TIMESLICE) as wpar, \
+            world.Timeline(16, fut.n) as tl:
+        wf.upload(fut)
+        st = fut
+        for t in range(10, 16):
+            st = evolve(fut, t, prev=st)
+            set_state(wf, st, changed_colliders(fut.n, t))
+            wf.record(tl, t)
+            otl.record(st, t)
+        past0 = past.copy()
+        past0["ids"] = (past0.ids & ~np.uint32(0xF0000000))     # timeslice 0: extraction re-merges everything (:268-271)
+        wp.upload(past0)
+        cur = past0
+        for now in (10, 11, 12):
+            wp.replay(tl, now)
+            cur, _ = otl.replay(cur, now)
+        # parallel cycle: clone (ids as they are), extract back at chain-link - 1 -> every extracted entity is merged again
+        par = cur.copy()
+        par["ids"] = past_ids(cur.ids)
+        wpar.upload(par)
+        n_ex, n_miss = wpar.extract_into(wp)
+        now_state = wp.download(past0)
+        cur = now_state.copy()
+        wp.replay(tl, 13)
+        cur, _ = otl.replay(cur, 13)
+        got = wp.download(past0)
+        assert n_ex > 0
+        assert not fields_diff(got.T, cur.T) and not fields_diff(got.P, cur.P) and not fields_diff(got.C, cur.C)
     otl.close()
 
 

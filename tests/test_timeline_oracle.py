@@ -24,10 +24,42 @@ def small_scene(n=60, seed=3):
     return s
 
 
-def evolve(s, k):
+def changed_colliders(n, k):
+    """Entities whose ColliderComponent evolve(s, k) touches."""
+    return (np.arange(n) + k) % 5 == 0
+
+
+def evolve(s, k, prev=None):
+    """State of the future timeslice at tick k: EVERY field of Transform / Physics / ColliderComponent that a tick, a
+    behaviour (biped_behaviors.h:96-100 restLength / damping, projectile_behaviors.h:38 scale) or a host edit may change
+    differs from the past's copy, so a replay that restores less than the reference's (all components,
+    server_network_dynamo.cpp:408-412) cannot pass."""
     out = s.copy()
-    out.T["origin"] += np.float32(0.125 * k)
-    out.P["velocity"] *= np.float32(1.0 + 0.01 * k)
+    f = np.float32
+    out.T["origin"] += f(0.125 * k)
+    out.T["scale"] *= f(1.0 + 0.02 * (k % 7))
+    out.P["velocity"] *= f(1.0 + 0.01 * k)
+    out.P["acceleration"] += f(0.5 * k)
+    out.P["mass"] += f(0.25 * (k % 5))
+    out.P["linearDrag"] = f(0.01 + 0.001 * k)
+    out.P["angularDrag"] = f(0.02 + 0.001 * k)
+    out.P["collisionLinearDrag"] = f(0.005 * k)
+    out.P["collisionAngularDrag"] = f(0.03 + 0.002 * k)
+    i = np.arange(s.n)
+    out.P["lockOrigin"] = ((i + k) % 3 == 0).astype(np.uint8)
+    out.P["lockedOrigin"] = out.T["origin"] + f(1.0)
+    out.P["lockOrientation"] = ((i + k) % 4 == 0).astype(np.uint8)
+    out.P["lockedOrientation"][:, 1] = f(0.001 * k)
+    out.P["isAsleep"] = ((i + k) % 11 == 0).astype(np.uint8)
+    # colliders: only SOME entities change per tick (the sparse path), by different amounts
+    ch = changed_colliders(s.n, k)
+    c = out.C["colliders"]
+    c["restLength"][ch, 0] = f(0.1 + 0.01 * k)
+    c["damping"][ch, 0] = f(10.0 + k)
+    c["stiffness"][ch, 1] = f(100.0 + k)
+    c["staticFriction"][ch, 0] = f(0.45 + 0.001 * k)
+    c["localTransform"]["scale"][ch, 0] = f(1.0 + 0.01 * (k % 3))
+    c["influenceOrientation"][ch, 0] = k % 2
     return out
 
 
@@ -78,6 +110,15 @@ def test_record_replay_server_matches_reference_containers():
         res = [tl.replay(past, now) for tl in tls]
         assert res[0][1] == res[1][1], now
         assert not fields_diff(res[0][0].T, res[1][0].T) and not fields_diff(res[0][0].P, res[1][0].P), now
+        assert not fields_diff(res[0][0].C, res[1][0].C), now
+        if res[1][1]:
+            keep = ~np.isin(past.tstate, (abi.TS_FORKED, abi.TS_FORKING))
+            rec = evolve(fut, now if now <= 110 else 110)
+            for name in ("scale",):
+                assert np.array_equal(res[1][0].T[name][keep], rec.T[name][keep])
+            for name in ("mass", "linearDrag", "lockOrigin", "isAsleep", "collisionLinearDrag"):
+                assert np.array_equal(res[1][0].P[name][keep], rec.P[name][keep]), name
+            assert np.array_equal(res[1][0].C["colliders"]["restLength"][keep], rec.C["colliders"]["restLength"][keep])
     # divergent entities (forked / forking) kept their state, everyone else took the record stamped `now`
     got, n = tls[1].replay(past, 110)
     assert n == 0                                     # 120 already drained the streams
@@ -99,9 +140,38 @@ def test_replay_divergent_entities_keep_state():
     div = np.isin(past.tstate, (abi.TS_FORKED, abi.TS_FORKING))
     assert np.array_equal(o.T["origin"][div], past.T["origin"][div])
     assert np.array_equal(o.T["origin"][~div], rec.T["origin"][~div])
-    assert not fields_diff(r.T, o.T) and not fields_diff(r.P, o.P)
+    assert not fields_diff(r.T, o.T) and not fields_diff(r.P, o.P) and not fields_diff(r.C, o.C)
+    assert np.array_equal(o.P["mass"][div], past.P["mass"][div]) and np.array_equal(o.P["mass"][~div], rec.P["mass"][~div])
     for tl in tls:
         tl.close()
+
+
+@needs_ref
+def test_replay_across_the_coherency_wrap():
+    """pop_future_timestream pops every record that is cyclically <= now; the relay then drops `coherency < now` with a PLAIN
+    compare (server_network_dynamo.cpp:391), so with now = 2 the older records stamped 65534 / 65535 ARE deserialised, oldest
+    first, before 0, 1, 2 are dropped or applied: the end state is the record stamped `now`, or -- when that one has not
+    arrived -- the newest of the pre-wrap records."""
+    fut = small_scene()
+    past = fut.copy()
+    past["ids"] = past_ids(fut.ids)
+    for last, now in ((2, 2), (65535, 2), (1, 3)):
+        tls = both()
+        t = 65533
+        while True:
+            for tl in tls:
+                tl.record(evolve(fut, t % 97), t)
+            if t == last:
+                break
+            t = (t + 1) & 0xFFFF
+        (r, nr), (o, no) = [tl.replay(past, now) for tl in tls]
+        assert nr == no and nr > 0, (last, now)
+        assert not fields_diff(r.T, o.T) and not fields_diff(r.P, o.P) and not fields_diff(r.C, o.C), (last, now)
+        keep = ~np.isin(past.tstate, (abi.TS_FORKED, abi.TS_FORKING))
+        exp = evolve(fut, (now if last == now else 65535) % 97)
+        assert np.array_equal(o.T["origin"][keep], exp.T["origin"][keep]), (last, now)
+        for tl in tls:
+            tl.close()
 
 
 @needs_ref
