@@ -185,7 +185,7 @@ def worldline_batch_bench(n_worldlines, per, ticks, rank, world_size, local_rank
     wb.upload(base)
     for t in range(ticks):                        # the base history every candidate is compared with (replicated, read-only)
         wb.step(DT)
-        wb.record(tl_base, t + 1)
+        wb.record(tl_base, t + 1, keep_link=True)
     wb.close()
     wc = icxworld.World(full_local.n, worldline_stride=per, host_timeslice=abi.NULL_TIMESLICE, device=local_rank)
     tl_new = icxworld.Timeline(2, full_local.n, device=local_rank)
@@ -196,18 +196,17 @@ def worldline_batch_bench(n_worldlines, per, ticks, rank, world_size, local_rank
     barrier()
     t0 = time.perf_counter()
     dev_ms = 0.0
-    flags = cnt = score = None
-    any_flag = np.zeros(len(mine), np.uint8)
     tl_base.profile(True)
     scan_ms = []
     for t in range(ticks):
         wc.replay(tl_new, t, mode=abi.REPLAY_PARALLEL)
         wc.step(DT)
         dev_ms += wc.last_step_ms()
-        wc.record(tl_new, t + 1)
-        flags, cnt, score = wc.divergence_scan(tl_base, t + 1, len(mine))
-        scan_ms.append(tl_base.kernel_ms(2))
-        any_flag |= flags
+        wc.record(tl_new, t + 1, at_breakpoint=False, keep_link=True)
+        wc.divergence_scan_enqueue(tl_base, t + 1, len(mine))          # verdicts stay on the device: no host round trip per tick
+        if t % 16 == 15 or t == ticks - 1:
+            scan_ms.append(tl_base.kernel_ms(2))
+    flags, any_flag, cnt, score = tl_base.scan_fetch(len(mine))          # the last tick's counts / scores + "ever flagged"
     gflags, gcnt, gscore = shard.gather_results(any_flag, cnt, score, n_worldlines, rank, world_size, device=dev)
     barrier()
     sec = time.perf_counter() - t0
@@ -226,7 +225,7 @@ def worldline_batch_bench(n_worldlines, per, ticks, rank, world_size, local_rank
             "divergent_worldlines": int(gflags.sum()), "most_congruent": shard.most_congruent(gflags, gscore),
             "gather": {"collective": "all_gather_into_tensor (NCCL)" if world_size > 1 else "none (1 rank)",
                        "bytes_per_rank": 24 * ((n_worldlines + world_size - 1) // world_size)},
-            "algorithmic_bytes_per_body_tick": {"record": 200, "scan": 26},
+            "algorithmic_bytes_per_body_tick": {"record": 296, "scan": 26},
             # k_divergence_scan over this rank's candidates: 16 B of live position per body from HBM (the tick and the record
             # ran in between, > L2); the 16 KB base record is shared by every world-line and stays in L2
             "scan_kernel_rank0": {"us": round(float(np.mean(scan_ms)) * 1e3, 2), "bodies": int(full_local.n),
@@ -240,7 +239,8 @@ def timeline_kernels_bench(w, n, peak, device, reps=24, depth=6):
     (icx_timeline_kernel_ms) over `reps` launches cycling through `depth` ring slots (depth x 100 B x n > L2);
     `call_us` = host clock per ABI call over the same batch (record / replay are asynchronous launches; the scan returns its
     reduction to the host, so its call includes one read-back and stream sync).
-    Algorithmic bytes per body: record / replay 100 B read + 100 B written (6 x float4 + state word), scan 26 B."""
+    Algorithmic bytes per body: record / replay 148 B read + 148 B written (the whole TransformComponent +
+    PhysicsComponent; the kernels move 164 B each way: vec3 fields padded to float4, plus the id), scan 26 B."""
     from intercession_b200 import abi, world as icxworld
     tl = icxworld.Timeline(depth, n, device=device)
     tl.profile(True)
@@ -267,22 +267,22 @@ def timeline_kernels_bench(w, n, peak, device, reps=24, depth=6):
         return e
 
     out = {}
-    sec, call = run(lambda k: w.record(tl, (c0 + k % depth) & 0xFFFF), 0, reps)
-    out["record"] = entry(sec, call, 200 * n)
+    sec, call = run(lambda k: w.record(tl, (c0 + k % depth) & 0xFFFF, keep_link=True), 0, reps)
+    out["record"] = entry(sec, call, 296 * n)
     rec_call = call
 
     def pair(k):                                   # a replay consumes its record (pop): re-record before each one
         c = (c0 + k % depth) & 0xFFFF
-        w.record(tl, c)
+        w.record(tl, c, keep_link=True)
         assert w.replay(tl, c, abi.REPLAY_SERVER)
     sec, call = run(pair, 1, reps)
-    out["replay"] = entry(sec, max(call - rec_call, 1e-9), 200 * n, "call_us = record + replay pair minus the record call")
+    out["replay"] = entry(sec, max(call - rec_call, 1e-9), 296 * n, "call_us = record + replay pair minus the record call")
     for k in range(depth):
-        w.record(tl, (c0 + k) & 0xFFFF)
+        w.record(tl, (c0 + k) & 0xFFFF, keep_link=True)
     sec, call = run(lambda k: w.divergence_scan(tl, (c0 + k % depth) & 0xFFFF, 1), 2, reps)
     out["divergence_scan"] = entry(sec, call, 26 * n, "call_us includes the result read-back and stream sync")
     out["entities"] = n
-    out["timing"] = f"CUDA events per launch, mean of {reps}; {depth} ring slots of {100 * n / 1e6:.0f} MB (larger than L2)"
+    out["timing"] = f"CUDA events per launch, mean of {reps}; {depth} ring slots of {164 * n / 1e6:.0f} MB (larger than L2)"
     tl.close()
     return out
 
@@ -317,10 +317,10 @@ def projectile_behaviors_bench(w, n, peak, reps=24):
 
 def timeslice_pipeline_bench(bodies, ticks, delay, rank, world_size, local_rank, barrier):
     """BASELINE.json configs[4] (reduced: no time travellers, no parallel cosmos): one timeslice per rank, each
-    `delay` ticks behind its future neighbour; per wall tick and link ONE snapshot of 100 B per entity travels
+    `delay` ticks behind its future neighbour; per wall tick and link ONE snapshot of 164 B per entity travels
     future -> past (ncclSend / ncclRecv over NVLink between ranks; a device copy when world_size == 1, where two
-    timeslices share the GPU so that the path is exercised).  Per tick and timeslice: record + export, import,
-    replay of the record that came due, fork ageing, physics tick."""
+    timeslices share the GPU so that the path is exercised).  Per tick and timeslice, in the reference's order: replay of the
+    record that came due, record + export, import, fork ageing, physics tick -- ordered by CUDA events, no host sync per tick."""
     import torch
     import torch.distributed as dist
     from intercession_b200 import abi, pipeline, scenes
@@ -344,7 +344,7 @@ def timeslice_pipeline_bench(bodies, ticks, delay, rank, world_size, local_rank,
         sent = pipeline.run_distributed(slices[0], ticks, rank, n_ts, local_rank)
     else:
         pipeline.run_local(slices, ticks, links)
-        sent = (n_ts - 1) * ticks * base.n * abi.SNAPSHOT_BYTES
+        sent = (n_ts - 1) * ticks * (base.n * abi.SNAPSHOT_BYTES + abi.SNAPSHOT_HEADER_BYTES)
     barrier()
     sec = time.perf_counter() - t0
     sec_t = torch.tensor([sec], dtype=torch.float64, device="cuda")
@@ -402,6 +402,49 @@ def timeslice_pipeline_bench(bodies, ticks, delay, rank, world_size, local_rank,
             "records_replayed_min": int(rep_t.item())}
 
 
+def long_run_bench(a, device):
+    """SURVEY 8(d) protocol (100 warm-up + 1000 timed ticks) as far as a wall-clock budget allows: the scene of the headline
+    (config 3, full size) and the 64 K scene of config 2, ticked from the drop; per window of 25 ticks the mean tick time, the
+    phase split and what drives the ordered resolve (dirty bodies, contacts, dependency rounds, replay attempts, movers).
+    Bodies fall up to 200 units: after ~tick 60 they reach the floor at up to 60 units/s and the pile is violent until it
+    settles -- the regime in which the reference's sequential single-pass resolution is hardest to reproduce in parallel."""
+    from intercession_b200 import world as icxworld
+    out = {}
+    for name, scene_name, bodies, share in (("headline_scene", a.workload, a.bodies, 0.6), ("config2_64k", "config2", 65536, 0.4)):
+        sc = build_scene(scene_name, bodies)
+        w = icxworld.World(sc.n, device=device)
+        w.upload(sc)
+        w.profile(True)
+        rows, done, t_start, window = [], 0, time.perf_counter(), 25
+        prev = {k: 0.0 for k in ("integrate_prep", "grid_sort", "pairs", "narrow", "resolve")}
+        prev_tot = w.totals()
+        status = "complete (100 + 1000 ticks)"
+        while done < 1100:
+            w.step(DT, window)
+            ms = w.last_step_ms()
+            done += window
+            st = w.stats()
+            ph, _, _ = w.phases()
+            tot = w.totals()
+            dt_ = {k: tot[k] - prev_tot[k] for k in tot}
+            if done in (25, 50, 100, 150, 200, 300, 400, 500, 700, 1000, 1100) or time.perf_counter() - t_start > share * a.long_seconds:
+                rows.append({"tick": done, "ms_per_tick": round(ms / window, 4),
+                             "phases_ms": {p_: round((ph[p_] - prev[p_]) / window, 4) for p_ in ph},
+                             "candidate_pairs": int(dt_["candidates"] / window), "contacts": int(dt_["contacts"] / window),
+                             "dirty_bodies": int(dt_["dirty"] / window), "rounds": round(dt_["rounds"] / window, 1),
+                             "attempts": round(dt_["attempts"] / window, 2), "movers": st.n_movers, "retries": st.n_retries})
+            prev, prev_tot = dict(ph), tot
+            if time.perf_counter() - t_start > share * a.long_seconds:
+                status = f"stopped by the wall-clock budget ({share * a.long_seconds:.0f} s) at tick {done}"
+                break
+        timed = [r for r in rows if r["tick"] > 100]
+        out[name] = {"workload": f"{scene_name}: {bodies} bodies, ticked from the drop", "status": status, "ticks": done,
+                     "colliders": int(sc.C["colliders"]["isActive"].sum()), "windows": rows,
+                     "slowest_window_ms_per_tick": max(r["ms_per_tick"] for r in rows)}
+        w.close()
+    return out
+
+
 def run_reference_arm(a, rank, world_size):
     if rank != 0:
         return
@@ -436,6 +479,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--long-seconds", type=float, default=75.0, help="wall-clock budget of the long-run section (0 = skip it)")
     ap.add_argument("--no-timeline", action="store_true", help="skip the record / replay / scan kernel timings")
     ap.add_argument("--worldlines", type=int, default=4096, help="config-4 world-line candidates (0 = skip that section)")
     ap.add_argument("--worldline-bodies", type=int, default=1024)
@@ -482,6 +526,7 @@ def main():
         barrier()
     phases, pticks, launches1 = w.phases()
     st = w.stats()
+    tot = w.totals()
     w.profile(False)
     ms_t = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if world_size > 1:
@@ -497,14 +542,16 @@ def main():
     per_rank = [[round(float(x), 4) for x in t.tolist()] for t in per_rank]
     value = world_size * n_colliders * a.steps / (ms_max * 1e-3)
 
-    # ---- roofline: algorithmic bytes of the tick over its measured duration ----
+    # ---- roofline: algorithmic bytes of the tick over its measured duration; pairs and contacts are the MEAN over the timed
+    # ticks (summed on the device side by the library), not the last tick's ----
     peak, peak_src = measured_peak()
-    alg_bytes = B_PER_COLLIDER * n_colliders + B_PER_PAIR * st.n_candidates + B_PER_CONTACT * st.n_contacts
+    mean_pairs, mean_contacts = tot["candidates"] / max(tot["ticks"], 1), tot["contacts"] / max(tot["ticks"], 1)
+    alg_bytes = B_PER_COLLIDER * n_colliders + B_PER_PAIR * mean_pairs + B_PER_CONTACT * mean_contacts
     tick_ms = ms / a.steps
     achieved = alg_bytes / (tick_ms * 1e-3) / 1e9
     per_kernel = {}
-    kernel_bytes = {"integrate_prep": B_PER_COLLIDER * n_colliders, "grid_sort": 0, "pairs": B_PER_PAIR * st.n_candidates,
-                    "narrow": 0, "resolve": B_PER_CONTACT * st.n_contacts}
+    kernel_bytes = {"integrate_prep": B_PER_COLLIDER * n_colliders, "grid_sort": 0, "pairs": B_PER_PAIR * mean_pairs,
+                    "narrow": 0, "resolve": B_PER_CONTACT * mean_contacts}
     for k, v in phases.items():
         kms = v / max(pticks, 1)
         per_kernel[k] = {"ms": round(kms, 4), "share": round(v / max(sum(phases.values()), 1e-9), 3),
@@ -520,24 +567,22 @@ def main():
                 "traffic_source": traffic_src,
                 "algorithmic_bytes_per_tick": alg_bytes, "phases": per_kernel}
 
-    # ---- e2e: host AoS in / out through the C ABI every step ----
-    ids, _k0 = pinned_like(s.ids)
+    # ---- e2e: host buffers in / out through the C ABI every step.  The colliders are resident after the first upload (the
+    # reference's ColliderSynchro resubmits references, not copies: collider_synchro.cpp:28-42); every step the host hands in
+    # the whole TransformComponent + PhysicsComponent arrays (what its behaviours may have edited: 148 B per entity, pinned) and
+    # takes them back in place plus the ordered contact records.  (icx_motion_download returns only the 76 B per entity a tick
+    # writes; scattering those rows into AoS components on the host costs more than the 72 B per entity it saves on PCIe.) ----
     T, _k1 = pinned_like(s.T)
     P, _k2 = pinned_like(s.P)
-    Cc, _k3 = pinned_like(s.C)
-    hasP, _k4 = pinned_like(s.hasP)
-    ts, _k5 = pinned_like(s.tstate)
-    tc, _k6 = pinned_like(s.tcoh)
-    from intercession_b200.scenes import Scene
-    hs = Scene(ids=ids, T=T, P=P, hasP=hasP, C=Cc, tstate=ts, tcoh=tc)
+    w.upload(s)                                        # untimed: scene load
     n_contacts = 0
     for it in range(2 + a.e2e_steps):
         if it == 2:
             barrier()
             t0 = time.perf_counter()
-        w.upload(hs)
+        w.update_all(T=T, P=P)
         w.step(DT)
-        w.download_into(T=T, P=P)
+        w.download_into(T=T, P=P)                      # straight into the caller's component arrays (the device packs the AoS rows)
         n_contacts = len(w.contacts())
     barrier()
     e2e_sec = time.perf_counter() - t0
@@ -545,12 +590,17 @@ def main():
     if world_size > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
     e2e_val = world_size * n_colliders * a.e2e_steps / float(e2e_t.item())
-    h2d = ids.nbytes + T.nbytes + P.nbytes + Cc.nbytes + hasP.nbytes + ts.nbytes + tc.nbytes + 4 * s.n
+    h2d = T.nbytes + P.nbytes
     d2h = T.nbytes + P.nbytes + n_contacts * 48
     tlk = timeline_kernels_bench(w, s.n, peak, local_rank) if (rank == 0 and not a.no_timeline) else None
     beh = projectile_behaviors_bench(w, s.n, peak) if (rank == 0 and not a.no_timeline) else None
     barrier()
     w.close()
+
+    long_run = None
+    if rank == 0 and a.long_seconds > 0:
+        long_run = long_run_bench(a, local_rank)
+    barrier()
 
     wlb = None
     if a.worldlines > 0:
@@ -580,13 +630,16 @@ def main():
                                        f"one scene replica per GPU, gravity on, dt=1/45",
                            "l2": "inputs larger than L2 (per-tick state and derived arrays > 126 MB)" if a.bodies >= 400000 else "inputs fit L2 (reduced size)",
                            "colliders_per_gpu": n_colliders, "candidate_pairs": st.n_candidates, "contacts": st.n_contacts,
-                           "dirty_bodies": st.n_dirty,
+                           "dirty_bodies": st.n_dirty, "window": f"ticks {a.warmup + 1}-{a.warmup + a.steps} after the drop (the scene is still in free fall; see long_run for later ticks)",
+                           "mean_candidate_pairs": round(mean_pairs, 1), "mean_contacts": round(mean_contacts, 1),
+                           "mean_rounds": round(tot["rounds"] / max(tot["ticks"], 1), 2), "mean_attempts": round(tot["attempts"] / max(tot["ticks"], 1), 2),
                            "resolve_rounds": st.n_rounds, "resolve_attempts": st.n_attempts, "retries": st.n_retries, "margin": st.margin,
                            "per_rank": {"columns": ["ms_per_step", "retries", "resolve_attempts_last_tick", "sm_mhz_min", "slowdown_reasons"],
                                         "rows": per_rank}},
                 "clocks": clk.summary(), "roofline": roofline,
                 "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
                 "gpu_launches": int(launches1 - launches0),
+                "long_run": long_run,
                 "timeline_kernels": tlk,
                 "behaviors": beh,
                 "worldline_batch": wlb,

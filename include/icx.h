@@ -239,8 +239,21 @@ ICX_API int icx_bodies_download(IcxWorld* w, uint32_t n_entities,
                         uint8_t* tstate,
                         uint16_t* tstate_coherency);
 
+/* What a tick writes: origin, orientation, velocity, acceleration, angularVelocity,
+ * angularAcceleration -- 76 B per entity instead of the 148 B of the two whole components.  The adapter scatters the rows
+ * back through its packet references. */
+typedef struct IcxMotionState {
+    float origin[3];
+    float orientation[4];   /* w, x, y, z */
+    float velocity[3];
+    float acceleration[3];
+    float angularVelocity[3];
+    float angularAcceleration[3];
+} IcxMotionState;
+ICX_API int icx_motion_download(IcxWorld* w, uint32_t n_entities, IcxMotionState* out);
+
 /* Host-side edits between ticks (behaviours, replay): overwrite `count` entities
- * listed in `index` (indices into the upload order) from the given AoS arrays,
+ * listed in `index` (indices into the upload order; NULL = the first `count` entities) from the given AoS arrays,
  * which are indexed by position in `index`.  NULL arrays are left untouched. */
 ICX_API int icx_bodies_update(IcxWorld* w, uint32_t count, const uint32_t* index,
                       const IcxTransform* transform,
@@ -312,6 +325,9 @@ ICX_API int icx_last_step_ms(IcxWorld* w, float* ms);
 #define ICX_N_PHASES 5
 ICX_API int icx_profile_enable(IcxWorld* w, int on);
 ICX_API int icx_phase_ms(IcxWorld* w, double* ms, uint64_t* n_ticks, uint64_t* n_launches);
+/* Sums over the ticks since the last icx_profile_enable call: out6 = {ticks, candidate pairs, contact records, dependency rounds,
+ * replay attempts, dirty bodies} -- the per-tick quantities the roofline's algorithmic bytes are made of. */
+ICX_API int icx_totals_fetch(IcxWorld* w, uint64_t* out6);
 
 /* Device-side timeline of the last ordered resolve (pairs of {globaltimer ns, tag}); tags:
  * 0 start, 0x1nnnn lists built / bodies reset (nnnn = dirty bodies), 0x2.... barrier passed,
@@ -320,6 +336,10 @@ ICX_API int icx_debug_trace(IcxWorld* w, int enable, uint64_t* out, size_t cap, 
 
 /* Raw device counters of the last tick (32 words; diagnostic, layout not stable). */
 ICX_API int icx_debug_counters(IcxWorld* w, uint32_t* out32);
+
+/* Per-entity diagnostic arrays of the last tick: which = 0 predicted push, 1 displacement budget, 2 largest component of the
+ * displacement static resolution produced (layout not stable). */
+ICX_API int icx_debug_array(IcxWorld* w, int which, float* out, size_t cap);
 
 /* CUDA stream of the world as a void* (cudaStream_t), for callers that time it. */
 ICX_API void* icx_world_stream(IcxWorld* w);
@@ -430,14 +450,15 @@ ICX_API int icx_fork_age(IcxWorld* w, uint32_t* n_promoted, int* resolution_need
 /* Snapshot transport between timeslices on different GPUs / processes (the future -> past ENTITY_UPDATE
  * stream, server_network_dynamo.cpp:642-679): pack the slot stamped `coherency` into / restore it from a
  * caller-owned DEVICE buffer, e.g. the buffer a ncclSend / ncclRecv moves:
- *   [10][n] float4 state | [n] uint32 id | 16-byte header {collider rows, 0, 0, 0} | rows x 176 B {index, pad, ColliderComponent}
+ *   [10][n] float4 state | [n] uint32 id (padded to 16 B) | 16-byte header {collider rows, 0, 0, 0} | rows x 176 B {index, pad, ColliderComponent}
  * ICX_SNAPSHOT_CAPACITY(n, rows) is the buffer size for n entities and up to `rows` changed colliders.  `stream` is a
  * cudaStream_t (NULL = default stream); both calls are ASYNCHRONOUS on it and ordered against the recording / replaying
  * worlds' streams by events, so a timeslice needs no host synchronisation per tick. */
 #define ICX_SNAPSHOT_BYTES 164
 #define ICX_SNAPSHOT_HEADER_BYTES 16
 #define ICX_SNAPSHOT_DELTA_BYTES 176
-#define ICX_SNAPSHOT_CAPACITY(n, rows) ((size_t)(n) * ICX_SNAPSHOT_BYTES + ICX_SNAPSHOT_HEADER_BYTES + (size_t)(rows) * ICX_SNAPSHOT_DELTA_BYTES)
+#define ICX_SNAPSHOT_DENSE_BYTES(n) ((size_t)(n) * 160 + (((size_t)(n) * 4 + 15) & ~(size_t)15))     /* the id array is padded to 16 bytes */
+#define ICX_SNAPSHOT_CAPACITY(n, rows) (ICX_SNAPSHOT_DENSE_BYTES(n) + ICX_SNAPSHOT_HEADER_BYTES + (size_t)(rows) * ICX_SNAPSHOT_DELTA_BYTES)
 ICX_API int icx_timeline_slot_export(IcxTimeline* tl, uint16_t coherency, void* device_buffer, size_t capacity_bytes,
                                      uint32_t* n_entities, void* stream);
 ICX_API int icx_timeline_slot_import(IcxTimeline* tl, uint16_t coherency, uint32_t n_entities, const void* device_buffer,

@@ -44,6 +44,9 @@ collider_dt = np.dtype({
 collider_component_dt = np.dtype([("colliders", collider_dt, 2)])
 assert collider_component_dt.itemsize == 168
 
+motion_dt = np.dtype([("origin", "<f4", 3), ("orientation", "<f4", 4), ("velocity", "<f4", 3), ("acceleration", "<f4", 3),
+                      ("angularVelocity", "<f4", 3), ("angularAcceleration", "<f4", 3)])
+assert motion_dt.itemsize == 76
 contact_dt = np.dtype([("entityA", "<u4"), ("entityB", "<u4"), ("slotA", "u1"), ("slotB", "u1"),
                        ("flags", "<u2"), ("point", "<f4", 3), ("normal", "<f4", 3), ("depth", "<f4"),
                        ("packetA", "<u4"), ("packetB", "<u4")])
@@ -65,7 +68,7 @@ RECORD_AT_BREAKPOINT, RECORD_KEEP_LINK = 1, 2
 
 def snapshot_capacity(n, rows=0):
     """ICX_SNAPSHOT_CAPACITY: transport buffer for n entities and up to `rows` changed ColliderComponents."""
-    return n * SNAPSHOT_BYTES + SNAPSHOT_HEADER_BYTES + rows * SNAPSHOT_DELTA_BYTES
+    return n * 160 + ((n * 4 + 15) & ~15) + SNAPSHOT_HEADER_BYTES + rows * SNAPSHOT_DELTA_BYTES
 
 
 def compose_entity(timeslice, genesis, link):
@@ -149,6 +152,7 @@ SIGNATURES = {
     "icx_bodies_upload": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "icx_bodies_download": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp, _vp]),
     "icx_bodies_update": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp]),
+    "icx_motion_download": (C.c_int, [_vp, _u32, _vp]),
     "icx_coherency_set": (C.c_int, [_vp, C.c_uint16]),
     "icx_coherency_get": (C.c_int, [_vp, C.POINTER(C.c_uint16)]),
     "icx_step": (C.c_int, [_vp, C.c_double]),
@@ -165,6 +169,7 @@ SIGNATURES = {
     "icx_last_step_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
     "icx_world_stream": (_vp, [_vp]),
     "icx_profile_enable": (C.c_int, [_vp, C.c_int]),
+    "icx_totals_fetch": (C.c_int, [_vp, C.POINTER(C.c_uint64)]),
     "icx_timeline_create": (C.c_int, [C.c_int, _u32, _u32, C.POINTER(_vp)]),
     "icx_timeline_destroy": (None, [_vp]),
     "icx_timeline_last_error": (C.c_char_p, [_vp]),
@@ -187,6 +192,7 @@ SIGNATURES = {
     "icx_world_extract": (C.c_int, [_vp, _vp, C.POINTER(_u32), C.POINTER(_u32)]),
     "icx_timeline_slot_info": (C.c_int, [_vp, C.c_uint16, C.POINTER(C.c_int), C.POINTER(_u32)]),
     "icx_debug_counters": (C.c_int, [_vp, _vp]),
+    "icx_debug_array": (C.c_int, [_vp, C.c_int, _vp, _sz]),
     "icx_debug_trace": (C.c_int, [_vp, C.c_int, _vp, _sz, _psz]),
     "icx_phase_ms": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "icx_projectiles_upload": (C.c_int, [_vp, _u32, _vp, _vp]),

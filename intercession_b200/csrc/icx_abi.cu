@@ -2,6 +2,8 @@
 // No CPU fallback: every compute entry point needs a CUDA device.
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
+#include <cmath>
 #include <cstring>
 #include <new>
 #include "icx_host.h"
@@ -54,11 +56,12 @@ int allocate(IcxWorld* w)
     CK(alloc(w, W.scan_partial, 4096 + 8));
     CK(alloc(w, W.s_lo, np)); CK(alloc(w, W.s_hi, np));
     CK(alloc(w, W.large_list, W.max_large));
-    CK(alloc(w, W.pairs, W.max_pairs)); CK(alloc(w, W.tight, W.max_pairs)); CK(alloc(w, W.push, ne)); CK(alloc(w, W.static_pairs, W.max_static));
+    CK(alloc(w, W.pairs, W.max_pairs)); CK(alloc(w, W.tight, W.max_pairs)); CK(alloc(w, W.push, ne)); CK(alloc(w, W.pushv, ne)); CK(alloc(w, W.static_pairs, W.max_static));
     CK(alloc(w, W.bm, ne)); CK(alloc(w, W.bm_keep, ne)); CK(alloc(w, W.bm_need, ne)); CK(alloc(w, W.mover_list, ne)); CK(alloc(w, W.xpairs, W.max_xpairs));
     CK(cudaMemset(W.bm_keep, 0, ne * sizeof(float))); CK(cudaMemset(W.bm_need, 0, ne * sizeof(uint32_t)));
     CK(alloc(w, W.dirty_slot, ne)); CK(alloc(w, W.dirty_list, ne));
-    CK(alloc(w, W.nbr, 2 * ne * (size_t)W.max_neighbors)); CK(alloc(w, W.nbr_count, 2 * ne)); CK(alloc(w, W.slot_info, ne));
+    W.max_nbr = (uint32_t)std::min<size_t>(ne * (size_t)W.max_neighbors, 0xFFFF0000u);
+    CK(alloc(w, W.nbr, (size_t)W.max_nbr)); CK(alloc(w, W.nbr_count, 2 * ne)); CK(alloc(w, W.nbr_fill, 2 * ne)); CK(alloc(w, W.slot_flag, ne)); CK(alloc(w, W.slot_info, ne));
     CK(alloc(w, W.head[0], ne)); CK(alloc(w, W.head[1], ne));
     CK(alloc(w, W.active[0], ne)); CK(alloc(w, W.active[1], ne)); CK(alloc(w, W.items, ne + W.max_static));
     CK(alloc(w, W.contacts, W.max_contacts)); CK(alloc(w, W.intercepts, W.max_contacts)); CK(alloc(w, W.intercept_key, W.max_contacts));
@@ -133,6 +136,7 @@ int run_tick_once(IcxWorld* w, double dt, int do_euler, int do_collide, uint32_t
 int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_coherency)
 {
     DeviceWorld& W = w->W;
+    uint32_t last_raised = 0;
     for (int attempt = 0; attempt < 24; attempt++) {
         uint32_t raised = 0;
         int rc = run_tick_once(w, dt, do_euler, do_collide, &raised);
@@ -148,17 +152,26 @@ int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_
             w->stats.n_interceptions = w->h_counters[CTR_INTERCEPTS];
             w->stats.n_dirty = w->h_counters[CTR_DIRTY]; w->stats.n_attempts = w->h_counters[CTR_ATTEMPTS] + 1;
             w->stats.n_movers = w->h_counters[CTR_MOVERS];
+            w->totals[0] += 1; w->totals[1] += w->h_counters[CTR_CANDIDATES] + std::min(w->h_counters[CTR_XPAIRS], W.max_xpairs);
+            w->totals[2] += w->h_counters[CTR_CONTACTS]; w->totals[3] += w->h_counters[CTR_ROUNDS];
+            w->totals[4] += w->h_counters[CTR_ATTEMPTS] + 1; w->totals[5] += w->h_counters[CTR_DIRTY];
             w->stats.margin = W.margin; w->stats.cell_size = W.cell_size; w->stats.max_neighbors = W.max_neighbors;
             w->have_results = do_collide != 0;
             return ICX_OK;
         }
         // `in` is untouched: adjust the capacity / margin that was exceeded and run the tick again
         w->stats.n_retries++;
+        last_raised = raised;
+        if (getenv("ICX_DEBUG_RETRY"))
+            fprintf(stderr, "[icx] tick %llu attempt %d: flags 0x%x dirty %u movers %u xpairs %u xmax %g violators %u candidates %u neighbors %u rounds %u\n",
+                    (unsigned long long)w->stats.ticks, attempt, raised, w->h_counters[CTR_DIRTY], w->h_counters[CTR_MOVERS], w->h_counters[CTR_XPAIRS],
+                    (double)*(float*)&w->h_counters[CTR_XMAX], w->h_counters[CTR_VIOLATORS], w->h_counters[CTR_CANDIDATES], W.max_neighbors, w->h_counters[CTR_ROUNDS]);
         if (raised & RF_CLIP_OVERFLOW) return fail(w, ICX_E_CAPACITY, "clipped manifold exceeded ICX_MAXV");
         if (raised & RF_NEIGHBOR_OVERFLOW) {
-            if (W.max_neighbors >= 4096) return fail(w, ICX_E_CAPACITY, "candidate list exceeded 4096 neighbours per collider");
-            W.max_neighbors = std::min<uint32_t>(W.max_neighbors * 2, 4096);
-            rc = regrow(w, W.nbr, 2 * (size_t)w->cap_entities * W.max_neighbors); if (rc) return rc;
+            if (W.max_neighbors >= 2048) return fail(w, ICX_E_CAPACITY, "candidate lists exceeded 2048 entries per entity on average (or 65535 in one list)");
+            W.max_neighbors *= 2;
+            W.max_nbr = (uint32_t)std::min<size_t>((size_t)w->cap_entities * W.max_neighbors, 0xFFFF0000u);
+            rc = regrow(w, W.nbr, (size_t)W.max_nbr); if (rc) return rc;
         }
         if (raised & RF_PAIR_OVERFLOW) {
             if (w->h_counters[CTR_CANDIDATES] > W.max_pairs) {
@@ -176,7 +189,7 @@ int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_
                 rc = regrow(w, W.items, (size_t)w->cap_entities + W.max_static); if (rc) return rc;     // static pairs ride in the first round's item list
             }
         }
-        if (raised & RF_MARGIN_VIOLATED) launch_budget_update(W, w->stream);       // only the bodies that moved too far get a larger budget
+        if (raised & RF_MARGIN_VIOLATED) return fail(w, ICX_E_CAPACITY, "resolve: per-body displacement budgets did not settle within the attempt limit");
         if (raised & RF_CELL_TOO_SMALL) {
             float need; std::memcpy(&need, &w->h_counters[CTR_NEED_CELL], 4);
             set_cell(w, std::max(need, W.cell_size) * 1.05f);
@@ -193,7 +206,8 @@ int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_
         }
         if (raised == RF_ROUNDS_EXCEEDED) return fail(w, ICX_E_CAPACITY, "resolve: dependency chain longer than ICX_MAX_ROUNDS");
     }
-    return fail(w, ICX_E_CAPACITY, "tick did not converge after 24 capacity/margin retries");
+    { char msg[160]; snprintf(msg, sizeof msg, "tick did not converge after 24 capacity / budget retries (last flags 0x%x, %u bodies over budget)", last_raised, w->h_counters[CTR_VIOLATORS]);
+      return fail(w, ICX_E_CAPACITY, msg); }
 }
 
 } // namespace
@@ -264,7 +278,7 @@ int icx_world_create(const IcxConfig* cfg, IcxWorld** out)
         w->cap_entities = cfg->max_entities; w->cap_packets = 2 * cfg->max_entities;
         W.margin = cfg->broadphase_margin > 0 ? cfg->broadphase_margin : 0.05f;
         set_cell(w, cfg->cell_size > 0 ? cfg->cell_size : 1.0f);
-        W.max_neighbors = cfg->max_neighbors ? std::min<uint32_t>(cfg->max_neighbors, 4096) : 24;
+        W.max_neighbors = cfg->max_neighbors ? std::min<uint32_t>(cfg->max_neighbors, 2048) : 24;
         W.max_pairs = cfg->max_pairs ? cfg->max_pairs : std::max<uint32_t>(8 * cfg->max_entities, 4096);
         W.max_static = 4096;
         W.max_xpairs = std::max<uint32_t>(cfg->max_entities, 4096);
@@ -382,30 +396,48 @@ int icx_bodies_download(IcxWorld* w, uint32_t n, IcxTransform* T, IcxPhysics* P,
 int icx_bodies_update(IcxWorld* w, uint32_t count, const uint32_t* index, const IcxTransform* T, const IcxPhysics* P, const IcxColliderComponent* C)
 {
     if (!w) return ICX_E_INVALID;
-    if (!index && count) return fail(w, ICX_E_INVALID, "update: null index");
+    if (count > w->n_entities) return fail(w, ICX_E_INVALID, "update: more rows than uploaded entities");
     if ((P && !w->have_P) || (C && !w->have_C)) return fail(w, ICX_E_STATE, "update: component was never uploaded");
     if (!count) return ICX_OK;
     if (C) { int mrc = icx_host_masks(w); if (mrc != ICX_OK) return mrc; }
-    for (uint32_t i = 0; i < count; i++) {
-        if (index[i] >= w->n_entities) return fail(w, ICX_E_INVALID, "update: index out of range");
+    if (index || C) for (uint32_t i = 0; i < count; i++) {
+        const uint32_t e = index ? index[i] : i;
+        if (e >= w->n_entities) return fail(w, ICX_E_INVALID, "update: index out of range");
         if (C) {
             uint8_t m = 0;
             for (int s = 0; s < ICX_COLLIDERS_PER_ENTITY; s++) if (C[i].colliders[s].isActive) m |= (uint8_t)(1u << s);
-            if (m != w->active_mask[index[i]]) return fail(w, ICX_E_STATE, "update: collider activation changed; call icx_bodies_upload");
+            if (m != w->active_mask[e]) return fail(w, ICX_E_STATE, "update: collider activation changed; call icx_bodies_upload");
         }
     }
     cudaSetDevice(w->device);
     cudaStream_t st = w->stream;
-    CK(w->st_index.ensure((size_t)count * 4));
-    CK(cudaMemcpyAsync(w->st_index.ptr, index, (size_t)count * 4, cudaMemcpyHostToDevice, st));
+    if (index) {
+        CK(w->st_index.ensure((size_t)count * 4));
+        CK(cudaMemcpyAsync(w->st_index.ptr, index, (size_t)count * 4, cudaMemcpyHostToDevice, st));
+    }
     if (T) { CK(w->st_T.ensure((size_t)count * sizeof(IcxTransform))); CK(cudaMemcpyAsync(w->st_T.ptr, T, (size_t)count * sizeof(IcxTransform), cudaMemcpyHostToDevice, st)); }
     if (P) { CK(w->st_P.ensure((size_t)count * sizeof(IcxPhysics))); CK(cudaMemcpyAsync(w->st_P.ptr, P, (size_t)count * sizeof(IcxPhysics), cudaMemcpyHostToDevice, st)); }
     if (C) { CK(w->st_C.ensure((size_t)count * sizeof(IcxColliderComponent))); CK(cudaMemcpyAsync(w->st_C.ptr, C, (size_t)count * sizeof(IcxColliderComponent), cudaMemcpyHostToDevice, st)); }
     Mirror M = mirror_of(w);
     if (!w->have_P) M.P = nullptr;
-    launch_import_kernel(w->W, M, (const uint32_t*)w->st_index.ptr, nullptr, T ? (const IcxTransform*)w->st_T.ptr : nullptr,
+    launch_import_kernel(w->W, M, index ? (const uint32_t*)w->st_index.ptr : nullptr, nullptr, T ? (const IcxTransform*)w->st_T.ptr : nullptr,
                          P ? (const IcxPhysics*)w->st_P.ptr : nullptr, C ? (const IcxColliderComponent*)w->st_C.ptr : nullptr,
                          nullptr, nullptr, nullptr, count, 0, w->have_C ? 1 : 0, C ? ++w->c_epoch : w->c_epoch, st);
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    return ICX_OK;
+}
+
+int icx_motion_download(IcxWorld* w, uint32_t n, IcxMotionState* out)
+{
+    if (!w || (!out && n)) return ICX_E_INVALID;
+    if (n != w->n_entities) return fail(w, ICX_E_INVALID, "motion_download: n differs from the uploaded entity count");
+    if (!n) return ICX_OK;
+    cudaSetDevice(w->device);
+    cudaStream_t st = w->stream;
+    CK(w->st_P.ensure((size_t)n * sizeof(IcxMotionState)));
+    launch_motion_export(w->W, (IcxMotionState*)w->st_P.ptr, n, st);
+    CK(cudaMemcpyAsync(out, w->st_P.ptr, (size_t)n * sizeof(IcxMotionState), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     CK(cudaGetLastError());
     return ICX_OK;
@@ -450,6 +482,7 @@ int icx_profile_enable(IcxWorld* w, int on)
     if (on && !w->pev[0]) for (auto& e : w->pev) cudaEventCreate(&e);
     w->profile = on != 0;
     for (auto& m : w->phase_ms) m = 0;
+    for (auto& t : w->totals) t = 0;
     w->phase_ticks = 0;
     return ICX_OK;
 }
@@ -460,6 +493,13 @@ int icx_phase_ms(IcxWorld* w, double* ms, uint64_t* n_ticks, uint64_t* n_launche
     if (ms) for (int k = 0; k < ICX_N_PHASES; k++) ms[k] = w->phase_ms[k];
     if (n_ticks) *n_ticks = w->phase_ticks;
     if (n_launches) *n_launches = w->launches;
+    return ICX_OK;
+}
+
+int icx_totals_fetch(IcxWorld* w, uint64_t* out6)
+{
+    if (!w || !out6) return ICX_E_INVALID;
+    for (int k = 0; k < 6; k++) out6[k] = w->totals[k];
     return ICX_OK;
 }
 
@@ -565,6 +605,22 @@ int icx_extra_pairs_fetch(IcxWorld* w, IcxPair* out, size_t cap, size_t* n)
     keys.erase(std::unique(keys.begin(), keys.end()), keys.end());       // rows that collide in the bucket hash are walked twice
     *n = keys.size();
     if (out) for (size_t i = 0; i < std::min(cap, keys.size()); i++) { out[i].a = (uint32_t)(keys[i] >> 32); out[i].b = (uint32_t)keys[i]; }
+    return ICX_OK;
+}
+
+// Diagnostic: which = 0 predicted push, 1 budget, 2 largest displacement component static resolution produced in the last tick.
+int icx_debug_array(IcxWorld* w, int which, float* out, size_t cap)
+{
+    if (!w || !out || which < 0 || which > 2) return ICX_E_INVALID;
+    cudaSetDevice(w->device);
+    const size_t n = std::min<size_t>(cap, w->n_entities);
+    if (!n) return ICX_OK;
+    if (which < 2) { CK(cudaMemcpyAsync(out, which ? w->W.bm : w->W.push, n * sizeof(float), cudaMemcpyDeviceToHost, w->stream)); CK(cudaStreamSynchronize(w->stream)); return ICX_OK; }
+    std::vector<float4> a(n), b(n);
+    CK(cudaMemcpyAsync(a.data(), w->W.in.pos, n * sizeof(float4), cudaMemcpyDeviceToHost, w->stream));
+    CK(cudaMemcpyAsync(b.data(), w->W.pos0, n * sizeof(float4), cudaMemcpyDeviceToHost, w->stream));
+    CK(cudaStreamSynchronize(w->stream));
+    for (size_t i = 0; i < n; i++) out[i] = std::max(std::max(std::fabs(a[i].x - b[i].x), std::fabs(a[i].y - b[i].y)), std::fabs(a[i].z - b[i].z));
     return ICX_OK;
 }
 

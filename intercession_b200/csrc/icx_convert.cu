@@ -122,6 +122,29 @@ __global__ void __launch_bounds__(128) k_export(DeviceWorld W, Mirror M, int hav
     if (tc_out) tc_out[e] = (uint16_t)(ts >> 16);
 }
 
+// The 76 bytes per entity a tick writes, as AoS rows.  A block stages its 256 rows (19 456 contiguous bytes) in shared memory and
+// writes them out with full-width coalesced stores.
+__global__ void __launch_bounds__(256) k_motion_export(DeviceWorld W, float* __restrict__ out, uint32_t n)
+{
+    __shared__ float rows[256 * 19];
+    const uint32_t base = blockIdx.x * 256u, e = base + threadIdx.x;
+    if (e < n) {
+        const float4 p = W.in.pos[e], r = W.in.rot[e], v = W.in.vel[e], a = W.in.acc[e], w = W.in.angvel[e], al = W.in.angacc[e];
+        float* o = rows + threadIdx.x * 19;                                         // stride 19 words: conflict-free
+        o[0] = p.x; o[1] = p.y; o[2] = p.z; o[3] = r.x; o[4] = r.y; o[5] = r.z; o[6] = r.w;
+        o[7] = v.x; o[8] = v.y; o[9] = v.z; o[10] = a.x; o[11] = a.y; o[12] = a.z;
+        o[13] = w.x; o[14] = w.y; o[15] = w.z; o[16] = al.x; o[17] = al.y; o[18] = al.z;
+    }
+    __syncthreads();
+    const uint32_t m = min(256u, n - base) * 19u;
+    float* dst = out + (size_t)base * 19;
+    for (uint32_t i = threadIdx.x; i < m; i += 256u) dst[i] = rows[i];
+}
+void launch_motion_export(const DeviceWorld& W, IcxMotionState* out, uint32_t n, cudaStream_t st)
+{
+    if (n) k_motion_export<<<(n + 255) / 256, 256, 0, st>>>(W, reinterpret_cast<float*>(out), n);
+}
+
 // ---- packet structure = ColliderSynchro::update's submission order (collider_synchro.cpp:28-42) ----
 // One packet per ACTIVE collider, entity by entity.  Computed on the device from the uploaded
 // components (count, exclusive scan, pack): walking 168 B per entity on the host costs more than the

@@ -11,7 +11,6 @@ namespace icx {
 void launch_integrate_prep(const DeviceWorld& W, double dt, int do_euler, cudaStream_t st);
 void launch_grid(const DeviceWorld& W, cudaStream_t st);      // 4 kernels: scan x3 + scatter
 void launch_pairs(const DeviceWorld& W, cudaStream_t st);
-void launch_budget_update(const DeviceWorld& W, cudaStream_t st);
 void launch_narrow(const DeviceWorld& W, int blocks, cudaStream_t st);
 int resolve_grid_blocks(int device, int phase);               // co-resident blocks of the persistent resolve kernels (0 = prepare, 1 = rounds)
 cudaError_t launch_resolve(const DeviceWorld& W, double dt, int do_euler, int prepare_blocks, int blocks, cudaStream_t st);
@@ -19,6 +18,7 @@ struct Mirror { uint32_t* ids; IcxTransform* T; IcxPhysics* P; IcxColliderCompon
 void launch_import_kernel(const DeviceWorld& W, Mirror M, const uint32_t* index, const uint32_t* ids, const IcxTransform* T,
                           const IcxPhysics* P, const IcxColliderComponent* C, const uint8_t* hasP, const uint8_t* ts,
                           const uint16_t* tc, uint32_t count, int full, int have_C, uint32_t epoch, cudaStream_t st);
+void launch_motion_export(const DeviceWorld& W, IcxMotionState* out, uint32_t n, cudaStream_t st);
 void launch_export_kernel(const DeviceWorld& W, Mirror M, int have_T, int have_P, int have_C, uint8_t* ts, uint16_t* tc,
                           uint32_t n, cudaStream_t st);
 
@@ -75,6 +75,7 @@ struct IcxWorld {
     cudaEvent_t pev[ICX_N_PHASES + 1] = {};
     double phase_ms[ICX_N_PHASES] = {};
     uint64_t phase_ticks = 0;
+    uint64_t totals[6] = {};            // since icx_profile_enable: ticks, candidate pairs, contacts, rounds, attempts, dirty bodies (summed over ticks)
     uint64_t launches = 0;              // kernels launched by icx_step* since creation
     int resolve_blocks = 0, prepare_blocks = 0, narrow_blocks = 0;
     std::string error;

@@ -34,7 +34,7 @@ __global__ void __launch_bounds__(256) k_integrate_prep(DeviceWorld W, double de
     W.out.ts[e] = W.in.ts[e];
     W.pos0[e] = r.pos;
     W.dirty_slot[e] = ICX_NONE;
-    W.push[e] = 0.0f;
+    W.push[e] = 0.0f; W.pushv[e] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     { const float k = W.bm_keep[e]; if (k > 0.0f) { const float d = k * 0.85f; W.bm_keep[e] = d > W.margin ? d : 0.0f; } }   // the carried budget floor fades
 
     // ---- per-collider derivation (ColliderSynchro::update + what every later pair test needs) ----
@@ -100,7 +100,10 @@ __global__ void __launch_bounds__(256) k_integrate_prep(DeviceWorld W, double de
         uint32_t cell = 0xFFFFFFFFu;
         if (type != ICX_COLLIDER_NONE) {
             const float ext = fmaxf(fmaxf(hi.x - lo.x, hi.y - lo.y), hi.z - lo.z);
-            if (ext > W.cell_size || !(ext == ext)) {
+            if (!(ext < 3.0e38f)) {
+                // non-finite bound (a NaN / Inf transform): the reference carries such a body along, every test against it
+                // fails; here it takes no part in the grid
+            } else if (ext > W.cell_size) {
                 if (ef & EF_IMMUTABLE) {
                     uint32_t idx = atomicAdd(&W.counters[CTR_LARGE], 1u);
                     if (idx < W.max_large) W.large_list[idx] = p; else atomicOr(W.flags, RF_LARGE_OVERFLOW);
@@ -434,23 +437,7 @@ __global__ void __launch_bounds__(PAIRS_TPB, PAIRS_MINB) k_pairs(DeviceWorld W)
     warp_flush(W, S.loose[tid >> 5], ws.n_loose, CTR_CANDIDATES, W.pairs, nullptr, 0);
 }
 
-// After an attempt that moved bodies beyond their budget: raise the carried floor of exactly those bodies (run_tick re-runs
-// the tick from the untouched input).
-__global__ void __launch_bounds__(256) k_budget_update(DeviceWorld W)
-{
-    const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= W.n_entities) return;
-    const uint32_t need = W.bm_need[e];
-    if (!need) return;
-    W.bm_need[e] = 0u;
-    W.bm_keep[e] = fmaxf(W.bm_keep[e], (__uint_as_float(need) * 1.5f + 0.01f) / 0.85f);    // k_integrate_prep fades it by 0.85 before use
-}
-
 // ---- launchers ------------------------------------------------------------------------
-void launch_budget_update(const DeviceWorld& W, cudaStream_t st)
-{
-    if (W.n_entities) k_budget_update<<<(W.n_entities + 255) / 256, 256, 0, st>>>(W);
-}
 void launch_integrate_prep(const DeviceWorld& W, double dt, int do_euler, cudaStream_t st)
 {
     if (W.n_entities == 0) return;

@@ -33,18 +33,22 @@ namespace icx {
 // list entry: x = other packet | ICX_NB_IMMUTABLE, y = its entity index (saves one dependent load per walk step)
 struct Cursor { uint32_t p0, npk, n0, n1, e; const uint2* l0; const uint2* l1; };
 
-// slot_info[slot] = {first packet | count << 30, n0, n1, entity}: everything a walk needs in ONE load
+// slot_info[slot] = {first packet | count << 30, n0 | n1 << 16, pool offset, entity}: everything a walk needs in ONE load
 __device__ __forceinline__ Cursor make_cursor(const DeviceWorld& W, uint32_t slot, uint4 info)
 {
     Cursor c;
-    c.npk = info.x >> 30; c.p0 = info.x & 0x3FFFFFFFu; c.n0 = info.y; c.n1 = info.z; c.e = info.w;
-    c.l0 = W.nbr + (size_t)(slot * 2u) * W.max_neighbors; c.l1 = c.l0 + W.max_neighbors;
+    c.npk = info.x >> 30; c.p0 = info.x & 0x3FFFFFFFu; c.n0 = info.y & 0xFFFFu; c.n1 = info.y >> 16; c.e = info.w;
+    c.l0 = W.nbr + info.z; c.l1 = c.l0 + c.n0;
     return c;
 }
 __device__ __forceinline__ Cursor load_cursor(const DeviceWorld& W, uint32_t slot) { return make_cursor(W, slot, W.slot_info[slot]); }
 // Next entry of the body's merged queue.  Order = the reference's lexicographic pair order seen
 // from this body: first pairs whose other packet precedes mine, by (other, my slot); then all
 // pairs of my slot-0 packet, then all of my slot-1 packet.
+// entry.y = partner's entity index (24 bits) | quantised lower bound of the gap between the two shapes on the post-integration
+// state << 24 (ICX_GAP_UNIT margins per step; 0 = touching / unknown): see gap_of / cannot_meet
+#define ICX_NB_ENT_MASK 0x00FFFFFFu
+#define ICX_GAP_UNIT 0.5f
 __device__ __forceinline__ bool cursor_head(const Cursor& c, uint32_t hw, uint32_t& k, uint32_t& entry, uint32_t& eo)
 {
     const uint32_t h0 = hw & 0xFFFFu, h1 = hw >> 16;
@@ -59,7 +63,7 @@ __device__ __forceinline__ bool cursor_head(const Cursor& c, uint32_t hw, uint32
         if (alow || blow) k = (alow && blow) ? (bo < ao ? 1u : 0u) : (alow ? 0u : 1u);
         else k = 0u;
     } else k = has0 ? 0u : 1u;
-    entry = k ? b : a; eo = k ? eb : ea;
+    entry = k ? b : a; eo = k ? eb : ea;                     // eo: raw .y (entity | gap << 24)
     return true;
 }
 __device__ __forceinline__ uint32_t cursor_advance(uint32_t hw, uint32_t k) { return k ? hw + 0x10000u : hw + 1u; }
@@ -128,7 +132,7 @@ __device__ __forceinline__ bool sat_may_hit(const float4* __restrict__ dA, const
 // would have to be pushed before the exact procedure could report a hit).  A gap above `far`
 // returns at once.  Used only to PREDICT which bodies the ordered replay will touch.
 __device__ __forceinline__ bool sat_measure(const float4* __restrict__ dA, const float4* __restrict__ dB, V3 posA, V3 posB, int tA, int tB,
-                                            float far, float& value)
+                                            float far, float& value, V3* push_dir = nullptr)
 {
     const float4 a0 = dA[0], a1 = dA[1], a2 = dA[2], a3 = dA[3], a4 = dA[4], a5 = dA[5];
     const float4 b0 = dB[0], b1 = dB[1], b2 = dB[2], b3 = dB[3], b4 = dB[4], b5 = dB[5];
@@ -161,7 +165,10 @@ __device__ __forceinline__ bool sat_measure(const float4* __restrict__ dA, const
             separated = true;
             maxsep = fmaxf(maxsep, (dist - s - tol) / len);
             if (maxsep > far) { value = maxsep; return false; }
-        } else minpen = fminf(minpen, (s - dist + tol) / len);
+        } else {
+            const float pen = (s - dist + tol) / len;
+            if (pen < minpen) { minpen = pen; if (push_dir) *push_dir = L * ((dot(d, L) >= 0.0f ? 1.0f : -1.0f) / len); }
+        }
     }
     value = separated ? maxsep : (minpen < INFINITY ? minpen : 0.0f);
     return !separated;
@@ -345,13 +352,13 @@ __device__ __forceinline__ void store_side(const DeviceWorld& W, uint32_t e, con
     W.out.angvel[e] = make_float4(S.angvel.x, S.angvel.y, S.angvel.z, 0.0f);
     if (rr) {
         W.out.pos[e] = make_float4(S.origin.x, S.origin.y, S.origin.z, 0.0f);
-        // the candidate lists cover a displacement of bm[e] (DESIGN.md "Broadphase bound"): beyond it the tick is re-run with
+        // the candidate lists cover a displacement of bm[e] (DESIGN.md "Broadphase bound"): beyond it the replay restarts with
         // this body's budget raised (a NaN origin is the reference's problem as much as ours: it is carried along)
         const float lim = W.bm[e] * 0.98f;
         const float dmax = fmaxf(fmaxf(fabsf(S.origin.x - s.pos0.x), fabsf(S.origin.y - s.pos0.y)), fabsf(S.origin.z - s.pos0.z));
         if (dmax > lim && dmax < 3.0e38f) {
-            atomicOr(W.flags, RF_MARGIN_VIOLATED);
-            if (atomicMax((int*)&W.bm_need[e], __float_as_int(dmax)) == 0) atomicAdd(&W.counters[CTR_VIOLATORS], 1u);
+            atomicMax((int*)&W.bm_need[e], __float_as_int(dmax));
+            atomicAdd(&W.counters[CTR_VIOLATORS], 1u);                             // the replay restarts with this body's budget raised
         }
     } else {
         W.out.acc[e] = make_float4(S.acc.x, S.acc.y, S.acc.z, 0.0f);
@@ -532,9 +539,10 @@ __global__ void __launch_bounds__(128) k_narrow(const __grid_constant__ DeviceWo
     const uint32_t ea = W.pk_entity[pa], eb = W.pk_entity[pb];
     const int tA = __float_as_uint(W.pk_lpos[pa].w) & PF_TYPE_MASK, tB = __float_as_uint(W.pk_lpos[pb].w) & PF_TYPE_MASK;
     float depth = 0.0f;
+    V3 dir = v3(0.0f, 0.0f, 0.0f);                  // direction static resolution would push A (least-penetration axis, from B towards A)
     if (is_sat_pair(tA, tB)) {
         float value;
-        if (!sat_measure(W.pk_d + (size_t)pa * 6, W.pk_d + (size_t)pb * 6, v3(W.out.pos[ea]), v3(W.out.pos[eb]), tA, tB, 0.0f, value)) continue;
+        if (!sat_measure(W.pk_d + (size_t)pa * 6, W.pk_d + (size_t)pb * 6, v3(W.out.pos[ea]), v3(W.out.pos[eb]), tA, tB, 0.0f, value, &dir)) continue;
         depth = value;
     } else {
         V3 baseA, baseB; Shape A, B; Hit h;
@@ -547,10 +555,26 @@ __global__ void __launch_bounds__(128) k_narrow(const __grid_constant__ DeviceWo
         if (k < W.max_static) W.static_pairs[k] = make_uint2(pa, pb); else atomicOr(W.flags, RF_PAIR_OVERFLOW);
         continue;
     }
-    // predicted push of each body = sum of the depths of its contacts; touching bodies pass pushes on
+    // Predicted push of each body.  Static resolution splits a penetration by inverse mass (collision_procedures.cpp:668-694)
+    // and moves the body along the contact normal; contacts on opposite sides cancel.  Kept per body: the largest single
+    // share (push) and the vector sum of all shares (pushv); budget_entity takes the larger of the two magnitudes.
     const bool ma = !(__float_as_uint(W.prm1[ea].w) & EF_IMMUTABLE), mb = !(__float_as_uint(W.prm1[eb].w) & EF_IMMUTABLE);
-    if (ma) { mark_dirty(W, ea); atomicAdd(&W.push[ea], depth); }
-    if (mb) { mark_dirty(W, eb); atomicAdd(&W.push[eb], depth); }
+    const float massA = W.prm0[ea].w, massB = W.prm0[eb].w;                        // 0 = infinite
+    float shareA = 1.0f, shareB = 1.0f;
+    if (massA == 0.0f && massB == 0.0f) { shareA = 0.0f; shareB = 0.0f; }
+    else if (massA == 0.0f) shareA = 0.0f;
+    else if (massB == 0.0f) shareB = 0.0f;
+    else { shareA = massB / (massA + massB); shareB = massA / (massA + massB); }
+    if (ma) {
+        mark_dirty(W, ea);
+        const float d = depth * shareA;
+        if (d > 0.0f) { atomicMax((int*)&W.push[ea], __float_as_int(d)); atomicAdd(&W.pushv[ea].x, dir.x * d); atomicAdd(&W.pushv[ea].y, dir.y * d); atomicAdd(&W.pushv[ea].z, dir.z * d); }
+    }
+    if (mb) {
+        mark_dirty(W, eb);
+        const float d = depth * shareB;
+        if (d > 0.0f) { atomicMax((int*)&W.push[eb], __float_as_int(d)); atomicAdd(&W.pushv[eb].x, -dir.x * d); atomicAdd(&W.pushv[eb].y, -dir.y * d); atomicAdd(&W.pushv[eb].z, -dir.z * d); }
+    }
     }
 }
 
@@ -561,12 +585,25 @@ __global__ void __launch_bounds__(128) k_narrow(const __grid_constant__ DeviceWo
 // bm[e] > margin.  Candidates are the pairs with overlap(S_i (+) x_i, S_j (+) x_j), x = bm - margin: for x_i = x_j = 0 that
 // is the flat list k_pairs emitted; the rest (xpairs) is found by the movers themselves, one warp each, walking the grid
 // cells their widened bound can reach.  Nobody else pays for a mover.
+#ifndef ICX_PREDICT_CAP
+#define ICX_PREDICT_CAP 8.0f
+#endif
+__device__ __forceinline__ float predicted_push(const DeviceWorld& W, uint32_t e)
+{
+    const float4 v = W.pushv[e];
+    return fmaxf(*(volatile float*)&W.push[e], fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fabsf(v.z)));
+}
+
 static __device__ __forceinline__ void budget_entity(const DeviceWorld& W, uint32_t e)
 {
     const float m0 = W.margin;
-    const float p = W.push[e], k = W.bm_keep[e];
+    const float k = W.bm_keep[e];
+    const float p = predicted_push(W, e);
     float b = fmaxf(m0, k);
-    if (p > 0.0f) b = fmaxf(b, 1.5f * p + 0.25f * m0);
+    // the prediction is trusted up to ICX_PREDICT_CAP margins (static resolution rarely moves a body further: measured p99.9);
+    // beyond that only a body that was CAUGHT moving further keeps a larger budget (bm_keep)
+    if (p > 0.0f) b = fmaxf(b, fminf(1.25f * p + 0.25f * m0, ICX_PREDICT_CAP * m0));
+    b = fminf(b, m0 + 6.0f * W.cell_size);                                          // a mover's walk stays bounded (beyond it: the attempt limit reports it)
     if (!(b == b) || (__float_as_uint(W.prm1[e].w) & EF_IMMUTABLE)) b = m0;
     W.bm[e] = b;
     if (b > m0 && (W.first_packet[e] >> 30)) {
@@ -592,8 +629,7 @@ __device__ __forceinline__ void emit_xpair(const DeviceWorld& W, uint32_t p, uin
 // One warp per mover entity: every packet whose widened bound overlaps the mover's widened bound but whose stored bound
 // does not (those pairs are in the flat list already).  A partner is binned by the centre of its stored bound, which lies
 // within half a cell of that bound: the walk covers the cells within x_i + x_max + cell / 2 of the mover's stored bound.
-// A pair of two movers is emitted by the one with the lower packet index.  Rows that collide in the bucket hash are visited
-// twice: the duplicates are dropped when the lists are sorted.
+// A pair of two movers is emitted by the one with the lower packet index.
 static __device__ __noinline__ void mover_walk_warp(const DeviceWorld& W, uint32_t e, float x_max)
 {
     const uint32_t lane = threadIdx.x & 31u;
@@ -624,6 +660,9 @@ static __device__ __noinline__ void mover_walk_warp(const DeviceWorld& W, uint32
                         const float4 blo = W.s_lo[j], bhi = W.s_hi[j];
                         const uint32_t btag = __float_as_uint(blo.w), be = __float_as_uint(bhi.w), q = btag & ICX_NB_INDEX_MASK;
                         if (be == e || (W.worldline_stride && be / W.worldline_stride != wl) || !can_intersect(type, (btag >> 28) & 3, W.cfg_flags)) continue;
+                        // rows that collide in the bucket hash share a block: a packet counts only in the row its own cell is in
+                        if (cell_coord(blo.y, bhi.y, W.inv_cell) != cy || cell_coord(blo.z, bhi.z, W.inv_cell) != cz ||
+                            (cell_coord(blo.x, bhi.x, W.inv_cell) >> ICX_XB) != xb) continue;
                         const bool q_immut = (btag & 0x40000000u) != 0;
                         const float xj = q_immut ? 0.0f : W.bm[be] - m0;
                         if (xj > 0.0f && q < p) continue;                          // two movers: the lower packet's walk emits the pair
@@ -646,98 +685,127 @@ static __device__ __noinline__ void mover_walk_warp(const DeviceWorld& W, uint32
 // every list ascending by packet index = the order the reference's pair loop meets the partners
 // (collision_physics_relay.h:29-37).  Streaming pass over the pairs with one atomic append per dirty endpoint, then one
 // warp per body sorts (and drops the duplicates the movers' walks may have produced).
-#define SORT_CAP 128
-__device__ __forceinline__ void list_append(const DeviceWorld& W, uint32_t e, uint32_t p, uint32_t first, uint32_t n_dirty, uint32_t other, uint32_t eo, bool o_immut)
+// Lists live in a pool that is bump-allocated per tick (CTR_POOL): count pass, allocation, fill pass, then one warp per body
+// sorts (lists of up to 32 entries in registers, longer ones by ranking into a fresh pool region).
+// mode of a list build: plain entries; entries with the gap between the shapes (may_meet); or the same for the flagged slots only
+enum { LISTS_PLAIN = 0, LISTS_GAPS = 1, LISTS_FLAGGED = 2 };
+__device__ __forceinline__ bool slot_wanted(const DeviceWorld& W, uint32_t s, uint32_t first, uint32_t n_dirty, int mode)
 {
-    const uint32_t s = W.dirty_slot[e];
-    if (s < first || s >= n_dirty) return;                                          // clean (ICX_NONE), or listed already
+    return s >= first && s < n_dirty && (mode != LISTS_FLAGGED || W.slot_flag[s] != 0u);   // s = ICX_NONE (clean) fails the range test
+}
+__device__ __forceinline__ void list_visit(const DeviceWorld& W, uint32_t s, uint32_t e, uint32_t p, uint32_t other, uint32_t eo, bool o_immut, bool fill, uint32_t gapq)
+{
     const uint32_t k = p - (W.first_packet[e] & 0x3FFFFFFFu);
-    const uint32_t at = atomicAdd(&W.nbr_count[s * 2u + k], 1u);
-    if (at < W.max_neighbors) W.nbr[(size_t)(s * 2u + k) * W.max_neighbors + at] = make_uint2(other | (o_immut ? ICX_NB_IMMUTABLE : 0u), eo);
+    if (!fill) { atomicAdd(&W.nbr_count[s * 2u + k], 1u); return; }
+    const uint4 info = W.slot_info[s];                                              // {.., n0 | n1 << 16, offset, ..} written by the allocation pass
+    if (info.z == ICX_NONE) return;                                                 // pool full: the tick is re-run with a larger pool
+    const uint32_t at = atomicAdd(&W.nbr_fill[s * 2u + k], 1u);
+    W.nbr[info.z + (k ? (info.y & 0xFFFFu) : 0u) + at] = make_uint2(other | (o_immut ? ICX_NB_IMMUTABLE : 0u), eo | (gapq << 24));
 }
 
-static __device__ __noinline__ void sort_lists_warp(const DeviceWorld& W, uint32_t slot, uint2* sm)
+// Lower bound of the distance between the shapes of packets pa, pb on the post-integration state, in steps of
+// ICX_GAP_UNIT * margin (0 = touching, not a separating-axis pair, or not worth knowing).
+__device__ __forceinline__ uint32_t gap_of(const DeviceWorld& W, uint32_t pa, uint32_t pb, uint32_t ea, uint32_t eb)
+{
+    const int tA = __float_as_uint(W.pk_lpos[pa].w) & PF_TYPE_MASK, tB = __float_as_uint(W.pk_lpos[pb].w) & PF_TYPE_MASK;
+    if (!is_sat_pair(tA, tB)) return 0u;
+    float value;
+    if (sat_measure(W.pk_d + (size_t)pa * 6, W.pk_d + (size_t)pb * 6, v3(W.pos0[ea]), v3(W.pos0[eb]), tA, tB, 3.0e38f, value)) return 0u;
+    const float steps = value / (ICX_GAP_UNIT * W.margin);
+    return steps >= 255.0f ? 255u : (uint32_t)steps;                                // truncation: a lower bound stays one
+}
+
+static __device__ __noinline__ void sort_lists_warp(const DeviceWorld& W, uint32_t slot)
 {
     const uint32_t FULL = 0xFFFFFFFFu, lane = threadIdx.x & 31u;
-    const uint32_t e = W.dirty_list[slot], cap = W.max_neighbors;
-    uint32_t out_cnt[2];
+    uint4 info = W.slot_info[slot];
+    if (info.z == ICX_NONE) return;
+    const uint32_t n0 = info.y & 0xFFFFu, n1 = info.y >> 16;
+    uint32_t new_off = info.z;
+    if (n0 > 32u || n1 > 32u) {                                                     // the ranked copy becomes the list
+        if (lane == 0) { new_off = atomicAdd(&W.counters[CTR_POOL], n0 + n1); if (new_off + n0 + n1 > W.max_nbr) { atomicOr(W.flags, RF_NEIGHBOR_OVERFLOW); new_off = ICX_NONE; } }
+        new_off = __shfl_sync(FULL, new_off, 0);
+        if (new_off == ICX_NONE) return;
+    }
     for (uint32_t k = 0; k < 2u; k++) {
-        uint2* list = W.nbr + (size_t)(slot * 2u + k) * cap;
-        uint32_t cnt = W.nbr_count[slot * 2u + k];
-        if (cnt > cap) { if (lane == 0) atomicOr(W.flags, RF_NEIGHBOR_OVERFLOW); cnt = cap; }
+        const uint32_t cnt = k ? n1 : n0;
+        uint2* list = W.nbr + info.z + (k ? n0 : 0u);
         if (cnt <= 32u) {
             const uint2 mine = lane < cnt ? list[lane] : make_uint2(0xFFFFFFFFu, 0u);
             const uint32_t key = mine.x & ICX_NB_INDEX_MASK;
-            bool first = lane < cnt;
-            for (uint32_t q = 0; q < cnt; q++) { const uint32_t other = __shfl_sync(FULL, key, q); if (q < lane && other == key) first = false; }
-            const uint32_t firsts = __ballot_sync(FULL, first);
             uint32_t rank = 0;
-            for (uint32_t q = 0; q < cnt; q++) { const uint32_t other = __shfl_sync(FULL, key, q); rank += ((firsts >> q & 1u) && other < key) ? 1u : 0u; }
+            for (uint32_t q = 0; q < cnt; q++) { const uint32_t other = __shfl_sync(FULL, key, q); rank += other < key ? 1u : 0u; }
             __syncwarp();
-            if (first) list[rank] = mine;
-            cnt = __popc(firsts);
-        } else if (cnt <= SORT_CAP) {
-            for (uint32_t i = lane; i < cnt; i += 32u) sm[i] = list[i];
-            __syncwarp();
-            uint32_t dupmask = 0;                                                   // bit t: my element lane + 32 t repeats an earlier one
-            for (uint32_t i = lane, t = 0; i < cnt; i += 32u, t++) {
-                const uint32_t key = sm[i].x & ICX_NB_INDEX_MASK;
-                bool dup = false;
-                for (uint32_t q = 0; q < i; q++) dup |= (sm[q].x & ICX_NB_INDEX_MASK) == key;
-                if (dup) dupmask |= 1u << t;
-            }
-            __syncwarp();
-            for (uint32_t i = lane, t = 0; i < cnt; i += 32u, t++) if (dupmask >> t & 1u) sm[i].y |= 0x80000000u;    // entity indices are < 2^24
-            __syncwarp();
-            uint32_t kept = 0;
-            for (uint32_t i = lane, t = 0; i < cnt; i += 32u, t++) {
-                if (dupmask >> t & 1u) continue;
-                const uint2 mine = sm[i]; const uint32_t key = mine.x & ICX_NB_INDEX_MASK;
-                uint32_t rank = 0;
-                for (uint32_t q = 0; q < cnt; q++) { const uint2 o = sm[q]; rank += (!(o.y >> 31) && (o.x & ICX_NB_INDEX_MASK) < key) ? 1u : 0u; }
-                list[rank] = mine; kept++;
-            }
-            cnt = __reduce_add_sync(FULL, kept);
-            __syncwarp();
+            if (lane < cnt) (new_off == info.z ? list : W.nbr + new_off + (k ? n0 : 0u))[rank] = mine;      // keys are distinct packet indices
         } else {
-            if (lane == 0) {
-                for (uint32_t i = 1; i < cnt; i++) {
-                    const uint2 v = list[i]; uint32_t q = i;
-                    while (q > 0 && (list[q - 1].x & ICX_NB_INDEX_MASK) > (v.x & ICX_NB_INDEX_MASK)) { list[q] = list[q - 1]; q--; }
-                    list[q] = v;
-                }
-                uint32_t w = cnt ? 1u : 0u;
-                for (uint32_t i = 1; i < cnt; i++) if ((list[i].x & ICX_NB_INDEX_MASK) != (list[w - 1].x & ICX_NB_INDEX_MASK)) list[w++] = list[i];
-                cnt = w;
+            uint2* dst = W.nbr + new_off + (k ? n0 : 0u);
+            for (uint32_t i = lane; i < cnt; i += 32u) {
+                const uint2 mine = list[i]; const uint32_t key = mine.x & ICX_NB_INDEX_MASK;
+                uint32_t rank = 0;
+                for (uint32_t q = 0; q < cnt; q++) rank += (list[q].x & ICX_NB_INDEX_MASK) < key ? 1u : 0u;
+                dst[rank] = mine;
             }
-            cnt = __shfl_sync(FULL, cnt, 0);
         }
         __syncwarp();
-        if (lane == 0) W.nbr_count[slot * 2u + k] = cnt;
-        out_cnt[k] = cnt;
     }
-    if (lane == 0) W.slot_info[slot] = make_uint4(W.first_packet[e], out_cnt[0], out_cnt[1], e);
+    if (lane == 0 && new_off != info.z) { info.z = new_off; W.slot_info[slot] = info; }
+}
+
+// Budgets of all bodies (a body an earlier attempt caught beyond its budget first gets its carried floor raised), then the
+// movers' own candidates.  Called by every thread of the grid; ends behind a grid barrier.
+template <typename Grid>
+__device__ __forceinline__ void budgets_and_movers(const DeviceWorld& W, Grid& grid, uint32_t tid, uint32_t nth)
+{
+    for (uint32_t e = tid; e < W.n_entities; e += nth) {
+        const uint32_t need = W.bm_need[e];
+        if (need) { W.bm_need[e] = 0u; W.bm_keep[e] = fmaxf(W.bm_keep[e], __uint_as_float(need) * 2.0f + 0.02f); }
+        budget_entity(W, e);
+    }
+    grid.sync();
+    const uint32_t n_mov = min(*(volatile uint32_t*)&W.counters[CTR_MOVERS], W.n_entities);
+    const float x_max = __uint_as_float(*(volatile uint32_t*)&W.counters[CTR_XMAX]);
+    for (uint32_t m = tid >> 5; m < n_mov; m += (nth >> 5)) mover_walk_warp(W, W.mover_list[m], x_max);
+    grid.sync();
 }
 
 template <typename Grid>
-__device__ __forceinline__ void lists_build(const DeviceWorld& W, uint32_t first, uint32_t n_dirty, Grid& grid, uint32_t tid, uint32_t nth, uint2* sort_sm)
+__device__ __forceinline__ void lists_build(const DeviceWorld& W, uint32_t first, uint32_t n_dirty, Grid& grid, uint32_t tid, uint32_t nth, int mode)
 {
     if (first >= n_dirty) return;                                                   // uniform
-    for (uint32_t s = first + tid; s < n_dirty; s += nth) { W.nbr_count[s * 2u] = 0u; W.nbr_count[s * 2u + 1u] = 0u; }
+    for (uint32_t s = first + tid; s < n_dirty; s += nth) if (slot_wanted(W, s, first, n_dirty, mode)) { W.nbr_count[s * 2u] = 0u; W.nbr_count[s * 2u + 1u] = 0u; }
     grid.sync();
     const uint32_t n_pairs = min(*(volatile uint32_t*)&W.counters[CTR_CANDIDATES], W.max_pairs);
     const uint32_t n_x = min(*(volatile uint32_t*)&W.counters[CTR_XPAIRS], W.max_xpairs);
-    for (uint32_t i = tid; i < n_pairs + n_x; i += nth) {
-        const uint2 pr = i < n_pairs ? W.pairs[i] : W.xpairs[i - n_pairs];
-        const uint32_t pa = pr.x & ICX_NB_INDEX_MASK, pb = pr.y & ICX_NB_INDEX_MASK;
-        const bool ia = (pr.x & ICX_PAIR_A_IMMUT) != 0, ib = (pr.y & ICX_PAIR_B_IMMUT) != 0;
-        if (ia && ib) continue;
-        const uint32_t ea = W.pk_entity[pa], eb = W.pk_entity[pb];
-        if (!ia) list_append(W, ea, pa, first, n_dirty, pb, eb, ib);
-        if (!ib) list_append(W, eb, pb, first, n_dirty, pa, ea, ia);
+    for (int fill = 0; fill < 2; fill++) {
+        for (uint32_t i = tid; i < n_pairs + n_x; i += nth) {
+            const uint2 pr = i < n_pairs ? W.pairs[i] : W.xpairs[i - n_pairs];
+            const uint32_t pa = pr.x & ICX_NB_INDEX_MASK, pb = pr.y & ICX_NB_INDEX_MASK;
+            const bool ia = (pr.x & ICX_PAIR_A_IMMUT) != 0, ib = (pr.y & ICX_PAIR_B_IMMUT) != 0;
+            if (ia && ib) continue;
+            const uint32_t ea = W.pk_entity[pa], eb = W.pk_entity[pb];
+            const uint32_t sa = ia ? ICX_NONE : W.dirty_slot[ea], sb = ib ? ICX_NONE : W.dirty_slot[eb];
+            const bool wa = slot_wanted(W, sa, first, n_dirty, mode), wb = slot_wanted(W, sb, first, n_dirty, mode);
+            if (!wa && !wb) continue;
+            uint32_t gapq = 0u;
+            if (fill && mode != LISTS_PLAIN && !ia && !ib) gapq = gap_of(W, pa, pb, ea, eb);   // both can move: how far apart are they (may_meet)?
+            if (wa) list_visit(W, sa, ea, pa, pb, eb, ib, fill != 0, gapq);
+            if (wb) list_visit(W, sb, eb, pb, pa, ea, ia, fill != 0, gapq);
+        }
+        grid.sync();
+        if (fill) break;
+        for (uint32_t s = first + tid; s < n_dirty; s += nth) {                     // allocation
+            if (!slot_wanted(W, s, first, n_dirty, mode)) continue;
+            const uint32_t c0 = W.nbr_count[s * 2u], c1 = W.nbr_count[s * 2u + 1u];
+            uint32_t off = ICX_NONE;
+            if (c0 <= 0xFFFFu && c1 <= 0xFFFFu) { off = atomicAdd(&W.counters[CTR_POOL], c0 + c1); if (off + c0 + c1 > W.max_nbr) off = ICX_NONE; }
+            if (off == ICX_NONE) atomicOr(W.flags, RF_NEIGHBOR_OVERFLOW);
+            const uint32_t e = W.dirty_list[s];
+            W.slot_info[s] = make_uint4(W.first_packet[e], off == ICX_NONE ? 0u : (c0 | (c1 << 16)), off, e);
+            W.nbr_fill[s * 2u] = 0u; W.nbr_fill[s * 2u + 1u] = 0u;
+        }
+        grid.sync();
     }
-    grid.sync();
-    for (uint32_t s = first + (tid >> 5); s < n_dirty; s += (nth >> 5)) sort_lists_warp(W, s, sort_sm);
+    for (uint32_t s = first + (tid >> 5); s < n_dirty; s += (nth >> 5)) if (slot_wanted(W, s, first, n_dirty, mode)) sort_lists_warp(W, s);
 }
 
 // Put a dirty body back to its post-integration state (bit-identical recomputation from the tick input).
@@ -750,6 +818,44 @@ static __device__ __noinline__ void restore_body(const DeviceWorld& W, uint32_t 
     W.out.ts[e] = W.in.ts[e];
     const uint32_t fp = W.first_packet[e];
     for (uint32_t k = 0; k < (fp >> 30); k++) W.pk_minparam[(fp & 0x3FFFFFFFu) + k] = 1.0f;
+}
+
+// One warp per dirty body: hand my predicted push on to the candidates it can reach (see resolve_body).  first_time:
+// the body's list is new, so clean partners within reach are marked too; otherwise only pushes that matter are passed on.
+static __device__ __noinline__ void predict_body_warp(const DeviceWorld& W, uint32_t sl, bool first_time)
+{
+    const uint32_t e = W.dirty_list[sl];
+    const float pa = predicted_push(W, e);
+    if (!(pa > 0.0f)) return;
+    const float m0 = W.margin;
+    if (!first_time && pa < 0.5f * m0) return;                                      // cannot lift anyone above the uniform margin
+    const uint4 info = W.slot_info[sl];
+    if (info.z == ICX_NONE) return;
+    const uint32_t p0 = info.x & 0x3FFFFFFFu, n0 = info.y & 0xFFFFu, n1 = info.y >> 16;
+    const float ma = W.prm0[e].w;                                                   // 0 = infinite
+    const float reach = 1.5f * pa + 0.02f * m0;
+    for (uint32_t i = threadIdx.x & 31u; i < n0 + n1; i += 32u) {
+        const uint32_t k = i < n0 ? 0u : 1u;
+        const uint2 en = W.nbr[info.z + i];
+        if (en.x & ICX_NB_IMMUTABLE) continue;
+        const uint32_t o = en.x & ICX_NB_INDEX_MASK, eo = en.y & ICX_NB_ENT_MASK;
+        const bool clean = W.dirty_slot[eo] == ICX_NONE;
+        if (!clean && pa < 0.5f * m0) continue;
+        const uint32_t p = p0 + k;
+        const int tP = __float_as_uint(W.pk_lpos[p].w) & PF_TYPE_MASK, tO = __float_as_uint(W.pk_lpos[o].w) & PF_TYPE_MASK;
+        if (!is_sat_pair(tP, tO)) continue;
+        float value;
+        const bool touching = sat_measure(W.pk_d + (size_t)p * 6, W.pk_d + (size_t)o * 6, v3(W.out.pos[e]), v3(W.out.pos[eo]), tP, tO, reach, value);
+        if (!(touching || value < reach)) continue;
+        if (clean) mark_dirty(W, eo);
+        const float mb = W.prm0[eo].w;
+        const float share = mb == 0.0f ? 0.0f : (ma == 0.0f ? 1.0f : ma / (ma + mb));     // the partner's part of a penetration between the two
+        const float inherit = (touching ? pa : pa - value) * share;
+        if (inherit > 0.0f) {
+            const float before = __int_as_float(atomicMax((int*)&W.push[eo], __float_as_int(inherit)));
+            if (inherit > before + 0.25f * m0) atomicAdd(&W.counters[CTR_PUSHED], 1u);          // worth another pass
+        }
+    }
 }
 
 // ---- dependency rounds -----------------------------------------------------------------
@@ -767,6 +873,22 @@ static __device__ __noinline__ void restore_body(const DeviceWorld& W, uint32_t 
 // separated by grid barriers.  Cursors are double buffered (head[parity]); each active body has
 // exactly one writer per round.
 
+
+// A two-sided entry (dirty partner) normally waits until it is at the head of BOTH queues.  Not if the pair cannot hit
+// wherever the partner may be: the partner's bound stays inside its stored bound widened by its budget for the whole pass
+// (store_side enforces it), so if MY current bound -- translated by what static resolution moved me so far -- misses that
+// region, or the gap between the two shapes after integration exceeds what I have moved plus what the partner can move, the
+// exact test would miss too and nothing changes.  The partner learns it from my cursor having passed the
+// entry (round_select), or finds the same on its own.  A mover's long list then costs a walk, not a chain of rounds.
+__device__ __forceinline__ bool may_meet(const DeviceWorld& W, float4 alo, float4 ahi, float moved, float4 blo, float4 bhi, uint32_t ey)
+{
+    const float bmj = W.bm[ey & ICX_NB_ENT_MASK], m0 = W.margin;
+    if (!overlap_x(alo, ahi, 0.0f, blo, bhi, bmj - m0)) return false;
+    // the shapes were at least gap apart; I have moved `moved` (Euclidean), the partner at most sqrt(3) * its budget
+    const float gap = (float)(ey >> 24) * (ICX_GAP_UNIT * m0);
+    return !(gap > moved + 1.7320509f * bmj + 1.0e-4f);
+}
+
 // Advance a body's cursor past the leading one-sided entries that cannot hit on the current state
 // (own state is final until the body's next exact pair, one-sided partners are never written).
 // Done by a whole WARP (uniform arguments and result).  Pass 1, one entry per lane: two-sided
@@ -781,6 +903,7 @@ __device__ __forceinline__ uint32_t skip_rejects_warp(const DeviceWorld& W, cons
     const uint32_t FULL = 0xFFFFFFFFu, lane = threadIdx.x & 31u;
     const float4 pe = W.out.pos[c.e], pe0 = W.pos0[c.e];
     const float dx = pe.x - pe0.x, dy = pe.y - pe0.y, dz = pe.z - pe0.z;
+    const float moved = sqrtf(dx * dx + dy * dy + dz * dz) * 1.000001f;
     kind = 0; k_out = 0; o_out = 0;
     for (;;) {
         const uint32_t h0 = hw & 0xFFFFu, h1 = hw >> 16;
@@ -795,12 +918,12 @@ __device__ __forceinline__ uint32_t skip_rejects_warp(const DeviceWorld& W, cons
             const uint2 en = k ? c.l1[h1 + idx] : c.l0[h0 + idx];
             entry = en.x; ent = en.y;
             const uint32_t p = c.p0 + k, o = entry & ICX_NB_INDEX_MASK;
-            const uint32_t ds = (entry & ICX_NB_IMMUTABLE) ? ICX_NONE : W.dirty_slot[en.y];
+            const uint32_t ds = (entry & ICX_NB_IMMUTABLE) ? ICX_NONE : W.dirty_slot[en.y & ICX_NB_ENT_MASK];
             float4 alo = W.pk_lo[p], ahi = W.pk_hi[p];
             const float4 blo = W.pk_lo[o], bhi = W.pk_hi[o];
             alo.x += dx; alo.y += dy; alo.z += dz; ahi.x += dx; ahi.y += dy; ahi.z += dz;
-            two = ds < n_dirty;
-            cand = !two && tight_overlap(alo, ahi, blo, bhi, W.margin);
+            two = ds < n_dirty && may_meet(W, alo, ahi, moved, blo, bhi, en.y);
+            cand = !(ds < n_dirty) && tight_overlap(alo, ahi, blo, bhi, W.margin);
         }
         const uint32_t twos = __ballot_sync(FULL, two), cands = __ballot_sync(FULL, cand);
         uint32_t a0 = 0, a1 = 0; bool boundary = false;
@@ -820,7 +943,7 @@ __device__ __forceinline__ uint32_t skip_rejects_warp(const DeviceWorld& W, cons
             const uint32_t bit = pick ? lb : la;
             if (twos >> bit & 1u) { kind = 1; break; }
             if (cands >> bit & 1u) {
-                const uint32_t o = (pick ? eb : ea) & ICX_NB_INDEX_MASK, eo = __shfl_sync(FULL, ent, bit), p = c.p0 + pick;
+                const uint32_t o = (pick ? eb : ea) & ICX_NB_INDEX_MASK, eo = __shfl_sync(FULL, ent, bit) & ICX_NB_ENT_MASK, p = c.p0 + pick;
                 const bool mh = p < o ? may_hit_warp(W, p, o, c.e, eo) : may_hit_warp(W, o, p, eo, c.e);
                 if (mh) { kind = 2; k_out = pick; o_out = o; break; }
             }
@@ -831,15 +954,22 @@ __device__ __forceinline__ uint32_t skip_rejects_warp(const DeviceWorld& W, cons
     }
 }
 
+
+// Publish a body's cursor for the next round.  A body whose queue is exhausted leaves the work lists; its final cursor goes
+// into BOTH buffers, because a partner that arrives at their common entry later must find it passed (round_select).
+__device__ __forceinline__ void publish_cursor(const DeviceWorld& W, uint32_t s, const Cursor& c, uint32_t hw, int parity, uint32_t ctr_out)
+{
+    W.head[parity ^ 1][s] = hw;
+    if (cursor_pending(c, hw)) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = s;
+    else W.head[parity][s] = hw;
+}
+
 // warp version of settle: lane 0 publishes the cursor
 __device__ __forceinline__ void settle_warp(const DeviceWorld& W, uint32_t s, const Cursor& c, uint32_t hw, uint32_t n_dirty, int parity, uint32_t ctr_out)
 {
     int kind; uint32_t kk, oo;
     hw = skip_rejects_warp(W, c, hw, n_dirty, kind, kk, oo);
-    if ((threadIdx.x & 31u) == 0u) {
-        W.head[parity ^ 1][s] = hw;
-        if (cursor_pending(c, hw)) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = s;
-    }
+    if ((threadIdx.x & 31u) == 0u) publish_cursor(W, s, c, hw, parity, ctr_out);
 }
 
 // The walk on ONE lane (lane-parallel items): the merged queue order is cursor_head's, the verdict per entry is the
@@ -850,18 +980,21 @@ __device__ __forceinline__ uint32_t skip_rejects_lane(const DeviceWorld& W, cons
 {
     const float4 pe = W.out.pos[c.e], pe0 = W.pos0[c.e];
     const float dx = pe.x - pe0.x, dy = pe.y - pe0.y, dz = pe.z - pe0.z;
+    const float moved = sqrtf(dx * dx + dy * dy + dz * dz) * 1.000001f;
     kind = 0; k_out = 0; o_out = 0;
 #pragma unroll 1
     for (;;) {
-        uint32_t k, entry, eo;
-        if (!cursor_head(c, hw, k, entry, eo)) return hw;
+        uint32_t k, entry, ey;
+        if (!cursor_head(c, hw, k, entry, ey)) return hw;
+        const uint32_t eo = ey & ICX_NB_ENT_MASK;
         const uint32_t p = c.p0 + k, o = entry & ICX_NB_INDEX_MASK;
         const uint32_t ds = (entry & ICX_NB_IMMUTABLE) ? ICX_NONE : W.dirty_slot[eo];
-        if (ds < n_dirty) { kind = 1; return hw; }
         float4 alo = W.pk_lo[p], ahi = W.pk_hi[p];
         const float4 blo = W.pk_lo[o], bhi = W.pk_hi[o];
         alo.x += dx; alo.y += dy; alo.z += dz; ahi.x += dx; ahi.y += dy; ahi.z += dz;
-        if (tight_overlap(alo, ahi, blo, bhi, W.margin)) {
+        if (ds < n_dirty) {
+            if (may_meet(W, alo, ahi, moved, blo, bhi, ey)) { kind = 1; return hw; }
+        } else if (tight_overlap(alo, ahi, blo, bhi, W.margin)) {
             const uint32_t qa = min(p, o), qb = max(p, o), ea = p < o ? c.e : eo, eb = p < o ? eo : c.e;
             const int tA = __float_as_uint(W.pk_lpos[qa].w) & PF_TYPE_MASK, tB = __float_as_uint(W.pk_lpos[qb].w) & PF_TYPE_MASK;
             const bool mh = !is_sat_pair(tA, tB)
@@ -874,14 +1007,14 @@ __device__ __forceinline__ uint32_t skip_rejects_lane(const DeviceWorld& W, cons
 
 __device__ __forceinline__ void round_select(const DeviceWorld& W, uint32_t s, uint32_t n_dirty, int parity, uint32_t ctr_out, uint32_t ctr_items)
 {
-    const uint32_t* __restrict__ hin = W.head[parity];
+    const volatile uint32_t* hin = W.head[parity];      // round-start cursors; a body that finishes during the round may already publish here (publish_cursor)
     const Cursor c = load_cursor(W, s);
     const uint32_t hw = hin[s];
     uint32_t k, entry, eo;
     if (!cursor_head(c, hw, k, entry, eo)) return;                                  // (not queued when nothing is pending)
     const uint32_t p = c.p0 + k, o = entry & ICX_NB_INDEX_MASK;
     uint32_t so = ICX_NONE;
-    if (!(entry & ICX_NB_IMMUTABLE)) so = W.dirty_slot[eo];
+    if (!(entry & ICX_NB_IMMUTABLE)) so = W.dirty_slot[eo & ICX_NB_ENT_MASK];
     if (so >= n_dirty) {                                                            // one-sided, not rejected by the filter
         W.items[atomicAdd(&W.counters[ctr_items], 1u)] = make_uint4(min(p, o), max(p, o), s, ICX_NONE);
         return;
@@ -890,9 +1023,15 @@ __device__ __forceinline__ void round_select(const DeviceWorld& W, uint32_t s, u
     const uint32_t hwo = hin[so];
     uint32_t ko, entryo, eoo;
     const bool ready = cursor_head(co, hwo, ko, entryo, eoo) && co.p0 + ko == o && (entryo & ICX_NB_INDEX_MASK) == p;
-    if (!ready) {                                                                   // wait: carry my cursor over
-        W.head[parity ^ 1][s] = hw;
-        W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = s;
+    if (!ready) {
+        // Has the partner's queue passed my entry?  Its lists are ascending by packet index and consumed front to back, so
+        // the entry for my packet p in the list of its packet o is gone iff that list's head is beyond p.  Then the partner
+        // found that the pair cannot hit wherever I am (may_meet): a miss for me too -- I walk on.
+        const uint32_t kq = o - co.p0, hq = kq ? (hwo >> 16) : (hwo & 0xFFFFu), nq = kq ? co.n1 : co.n0;
+        const bool passed = hq >= nq || p < ((kq ? co.l1 : co.l0)[hq].x & ICX_NB_INDEX_MASK);
+        uint32_t hn = hw;
+        if (passed) { int kind; uint32_t kk, oo; hn = skip_rejects_lane(W, c, cursor_advance(hw, k), n_dirty, kind, kk, oo); }
+        publish_cursor(W, s, c, hn, parity, ctr_out);                               // (not passed: wait, the cursor is carried over)
         return;
     }
     if (p > o) return;                                                              // the lower packet's lane acts for both
@@ -956,10 +1095,7 @@ __device__ __forceinline__ void round_execute(const DeviceWorld& W, uint4 item, 
                 k_run = kk; pa = min(p, oo); pb = max(p, oo); run = true;
                 break;
             }
-            if (lane == 0u) {
-                W.head[parity ^ 1][sb] = hw;
-                if (cursor_pending(c, hw)) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = sb;
-            }
+            if (lane == 0u) publish_cursor(W, sb, c, hw, parity, ctr_out);
             entered = false;
         }
         if (!run) break;
@@ -1004,8 +1140,7 @@ __device__ __forceinline__ void round_execute_lanes(const DeviceWorld& W, uint4 
                 k_run = kk; pa = min(p, oo); pb = max(p, oo); run = true;
                 break;
             }
-            W.head[parity ^ 1][sb] = hw;
-            if (cursor_pending(c, hw)) W.active[parity ^ 1][atomicAdd(&W.counters[ctr_out], 1u)] = sb;
+            publish_cursor(W, sb, c, hw, parity, ctr_out);
             entered = false;
         }
         if (!run) done = true;
@@ -1029,6 +1164,7 @@ __device__ __forceinline__ void trace_mark(const DeviceWorld& W, uint32_t& n, ui
 // the exact procedures).  So the first attempt is split over two cooperative launches with different shapes:
 // PHASE 0 = prepare (2 x 384 threads per SM), PHASE 1 = rounds (1 x 256 threads per SM, 251 registers) --
 // which also carries the whole loop for the rare restarts.
+#define ICX_MAX_ATTEMPTS 96u
 #ifndef ICX_LANE_MIN
 #define ICX_LANE_MIN 4u          // items per warp from which a round runs lane-parallel (break-even measured at ~4: the lane-parallel pass costs ~40 us flat, a warp-mode item ~19 us, a cursor walk ~9.5 us)
 #endif
@@ -1040,7 +1176,7 @@ __device__ __forceinline__ void trace_mark(const DeviceWorld& W, uint32_t& n, ui
 #define PREPARE_MINB 2
 #endif
 template <int PHASE>
-__device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, int do_euler, V3* scratch, uint2* sort_sm)
+__device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, int do_euler, V3* scratch)
 {
     uint32_t tn = 2;        // trace[0] = number of words used
     if (PHASE == 1 && W.trace) tn = (uint32_t)W.trace[0];
@@ -1048,58 +1184,56 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
     volatile uint32_t* ctr = W.counters;
     uint32_t attempts = 0, rounds = 0;
+    bool rebudget = false;
     if (PHASE != 1 && tid == 0) trace_mark(W, tn, 0u);
-    if (PHASE != 1) {   // Predict which clean bodies the replay will reach: a body that static resolution may push by up to
-        // push[a] (sum of the depths of its speculative contacts) reaches the candidates whose gap is smaller;
-        // those are replayed in order too and inherit the remainder of the push.  One warp per dirty body walks
-        // its candidate list, at most three generations.  Only a prediction: a body it misses triggers the
-        // restart further down.
-        // budgets of all bodies, then the movers' own candidates (see budget_entity / mover_walk_warp)
-        for (uint32_t e = tid; e < W.n_entities; e += nth) budget_entity(W, e);
-        grid.sync();
-        {
-            const uint32_t n_mov = min(ctr[CTR_MOVERS], W.n_entities);
-            const float x_max = __uint_as_float(ctr[CTR_XMAX]);
-            for (uint32_t m = tid >> 5; m < n_mov; m += (nth >> 5)) mover_walk_warp(W, W.mover_list[m], x_max);
-            if (tid == 0) trace_mark(W, tn, 0x80000u | min(n_mov, 0xFFFFu));
-        }
-        grid.sync();
+    if (PHASE != 1) {
+        // Predict how far static resolution may push each body, and with it which clean bodies the replay will reach.
+        // push[e] starts as the sum of the depths of e's speculative contacts (k_narrow).  A body pushed by up to p reaches
+        // the candidates whose gap is smaller and hands them the remainder, scaled by its share of the two masses (static
+        // resolution splits a penetration by inverse mass, collision_procedures.cpp:668-694); clean ones become dirty.
+        // Up to four passes over the candidate lists of the uniform margin.  Then budgets (bm = what the lists must cover),
+        // the movers' own wider candidates, and -- only if there are any -- the lists once more with those included.
+        // Only a prediction: a body it misses, or a budget that proves too small, restarts the replay further down.
         uint32_t done = 0;
-        for (int sweep = 0; sweep < 3; sweep++) {
+        for (int sweep = 0; sweep < 4; sweep++) {
             const uint32_t n_dirty = ctr[CTR_DIRTY];
-            if (n_dirty == done) break;                         // uniform: read after a grid barrier
-            lists_build(W, done, n_dirty, grid, tid, nth, sort_sm);
+            const uint32_t changed = sweep ? ctr[CTR_PUSHED] : 1u;
+            grid.sync();                                        // every thread has read the counters before thread 0 resets one
+            if (n_dirty == done && changed == 0u) break;        // uniform
+            if (tid == 0) { ctr[CTR_PUSHED] = 0u; __threadfence(); }
+            lists_build(W, done, n_dirty, grid, tid, nth, LISTS_PLAIN);
+            if (tid == 0) trace_mark(W, tn, 0x60000u | min(n_dirty - done, 0xFFFFu));
             grid.sync();
-            if (tid == 0) trace_mark(W, tn, 0x60000u | min(n_dirty - done, 0xFFFFu));      // lists of this sweep's bodies built
-            for (uint32_t sl = done + (tid >> 5); sl < n_dirty; sl += (nth >> 5)) {
-                const uint32_t e = W.dirty_list[sl];
-                const float pa = *(volatile float*)&W.push[e];
-                if (!(pa > 0.0f)) continue;
-                const uint32_t p0 = W.first_packet[e] & 0x3FFFFFFFu;
-                const uint32_t n0 = W.nbr_count[sl * 2u], n1 = W.nbr_count[sl * 2u + 1u];
-                for (uint32_t i = tid & 31u; i < n0 + n1; i += 32u) {
-                    const uint32_t k = i < n0 ? 0u : 1u;
-                    const uint2 en = W.nbr[(size_t)(sl * 2u + k) * W.max_neighbors + (k ? i - n0 : i)];
-                    const uint32_t entry = en.x;
-                    if (entry & ICX_NB_IMMUTABLE) continue;
-                    const uint32_t o = entry & ICX_NB_INDEX_MASK, eo = en.y;
-                    if (W.dirty_slot[eo] != ICX_NONE) continue;
-                    const uint32_t p = p0 + k;
-                    const int tP = __float_as_uint(W.pk_lpos[p].w) & PF_TYPE_MASK, tO = __float_as_uint(W.pk_lpos[o].w) & PF_TYPE_MASK;
-                    if (!is_sat_pair(tP, tO)) continue;
-                    float value;
-                    const float reach = 1.5f * pa + 0.02f * W.margin;
-                    const bool touching = sat_measure(W.pk_d + (size_t)p * 6, W.pk_d + (size_t)o * 6, v3(W.out.pos[e]), v3(W.out.pos[eo]), tP, tO, reach, value);
-                    if (touching || value < reach) {
-                        mark_dirty(W, eo);
-                        const float inherit = touching ? pa : pa - value;
-                        if (inherit > 0.0f) atomicMax((int*)&W.push[eo], __float_as_int(inherit));
-                    }
-                }
-            }
+            for (uint32_t sl = (tid >> 5); sl < n_dirty; sl += (nth >> 5)) predict_body_warp(W, sl, sl >= done);
             done = n_dirty;
             grid.sync();
             if (tid == 0) trace_mark(W, tn, 0x70000u | (uint32_t)sweep);                       // prediction sweep done
+        }
+        budgets_and_movers(W, grid, tid, nth);
+        if (tid == 0) trace_mark(W, tn, 0x80000u | min(ctr[CTR_MOVERS], 0xFFFFu));
+        if (ctr[CTR_MOVERS] != 0u) {                            // (uniform) the lists of the movers and of the bodies their extra candidates name,
+            const uint32_t n_dirty = ctr[CTR_DIRTY];            // again: now with those candidates and with the gaps may_meet prunes by
+            const uint32_t n_mov = min(ctr[CTR_MOVERS], W.n_entities), n_x = min(ctr[CTR_XPAIRS], W.max_xpairs);
+            grid.sync();
+            lists_build(W, done, n_dirty, grid, tid, nth, LISTS_PLAIN);     // (bodies the last prediction pass marked)
+            for (uint32_t s = tid; s < n_dirty; s += nth) W.slot_flag[s] = 0u;
+            grid.sync();
+            for (uint32_t m = tid; m < n_mov; m += nth) { const uint32_t s = W.dirty_slot[W.mover_list[m]]; if (s < n_dirty) W.slot_flag[s] = 1u; }
+            for (uint32_t i = tid; i < n_x; i += nth) {
+                const uint2 pr = W.xpairs[i];
+                if (!(pr.x & ICX_PAIR_A_IMMUT)) { const uint32_t s = W.dirty_slot[W.pk_entity[pr.x & ICX_NB_INDEX_MASK]]; if (s < n_dirty) W.slot_flag[s] = 1u; }
+                if (!(pr.y & ICX_PAIR_B_IMMUT)) { const uint32_t s = W.dirty_slot[W.pk_entity[pr.y & ICX_NB_INDEX_MASK]]; if (s < n_dirty) W.slot_flag[s] = 1u; }
+            }
+            grid.sync();
+            lists_build(W, 0u, n_dirty, grid, tid, nth, LISTS_FLAGGED);
+            grid.sync();
+            // ... and the clean bodies a mover can reach through them are replayed in order too
+            for (uint32_t m = (tid >> 5); m < n_mov; m += (nth >> 5)) {
+                const uint32_t sl = W.dirty_slot[W.mover_list[m]];
+                if (sl < n_dirty) predict_body_warp(W, sl, true);
+            }
+            done = n_dirty;
+            grid.sync();
         }
         if (tid == 0) ctr[CTR_LISTED] = done;
         grid.sync();
@@ -1109,7 +1243,12 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
         if (PHASE == 1 && attempts == 0) {                  // the prepare launch did all of this for the first attempt
             if (*(volatile uint32_t*)W.flags & RF_NEIGHBOR_OVERFLOW) break;
         } else {
-        lists_build(W, n_listed, n_dirty, grid, tid, nth, sort_sm);
+        if (rebudget) {                                     // (uniform) some body moved beyond its budget: new budgets, the movers walk again, all lists again
+            if (tid == 0) { ctr[CTR_MOVERS] = 0u; ctr[CTR_XPAIRS] = 0u; ctr[CTR_XMAX] = 0u; ctr[CTR_VIOLATORS] = 0u; ctr[CTR_POOL] = 0u; __threadfence(); }
+            grid.sync();
+            budgets_and_movers(W, grid, tid, nth);
+            lists_build(W, 0u, n_dirty, grid, tid, nth, LISTS_GAPS);
+        } else lists_build(W, n_listed, n_dirty, grid, tid, nth, LISTS_PLAIN);
         for (uint32_t s = tid; s < n_dirty; s += nth)
             if (attempts > 0 && s < n_listed) restore_body(W, W.dirty_list[s], dt, do_euler);
         if (tid == 0) trace_mark(W, tn, 0x10000u | min(n_dirty, 0xFFFFu));
@@ -1130,7 +1269,7 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
             const Cursor c = load_cursor(W, s);                                     // 32 bodies per warp hide it better than 32 entries of one body)
             int kind; uint32_t kk, oo;
             const uint32_t hw = skip_rejects_lane(W, c, 0u, n_dirty, kind, kk, oo);
-            W.head[0][s] = hw;
+            W.head[0][s] = hw; W.head[1][s] = hw;
             if (cursor_pending(c, hw)) W.active[0][atomicAdd(&W.counters[CTR_ACTIVE], 1u)] = s;   // writes head[0] / active[0]
         }
         grid.sync();
@@ -1143,6 +1282,7 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
             const uint32_t n_act = ctr[CTR_ACTIVE + rounds % 3u];
             const uint32_t grew = rounds ? ctr[CTR_NEWD + (rounds + 2u) % 3u] : 0u;    // written in the previous round only
             if ((n_act == 0u && !(rounds == 0u && n_static)) || grew != 0u) break;       // done, or the dirty set grew: restart at once
+            // (a body beyond its budget does not stop the attempt: finishing it catches the others of its kind in ONE restart)
             if (rounds >= ICX_MAX_ROUNDS) { if (tid == 0) atomicOr(W.flags, RF_ROUNDS_EXCEEDED); break; }
             const uint32_t ctr_out = CTR_ACTIVE + (rounds + 1u) % 3u, ctr_items = CTR_ITEMS + (rounds & 1u);
             if (tid == 0) { ctr[CTR_ACTIVE + (rounds + 2u) % 3u] = 0u; ctr[CTR_NEWD + (rounds + 1u) % 3u] = 0u; ctr[CTR_ITEMS + ((rounds + 1u) & 1u)] = 0u;
@@ -1175,8 +1315,11 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
             rounds++; parity ^= 1;
         }
         grid.sync();
-        if (ctr[CTR_DIRTY] == n_dirty || (*(volatile uint32_t*)W.flags & RF_ROUNDS_EXCEEDED)) break;
+        rebudget = ctr[CTR_VIOLATORS] != 0u;
+        if (tid == 0) { if (rebudget) ctr[CTR_NBUDGET] += 1u; if (ctr[CTR_DIRTY] != n_dirty) ctr[CTR_NGREW] += 1u; }
+        if ((ctr[CTR_DIRTY] == n_dirty && !rebudget) || (*(volatile uint32_t*)W.flags & RF_ROUNDS_EXCEEDED)) break;
         attempts++;
+        if (attempts > ICX_MAX_ATTEMPTS) { if (tid == 0) atomicOr(W.flags, RF_MARGIN_VIOLATED); break; }      // budgets do not settle: the host reports it
         grid.sync();
     }
     if (tid == 0) { ctr[CTR_ROUNDS] = rounds; ctr[CTR_ATTEMPTS] = attempts; trace_mark(W, tn, 0x40000u); if (W.trace) W.trace[0] = tn; }
@@ -1184,15 +1327,13 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
 
 __global__ void __launch_bounds__(PREPARE_TPB, PREPARE_MINB) k_resolve_prepare(const __grid_constant__ DeviceWorld W, double dt, int do_euler)
 {
-    __shared__ uint2 sort_all[PREPARE_TPB / 32][SORT_CAP];
-    resolve_body<0>(W, dt, do_euler, nullptr, sort_all[threadIdx.x >> 5]);
+    resolve_body<0>(W, dt, do_euler, nullptr);
 }
 __global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(const __grid_constant__ DeviceWorld W, double dt, int do_euler)
 {
     // per-warp scratch of the exact procedures (contact manifolds, clipping): see pseudo_clip_polyhedra_s
     __shared__ V3 scratch_all[RESOLVE_TPB / 32][8 + 2 * ICX_MAXV];
-    __shared__ uint2 sort_all[RESOLVE_TPB / 32][SORT_CAP];
-    resolve_body<1>(W, dt, do_euler, scratch_all[threadIdx.x >> 5], sort_all[threadIdx.x >> 5]);
+    resolve_body<1>(W, dt, do_euler, scratch_all[threadIdx.x >> 5]);
 }
 
 void launch_narrow(const DeviceWorld& W, int blocks, cudaStream_t st)

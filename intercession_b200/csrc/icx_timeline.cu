@@ -199,6 +199,13 @@ __global__ void __launch_bounds__(256) k_replay_pending(DeviceWorld W, IcxCollid
     }
 }
 
+// transport: the used part of a buffer's collider rows (count on the device), 16 bytes per thread
+__global__ void __launch_bounds__(256) k_copy_rows(uint4* __restrict__ dst, const uint4* __restrict__ src, const uint32_t* __restrict__ d_n, uint32_t room)
+{
+    const uint32_t words = min(*d_n, room) * (uint32_t)(sizeof(DeltaRow) / 16);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < words; i += gridDim.x * blockDim.x) dst[i] = src[i];
+}
+
 // ---- TMA helpers (1-D bulk copies, mbarrier completion) ----
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -708,7 +715,7 @@ int icx_timeline_slot_export(IcxTimeline* tl, uint16_t coherency, void* device_b
         TCK(cudaMemcpyAsync(&r, tl->d_delta_n + s, 4, cudaMemcpyDeviceToHost, st)); TCK(cudaStreamSynchronize(st));
         rows = std::min<uint32_t>(r, tl->delta_cap);
     }
-    const size_t dense = (size_t)n * ICX_SNAPSHOT_BYTES;
+    const size_t dense = ICX_SNAPSHOT_DENSE_BYTES(n);
     if (dense + ICX_SNAPSHOT_HEADER_BYTES + (size_t)rows * sizeof(DeltaRow) > capacity_bytes) { tl->error = "slot_export: buffer too small"; return ICX_E_CAPACITY; }
     char* out = (char*)device_buffer;
     if (n) {
@@ -725,7 +732,7 @@ int icx_timeline_slot_import(IcxTimeline* tl, uint16_t coherency, uint32_t n, co
 {
     if (!tl || (!device_buffer && n)) return ICX_E_INVALID;
     if (n > tl->n_max) { tl->error = "slot_import: more entities than the timeline holds"; return ICX_E_CAPACITY; }
-    const size_t dense = (size_t)n * ICX_SNAPSHOT_BYTES;
+    const size_t dense = ICX_SNAPSHOT_DENSE_BYTES(n);
     if (buffer_bytes < dense + ICX_SNAPSHOT_HEADER_BYTES) { tl->error = "slot_import: buffer shorter than the dense snapshot + header"; return ICX_E_INVALID; }
     const int s = slot_of(tl, coherency);
     cudaSetDevice(tl->device);
@@ -739,7 +746,8 @@ int icx_timeline_slot_import(IcxTimeline* tl, uint16_t coherency, uint32_t n, co
         TCK(cudaMemcpyAsync(slot_ids(tl, s), in + (size_t)n * 16 * TL_ARRAYS, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
     }
     TCK(cudaMemcpyAsync(tl->d_delta_n + s, in + dense, 4, cudaMemcpyDeviceToDevice, st));
-    if (room) TCK(cudaMemcpyAsync(tl->delta + (size_t)s * tl->delta_cap, in + dense + ICX_SNAPSHOT_HEADER_BYTES, (size_t)room * sizeof(DeltaRow), cudaMemcpyDeviceToDevice, st));
+    if (room) k_copy_rows<<<std::min<int>(tl->sms * 2, (int)((room * 11u + 255u) / 256u)), 256, 0, st>>>(
+                  (uint4*)(tl->delta + (size_t)s * tl->delta_cap), (const uint4*)(in + dense + ICX_SNAPSHOT_HEADER_BYTES), tl->d_delta_n + s, room);
     TCK(cudaEventRecord(tl->slot_ev[s], st));
     tl->delta_n[s] = room ? -1 : 0;
     tl->stamp[s] = coherency; tl->valid[s] = 1; tl->count[s] = n; tl->seq[s] = tl->next_seq++;

@@ -47,7 +47,7 @@ enum : uint32_t {
 
 // error / retry flags raised by kernels (World::d_flags)
 enum : uint32_t {
-    RF_NEIGHBOR_OVERFLOW = 1u << 0,   // a candidate list exceeded max_neighbors
+    RF_NEIGHBOR_OVERFLOW = 1u << 0,   // the candidate-list pool is full (or one list has more than 65535 entries)
     RF_MARGIN_VIOLATED   = 1u << 1,   // static resolution moved a body further than the margin
     RF_CELL_TOO_SMALL    = 1u << 2,   // a mutable collider is larger than a grid cell
     RF_CONTACT_OVERFLOW  = 1u << 3,
@@ -105,7 +105,8 @@ struct DeviceWorld {
     uint32_t* large_list;           // packets larger than a cell (immutable only)
     // flat candidate pair list (the broadphase output, icx_pairs_fetch)
     uint2* pairs; uint32_t max_pairs;
-    float* push;                    // per entity: predicted displacement by static resolution this tick
+    float* push;                    // per entity: largest single predicted push by static resolution this tick (own contacts, or handed on by a neighbour)
+    float4* pushv;                  // per entity: vector sum of the predicted pushes of its own speculative contacts
     // Per-body displacement budget (DESIGN.md "Broadphase bound"): the stored bounds are inflated by the uniform `margin`;
     // a body the speculative pass predicts to be pushed further, or that was caught moving further, gets bm[e] > margin and is
     // a MOVER: its extra candidates (xpairs) come from a wide grid walk of its own, nobody else pays for it.
@@ -119,10 +120,13 @@ struct DeviceWorld {
     // bodies touched by at least one hit ("dirty"): only these need the reference's sequential order
     uint32_t* dirty_slot;           // per entity: index into dirty_list, ICX_NONE = clean
     uint32_t* dirty_list;           // entity indices, arbitrary order
-    uint2* nbr;                     // sorted candidate lists of dirty bodies: nbr[(slot * 2 + k) * max_neighbors + i] = {other packet | flags, its entity}
-    uint32_t* nbr_count;            // [slot * 2 + k]
-    uint4* slot_info;               // per dirty slot: {first packet | count << 30, n0, n1, entity}
-    uint32_t max_neighbors;
+    uint2* nbr;                     // pool of sorted candidate lists of the dirty bodies (bump-allocated per tick, CTR_POOL): entry = {other packet | flags, its entity}
+    uint32_t* nbr_count;            // [slot * 2 + k] entries of the list being built
+    uint32_t* nbr_fill;             // [slot * 2 + k] fill cursor while the list is written
+    uint32_t* slot_flag;            // per dirty slot: list to be rebuilt with the movers' candidates
+    uint4* slot_info;               // per dirty slot: {first packet | count << 30, n0 | n1 << 16, pool offset of list 0 (list 1 follows), entity}
+    uint32_t max_neighbors;         // pool capacity per entity (pool = max_neighbors * capacity in entities)
+    uint32_t max_nbr;               // pool capacity in entries
     uint32_t* head[2];              // per dirty slot: consumed entries of the slot-0 list | slot-1 list << 16
     uint32_t* active[2];            // dirty-slot work lists of the dependency rounds
     uint4* items;                   // per round: pairs that need the exact procedure {pa, pb, slot a, slot b | ICX_NONE}
@@ -150,7 +154,10 @@ enum { CTR_LARGE = 0, CTR_DIRTY = 1, CTR_CONTACTS = 2, CTR_INTERCEPTS = 3, CTR_C
        CTR_FETCH = 23,          // 2 alternating work-item fetch counters
        CTR_MOVERS = 25, CTR_XPAIRS = 26,
        CTR_XMAX = 27,           // float bits: largest (bm - margin) of this tick
-       CTR_VIOLATORS = 28,      // bodies that moved beyond their budget (diagnostic)
+       CTR_VIOLATORS = 28,      // bodies the current attempt moved beyond their budget
+       CTR_POOL = 29,           // entries of the list pool in use
+       CTR_NGREW = 30, CTR_NBUDGET = 31,   // restarts of the replay by reason (diagnostic)
+       CTR_PUSHED = 16,         // predicted pushes raised by the current prediction pass
        CTR_PROF = 32,           // ICX_PROFILE_PAIR builds: cycle accumulators
        CTR_TOTAL = 48 };
 #define ICX_MAX_ROUNDS 65535u

@@ -47,7 +47,8 @@ def past_ids(ids, steps=1):
     return ids
 
 
-DELTA_ROWS = 256        # changed ColliderComponents a transport buffer has room for per tick
+DELTA_ROWS = None       # changed ColliderComponents a transport buffer has room for per tick; None = every entity (the first record of a
+                        # ring, and the one after a parallel cycle wrote into the timeslice, carry all of them)
 
 
 class LoopbackLink:
@@ -55,7 +56,7 @@ class LoopbackLink:
 
     def __init__(self, n_entities, device=0, rows=DELTA_ROWS):
         import torch
-        self.buf = torch.empty(abi.snapshot_capacity(max(n_entities, 1), rows), dtype=torch.uint8, device=torch.device("cuda", device))
+        self.buf = torch.empty(abi.snapshot_capacity(max(n_entities, 1), n_entities if rows is None else rows), dtype=torch.uint8, device=torch.device("cuda", device))
         self.pending = None
 
     def ptr(self):
@@ -146,7 +147,7 @@ def run_distributed(ts, ticks, rank, n_ranks, device, dt=DT, rows=DELTA_ROWS):
     import torch
     import torch.distributed as dist
     dev = torch.device("cuda", device)
-    nbytes = abi.snapshot_capacity(max(ts.scene.n, 1), rows)
+    nbytes = abi.snapshot_capacity(max(ts.scene.n, 1), ts.scene.n if rows is None else rows)
     out = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     inp = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     st = torch.cuda.current_stream(dev).cuda_stream

@@ -77,6 +77,16 @@ class World:
         index = np.ascontiguousarray(index, np.uint32)
         self._ck(self.lib.icx_bodies_update(self.handle, len(index), abi.ptr(index), abi.ptr(T), abi.ptr(P), abi.ptr(Cc)))
 
+    def update_all(self, T=None, P=None):
+        """Transform / physics of every entity (what the synchros resubmit each frame); colliders stay resident."""
+        self._ck(self.lib.icx_bodies_update(self.handle, self.n, None, abi.ptr(T), abi.ptr(P), None))
+
+    def motion_download(self, out=None):
+        """The 76 B per entity a tick writes (origin, orientation, velocity, acceleration, angular velocity / acceleration)."""
+        out = np.zeros(self.n, abi.motion_dt) if out is None else out
+        self._ck(self.lib.icx_motion_download(self.handle, self.n, abi.ptr(out)))
+        return out
+
     # ---- PhysicsDynamo::run_relays ----
     def step(self, dt=1.0 / 45, n=1):
         self._ck(self.lib.icx_step_n(self.handle, dt, n) if n != 1 else self.lib.icx_step(self.handle, dt))
@@ -180,6 +190,12 @@ class World:
         self._ck(self.lib.icx_phase_ms(self.handle, ms, C.byref(nt), C.byref(nl)))
         names = ("integrate_prep", "grid_sort", "pairs", "narrow", "resolve")
         return dict(zip(names, list(ms))), nt.value, nl.value
+
+    def totals(self):
+        """Sums over the ticks since profile(): ticks, candidate pairs, contacts, rounds, attempts, dirty bodies."""
+        out = (C.c_uint64 * 6)()
+        self._ck(self.lib.icx_totals_fetch(self.handle, out))
+        return dict(zip(("ticks", "candidates", "contacts", "rounds", "attempts", "dirty"), [int(v) for v in out]))
 
     def trace(self, enable=True):
         """Device timeline of the last ordered resolve: list of (ns since its start, tag)."""

@@ -67,13 +67,14 @@ def test_middle_timeslice_forwards_what_it_replayed(built):
     inject_at = slices[0].w.coherency() + 3
     idx = np.array([10, 50, 90], np.uint32)
     marker = np.float32(123.5)
-    seen = {}
+    seen, before = {}, {}
 
     def on_tick(t, phase):
         if phase == "replayed":
             w0 = slices[0].w
             if w0.coherency() == inject_at:                       # external edit on the future-most timeslice, before it records
                 cur = w0.download(slices[0].scene)
+                before["T"] = cur.T.copy()
                 P = np.ascontiguousarray(cur.P[idx]); P["linearDrag"] = marker
                 T = np.ascontiguousarray(cur.T[idx]); T["scale"] *= np.float32(1.25)
                 w0.update(idx, T=T, P=P)
@@ -82,11 +83,12 @@ def test_middle_timeslice_forwards_what_it_replayed(built):
     try:
         pipeline.run_local(slices, 3 + 2 * delay + 3, links, on_tick=on_tick)
         got = seen[(2, inject_at)]                                # timeslice 2 right after ITS replay at that coherency
-        src = seen[(0, inject_at)]                                # (captured before the injection: compare with the recorded state)
+        src = seen[(0, inject_at)]                                # timeslice 0 right after the injection
         assert np.all(got.P["linearDrag"][idx] == marker)
         mid = seen[(1, inject_at)]
         assert np.all(mid.P["linearDrag"][idx] == marker)
-        assert np.array_equal(got.T["scale"][idx], mid.T["scale"][idx]) and not np.array_equal(got.T["scale"][idx], src.T["scale"][idx])
+        assert np.array_equal(got.T["scale"][idx], mid.T["scale"][idx]) and np.array_equal(got.T["scale"][idx], src.T["scale"][idx])
+        assert not np.array_equal(got.T["scale"][idx], before["T"]["scale"][idx])
     finally:
         for ts in slices:
             ts.close()
@@ -98,7 +100,7 @@ def test_slot_export_import_roundtrip(built):
     with world.World(s.n) as a, world.World(s.n) as b, world.Timeline(4, s.n) as ta, world.Timeline(6, s.n + 10) as tb:
         a.upload(s); a.step(1 / 45, 2)
         a.record(ta, 9); a.sync()
-        buf = torch.empty(abi.snapshot_capacity(s.n, 8), dtype=torch.uint8, device="cuda")
+        buf = torch.empty(abi.snapshot_capacity(s.n, s.n), dtype=torch.uint8, device="cuda")      # the first record of a ring carries every collider row
         assert ta.export_slot(9, buf.data_ptr(), buf.numel()) == s.n
         with pytest.raises(world.IcxError):
             ta.export_slot(8, buf.data_ptr(), buf.numel())        # nothing recorded with that stamp

@@ -33,8 +33,11 @@ def evolve(s, k, prev=None):
     """State of the future timeslice at tick k: EVERY field of Transform / Physics / ColliderComponent that a tick, a
     behaviour (biped_behaviors.h:96-100 restLength / damping, projectile_behaviors.h:38 scale) or a host edit may change
     differs from the past's copy, so a replay that restores less than the reference's (all components,
-    server_network_dynamo.cpp:408-412) cannot pass."""
+    server_network_dynamo.cpp:408-412) cannot pass.  prev: the state of tick k - 1, whose collider edits persist (a world keeps
+    what it was told)."""
     out = s.copy()
+    if prev is not None:
+        out["C"] = prev.C.copy()
     f = np.float32
     out.T["origin"] += f(0.125 * k)
     out.T["scale"] *= f(1.0 + 0.02 * (k % 7))

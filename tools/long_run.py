@@ -36,7 +36,12 @@ while done < ticks:
            "phases_ms": {p: round((ph[p] - prev[p]) / k, 4) for p in ph},
            "candidates": st.n_candidates, "dirty": st.n_dirty, "contacts": st.n_contacts, "rounds": st.n_rounds,
            "attempts": st.n_attempts, "retries": st.n_retries, "margin": round(st.margin, 4), "cell": round(st.cell_size, 4),
-           "max_neighbors": st.max_neighbors}
+           "max_neighbors": st.max_neighbors, "movers": st.n_movers}
+    import ctypes
+    import numpy as np
+    cn = np.zeros(48, np.uint32)
+    w.lib.icx_debug_counters(w.handle, cn.ctypes.data_as(ctypes.c_void_p))
+    row["restarts_grew"], row["restarts_budget"], row["xpairs"], row["xmax"], row["pool"] = int(cn[30]), int(cn[31]), int(cn[26]), round(float(cn[27:28].view(np.float32)[0]), 3), int(cn[29])
     prev = dict(ph)
     rows.append(row)
     print(json.dumps(row), flush=True)
