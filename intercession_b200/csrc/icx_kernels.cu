@@ -35,6 +35,7 @@ __global__ void __launch_bounds__(256) k_integrate_prep(DeviceWorld W, double de
     W.pos0[e] = r.pos;
     W.dirty_slot[e] = ICX_NONE;
     W.push[e] = 0.0f; W.pushv[e] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    W.bm[e] = W.margin;                                 // displacement budget: the uniform margin unless the ordered pass decides otherwise (budget_entity)
     { const float k = W.bm_keep[e]; if (k > 0.0f) { const float d = k * 0.85f; W.bm_keep[e] = d > W.margin ? d : 0.0f; } }   // the carried budget floor fades
 
     // ---- per-collider derivation (ColliderSynchro::update + what every later pair test needs) ----

@@ -689,9 +689,10 @@ static __device__ __noinline__ void mover_walk_warp(const DeviceWorld& W, uint32
 // sorts (lists of up to 32 entries in registers, longer ones by ranking into a fresh pool region).
 // mode of a list build: plain entries; entries with the gap between the shapes (may_meet); or the same for the flagged slots only
 enum { LISTS_PLAIN = 0, LISTS_GAPS = 1, LISTS_FLAGGED = 2 };
-__device__ __forceinline__ bool slot_wanted(const DeviceWorld& W, uint32_t s, uint32_t first, uint32_t n_dirty, int mode)
+__device__ __forceinline__ bool slot_wanted(const DeviceWorld& W, uint32_t s, uint32_t first, uint32_t n_dirty, int mode, uint32_t always_from)
 {
-    return s >= first && s < n_dirty && (mode != LISTS_FLAGGED || W.slot_flag[s] != 0u);   // s = ICX_NONE (clean) fails the range test
+    // s = ICX_NONE (clean) fails the range test; in LISTS_FLAGGED mode the slots from always_from on have no list yet and are wanted too
+    return s >= first && s < n_dirty && (mode != LISTS_FLAGGED || s >= always_from || W.slot_flag[s] != 0u);
 }
 __device__ __forceinline__ void list_visit(const DeviceWorld& W, uint32_t s, uint32_t e, uint32_t p, uint32_t other, uint32_t eo, bool o_immut, bool fill, uint32_t gapq)
 {
@@ -751,12 +752,13 @@ static __device__ __noinline__ void sort_lists_warp(const DeviceWorld& W, uint32
     if (lane == 0 && new_off != info.z) { info.z = new_off; W.slot_info[slot] = info; }
 }
 
-// Budgets of all bodies (a body an earlier attempt caught beyond its budget first gets its carried floor raised), then the
-// movers' own candidates.  Called by every thread of the grid; ends behind a grid barrier.
+// Budgets of the dirty bodies (a body an earlier attempt caught beyond its budget first gets its carried floor raised), then
+// the movers' own candidates.  Called by every thread of the grid; ends behind a grid barrier.
 template <typename Grid>
-__device__ __forceinline__ void budgets_and_movers(const DeviceWorld& W, Grid& grid, uint32_t tid, uint32_t nth)
+__device__ __forceinline__ void budgets_and_movers(const DeviceWorld& W, Grid& grid, uint32_t tid, uint32_t nth, uint32_t n_dirty)
 {
-    for (uint32_t e = tid; e < W.n_entities; e += nth) {
+    for (uint32_t s = tid; s < n_dirty; s += nth) {             // clean bodies keep the uniform margin (k_integrate_prep)
+        const uint32_t e = W.dirty_list[s];
         const uint32_t need = W.bm_need[e];
         if (need) { W.bm_need[e] = 0u; W.bm_keep[e] = fmaxf(W.bm_keep[e], __uint_as_float(need) * 2.0f + 0.02f); }
         budget_entity(W, e);
@@ -769,10 +771,10 @@ __device__ __forceinline__ void budgets_and_movers(const DeviceWorld& W, Grid& g
 }
 
 template <typename Grid>
-__device__ __forceinline__ void lists_build(const DeviceWorld& W, uint32_t first, uint32_t n_dirty, Grid& grid, uint32_t tid, uint32_t nth, int mode)
+__device__ __forceinline__ void lists_build(const DeviceWorld& W, uint32_t first, uint32_t n_dirty, Grid& grid, uint32_t tid, uint32_t nth, int mode, uint32_t always_from)
 {
     if (first >= n_dirty) return;                                                   // uniform
-    for (uint32_t s = first + tid; s < n_dirty; s += nth) if (slot_wanted(W, s, first, n_dirty, mode)) { W.nbr_count[s * 2u] = 0u; W.nbr_count[s * 2u + 1u] = 0u; }
+    for (uint32_t s = first + tid; s < n_dirty; s += nth) if (slot_wanted(W, s, first, n_dirty, mode, always_from)) { W.nbr_count[s * 2u] = 0u; W.nbr_count[s * 2u + 1u] = 0u; }
     grid.sync();
     const uint32_t n_pairs = min(*(volatile uint32_t*)&W.counters[CTR_CANDIDATES], W.max_pairs);
     const uint32_t n_x = min(*(volatile uint32_t*)&W.counters[CTR_XPAIRS], W.max_xpairs);
@@ -784,7 +786,7 @@ __device__ __forceinline__ void lists_build(const DeviceWorld& W, uint32_t first
             if (ia && ib) continue;
             const uint32_t ea = W.pk_entity[pa], eb = W.pk_entity[pb];
             const uint32_t sa = ia ? ICX_NONE : W.dirty_slot[ea], sb = ib ? ICX_NONE : W.dirty_slot[eb];
-            const bool wa = slot_wanted(W, sa, first, n_dirty, mode), wb = slot_wanted(W, sb, first, n_dirty, mode);
+            const bool wa = slot_wanted(W, sa, first, n_dirty, mode, always_from), wb = slot_wanted(W, sb, first, n_dirty, mode, always_from);
             if (!wa && !wb) continue;
             uint32_t gapq = 0u;
             if (fill && mode != LISTS_PLAIN && !ia && !ib) gapq = gap_of(W, pa, pb, ea, eb);   // both can move: how far apart are they (may_meet)?
@@ -794,7 +796,7 @@ __device__ __forceinline__ void lists_build(const DeviceWorld& W, uint32_t first
         grid.sync();
         if (fill) break;
         for (uint32_t s = first + tid; s < n_dirty; s += nth) {                     // allocation
-            if (!slot_wanted(W, s, first, n_dirty, mode)) continue;
+            if (!slot_wanted(W, s, first, n_dirty, mode, always_from)) continue;
             const uint32_t c0 = W.nbr_count[s * 2u], c1 = W.nbr_count[s * 2u + 1u];
             uint32_t off = ICX_NONE;
             if (c0 <= 0xFFFFu && c1 <= 0xFFFFu) { off = atomicAdd(&W.counters[CTR_POOL], c0 + c1); if (off + c0 + c1 > W.max_nbr) off = ICX_NONE; }
@@ -805,7 +807,7 @@ __device__ __forceinline__ void lists_build(const DeviceWorld& W, uint32_t first
         }
         grid.sync();
     }
-    for (uint32_t s = first + (tid >> 5); s < n_dirty; s += (nth >> 5)) if (slot_wanted(W, s, first, n_dirty, mode)) sort_lists_warp(W, s);
+    for (uint32_t s = first + (tid >> 5); s < n_dirty; s += (nth >> 5)) if (slot_wanted(W, s, first, n_dirty, mode, always_from)) sort_lists_warp(W, s);
 }
 
 // Put a dirty body back to its post-integration state (bit-identical recomputation from the tick input).
@@ -1195,13 +1197,14 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
         // the movers' own wider candidates, and -- only if there are any -- the lists once more with those included.
         // Only a prediction: a body it misses, or a budget that proves too small, restarts the replay further down.
         uint32_t done = 0;
-        for (int sweep = 0; sweep < 4; sweep++) {
+        for (int sweep = 0; sweep < 3; sweep++) {
             const uint32_t n_dirty = ctr[CTR_DIRTY];
             const uint32_t changed = sweep ? ctr[CTR_PUSHED] : 1u;
             grid.sync();                                        // every thread has read the counters before thread 0 resets one
-            if (n_dirty == done && changed == 0u) break;        // uniform
+            // another pass only if it matters: many new bodies to list, or many pushes handed on (uniform)
+            if (sweep && (n_dirty - done) * 50u < n_dirty && changed * 100u < n_dirty) break;
             if (tid == 0) { ctr[CTR_PUSHED] = 0u; __threadfence(); }
-            lists_build(W, done, n_dirty, grid, tid, nth, LISTS_PLAIN);
+            lists_build(W, done, n_dirty, grid, tid, nth, LISTS_PLAIN, 0u);
             if (tid == 0) trace_mark(W, tn, 0x60000u | min(n_dirty - done, 0xFFFFu));
             grid.sync();
             for (uint32_t sl = (tid >> 5); sl < n_dirty; sl += (nth >> 5)) predict_body_warp(W, sl, sl >= done);
@@ -1209,31 +1212,31 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
             grid.sync();
             if (tid == 0) trace_mark(W, tn, 0x70000u | (uint32_t)sweep);                       // prediction sweep done
         }
-        budgets_and_movers(W, grid, tid, nth);
-        if (tid == 0) trace_mark(W, tn, 0x80000u | min(ctr[CTR_MOVERS], 0xFFFFu));
-        if (ctr[CTR_MOVERS] != 0u) {                            // (uniform) the lists of the movers and of the bodies their extra candidates name,
-            const uint32_t n_dirty = ctr[CTR_DIRTY];            // again: now with those candidates and with the gaps may_meet prunes by
+        {
+            const uint32_t n_dirty = ctr[CTR_DIRTY];
+            budgets_and_movers(W, grid, tid, nth, n_dirty);
+            if (tid == 0) trace_mark(W, tn, 0x80000u | min(ctr[CTR_MOVERS], 0xFFFFu));
             const uint32_t n_mov = min(ctr[CTR_MOVERS], W.n_entities), n_x = min(ctr[CTR_XPAIRS], W.max_xpairs);
-            grid.sync();
-            lists_build(W, done, n_dirty, grid, tid, nth, LISTS_PLAIN);     // (bodies the last prediction pass marked)
-            for (uint32_t s = tid; s < n_dirty; s += nth) W.slot_flag[s] = 0u;
-            grid.sync();
-            for (uint32_t m = tid; m < n_mov; m += nth) { const uint32_t s = W.dirty_slot[W.mover_list[m]]; if (s < n_dirty) W.slot_flag[s] = 1u; }
-            for (uint32_t i = tid; i < n_x; i += nth) {
-                const uint2 pr = W.xpairs[i];
-                if (!(pr.x & ICX_PAIR_A_IMMUT)) { const uint32_t s = W.dirty_slot[W.pk_entity[pr.x & ICX_NB_INDEX_MASK]]; if (s < n_dirty) W.slot_flag[s] = 1u; }
-                if (!(pr.y & ICX_PAIR_B_IMMUT)) { const uint32_t s = W.dirty_slot[W.pk_entity[pr.y & ICX_NB_INDEX_MASK]]; if (s < n_dirty) W.slot_flag[s] = 1u; }
+            if (n_mov != 0u) {                                  // (uniform) the lists of the movers and of the bodies their extra candidates name
+                for (uint32_t s = tid; s < n_dirty; s += nth) W.slot_flag[s] = 0u;      // again, now with those candidates and with the gaps may_meet prunes by
+                grid.sync();
+                for (uint32_t m = tid; m < n_mov; m += nth) { const uint32_t s = W.dirty_slot[W.mover_list[m]]; if (s < n_dirty) W.slot_flag[s] = 1u; }
+                for (uint32_t i = tid; i < n_x; i += nth) {
+                    const uint2 pr = W.xpairs[i];
+                    if (!(pr.x & ICX_PAIR_A_IMMUT)) { const uint32_t s = W.dirty_slot[W.pk_entity[pr.x & ICX_NB_INDEX_MASK]]; if (s < n_dirty) W.slot_flag[s] = 1u; }
+                    if (!(pr.y & ICX_PAIR_B_IMMUT)) { const uint32_t s = W.dirty_slot[W.pk_entity[pr.y & ICX_NB_INDEX_MASK]]; if (s < n_dirty) W.slot_flag[s] = 1u; }
+                }
+                grid.sync();
+                lists_build(W, 0u, n_dirty, grid, tid, nth, LISTS_FLAGGED, done);      // (+ plain lists of the bodies the last pass marked: slots >= done)
+                grid.sync();
+                // ... and the clean bodies a mover can reach through them are replayed in order too
+                for (uint32_t m = (tid >> 5); m < n_mov; m += (nth >> 5)) {
+                    const uint32_t sl = W.dirty_slot[W.mover_list[m]];
+                    if (sl < n_dirty) predict_body_warp(W, sl, true);
+                }
+                done = n_dirty;
+                grid.sync();
             }
-            grid.sync();
-            lists_build(W, 0u, n_dirty, grid, tid, nth, LISTS_FLAGGED);
-            grid.sync();
-            // ... and the clean bodies a mover can reach through them are replayed in order too
-            for (uint32_t m = (tid >> 5); m < n_mov; m += (nth >> 5)) {
-                const uint32_t sl = W.dirty_slot[W.mover_list[m]];
-                if (sl < n_dirty) predict_body_warp(W, sl, true);
-            }
-            done = n_dirty;
-            grid.sync();
         }
         if (tid == 0) ctr[CTR_LISTED] = done;
         grid.sync();
@@ -1246,9 +1249,9 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
         if (rebudget) {                                     // (uniform) some body moved beyond its budget: new budgets, the movers walk again, all lists again
             if (tid == 0) { ctr[CTR_MOVERS] = 0u; ctr[CTR_XPAIRS] = 0u; ctr[CTR_XMAX] = 0u; ctr[CTR_VIOLATORS] = 0u; ctr[CTR_POOL] = 0u; __threadfence(); }
             grid.sync();
-            budgets_and_movers(W, grid, tid, nth);
-            lists_build(W, 0u, n_dirty, grid, tid, nth, LISTS_GAPS);
-        } else lists_build(W, n_listed, n_dirty, grid, tid, nth, LISTS_PLAIN);
+            budgets_and_movers(W, grid, tid, nth, n_dirty);
+            lists_build(W, 0u, n_dirty, grid, tid, nth, LISTS_GAPS, 0u);
+        } else lists_build(W, n_listed, n_dirty, grid, tid, nth, LISTS_PLAIN, 0u);
         for (uint32_t s = tid; s < n_dirty; s += nth)
             if (attempts > 0 && s < n_listed) restore_body(W, W.dirty_list[s], dt, do_euler);
         if (tid == 0) trace_mark(W, tn, 0x10000u | min(n_dirty, 0xFFFFu));

@@ -174,14 +174,16 @@ __device__ __forceinline__ void apply_collider_row(const DeviceWorld& W, IcxColl
 __global__ void __launch_bounds__(128) k_replay_delta(DeviceWorld W, IcxColliderComponent* __restrict__ MC, const DeltaRow* __restrict__ rows,
                                                       const uint32_t* __restrict__ d_n, uint32_t cap, uint32_t epoch,
                                                       IcxColliderComponent* __restrict__ pend_rows, uint8_t* __restrict__ pend_flag,
-                                                      unsigned long long* __restrict__ mismatch)
+                                                      unsigned long long* __restrict__ mismatch, int keep_all)
 {
     const uint32_t n = min(*d_n, cap);
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const uint32_t e = rows[i].idx;
         if (e >= W.n_entities) { atomicAdd(mismatch, 1ull); continue; }
         const uint32_t state = W.in.ts[e] & 0xFFu;
-        if (state == ICX_TS_FORKING || state == ICX_TS_FORKED) { pend_rows[e] = rows[i].C; pend_flag[e] = 1; continue; }
+        // keep_all: the record itself is dropped as stale (server_network_dynamo.cpp:391), but the NEXT record the entity takes
+        // carries this row unchanged (every record holds every component): kept until then
+        if (keep_all || state == ICX_TS_FORKING || state == ICX_TS_FORKED) { pend_rows[e] = rows[i].C; pend_flag[e] = 1; continue; }
         pend_flag[e] = 0;
         apply_collider_row(W, MC, e, rows[i].C, epoch, mismatch);
     }
@@ -542,7 +544,7 @@ int icx_replay(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, int mode, int* 
     // the relay then drops those with `coherency < now` -- a PLAIN integer compare (server_network_dynamo.cpp:391), so across
     // the uint16 wrap an older record (65535 with now = 2) is still deserialised, before the current one.  pop_front stops at
     // the breakpoint; pop_at_breakpoint only takes what lies behind it.
-    std::vector<int> use;
+    std::vector<int> popped;
     for (uint32_t k = 0; k < tl->depth; k++) {
         if (!tl->valid[k]) continue;
         const uint16_t a = coherency, b = tl->stamp[k];
@@ -551,40 +553,46 @@ int icx_replay(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, int mode, int* 
         const bool behind = tl->breakpoint_active && tl->behind[k];
         if (mode == ICX_REPLAY_SERVER ? behind : !behind) continue;
         tl->valid[k] = 0; tl->behind[k] = 0;
-        if (!(b < coherency)) use.push_back((int)k);
+        popped.push_back((int)k);
     }
-    if (use.empty() || mode == ICX_REPLAY_PARALLEL) return ICX_OK;          // parallel_network_dynamo.cpp:78-86: upstream components only
-    std::sort(use.begin(), use.end(), [&](int x, int y) { return tl->seq[x] < tl->seq[y]; });
+    if (popped.empty() || mode == ICX_REPLAY_PARALLEL) return ICX_OK;       // parallel_network_dynamo.cpp:78-86: upstream components only
+    std::sort(popped.begin(), popped.end(), [&](int x, int y) { return tl->seq[x] < tl->seq[y]; });
+    int last = -1;                                                          // position of the newest record that is not dropped as stale
+    for (size_t i = 0; i < popped.size(); i++) if (!(tl->stamp[popped[i]] < coherency)) last = (int)i;
     const uint32_t n = w->n_entities;
     if (!n) return ICX_OK;
     cudaSetDevice(w->device);
     cudaStream_t st = w->stream;
-    const int last = use.back();
-    const uint32_t n_src = tl->count[last];
-    if (!n_src) return ICX_OK;
+    const uint32_t n_src = last >= 0 ? tl->count[popped[last]] : n;
+    if (last >= 0 && !n_src) return ICX_OK;
     if (n_src != n && !(w->W.worldline_stride && n_src == w->W.worldline_stride)) { tl->error = "replay: record size matches neither the world nor one world-line"; return ICX_E_INVALID; }
-    for (int k : use) TCK(cudaStreamWaitEvent(st, tl->slot_ev[k], 0));
-    // collider rows first (every popped record in order), then the dense part of the newest: each overwrites everything
+    for (int k : popped) TCK(cudaStreamWaitEvent(st, tl->slot_ev[k], 0));
+    // Collider rows first, oldest record first.  The reference's records repeat every component, so the record that is applied
+    // in the end carries the rows of ALL earlier ones: rows of records dropped as stale are applied too (when an applied record
+    // follows in this very replay) or kept for the next record the entity takes (when none does).
     bool rows_any = false;
-    for (int k : use) rows_any |= tl->delta_n[k] != 0;
-    if (w->have_C && n_src == n && (rows_any || w->pend_any)) {
+    for (int k : popped) rows_any |= tl->delta_n[k] != 0;
+    if (w->have_C && n_src == n && (rows_any || (w->pend_any && last >= 0))) {
         int rc = ensure_pending(w, tl); if (rc != ICX_OK) return rc;
         const uint32_t epoch = ++w->c_epoch;
         IcxColliderComponent* MC = (IcxColliderComponent*)w->mir_C.ptr;
-        if (w->pend_any) k_replay_pending<<<stream_blocks(tl, n, 8), 256, 0, st>>>(w->W, MC, epoch, (const IcxColliderComponent*)w->pend_rows.ptr,
-                                                                                 (uint8_t*)w->pend_flag.ptr, tl->d_mismatch);
-        for (int k : use) {
+        if (w->pend_any && last >= 0) k_replay_pending<<<stream_blocks(tl, n, 8), 256, 0, st>>>(w->W, MC, epoch, (const IcxColliderComponent*)w->pend_rows.ptr,
+                                                                                              (uint8_t*)w->pend_flag.ptr, tl->d_mismatch);
+        for (size_t i = 0; i < popped.size(); i++) {
+            const int k = popped[i];
             if (tl->delta_n[k] == 0) continue;
             const uint32_t guess = tl->delta_n[k] > 0 ? (uint32_t)tl->delta_n[k] : tl->delta_cap;
             k_replay_delta<<<std::max(1, std::min<int>((int)((guess + 127) / 128), tl->sms * 4)), 128, 0, st>>>(
                 w->W, MC, tl->delta + (size_t)k * tl->delta_cap, tl->d_delta_n + k, tl->delta_cap, epoch,
-                (IcxColliderComponent*)w->pend_rows.ptr, (uint8_t*)w->pend_flag.ptr, tl->d_mismatch);
-            w->pend_any = true;         // a row may have met a divergent entity (conservative: costs one flag pass per replay)
+                (IcxColliderComponent*)w->pend_rows.ptr, (uint8_t*)w->pend_flag.ptr, tl->d_mismatch, (int)i > last ? 1 : 0);
+            w->pend_any = true;         // a row may have been kept (conservative: costs one flag pass per replay)
         }
         TCK(cudaGetLastError());
     }
+    if (last < 0) return ICX_OK;                                            // every popped record was stale
+    const int last_slot = popped[last];
     if (tl->profile) cudaEventRecord(tl->pev[1][0], st);
-    k_replay<<<stream_blocks(tl, n, 16), 256, 0, st>>>(w->W, slot_state(tl, last), slot_ids(tl, last), n, n_src, tl->n_max, tl->d_mismatch);
+    k_replay<<<stream_blocks(tl, n, 16), 256, 0, st>>>(w->W, slot_state(tl, last_slot), slot_ids(tl, last_slot), n, n_src, tl->n_max, tl->d_mismatch);
     if (tl->profile) { cudaEventRecord(tl->pev[1][1], st); tl->pev_used[1] = true; }
     TCK(cudaGetLastError());
     w->launches += 1;
