@@ -2,9 +2,11 @@
 ParallelCosmosContext::load_and_link and ::extract_entity_updates
 (source/spacetime/parallel_cosmos_context.cpp:60-169, :171-423) over the AoS scene arrays.
 
-Parity status: RESTATED, NOT EXECUTED -- ParallelCosmosContext cannot be compiled in this
-container (staging / assimp / asio dependencies), so this file follows the source
-line by line and is pinned only by the hand-derived cases in tests/test_clone_oracle.py.
+Parity status: PINNED.  ParallelCosmosContext itself cannot be compiled in this container (staging / assimp / asio
+dependencies), but its two entity loops only talk to Cosmos and EntityTimestreamMap: oracle/ref/ref_clone.cpp
+lifts them around the REAL objects (real serialize / deserialize_entity_components, state table, id helpers) and
+tests/test_clone_oracle.py checks this file against it on random scenes (filters, states, stamps, missing components,
+chain-link 0).  Not covered: the worldline-shift ("mandela") branch :229-316.
 Only tests/ may import it.
 """
 import numpy as np

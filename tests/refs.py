@@ -204,3 +204,44 @@ def projectile_update(lib, prefix, T, proj, dt, n_updates=1):
     rc = getattr(lib, prefix + "_projectile_update")(len(proj), dt, n_updates, abi.ptr(T), abi.ptr(proj), abi.ptr(condemned))
     assert rc == 0
     return T["scale"].copy(), proj, condemned
+
+
+# ---- a22: the reference's load_and_link / extract entity loops lifted around the real Cosmos (oracle/ref/ref_clone.cpp) ----
+_u16p = C.POINTER(C.c_uint16)
+REF_SIGS["icxref_load_and_link"] = (C.c_int, [_u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_uint16, _u32, _vp,
+                                             _u32, C.POINTER(_u32), _vp, _vp, _vp, _vp, _vp, _vp, _vp, _u16p])
+REF_SIGS["icxref_extract"] = (C.c_int, [_u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_uint16,
+                                       _u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _u32, C.POINTER(_u32), C.POINTER(_u32)])
+
+
+def ref_load_and_link(src, src_coherency, has_future=None, src_host=2):
+    """Returns (parallel scene, parallel coherency); mutates src.tstate / src.tcoh like the reference (real Cosmos objects)."""
+    from intercession_b200 import scenes
+    ids16 = narrow16(src.ids)
+    hf = None if has_future is None else np.ascontiguousarray(has_future, np.uint8)
+    cap = src.n
+    out = scenes._empty(cap)
+    o_ids = np.zeros(cap, np.uint16)
+    n_out, coh = _u32(0), C.c_uint16(0)
+    rc = ref().icxref_load_and_link(src.n, abi.ptr(ids16), abi.ptr(src.T), abi.ptr(src.P), abi.ptr(src.hasP), abi.ptr(src.C),
+                                    abi.ptr(src.tstate), abi.ptr(src.tcoh), src_coherency, src_host, abi.ptr(hf),
+                                    cap, C.byref(n_out), abi.ptr(o_ids), abi.ptr(out.T), abi.ptr(out.P), abi.ptr(out.hasP), abi.ptr(out.C),
+                                    abi.ptr(out.tstate), abi.ptr(out.tcoh), C.byref(coh))
+    assert rc == 0, rc
+    k = n_out.value
+    par = scenes.Scene({key: (v[:k].copy() if isinstance(v, np.ndarray) else v) for key, v in out.items()})
+    par["ids"] = np.array([abi.widen_entity(e) for e in o_ids[:k]], np.uint32)
+    return par, coh.value
+
+
+def ref_extract(par, dst, coherency, dst_host_id):
+    """Mutates dst like the reference; returns (extracted, ids the reference had to register in dst) or raises on chain-link 0."""
+    n_ex, n_reg = _u32(0), _u32(0)
+    rc = ref().icxref_extract(par.n, abi.ptr(narrow16(par.ids)), abi.ptr(par.T), abi.ptr(par.P), abi.ptr(par.hasP), abi.ptr(par.C),
+                              abi.ptr(par.tstate), abi.ptr(par.tcoh), coherency,
+                              dst.n, abi.ptr(narrow16(dst.ids)), abi.ptr(dst.T), abi.ptr(dst.P), abi.ptr(dst.hasP), abi.ptr(dst.C),
+                              abi.ptr(dst.tstate), abi.ptr(dst.tcoh), dst_host_id, C.byref(n_ex), C.byref(n_reg))
+    if rc == 2:
+        raise ValueError("chain-link 0 in the parallel cosmos (std::range_error in the reference)")
+    assert rc == 0, rc
+    return n_ex.value, n_reg.value

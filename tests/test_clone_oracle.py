@@ -83,3 +83,86 @@ def test_extract_ignores_parallel_created_and_rejects_link0():
     par["ids"] = np.array([abi.compose_entity(2, 1, 0)], np.uint32)
     with pytest.raises(ValueError):
         clone_oracle.extract_entity_updates(par, dst, 1, 1)
+
+
+# ---- pinned: the numpy restatement against the reference's own entity loops run on the real Cosmos (oracle/ref/ref_clone.cpp) ----
+import refs  # noqa: E402
+
+needs_ref = pytest.mark.skipif(refs.ref() is None, reason="oracle/_ref not built (no /root/reference here)")
+
+
+def random_past_scene(n, seed):
+    s = scenes.arena(n, seed=seed, walls=False, temporal=True, timeslice=2, fill_side=14.0)
+    rng = np.random.default_rng(seed)
+    g = np.arange(n, dtype=np.uint32) + 1                                       # genesis < 255: the real Entity is 16 bits wide
+    link = rng.choice([0, 1, 2, 3, 14, 15], n, p=[0.25, 0.25, 0.2, 0.15, 0.05, 0.1]).astype(np.uint32)
+    s["ids"] = (np.uint32(2) << np.uint32(28)) | (g << np.uint32(4)) | link
+    s.tstate[:] = rng.choice([abi.TS_MERGED, abi.TS_FORKED, abi.TS_FORKING, abi.TS_SUPERPOSITION, abi.TS_GHOST], n, p=[0.5, 0.2, 0.15, 0.1, 0.05])
+    s.tcoh[:] = rng.integers(0, 60, n).astype(np.uint16)
+    s.tcoh[s.tstate == abi.TS_MERGED] = np.where(rng.random((s.tstate == abi.TS_MERGED).sum()) < 0.5, 0, s.tcoh[s.tstate == abi.TS_MERGED])
+    s.hasP[rng.random(n) < 0.1] = 0
+    has_future = (rng.random(n) < 0.6).astype(np.uint8)
+    return s, has_future
+
+
+def same_scene(a, b):
+    assert a.n == b.n and np.array_equal(a.ids, b.ids)
+    for k in ("T", "C"):
+        assert not fields_diff(a[k], b[k]), k
+    hp = a.hasP.astype(bool)
+    assert np.array_equal(a.hasP, b.hasP) and not fields_diff(a.P[hp], b.P[hp])
+    assert np.array_equal(a.tstate, b.tstate) and np.array_equal(a.tcoh, b.tcoh)
+
+
+@needs_ref
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_load_and_link_matches_the_reference_loop(seed):
+    s, hf = random_past_scene(200, seed)
+    a, b = s.copy(), s.copy()
+    par_o, coh_o = clone_oracle.load_and_link(a, 41, hf)
+    par_r, coh_r = refs.ref_load_and_link(b, 41, hf)
+    assert coh_o == coh_r == 41
+    same_scene(par_o, par_r)
+    assert np.array_equal(a.tstate, b.tstate) and np.array_equal(a.tcoh, b.tcoh)        # forked entities re-merged in the source, stamped
+    assert (a.tstate != s.tstate).any() and par_o.n < s.n
+
+
+@needs_ref
+@pytest.mark.parametrize("seed,host", [(4, 3), (5, 0), (6, 1)])
+def test_extract_matches_the_reference_loop(seed, host):
+    dst, _ = random_past_scene(200, seed)
+    dst["ids"] = (dst.ids & ~np.uint32(0xF0000000)) | (np.uint32(host) << np.uint32(28))
+    link = dst.ids & 15
+    keep = link != 14                                                           # a past copy of a link-14 id does not exist (increment refused)
+    rng = np.random.default_rng(seed)
+    par = dst.copy()
+    for k in ("ids", "T", "P", "hasP", "C", "tstate", "tcoh"):
+        par[k] = dst[k][keep].copy()
+    plink = par.ids & 15
+    par["ids"] = np.where(plink == 15, par.ids, par.ids + 1).astype(np.uint32)  # the parallel cosmos holds the past's ids (link + 1)
+    created = rng.random(par.n) < 0.1                                           # entities created during the parallel run: timeslice 14 (:223-229)
+    par["ids"] = np.where(created, (par.ids & ~np.uint32(0xF0000000)) | (np.uint32(abi.NULL_TIMESLICE) << np.uint32(28)), par.ids).astype(np.uint32)
+    order = np.argsort(par.ids, kind="stable")
+    for k in ("ids", "T", "P", "hasP", "C", "tstate", "tcoh"):
+        par[k] = par[k][order].copy()
+    par.T["origin"] += np.float32(3.0)
+    par.P["velocity"] *= np.float32(-2.0)
+    par.C["colliders"]["restLength"] += np.float32(0.5)
+    par.tstate[:] = rng.choice([abi.TS_MERGED, abi.TS_FORKED, abi.TS_FORKING], par.n)
+    a, b = dst.copy(), dst.copy()
+    n_o, miss_o = clone_oracle.extract_entity_updates(par, a, 88, host)
+    n_r, reg_r = refs.ref_extract(par, b, 88, host)
+    assert miss_o == reg_r == 0 and n_o == n_r > 50
+    same_scene(a, b)
+    assert (a.T["origin"] != dst.T["origin"]).any()
+
+
+@needs_ref
+def test_extract_chain_link_zero_throws_like_the_reference():
+    dst, _ = random_past_scene(20, 9)
+    par = dst.copy()
+    par["ids"] = (par.ids & ~np.uint32(15))                                     # chain-link 0 everywhere
+    with pytest.raises(ValueError):
+        refs.ref_extract(par, dst.copy(), 5, 1)
+    with pytest.raises(ValueError):
+        clone_oracle.extract_entity_updates(par, dst.copy(), 5, 1)
