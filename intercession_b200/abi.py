@@ -200,6 +200,13 @@ SIGNATURES = {
     "icx_projectiles_download": (C.c_int, [_vp, _u32, _vp]),
     "icx_projectiles_condemned": (C.c_int, [_vp, _vp, _sz, _psz]),
     "icx_projectiles_kernel_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
+    # include/icx_nccl.h
+    "icx_nccl_available": (C.c_int, []),
+    "icx_scores_allgather": (C.c_int, [_vp, _u32, _u32, C.c_int, _vp, _vp, _vp, _vp]),
+    "icx_timeline_slot_send": (C.c_int, [_vp, C.c_uint16, _vp, C.c_int, _vp, _sz, _vp]),
+    "icx_timeline_slot_recv": (C.c_int, [_vp, C.c_uint16, _u32, _vp, C.c_int, _vp, _sz, _vp]),
+    "icx_nccl_group_start": (C.c_int, []),
+    "icx_nccl_group_end": (C.c_int, []),
 }
 
 _lib = None

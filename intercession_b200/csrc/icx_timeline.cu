@@ -389,6 +389,17 @@ int ensure_pending(IcxWorld* w, IcxTimeline* tl)
 
 } // namespace
 
+// accessors for icx_nccl.cu (IcxTimeline is opaque outside this file)
+int icx_tl_scan_buffers(IcxTimeline* tl, uint32_t n_worldlines, const uint32_t** d_count, const unsigned long long** d_score, const uint8_t** d_ever,
+                        cudaStream_t* scan_stream, int* device)
+{
+    if (!tl->scan_wl || tl->scan_wl != n_worldlines) { tl->error = "no scan of that many world-lines was enqueued on this timeline"; return ICX_E_STATE; }
+    *d_count = tl->d_count; *d_score = tl->d_score; *d_ever = tl->d_ever; *scan_stream = tl->scan_stream; *device = tl->device;
+    return ICX_OK;
+}
+void icx_tl_set_error(IcxTimeline* tl, const char* msg) { if (tl) tl->error = msg; }
+int icx_tl_device(const IcxTimeline* tl) { return tl->device; }
+
 extern "C" {
 
 int icx_timeline_create(int device, uint32_t depth_ticks, uint32_t n_max, IcxTimeline** out)

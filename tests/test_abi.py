@@ -13,13 +13,16 @@ import pytest
 from intercession_b200 import abi
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-HEADER = os.path.join(ROOT, "include", "icx.h")
+HEADERS = [os.path.join(ROOT, "include", "icx.h"), os.path.join(ROOT, "include", "icx_nccl.h")]
 
 
 def declared_symbols():
-    text = open(HEADER).read()
-    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return re.findall(r"ICX_API\s+[\w\s\*]+?\b(icx_\w+)\s*\(", text)
+    out = []
+    for h in HEADERS:
+        text = open(h).read()
+        text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+        out += re.findall(r"ICX_API\s+[\w\s\*]+?\b(icx_\w+)\s*\(", text)
+    return out
 
 
 def test_header_symbols_exported_and_bound(built):
@@ -40,7 +43,7 @@ def test_header_symbols_exported_and_bound(built):
 
 def test_header_compiles_as_plain_c(tmp_path):
     src = tmp_path / "t.c"
-    src.write_text('#include "icx.h"\n_Static_assert(sizeof(IcxTransform)==40,"T");_Static_assert(sizeof(IcxPhysics)==108,"P");\n'
+    src.write_text('#include "icx.h"\n#include "icx_nccl.h"\n_Static_assert(sizeof(IcxTransform)==40,"T");_Static_assert(sizeof(IcxPhysics)==108,"P");\n'
                    '_Static_assert(sizeof(IcxCollider)==84,"C");_Static_assert(sizeof(IcxColliderComponent)==168,"CC");\n'
                    '_Static_assert(sizeof(IcxContact)==48,"K");int main(void){IcxConfig c; icx_config_default(&c); return (int)c.struct_size;}\n')
     subprocess.run(["gcc", "-std=c11", "-Wall", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"), "-c", str(src),

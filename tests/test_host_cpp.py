@@ -53,3 +53,32 @@ def test_host_mirror_reproduces_case_study(exe):
             assert float(w[2]) == 299.99 + 1.0 / 60 and int(w[4]) == 1
             seen += 1
     assert seen == 5
+
+
+NCCL_SRC = os.path.join(ROOT, "tests", "host", "test_host_nccl.cpp")
+NCCL_EXE = os.path.join(ROOT, "build", "test_host_nccl")
+
+
+@pytest.fixture(scope="module")
+def nccl_exe(built):
+    libdir = os.path.join(ROOT, "intercession_b200")
+    os.makedirs(os.path.dirname(NCCL_EXE), exist_ok=True)
+    subprocess.run(["g++", "-std=c++17", "-O1", "-Wall", "-Wextra", "-Werror", "-I/usr/local/cuda/include", NCCL_SRC, "-o", NCCL_EXE,
+                    "-L", libdir, "-licx", "-L/usr/local/cuda/lib64", "-lcudart", "-ldl", "-lpthread", f"-Wl,-rpath,{libdir}"], check=True)
+    return NCCL_EXE
+
+
+def test_nccl_host_compiles_and_refuses_without_gpu(nccl_exe):
+    from intercession_b200 import abi
+    if abi.load().icx_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    r = subprocess.run([nccl_exe], capture_output=True, text=True)
+    assert r.returncode == 2 and "no CPU fallback" in r.stdout
+
+
+@pytest.mark.gpu
+def test_cpp_server_runs_config4_and_config5_exchanges_over_nccl(nccl_exe):
+    """include/icx_nccl.h from a plain C++ host with its own ncclComm_t (world size 2 when the box has two GPUs, else 1)."""
+    r = subprocess.run([nccl_exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "config4 allgather ok" in r.stdout and "config5 send/recv ok applied 1 id_mismatches 0" in r.stdout, r.stdout
