@@ -145,6 +145,19 @@ typedef struct IcxContact {
 #define ICX_CONTACT_BEHAVIORS_A 0x2u
 #define ICX_CONTACT_BEHAVIORS_B 0x4u
 
+/* What BipedBehaviors::on_collision (source/behaviors/biped_behaviors.h:336-366) writes into the caller's BipedComponent:
+ * isGrounded = true, groundNormal = the collision normal as handed to the caller, groundDist = length(caller's origin at
+ * callback time - collision point).  icx_grounds_fetch returns, per entity that received at least one such call in the last
+ * tick (a collider with useBehaviorsResponse was hit), the values of the LAST call in the reference's pair order -- what the
+ * component holds after the tick.  (packetA, packetB, side) identify that call. */
+typedef struct IcxGround {
+    IcxEntity entity;
+    float     normal[3];
+    float     dist;
+    uint32_t  packetA, packetB;
+    uint32_t  side;                 /* 0: the entity was the pair's A (lower packet), 1: its B */
+} IcxGround;
+
 /* events::cosmos::TIMESTREAM_INTERCEPTION_params, source/events/event_types.h:133-139 */
 typedef struct IcxInterception {
     IcxEntity agent;
@@ -312,6 +325,7 @@ ICX_API int icx_contacts_fetch(IcxWorld* w, IcxContact* out, size_t cap, size_t*
 ICX_API int icx_extra_pairs_fetch(IcxWorld* w, IcxPair* out, size_t cap, size_t* n);
 ICX_API int icx_budgets_fetch(IcxWorld* w, float* out, size_t cap);
 ICX_API int icx_interceptions_fetch(IcxWorld* w, IcxInterception* out, size_t cap, size_t* n);
+ICX_API int icx_grounds_fetch(IcxWorld* w, IcxGround* out, size_t cap, size_t* n);         /* ascending entity id */
 ICX_API int icx_stats_fetch(IcxWorld* w, IcxStats* out);
 
 /* Device-timed duration (ms) of the last icx_step/icx_step_n, CUDA events on
@@ -465,6 +479,31 @@ ICX_API int icx_timeline_slot_import(IcxTimeline* tl, uint16_t coherency, uint32
                                      size_t buffer_bytes, void* stream);
 
 ICX_API int icx_timeline_slot_info(const IcxTimeline* tl, uint16_t coherency, int* valid, uint32_t* n_recorded);
+
+/* ==== wire / record format ==========================================
+ * The reference's ENTITY_UPDATE message for every entity of the world, byte for byte as ServerNetworkDynamo's record phase
+ * builds it for the child timestream (server_network_dynamo.cpp:666-677): MessageHeader<EventId> {id, coherency, size}
+ * (events/message.h:22-28, 12 B), then the body stack (message.h:57-83) -- the components in DESCENDING component-type
+ * order (ComponentRegistry::serialize_entity_components, ecs/component_registry.h:238-253), then ENTITY_UPDATE_params
+ * {Entity, Signature, ComponentCategory::all} (events/event_types.h:102-111; 24 B under libstdc++, where std::bitset<32> is
+ * one unsigned long) -- so that an un-accelerated timeslice or client can push it through its own
+ * EventMessage >> params / deserialize_entity_components.  Only the physics segments exist on the device
+ * (TransformComponent, PhysicsComponent, ColliderComponent); their ComponentType indices and the event id come from the
+ * caller (hard_config_cosmos.h:47-58 registers them as 0, 6, 7; ENTITY_UPDATE is 102).  The entity id is the reference's
+ * 16-bit one: ids whose genesis does not fit 8 bits make the call fail with ICX_E_INVALID.
+ * Messages are written at a fixed stride (*stride_bytes = ICX_WIRE_MAX_BYTES); message k is entity k of the upload order,
+ * its length is 12 + header.size. */
+typedef struct IcxWireLayout {
+    uint32_t event_id;              /* events::cosmos::ENTITY_UPDATE                              */
+    uint8_t  type_transform, type_physics, type_collider;   /* ComponentType of each registered component */
+    uint8_t  increment_link;        /* 1: the id travels with chain-link + 1 (push_past_timestream, :673) */
+} IcxWireLayout;
+#define ICX_WIRE_HEADER_BYTES 12
+#define ICX_WIRE_PARAMS_BYTES 24
+#define ICX_WIRE_MAX_BYTES (ICX_WIRE_HEADER_BYTES + 168 + 108 + 40 + ICX_WIRE_PARAMS_BYTES)
+ICX_API void icx_wire_layout_default(IcxWireLayout* layout);
+ICX_API int icx_entity_update_messages(IcxWorld* w, const IcxWireLayout* layout, uint16_t coherency,
+                                       void* out, size_t capacity_bytes, size_t* stride_bytes, uint32_t* n_messages);
 
 #ifdef __cplusplus
 }

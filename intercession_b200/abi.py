@@ -51,6 +51,8 @@ contact_dt = np.dtype([("entityA", "<u4"), ("entityB", "<u4"), ("slotA", "u1"), 
                        ("flags", "<u2"), ("point", "<f4", 3), ("normal", "<f4", 3), ("depth", "<f4"),
                        ("packetA", "<u4"), ("packetB", "<u4")])
 assert contact_dt.itemsize == 48
+ground_dt = np.dtype([("entity", "<u4"), ("normal", "<f4", 3), ("dist", "<f4"), ("packetA", "<u4"), ("packetB", "<u4"), ("side", "<u4")])
+assert ground_dt.itemsize == 32
 interception_dt = np.dtype([("agent", "<u4"), ("recipient", "<u4")])
 pair_dt = np.dtype([("a", "<u4"), ("b", "<u4")])
 
@@ -129,6 +131,14 @@ class IcxConfig(C.Structure):
                 ("worldline_stride", C.c_uint32), ("max_pairs", C.c_uint32)]
 
 
+class IcxWireLayout(C.Structure):
+    _fields_ = [("event_id", C.c_uint32), ("type_transform", C.c_uint8), ("type_physics", C.c_uint8), ("type_collider", C.c_uint8),
+                ("increment_link", C.c_uint8)]
+
+
+WIRE_MAX_BYTES = 12 + 168 + 108 + 40 + 24
+
+
 class IcxStats(C.Structure):
     _fields_ = [("ticks", C.c_uint64), ("n_entities", C.c_uint32), ("n_packets", C.c_uint32),
                 ("n_large", C.c_uint32), ("n_candidates", C.c_uint32), ("n_contacts", C.c_uint32),
@@ -165,6 +175,7 @@ SIGNATURES = {
     "icx_extra_pairs_fetch": (C.c_int, [_vp, _vp, _sz, _psz]),
     "icx_budgets_fetch": (C.c_int, [_vp, _vp, _sz]),
     "icx_interceptions_fetch": (C.c_int, [_vp, _vp, _sz, _psz]),
+    "icx_grounds_fetch": (C.c_int, [_vp, _vp, _sz, _psz]),
     "icx_stats_fetch": (C.c_int, [_vp, C.POINTER(IcxStats)]),
     "icx_last_step_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
     "icx_world_stream": (_vp, [_vp]),
@@ -200,6 +211,8 @@ SIGNATURES = {
     "icx_projectiles_download": (C.c_int, [_vp, _u32, _vp]),
     "icx_projectiles_condemned": (C.c_int, [_vp, _vp, _sz, _psz]),
     "icx_projectiles_kernel_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
+    "icx_wire_layout_default": (None, [_vp]),
+    "icx_entity_update_messages": (C.c_int, [_vp, _vp, C.c_uint16, _vp, _sz, _psz, C.POINTER(_u32)]),
     # include/icx_nccl.h
     "icx_nccl_available": (C.c_int, []),
     "icx_scores_allgather": (C.c_int, [_vp, _u32, _u32, C.c_int, _vp, _vp, _vp, _vp]),

@@ -64,7 +64,7 @@ int allocate(IcxWorld* w)
     CK(alloc(w, W.nbr, (size_t)W.max_nbr)); CK(alloc(w, W.nbr_count, 2 * ne)); CK(alloc(w, W.nbr_fill, 2 * ne)); CK(alloc(w, W.slot_flag, ne)); CK(alloc(w, W.slot_info, ne));
     CK(alloc(w, W.head[0], ne)); CK(alloc(w, W.head[1], ne));
     CK(alloc(w, W.active[0], ne)); CK(alloc(w, W.active[1], ne)); CK(alloc(w, W.items, ne + W.max_static));
-    CK(alloc(w, W.contacts, W.max_contacts)); CK(alloc(w, W.intercepts, W.max_contacts)); CK(alloc(w, W.intercept_key, W.max_contacts));
+    CK(alloc(w, W.contacts, W.max_contacts)); CK(alloc(w, W.intercepts, W.max_contacts)); CK(alloc(w, W.intercept_key, W.max_contacts)); CK(alloc(w, W.grounds, W.max_contacts));
     CK(alloc(w, W.counters, CTR_TOTAL)); CK(alloc(w, W.flags, 4));
     CK(cudaMemset(W.counters, 0, CTR_TOTAL * sizeof(uint32_t))); CK(cudaMemset(W.flags, 0, 16));
     W.trace = nullptr;
@@ -199,6 +199,7 @@ int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_
             rc = regrow(w, W.contacts, W.max_contacts); if (rc) return rc;
             rc = regrow(w, W.intercepts, W.max_contacts); if (rc) return rc;
             rc = regrow(w, W.intercept_key, W.max_contacts); if (rc) return rc;
+            rc = regrow(w, W.grounds, W.max_contacts); if (rc) return rc;
         }
         if (raised & RF_LARGE_OVERFLOW) {
             W.max_large *= 2;
@@ -443,6 +444,34 @@ int icx_motion_download(IcxWorld* w, uint32_t n, IcxMotionState* out)
     return ICX_OK;
 }
 
+void icx_wire_layout_default(IcxWireLayout* l)
+{
+    if (!l) return;
+    l->event_id = 102; l->type_transform = 0; l->type_physics = 6; l->type_collider = 7; l->increment_link = 1;     // event_types.h:102, hard_config_cosmos.h:47-58
+}
+
+int icx_entity_update_messages(IcxWorld* w, const IcxWireLayout* layout, uint16_t coherency, void* out, size_t capacity, size_t* stride_bytes, uint32_t* n_messages)
+{
+    if (!w || !layout || !out) return ICX_E_INVALID;
+    const uint32_t n = w->n_entities;
+    if (stride_bytes) *stride_bytes = ICX_WIRE_MAX_BYTES;
+    if (n_messages) *n_messages = n;
+    if ((size_t)n * ICX_WIRE_MAX_BYTES > capacity) return fail(w, ICX_E_CAPACITY, "entity_update_messages: buffer too small");
+    if (layout->type_transform > 31 || layout->type_physics > 31 || layout->type_collider > 31) return fail(w, ICX_E_INVALID, "entity_update_messages: component type > 31");
+    for (uint32_t i = 0; i < n; i++) if (((w->h_ids[i] >> 4) & 0xFFFFFFu) > 0xFFu) return fail(w, ICX_E_INVALID, "entity_update_messages: genesis id does not fit the reference's 16-bit Entity");
+    if (!n) return ICX_OK;
+    cudaSetDevice(w->device);
+    cudaStream_t st = w->stream;
+    CK(w->st_C.ensure((size_t)n * ICX_WIRE_MAX_BYTES));
+    launch_export_kernel(w->W, mirror_of(w), 1, w->have_P ? 1 : 0, w->have_C ? 1 : 0, nullptr, nullptr, n, st);
+    Mirror M = mirror_of(w);
+    launch_wire_messages(w->W, M, *layout, coherency, w->have_C ? 1 : 0, (uint32_t*)w->st_C.ptr, n, st);
+    CK(cudaMemcpyAsync(out, w->st_C.ptr, (size_t)n * ICX_WIRE_MAX_BYTES, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    return ICX_OK;
+}
+
 int icx_coherency_set(IcxWorld* w, uint16_t c) { if (!w) return ICX_E_INVALID; w->W.coherency = c; return ICX_OK; }
 int icx_coherency_get(IcxWorld* w, uint16_t* c) { if (!w || !c) return ICX_E_INVALID; *c = w->W.coherency; return ICX_OK; }
 
@@ -565,6 +594,33 @@ int icx_interceptions_fetch(IcxWorld* w, IcxInterception* out, size_t cap, size_
     std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
         return key[a].x < key[b].x || (key[a].x == key[b].x && key[a].y < key[b].y); });
     for (size_t i = 0; i < std::min(cap, total); i++) out[i] = ev[order[i]];
+    return ICX_OK;
+}
+
+int icx_grounds_fetch(IcxWorld* w, IcxGround* out, size_t cap, size_t* n)
+{
+    if (!w || !n) return ICX_E_INVALID;
+    *n = 0;
+    if (!w->have_results) return ICX_OK;
+    const size_t total = std::min<size_t>(w->h_counters[CTR_GROUNDS], w->W.max_contacts);
+    if (!total) return ICX_OK;
+    cudaSetDevice(w->device);
+    std::vector<IcxGround> tmp(total);
+    CK(cudaMemcpyAsync(tmp.data(), w->W.grounds, total * sizeof(IcxGround), cudaMemcpyDeviceToHost, w->stream));
+    CK(cudaStreamSynchronize(w->stream));
+    // calls arrive out of order; the component keeps the LAST call in pair order (A's call of a pair precedes B's, relay :114-155)
+    std::sort(tmp.begin(), tmp.end(), [](const IcxGround& a, const IcxGround& b) {
+        if (a.entity != b.entity) return a.entity < b.entity;
+        if (a.packetA != b.packetA) return a.packetA < b.packetA;
+        if (a.packetB != b.packetB) return a.packetB < b.packetB;
+        return a.side < b.side; });
+    size_t k = 0;
+    for (size_t i = 0; i < total; i++) {
+        if (i + 1 < total && tmp[i + 1].entity == tmp[i].entity) continue;
+        if (out && k < cap) out[k] = tmp[i];
+        k++;
+    }
+    *n = k;
     return ICX_OK;
 }
 

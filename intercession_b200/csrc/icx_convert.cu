@@ -145,6 +145,43 @@ void launch_motion_export(const DeviceWorld& W, IcxMotionState* out, uint32_t n,
     if (n) k_motion_export<<<(n + 255) / 256, 256, 0, st>>>(W, reinterpret_cast<float*>(out), n);
 }
 
+// ENTITY_UPDATE messages in the reference's wire layout (include/icx.h "wire / record format"): one thread per 4-byte word of
+// a message, so that a warp writes 128 contiguous bytes.  The mirror rows are current (k_export ran just before).
+__global__ void __launch_bounds__(256) k_wire_messages(DeviceWorld W, Mirror M, IcxWireLayout lay, uint32_t coherency, int have_C, uint32_t* __restrict__ out, uint32_t n)
+{
+    const uint32_t WPM = ICX_WIRE_MAX_BYTES / 4;                                   // words per message slot
+    const size_t total = (size_t)n * WPM;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t e = (uint32_t)(i / WPM), wd = (uint32_t)(i % WPM);
+        const bool hasP = M.hasP[e] != 0;
+        const uint32_t nC = have_C ? 42u : 0u, nP = hasP ? 27u : 0u, nT = 10u;      // words: 168 / 108 / 40 bytes
+        const uint32_t body = nC + nP + nT + 6u;
+        uint32_t v = 0u;
+        if (wd == 0u) v = lay.event_id;
+        else if (wd == 1u) v = coherency & 0xFFFFu;                                  // uint16 coherency + 2 bytes of padding
+        else if (wd == 2u) v = body * 4u;                                            // header.size
+        else {
+            uint32_t b = wd - 3u;
+            if (b < nC) v = reinterpret_cast<const uint32_t*>(&M.C[e])[b];
+            else if ((b -= nC) < nP) v = reinterpret_cast<const uint32_t*>(&M.P[e])[b];
+            else if ((b -= nP) < nT) v = reinterpret_cast<const uint32_t*>(&M.T[e])[b];
+            else if ((b -= nT) < 6u) {
+                // ENTITY_UPDATE_params: Entity (uint16) @0, Signature (bitset<32> = unsigned long) @8, ComponentCategory @16
+                uint32_t id = W.entity_id[e];
+                if (lay.increment_link && (id & 0xFu) + 1u < 15u) id += 1u;         // increment_causal_chain_link, ecs_types.h:118-136
+                const uint32_t id16 = ((id >> 28) << 12) | (((id >> 4) & 0xFFu) << 4) | (id & 0xFu);
+                const uint32_t sign = (1u << lay.type_transform) | (hasP ? 1u << lay.type_physics : 0u) | (have_C ? 1u << lay.type_collider : 0u);
+                v = b == 0u ? id16 : (b == 2u ? sign : 0u);                          // category all = 0
+            }
+        }
+        out[i] = v;
+    }
+}
+void launch_wire_messages(const DeviceWorld& W, Mirror M, const IcxWireLayout& lay, uint32_t coherency, int have_C, uint32_t* out, uint32_t n, cudaStream_t st)
+{
+    if (n) k_wire_messages<<<148 * 8, 256, 0, st>>>(W, M, lay, coherency, have_C, out, n);
+}
+
 // ---- packet structure = ColliderSynchro::update's submission order (collider_synchro.cpp:28-42) ----
 // One packet per ACTIVE collider, entity by entity.  Computed on the device from the uploaded
 // components (count, exclusive scan, pack): walking 168 B per entity on the host costs more than the

@@ -18,6 +18,7 @@ struct Mirror { uint32_t* ids; IcxTransform* T; IcxPhysics* P; IcxColliderCompon
 void launch_import_kernel(const DeviceWorld& W, Mirror M, const uint32_t* index, const uint32_t* ids, const IcxTransform* T,
                           const IcxPhysics* P, const IcxColliderComponent* C, const uint8_t* hasP, const uint8_t* ts,
                           const uint16_t* tc, uint32_t count, int full, int have_C, uint32_t epoch, cudaStream_t st);
+void launch_wire_messages(const DeviceWorld& W, Mirror M, const IcxWireLayout& lay, uint32_t coherency, int have_C, uint32_t* out, uint32_t n, cudaStream_t st);
 void launch_motion_export(const DeviceWorld& W, IcxMotionState* out, uint32_t n, cudaStream_t st);
 void launch_export_kernel(const DeviceWorld& W, Mirror M, int have_T, int have_P, int have_C, uint8_t* ts, uint16_t* tc,
                           uint32_t n, cudaStream_t st);

@@ -453,6 +453,7 @@ __device__ __forceinline__ void process_pair(const DeviceWorld& W, uint32_t pa, 
     // ***** physics response, :82-107 *****
     const uint32_t ctA = (bitsA >> PF_CTYPE_SHIFT) & 3u, ctB = (bitsB >> PF_CTYPE_SHIFT) & 3u;
     uint32_t cflags = 0;
+    V3 originA = posA, originB = posB;
     if (ctA != ICX_COLLISION_NOOP && ctB != ICX_COLLISION_NOOP && (efA & EF_HAS_PHYSICS) && (efB & EF_HAS_PHYSICS)) {
         cflags |= ICX_CONTACT_RESPONDED;
         const bool rr = ctA == ICX_COLLISION_RIGID && ctB == ICX_COLLISION_RIGID;
@@ -473,6 +474,7 @@ __device__ __forceinline__ void process_pair(const DeviceWorld& W, uint32_t pa, 
                 if (!(efA & EF_IMMUTABLE)) store_side(W, ea, SA, a, rr);
                 if (!(efB & EF_IMMUTABLE)) store_side(W, eb, SB, b, rr);
             }
+            if (rr) { if (!(efA & EF_IMMUTABLE)) originA = SA.origin; if (!(efB & EF_IMMUTABLE)) originB = SB.origin; }     // what the callbacks below see
         }
     }
 
@@ -495,6 +497,25 @@ __device__ __forceinline__ void process_pair(const DeviceWorld& W, uint32_t pa, 
             c.depth = h.depth; c.packetA = pa; c.packetB = pb;
             W.contacts[ci] = c;
         } else atomicOr(W.flags, RF_CONTACT_OVERFLOW);
+    }
+    // The contact half of BipedBehaviors::on_collision (behaviors/biped_behaviors.h:336-366), which needs the CALLER's origin
+    // at callback time (after this pair's static resolution): isGrounded, groundNormal = the normal as the caller is handed it,
+    // groundDist = length(caller origin - collision point).  B is called with the inverted data (relay :137-146).  One record
+    // per call; the last one per entity in pair order is what the component ends up with (icx_grounds_fetch).
+    if (cflags & (ICX_CONTACT_BEHAVIORS_A | ICX_CONTACT_BEHAVIORS_B)) {
+        for (int side = 0; side < 2; side++) {
+            if (!(cflags & (side ? ICX_CONTACT_BEHAVIORS_B : ICX_CONTACT_BEHAVIORS_A))) continue;
+            const V3 n = side ? -h.normal : h.normal;
+            const V3 pt = side ? h.point - (h.normal * h.depth) : h.point;
+            const V3 o = side ? originB : originA;
+            const uint32_t gi = atomicAdd(&W.counters[CTR_GROUNDS], 1u);
+            if (gi < W.max_contacts) {
+                IcxGround g;
+                g.entity = side ? idB : idA; g.normal[0] = n.x; g.normal[1] = n.y; g.normal[2] = n.z; g.dist = length(o - pt);
+                g.packetA = pa; g.packetB = pb; g.side = (uint32_t)side;
+                W.grounds[gi] = g;
+            } else atomicOr(W.flags, RF_CONTACT_OVERFLOW);
+        }
     }
 
     // ***** timestream response :157-228 *****
@@ -649,27 +670,30 @@ static __device__ __noinline__ void mover_walk_warp(const DeviceWorld& W, uint32
         const int cx0 = (int)floorf((lo.x - sx) * W.inv_cell), cx1 = (int)floorf((hi.x + sx) * W.inv_cell);
         const int cy0 = (int)floorf((lo.y - sy) * W.inv_cell), cy1 = (int)floorf((hi.y + sy) * W.inv_cell);
         const int cz0 = (int)floorf((lo.z - sz) * W.inv_cell), cz1 = (int)floorf((hi.z + sz) * W.inv_cell);
-        for (int cz = cz0; cz <= cz1; cz++)
-            for (int cy = cy0; cy <= cy1; cy++)
-                for (int xb = cx0 >> ICX_XB; xb <= (cx1 >> ICX_XB); xb++) {
-                    const uint32_t block = row_block(xb, cy, cz, wl, W.n_buckets);
-                    const int x_lo = max(cx0, xb << ICX_XB), x_hi = min(cx1, (xb << ICX_XB) + ICX_XMASK);
-                    const uint32_t beg = W.cell_count[(block << ICX_XB) | (uint32_t)(x_lo & ICX_XMASK)];
-                    const uint32_t end = W.cell_count[((block << ICX_XB) | (uint32_t)(x_hi & ICX_XMASK)) + 1u];
-                    for (uint32_t j = beg + lane; j < end; j += 32u) {
-                        const float4 blo = W.s_lo[j], bhi = W.s_hi[j];
-                        const uint32_t btag = __float_as_uint(blo.w), be = __float_as_uint(bhi.w), q = btag & ICX_NB_INDEX_MASK;
-                        if (be == e || (W.worldline_stride && be / W.worldline_stride != wl) || !can_intersect(type, (btag >> 28) & 3, W.cfg_flags)) continue;
-                        // rows that collide in the bucket hash share a block: a packet counts only in the row its own cell is in
-                        if (cell_coord(blo.y, bhi.y, W.inv_cell) != cy || cell_coord(blo.z, bhi.z, W.inv_cell) != cz ||
-                            (cell_coord(blo.x, bhi.x, W.inv_cell) >> ICX_XB) != xb) continue;
-                        const bool q_immut = (btag & 0x40000000u) != 0;
-                        const float xj = q_immut ? 0.0f : W.bm[be] - m0;
-                        if (xj > 0.0f && q < p) continue;                          // two movers: the lower packet's walk emits the pair
-                        if (!overlap_x(lo, hi, xi, blo, bhi, xj) || overlap(lo, hi, blo, bhi)) continue;
-                        emit_xpair(W, p, q, q_immut);
-                    }
-                }
+        // one grid row (x-run of up to 16 cells at fixed y, z) per lane: the walk is a chain of dependent loads per row, 32 rows hide it
+        const int nxb = (cx1 >> ICX_XB) - (cx0 >> ICX_XB) + 1, ny = cy1 - cy0 + 1, nz = cz1 - cz0 + 1;
+        const uint32_t n_rows = (uint32_t)nxb * (uint32_t)ny * (uint32_t)nz;
+        for (uint32_t row = lane; row < n_rows; row += 32u) {
+            const int xb = (cx0 >> ICX_XB) + (int)(row % (uint32_t)nxb), cy = cy0 + (int)((row / (uint32_t)nxb) % (uint32_t)ny), cz = cz0 + (int)(row / ((uint32_t)nxb * (uint32_t)ny));
+            const uint32_t block = row_block(xb, cy, cz, wl, W.n_buckets);
+            const int x_lo = max(cx0, xb << ICX_XB), x_hi = min(cx1, (xb << ICX_XB) + ICX_XMASK);
+            const uint32_t beg = W.cell_count[(block << ICX_XB) | (uint32_t)(x_lo & ICX_XMASK)];
+            const uint32_t end = W.cell_count[((block << ICX_XB) | (uint32_t)(x_hi & ICX_XMASK)) + 1u];
+            for (uint32_t j = beg; j < end; j++) {
+                const float4 blo = W.s_lo[j], bhi = W.s_hi[j];
+                const uint32_t btag = __float_as_uint(blo.w), be = __float_as_uint(bhi.w), q = btag & ICX_NB_INDEX_MASK;
+                if (be == e || (W.worldline_stride && be / W.worldline_stride != wl) || !can_intersect(type, (btag >> 28) & 3, W.cfg_flags)) continue;
+                // rows that collide in the bucket hash share a block: a packet counts only in the row its own cell is in
+                if (cell_coord(blo.y, bhi.y, W.inv_cell) != cy || cell_coord(blo.z, bhi.z, W.inv_cell) != cz ||
+                    (cell_coord(blo.x, bhi.x, W.inv_cell) >> ICX_XB) != xb) continue;
+                const bool q_immut = (btag & 0x40000000u) != 0;
+                const float xj = q_immut ? 0.0f : W.bm[be] - m0;
+                if (xj > 0.0f && q < p) continue;                                  // two movers: the lower packet's walk emits the pair
+                if (!overlap_x(lo, hi, xi, blo, bhi, xj) || overlap(lo, hi, blo, bhi)) continue;
+                emit_xpair(W, p, q, q_immut);
+            }
+        }
+        __syncwarp();
         for (uint32_t i = lane; i < n_large; i += 32u) {                           // large colliders (immutable, not in the grid)
             const uint32_t q = W.large_list[i], qe = W.pk_entity[q];
             if (qe == e || (W.worldline_stride && qe / W.worldline_stride != wl) ||
@@ -830,7 +854,8 @@ static __device__ __noinline__ void predict_body_warp(const DeviceWorld& W, uint
     const float pa = predicted_push(W, e);
     if (!(pa > 0.0f)) return;
     const float m0 = W.margin;
-    if (!first_time && pa < 0.5f * m0) return;                                      // cannot lift anyone above the uniform margin
+    if (!first_time && pa < 0.5f * m0) return;                                      // cannot lift anyone above the uniform margin (measured: skipping small pushes
+                                                                                    // on the first pass too costs more in restarts than the pass itself)
     const uint4 info = W.slot_info[sl];
     if (info.z == ICX_NONE) return;
     const uint32_t p0 = info.x & 0x3FFFFFFFu, n0 = info.y & 0xFFFFu, n1 = info.y >> 16;
@@ -1259,7 +1284,7 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
         if (tid == 0) trace_mark(W, tn, 0x20000u);
         if (*(volatile uint32_t*)W.flags & RF_NEIGHBOR_OVERFLOW) break;     // lists are incomplete: the host grows them and re-runs the tick
         if (tid == 0) {
-            ctr[CTR_LISTED] = n_dirty; ctr[CTR_CONTACTS] = 0; ctr[CTR_INTERCEPTS] = 0;
+            ctr[CTR_LISTED] = n_dirty; ctr[CTR_CONTACTS] = 0; ctr[CTR_INTERCEPTS] = 0; ctr[CTR_GROUNDS] = 0;
             ctr[CTR_NEWD] = 0; ctr[CTR_NEWD + 1] = 0; ctr[CTR_NEWD + 2] = 0;
             ctr[CTR_ACTIVE] = 0; ctr[CTR_ACTIVE + 1] = 0; ctr[CTR_ACTIVE + 2] = 0;
             ctr[CTR_ITEMS] = 0; ctr[CTR_ITEMS + 1] = 0; ctr[CTR_FETCH] = 0; ctr[CTR_FETCH + 1] = 0;

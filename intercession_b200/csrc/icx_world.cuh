@@ -132,6 +132,7 @@ struct DeviceWorld {
     uint4* items;                   // per round: pairs that need the exact procedure {pa, pb, slot a, slot b | ICX_NONE}
     // outputs
     IcxContact* contacts; IcxInterception* intercepts; uint2* intercept_key; uint32_t max_contacts;
+    IcxGround* grounds;             // one record per on_collision call a BipedBehaviors drivetrain would receive (CTR_GROUNDS)
     // counters, one cache line each would be nicer; they are cold
     uint32_t* counters;             // see CTR_*
     uint32_t* flags;                // RF_*
@@ -157,6 +158,7 @@ enum { CTR_LARGE = 0, CTR_DIRTY = 1, CTR_CONTACTS = 2, CTR_INTERCEPTS = 3, CTR_C
        CTR_VIOLATORS = 28,      // bodies the current attempt moved beyond their budget
        CTR_POOL = 29,           // entries of the list pool in use
        CTR_NGREW = 30, CTR_NBUDGET = 31,   // restarts of the replay by reason (diagnostic)
+       CTR_GROUNDS = 17,
        CTR_PUSHED = 16,         // predicted pushes raised by the current prediction pass
        CTR_PROF = 32,           // ICX_PROFILE_PAIR builds: cycle accumulators
        CTR_TOTAL = 48 };

@@ -130,6 +130,10 @@ class World:
     def pairs(self):
         return self._fetch(self.lib.icx_pairs_fetch, abi.pair_dt)
 
+    def grounds(self):
+        """Per entity whose BipedBehaviors::on_collision would have run: what it leaves in the BipedComponent."""
+        return self._fetch(self.lib.icx_grounds_fetch, abi.ground_dt)
+
     def extra_pairs(self):
         return self._fetch(self.lib.icx_extra_pairs_fetch, abi.pair_dt)
 
@@ -141,6 +145,19 @@ class World:
     def budgets(self):
         out = np.zeros(self.n, np.float32)
         self._ck(self.lib.icx_budgets_fetch(self.handle, abi.ptr(out), len(out)))
+        return out
+
+    def entity_update_messages(self, coherency, types=(0, 6, 7), event_id=102, increment_link=True):
+        """ENTITY_UPDATE messages of every entity in the reference's wire layout: list of bytes objects (header + body)."""
+        lay = abi.IcxWireLayout(event_id, types[0], types[1], types[2], 1 if increment_link else 0)
+        buf = np.zeros(max(self.n, 1) * abi.WIRE_MAX_BYTES, np.uint8)
+        stride, n = C.c_size_t(0), C.c_uint32(0)
+        self._ck(self.lib.icx_entity_update_messages(self.handle, C.byref(lay), coherency, abi.ptr(buf), buf.nbytes, C.byref(stride), C.byref(n)))
+        out = []
+        for k in range(n.value):
+            m = buf[k * stride.value:(k + 1) * stride.value]
+            size = int(m[8:12].view(np.uint32)[0])
+            out.append(bytes(m[:12 + size]))
         return out
 
     def stats(self):

@@ -644,6 +644,7 @@ inline bool can_intersect(int a, int b, uint32_t flags) {
 }
 
 struct Packet { uint32_t entityIndex; uint8_t slot; };
+thread_local std::map<IcxEntity, IcxGround> g_grounds;      // per entity: what the last on_collision call of the last collision pass left
 
 // ColliderSynchro::update, source/physics/collider_synchro.cpp:28-42
 inline void build_packets(uint32_t n, IcxColliderComponent* C, std::vector<Packet>& packets, bool reset) {
@@ -689,6 +690,17 @@ struct Collide {
             st3(c.point, h.point); st3(c.normal, h.normal); c.depth = h.depth; c.packetA = ia; c.packetB = ib;
         }
         nh++;
+        // BipedBehaviors::on_collision, behaviors/biped_behaviors.h:336-366, for each side the relay calls (:114-155): the caller's
+        // origin is the LIVE transform (after this pair's static resolution); B gets the inverted normal / point (:137-146)
+        for (int side = 0; side < 2; side++) {
+            if (!(cflags & (side ? ICX_CONTACT_BEHAVIORS_B : ICX_CONTACT_BEHAVIORS_A))) continue;
+            const V3 n = side ? h.normal * -1.0f : h.normal;
+            const V3 pt = side ? h.point - (h.normal * h.depth) : h.point;
+            const IcxTransform& tc = side ? tB : tA;
+            IcxGround g; g.entity = id ? id[side ? pb.entityIndex : pa.entityIndex] : (side ? pb.entityIndex : pa.entityIndex);
+            st3(g.normal, n); g.dist = length(ld3(tc.origin) - pt); g.packetA = ia; g.packetB = ib; g.side = (uint32_t)side;
+            g_grounds[g.entity] = g;                                                // calls arrive in pair order: the last one stays
+        }
         // timestream response, :157-228
         if (!id) return;
         const IcxEntity eA = id[pa.entityIndex], eB = id[pb.entityIndex];
@@ -736,6 +748,15 @@ int icxo_euler(uint32_t n, IcxTransform* T, IcxPhysics* P, const uint8_t* has_ph
 }
 
 // CollisionPhysicsRelay::engage, collision_physics_relay.h:24-231.  cand == NULL: all pairs.
+// what BipedBehaviors::on_collision left per entity during the last icxo_collide of this thread (ascending entity id)
+int icxo_last_grounds(IcxGround* out, size_t cap, size_t* n)
+{
+    size_t k = 0;
+    for (auto& kv : g_grounds) { if (out && k < cap) out[k] = kv.second; k++; }
+    if (n) *n = k;
+    return 0;
+}
+
 int icxo_collide(uint32_t n, const IcxEntity* id, IcxTransform* T, IcxPhysics* P, const uint8_t* has_physics,
                  IcxColliderComponent* C, uint8_t* tstate, uint16_t* tcoh, uint16_t coherency,
                  uint32_t host_timeslice, uint32_t flags, uint32_t worldline_stride,
@@ -748,6 +769,7 @@ int icxo_collide(uint32_t n, const IcxEntity* id, IcxTransform* T, IcxPhysics* P
     cx.id = id; cx.T = T; cx.P = P; cx.hasP = has_physics; cx.C = C; cx.tstate = tstate; cx.tcoh = tcoh;
     cx.coherency = coherency; cx.host = host_timeslice; cx.flags = flags; cx.stride = worldline_stride;
     cx.hits = hits; cx.hcap = hit_cap; cx.nh = 0; cx.ints = ints; cx.icap = int_cap; cx.ni = 0;
+    g_grounds.clear();
     build_packets(n, C, cx.packets, true);
     const uint32_t np = (uint32_t)cx.packets.size();
     auto t0 = std::chrono::steady_clock::now();

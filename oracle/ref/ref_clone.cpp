@@ -207,3 +207,53 @@ int icxref_extract(uint32_t n_par, const uint16_t* par_ids, const IcxTransform* 
 }
 
 } // extern "C"
+
+// ---- wire / record format ----
+// The child-timestream ENTITY_UPDATE of every entity exactly as ServerNetworkDynamo::run_relays phase 4 builds it
+// (server_network_dynamo.cpp:666-677) on the REAL Cosmos / EventMessage: header + body bytes at a fixed stride.
+// n_dummy_before_physics: unrelated component types registered between Transform and Physics, so that the ComponentType
+// indices can be those of hard_config_cosmos.h:47-58 (Transform 0, Physics 6, Collider 7).
+namespace { template <int N> struct Filler { int v[2]; }; }
+extern "C" int icxref_entity_update_messages(uint32_t n, const uint16_t* ids, const IcxTransform* T, const IcxPhysics* P, const uint8_t* hasP,
+                                             const IcxColliderComponent* C, uint16_t coherency, int hard_config_types, int increment_link,
+                                             uint8_t* out, size_t stride)
+{
+    auto broker = std::make_shared<EventBroker>();
+    auto cosmos = std::make_shared<Cosmos>(broker, (TimesliceId)0);
+    cosmos->register_component<TransformComponent>();
+    if (hard_config_types) {
+        cosmos->register_component<Filler<1>>(); cosmos->register_component<Filler<2>>(); cosmos->register_component<Filler<3>>();
+        cosmos->register_component<Filler<4>>(); cosmos->register_component<Filler<5>>();
+    }
+    cosmos->register_component<PhysicsComponent>();
+    cosmos->register_component<ColliderComponent>();
+    for (uint32_t i = 0; i < n; i++) {
+        const Entity e = ids[i];
+        if (!cosmos->register_entity(e)) return 1;
+        cosmos->add_component(e, *reinterpret_cast<const TransformComponent*>(&T[i]));
+        if (!hasP || hasP[i]) cosmos->add_component(e, *reinterpret_cast<const PhysicsComponent*>(&P[i]));
+        if (C) cosmos->add_component(e, *reinterpret_cast<const ColliderComponent*>(&C[i]));
+    }
+    cosmos->set_coherency(coherency);
+    const uint16_t currentCoherency = cosmos->get_coherency();
+    for (uint32_t i = 0; i < n; i++) {
+        const Entity entity = ids[i];
+        const Signature sign = cosmos->get_entity_signature(entity);
+        // :666-676
+        EventMessage childUpdateMsg(events::cosmos::ENTITY_UPDATE, currentCoherency);
+        events::cosmos::ENTITY_UPDATE_params childUpdateInfo;
+        std::memset(&childUpdateInfo, 0, sizeof(childUpdateInfo));                  // (padding bytes: the reference leaves them unspecified)
+        childUpdateInfo.entity = entity; childUpdateInfo.sign = sign; childUpdateInfo.category = ComponentCategory::all;
+        cosmos->serialize_entity_components(childUpdateInfo.entity, childUpdateInfo.sign, childUpdateMsg);
+        if (increment_link) increment_causal_chain_link(childUpdateInfo.entity);
+        childUpdateMsg << childUpdateInfo;
+        uint8_t* o = out + (size_t)i * stride;
+        std::memset(o, 0, stride);
+        MessageHeader<EventId> h; std::memset(&h, 0, sizeof(h));
+        h.id = childUpdateMsg.header.id; h.coherency = childUpdateMsg.header.coherency; h.size = childUpdateMsg.header.size;
+        if (sizeof(h) + childUpdateMsg.body.size() > stride) return 2;
+        std::memcpy(o, &h, sizeof(h));
+        std::memcpy(o + sizeof(h), childUpdateMsg.body.data(), childUpdateMsg.body.size());
+    }
+    return (int)sizeof(MessageHeader<EventId>) == 12 && sizeof(events::cosmos::ENTITY_UPDATE_params) == 24 ? 0 : 3;
+}

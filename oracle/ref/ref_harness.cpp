@@ -33,6 +33,7 @@
 #include "spacetime/timestream_state.h"
 
 #include <chrono>
+#include <map>
 
 using namespace pleep;
 
@@ -69,6 +70,7 @@ struct Recorder : public I_BehaviorsDrivetrain {
     HitSink* sink = nullptr;
     std::unordered_map<Entity, uint32_t> firstPacket;   // entity -> packet index of its first active collider
     std::unordered_map<Entity, std::array<uint8_t, 2>> wantsBehaviors;  // caller's original flags
+    std::map<IcxEntity, IcxGround> grounds;                             // last on_collision call per entity (cleared per tick)
     uint32_t packet_of(const ColliderPacket& p, uint8_t& slot) {
         ColliderComponent& cc = cosmos->get_component<ColliderComponent>(p.collidee);
         slot = (&p.collider == &cc.colliders[1]) ? 1 : 0;
@@ -79,6 +81,16 @@ struct Recorder : public I_BehaviorsDrivetrain {
                       std::shared_ptr<EventBroker>) override {
         uint8_t sa, sb;
         uint32_t pa = packet_of(a, sa), pb = packet_of(b, sb);
+        if (wantsBehaviors[a.collidee][sa]) {
+            // what BipedBehaviors::on_collision does with these very arguments (behaviors/biped_behaviors.h:348-351), evaluated
+            // INSIDE the reference's own callback: callerData.transform is the live transform at callback time
+            IcxGround g{};
+            g.entity = widen(a.collidee);
+            for (int k = 0; k < 3; k++) g.normal[k] = n[k];
+            g.dist = glm::length(a.transform.origin - point);
+            g.packetA = pa < pb ? pa : pb; g.packetB = pa < pb ? pb : pa; g.side = pa < pb ? 0u : 1u;
+            grounds[g.entity] = g;
+        }
         if (pa > pb) return;   // B-side callback of the same hit (inverted data): recorded once, from A
         IcxContact c{};
         c.entityA = widen(a.collidee); c.entityB = widen(b.collidee);
@@ -114,9 +126,21 @@ struct InterceptionListener {
 
 } // namespace
 
+static std::map<IcxEntity, IcxGround> g_last_grounds;
+
 extern "C" {
 
 int icxref_abi_version(void) { return ICX_ABI_VERSION; }
+
+// per entity: the arguments of the last on_collision call of the LAST tick of the last icxref_verbatim_run, as
+// BipedBehaviors::on_collision would have stored them (ascending entity id)
+int icxref_last_grounds(IcxGround* out, size_t cap, size_t* n)
+{
+    size_t k = 0;
+    for (auto& kv : g_last_grounds) { if (out && k < cap) out[k] = kv.second; k++; }
+    if (n) *n = k;
+    return 0;
+}
 
 // Reference objects, reference call sequence:
 //   cosmos->update(); dynamo->run_relays(dt); dynamo->reset_relays(); cosmos->increment_coherency();
@@ -187,7 +211,7 @@ int icxref_verbatim_run(uint32_t n, const uint16_t* ids,
 
     auto t0 = std::chrono::steady_clock::now();
     for (uint32_t t = 0; t < n_ticks; t++) {
-        hs.n = 0; is.n = 0;
+        hs.n = 0; is.n = 0; rec->grounds.clear();
         cosmos->update();
         dynamo->run_relays(dt);
         dynamo->reset_relays();
@@ -212,6 +236,7 @@ int icxref_verbatim_run(uint32_t n, const uint16_t* ids,
             if (tcoh) tcoh[i] = st.second;
         }
     }
+    g_last_grounds = rec->grounds;
     if (coherency) *coherency = cosmos->get_coherency();
     if (n_hits) *n_hits = hs.n;
     if (n_ints) *n_ints = is.n;

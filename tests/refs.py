@@ -245,3 +245,36 @@ def ref_extract(par, dst, coherency, dst_host_id):
         raise ValueError("chain-link 0 in the parallel cosmos (std::range_error in the reference)")
     assert rc == 0, rc
     return n_ex.value, n_reg.value
+
+
+REF_SIGS["icxref_entity_update_messages"] = (C.c_int, [_u32, _vp, _vp, _vp, _vp, _vp, C.c_uint16, C.c_int, C.c_int, _vp, _sz])
+
+
+def ref_entity_update_messages(s, coherency, hard_config_types=True, increment_link=True):
+    """The reference's own ENTITY_UPDATE messages (real Cosmos::serialize_entity_components + EventMessage << params)."""
+    stride = abi.WIRE_MAX_BYTES
+    buf = np.zeros(s.n * stride, np.uint8)
+    rc = ref().icxref_entity_update_messages(s.n, abi.ptr(narrow16(s.ids)), abi.ptr(s.T), abi.ptr(s.P), abi.ptr(s.hasP), abi.ptr(s.C), coherency,
+                                             1 if hard_config_types else 0, 1 if increment_link else 0, abi.ptr(buf), stride)
+    assert rc == 0, rc
+    out = []
+    for k in range(s.n):
+        m = buf[k * stride:(k + 1) * stride]
+        size = int(m[8:12].view(np.uint32)[0])
+        out.append(bytes(m[:12 + size]))
+    return out
+
+
+REF_SIGS["icxref_last_grounds"] = (C.c_int, [_vp, _sz, _psz])
+ORACLE_SIGS["icxo_last_grounds"] = (C.c_int, [_vp, _sz, _psz])
+
+
+def last_grounds(lib, prefix):
+    """What BipedBehaviors::on_collision left per entity during the checker's last collision pass."""
+    n = C.c_size_t(0)
+    fn = getattr(lib, prefix + "_last_grounds")
+    fn(None, 0, C.byref(n))
+    out = np.zeros(n.value, abi.ground_dt)
+    if n.value:
+        fn(abi.ptr(out), n.value, C.byref(n))
+    return out
