@@ -483,7 +483,7 @@ def main():
     ap.add_argument("--no-timeline", action="store_true", help="skip the record / replay / scan kernel timings")
     ap.add_argument("--worldlines", type=int, default=4096, help="config-4 world-line candidates (0 = skip that section)")
     ap.add_argument("--worldline-bodies", type=int, default=1024)
-    ap.add_argument("--worldline-ticks", type=int, default=8)
+    ap.add_argument("--worldline-ticks", type=int, default=225, help="config 4 as written: 225 ticks against a 225-deep base history")
     ap.add_argument("--pipeline-bodies", type=int, default=100000, help="config-5 bodies per timeslice (0 = skip that section)")
     ap.add_argument("--pipeline-ticks", type=int, default=12)
     ap.add_argument("--pipeline-delay", type=int, default=5)

@@ -36,7 +36,8 @@ ICX_API int icx_scores_allgather(IcxTimeline* tl, uint32_t n_local, uint32_t n_p
  * (server_network_dynamo.cpp:642-679).  send = icx_timeline_slot_export + ncclSend, recv = ncclRecv + icx_timeline_slot_import,
  * all enqueued on `stream`; device_scratch is a caller-owned device buffer of scratch_bytes = ICX_SNAPSHOT_CAPACITY(n, rows)
  * bytes, the same on both sides.  A rank that both sends and receives in a tick brackets the two calls with
- * icx_nccl_group_start / _end so that neighbours cannot deadlock.
+ * icx_nccl_group_start / _end so that neighbours cannot deadlock; NCCL launches a group's operations at its end, so the import
+ * of a receive posted inside a group is enqueued by icx_nccl_group_end (use ONE stream per communicator inside a group).
  */
 ICX_API int icx_timeline_slot_send(IcxTimeline* tl, uint16_t coherency, ncclComm_t comm, int peer,
                                    void* device_scratch, size_t scratch_bytes, void* stream);

@@ -59,6 +59,12 @@ __global__ void k_pack_scores(const uint32_t* __restrict__ count, const unsigned
 
 DeviceBuffer g_send[64], g_recv[64];                                       // per device staging of the gather
 
+// NCCL launches the operations of a group at ncclGroupEnd: an import enqueued right after ncclRecv inside a group would run
+// BEFORE the receive.  Receives posted inside icx_nccl_group_start / _end are therefore imported by icx_nccl_group_end.
+struct PendingImport { IcxTimeline* tl; uint16_t coherency; uint32_t n; void* scratch; size_t bytes; void* stream; };
+thread_local int g_group_depth = 0;
+thread_local std::vector<PendingImport> g_pending;
+
 } // namespace
 
 extern "C" {
@@ -111,10 +117,28 @@ int icx_timeline_slot_recv(IcxTimeline* tl, uint16_t coherency, uint32_t n_entit
     cudaSetDevice(icx_tl_device(tl));
     int nrc = g_nccl.recv(device_scratch, scratch_bytes, NCCL_UINT8, peer, comm, (cudaStream_t)stream);
     if (nrc != 0) { icx_tl_set_error(tl, (std::string("ncclRecv: ") + (g_nccl.err ? g_nccl.err(nrc) : "error")).c_str()); return ICX_E_CUDA; }
+    if (g_group_depth > 0) { g_pending.push_back({tl, coherency, n_entities, device_scratch, scratch_bytes, stream}); return ICX_OK; }
     return icx_timeline_slot_import(tl, coherency, n_entities, device_scratch, scratch_bytes, stream);
 }
 
-int icx_nccl_group_start(void) { return nccl_bind() && g_nccl.group_start() == 0 ? ICX_OK : ICX_E_STATE; }
-int icx_nccl_group_end(void) { return nccl_bind() && g_nccl.group_end() == 0 ? ICX_OK : ICX_E_STATE; }
+int icx_nccl_group_start(void)
+{
+    if (!nccl_bind() || g_nccl.group_start() != 0) return ICX_E_STATE;
+    g_group_depth++;
+    return ICX_OK;
+}
+int icx_nccl_group_end(void)
+{
+    if (!nccl_bind() || g_group_depth <= 0) return ICX_E_STATE;
+    const int nrc = g_nccl.group_end();
+    g_group_depth--;
+    if (nrc != 0) { g_pending.clear(); return ICX_E_CUDA; }
+    int rc = ICX_OK;
+    if (g_group_depth == 0) {
+        for (const PendingImport& p : g_pending) { const int r = icx_timeline_slot_import(p.tl, p.coherency, p.n, p.scratch, p.bytes, p.stream); if (r != ICX_OK) rc = r; }
+        g_pending.clear();
+    }
+    return rc;
+}
 
 } // extern "C"

@@ -85,10 +85,6 @@ int main()
             CK(icx_step(cand[r], 1.0 / 45)); CK(icx_divergence_scan_enqueue(cand[r], tlb[r], (uint16_t)(t + 1), wl_per_rank));
         }
     std::vector<uint8_t> ever[2]; std::vector<uint32_t> cnt[2]; std::vector<double> score[2];
-    CK(icx_nccl_group_start());
-    // (the gather is a collective: with several devices in one process every rank's call sits inside one group; the copy back
-    //  happens after the group in this test, so the call is split by hand here)
-    CK(icx_nccl_group_end());
     for (int r = 0; r < R; r++) { ever[r].assign(wl_per_rank * R, 9); cnt[r].assign(wl_per_rank * R, 0); score[r].assign(wl_per_rank * R, 0.0); }
     if (R == 1) CK(icx_scores_allgather(tlb[0], wl_per_rank, wl_per_rank, 1, comm[0], ever[0].data(), cnt[0].data(), score[0].data()));
     else {
@@ -129,9 +125,12 @@ int main()
     CK(icx_record(wf, tf, 105));
     const size_t bytes = ICX_SNAPSHOT_CAPACITY(n, n);
     void* bs; void* br; cudaSetDevice(devs[src]); cudaMalloc(&bs, bytes); cudaSetDevice(devs[dst]); cudaMalloc(&br, bytes);
+    // one stream per communicator inside a group (with a single rank both calls use the same communicator); the replay on the
+    // receiving world's own stream is ordered behind the import by the slot's event
+    void* recv_stream = R == 1 ? icx_world_stream(wf) : icx_world_stream(wp);
     CK(icx_nccl_group_start());
     CK(icx_timeline_slot_send(tf, 105, comm[src], dst, bs, bytes, icx_world_stream(wf)));
-    CK(icx_timeline_slot_recv(tp, 105, n, comm[dst], src, br, bytes, icx_world_stream(wp)));
+    CK(icx_timeline_slot_recv(tp, 105, n, comm[dst], src, br, bytes, recv_stream));
     CK(icx_nccl_group_end());
     int applied = 0;
     CK(icx_replay(wp, tp, 105, ICX_REPLAY_SERVER, &applied));
