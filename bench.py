@@ -598,7 +598,7 @@ def main():
     w.close()
 
     long_run = None
-    if rank == 0 and a.long_seconds > 0:
+    if rank == 0 and world_size == 1 and a.long_seconds > 0:          # (N = 1 only: the other ranks would sit in the barrier)
         long_run = long_run_bench(a, local_rank)
     barrier()
 
