@@ -395,9 +395,12 @@ ICX_API int icx_projectiles_kernel_ms(IcxWorld* w, float* ms);
  * server_network_dynamo.cpp:666-677; layout component_registry.h:238-279): per entity the whole
  * TransformComponent and PhysicsComponent and the id the receiving cosmos knows it by (causal chain-link + 1,
  * :673); ColliderComponents travel as a sparse list of the rows that changed since the previous record into
- * the ring (every record of the reference repeats them unchanged).  Entities are addressed by upload index
- * AND checked by id: a replay leaves an entity whose id is not the recorded one alone and counts it
- * (icx_timeline_id_mismatches).  create / remove / jump events stay on the host TimelineApi queues. */
+ * the ring (every record of the reference repeats them unchanged).  Records are addressed by ID, as the reference's
+ * per-entity streams are: the receiving cosmos may hold other entities than the recording one (a time traveller has no
+ * future stream, a parallel cosmos omits it); an entity finds its record by its id -- at its own row when both hold the
+ * same entities, else by binary search, which needs ids in ascending submission order (std::set<Entity>, ecs/i_synchro.h:48)
+ * -- and an entity without a record is left alone and counted (icx_timeline_id_mismatches).
+ * create / remove / jump events stay on the host TimelineApi queues. */
 #define ICX_REPLAY_SERVER   0   /* ServerNetworkDynamo::run_relays phase 2, server_network_dynamo.cpp:377-421  */
 #define ICX_REPLAY_PARALLEL 1   /* ParallelNetworkDynamo::run_relays,     parallel_network_dynamo.cpp:51-89 */
 
@@ -464,7 +467,7 @@ ICX_API int icx_fork_age(IcxWorld* w, uint32_t* n_promoted, int* resolution_need
 /* Snapshot transport between timeslices on different GPUs / processes (the future -> past ENTITY_UPDATE
  * stream, server_network_dynamo.cpp:642-679): pack the slot stamped `coherency` into / restore it from a
  * caller-owned DEVICE buffer, e.g. the buffer a ncclSend / ncclRecv moves:
- *   [10][n] float4 state | [n] uint32 id (padded to 16 B) | 16-byte header {collider rows, 0, 0, 0} | rows x 176 B {index, pad, ColliderComponent}
+ *   [10][n] float4 state | [n] uint32 id (padded to 16 B) | 16-byte header {collider rows, 0, 0, 0} | rows x 176 B {sender row, id, ColliderComponent}
  * ICX_SNAPSHOT_CAPACITY(n, rows) is the buffer size for n entities and up to `rows` changed colliders.  `stream` is a
  * cudaStream_t (NULL = default stream); both calls are ASYNCHRONOUS on it and ordered against the recording / replaying
  * worlds' streams by events, so a timeslice needs no host synchronisation per tick. */

@@ -32,7 +32,7 @@ using namespace icx;
 
 #define TL_ARRAYS 10                    // float4 arrays per slot: pos rot vel acc angvel angacc | prm0 prm1 locked_pos locked_rot
 
-struct DeltaRow { uint32_t idx, _pad; IcxColliderComponent C; };       // 176 B, 16-byte aligned
+struct DeltaRow { uint32_t idx, id; IcxColliderComponent C; };         // 176 B, 16-byte aligned: sender's row (a hint), recorded id (the address)
 static_assert(sizeof(DeltaRow) == ICX_SNAPSHOT_DELTA_BYTES, "delta row layout");
 
 struct IcxTimeline {
@@ -94,8 +94,17 @@ __global__ void __launch_bounds__(256) k_record(RecordSrc R, float4* __restrict_
 // component of the record; a divergent one only the `upstream` category, which holds no physics
 // component (hard_config_cosmos.h:47-58 registers only SpacialInputComponent upstream).  The record is
 // addressed to the id it carries: an entity whose id differs is left alone and counted.
+// Row of `id` in an ascending id array (the order entities are submitted in: std::set<Entity>, ecs/i_synchro.h:48), hint first.
+__device__ __forceinline__ uint32_t find_id(const uint32_t* __restrict__ ids, uint32_t n, uint32_t id, uint32_t hint)
+{
+    if (hint < n && ids[hint] == id) return hint;
+    uint32_t lo = 0, hi = n;
+    while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (ids[mid] < id) lo = mid + 1; else hi = mid; }
+    return (lo < n && ids[lo] == id) ? lo : ICX_NONE;
+}
+
 __global__ void __launch_bounds__(256) k_replay(DeviceWorld W, const float4* __restrict__ src, const uint32_t* __restrict__ src_ids,
-                                                uint32_t n, uint32_t n_src, uint32_t n_max, unsigned long long* __restrict__ mismatch)
+                                                uint32_t n, uint32_t n_src, uint32_t n_max, int by_id, unsigned long long* __restrict__ mismatch)
 {
     const EntityState S = W.in;
     const size_t m = n_max;
@@ -103,9 +112,12 @@ __global__ void __launch_bounds__(256) k_replay(DeviceWorld W, const float4* __r
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const uint32_t state = S.ts[i] & 0xFFu;
         if (state == ICX_TS_FORKING || state == ICX_TS_FORKED) continue;            // is_divergent, timestream_state.h:41-44
-        const uint32_t j = n_src == n ? i : i % n_src;
         const uint32_t id = W.entity_id[i];
-        if (n_src == n && src_ids[j] != id) { bad++; continue; }
+        uint32_t j;
+        if (by_id) {                                                                // the record is addressed to ids: find mine (same row when the two
+            j = find_id(src_ids, n_src, id, i);                                     // cosmoses hold the same entities; a stream that has no record for me
+            if (j == ICX_NONE) { bad++; continue; }                                 // leaves me alone, as EntityTimestreamMap does)
+        } else j = i % n_src;                                                       // one world-line's record shared by all candidates
         S.pos[i] = src[j]; S.rot[i] = src[m + j];                                   // TransformComponent
         const float4 r0 = src[6 * m + j], r1 = src[7 * m + j];
         const float4 o0 = W.prm0[i], o1 = W.prm1[i];
@@ -137,6 +149,7 @@ __global__ void __launch_bounds__(256) k_delta_count(const uint32_t* __restrict_
     if (c && (threadIdx.x & 31u) == 0) atomicAdd(out, c);
 }
 __global__ void __launch_bounds__(256) k_delta_collect(const uint32_t* __restrict__ c_ver, uint32_t* __restrict__ seen, const IcxColliderComponent* __restrict__ C,
+                                                       const uint32_t* __restrict__ ids, int link_inc,
                                                        uint32_t n, int all, DeltaRow* __restrict__ dst, uint32_t cap, uint32_t* __restrict__ counter)
 {
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -144,7 +157,7 @@ __global__ void __launch_bounds__(256) k_delta_collect(const uint32_t* __restric
         if (!all && v == seen[i]) continue;
         seen[i] = v;
         const uint32_t at = atomicAdd(counter, 1u);
-        if (at < cap) { dst[at].idx = i; dst[at]._pad = 0; dst[at].C = C[i]; }
+        if (at < cap) { dst[at].idx = i; dst[at].id = link_inc ? inc_link(ids[i]) : ids[i]; dst[at].C = C[i]; }
     }
 }
 
@@ -178,8 +191,8 @@ __global__ void __launch_bounds__(128) k_replay_delta(DeviceWorld W, IcxCollider
 {
     const uint32_t n = min(*d_n, cap);
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const uint32_t e = rows[i].idx;
-        if (e >= W.n_entities) { atomicAdd(mismatch, 1ull); continue; }
+        const uint32_t e = find_id(W.entity_id, W.n_entities, rows[i].id, rows[i].idx);
+        if (e == ICX_NONE) { atomicAdd(mismatch, 1ull); continue; }
         const uint32_t state = W.in.ts[e] & 0xFFu;
         // keep_all: the record itself is dropped as stale (server_network_dynamo.cpp:391), but the NEXT record the entity takes
         // carries this row unchanged (every record holds every component): kept until then
@@ -530,7 +543,8 @@ int icx_record_ex(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, uint32_t fla
         if (cnt) { int rc = ensure_delta_cap(tl, cnt); if (rc != ICX_OK) return rc; }
         TCK(cudaMemsetAsync(tl->d_delta_n + s, 0, 4, st));
         if (cnt) {
-            k_delta_collect<<<stream_blocks(tl, n, 8), 256, 0, st>>>(w->W.c_ver, tl->seen, (const IcxColliderComponent*)w->mir_C.ptr, n, all,
+            k_delta_collect<<<stream_blocks(tl, n, 8), 256, 0, st>>>(w->W.c_ver, tl->seen, (const IcxColliderComponent*)w->mir_C.ptr, w->W.entity_id,
+                                                                   (flags & ICX_RECORD_KEEP_LINK) ? 0 : 1, n, all,
                                                                    tl->delta + (size_t)s * tl->delta_cap, tl->delta_cap, tl->d_delta_n + s);
             TCK(cudaGetLastError());
             w->launches += 2;
@@ -576,14 +590,15 @@ int icx_replay(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, int mode, int* 
     cudaStream_t st = w->stream;
     const uint32_t n_src = last >= 0 ? tl->count[popped[last]] : n;
     if (last >= 0 && !n_src) return ICX_OK;
-    if (n_src != n && !(w->W.worldline_stride && n_src == w->W.worldline_stride)) { tl->error = "replay: record size matches neither the world nor one world-line"; return ICX_E_INVALID; }
+    // a record of one world-line replayed into every candidate is addressed by position; everything else by id
+    const bool by_stride = w->W.worldline_stride && n_src == w->W.worldline_stride && n_src != n;
     for (int k : popped) TCK(cudaStreamWaitEvent(st, tl->slot_ev[k], 0));
     // Collider rows first, oldest record first.  The reference's records repeat every component, so the record that is applied
     // in the end carries the rows of ALL earlier ones: rows of records dropped as stale are applied too (when an applied record
     // follows in this very replay) or kept for the next record the entity takes (when none does).
     bool rows_any = false;
     for (int k : popped) rows_any |= tl->delta_n[k] != 0;
-    if (w->have_C && n_src == n && (rows_any || (w->pend_any && last >= 0))) {
+    if (w->have_C && !by_stride && (rows_any || (w->pend_any && last >= 0))) {
         int rc = ensure_pending(w, tl); if (rc != ICX_OK) return rc;
         const uint32_t epoch = ++w->c_epoch;
         IcxColliderComponent* MC = (IcxColliderComponent*)w->mir_C.ptr;
@@ -603,7 +618,7 @@ int icx_replay(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, int mode, int* 
     if (last < 0) return ICX_OK;                                            // every popped record was stale
     const int last_slot = popped[last];
     if (tl->profile) cudaEventRecord(tl->pev[1][0], st);
-    k_replay<<<stream_blocks(tl, n, 16), 256, 0, st>>>(w->W, slot_state(tl, last_slot), slot_ids(tl, last_slot), n, n_src, tl->n_max, tl->d_mismatch);
+    k_replay<<<stream_blocks(tl, n, 16), 256, 0, st>>>(w->W, slot_state(tl, last_slot), slot_ids(tl, last_slot), n, n_src, tl->n_max, by_stride ? 0 : 1, tl->d_mismatch);
     if (tl->profile) { cudaEventRecord(tl->pev[1][1], st); tl->pev_used[1] = true; }
     TCK(cudaGetLastError());
     w->launches += 1;

@@ -1,0 +1,183 @@
+"""Config 5 end to end (BASELINE.json configs[4]): a chain of timeslices with a time traveller.
+
+What the reference's timeline exists for, on the device pieces of this package:
+
+  a traveller arrives in a past timeslice (chain-link 0, no future timestream)          server_network_dynamo.cpp:748-812
+  -> it collides with local entities: TIMESTREAM_INTERCEPTION, recipient -> forking      collision_physics_relay.h:157-228, server_network_dynamo.cpp:813-838
+  -> fork ageing: forking -> forked after 13 ticks, resolution needed after 13 more      server_network_dynamo.cpp:681-705
+  -> parallel_notify_divergence -> INIT to the past-most timeslice                      parallel_cosmos_context.cpp:425-453
+  -> load_and_link (clone, breakpoints on that timeslice's future stream)                server_network_dynamo.cpp:321-337, parallel_cosmos_context.cpp:60-169
+  -> the parallel cosmos re-simulates up to the future neighbour's coherency, consuming old history at the breakpoint and
+     writing new history in front of it                                                  parallel_network_dynamo.cpp:51-89, :369-385
+  -> extract into the future neighbour at chain-link - 1, INIT on that timeslice, ... down to timeslice 0
+                                                                                         parallel_cosmos_context.cpp:171-423, server_network_dynamo.cpp:339-364
+
+The reference runs the parallel cosmos on its own thread "as fast as the CPU can" (parallel_cosmos_context.cpp:534-536) and
+re-targets it until its coherency meets the future neighbour's (server_network_dynamo.cpp:339-364): WHEN inside a wall tick
+that happens is a race there.  The schedule here is the deterministic limit of it -- the cycle runs to completion, down the
+whole chain, at the start of the wall tick in which resolution is needed (phase 1 of the networker, before replay / record) --
+so that the same schedule can be driven through two back ends and compared tick by tick: DeviceBackend (this file: IcxWorld /
+IcxTimeline through the C ABI) and the CPU restatement on the oracle procedures and the reference's real EntityTimestreamMap
+(tests/cpu_timetravel.py).  Jump events themselves (JUMP_REQUEST / DEPARTURE / ARRIVAL) are host-side in the reference too and
+are scripted: an arrival is a row inserted into the destination timeslice.
+"""
+import numpy as np
+
+from . import abi, pipeline, world
+from .scenes import Scene
+
+DT = 1.0 / 45
+KEYS = ("ids", "T", "P", "hasP", "C", "tstate", "tcoh")
+
+
+def insert_row(scene, row):
+    """Scene with `row` (a 1-entity Scene) inserted at its place in ascending id order."""
+    at = int(np.searchsorted(scene.ids, row.ids[0]))
+    out = Scene({k: v for k, v in scene.items() if k not in KEYS})
+    for k in KEYS:
+        out[k] = np.concatenate([scene[k][:at], row[k], scene[k][at:]])
+    return out, at
+
+
+def traveller_row(scene, index, genesis, timeslice):
+    """A copy of entity `index` arriving as a time traveller: chain-link 0, its own genesis id, merged state."""
+    row = Scene({k: scene[k][index:index + 1].copy() for k in KEYS})
+    row["ids"] = np.array([abi.compose_entity(timeslice, genesis, 0)], np.uint32)
+    row["tstate"][:] = abi.TS_MERGED
+    row["tcoh"][:] = 0
+    return row
+
+
+class DeviceBackend:
+    """Timeslice k = one IcxWorld (+ the ring of records its future neighbour pushes); the parallel cosmos = one more world.
+    devices[k] = CUDA device of timeslice k, devices[-1] = device of the parallel cosmos (all in this process)."""
+
+    def __init__(self, scenes_per_slice, delay, base=100, devices=None, capacity_slack=8):
+        self.n = len(scenes_per_slice)
+        self.delay, self.base = delay, base
+        self.devices = devices or [0] * (self.n + 1)
+        self.scene = list(scenes_per_slice)
+        cap = max(s.n for s in scenes_per_slice) + capacity_slack
+        self.cap = cap
+        self.w = [world.World(cap, host_timeslice=k, device=self.devices[k]) for k in range(self.n)]
+        for k in range(self.n):
+            self.w[k].upload(self.scene[k])
+            self.w[k].set_coherency(pipeline.start_coherency(k, self.n, delay, base))
+        self.tl_in = [None] + [world.Timeline(2 * delay + 4, cap, device=self.devices[k]) for k in range(1, self.n)]
+        self.par = world.World(cap, host_timeslice=abi.NULL_TIMESLICE, device=self.devices[self.n])
+        self.par_scene = None
+        self.link = {}
+        if any(self.devices[k] != self.devices[k + 1] for k in range(self.n - 1)):
+            import torch
+            for k in range(self.n - 1):
+                nb = abi.snapshot_capacity(cap, cap)
+                self.link[k] = (torch.empty(nb, dtype=torch.uint8, device=torch.device("cuda", self.devices[k])),
+                                torch.empty(nb, dtype=torch.uint8, device=torch.device("cuda", self.devices[k + 1])),
+                                world.Timeline(2, cap, device=self.devices[k]))
+
+    def close(self):
+        for o in self.w + [self.par] + [t for t in self.tl_in if t is not None] + [v[2] for v in self.link.values()]:
+            o.close()
+
+    def coherency(self, k):
+        return self.w[k].coherency()
+
+    # ---- networker phases ----
+    def replay(self, k):
+        return k > 0 and self.w[k].replay(self.tl_in[k], self.coherency(k), abi.REPLAY_SERVER)
+
+    def record_to_past(self, k):
+        if k + 1 >= self.n:
+            return
+        c = self.coherency(k)
+        if self.devices[k] == self.devices[k + 1]:
+            self.w[k].record(self.tl_in[k + 1], c)                           # push_past_timestream straight into the neighbour's ring
+            return
+        import torch
+        src, dst, tl_out = self.link[k]
+        self.w[k].record(tl_out, c)
+        n = tl_out.export_slot(c, src.data_ptr(), src.numel(), self.w[k].stream())
+        self.w[k].sync()
+        dst.copy_(src)                                                      # peer copy (NVLink)
+        torch.cuda.synchronize(self.devices[k + 1])
+        self.tl_in[k + 1].import_slot(c, n, dst.data_ptr(), dst.numel(), self.w[k + 1].stream())
+
+    def fork_age(self, k):
+        return self.w[k].fork_age()
+
+    def step(self, k):
+        self.w[k].step(DT)
+        return self.w[k].interceptions()
+
+    def state(self, k):
+        return self.w[k].download(self.scene[k])
+
+    def arrive(self, k, row):
+        """Entity lifecycle is host-side: the arrival of a traveller is a re-submission of the timeslice's entities."""
+        cur = self.state(k)
+        self.scene[k], at = insert_row(cur, row)
+        c = self.coherency(k)
+        self.w[k].upload(self.scene[k])
+        self.w[k].set_coherency(c)
+        return at
+
+    def has_future(self, k):
+        """entity_has_timestream for every entity of timeslice k: the future neighbour pushes its entities at chain-link + 1."""
+        pushed = set(pipeline.past_ids(self.scene[k - 1].ids).tolist())
+        return np.array([int(e) in pushed for e in self.scene[k].ids], np.uint8)
+
+    # ---- one parallel cycle step: shadow timeslice k, re-simulate up to its future neighbour, extract into it ----
+    def cycle_step(self, k):
+        tl, src, dst = self.tl_in[k], self.w[k], self.w[k - 1]
+        hf = self.has_future(k)
+        tl.set_breakpoint()                                                 # link_timestreams(future stream of k)
+        n = src.clone_into(self.par, hf)
+        par_scene = Scene({key: (v[hf.astype(bool) | ((self.scene[k].ids & 15) != 0)] if isinstance(v, np.ndarray) and key in KEYS else v)
+                           for key, v in self.scene[k].items()})
+        assert par_scene.n == n
+        ints = []
+        c, target = self.coherency(k), self.coherency(k - 1)
+        while c != target:
+            self.par.replay(tl, c, abi.REPLAY_PARALLEL)                     # pop_timestream_at_breakpoint: consumes old history
+            self.par.record(tl, c, at_breakpoint=True)                      # push_timestream_at_breakpoint: new history
+            self.par.step(DT)
+            ints.append(self.par.interceptions())
+            c = (c + 1) & 0xFFFF
+        end = self.par.download(par_scene)
+        n_ex, n_miss = self.par.extract_into(dst)
+        tl.clear_breakpoint()
+        return {"cloned": n, "extracted": n_ex, "missing": n_miss, "interceptions": ints, "parallel_end": end}
+
+
+def run(backend, wall_ticks, arrivals=(), observe=None):
+    """Drive the chain for `wall_ticks` wall ticks.  arrivals: [(wall tick, timeslice, row)].  observe(tick, phase, data) is called
+    with what both back ends must agree on.  Returns the number of parallel cycles that ran."""
+    cycles = 0
+    n = backend.n
+    for t in range(wall_ticks):
+        for (ta, k, row) in arrivals:
+            if ta == t:
+                backend.arrive(k, row)
+        # fork ageing of the PREVIOUS tick decided whether a resolution is needed; the cycle runs before this tick's networker
+        need = getattr(backend, "_need", False)
+        if need:
+            results = [backend.cycle_step(k) for k in range(n - 1, 0, -1)]  # INIT to the past-most timeslice, then down the chain
+            cycles += 1
+            backend._need = False
+            if observe:
+                observe(t, "cycle", results)
+        for k in range(n):
+            backend.replay(k)                                               # phase 2
+        for k in range(n):
+            backend.record_to_past(k)                                       # phase 4
+        need = False
+        ages = []
+        for k in range(n):
+            promoted, nd = backend.fork_age(k)                              # phase 5
+            ages.append((promoted, nd))
+            need |= nd
+        backend._need = need
+        ints = [backend.step(k) for k in range(n)]                          # physicser
+        if observe:
+            observe(t, "tick", {"ages": ages, "interceptions": ints, "states": [backend.state(k) for k in range(n)]})
+    return cycles

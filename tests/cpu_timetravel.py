@@ -1,0 +1,82 @@
+"""TEST INFRASTRUCTURE: the CPU side of intercession_b200/timetravel.py -- the same schedule driven over the oracle procedures
+(tick, interception predicate + handlers, fork ageing), the reference's REAL EntityTimestreamMap / TsBreakpointQueue when
+oracle/_ref is built (else their restatement), and oracle/clone_oracle.py (pinned against the reference's entity loops)."""
+import os
+import sys
+
+import numpy as np
+
+from intercession_b200 import abi, pipeline, timetravel
+from intercession_b200.scenes import Scene
+import refs
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "oracle"))
+import clone_oracle  # noqa: E402
+
+
+class CpuBackend:
+    def __init__(self, scenes_per_slice, delay, base=100):
+        self.n, self.delay = len(scenes_per_slice), delay
+        self.scene = [s.copy() for s in scenes_per_slice]
+        self.coh = [pipeline.start_coherency(k, self.n, delay, base) for k in range(self.n)]
+        lib, prefix = (refs.ref(), "icxref") if refs.ref() is not None else (refs.oracle(), "icxo")
+        self.tl_in = [None] + [refs.CpuTimeline(lib, prefix) for _ in range(1, self.n)]
+
+    def close(self):
+        for t in self.tl_in:
+            if t is not None:
+                t.close()
+
+    def coherency(self, k):
+        return self.coh[k]
+
+    def replay(self, k):
+        if k == 0:
+            return False
+        self.scene[k], n = self.tl_in[k].replay(self.scene[k], self.coh[k])
+        return n > 0
+
+    def record_to_past(self, k):
+        if k + 1 < self.n:
+            self.tl_in[k + 1].record(self.scene[k], self.coh[k], link_inc=True)
+
+    def fork_age(self, k):
+        self.scene[k], promoted, need = refs.oracle_fork_age(self.scene[k], self.coh[k])
+        return promoted, need
+
+    def step(self, k):
+        out = refs.procedures_tick(refs.oracle(), "icxo", self.scene[k], host=k, coherency=self.coh[k])
+        ints = out["ints"]
+        self.scene[k] = Scene({key: v for key, v in out.items() if key not in ("hits", "ints", "seconds")})
+        self.coh[k] = (self.coh[k] + 1) & 0xFFFF
+        return ints
+
+    def state(self, k):
+        return self.scene[k]
+
+    def arrive(self, k, row):
+        self.scene[k], at = timetravel.insert_row(self.scene[k], row)
+        return at
+
+    def has_future(self, k):
+        pushed = set(pipeline.past_ids(self.scene[k - 1].ids).tolist())
+        return np.array([int(e) in pushed for e in self.scene[k].ids], np.uint8)
+
+    def cycle_step(self, k):
+        tl = self.tl_in[k]
+        hf = self.has_future(k)
+        tl.breakpoint(True)
+        par, c = clone_oracle.load_and_link(self.scene[k], self.coh[k], hf)
+        n = par.n
+        ints = []
+        target = self.coh[k - 1]
+        while c != target:
+            tl.replay(par, c, mode=abi.REPLAY_PARALLEL)
+            tl.record(par, c, at_breakpoint=True, link_inc=False)
+            out = refs.procedures_tick(refs.oracle(), "icxo", par, host=abi.NULL_TIMESLICE, coherency=c)
+            ints.append(out["ints"])
+            par = Scene({key: v for key, v in out.items() if key not in ("hits", "ints", "seconds")})
+            c = (c + 1) & 0xFFFF
+        n_ex, n_miss = clone_oracle.extract_entity_updates(par, self.scene[k - 1], self.coh[k - 1], k - 1)
+        tl.breakpoint(False)
+        return {"cloned": n, "extracted": n_ex, "missing": n_miss, "interceptions": ints, "parallel_end": par}

@@ -1,0 +1,78 @@
+"""GPU: config 5 end to end at a reduced size ("interception / flag parity vs the CPU restatement at <= 4 K
+bodies"): three timeslices, a time traveller arrives in the past-most one, collides, its victims fork, the forks age, the
+parallel cosmos is loaded from the past-most timeslice, re-simulates with the breakpoint record / replay, extracts up the chain.
+Device (IcxWorld / IcxTimeline through the C ABI, intercession_b200/timetravel.py) and CPU restatement (oracle procedures + the
+reference's real EntityTimestreamMap + clone oracle, tests/cpu_timetravel.py) run the SAME schedule; every tick the interception
+lists, the timestream states and stamps, and the whole component state of every timeslice must be identical, and so must the
+parallel cosmos at the end of every re-simulation."""
+import numpy as np
+import pytest
+
+from intercession_b200 import abi, pipeline, scenes, timetravel
+from util import fields_diff
+from cpu_timetravel import CpuBackend
+
+pytestmark = pytest.mark.gpu
+
+
+def make_chain(n_bodies, n_ts, seed=31):
+    side = 2.0 + 1.1 * round(n_bodies ** (1 / 3) + 1)
+    base = scenes.arena(n_bodies, seed=seed, walls=True, temporal=True, fill_side=side, spacing=1.05, jitter=0.25, kinds=("sphere", "box", "aabb"))
+    base.T["orientation"][:] = (1, 0, 0, 0)                       # no rotation anywhere: the tick is bit-exact end to end (no sin / cos ulp),
+    base.P["lockOrientation"][:] = 1                              # so device and CPU can free-run side by side for the whole scenario
+    base.P["lockedOrientation"][:] = (1, 0, 0, 0)
+    base.P["angularVelocity"][:] = 0
+    chain = []
+    for k in range(n_ts):
+        s = base.copy()
+        s["ids"] = pipeline.past_ids(base.ids, k)
+        chain.append(s)
+    return chain
+
+
+def same_scene(a, b, what):
+    assert a.n == b.n and np.array_equal(a.ids, b.ids), what
+    for key in ("T", "P", "C"):
+        d = fields_diff(a[key], b[key])
+        assert not d, (what, key, d[:3])
+    assert np.array_equal(a.tstate, b.tstate) and np.array_equal(a.tcoh, b.tcoh), what
+
+
+def test_traveller_forks_its_victims_and_the_parallel_cosmos_resolves_them(built):
+    n_ts, delay, ticks = 3, 4, 38
+    chain = make_chain(500, n_ts)
+    # the traveller: a copy of body 100 of the past-most timeslice, pushed 0.3 units into it, arriving at wall tick 3
+    row = timetravel.traveller_row(chain[n_ts - 1], 6 + 100, genesis=2000, timeslice=n_ts - 1)
+    row.T["origin"][0, 0] += np.float32(0.3)
+    arrivals = [(3, n_ts - 1, row)]
+    dev = timetravel.DeviceBackend(chain, delay)
+    cpu = CpuBackend(chain, delay)
+    log = {"dev": [], "cpu": []}
+    try:
+        cd = timetravel.run(dev, ticks, arrivals, lambda t, ph, d: log["dev"].append((t, ph, d)))
+        cc = timetravel.run(cpu, ticks, arrivals, lambda t, ph, d: log["cpu"].append((t, ph, d)))
+    finally:
+        dev.close(); cpu.close()
+    assert cd == cc >= 1                                           # at least one parallel cycle ran, on the same wall tick(s)
+    assert len(log["dev"]) == len(log["cpu"])
+    n_ints = n_forked = 0
+    for (t, ph, d), (t2, ph2, c) in zip(log["dev"], log["cpu"]):
+        assert (t, ph) == (t2, ph2)
+        if ph == "tick":
+            assert d["ages"] == c["ages"], t
+            for k in range(n_ts):
+                assert len(d["interceptions"][k]) == len(c["interceptions"][k]) and not fields_diff(d["interceptions"][k], c["interceptions"][k]), (t, k)
+                same_scene(d["states"][k], c["states"][k], (t, k))
+                n_ints += len(d["interceptions"][k])
+                n_forked += int((d["states"][k].tstate == abi.TS_FORKED).sum())
+        else:
+            for rd, rc in zip(d, c):
+                assert (rd["cloned"], rd["extracted"], rd["missing"]) == (rc["cloned"], rc["extracted"], rc["missing"]), t
+                assert len(rd["interceptions"]) == len(rc["interceptions"])
+                for a, b in zip(rd["interceptions"], rc["interceptions"]):
+                    assert len(a) == len(b) and not fields_diff(a, b), t
+                same_scene(rd["parallel_end"], rc["parallel_end"], (t, "parallel"))
+    assert n_ints > 0 and n_forked > 0
+    # after the cycle every timeslice but the traveller's own victims' copies in timeslice 0 ... : timeslice 0 is fully merged again
+    last = [e for e in log["dev"] if e[1] == "tick"][-1][2]["states"]
+    assert (last[0].tstate == abi.TS_MERGED).all()
