@@ -35,7 +35,10 @@ def insert_row(scene, row):
     at = int(np.searchsorted(scene.ids, row.ids[0]))
     out = Scene({k: v for k, v in scene.items() if k not in KEYS})
     for k in KEYS:
-        out[k] = np.concatenate([scene[k][:at], row[k], scene[k][at:]])
+        # not np.concatenate: its dtype promotion drops the trailing padding of the aligned component rows
+        v = np.empty(scene.n + 1, scene[k].dtype)
+        v[:at], v[at], v[at + 1:] = scene[k][:at], row[k][0], scene[k][at:]
+        out[k] = v
     return out, at
 
 

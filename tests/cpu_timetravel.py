@@ -19,7 +19,11 @@ class CpuBackend:
         self.n, self.delay = len(scenes_per_slice), delay
         self.scene = [s.copy() for s in scenes_per_slice]
         self.coh = [pipeline.start_coherency(k, self.n, delay, base) for k in range(self.n)]
-        lib, prefix = (refs.ref(), "icxref") if refs.ref() is not None else (refs.oracle(), "icxo")
+        # the reference's Entity is 16 bits wide (genesis < 255): its real containers serve the small scenarios, their restatement
+        # in the oracle (pinned to them by tests/test_timeline_oracle.py) the larger ones
+        small = max(s.n for s in scenes_per_slice) + 8 < 250 and all(((s.ids >> 4) & 0xFFFFFF).max() < 250 for s in scenes_per_slice)
+        lib, prefix = (refs.ref(), "icxref") if (refs.ref() is not None and small) else (refs.oracle(), "icxo")
+        self.containers = prefix
         self.tl_in = [None] + [refs.CpuTimeline(lib, prefix) for _ in range(1, self.n)]
 
     def close(self):
@@ -52,7 +56,7 @@ class CpuBackend:
         return ints
 
     def state(self, k):
-        return self.scene[k]
+        return self.scene[k].copy()                                         # extract mutates the future neighbour's scene in place
 
     def arrive(self, k, row):
         self.scene[k], at = timetravel.insert_row(self.scene[k], row)
