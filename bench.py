@@ -402,6 +402,87 @@ def timeslice_pipeline_bench(bodies, ticks, delay, rank, world_size, local_rank,
             "records_replayed_min": int(rep_t.item())}
 
 
+def time_travel_bench(bodies, n_ts, n_travellers, delay, wall_ticks, rank, world_size, local_rank, barrier):
+    """BASELINE.json configs[4] end to end (intercession_b200/timetravel.py): `n_ts` timeslices of `bodies` temporal bodies,
+    `n_travellers` time travellers arriving at scripted ticks one timeslice into their past (JUMP_REQUEST{timesliceDelta=+1}),
+    interceptions -> fork ageing -> parallel_notify_divergence -> load_and_link -> re-simulation with record / replay at the
+    breakpoint -> extract, down the whole chain.  ONE host process (rank 0) drives every timeslice: timeslice k on GPU
+    k mod N, one host thread per timeslice inside a phase, the parallel cosmos on the GPU of the timeslice it shadows.  The
+    other ranks wait on the rendezvous store (host side: a pending NCCL kernel on their GPUs would keep the cooperative
+    launches of rank 0 from ever becoming resident there)."""
+    import datetime
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from intercession_b200 import abi, pipeline, scenes, timetravel
+    barrier()
+    store = dist.distributed_c10d._get_default_store() if world_size > 1 else None
+    if rank != 0:
+        store.wait(["icx_time_travel_done"], datetime.timedelta(seconds=900))
+        return None
+    out = None
+    try:
+        n_dev = max(1, min(world_size, torch.cuda.device_count()))
+        devices = [k % n_dev for k in range(n_ts)]
+        base = scenes.arena(bodies, seed=20261107, kinds=("sphere", "box"), temporal=True)
+        chain = []
+        for k in range(n_ts):
+            sc = base.copy()
+            sc["ids"] = pipeline.past_ids(base.ids, k)
+            chain.append(sc)
+        kinds = base.C["colliders"]["colliderType"][:, 0]
+        boxes = np.nonzero((kinds == abi.COLLIDER_BOX) & ((base.ids & 15) != 15))[0]
+        twins = boxes[np.linspace(0, len(boxes) - 1, n_travellers).astype(np.int64)]
+        arrivals = []
+        for i, twin in enumerate(twins):                            # traveller i: a copy of `twin`, 0.3 units inside it, chain-link 0
+            k = 1 + i % (n_ts - 1)
+            row = timetravel.traveller_row(chain[k], int(twin), genesis=2000000 + i, timeslice=k)
+            row.T["origin"][0, 0] += np.float32(0.3)
+            arrivals.append((3 + (i // (n_ts - 1)) % 8, k, row))
+        be = timetravel.DeviceBackend(chain, delay, devices=devices, capacity_slack=n_travellers + 8)
+        be.keep_parallel_end = False
+        seen = {"ints": 0, "promoted": 0, "cycle_ints": 0, "extracted": 0, "missing": 0}
+
+        def observe(t, phase, d):
+            if phase == "tick":
+                seen["ints"] += sum(len(i) for i in d["interceptions"])
+                seen["promoted"] += sum(p for p, _ in d["ages"])
+            else:
+                for r in d:
+                    seen["cycle_ints"] += sum(len(i) for i in r["interceptions"])
+                    seen["extracted"] += r["extracted"]; seen["missing"] += r["missing"]
+        for dv in set(devices):
+            torch.cuda.synchronize(dv)
+        t0 = time.perf_counter()
+        cycles = timetravel.run(be, wall_ticks, arrivals, observe, with_states=False)
+        for k in range(n_ts):
+            be.w[k].sync()
+        sec = time.perf_counter() - t0
+        cyc = getattr(be, "cycle_seconds", [])
+        mism = [int(t.id_mismatches()) for t in be.tl_in if t is not None]
+        be.close()
+        tick_sec = sec - sum(cyc)
+        out = {"workload": f"config5: {n_ts} timeslices x {bodies} temporal bodies + 6 walls, {n_travellers} time travellers arriving one timeslice "
+                           f"into their past at wall ticks 3-10, timeslice delay {delay} ticks"
+                           + ("" if delay >= 225 else " (config 5 says 5 s = 225 ticks: reduced so that the default run stays within minutes; --tt-delay 225 runs it as written)")
+                           + f", {wall_ticks} wall ticks; interceptions, fork ageing and the parallel cycle down the whole chain inside the run",
+               "n_timeslices": n_ts, "gpus_used": n_dev, "devices": devices, "host": "one process, one thread per timeslice and phase",
+               "wall_ticks": wall_ticks, "seconds": round(sec, 4),
+               "wall_ticks_per_s_outside_cycles": round(wall_ticks / tick_sec, 2), "ticks_per_s_per_timeslice": round(wall_ticks / tick_sec, 2),
+               "collider_steps_per_s_outside_cycles": round(n_ts * base.n * wall_ticks / tick_sec, 1),
+               "parallel_cycles": cycles, "cycle_latency_ms": [round(c * 1e3, 2) for c in cyc],
+               "cycle_work": f"{n_ts - 1} x (load_and_link + {delay} re-simulated ticks with replay / record at the breakpoint + extract)",
+               "interceptions": seen["ints"], "forks_promoted": seen["promoted"], "interceptions_in_cycles": seen["cycle_ints"],
+               "entities_extracted": seen["extracted"], "entities_missing_on_extract": seen["missing"],
+               "records_of_unknown_ids": mism,
+               "parity": "tests/test_gpu_timetravel.py: the same schedule at 150 / 500 bodies, every tick bit-exact against the CPU restatement"}
+    finally:
+        if store is not None:
+            store.set("icx_time_travel_done", "1")
+    return out
+
+
 def long_run_bench(a, device):
     """SURVEY 8(d) protocol (100 warm-up + 1000 timed ticks) as far as a wall-clock budget allows: the scene of the headline
     (config 3, full size) and the 64 K scene of config 2, ticked from the drop; per window of 25 ticks the mean tick time, the
@@ -487,6 +568,10 @@ def main():
     ap.add_argument("--pipeline-bodies", type=int, default=100000, help="config-5 bodies per timeslice (0 = skip that section)")
     ap.add_argument("--pipeline-ticks", type=int, default=12)
     ap.add_argument("--pipeline-delay", type=int, default=5)
+    ap.add_argument("--tt-timeslices", type=int, default=7, help="config 5 with time travellers: timeslices (0 = skip that section)")
+    ap.add_argument("--tt-travellers", type=int, default=64)
+    ap.add_argument("--tt-delay", type=int, default=20, help="timeslice delay in ticks (config 5 as written: 225)")
+    ap.add_argument("--tt-ticks", type=int, default=50)
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3) if a.impl == "ours" else a.warmup
 
@@ -610,6 +695,11 @@ def main():
     if a.pipeline_bodies > 0:
         tsp = timeslice_pipeline_bench(a.pipeline_bodies, a.pipeline_ticks, a.pipeline_delay, rank, world_size, local_rank, barrier)
 
+    tt = None
+    if a.pipeline_bodies > 0 and a.tt_timeslices > 1:
+        tt = time_travel_bench(a.pipeline_bodies, a.tt_timeslices, a.tt_travellers, a.tt_delay, a.tt_ticks, rank, world_size, local_rank, barrier)
+        barrier()
+
     cpu = None
     if rank == 0 and world_size == 1 and not a.no_cpu:          # reported at N = 1 only (the reference arm covers every N)
         cores = os.cpu_count() or 1
@@ -644,6 +734,7 @@ def main():
                 "behaviors": beh,
                 "worldline_batch": wlb,
                 "timeslice_pipeline": tsp,
+                "time_travel": tt,
                 "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if world_size > 1:

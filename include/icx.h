@@ -286,6 +286,23 @@ ICX_API int icx_bodies_update(IcxWorld* w, uint32_t count, const uint32_t* index
 ICX_API int icx_world_clone(IcxWorld* src, IcxWorld* dst, const uint8_t* has_future, uint32_t* n_cloned);
 
 /*
+ * Entity lifecycle on the device: Cosmos::register_entity / condemn_entity as the timeline's ENTITY_CREATED / ENTITY_REMOVED
+ * handlers (source/server/server_network_dynamo.cpp:422-463) and the arrival of a time traveller (:748-812) call them.
+ * The new rows come from the host; the entities the world already holds never leave the device: they are gathered into the
+ * new submission order (ascending ids when the live ids are ascending, else the new rows go last) and re-imported there, so
+ * that everything derived from the row order is what icx_bodies_upload of the merged arrays would have built.  An id that
+ * exists already is left alone (:431-437), removing an id that is not there does nothing.  The coherency is kept.
+ * Row indices of entities behind an inserted / removed row change: host-side row tables must be refreshed
+ * (icx_entity_ids_fetch).  Synchronous.
+ */
+ICX_API int icx_entities_create(IcxWorld* w, uint32_t count, const IcxEntity* entity, const IcxTransform* T, const IcxPhysics* P,
+                                const uint8_t* has_physics, const IcxColliderComponent* C, const uint8_t* tstate, const uint16_t* tcoh,
+                                uint32_t* n_created);
+ICX_API int icx_entities_remove(IcxWorld* w, uint32_t count, const IcxEntity* entity, uint32_t* n_removed);
+/* The ids of the world's entities in row order (n_out = their count; at most `cap` are written). */
+ICX_API int icx_entity_ids_fetch(IcxWorld* w, IcxEntity* out, size_t cap, size_t* n_out);
+
+/*
  * ParallelCosmosContext::extract_entity_updates (:171-423, entity loop :206-272): write every
  * temporal entity of the parallel world `par` back into `dst` under its id with the causal
  * chain-link decremented (:212), all components (:252); the entity's timestream state follows if
@@ -440,8 +457,9 @@ ICX_API int icx_breakpoint_clear(IcxTimeline* tl);
  * physics path has none).  *applied = 1 if a record was applied.  Asynchronous on the world's stream. */
 ICX_API int icx_replay(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, int mode, int* applied);
 
-/* Entities (and collider rows) replays from this ring have skipped so far because the recorded id / packet structure was not
- * the receiving entity's.  Synchronises the device. */
+/* Entities replays from this ring have left alone so far because the record held nothing addressed to their id, plus collider
+ * rows whose packet structure was not the receiving entity's.  (A recorded row whose entity does not exist in the receiving
+ * cosmos is a stream nobody pops: not counted.)  Synchronises the device. */
 ICX_API int icx_timeline_id_mismatches(IcxTimeline* tl, uint64_t* total);
 
 /* Divergence scan: live origins against the record stamped `coherency`, with the reference's

@@ -57,9 +57,142 @@ cudaError_t xcopy(IcxWorld* dst, void* d, IcxWorld* src, const void* s, size_t b
     return cudaMemcpyPeerAsync(d, dst->device, s, src->device, bytes, dst->stream);
 }
 
+// ---- entity lifecycle on the device (Cosmos::register_entity / condemn_entity as the timeline's ENTITY_CREATED / ENTITY_REMOVED
+// handlers call them, server_network_dynamo.cpp:422-463; arrivals of time travellers, :748-812) ----
+// Rows [n_old, n_old + n_app) of the AoS mirror and of in.ts hold the entities to add.  order[i] = the row (old or appended)
+// that becomes row i of the new submission order.  The rows are gathered on the device into that order and re-imported like a
+// fresh submission: existing entities never cross PCIe, and everything derived from the row order (packets, grid, candidate
+// lists, collider-row versions) is rebuilt exactly as icx_bodies_upload of the merged arrays would build it.
+int restructure(IcxWorld* w, const std::vector<uint32_t>& order)
+{
+    const uint32_t n_new = (uint32_t)order.size();
+    std::vector<uint32_t> ids(n_new);           // (the caller put the ids of appended rows behind the live ones in h_ids)
+    for (uint32_t i = 0; i < n_new; i++) ids[i] = w->h_ids[order[i]];
+    int rc = gather(w, order, 1);               // refreshes the mirror rows of the old entities first; state words travel unchanged
+    if (rc != ICX_OK) return rc;
+    cudaSetDevice(w->device);
+    cudaStream_t st = w->stream;
+    DeviceWorld& W = w->W;
+    const size_t cap = w->cap_entities;
+    CKW(w, w->st_ts.ensure(cap)); CKW(w, w->st_tc.ensure(cap * 2));
+    CKW(w, w->d_mask.ensure(cap)); CKW(w, w->st_scan.ensure((cap + 4) * 4));
+    if (n_new) {
+        CKW(w, cudaMemcpyAsync(w->mir_ids.ptr, w->cl_ids.ptr, (size_t)n_new * 4, cudaMemcpyDeviceToDevice, st));
+        CKW(w, cudaMemcpyAsync(w->mir_T.ptr, w->cl_T.ptr, (size_t)n_new * sizeof(IcxTransform), cudaMemcpyDeviceToDevice, st));
+        CKW(w, cudaMemcpyAsync(w->mir_hasP.ptr, w->cl_hasP.ptr, n_new, cudaMemcpyDeviceToDevice, st));
+        if (w->have_P) CKW(w, cudaMemcpyAsync(w->mir_P.ptr, w->cl_P.ptr, (size_t)n_new * sizeof(IcxPhysics), cudaMemcpyDeviceToDevice, st));
+        if (w->have_C) CKW(w, cudaMemcpyAsync(w->mir_C.ptr, w->cl_C.ptr, (size_t)n_new * sizeof(IcxColliderComponent), cudaMemcpyDeviceToDevice, st));
+        CKW(w, cudaMemcpyAsync(w->st_ts.ptr, w->cl_ts.ptr, n_new, cudaMemcpyDeviceToDevice, st));
+        CKW(w, cudaMemcpyAsync(w->st_tc.ptr, w->cl_tc.ptr, (size_t)n_new * 2, cudaMemcpyDeviceToDevice, st));
+    }
+    launch_packet_structure(w->have_C ? (const IcxColliderComponent*)w->mir_C.ptr : nullptr, n_new, (uint32_t*)w->st_scan.ptr, W.scan_partial,
+                            (uint8_t*)w->d_mask.ptr, W.first_packet, st);
+    CKW(w, cudaMemsetAsync(W.counters, 0, CTR_TOTAL * sizeof(uint32_t), st));
+    CKW(w, cudaMemsetAsync(W.bm_keep, 0, cap * sizeof(float), st)); CKW(w, cudaMemsetAsync(W.bm_need, 0, cap * sizeof(uint32_t), st));
+    W.n_entities = n_new; w->n_entities = n_new;
+    w->n_projectiles = 0; w->pj_updated = false;
+    w->h_ids = ids; w->masks_on_host = false;
+    Mirror M = mirror(w);
+    if (!w->have_P) M.P = nullptr;
+    launch_import_kernel(W, M, nullptr, M.ids, M.T, M.P, w->have_C ? M.C : nullptr, M.hasP, (const uint8_t*)w->st_ts.ptr,
+                         (const uint16_t*)w->st_tc.ptr, n_new, 1, w->have_C ? 1 : 0, ++w->c_epoch, st);
+    w->pend_any = false;
+    CKW(w, cudaMemcpyAsync(w->h_counters, W.counters, CTR_TOTAL * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    CKW(w, cudaMemcpyAsync(w->h_flags + 1, (uint32_t*)w->st_scan.ptr + n_new, 4, cudaMemcpyDeviceToHost, st));
+    CKW(w, cudaStreamSynchronize(st));
+    CKW(w, cudaGetLastError());
+    const uint32_t np = n_new ? w->h_flags[1] : 0u;
+    if (np > w->cap_packets || np >= (1u << 28)) return cfail(w, ICX_E_CAPACITY, "entity lifecycle: too many active colliders");
+    W.n_packets = np; w->n_packets = np;
+    icx_size_buckets(w);
+    if (!(w->cfg.cell_size > 0)) {                                                  // same rule as icx_bodies_upload
+        float ext; std::memcpy(&ext, &w->h_counters[CTR_EXTENT], 4);
+        if (!(ext > 0)) ext = 1.0f;
+        W.cell_size = (ext + 2.0f * W.margin) * 1.02f; W.inv_cell = 1.0f / W.cell_size;
+    }
+    w->stats.n_entities = n_new; w->stats.n_packets = np;
+    w->have_results = false;
+    return ICX_OK;
+}
+
 } // namespace
 
 extern "C" {
+
+int icx_entities_create(IcxWorld* w, uint32_t count, const IcxEntity* entity, const IcxTransform* T, const IcxPhysics* P,
+                        const uint8_t* has_physics, const IcxColliderComponent* C, const uint8_t* tstate, const uint16_t* tcoh,
+                        uint32_t* n_created)
+{
+    if (!w) return ICX_E_INVALID;
+    if (n_created) *n_created = 0;
+    if (!count) return ICX_OK;
+    if (!entity || !T) return cfail(w, ICX_E_INVALID, "create: null ids / transforms");
+    if ((w->have_P && !P) || (w->have_C && !C)) return cfail(w, ICX_E_INVALID, "create: the world holds physics / collider components, the new rows need them too");
+    const uint32_t n_old = w->n_entities;
+    // an id that exists already is left alone (server_network_dynamo.cpp:431-437 "excessive creation ... ignoring")
+    std::unordered_map<uint32_t, uint32_t> have; have.reserve((size_t)n_old * 2 + count);
+    for (uint32_t j = 0; j < n_old; j++) have.emplace(w->h_ids[j], j);
+    std::vector<uint32_t> take;                                                     // rows of the caller's arrays that are created
+    for (uint32_t i = 0; i < count; i++) if (have.emplace(entity[i], n_old + (uint32_t)take.size()).second) take.push_back(i);
+    const uint32_t n_app = (uint32_t)take.size();
+    if (!n_app) return ICX_OK;
+    if ((size_t)n_old + n_app > w->cap_entities) return cfail(w, ICX_E_CAPACITY, "create: max_entities too small");
+    cudaSetDevice(w->device);
+    cudaStream_t st = w->stream;
+    const size_t cap = w->cap_entities;
+    CKW(w, w->mir_ids.ensure(cap * 4)); CKW(w, w->mir_T.ensure(cap * sizeof(IcxTransform))); CKW(w, w->mir_hasP.ensure(cap));
+    if (w->have_P) CKW(w, w->mir_P.ensure(cap * sizeof(IcxPhysics)));
+    if (w->have_C) CKW(w, w->mir_C.ensure(cap * sizeof(IcxColliderComponent)));
+    std::vector<uint32_t> ts(n_app); std::vector<uint8_t> hp(n_app);
+    w->h_ids.resize(n_old);
+    for (uint32_t a = 0; a < n_app; a++) {                                          // appended behind the live rows (mirror and state word)
+        const uint32_t i = take[a];
+        w->h_ids.push_back(entity[i]);
+        ts[a] = (uint32_t)(tstate ? tstate[i] : ICX_TS_MERGED) | ((uint32_t)(tcoh ? tcoh[i] : 0) << 16);
+        hp[a] = (uint8_t)((has_physics ? has_physics[i] != 0 : P != nullptr) ? 1 : 0);
+        CKW(w, cudaMemcpyAsync((uint32_t*)w->mir_ids.ptr + n_old + a, entity + i, 4, cudaMemcpyHostToDevice, st));
+        CKW(w, cudaMemcpyAsync((IcxTransform*)w->mir_T.ptr + n_old + a, T + i, sizeof(IcxTransform), cudaMemcpyHostToDevice, st));
+        if (w->have_P) CKW(w, cudaMemcpyAsync((IcxPhysics*)w->mir_P.ptr + n_old + a, P + i, sizeof(IcxPhysics), cudaMemcpyHostToDevice, st));
+        if (w->have_C) CKW(w, cudaMemcpyAsync((IcxColliderComponent*)w->mir_C.ptr + n_old + a, C + i, sizeof(IcxColliderComponent), cudaMemcpyHostToDevice, st));
+    }
+    CKW(w, cudaMemcpyAsync((uint8_t*)w->mir_hasP.ptr + n_old, hp.data(), n_app, cudaMemcpyHostToDevice, st));
+    CKW(w, cudaMemcpyAsync(w->W.in.ts + n_old, ts.data(), (size_t)n_app * 4, cudaMemcpyHostToDevice, st));
+    CKW(w, cudaStreamSynchronize(st));                                              // ts / hp are locals
+    // new submission order: ascending ids when the live ones are (std::set<Entity>, ecs/i_synchro.h:48), else appended
+    std::vector<uint32_t> order(n_old + n_app);
+    for (uint32_t i = 0; i < n_old + n_app; i++) order[i] = i;
+    if (std::is_sorted(w->h_ids.begin(), w->h_ids.begin() + n_old))
+        std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return w->h_ids[a] < w->h_ids[b]; });
+    const int rc = restructure(w, order);
+    if (rc == ICX_OK && n_created) *n_created = n_app;
+    return rc;
+}
+
+int icx_entity_ids_fetch(IcxWorld* w, IcxEntity* out, size_t cap, size_t* n_out)
+{
+    if (!w) return ICX_E_INVALID;
+    if (n_out) *n_out = w->n_entities;
+    if (out) std::memcpy(out, w->h_ids.data(), std::min<size_t>(cap, w->n_entities) * sizeof(IcxEntity));
+    return ICX_OK;
+}
+
+int icx_entities_remove(IcxWorld* w, uint32_t count, const IcxEntity* entity, uint32_t* n_removed)
+{
+    if (!w) return ICX_E_INVALID;
+    if (n_removed) *n_removed = 0;
+    if (!count) return ICX_OK;
+    if (!entity) return cfail(w, ICX_E_INVALID, "remove: null ids");
+    std::vector<uint32_t> gone(entity, entity + count);
+    std::sort(gone.begin(), gone.end());
+    std::vector<uint32_t> order; order.reserve(w->n_entities);
+    for (uint32_t j = 0; j < w->n_entities; j++)
+        if (!std::binary_search(gone.begin(), gone.end(), w->h_ids[j])) order.push_back(j);
+    const uint32_t removed = w->n_entities - (uint32_t)order.size();
+    if (!removed) return ICX_OK;                                                    // condemning an entity that is not there does nothing
+    const int rc = restructure(w, order);
+    if (rc == ICX_OK && n_removed) *n_removed = removed;
+    return rc;
+}
 
 int icx_world_clone(IcxWorld* src, IcxWorld* dst, const uint8_t* has_future, uint32_t* n_cloned)
 {

@@ -21,6 +21,8 @@ IcxTimeline through the C ABI) and the CPU restatement on the oracle procedures 
 (tests/cpu_timetravel.py).  Jump events themselves (JUMP_REQUEST / DEPARTURE / ARRIVAL) are host-side in the reference too and
 are scripted: an arrival is a row inserted into the destination timeslice.
 """
+import time
+
 import numpy as np
 
 from . import abi, pipeline, world
@@ -52,13 +54,15 @@ def traveller_row(scene, index, genesis, timeslice):
 
 
 class DeviceBackend:
-    """Timeslice k = one IcxWorld (+ the ring of records its future neighbour pushes); the parallel cosmos = one more world.
-    devices[k] = CUDA device of timeslice k, devices[-1] = device of the parallel cosmos (all in this process)."""
+    """Timeslice k = one IcxWorld (+ the ring of records its future neighbour pushes) on CUDA device devices[k] (all in this
+    process).  The parallel cosmos is one more world on the device of the timeslice it is shadowing: load_and_link and the
+    replay / record at the breakpoint then stay on that GPU (the ring is never read over NVLink), and only the extract into the
+    future neighbour crosses to devices[k - 1] as one peer copy."""
 
     def __init__(self, scenes_per_slice, delay, base=100, devices=None, capacity_slack=8):
         self.n = len(scenes_per_slice)
         self.delay, self.base = delay, base
-        self.devices = devices or [0] * (self.n + 1)
+        self.devices = list(devices) if devices else [0] * self.n
         self.scene = list(scenes_per_slice)
         cap = max(s.n for s in scenes_per_slice) + capacity_slack
         self.cap = cap
@@ -67,8 +71,9 @@ class DeviceBackend:
             self.w[k].upload(self.scene[k])
             self.w[k].set_coherency(pipeline.start_coherency(k, self.n, delay, base))
         self.tl_in = [None] + [world.Timeline(2 * delay + 4, cap, device=self.devices[k]) for k in range(1, self.n)]
-        self.par = world.World(cap, host_timeslice=abi.NULL_TIMESLICE, device=self.devices[self.n])
-        self.par_scene = None
+        self.par = {}                                                       # device -> the parallel cosmos' world there
+        self._pool = None
+        self.keep_parallel_end = True
         self.link = {}
         if any(self.devices[k] != self.devices[k + 1] for k in range(self.n - 1)):
             import torch
@@ -79,7 +84,9 @@ class DeviceBackend:
                                 world.Timeline(2, cap, device=self.devices[k]))
 
     def close(self):
-        for o in self.w + [self.par] + [t for t in self.tl_in if t is not None] + [v[2] for v in self.link.values()]:
+        if self._pool is not None:
+            self._pool.shutdown()
+        for o in self.w + list(self.par.values()) + [t for t in self.tl_in if t is not None] + [v[2] for v in self.link.values()]:
             o.close()
 
     def coherency(self, k):
@@ -115,72 +122,92 @@ class DeviceBackend:
     def state(self, k):
         return self.w[k].download(self.scene[k])
 
-    def arrive(self, k, row):
-        """Entity lifecycle is host-side: the arrival of a traveller is a re-submission of the timeslice's entities."""
-        cur = self.state(k)
-        self.scene[k], at = insert_row(cur, row)
-        c = self.coherency(k)
-        self.w[k].upload(self.scene[k])
-        self.w[k].set_coherency(c)
-        return at
+    def arrive(self, k, rows):
+        """A traveller arrives: icx_entities_create -- the timeslice's own entities stay on the device (the host keeps only the
+        row template: ids, hasP)."""
+        cur = self.scene[k]
+        all_rows = None
+        for row in rows:
+            cur, _ = insert_row(cur, row)
+            all_rows = row if all_rows is None else insert_row(all_rows, row)[0]
+        self.scene[k] = cur
+        assert self.w[k].create_entities(all_rows) == len(rows)
+        assert np.array_equal(self.w[k].entity_ids(), cur.ids)
 
     def has_future(self, k):
         """entity_has_timestream for every entity of timeslice k: the future neighbour pushes its entities at chain-link + 1."""
-        pushed = set(pipeline.past_ids(self.scene[k - 1].ids).tolist())
-        return np.array([int(e) in pushed for e in self.scene[k].ids], np.uint8)
+        return np.isin(self.scene[k].ids, pipeline.past_ids(self.scene[k - 1].ids)).astype(np.uint8)
+
+    def pmap(self, fn, ks):
+        """One phase of a wall tick over the timeslices: concurrently (one host thread per timeslice; the C ABI calls release
+        the GIL and every world has its own device / stream) when they live on different GPUs."""
+        ks = list(ks)
+        if len(set(self.devices)) == 1:
+            return [fn(k) for k in ks]
+        if self._pool is None:
+            from concurrent.futures import ThreadPoolExecutor
+            self._pool = ThreadPoolExecutor(max_workers=self.n)
+        return list(self._pool.map(fn, ks))
 
     # ---- one parallel cycle step: shadow timeslice k, re-simulate up to its future neighbour, extract into it ----
     def cycle_step(self, k):
         tl, src, dst = self.tl_in[k], self.w[k], self.w[k - 1]
+        if self.devices[k] not in self.par:
+            self.par[self.devices[k]] = world.World(self.cap, host_timeslice=abi.NULL_TIMESLICE, device=self.devices[k])
+        par = self.par[self.devices[k]]
         hf = self.has_future(k)
+        t0 = time.perf_counter()
         tl.set_breakpoint()                                                 # link_timestreams(future stream of k)
-        n = src.clone_into(self.par, hf)
-        par_scene = Scene({key: (v[hf.astype(bool) | ((self.scene[k].ids & 15) != 0)] if isinstance(v, np.ndarray) and key in KEYS else v)
-                           for key, v in self.scene[k].items()})
-        assert par_scene.n == n
+        n = src.clone_into(par, hf)
+        par_scene = None
+        if self.keep_parallel_end:                                          # (tests) the parallel cosmos' entities, for the download below
+            keep = hf.astype(bool) | ((self.scene[k].ids & 15) != 0)
+            par_scene = Scene({key: (v[keep] if isinstance(v, np.ndarray) and key in KEYS else v) for key, v in self.scene[k].items()})
+            assert par_scene.n == n
         ints = []
         c, target = self.coherency(k), self.coherency(k - 1)
+        t1 = time.perf_counter()
         while c != target:
-            self.par.replay(tl, c, abi.REPLAY_PARALLEL)                     # pop_timestream_at_breakpoint: consumes old history
-            self.par.record(tl, c, at_breakpoint=True)                      # push_timestream_at_breakpoint: new history
-            self.par.step(DT)
-            ints.append(self.par.interceptions())
+            par.replay(tl, c, abi.REPLAY_PARALLEL)                          # pop_timestream_at_breakpoint: consumes old history
+            par.record(tl, c, at_breakpoint=True)                           # push_timestream_at_breakpoint: new history
+            par.step(DT)
+            ints.append(par.interceptions())
             c = (c + 1) & 0xFFFF
-        end = self.par.download(par_scene)
-        n_ex, n_miss = self.par.extract_into(dst)
+        t2 = time.perf_counter()
+        end = par.download(par_scene) if par_scene is not None else None
+        n_ex, n_miss = par.extract_into(dst)
         tl.clear_breakpoint()
+        t3 = time.perf_counter()
+        self.cycle_split = getattr(self, "cycle_split", []) + [(t1 - t0, t2 - t1, t3 - t2)]
         return {"cloned": n, "extracted": n_ex, "missing": n_miss, "interceptions": ints, "parallel_end": end}
 
 
-def run(backend, wall_ticks, arrivals=(), observe=None):
+def run(backend, wall_ticks, arrivals=(), observe=None, with_states=True):
     """Drive the chain for `wall_ticks` wall ticks.  arrivals: [(wall tick, timeslice, row)].  observe(tick, phase, data) is called
     with what both back ends must agree on.  Returns the number of parallel cycles that ran."""
     cycles = 0
     n = backend.n
+    pmap = getattr(backend, "pmap", None) or (lambda fn, ks: [fn(k) for k in ks])
     for t in range(wall_ticks):
-        for (ta, k, row) in arrivals:
-            if ta == t:
-                backend.arrive(k, row)
+        for k in range(n):
+            rows = [row for (ta, ka, row) in arrivals if ta == t and ka == k]
+            if rows:
+                backend.arrive(k, rows)
         # fork ageing of the PREVIOUS tick decided whether a resolution is needed; the cycle runs before this tick's networker
         need = getattr(backend, "_need", False)
         if need:
+            t0 = time.perf_counter()
             results = [backend.cycle_step(k) for k in range(n - 1, 0, -1)]  # INIT to the past-most timeslice, then down the chain
+            backend.cycle_seconds = getattr(backend, "cycle_seconds", []) + [time.perf_counter() - t0]
             cycles += 1
             backend._need = False
             if observe:
                 observe(t, "cycle", results)
-        for k in range(n):
-            backend.replay(k)                                               # phase 2
-        for k in range(n):
-            backend.record_to_past(k)                                       # phase 4
-        need = False
-        ages = []
-        for k in range(n):
-            promoted, nd = backend.fork_age(k)                              # phase 5
-            ages.append((promoted, nd))
-            need |= nd
-        backend._need = need
-        ints = [backend.step(k) for k in range(n)]                          # physicser
+        pmap(backend.replay, range(n))                                      # phase 2
+        pmap(backend.record_to_past, range(n))                              # phase 4
+        ages = [tuple(a) for a in pmap(backend.fork_age, range(n))]         # phase 5
+        backend._need = any(nd for _, nd in ages)
+        ints = pmap(backend.step, range(n))                                 # physicser
         if observe:
-            observe(t, "tick", {"ages": ages, "interceptions": ints, "states": [backend.state(k) for k in range(n)]})
+            observe(t, "tick", {"ages": ages, "interceptions": ints, "states": [backend.state(k) for k in range(n)] if with_states else None})
     return cycles

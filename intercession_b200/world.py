@@ -271,6 +271,29 @@ class World:
             raise IcxError(rc, self.lib.icx_last_error(dst.handle).decode())
         return n.value, miss.value
 
+    # ---- entity lifecycle (Cosmos::register_entity / condemn_entity) ----
+    def create_entities(self, rows):
+        """Add the entities of the Scene `rows`; the ones the world holds stay on the device.  Returns how many were new."""
+        n = C.c_uint32(0)
+        self._ck(self.lib.icx_entities_create(self.handle, rows.n, abi.ptr(np.ascontiguousarray(rows.ids, np.uint32)), abi.ptr(rows.T), abi.ptr(rows.P),
+                                              abi.ptr(rows.hasP), abi.ptr(rows.C), abi.ptr(rows.tstate), abi.ptr(rows.tcoh), C.byref(n)))
+        self.n = len(self.entity_ids())
+        return n.value
+
+    def remove_entities(self, ids):
+        ids = np.ascontiguousarray(ids, np.uint32)
+        n = C.c_uint32(0)
+        self._ck(self.lib.icx_entities_remove(self.handle, len(ids), abi.ptr(ids), C.byref(n)))
+        self.n = len(self.entity_ids())
+        return n.value
+
+    def entity_ids(self):
+        k = C.c_size_t(0)
+        self.lib.icx_entity_ids_fetch(self.handle, None, 0, C.byref(k))
+        out = np.zeros(k.value, np.uint32)
+        self.lib.icx_entity_ids_fetch(self.handle, abi.ptr(out), len(out), C.byref(k))
+        return out
+
     def _ck_tl(self, tl, rc):
         if rc != abi.OK:
             raise IcxError(rc, (self.lib.icx_timeline_last_error(tl.handle) or self.lib.icx_last_error(self.handle)).decode())

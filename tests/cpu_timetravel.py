@@ -58,13 +58,12 @@ class CpuBackend:
     def state(self, k):
         return self.scene[k].copy()                                         # extract mutates the future neighbour's scene in place
 
-    def arrive(self, k, row):
-        self.scene[k], at = timetravel.insert_row(self.scene[k], row)
-        return at
+    def arrive(self, k, rows):
+        for row in rows:
+            self.scene[k], _ = timetravel.insert_row(self.scene[k], row)
 
     def has_future(self, k):
-        pushed = set(pipeline.past_ids(self.scene[k - 1].ids).tolist())
-        return np.array([int(e) in pushed for e in self.scene[k].ids], np.uint8)
+        return np.isin(self.scene[k].ids, pipeline.past_ids(self.scene[k - 1].ids)).astype(np.uint8)
 
     def cycle_step(self, k):
         tl = self.tl_in[k]

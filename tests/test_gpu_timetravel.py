@@ -38,15 +38,32 @@ def same_scene(a, b, what):
     assert np.array_equal(a.tstate, b.tstate) and np.array_equal(a.tcoh, b.tcoh), what
 
 
-def test_traveller_forks_its_victims_and_the_parallel_cosmos_resolves_them(built):
+def _device_layouts():
+    import torch
+    out = [pytest.param([0, 0, 0], id="one-gpu")]
+    if torch.cuda.is_available() and torch.cuda.device_count() >= 2:
+        out.append(pytest.param([0, 1, 0], id="two-gpus"))          # every link and every extract crosses NVLink
+    return out
+
+
+# 150 bodies, genesis ids < 255: the CPU side keeps its records in the reference's REAL EntityTimestreamMap / TsBreakpointQueue
+# (16-bit Entity); 500 bodies, traveller genesis 2000: in their restatement (pinned to them by tests/test_timeline_oracle.py)
+@pytest.mark.parametrize("n_bodies,genesis", [(150, 240), (500, 2000)], ids=["reference-containers", "wide-ids"])
+@pytest.mark.parametrize("devices", _device_layouts())
+def test_traveller_forks_its_victims_and_the_parallel_cosmos_resolves_them(built, devices, n_bodies, genesis):
+    import refs
     n_ts, delay, ticks = 3, 4, 38
-    chain = make_chain(500, n_ts)
-    # the traveller: a copy of body 100 of the past-most timeslice, pushed 0.3 units into it, arriving at wall tick 3
-    row = timetravel.traveller_row(chain[n_ts - 1], 6 + 100, genesis=2000, timeslice=n_ts - 1)
+    chain = make_chain(n_bodies, n_ts)
+    # the traveller: a copy of a box of the past-most timeslice, pushed 0.3 units into it, arriving at wall tick 3
+    kinds = chain[0].C["colliders"]["colliderType"][:, 0]
+    twin = next(i for i in range(6 + n_bodies // 5, chain[0].n) if kinds[i] == abi.COLLIDER_BOX)
+    row = timetravel.traveller_row(chain[n_ts - 1], twin, genesis=genesis, timeslice=n_ts - 1)
     row.T["origin"][0, 0] += np.float32(0.3)
     arrivals = [(3, n_ts - 1, row)]
-    dev = timetravel.DeviceBackend(chain, delay)
+    dev = timetravel.DeviceBackend(chain, delay, devices=devices)
     cpu = CpuBackend(chain, delay)
+    if genesis < 255 and refs.ref() is not None:
+        assert cpu.containers == "icxref"
     log = {"dev": [], "cpu": []}
     try:
         cd = timetravel.run(dev, ticks, arrivals, lambda t, ph, d: log["dev"].append((t, ph, d)))

@@ -1,0 +1,47 @@
+"""CPU: the time-travel schedule (intercession_b200/timetravel.py run()) over the CPU back end alone -- the oracle procedures,
+the reference's real EntityTimestreamMap / TsBreakpointQueue (oracle/_ref) and the pinned clone oracle.  What the reference's
+chain of events must produce is asserted on its own here; tests/test_gpu_timetravel.py then holds the device to it
+tick by tick."""
+import numpy as np
+
+from intercession_b200 import abi, timetravel
+from cpu_timetravel import CpuBackend
+from test_gpu_timetravel import make_chain
+
+
+def test_one_traveller_one_cycle_on_the_reference_containers():
+    import refs
+    n_ts, delay = 3, 4
+    chain = make_chain(150, n_ts)
+    kinds = chain[0].C["colliders"]["colliderType"][:, 0]
+    twin = next(i for i in range(36, chain[0].n) if kinds[i] == abi.COLLIDER_BOX)
+    row = timetravel.traveller_row(chain[n_ts - 1], twin, genesis=240, timeslice=n_ts - 1)
+    row.T["origin"][0, 0] += np.float32(0.3)
+    cpu = CpuBackend(chain, delay)
+    if refs.ref() is not None:
+        assert cpu.containers == "icxref"
+    log = []
+    try:
+        cycles = timetravel.run(cpu, 34, [(3, n_ts - 1, row)], lambda t, ph, d: log.append((t, ph, d)))
+    finally:
+        cpu.close()
+    ticks = [(t, d) for t, ph, d in log if ph == "tick"]
+    # the traveller exists in the past-most timeslice only, and only there anything is intercepted
+    assert all(len(d["interceptions"][0]) == 0 and len(d["interceptions"][1]) == 0 for _, d in ticks)
+    first = next(t for t, d in ticks if len(d["interceptions"][2]))
+    assert first >= 3
+    # forking -> forked 13 ticks after the first interception, resolution needed 13 ticks after that (server_network_dynamo.cpp:681-705)
+    promoted = next(t for t, d in ticks if d["ages"][2][0] > 0)
+    needed = next(t for t, d in ticks if d["ages"][2][1])
+    assert promoted == first + 13 and needed == promoted + 13
+    # ... and the cycle runs at the start of the next wall tick, down the whole chain
+    assert cycles == 1
+    (tc, _, res), = [e for e in log if e[1] == "cycle"]
+    assert tc == needed + 1 and len(res) == n_ts - 1
+    for r in res:
+        assert r["cloned"] == chain[0].n                       # the traveller (chain-link 0, no future timestream) is not cloned
+        assert r["extracted"] == 150 and r["missing"] == 0     # every temporal body goes up the chain at chain-link - 1
+        assert len(r["interceptions"]) == delay                # re-simulated up to the future neighbour's coherency
+    # load_and_link reset the source timeslice: nothing is forked right after the cycle
+    after = next(d for t, d in ticks if t == tc)
+    assert (after["states"][2].tstate != abi.TS_FORKED).all()
