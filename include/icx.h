@@ -482,15 +482,49 @@ ICX_API int icx_divergence_scan_fetch(IcxTimeline* tl, uint32_t n_worldlines, ui
  * With both out-pointers NULL the call only enqueues the promotion kernel (no host round trip). */
 ICX_API int icx_fork_age(IcxWorld* w, uint32_t* n_promoted, int* resolution_needed);
 
+/*
+ * Event records in the timeline: what a timeslice pushes into its past besides ENTITY_UPDATE -- ENTITY_CREATED / ENTITY_REMOVED
+ * (_entity_created_handler / _entity_removed_handler, server_network_dynamo.cpp:748-811) and JUMP_REQUEST / JUMP_DEPARTURE /
+ * JUMP_ARRIVAL (:878-976, :466-498).  A record is stamped with the coherency it is pushed at, lives in the ring slot of that
+ * tick ON THE DEVICE next to the tick's snapshot, travels inside the same transport buffer (slot_export / slot_import: one
+ * ncclSend per tick carries states, collider rows and events), and comes out of icx_timeline_events_pop in the order the
+ * reference's per-entity streams hand messages out: every record with coherency <= now (cyclic compare), oldest first, those
+ * with coherency < now (plain compare, :391) dropped.  `entity` / `source` are what the RECEIVING cosmos knows them by (the
+ * sender increments the causal chain-link, :767-768).  payload is opaque (JUMP_params: tripId, timesliceDelta, isFocal, ...).
+ * The handlers stay with the host (they call Cosmos::register_entity / condemn_entity = icx_entities_create / _remove).
+ */
+#define ICX_EVENT_ENTITY_CREATED 1
+#define ICX_EVENT_ENTITY_REMOVED 2
+#define ICX_EVENT_JUMP_REQUEST 3
+#define ICX_EVENT_JUMP_DEPARTURE 4
+#define ICX_EVENT_JUMP_ARRIVAL 5
+typedef struct IcxTimelineEvent {
+    uint32_t type;
+    IcxEntity entity;
+    IcxEntity source;
+    uint16_t coherency;     /* written by the push */
+    uint16_t reserved;
+    uint32_t payload[4];
+} IcxTimelineEvent;         /* 32 bytes */
+/* Push `count` records stamped `coherency` (at most ICX_TIMELINE_EVENTS_PER_TICK per tick: ICX_E_CAPACITY beyond).  May be
+ * called before or after the icx_record of the same tick. */
+ICX_API int icx_timeline_event_push(IcxTimeline* tl, uint16_t coherency, const IcxTimelineEvent* events, uint32_t count);
+/* Pop the records that are due at `now` (see above) WITHOUT consuming the ticks' snapshots: call it before icx_replay of
+ * the same tick (ENTITY_CREATED must run before the ENTITY_UPDATE that fills the new entity's components).  At most `cap`
+ * records are written, *n_out = how many were due.  mode as icx_replay (ICX_REPLAY_PARALLEL: behind the breakpoint). */
+ICX_API int icx_timeline_events_pop(IcxTimeline* tl, uint16_t now, int mode, IcxTimelineEvent* out, size_t cap, size_t* n_out);
+
 /* Snapshot transport between timeslices on different GPUs / processes (the future -> past ENTITY_UPDATE
  * stream, server_network_dynamo.cpp:642-679): pack the slot stamped `coherency` into / restore it from a
  * caller-owned DEVICE buffer, e.g. the buffer a ncclSend / ncclRecv moves:
- *   [10][n] float4 state | [n] uint32 id (padded to 16 B) | 16-byte header {collider rows, 0, 0, 0} | rows x 176 B {sender row, id, ColliderComponent}
+ *   [10][n] float4 state | [n] uint32 id (padded to 16 B) | header {collider rows, events, 0, 0} + 32 event records of 32 B |
+ *   rows x 176 B {sender row, id, ColliderComponent}
  * ICX_SNAPSHOT_CAPACITY(n, rows) is the buffer size for n entities and up to `rows` changed colliders.  `stream` is a
  * cudaStream_t (NULL = default stream); both calls are ASYNCHRONOUS on it and ordered against the recording / replaying
  * worlds' streams by events, so a timeslice needs no host synchronisation per tick. */
 #define ICX_SNAPSHOT_BYTES 164
-#define ICX_SNAPSHOT_HEADER_BYTES 16
+#define ICX_TIMELINE_EVENTS_PER_TICK 32
+#define ICX_SNAPSHOT_HEADER_BYTES (16 + 32 * ICX_TIMELINE_EVENTS_PER_TICK)
 #define ICX_SNAPSHOT_DELTA_BYTES 176
 #define ICX_SNAPSHOT_DENSE_BYTES(n) ((size_t)(n) * 160 + (((size_t)(n) * 4 + 15) & ~(size_t)15))     /* the id array is padded to 16 bytes */
 #define ICX_SNAPSHOT_CAPACITY(n, rows) (ICX_SNAPSHOT_DENSE_BYTES(n) + ICX_SNAPSHOT_HEADER_BYTES + (size_t)(rows) * ICX_SNAPSHOT_DELTA_BYTES)

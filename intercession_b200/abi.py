@@ -55,6 +55,9 @@ ground_dt = np.dtype([("entity", "<u4"), ("normal", "<f4", 3), ("dist", "<f4"), 
 assert ground_dt.itemsize == 32
 interception_dt = np.dtype([("agent", "<u4"), ("recipient", "<u4")])
 pair_dt = np.dtype([("a", "<u4"), ("b", "<u4")])
+event_dt = np.dtype([("type", "<u4"), ("entity", "<u4"), ("source", "<u4"), ("coherency", "<u2"), ("reserved", "<u2"), ("payload", "<u4", 4)])
+assert event_dt.itemsize == 32
+EVENT_ENTITY_CREATED, EVENT_ENTITY_REMOVED, EVENT_JUMP_REQUEST, EVENT_JUMP_DEPARTURE, EVENT_JUMP_ARRIVAL = 1, 2, 3, 4, 5
 
 COLLIDER_NONE, COLLIDER_BOX, COLLIDER_SPHERE, COLLIDER_RAY = 0, 1, 2, 3
 COLLISION_NOOP, COLLISION_RIGID, COLLISION_SPRING, COLLISION_FORCE = 0, 1, 2, 3
@@ -64,7 +67,8 @@ F_SPHERE_SPHERE, F_NO_GRAVITY, F_LANE_ROUNDS = 1, 2, 4
 CONTACT_RESPONDED, CONTACT_BEHAVIORS_A, CONTACT_BEHAVIORS_B = 1, 2, 4
 OK, E_INVALID, E_CUDA, E_CAPACITY, E_NOMEM, E_STATE = 0, 1, 2, 3, 4, 5
 REPLAY_SERVER, REPLAY_PARALLEL = 0, 1
-SNAPSHOT_BYTES, SNAPSHOT_HEADER_BYTES, SNAPSHOT_DELTA_BYTES = 164, 16, 176
+TIMELINE_EVENTS_PER_TICK = 32
+SNAPSHOT_BYTES, SNAPSHOT_HEADER_BYTES, SNAPSHOT_DELTA_BYTES = 164, 16 + 32 * TIMELINE_EVENTS_PER_TICK, 176
 RECORD_AT_BREAKPOINT, RECORD_KEEP_LINK = 1, 2
 
 
@@ -190,6 +194,8 @@ SIGNATURES = {
     "icx_record_at_breakpoint": (C.c_int, [_vp, _vp, C.c_uint16]),
     "icx_record_ex": (C.c_int, [_vp, _vp, C.c_uint16, _u32]),
     "icx_timeline_id_mismatches": (C.c_int, [_vp, C.POINTER(C.c_uint64)]),
+    "icx_timeline_event_push": (C.c_int, [_vp, C.c_uint16, _vp, _u32]),
+    "icx_timeline_events_pop": (C.c_int, [_vp, C.c_uint16, C.c_int, _vp, _sz, _psz]),
     "icx_divergence_scan_enqueue": (C.c_int, [_vp, _vp, C.c_uint16, _u32]),
     "icx_divergence_scan_fetch": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp, C.c_int]),
     "icx_breakpoint_set": (C.c_int, [_vp]),

@@ -34,6 +34,8 @@ using namespace icx;
 
 struct DeltaRow { uint32_t idx, id; IcxColliderComponent C; };         // 176 B, 16-byte aligned: sender's row (a hint), recorded id (the address)
 static_assert(sizeof(DeltaRow) == ICX_SNAPSHOT_DELTA_BYTES, "delta row layout");
+static_assert(sizeof(IcxTimelineEvent) == 32, "event record layout");
+static_assert(16 + 32 * ICX_TIMELINE_EVENTS_PER_TICK == ICX_SNAPSHOT_HEADER_BYTES, "transport header = row count word + events block");
 
 struct IcxTimeline {
     int device = 0, sms = 148;
@@ -54,6 +56,13 @@ struct IcxTimeline {
     uint32_t* seen = nullptr;           // [n_max]: DeviceWorld::c_ver of each entity at its last collected row
     const IcxWorld* last_recorder = nullptr; uint32_t last_epoch = 0;
     unsigned long long* d_mismatch = nullptr;   // entities a replay skipped because the recorded id is not theirs
+    // event records (ENTITY_CREATED / REMOVED, JUMP_*): one block per slot on the device (it travels in the transport header),
+    // mirrored in pinned host memory; the slot's snapshot and its events are consumed independently
+    struct EvBlock { uint32_t rows_unused, n_events, pad[2]; IcxTimelineEvent ev[ICX_TIMELINE_EVENTS_PER_TICK]; };
+    EvBlock* d_ev = nullptr; EvBlock* h_ev = nullptr;       // [depth]
+    std::vector<uint8_t> ev_valid, ev_behind, ev_pending;   // pending: the host mirror is being filled by the import's copy (slot_ev)
+    std::vector<uint16_t> ev_stamp;
+    std::vector<uint64_t> ev_seq;
     std::vector<cudaEvent_t> slot_ev;   // slot contents complete (record / import) -- waited on by replay / export on other streams
     // scan outputs (device) + pinned host mirror
     unsigned long long* d_score = nullptr; uint32_t* d_count = nullptr; uint32_t cap_wl = 0;
@@ -425,6 +434,8 @@ int icx_timeline_create(int device, uint32_t depth_ticks, uint32_t n_max, IcxTim
     tl->device = device; tl->depth = depth_ticks; tl->n_max = n_max;
     tl->stamp.assign(depth_ticks, 0); tl->valid.assign(depth_ticks, 0); tl->behind.assign(depth_ticks, 0); tl->count.assign(depth_ticks, 0);
     tl->seq.assign(depth_ticks, 0); tl->delta_n.assign(depth_ticks, 0); tl->slot_ev.assign(depth_ticks, nullptr);
+    tl->ev_valid.assign(depth_ticks, 0); tl->ev_behind.assign(depth_ticks, 0); tl->ev_pending.assign(depth_ticks, 0);
+    tl->ev_stamp.assign(depth_ticks, 0); tl->ev_seq.assign(depth_ticks, 0);
     cudaSetDevice(device);
     cudaDeviceGetAttribute(&tl->sms, cudaDevAttrMultiProcessorCount, device);
     cudaError_t e = cudaMalloc((void**)&tl->state, (size_t)depth_ticks * TL_ARRAYS * n_max * sizeof(float4));
@@ -433,6 +444,10 @@ int icx_timeline_create(int device, uint32_t depth_ticks, uint32_t n_max, IcxTim
     if (e == cudaSuccess) e = cudaMalloc((void**)&tl->d_delta_n, ((size_t)depth_ticks + 1) * sizeof(uint32_t));
     if (e == cudaSuccess) e = cudaMalloc((void**)&tl->d_mismatch, sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc((void**)&tl->d_age, 2 * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&tl->d_ev, (size_t)depth_ticks * sizeof(IcxTimeline::EvBlock));
+    if (e == cudaSuccess) e = cudaMallocHost((void**)&tl->h_ev, (size_t)depth_ticks * sizeof(IcxTimeline::EvBlock));
+    if (e == cudaSuccess) e = cudaMemset(tl->d_ev, 0, (size_t)depth_ticks * sizeof(IcxTimeline::EvBlock));
+    if (e == cudaSuccess) std::memset(tl->h_ev, 0, (size_t)depth_ticks * sizeof(IcxTimeline::EvBlock));
     if (e == cudaSuccess) e = cudaMemset(tl->seen, 0, (size_t)n_max * sizeof(uint32_t));
     if (e == cudaSuccess) e = cudaMemset(tl->d_delta_n, 0, ((size_t)depth_ticks + 1) * sizeof(uint32_t));
     if (e == cudaSuccess) e = cudaMemset(tl->d_mismatch, 0, sizeof(unsigned long long));
@@ -447,8 +462,9 @@ void icx_timeline_destroy(IcxTimeline* tl)
     if (!tl) return;
     cudaSetDevice(tl->device);
     cudaDeviceSynchronize();
-    void* bufs[] = {tl->state, tl->ids, tl->seen, tl->d_delta_n, tl->d_mismatch, tl->delta, tl->d_score, tl->d_count, tl->d_ever, tl->d_age};
+    void* bufs[] = {tl->state, tl->ids, tl->seen, tl->d_delta_n, tl->d_mismatch, tl->delta, tl->d_score, tl->d_count, tl->d_ever, tl->d_age, tl->d_ev};
     for (void* b : bufs) if (b) cudaFree(b);
+    if (tl->h_ev) cudaFreeHost(tl->h_ev);
     for (cudaEvent_t e : tl->slot_ev) if (e) cudaEventDestroy(e);
     for (auto& pair : tl->pev) for (cudaEvent_t e : pair) if (e) cudaEventDestroy(e);
     delete tl;
@@ -497,14 +513,14 @@ int icx_record_at_breakpoint(IcxWorld* w, IcxTimeline* tl, uint16_t coherency)
 int icx_breakpoint_set(IcxTimeline* tl)
 {
     if (!tl) return ICX_E_INVALID;
-    for (uint32_t s = 0; s < tl->depth; s++) tl->behind[s] = tl->valid[s];
+    for (uint32_t s = 0; s < tl->depth; s++) { tl->behind[s] = tl->valid[s]; tl->ev_behind[s] = tl->ev_valid[s]; }
     tl->breakpoint_active = true;
     return ICX_OK;
 }
 int icx_breakpoint_clear(IcxTimeline* tl)
 {
     if (!tl) return ICX_E_INVALID;
-    std::fill(tl->behind.begin(), tl->behind.end(), 0);
+    std::fill(tl->behind.begin(), tl->behind.end(), 0); std::fill(tl->ev_behind.begin(), tl->ev_behind.end(), 0);
     tl->breakpoint_active = false;
     return ICX_OK;
 }
@@ -733,6 +749,59 @@ int icx_fork_age(IcxWorld* w, uint32_t* n_promoted, int* resolution_needed)
 // Both are asynchronous on `stream` (cudaStream_t, NULL = the default stream): the export waits for the
 // record on the recording world's stream through an event, a replay / scan on another stream waits for the
 // import the same way -- no host synchronisation unless the number of collider rows is unknown to the host.
+// ---- event records ----
+// the events block of slot s belongs to the tick stamped `coherency`: a block left by an older tick is emptied
+static void ev_claim(IcxTimeline* tl, int s, uint16_t coherency)
+{
+    if (tl->ev_valid[s] && tl->ev_stamp[s] == coherency) return;
+    tl->h_ev[s].n_events = 0; tl->ev_valid[s] = 0; tl->ev_pending[s] = 0; tl->ev_behind[s] = 0; tl->ev_stamp[s] = coherency;
+}
+
+int icx_timeline_event_push(IcxTimeline* tl, uint16_t coherency, const IcxTimelineEvent* events, uint32_t count)
+{
+    if (!tl || (!events && count)) return ICX_E_INVALID;
+    if (!count) return ICX_OK;
+    const int s = slot_of(tl, coherency);
+    cudaSetDevice(tl->device);
+    if (tl->ev_pending[s]) { TCK(cudaEventSynchronize(tl->slot_ev[s])); tl->ev_pending[s] = 0; }
+    ev_claim(tl, s, coherency);
+    IcxTimeline::EvBlock& b = tl->h_ev[s];
+    if (b.n_events + count > ICX_TIMELINE_EVENTS_PER_TICK) { tl->error = "event_push: more than ICX_TIMELINE_EVENTS_PER_TICK records in one tick"; return ICX_E_CAPACITY; }
+    for (uint32_t i = 0; i < count; i++) { IcxTimelineEvent e = events[i]; e.coherency = coherency; e.reserved = 0; b.ev[b.n_events++] = e; }
+    if (!tl->ev_valid[s]) { tl->ev_valid[s] = 1; tl->ev_seq[s] = tl->next_seq++; tl->ev_behind[s] = 0; }   // (pushed in front of a breakpoint, like a record at it)
+    TCK(cudaMemcpy(tl->d_ev + s, &b, sizeof(b), cudaMemcpyHostToDevice));   // rare and 1 KB: synchronous, so any later export sees it
+    return ICX_OK;
+}
+
+int icx_timeline_events_pop(IcxTimeline* tl, uint16_t now, int mode, IcxTimelineEvent* out, size_t cap, size_t* n_out)
+{
+    if (!tl) return ICX_E_INVALID;
+    if (n_out) *n_out = 0;
+    if (mode != ICX_REPLAY_SERVER && mode != ICX_REPLAY_PARALLEL) return ICX_E_INVALID;
+    std::vector<int> popped;
+    for (uint32_t k = 0; k < tl->depth; k++) {
+        if (!tl->ev_valid[k]) continue;
+        const uint16_t a = now, b = tl->ev_stamp[k];
+        const bool le_now = (a >= b && a - b <= 32768) || (a <= b && b - a > 32768);      // message.h:179-183
+        if (!le_now) continue;
+        const bool behind = tl->breakpoint_active && tl->ev_behind[k];
+        if (mode == ICX_REPLAY_SERVER ? behind : !behind) continue;
+        popped.push_back((int)k);
+    }
+    std::sort(popped.begin(), popped.end(), [&](int x, int y) { return tl->ev_seq[x] < tl->ev_seq[y]; });
+    cudaSetDevice(tl->device);
+    size_t n = 0;
+    for (int k : popped) {
+        if (tl->ev_pending[k]) { TCK(cudaEventSynchronize(tl->slot_ev[k])); tl->ev_pending[k] = 0; }
+        const IcxTimeline::EvBlock& b = tl->h_ev[k];
+        tl->ev_valid[k] = 0; tl->ev_behind[k] = 0;
+        if (tl->ev_stamp[k] < now) continue;                                            // server_network_dynamo.cpp:391 (plain compare)
+        for (uint32_t i = 0; i < std::min<uint32_t>(b.n_events, ICX_TIMELINE_EVENTS_PER_TICK); i++) { if (out && n < cap) out[n] = b.ev[i]; n++; }
+    }
+    if (n_out) *n_out = n;
+    return ICX_OK;
+}
+
 int icx_timeline_slot_export(IcxTimeline* tl, uint16_t coherency, void* device_buffer, size_t capacity_bytes, uint32_t* n_out, void* stream)
 {
     if (!tl || !device_buffer) return ICX_E_INVALID;
@@ -756,7 +825,8 @@ int icx_timeline_slot_export(IcxTimeline* tl, uint16_t coherency, void* device_b
         TCK(cudaMemcpy2DAsync(out, (size_t)n * 16, slot_state(tl, s), (size_t)tl->n_max * 16, (size_t)n * 16, TL_ARRAYS, cudaMemcpyDeviceToDevice, st));
         TCK(cudaMemcpyAsync(out + (size_t)n * 16 * TL_ARRAYS, slot_ids(tl, s), (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
     }
-    TCK(cudaMemsetAsync(out + dense, 0, ICX_SNAPSHOT_HEADER_BYTES, st));
+    if (tl->ev_valid[s] && tl->ev_stamp[s] == coherency) TCK(cudaMemcpyAsync(out + dense, tl->d_ev + s, ICX_SNAPSHOT_HEADER_BYTES, cudaMemcpyDeviceToDevice, st));
+    else TCK(cudaMemsetAsync(out + dense, 0, ICX_SNAPSHOT_HEADER_BYTES, st));
     TCK(cudaMemcpyAsync(out + dense, tl->d_delta_n + s, 4, cudaMemcpyDeviceToDevice, st));
     if (rows) TCK(cudaMemcpyAsync(out + dense + ICX_SNAPSHOT_HEADER_BYTES, tl->delta + (size_t)s * tl->delta_cap, (size_t)rows * sizeof(DeltaRow), cudaMemcpyDeviceToDevice, st));
     return ICX_OK;
@@ -780,6 +850,11 @@ int icx_timeline_slot_import(IcxTimeline* tl, uint16_t coherency, uint32_t n, co
         TCK(cudaMemcpyAsync(slot_ids(tl, s), in + (size_t)n * 16 * TL_ARRAYS, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
     }
     TCK(cudaMemcpyAsync(tl->d_delta_n + s, in + dense, 4, cudaMemcpyDeviceToDevice, st));
+    if (tl->ev_pending[s]) { TCK(cudaEventSynchronize(tl->slot_ev[s])); tl->ev_pending[s] = 0; }
+    TCK(cudaMemcpyAsync(tl->d_ev + s, in + dense, ICX_SNAPSHOT_HEADER_BYTES, cudaMemcpyDeviceToDevice, st));
+    TCK(cudaMemcpyAsync(tl->h_ev + s, in + dense, ICX_SNAPSHOT_HEADER_BYTES, cudaMemcpyDeviceToHost, st));      // pinned: read by events_pop after slot_ev
+    tl->ev_valid[s] = 1; tl->ev_pending[s] = 1; tl->ev_stamp[s] = coherency; tl->ev_seq[s] = tl->next_seq++;
+    tl->ev_behind[s] = tl->breakpoint_active ? 1 : 0;
     if (room) k_copy_rows<<<std::min<int>(tl->sms * 2, (int)((room * 11u + 255u) / 256u)), 256, 0, st>>>(
                   (uint4*)(tl->delta + (size_t)s * tl->delta_cap), (const uint4*)(in + dense + ICX_SNAPSHOT_HEADER_BYTES), tl->d_delta_n + s, room);
     TCK(cudaEventRecord(tl->slot_ev[s], st));

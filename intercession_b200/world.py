@@ -328,6 +328,23 @@ class Timeline:
         if rc != abi.OK:
             raise IcxError(rc, self.lib.icx_timeline_last_error(self.handle).decode())
 
+    def _ck(self, rc):
+        if rc != abi.OK:
+            raise IcxError(rc, self.lib.icx_timeline_last_error(self.handle).decode())
+
+    def push_events(self, coherency, events):
+        """Event records (abi.event_dt) of the tick stamped `coherency`: they live in that tick's ring slot on the device."""
+        events = np.ascontiguousarray(events, abi.event_dt)
+        self._ck(self.lib.icx_timeline_event_push(self.handle, coherency, abi.ptr(events), len(events)))
+
+    def pop_events(self, now, mode=abi.REPLAY_SERVER):
+        out = np.zeros(4 * abi.TIMELINE_EVENTS_PER_TICK, abi.event_dt)
+        n = C.c_size_t(0)
+        self._ck(self.lib.icx_timeline_events_pop(self.handle, now, mode, abi.ptr(out), len(out), C.byref(n)))
+        if n.value > len(out):
+            raise RuntimeError("more event records due than the pop buffer holds")
+        return out[:n.value]
+
     def id_mismatches(self):
         v = C.c_uint64(0)
         self.lib.icx_timeline_id_mismatches(self.handle, C.byref(v))

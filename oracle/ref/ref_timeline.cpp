@@ -30,6 +30,8 @@
 #include "core/cosmos.h"
 #include "spacetime/timejump_conditions.h"
 
+#include <algorithm>
+#include <cstring>
 #include <memory>
 #include <unordered_map>
 #include <unordered_set>
@@ -41,7 +43,10 @@ namespace {
 
 struct RefTimeline {
     EntityTimestreamMap map;
+    EntityTimestreamMap events;     // ENTITY_CREATED / REMOVED / JUMP_* messages: the same real container, keyed by the same ids
 };
+
+inline IcxEntity widen(Entity e) { return e == NULL_ENTITY ? ICX_NULL_ENTITY : (((IcxEntity)(e >> 12) << 28) | ((IcxEntity)((e >> 4) & 0xFFu) << 4) | (e & 0xFu)); }
 
 inline Entity narrow(IcxEntity e) { return (Entity)(((e >> 28) << 12) | (((e >> 4) & 0xFFu) << 4) | (e & 0xFu)); }
 
@@ -56,7 +61,61 @@ void icxref_tl_destroy(void* h) { delete static_cast<RefTimeline*>(h); }
 void icxref_tl_breakpoint(void* h, int set)
 {
     RefTimeline* tl = static_cast<RefTimeline*>(h);
-    if (set) tl->map.set_breakpoints(); else tl->map.remove_breakpoints();
+    if (set) { tl->map.set_breakpoints(); tl->events.set_breakpoints(); } else { tl->map.remove_breakpoints(); tl->events.remove_breakpoints(); }
+}
+
+// Event records as the handlers push them (server_network_dynamo.cpp:748-811, :878-976): REAL EventMessages with the
+// reference's own params structs in the real per-entity streams.  ev->entity / ev->source are already the receiver's ids.
+int icxref_tl_event_push(void* h, uint16_t coherency, const IcxTimelineEvent* ev, uint32_t count, int at_breakpoint)
+{
+    RefTimeline* tl = static_cast<RefTimeline*>(h);
+    for (uint32_t i = 0; i < count; i++) {
+        const Entity e = narrow(ev[i].entity), src = ev[i].source == ICX_NULL_ENTITY ? NULL_ENTITY : narrow(ev[i].source);
+        EventMessage msg(1, coherency);
+        switch (ev[i].type) {
+        case ICX_EVENT_ENTITY_CREATED: { msg.header.id = events::cosmos::ENTITY_CREATED; events::cosmos::ENTITY_CREATED_params p; p.entity = e; p.sign = Signature(ev[i].payload[0]); p.source = src; msg << p; } break;
+        case ICX_EVENT_ENTITY_REMOVED: { msg.header.id = events::cosmos::ENTITY_REMOVED; events::cosmos::ENTITY_REMOVED_params p; p.entity = e; p.source = src; msg << p; } break;
+        default: {
+            msg.header.id = ev[i].type == ICX_EVENT_JUMP_REQUEST ? events::network::JUMP_REQUEST
+                          : ev[i].type == ICX_EVENT_JUMP_DEPARTURE ? events::network::JUMP_DEPARTURE : events::network::JUMP_ARRIVAL;
+            events::network::JUMP_params p; p.entity = e; p.tripId = ev[i].payload[0]; p.timesliceDelta = (int)ev[i].payload[1]; p.isFocal = ev[i].payload[2] != 0;
+            p.sign = Signature(ev[i].payload[3]); msg << p; } break;
+        }
+        if (at_breakpoint) tl->events.push_to_timestream_at_breakpoint(e, msg); else tl->events.push_to_timestream(e, msg);
+    }
+    return 0;
+}
+
+// The pop loop of server_network_dynamo.cpp:377-392 (parallel_network_dynamo.cpp:51-77 at the breakpoint) over the event
+// streams: every stream, every message that is due, stale ones dropped.  Streams are visited in ascending id order here
+// (the reference walks an unordered container); per stream the order is the container's.
+int icxref_tl_events_pop(void* h, uint16_t now, int mode, IcxTimelineEvent* out, size_t cap, size_t* n_out)
+{
+    RefTimeline* tl = static_cast<RefTimeline*>(h);
+    std::vector<Entity> es = tl->events.get_entities_with_streams();
+    std::sort(es.begin(), es.end());
+    size_t n = 0;
+    for (Entity e : es) {
+        EventMessage evnt(1);
+        for (;;) {
+            const bool got = mode == ICX_REPLAY_PARALLEL ? tl->events.pop_from_timestream_at_breakpoint(e, now, evnt) : tl->events.pop_from_timestream(e, now, evnt);
+            if (!got) break;
+            if (evnt.header.coherency < now) continue;                                          // :391
+            IcxTimelineEvent r; std::memset(&r, 0, sizeof(r));
+            r.coherency = evnt.header.coherency;
+            if (evnt.header.id == events::cosmos::ENTITY_CREATED) { events::cosmos::ENTITY_CREATED_params p; evnt >> p; r.type = ICX_EVENT_ENTITY_CREATED; r.entity = widen(p.entity); r.source = widen(p.source); r.payload[0] = (uint32_t)p.sign.to_ulong(); }
+            else if (evnt.header.id == events::cosmos::ENTITY_REMOVED) { events::cosmos::ENTITY_REMOVED_params p; evnt >> p; r.type = ICX_EVENT_ENTITY_REMOVED; r.entity = widen(p.entity); r.source = widen(p.source); }
+            else {
+                events::network::JUMP_params p; evnt >> p;
+                r.type = evnt.header.id == events::network::JUMP_REQUEST ? ICX_EVENT_JUMP_REQUEST : evnt.header.id == events::network::JUMP_DEPARTURE ? ICX_EVENT_JUMP_DEPARTURE : ICX_EVENT_JUMP_ARRIVAL;
+                r.entity = widen(p.entity); r.source = ICX_NULL_ENTITY; r.payload[0] = p.tripId; r.payload[1] = (uint32_t)p.timesliceDelta; r.payload[2] = p.isFocal ? 1u : 0u; r.payload[3] = (uint32_t)p.sign.to_ulong();
+            }
+            if (out && n < cap) out[n] = r;
+            n++;
+        }
+    }
+    if (n_out) *n_out = n;
+    return 0;
 }
 
 // Record every entity at `coherency`.  link_inc: the server increments the causal chain-link of the

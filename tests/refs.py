@@ -151,6 +151,8 @@ _TL_SIGS = {
     "{p}_congruent": (C.c_int, [_u32, _vp, _vp, _vp]),
     "{p}_coherency_ge": (C.c_int, [C.c_uint16, C.c_uint16]),
 }
+REF_SIGS["icxref_tl_event_push"] = (C.c_int, [_vp, C.c_uint16, _vp, _u32, C.c_int])
+REF_SIGS["icxref_tl_events_pop"] = (C.c_int, [_vp, C.c_uint16, C.c_int, _vp, _sz, C.POINTER(_sz)])
 REF_SIGS.update({k.format(p="icxref"): v for k, v in _TL_SIGS.items()})
 ORACLE_SIGS.update({k.format(p="icxo"): v for k, v in _TL_SIGS.items()})
 ORACLE_SIGS["icxo_divergence_scan"] = (C.c_int, [_u32, _vp, _u32, _vp, _u32, _vp, _vp, _vp])
@@ -169,6 +171,17 @@ class CpuTimeline:
 
     def breakpoint(self, on):
         getattr(self.lib, self.p + "_tl_breakpoint")(self.h, 1 if on else 0)
+
+    def push_events(self, coherency, events, at_breakpoint=False):
+        """(reference containers only) REAL EventMessages with the reference's params structs in the real per-entity streams."""
+        events = np.ascontiguousarray(events, abi.event_dt)
+        assert getattr(self.lib, self.p + "_tl_event_push")(self.h, coherency, abi.ptr(events), len(events), 1 if at_breakpoint else 0) == 0
+
+    def pop_events(self, now, mode=0):
+        out = np.zeros(4096, abi.event_dt)
+        n = C.c_size_t(0)
+        assert getattr(self.lib, self.p + "_tl_events_pop")(self.h, now, mode, abi.ptr(out), len(out), C.byref(n)) == 0
+        return out[:n.value]
 
     def record(self, s, coherency, at_breakpoint=False, link_inc=True, colliders=True):
         """ENTITY_UPDATE of every entity with ALL its components (Transform, Physics, ColliderComponent)."""
