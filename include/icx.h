@@ -477,6 +477,18 @@ ICX_API int icx_divergence_scan_enqueue(IcxWorld* w, IcxTimeline* tl, uint16_t c
 ICX_API int icx_divergence_scan_fetch(IcxTimeline* tl, uint32_t n_worldlines, uint8_t* flags, uint8_t* flags_ever,
                               uint32_t* incongruent, double* score, int reset_ever);
 
+/* icx_divergence_scan without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, same results as icx_divergence_scan (synchronous; flags / incongruent / score may each be NULL), but the
+ * per-world-line accumulators live in a file-scope `static __device__` array of ICX_SCAN_STATIC_MAX_WORLDLINES entries
+ * (96 KB, held by every GPU that loads the library until exit) instead of the timeline's lazily grown buffers: the call
+ * performs no cudaMalloc / cudaFree and no host allocation.  More world-lines than the maximum: ICX_E_CAPACITY.  The array is
+ * shared by every call on that GPU and cleared at the start of each: calls that overlap on one GPU (two worlds on different
+ * streams, two host threads) race -- serialise them.  It does not touch the "ever flagged" bytes of _enqueue / _fetch. */
+#define ICX_SCAN_STATIC_MAX_WORLDLINES 8192
+ICX_API int icx_divergence_scan_static(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, uint32_t n_worldlines,
+                                       uint8_t* flags, uint32_t* incongruent, double* score);
+
 /* Fork ageing (server_network_dynamo.cpp:13-15, :681-705): forking -> forked after 13 ticks;
  * *resolution_needed = some entity has been forked for >= 13 ticks (parallel_notify_divergence).
  * With both out-pointers NULL the call only enqueues the promotion kernel (no host round trip). */

@@ -202,6 +202,7 @@ SIGNATURES = {
     "icx_breakpoint_clear": (C.c_int, [_vp]),
     "icx_replay": (C.c_int, [_vp, _vp, C.c_uint16, C.c_int, C.POINTER(C.c_int)]),
     "icx_divergence_scan": (C.c_int, [_vp, _vp, C.c_uint16, _u32, _vp, _vp, _vp]),
+    "icx_divergence_scan_static": (C.c_int, [_vp, _vp, C.c_uint16, _u32, _vp, _vp, _vp]),
     "icx_fork_age": (C.c_int, [_vp, C.POINTER(_u32), C.POINTER(C.c_int)]),
     "icx_timeline_slot_export": (C.c_int, [_vp, C.c_uint16, _vp, _sz, C.POINTER(_u32), _vp]),
     "icx_timeline_slot_import": (C.c_int, [_vp, C.c_uint16, _u32, _vp, _sz, _vp]),

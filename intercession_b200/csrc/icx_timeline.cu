@@ -716,6 +716,61 @@ int icx_divergence_scan(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, uint32
     return icx_divergence_scan_fetch(tl, n_worldlines, flags, nullptr, incongruent, score, 0);
 }
 
+// ---- the scan without any allocation (no counterpart in the reference) ----
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops): the per-world-line accumulators the
+// scan kernel adds into live in a file-scope device array instead of the timeline's lazily grown buffers.  Every GPU that
+// loads the library holds the array (96 KB) until exit; all calls share it, so calls that overlap on one GPU race.
+static __device__ __align__(256) unsigned char g_scan_scratch[ICX_SCAN_STATIC_MAX_WORLDLINES * 12];   // [MAX] u64 scores, then [MAX] u32 counts
+static void* g_scan_scratch_ptr[64] = {};       // device address of the array per device (the name above is only a host-side stand-in)
+
+int icx_divergence_scan_static(IcxWorld* w, IcxTimeline* tl, uint16_t coherency, uint32_t n_worldlines,
+                               uint8_t* flags, uint32_t* incongruent, double* score)
+{
+    if (!w || !tl || n_worldlines == 0) return ICX_E_INVALID;
+    if (n_worldlines > ICX_SCAN_STATIC_MAX_WORLDLINES) { tl->error = "scan_static: more world-lines than ICX_SCAN_STATIC_MAX_WORLDLINES (the static scratch holds 8192)"; return ICX_E_CAPACITY; }
+    if (w->device < 0 || w->device >= 64) { tl->error = "scan_static: device index beyond the address table"; return ICX_E_INVALID; }
+    const int s = slot_of(tl, coherency);
+    if (!tl->valid[s] || tl->stamp[s] != coherency) { tl->error = "scan: no record stamped with this coherency"; return ICX_E_STATE; }
+    const uint32_t n = w->n_entities, n_snap = tl->count[s], stride = w->W.worldline_stride;
+    if ((stride ? (n + stride - 1) / stride : 1u) != n_worldlines) { tl->error = "scan: n_worldlines does not match the world"; return ICX_E_INVALID; }
+    if (n_snap != n && !(stride && n_snap == stride && stride % SCAN_TILE == 0)) { tl->error = "scan: record must cover the world, or one world-line whose size is a multiple of 1024"; return ICX_E_INVALID; }
+    TCK(cudaSetDevice(w->device));
+    const size_t smem = (size_t)2 * SCAN_STAGES * SCAN_TILE * sizeof(float4) + (SCAN_STAGES + 1) * sizeof(uint64_t);
+    if (!g_scan_scratch_ptr[w->device]) {                                   // set-up, once per device, with that device current
+        void* ptr = nullptr;
+        TCK(cudaGetSymbolAddress(&ptr, g_scan_scratch));
+        TCK(cudaFuncSetAttribute(k_divergence_scan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        g_scan_scratch_ptr[w->device] = ptr;
+    }
+    unsigned long long* d_score = (unsigned long long*)g_scan_scratch_ptr[w->device];
+    uint32_t* d_count = (uint32_t*)((unsigned char*)g_scan_scratch_ptr[w->device] + (size_t)ICX_SCAN_STATIC_MAX_WORLDLINES * 8);
+    cudaStream_t st = w->stream;
+    TCK(cudaStreamWaitEvent(st, tl->slot_ev[s], 0));
+    // the array keeps the last call's sums: both accumulators start at zero
+    TCK(cudaMemsetAsync(d_score, 0, (size_t)n_worldlines * 8, st)); TCK(cudaMemsetAsync(d_count, 0, (size_t)n_worldlines * 4, st));
+    if (n) {
+        const uint32_t n_tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+        const int blocks = (int)std::min<uint32_t>(n_tiles, (uint32_t)(tl->sms * SCAN_CTAS));
+        k_divergence_scan<<<blocks, SCAN_TPB, smem, st>>>(w->W.in.pos, slot_state(tl, s), n, n_snap, stride, d_count, d_score);
+        TCK(cudaGetLastError());
+        w->launches += 1;
+    }
+    // results straight into the caller's arrays (no host allocation either): the fixed-point sums land in `score` and are
+    // converted in place, the counts in `incongruent` -- or, without it, pass through a bounded buffer on the stack
+    uint32_t local_count[256];
+    if (score) TCK(cudaMemcpyAsync(score, d_score, (size_t)n_worldlines * 8, cudaMemcpyDeviceToHost, st));
+    if (incongruent) TCK(cudaMemcpyAsync(incongruent, d_count, (size_t)n_worldlines * 4, cudaMemcpyDeviceToHost, st));
+    TCK(cudaStreamSynchronize(st));
+    if (score) for (uint32_t k = 0; k < n_worldlines; k++) { unsigned long long fx; std::memcpy(&fx, &score[k], 8); score[k] = (double)fx / 65536.0; }
+    if (flags && incongruent) for (uint32_t k = 0; k < n_worldlines; k++) flags[k] = incongruent[k] ? 1 : 0;
+    else if (flags) for (uint32_t k0 = 0; k0 < n_worldlines; k0 += 256) {
+        const uint32_t c = std::min<uint32_t>(256u, n_worldlines - k0);
+        TCK(cudaMemcpy(local_count, d_count + k0, (size_t)c * 4, cudaMemcpyDeviceToHost));
+        for (uint32_t k = 0; k < c; k++) flags[k0 + k] = local_count[k] ? 1 : 0;
+    }
+    return ICX_OK;
+}
+
 int icx_fork_age(IcxWorld* w, uint32_t* n_promoted, int* resolution_needed)
 {
     if (!w) return ICX_E_INVALID;
