@@ -440,12 +440,16 @@ def time_travel_bench(bodies, n_ts, n_travellers, delay, wall_ticks, rank, world
             row = timetravel.traveller_row(chain[k], int(twin), genesis=2000000 + i, timeslice=k)
             row.T["origin"][0, 0] += np.float32(0.3)
             arrivals.append((3 + (i // (n_ts - 1)) % 8, k, row))
-        be = timetravel.DeviceBackend(chain, delay, devices=devices, capacity_slack=n_travellers + 8)
-        be.keep_parallel_end = False
+        be = timetravel.DeviceBackend(chain, delay, devices=devices, capacity_slack=n_travellers + 8, host_rows=False)
         seen = {"ints": 0, "promoted": 0, "cycle_ints": 0, "extracted": 0, "missing": 0}
 
+        stamps, cycle_ticks = [], []
+
         def observe(t, phase, d):
+            if phase == "cycle":
+                cycle_ticks.append(t)
             if phase == "tick":
+                stamps.append(time.perf_counter())
                 seen["ints"] += sum(len(i) for i in d["interceptions"])
                 seen["promoted"] += sum(p for p, _ in d["ages"])
             else:
@@ -463,13 +467,23 @@ def time_travel_bench(bodies, n_ts, n_travellers, delay, wall_ticks, rank, world
         mism = [int(t.id_mismatches()) for t in be.tl_in if t is not None]
         be.close()
         tick_sec = sec - sum(cyc)
+        # wall time of the ticks with neither an arrival nor a cycle in them, before and after the first cycle (after it the
+        # future-most timeslices hold the re-simulated history: delay x (n_ts - 1) more ticks of the drop, bodies piled on the floor)
+        per_tick = np.diff(np.array([t0] + stamps))
+        arrival_ticks = {ta for ta, _, _ in arrivals}
+        first_cycle = cycle_ticks[0] if cycle_ticks else wall_ticks
+        quiet_before = [per_tick[t] for t in range(wall_ticks) if t not in arrival_ticks and t < first_cycle and t >= 2]
+        quiet_after = [per_tick[t] for t in range(wall_ticks) if t not in cycle_ticks and t > first_cycle]
         out = {"workload": f"config5: {n_ts} timeslices x {bodies} temporal bodies + 6 walls, {n_travellers} time travellers arriving one timeslice "
                            f"into their past at wall ticks 3-10, timeslice delay {delay} ticks"
                            + ("" if delay >= 225 else " (config 5 says 5 s = 225 ticks: reduced so that the default run stays within minutes; --tt-delay 225 runs it as written)")
                            + f", {wall_ticks} wall ticks; interceptions, fork ageing and the parallel cycle down the whole chain inside the run",
                "n_timeslices": n_ts, "gpus_used": n_dev, "devices": devices, "host": "one process, one thread per timeslice and phase",
                "wall_ticks": wall_ticks, "seconds": round(sec, 4),
-               "wall_ticks_per_s_outside_cycles": round(wall_ticks / tick_sec, 2), "ticks_per_s_per_timeslice": round(wall_ticks / tick_sec, 2),
+               "wall_ticks_per_s_outside_cycles": round(wall_ticks / tick_sec, 2),
+               "ticks_per_s_per_timeslice_before_first_cycle": round(len(quiet_before) / max(sum(quiet_before), 1e-9), 1) if quiet_before else None,
+               "ticks_per_s_per_timeslice_after_first_cycle": round(len(quiet_after) / max(sum(quiet_after), 1e-9), 1) if quiet_after else None,
+               "arrival_ms_per_tick_with_arrivals": round(1e3 * float(np.mean([per_tick[t] for t in sorted(arrival_ticks) if t < wall_ticks])), 2) if arrivals else None,
                "collider_steps_per_s_outside_cycles": round(n_ts * base.n * wall_ticks / tick_sec, 1),
                "parallel_cycles": cycles, "cycle_latency_ms": [round(c * 1e3, 2) for c in cyc],
                "cycle_work": f"{n_ts - 1} x (load_and_link + {delay} re-simulated ticks with replay / record at the breakpoint + extract)",

@@ -44,6 +44,18 @@ def insert_row(scene, row):
     return out, at
 
 
+def insert_rows(scene, rows):
+    """Scene with every entity of the Scene `rows` inserted at its place in ascending id order (one pass per array)."""
+    ids = np.concatenate([scene.ids, rows.ids])
+    order = np.argsort(ids, kind="stable")
+    out = Scene({k: v for k, v in scene.items() if k not in KEYS})
+    for k in KEYS:
+        v = np.empty(scene.n + rows.n, scene[k].dtype)                      # (not np.concatenate: see insert_row)
+        v[:scene.n], v[scene.n:] = scene[k], rows[k]
+        out[k] = v[order]
+    return out
+
+
 def traveller_row(scene, index, genesis, timeslice):
     """A copy of entity `index` arriving as a time traveller: chain-link 0, its own genesis id, merged state."""
     row = Scene({k: scene[k][index:index + 1].copy() for k in KEYS})
@@ -59,11 +71,14 @@ class DeviceBackend:
     replay / record at the breakpoint then stay on that GPU (the ring is never read over NVLink), and only the extract into the
     future neighbour crosses to devices[k - 1] as one peer copy."""
 
-    def __init__(self, scenes_per_slice, delay, base=100, devices=None, capacity_slack=8):
+    def __init__(self, scenes_per_slice, delay, base=100, devices=None, capacity_slack=8, host_rows=True):
+        """host_rows=False: the host keeps only the ids of every timeslice (what a server needs for entity_has_timestream);
+        state() and the parallel cosmos' end state are then not available."""
         self.n = len(scenes_per_slice)
         self.delay, self.base = delay, base
         self.devices = list(devices) if devices else [0] * self.n
         self.scene = list(scenes_per_slice)
+        self.host_rows = host_rows
         cap = max(s.n for s in scenes_per_slice) + capacity_slack
         self.cap = cap
         self.w = [world.World(cap, host_timeslice=k, device=self.devices[k]) for k in range(self.n)]
@@ -73,8 +88,10 @@ class DeviceBackend:
         self.tl_in = [None] + [world.Timeline(2 * delay + 4, cap, device=self.devices[k]) for k in range(1, self.n)]
         self.par = {}                                                       # device -> the parallel cosmos' world there
         self._pool = None
-        self.keep_parallel_end = True
+        self.keep_parallel_end = host_rows
         self.link = {}
+        if not host_rows:
+            self.scene = [Scene(ids=s.ids.copy()) for s in self.scene]
         if any(self.devices[k] != self.devices[k + 1] for k in range(self.n - 1)):
             import torch
             for k in range(self.n - 1):
@@ -123,16 +140,14 @@ class DeviceBackend:
         return self.w[k].download(self.scene[k])
 
     def arrive(self, k, rows):
-        """A traveller arrives: icx_entities_create -- the timeslice's own entities stay on the device (the host keeps only the
+        """Travellers arrive: icx_entities_create -- the timeslice's own entities stay on the device (the host keeps only the
         row template: ids, hasP)."""
-        cur = self.scene[k]
-        all_rows = None
-        for row in rows:
-            cur, _ = insert_row(cur, row)
-            all_rows = row if all_rows is None else insert_row(all_rows, row)[0]
-        self.scene[k] = cur
+        all_rows = rows[0]
+        for row in rows[1:]:
+            all_rows, _ = insert_row(all_rows, row)
+        self.scene[k] = insert_rows(self.scene[k], all_rows) if self.host_rows else Scene(ids=np.sort(np.concatenate([self.scene[k].ids, all_rows.ids])))
         assert self.w[k].create_entities(all_rows) == len(rows)
-        assert np.array_equal(self.w[k].entity_ids(), cur.ids)
+        assert np.array_equal(self.w[k].entity_ids(), self.scene[k].ids)
 
     def has_future(self, k):
         """entity_has_timestream for every entity of timeslice k: the future neighbour pushes its entities at chain-link + 1."""

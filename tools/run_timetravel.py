@@ -28,10 +28,8 @@ for i, twin in enumerate(twins):
     row = timetravel.traveller_row(chain[k], int(twin), genesis=2000000 + i, timeslice=k)
     row.T["origin"][0, 0] += np.float32(0.3)
     arrivals.append((3 + (i // (n_ts - 1)) % 8, k, row))
-be = timetravel.DeviceBackend(chain, delay, capacity_slack=n_trav + 8)
-be.keep_parallel_end = False
+be = timetravel.DeviceBackend(chain, delay, capacity_slack=n_trav + 8, host_rows=False)
 acc = {}
-_state, _upload, _insert = be.state, None, timetravel.insert_row
 
 
 def timed(label, f):
@@ -43,10 +41,8 @@ def timed(label, f):
     return g
 
 
-be.state = timed("arrive.download", be.state)
-timetravel.insert_row = timed("arrive.insert_row", timetravel.insert_row)
 for wk in be.w:
-    wk.upload = timed("arrive.upload", wk.upload)
+    wk.create_entities = timed("arrive.create_entities", wk.create_entities)
 for name in ("replay", "record_to_past", "fork_age", "step", "arrive", "cycle_step"):
     f = getattr(be, name)
 
