@@ -691,6 +691,33 @@ def main():
     e2e_val = world_size * n_colliders * a.e2e_steps / float(e2e_t.item())
     h2d = T.nbytes + P.nbytes
     d2h = T.nbytes + P.nbytes + n_contacts * 48
+    # ---- the same loop with device-shared component pools (host/component_pools.hpp): the device copy is
+    # authoritative between ticks, the host sends only the rows it edited (here 1 % of the entities per step, a behaviours-sized
+    # share) and takes Transform + Physics back in place.  Reported beside e2e, not instead of it. ----
+    rng = np.random.default_rng(5)
+    k_edit = max(1, s.n // 100)
+    Te, _k3 = pinned_like(s.T[:k_edit])
+    Pe, _k4 = pinned_like(s.P[:k_edit])
+    for it in range(2 + a.e2e_steps):
+        if it == 2:
+            barrier()
+            t0 = time.perf_counter()
+        rows = np.sort(rng.choice(s.n, size=k_edit, replace=False)).astype(np.uint32)
+        Te[:] = T[rows]; Pe[:] = P[rows]                  # the host's edit: the rows as it last saw them (gathered like ComponentPools::to_device)
+        w.update(rows, T=Te, P=Pe)
+        w.step(DT)
+        w.download_into(T=T, P=P)
+        n_contacts2 = len(w.contacts())
+    barrier()
+    pools_sec = time.perf_counter() - t0
+    pools_t = torch.tensor([pools_sec], dtype=torch.float64, device="cuda")
+    if world_size > 1:
+        dist.all_reduce(pools_t, op=dist.ReduceOp.MAX)
+    e2e_pools = {"value": world_size * n_colliders * a.e2e_steps / float(pools_t.item()), "unit": UNIT,
+                 "h2d_bytes_per_step": int(k_edit * (4 + 148)), "d2h_bytes_per_step": int(T.nbytes + P.nbytes + n_contacts2 * 48),
+                 "what": "device-shared component pools: 1 % of the rows edited by the host and resubmitted per step (icx_bodies_update with a row list), "
+                         "Transform + Physics of every entity read back in place; C++ form: icx_host::ComponentPools bound to PhysicsDynamo::run_relays "
+                         "(tests/host/test_host_pools.cpp)"}
     tlk = timeline_kernels_bench(w, s.n, peak, local_rank) if (rank == 0 and not a.no_timeline) else None
     beh = projectile_behaviors_bench(w, s.n, peak) if (rank == 0 and not a.no_timeline) else None
     barrier()
@@ -742,6 +769,7 @@ def main():
                                         "rows": per_rank}},
                 "clocks": clk.summary(), "roofline": roofline,
                 "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+                "e2e_device_shared_pools": e2e_pools,
                 "gpu_launches": int(launches1 - launches0),
                 "long_run": long_run,
                 "timeline_kernels": tlk,

@@ -285,6 +285,13 @@ ICX_API int icx_bodies_update(IcxWorld* w, uint32_t count, const uint32_t* index
  */
 ICX_API int icx_world_clone(IcxWorld* src, IcxWorld* dst, const uint8_t* has_future, uint32_t* n_cloned);
 
+/* Page-locked host memory for component storage that is handed to icx_bodies_upload / _update / _download every tick (the
+ * copies then run at full PCIe rate and asynchronously; with pageable memory the driver stages them).  For hosts that do
+ * not link the CUDA runtime themselves (icx_host::ComponentPools, host/component_pools.hpp, keeps its rows in it).
+ * NULL when the allocation fails or no device is present. */
+ICX_API void* icx_host_alloc(size_t bytes);
+ICX_API void icx_host_free(void* p);
+
 /*
  * Entity lifecycle on the device: Cosmos::register_entity / condemn_entity as the timeline's ENTITY_CREATED / ENTITY_REMOVED
  * handlers (source/server/server_network_dynamo.cpp:422-463) and the arrival of a time traveller (:748-812) call them.

@@ -208,6 +208,8 @@ SIGNATURES = {
     "icx_timeline_slot_import": (C.c_int, [_vp, C.c_uint16, _u32, _vp, _sz, _vp]),
     "icx_world_clone": (C.c_int, [_vp, _vp, _vp, C.POINTER(_u32)]),
     "icx_world_extract": (C.c_int, [_vp, _vp, C.POINTER(_u32), C.POINTER(_u32)]),
+    "icx_host_alloc": (C.c_void_p, [_sz]),
+    "icx_host_free": (None, [_vp]),
     "icx_entities_create": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.POINTER(_u32)]),
     "icx_entities_remove": (C.c_int, [_vp, _u32, _vp, C.POINTER(_u32)]),
     "icx_entity_ids_fetch": (C.c_int, [_vp, _vp, C.c_size_t, C.POINTER(C.c_size_t)]),

@@ -320,6 +320,15 @@ void icx_world_destroy(IcxWorld* w)
 
 const char* icx_last_error(const IcxWorld* w) { return w ? w->error.c_str() : "null world"; }
 
+void* icx_host_alloc(size_t bytes)
+{
+    void* p = nullptr;
+    if (icx_device_count() <= 0) return nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void icx_host_free(void* p) { if (p) cudaFreeHost(p); }
+
 int icx_bodies_upload(IcxWorld* w, uint32_t n, const IcxEntity* entity, const IcxTransform* T, const IcxPhysics* P,
                       const uint8_t* has_physics, const IcxColliderComponent* C, const uint8_t* tstate, const uint16_t* tcoh)
 {

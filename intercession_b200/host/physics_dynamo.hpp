@@ -25,6 +25,8 @@
 // real headers).
 #pragma once
 #include <cstdint>
+#include <algorithm>
+#include <cstring>
 #include <functional>
 #include <memory>
 #include <stdexcept>
@@ -33,6 +35,7 @@
 #include <vector>
 
 #include "../../include/icx.h"
+#include "component_pools.hpp"
 
 namespace icx_host {
 
@@ -114,13 +117,17 @@ public:
     void submit(ColliderPacket data) { m_colliders.push_back(data); }
     void run_relays(double deltaTime)
     {
-        gather();
+        if (m_pools) m_pools->to_device(m_world); else gather();
         check(icx_coherency_set(m_world, m_coherency), m_world, "icx_coherency_set");
         m_motionStep->engage(deltaTime);        // Euler then collision, as physics_dynamo.cpp:38-46
         m_collisionStep->engage(deltaTime);
-        scatter();
+        if (m_pools) m_pools->from_device(m_world, m_collidersBack); else scatter();
         replay_upcalls();
     }
+    // Device-shared component storage instead of per-entity packets (host/component_pools.hpp): the synchros have nothing to
+    // submit, run_relays sends the rows the host edited and takes Transform + Physics back in place.  colliders_back: also the
+    // ColliderComponents (minParametricValue of ray colliders is written by the tick).
+    void bind(ComponentPools* pools, bool colliders_back = false) { m_pools = pools; m_collidersBack = colliders_back; }
     void reset_relays() { m_motionStep->clear(); m_collisionStep->clear(); }
 
     // ---- what the reference reaches through Cosmos / EventBroker / BehaviorsComponent ----
@@ -146,37 +153,59 @@ private:
     // one row per entity, in submission (= ascending id) order; packets of one entity share a Transform
     void gather()
     {
-        m_rows.clear(); m_index.clear();
-        auto row_of = [&](TransformComponent* t) -> size_t {
-            auto it = m_index.find(t);
-            if (it != m_index.end()) return it->second;
-            m_index.emplace(t, m_rows.size());
-            m_rows.push_back(Row{t, nullptr, {nullptr, nullptr}, ICX_NULL_ENTITY});
-            return m_rows.size() - 1;
-        };
-        for (auto& p : m_colliders) {                                   // collider_synchro.cpp:28-42: slot 0 then slot 1
-            Row& r = m_rows[row_of(&p.transform)];
-            r.entity = p.collidee;
-            r.col[r.col[0] ? 1 : 0] = &p.collider;
+        // The packets of one frame are the packets of the last one unless entities came or went: the row table (and the
+        // device's packet structure with it) is rebuilt only when the submitted references differ.
+        m_sig.clear();
+        for (auto& p : m_colliders) { m_sig.push_back(&p.transform); m_sig.push_back(&p.collider); m_sig.push_back((const void*)(uintptr_t)p.collidee); }
+        m_sig.push_back(nullptr);
+        for (auto& p : m_physics) { m_sig.push_back(&p.transform); m_sig.push_back(&p.physics); }
+        const bool same_rows = m_uploaded && m_sig == m_sigLast;
+        if (!same_rows) {
+            m_rows.clear(); m_index.clear();
+            auto row_of = [&](TransformComponent* t) -> size_t {
+                auto it = m_index.find(t);
+                if (it != m_index.end()) return it->second;
+                m_index.emplace(t, m_rows.size());
+                m_rows.push_back(Row{t, nullptr, {nullptr, nullptr}, ICX_NULL_ENTITY});
+                return m_rows.size() - 1;
+            };
+            for (auto& p : m_colliders) {                               // collider_synchro.cpp:28-42: slot 0 then slot 1
+                Row& r = m_rows[row_of(&p.transform)];
+                r.entity = p.collidee;
+                r.col[r.col[0] ? 1 : 0] = &p.collider;
+            }
+            for (auto& p : m_physics) m_rows[row_of(&p.transform)].physics = &p.physics;
+            m_rowOf.clear();
+            for (size_t i = 0; i < m_rows.size(); i++) m_rowOf.emplace_back(m_rows[i].entity, i);
+            std::sort(m_rowOf.begin(), m_rowOf.end());
+            m_sigLast = m_sig;
         }
-        for (auto& p : m_physics) m_rows[row_of(&p.transform)].physics = &p.physics;
         const size_t n = m_rows.size();
-        m_ids.resize(n); m_T.resize(n); m_P.resize(n); m_hasP.resize(n); m_C.resize(n); m_ts.resize(n); m_tc.resize(n);
+        m_ids.resize(n); m_T.resize(n); m_P.resize(n); m_hasP.resize(n); m_Cnew.resize(n); m_ts.resize(n); m_tc.resize(n);
+        bool state_changed = false;
         for (size_t i = 0; i < n; i++) {
             const Row& r = m_rows[i];
             m_ids[i] = r.entity; m_T[i] = *r.transform;
             m_hasP[i] = r.physics ? 1 : 0;
             if (r.physics) m_P[i] = *r.physics;
             for (int s = 0; s < ICX_COLLIDERS_PER_ENTITY; s++) {
-                if (r.col[s]) m_C[i].colliders[s] = *r.col[s];
-                else { m_C[i].colliders[s] = Collider{}; m_C[i].colliders[s].isActive = 0; }
+                if (r.col[s]) m_Cnew[i].colliders[s] = *r.col[s];
+                else { std::memset(&m_Cnew[i].colliders[s], 0, sizeof(Collider)); m_Cnew[i].colliders[s] = Collider{}; m_Cnew[i].colliders[s].isActive = 0; }
             }
             std::pair<uint8_t, uint16_t> st{ICX_TS_MERGED, 0};
             if (m_getState && r.entity != ICX_NULL_ENTITY) st = m_getState(r.entity);
+            if (same_rows && (m_ts2[i] != st.first || m_tc2[i] != st.second)) state_changed = true;      // the host changed a timestream state
             m_ts[i] = st.first; m_tc[i] = st.second;
+        }
+        const bool same_colliders = same_rows && m_C.size() == n && std::memcmp(m_C.data(), m_Cnew.data(), n * sizeof(ColliderComponent)) == 0;
+        m_C.swap(m_Cnew);
+        if (same_rows && same_colliders && !state_changed) {            // Transform + Physics only; the ColliderComponents stay resident
+            check(icx_bodies_update(m_world, (uint32_t)n, nullptr, m_T.data(), m_P.data(), nullptr), m_world, "icx_bodies_update");
+            return;
         }
         check(icx_bodies_upload(m_world, (uint32_t)n, m_ids.data(), m_T.data(), m_P.data(), m_hasP.data(), m_C.data(), m_ts.data(), m_tc.data()),
               m_world, "icx_bodies_upload");
+        m_uploaded = true;
     }
     void scatter()
     {
@@ -197,19 +226,21 @@ private:
         check(icx_contacts_fetch(m_world, nullptr, 0, &n), m_world, "icx_contacts_fetch");
         m_contacts.resize(n);
         if (n) check(icx_contacts_fetch(m_world, m_contacts.data(), n, &n), m_world, "icx_contacts_fetch");
-        if (m_onCollision) {
-            std::unordered_map<Entity, size_t> row;
-            for (size_t i = 0; i < m_rows.size(); i++) row[m_rows[i].entity] = i;
+        if (m_onCollision && m_pools) {
             for (const IcxContact& c : m_contacts) {
                 if (!(c.flags & (ICX_CONTACT_BEHAVIORS_A | ICX_CONTACT_BEHAVIORS_B))) continue;
-                const Row& ra = m_rows[row[c.entityA]]; const Row& rb = m_rows[row[c.entityB]];
+                const size_t ra = m_pools->row_of(c.entityA), rb = m_pools->row_of(c.entityB);
+                // the callee gets mutable references, as in the reference: the rows count as edited
+                ColliderPacket A{m_pools->edit_transform(ra), m_pools->edit_colliders(ra).colliders[c.slotA], c.entityA};
+                ColliderPacket B{m_pools->edit_transform(rb), m_pools->edit_colliders(rb).colliders[c.slotB], c.entityB};
+                upcall_pair(A, B, c);
+            }
+        } else if (m_onCollision) {
+            for (const IcxContact& c : m_contacts) {
+                if (!(c.flags & (ICX_CONTACT_BEHAVIORS_A | ICX_CONTACT_BEHAVIORS_B))) continue;
+                const Row& ra = m_rows[row_of_entity(c.entityA)]; const Row& rb = m_rows[row_of_entity(c.entityB)];
                 ColliderPacket A{*ra.transform, *ra.col[packet_slot(ra, c.slotA)], c.entityA}, B{*rb.transform, *rb.col[packet_slot(rb, c.slotB)], c.entityB};
-                if (c.flags & ICX_CONTACT_BEHAVIORS_A) m_onCollision(A, B, c.normal, c.depth, c.point);             // :114-131
-                if (c.flags & ICX_CONTACT_BEHAVIORS_B) {                                                            // :133-155
-                    const float inv_n[3] = {-c.normal[0], -c.normal[1], -c.normal[2]};
-                    const float inv_p[3] = {c.point[0] - c.normal[0] * c.depth, c.point[1] - c.normal[1] * c.depth, c.point[2] - c.normal[2] * c.depth};
-                    m_onCollision(B, A, inv_n, c.depth, inv_p);
-                }
+                upcall_pair(A, B, c);
             }
         }
         if (m_onInterception) {
@@ -218,6 +249,21 @@ private:
             if (n) check(icx_interceptions_fetch(m_world, ev.data(), n, &n), m_world, "icx_interceptions_fetch");
             for (const IcxInterception& e : ev) m_onInterception(e.agent, e.recipient);
         }
+    }
+    void upcall_pair(ColliderPacket& A, ColliderPacket& B, const IcxContact& c)
+    {
+        if (c.flags & ICX_CONTACT_BEHAVIORS_A) m_onCollision(A, B, c.normal, c.depth, c.point);                     // :114-131
+        if (c.flags & ICX_CONTACT_BEHAVIORS_B) {                                                                    // :133-155
+            const float inv_n[3] = {-c.normal[0], -c.normal[1], -c.normal[2]};
+            const float inv_p[3] = {c.point[0] - c.normal[0] * c.depth, c.point[1] - c.normal[1] * c.depth, c.point[2] - c.normal[2] * c.depth};
+            m_onCollision(B, A, inv_n, c.depth, inv_p);
+        }
+    }
+    // entity -> row of the packet path: a sorted table rebuilt only when the submitted references change
+    size_t row_of_entity(Entity e) const
+    {
+        auto it = std::lower_bound(m_rowOf.begin(), m_rowOf.end(), std::make_pair(e, (size_t)0));
+        return it->second;
     }
     struct Row { TransformComponent* transform; PhysicsComponent* physics; Collider* col[2]; Entity entity; };
     // IcxContact::slotX is the ColliderComponent slot; Row::col is filled in submission order
@@ -229,7 +275,12 @@ private:
     std::vector<PhysicsPacket> m_physics;
     std::vector<ColliderPacket> m_colliders;
     std::vector<Row> m_rows;
-    std::unordered_map<TransformComponent*, size_t> m_index;
+    std::unordered_map<TransformComponent*, size_t> m_index;       // used only while the row table is rebuilt
+    std::vector<std::pair<Entity, size_t>> m_rowOf;
+    std::vector<const void*> m_sig, m_sigLast;
+    std::vector<ColliderComponent> m_Cnew;
+    bool m_uploaded = false;
+    ComponentPools* m_pools = nullptr; bool m_collidersBack = false;
     std::vector<Entity> m_ids; std::vector<TransformComponent> m_T; std::vector<PhysicsComponent> m_P; std::vector<uint8_t> m_hasP;
     std::vector<ColliderComponent> m_C; std::vector<uint8_t> m_ts, m_ts2; std::vector<uint16_t> m_tc, m_tc2;
     std::vector<IcxContact> m_contacts;

@@ -82,3 +82,37 @@ def test_cpp_server_runs_config4_and_config5_exchanges_over_nccl(nccl_exe):
     r = subprocess.run([nccl_exe], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "config4 allgather ok" in r.stdout and "config5 send/recv ok applied 1 id_mismatches 0" in r.stdout, r.stdout
+
+
+POOLS_SRC = os.path.join(ROOT, "tests", "host", "test_host_pools.cpp")
+POOLS_EXE = os.path.join(ROOT, "build", "test_host_pools")
+
+
+@pytest.fixture(scope="module")
+def pools_exe(built):
+    libdir = os.path.join(ROOT, "intercession_b200")
+    os.makedirs(os.path.dirname(POOLS_EXE), exist_ok=True)
+    subprocess.run(["g++", "-std=c++17", "-O2", "-Wall", "-Wextra", "-Werror", POOLS_SRC, "-o", POOLS_EXE, "-L", libdir, "-licx",
+                    f"-Wl,-rpath,{libdir}"], check=True)
+    return POOLS_EXE
+
+
+def test_component_pools_compile_and_refuse_without_gpu(pools_exe):
+    from intercession_b200 import abi
+    if abi.load().icx_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    r = subprocess.run([pools_exe, "64", "2"], capture_output=True, text=True)
+    assert r.returncode == 2 and "error" in r.stdout            # pinned rows cannot be allocated: no CPU fallback
+
+
+@pytest.mark.gpu
+def test_component_pools_equal_the_packet_path(pools_exe):
+    """Device-shared pools (only edited rows cross PCIe; create / remove on the device) and the packet path that resubmits
+    every component every tick give byte-identical Transform / Physics rows after every tick."""
+    r = subprocess.run([pools_exe, "4096", "12"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    w = r.stdout.splitlines()[0].split()
+    assert w[0] == "pools" and int(w[2]) == int(w[4]) == 4097 and int(w[6]) == 0            # + 1 created - 1 removed + the floor
+    assert int(w[8]) == 1                                                                   # one full upload: the first tick
+    assert 4097 <= int(w[10]) < 4097 + 12 * 8                                               # afterwards a handful of rows per tick
+    assert r.stdout.splitlines()[2].split()[1] == "1"
