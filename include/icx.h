@@ -285,6 +285,37 @@ ICX_API int icx_bodies_update(IcxWorld* w, uint32_t count, const uint32_t* index
  */
 ICX_API int icx_world_clone(IcxWorld* src, IcxWorld* dst, const uint8_t* has_future, uint32_t* n_cloned);
 
+/*
+ * Static triangle mesh (extension).  NO COUNTERPART IN THE REFERENCE: ColliderType::mesh is commented out there
+ * (source/physics/collider.h:18-29); BASELINE.json's north_star and configs[2] name triangle-mesh colliders, so the
+ * definition is this library's own and its checker is a CPU restatement of that definition
+ * (oracle icxo_mesh_pass: self-oracle, parity unpinned).
+ * A world may hold one mesh: world-space triangles, immutable, infinite mass.  After the pair loop of every collision pass
+ * (icx_collision_engage / icx_step) each entity that has a PhysicsComponent meets the mesh: entities in row order, their
+ * active box / sphere colliders of collision type rigid in slot order, and for each collider the triangles whose bounds
+ * overlap the collider's bounds (taken when the collider's turn starts) in ascending triangle index.  A hit (sphere -
+ * triangle: closest point; box - triangle: 13-axis separating-axis test) is answered with the reference's
+ * rigid_rigid_response (collision_procedures.cpp:636-874) against an immovable body of the mesh's material, so later
+ * triangles see the moved body.  Entities do not interact in this pass.  Contacts: icx_mesh_contacts_fetch, in that order.
+ */
+typedef struct IcxMeshMaterial { float staticFriction, dynamicFriction, restitution; } IcxMeshMaterial;
+typedef struct IcxMeshContact {
+    IcxEntity entity;
+    uint32_t row;           /* the entity's row */
+    uint32_t slot;          /* collider slot */
+    uint32_t triangle;
+    float point[3];         /* on the triangle */
+    float normal[3];        /* from the triangle towards the entity */
+    float depth;
+} IcxMeshContact;           /* 44 bytes */
+/* vertices [n_vertices][3], triangles [n_triangles][3] vertex indices; material NULL = {0.45, 0.45, 0.70} (collider.h:58-92
+ * defaults).  n_triangles == 0 removes the mesh.  Synchronous. */
+ICX_API int icx_mesh_upload(IcxWorld* w, const float* vertices, uint32_t n_vertices, const uint32_t* triangles, uint32_t n_triangles,
+                            const IcxMeshMaterial* material);
+ICX_API int icx_mesh_contacts_fetch(IcxWorld* w, IcxMeshContact* out, size_t cap, size_t* n_out);
+/* device time of the last mesh pass in microseconds (0 if none ran) */
+ICX_API int icx_mesh_kernel_us(IcxWorld* w, float* us);
+
 /* Page-locked host memory for component storage that is handed to icx_bodies_upload / _update / _download every tick (the
  * copies then run at full PCIe rate and asynchronously; with pageable memory the driver stages them).  For hosts that do
  * not link the CUDA runtime themselves (icx_host::ComponentPools, host/component_pools.hpp, keeps its rows in it).

@@ -55,6 +55,9 @@ ground_dt = np.dtype([("entity", "<u4"), ("normal", "<f4", 3), ("dist", "<f4"), 
 assert ground_dt.itemsize == 32
 interception_dt = np.dtype([("agent", "<u4"), ("recipient", "<u4")])
 pair_dt = np.dtype([("a", "<u4"), ("b", "<u4")])
+mesh_contact_dt = np.dtype([("entity", "<u4"), ("row", "<u4"), ("slot", "<u4"), ("triangle", "<u4"), ("point", "<f4", 3), ("normal", "<f4", 3), ("depth", "<f4")])
+assert mesh_contact_dt.itemsize == 44
+mesh_material_dt = np.dtype([("staticFriction", "<f4"), ("dynamicFriction", "<f4"), ("restitution", "<f4")])
 event_dt = np.dtype([("type", "<u4"), ("entity", "<u4"), ("source", "<u4"), ("coherency", "<u2"), ("reserved", "<u2"), ("payload", "<u4", 4)])
 assert event_dt.itemsize == 32
 EVENT_ENTITY_CREATED, EVENT_ENTITY_REMOVED, EVENT_JUMP_REQUEST, EVENT_JUMP_DEPARTURE, EVENT_JUMP_ARRIVAL = 1, 2, 3, 4, 5
@@ -208,6 +211,9 @@ SIGNATURES = {
     "icx_timeline_slot_import": (C.c_int, [_vp, C.c_uint16, _u32, _vp, _sz, _vp]),
     "icx_world_clone": (C.c_int, [_vp, _vp, _vp, C.POINTER(_u32)]),
     "icx_world_extract": (C.c_int, [_vp, _vp, C.POINTER(_u32), C.POINTER(_u32)]),
+    "icx_mesh_upload": (C.c_int, [_vp, _vp, _u32, _vp, _u32, _vp]),
+    "icx_mesh_contacts_fetch": (C.c_int, [_vp, _vp, _sz, _psz]),
+    "icx_mesh_kernel_us": (C.c_int, [_vp, C.POINTER(C.c_float)]),
     "icx_host_alloc": (C.c_void_p, [_sz]),
     "icx_host_free": (None, [_vp]),
     "icx_entities_create": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.POINTER(_u32)]),

@@ -157,6 +157,7 @@ int run_tick(IcxWorld* w, double dt, int do_euler, int do_collide, bool advance_
             w->totals[4] += w->h_counters[CTR_ATTEMPTS] + 1; w->totals[5] += w->h_counters[CTR_DIRTY];
             w->stats.margin = W.margin; w->stats.cell_size = W.cell_size; w->stats.max_neighbors = W.max_neighbors;
             w->have_results = do_collide != 0;
+            if (do_collide) return icx_mesh_pass(w);        // static triangle mesh (extension): after the pair loop, on the swapped state
             return ICX_OK;
         }
         // `in` is untouched: adjust the capacity / margin that was exceeded and run the tick again
@@ -307,6 +308,7 @@ void icx_world_destroy(IcxWorld* w)
                              &w->pj_proj, &w->pj_index, &w->pj_condemned, &w->pj_count,
                              &w->pend_rows, &w->pend_flag, &w->pend_list, &w->pend_count};
     for (auto* b : extra) b->release();
+    icx_mesh_release(w);
     if (w->h_counters) cudaFreeHost(w->h_counters);
     if (w->h_flags) cudaFreeHost(w->h_flags);
     if (w->ev0) cudaEventDestroy(w->ev0);

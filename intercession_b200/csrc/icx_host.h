@@ -13,6 +13,7 @@ void launch_grid(const DeviceWorld& W, cudaStream_t st);      // 4 kernels: scan
 void launch_pairs(const DeviceWorld& W, cudaStream_t st);
 void launch_narrow(const DeviceWorld& W, int blocks, cudaStream_t st);
 int resolve_grid_blocks(int device, int phase);               // co-resident blocks of the persistent resolve kernels (0 = prepare, 1 = rounds)
+void launch_mesh_pass(const DeviceWorld& W, const DeviceMesh& M, cudaStream_t st);
 cudaError_t launch_resolve(const DeviceWorld& W, double dt, int do_euler, int prepare_blocks, int blocks, cudaStream_t st);
 struct Mirror { uint32_t* ids; IcxTransform* T; IcxPhysics* P; IcxColliderComponent* C; uint8_t* hasP; };
 void launch_import_kernel(const DeviceWorld& W, Mirror M, const uint32_t* index, const uint32_t* ids, const IcxTransform* T,
@@ -67,6 +68,11 @@ struct IcxWorld {
     // collider deltas a replay met while their entity was divergent: kept until the entity takes records again (icx_timeline.cu)
     icx::DeviceBuffer pend_rows, pend_flag, pend_list, pend_count;
     bool pend_any = false;
+    // static triangle mesh (extension, icx_mesh.cu): device arrays + the pass's contact list
+    icx::DeviceBuffer mesh_tri, mesh_cell_start, mesh_cell_tri, mesh_contacts, mesh_counter;
+    icx::DeviceMesh mesh = {};
+    bool mesh_ran = false;              // a mesh pass ran in the last collision pass (its contacts are the ones to fetch)
+    cudaEvent_t mesh_ev0 = nullptr, mesh_ev1 = nullptr;
     uint32_t* h_counters = nullptr;     // pinned
     uint32_t* h_flags = nullptr;        // pinned
     IcxStats stats;
@@ -102,3 +108,5 @@ inline void icx_size_buckets(IcxWorld* w)
 
 // make w->active_mask valid (one small device-to-host copy after an upload); ICX_OK or ICX_E_CUDA
 int icx_host_masks(IcxWorld* w);
+int icx_mesh_pass(IcxWorld* w);       // after a successful collision pass (state in W.in)
+void icx_mesh_release(IcxWorld* w);

@@ -19,6 +19,7 @@
 #include <cooperative_groups.h>
 #include "icx_world.cuh"
 #include "icx_response.cuh"
+#include "icx_mesh.cuh"
 #include "icx_device.cuh"
 
 namespace cg = cooperative_groups;
@@ -1362,6 +1363,112 @@ __global__ void __launch_bounds__(RESOLVE_TPB) k_resolve(const __grid_constant__
     // per-warp scratch of the exact procedures (contact manifolds, clipping): see pseudo_clip_polyhedra_s
     __shared__ V3 scratch_all[RESOLVE_TPB / 32][8 + 2 * ICX_MAXV];
     resolve_body<1>(W, dt, do_euler, scratch_all[threadIdx.x >> 5]);
+}
+
+// ---- static triangle mesh pass (extension, no counterpart in the reference: include/icx.h, icx_mesh.cuh) ----------------
+// One thread per entity, on the state the pair loop left in `in` (the tick has swapped): entities do not interact here, so
+// the pass is embarrassingly parallel and still has ONE defined order per entity -- slot order, then ascending triangle
+// index over the triangles whose bounds overlap the collider's bounds at the start of its turn.  The grid only narrows
+// the search: a triangle is registered in every cell its (slightly inflated) bounds touch, and the exact bounds test below
+// decides, so the visited set is the definition's whatever the cell size.
+__device__ __forceinline__ bool tri_bounds_overlap(const Tri& t, V3 lo, V3 hi)
+{
+    const V3 tlo = v3(smin(smin(t.a.x, t.b.x), t.c.x), smin(smin(t.a.y, t.b.y), t.c.y), smin(smin(t.a.z, t.b.z), t.c.z));
+    const V3 thi = v3(smax(smax(t.a.x, t.b.x), t.c.x), smax(smax(t.a.y, t.b.y), t.c.y), smax(smax(t.a.z, t.b.z), t.c.z));
+    return tlo.x <= hi.x && lo.x <= thi.x && tlo.y <= hi.y && lo.y <= thi.y && tlo.z <= hi.z && lo.z <= thi.z;
+}
+
+__global__ void __launch_bounds__(128) k_mesh_pass(const __grid_constant__ DeviceWorld W, const __grid_constant__ DeviceMesh M)
+{
+    const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= W.n_entities) return;
+    const float4 prm1 = W.prm1[e];
+    const uint32_t ef = __float_as_uint(prm1.w);
+    if (!(ef & EF_HAS_PHYSICS)) return;
+    const uint32_t fp = W.first_packet[e], npk = fp >> 30, p0 = fp & 0x3FFFFFFFu;
+    for (uint32_t k = 0; k < npk; k++) {
+        const uint32_t p = p0 + k;
+        const uint32_t bits = __float_as_uint(W.pk_lpos[p].w);
+        const int type = (int)(bits & PF_TYPE_MASK);
+        if (type != ICX_COLLIDER_BOX && type != ICX_COLLIDER_SPHERE) continue;
+        if (((bits >> PF_CTYPE_SHIFT) & 3u) != ICX_COLLISION_RIGID) continue;
+        // the collider as the pair loop left it
+        SideData sd;
+        sd.pos = W.in.pos[e]; sd.vel = W.in.vel[e]; sd.angvel = W.in.angvel[e]; sd.acc = W.in.acc[e]; sd.angacc = W.in.angacc[e];
+        sd.prm0 = W.prm0[e]; sd.prm1 = prm1; sd.pos0 = sd.pos; sd.slot = ICX_NONE; sd.ts = 0u; sd.id = 0u;
+        sd.mat0 = W.pk_mat0[p]; sd.lscale = W.pk_lscale[p]; sd.damping = W.pk_damping[p]; sd.minparam = 1.0f;
+        const float4* d = W.pk_d + (size_t)p * 6;
+#pragma unroll
+        for (int q = 0; q < 6; q++) sd.d[q] = d[q];
+        V3 base; Shape sh = shape_of(sd, type, base);
+        // bounds of the collider at the start of its turn
+        V3 half;
+        if (type == ICX_COLLIDER_SPHERE) { const float r = length(xform(sh.M, ICX_UNIT_RADIUS, 0.0f, 0.0f) - xform(sh.M, 0.0f, 0.0f, 0.0f)); half = v3(r, r, r); }
+        else half = v3(((fabsf(sh.M.c[0].x) + fabsf(sh.M.c[1].x)) + fabsf(sh.M.c[2].x)) * ICX_UNIT_RADIUS,
+                       ((fabsf(sh.M.c[0].y) + fabsf(sh.M.c[1].y)) + fabsf(sh.M.c[2].y)) * ICX_UNIT_RADIUS,
+                       ((fabsf(sh.M.c[0].z) + fabsf(sh.M.c[1].z)) + fabsf(sh.M.c[2].z)) * ICX_UNIT_RADIUS);
+        const V3 lo = sh.M.t - half, hi = sh.M.t + half;
+        if (!(lo.x == lo.x && hi.x == hi.x)) continue;                              // NaN state: nothing overlaps
+        int c0[3], c1[3]; bool outside = false;
+        const float l3[3] = {lo.x, lo.y, lo.z}, h3[3] = {hi.x, hi.y, hi.z};
+        for (int a = 0; a < 3; a++) {
+            const float f0 = floorf((l3[a] - M.lo[a]) * M.inv_cell), f1 = floorf((h3[a] - M.lo[a]) * M.inv_cell);
+            if (f1 < 0.0f || f0 > (float)(M.dim[a] - 1)) outside = true;
+            c0[a] = (int)fminf(fmaxf(f0, 0.0f), (float)(M.dim[a] - 1)); c1[a] = (int)fminf(fmaxf(f1, 0.0f), (float)(M.dim[a] - 1));
+        }
+        if (outside) continue;
+        Side A = side_of(sd, sh, base, bits);
+        bool touched = false;
+        uint32_t last = ICX_NONE;                                                   // ICX_NONE = none visited yet
+        for (;;) {
+            uint32_t next = ICX_NONE;
+            for (int cz = c0[2]; cz <= c1[2]; cz++) for (int cy = c0[1]; cy <= c1[1]; cy++) for (int cx = c0[0]; cx <= c1[0]; cx++) {
+                const uint32_t cell = ((uint32_t)cz * (uint32_t)M.dim[1] + (uint32_t)cy) * (uint32_t)M.dim[0] + (uint32_t)cx;
+                const uint32_t b = M.cell_start[cell], en = M.cell_start[cell + 1];
+                for (uint32_t i = b; i < en; i++) {
+                    const uint32_t t = M.cell_tri[i];
+                    if (last != ICX_NONE && t <= last) continue;
+                    if (t >= next) break;                                           // ascending per cell
+                    Tri tr; tr.a = v3(M.tri[3 * t]); tr.b = v3(M.tri[3 * t + 1]); tr.c = v3(M.tri[3 * t + 2]);
+                    if (tri_bounds_overlap(tr, lo, hi)) { next = t; break; }
+                }
+            }
+            if (next == ICX_NONE) break;
+            last = next;
+            Tri tr; tr.a = v3(M.tri[3 * next]); tr.b = v3(M.tri[3 * next + 1]); tr.c = v3(M.tri[3 * next + 2]);
+            sh.M.t = A.base + (A.origin + v3(0.0f, 0.0f, 0.0f));                    // the body where the previous triangle left it
+            Hit h; h.point = v3(0.0f, 0.0f, 0.0f); h.normal = v3(0.0f, 0.0f, 0.0f); h.depth = 0.0f;
+            const bool hit = type == ICX_COLLIDER_SPHERE ? sphere_triangle_hit(sh.M, tr, h) : box_triangle_hit(sh.M, tr, h);
+            if (!hit) continue;
+            Side B;                                                                 // the mesh: immovable, identity transform, its material
+            B.origin = v3(0.0f, 0.0f, 0.0f); B.vel = B.origin; B.angvel = B.origin; B.acc = B.origin; B.angacc = B.origin;
+            B.mass = 0.0f; B.colAngDrag = 0.0f;
+            B.L = diag3(v3(1.0f, 1.0f, 1.0f)); B.base = B.origin; B.inv = B.L; B.inertia = B.origin;
+            B.staticFriction = M.staticFriction; B.dynamicFriction = M.dynamicFriction; B.restitution = M.restitution;
+            B.stiffness = 0.0f; B.damping = 0.0f; B.restLength = 0.0f; B.influenceOrientation = false;
+            rigid_rigid_response(A, B, h);
+            touched = true;
+            const uint32_t at = atomicAdd(&M.counter[0], 1u);
+            if (at < M.max_contacts) {
+                IcxMeshContact c;
+                c.entity = W.entity_id[e]; c.row = e; c.slot = (bits & PF_SLOT) ? 1u : 0u; c.triangle = next;
+                c.point[0] = h.point.x; c.point[1] = h.point.y; c.point[2] = h.point.z;
+                c.normal[0] = h.normal.x; c.normal[1] = h.normal.y; c.normal[2] = h.normal.z; c.depth = h.depth;
+                M.contacts[at] = c;
+            } else M.counter[1] = 1u;
+        }
+        if (touched) {
+            W.in.pos[e] = make_float4(A.origin.x, A.origin.y, A.origin.z, 0.0f);
+            W.in.vel[e] = make_float4(A.vel.x, A.vel.y, A.vel.z, 0.0f);
+            W.in.angvel[e] = make_float4(A.angvel.x, A.angvel.y, A.angvel.z, 0.0f);
+        }
+    }
+}
+
+void launch_mesh_pass(const DeviceWorld& W, const DeviceMesh& M, cudaStream_t st)
+{
+    if (!W.n_entities || !M.n_tri) return;
+    k_mesh_pass<<<(W.n_entities + 127) / 128, 128, 0, st>>>(W, M);
 }
 
 void launch_narrow(const DeviceWorld& W, int blocks, cudaStream_t st)

@@ -165,4 +165,12 @@ enum { CTR_LARGE = 0, CTR_DIRTY = 1, CTR_CONTACTS = 2, CTR_INTERCEPTS = 3, CTR_C
 #define ICX_MAX_ROUNDS 65535u
 #define ICX_TRACE_CAP 512
 
+// static triangle mesh (icx_mesh.cuh): triangles as 3 float4 each, a uniform grid over them (CSR, ascending indices per cell)
+struct DeviceMesh {
+    const float4* tri; const uint32_t* cell_start; const uint32_t* cell_tri;
+    uint32_t n_tri; int dim[3]; float lo[3]; float inv_cell;
+    float staticFriction, dynamicFriction, restitution;
+    IcxMeshContact* contacts; uint32_t max_contacts; uint32_t* counter;      // counter[0] contacts, counter[1] overflow
+};
+
 } // namespace icx

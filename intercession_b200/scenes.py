@@ -192,3 +192,35 @@ def worldline_batch(n_worldlines, bodies_per_worldline=1024, seed=20261106, pert
     s["base"] = base
     s["stride"] = n
     return s
+
+
+def torus_mesh(centre=(0.0, 0.0, 0.0), major=6.0, minor=2.0, n_major=48, n_minor=24, axis=1):
+    """A torus as a triangle soup (what resources/torus.obj is in the reference's asset folder; generated, not loaded:
+    BASELINE config 3 "plus torus.obj triangle-mesh colliders").  Returns (vertices [n, 3] float32, triangles [m, 3] uint32);
+    the ring lies in the plane normal to `axis` (1 = y: it lies flat)."""
+    u = np.arange(n_major, dtype=np.float64) * (2 * np.pi / n_major)
+    v = np.arange(n_minor, dtype=np.float64) * (2 * np.pi / n_minor)
+    uu, vv = np.meshgrid(u, v, indexing="ij")
+    ring = major + minor * np.cos(vv)
+    p = np.stack([ring * np.cos(uu), minor * np.sin(vv), ring * np.sin(uu)], axis=-1)          # y up
+    if axis != 1:
+        p = np.roll(p, axis - 1, axis=-1)
+    verts = (p.reshape(-1, 3) + np.asarray(centre, np.float64)).astype(np.float32)
+    i, j = np.meshgrid(np.arange(n_major), np.arange(n_minor), indexing="ij")
+    a = (i * n_minor + j).ravel(); b = (((i + 1) % n_major) * n_minor + j).ravel()
+    c = (((i + 1) % n_major) * n_minor + (j + 1) % n_minor).ravel(); d = (i * n_minor + (j + 1) % n_minor).ravel()
+    tris = np.concatenate([np.stack([a, b, c], axis=1), np.stack([a, c, d], axis=1)]).astype(np.uint32)
+    return verts, tris
+
+
+def height_mesh(side, cells, y=0.0, bump=0.0, seed=0, centre=(0.0, 0.0)):
+    """A (cells x cells) grid of triangles over a square of edge `side`: a floor (bump = 0) or a rolling ground."""
+    rng = np.random.default_rng(seed)
+    g = np.linspace(-0.5 * side, 0.5 * side, cells + 1)
+    xx, zz = np.meshgrid(g + centre[0], g + centre[1], indexing="ij")
+    yy = y + bump * rng.standard_normal(xx.shape)
+    verts = np.stack([xx, yy, zz], axis=-1).reshape(-1, 3).astype(np.float32)
+    i, j = np.meshgrid(np.arange(cells), np.arange(cells), indexing="ij")
+    a = (i * (cells + 1) + j).ravel(); b = a + 1; c = a + cells + 1; d = c + 1
+    tris = np.concatenate([np.stack([a, b, d], axis=1), np.stack([a, d, c], axis=1)]).astype(np.uint32)
+    return verts, tris

@@ -271,6 +271,27 @@ class World:
             raise IcxError(rc, self.lib.icx_last_error(dst.handle).decode())
         return n.value, miss.value
 
+    # ---- static triangle mesh (extension without a counterpart in the reference) ----
+    def upload_mesh(self, vertices, triangles, material=None):
+        v = np.ascontiguousarray(vertices, np.float32).reshape(-1, 3)
+        t = np.ascontiguousarray(triangles, np.uint32).reshape(-1, 3)
+        m = None
+        if material is not None:
+            m = np.zeros(1, abi.mesh_material_dt)
+            m["staticFriction"], m["dynamicFriction"], m["restitution"] = material
+        self._ck(self.lib.icx_mesh_upload(self.handle, abi.ptr(v), len(v), abi.ptr(t), len(t), abi.ptr(m)))
+
+    def remove_mesh(self):
+        self._ck(self.lib.icx_mesh_upload(self.handle, None, 0, None, 0, None))
+
+    def mesh_contacts(self):
+        return self._fetch(self.lib.icx_mesh_contacts_fetch, abi.mesh_contact_dt)
+
+    def mesh_kernel_us(self):
+        us = C.c_float(0)
+        self._ck(self.lib.icx_mesh_kernel_us(self.handle, C.byref(us)))
+        return us.value
+
     # ---- entity lifecycle (Cosmos::register_entity / condemn_entity) ----
     def create_entities(self, rows):
         """Add the entities of the Scene `rows`; the ones the world holds stay on the device.  Returns how many were new."""

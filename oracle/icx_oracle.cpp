@@ -1037,3 +1037,132 @@ int icxo_projectile_update(uint32_t n, double dt, uint32_t n_updates, IcxTransfo
 }
 
 } // extern "C"
+
+// ---- static triangle mesh pass: SELF-ORACLE, PARITY UNPINNED ------------------------------------------------------------
+// The reference has no mesh collider (source/physics/collider.h:18-29 comments `mesh` out), so there is nothing
+// to pin this against.  What follows restates the DEFINITION in include/icx.h ("Static triangle mesh (extension)") on the
+// reference-shaped component structs with the oracle's own arithmetic, brute force over all triangles: a second, independent
+// statement of the same rules that the device pass (csrc/icx_mesh.cuh, k_mesh_pass) must reproduce bit for bit.
+namespace {
+struct MeshTri { V3 a, b, c; };
+
+V3 mesh_closest_point(V3 p, const MeshTri& t) {
+    const V3 ab = t.b - t.a, ac = t.c - t.a, ap = p - t.a;
+    const float d1 = dot(ab, ap), d2 = dot(ac, ap);
+    if (d1 <= 0.0f && d2 <= 0.0f) return t.a;                                       // vertex region a
+    const V3 bp = p - t.b;
+    const float d3 = dot(ab, bp), d4 = dot(ac, bp);
+    if (d3 >= 0.0f && d4 <= d3) return t.b;                                         // vertex region b
+    const float vc = d1 * d4 - d3 * d2;
+    if (vc <= 0.0f && d1 >= 0.0f && d3 <= 0.0f) return t.a + ab * (d1 / (d1 - d3)); // edge ab
+    const V3 cp = p - t.c;
+    const float d5 = dot(ab, cp), d6 = dot(ac, cp);
+    if (d6 >= 0.0f && d5 <= d6) return t.c;                                         // vertex region c
+    const float vb = d5 * d2 - d1 * d6;
+    if (vb <= 0.0f && d2 >= 0.0f && d6 <= 0.0f) return t.a + ac * (d2 / (d2 - d6)); // edge ac
+    const float va = d3 * d6 - d5 * d4;
+    if (va <= 0.0f && (d4 - d3) >= 0.0f && (d5 - d6) >= 0.0f) return t.b + (t.c - t.b) * ((d4 - d3) / ((d4 - d3) + (d5 - d6)));   // edge bc
+    const float denom = 1.0f / (va + vb + vc);                                      // face
+    return (t.a + ab * (vb * denom)) + ac * (vc * denom);
+}
+
+bool mesh_sphere_hit(const M4& m, const MeshTri& t, Hit& h) {
+    const V3 centre = xform(m, 0, 0, 0);
+    const float radius = length(xform(m, UNIT_RADIUS, 0, 0) - centre);              // project_sphere's radius
+    const V3 q = mesh_closest_point(centre, t);
+    const V3 d = centre - q;
+    const float dist2 = dot(d, d);
+    if (!(dist2 < radius * radius)) return false;
+    const float dist = std::sqrt(dist2);
+    V3 n;
+    if (dist > 0.0f) n = d * (1.0f / dist);
+    else { n = normalize(cross(t.b - t.a, t.c - t.a)); if (std::isnan(n.x)) return false; }
+    h.normal = n; h.depth = radius - dist; h.point = q;
+    return true;
+}
+
+bool mesh_box_hit(const M4& m, const MeshTri& t, Hit& h) {
+    const V3 centre = m.t;
+    const V3 edge[3] = {t.b - t.a, t.c - t.b, t.a - t.c};
+    V3 axes[13];
+    axes[0] = cross(edge[0], t.c - t.a);
+    for (int i = 0; i < 3; i++) axes[1 + i] = m.c[i];
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) axes[4 + 3 * i + j] = cross(m.c[i], edge[j]);
+    float best = INFINITY; V3 bestN = v3(0, 0, 0);
+    for (int k = 0; k < 13; k++) {
+        V3 L = axes[k];
+        const float len2 = dot(L, L);
+        if (!(len2 > 1.0e-12f)) continue;
+        L = L * (1.0f / std::sqrt(len2));
+        const float rb = UNIT_RADIUS * ((std::fabs(dot(m.c[0], L)) + std::fabs(dot(m.c[1], L))) + std::fabs(dot(m.c[2], L)));
+        const float cb = dot(centre, L);
+        const float pa = dot(t.a, L), pb = dot(t.b, L), pc = dot(t.c, L);
+        const float tmin = smin(smin(pa, pb), pc), tmax = smax(smax(pa, pb), pc);
+        float pen; bool flip = false;
+        if (cb > (tmin + tmax) * 0.5f) pen = tmax - (cb - rb);
+        else { pen = (cb + rb) - tmin; flip = true; }
+        if (pen <= 0.0f) return false;
+        if (pen < best) { best = pen; bestN = flip ? -L : L; }
+    }
+    if (best == INFINITY) return false;
+    h.normal = bestN; h.depth = best; h.point = mesh_closest_point(centre, t);
+    return true;
+}
+} // namespace
+
+extern "C" int icxo_mesh_pass(uint32_t n, const IcxEntity* id, IcxTransform* T, IcxPhysics* P, const uint8_t* has_physics, IcxColliderComponent* C,
+                              const float* vertices, uint32_t n_vertices, const uint32_t* triangles, uint32_t n_triangles, const IcxMeshMaterial* material,
+                              IcxMeshContact* out, size_t cap, size_t* n_out)
+{
+    if (!T || !P || !C || !vertices || !triangles) return 1;
+    std::vector<MeshTri> tris(n_triangles);
+    for (uint32_t t = 0; t < n_triangles; t++) {
+        for (int k = 0; k < 3; k++) if (triangles[3 * t + k] >= n_vertices) return 1;
+        tris[t].a = ld3(vertices + 3 * (size_t)triangles[3 * t]); tris[t].b = ld3(vertices + 3 * (size_t)triangles[3 * t + 1]); tris[t].c = ld3(vertices + 3 * (size_t)triangles[3 * t + 2]);
+    }
+    // the mesh as a body: immovable, identity transform, its material
+    IcxTransform tM; std::memset(&tM, 0, sizeof(tM)); tM.orientation[0] = 1.0f; tM.scale[0] = tM.scale[1] = tM.scale[2] = 1.0f;
+    IcxPhysics pM; std::memset(&pM, 0, sizeof(pM)); pM.lockedOrientation[0] = 1.0f;
+    IcxCollider cM; std::memset(&cM, 0, sizeof(cM));
+    cM.colliderType = ICX_COLLIDER_BOX; cM.collisionType = ICX_COLLISION_RIGID; cM.isActive = 1; cM.localTransform = tM; cM.inheritOrientation = 1;
+    cM.staticFriction = material ? material->staticFriction : 0.45f; cM.dynamicFriction = material ? material->dynamicFriction : 0.45f;
+    cM.restitution = material ? material->restitution : 0.70f;
+    size_t k = 0;
+    for (uint32_t e = 0; e < n; e++) {
+        if (has_physics && !has_physics[e]) continue;
+        for (uint32_t s = 0; s < ICX_COLLIDERS_PER_ENTITY; s++) {
+            IcxCollider& c = C[e].colliders[s];
+            if (!c.isActive) continue;
+            if (c.colliderType != ICX_COLLIDER_BOX && c.colliderType != ICX_COLLIDER_SPHERE) continue;
+            if (c.collisionType != ICX_COLLISION_RIGID) continue;
+            const M4 m0 = compose_transform(c, T[e]);
+            V3 half;
+            if (c.colliderType == ICX_COLLIDER_SPHERE) { const float r = length(xform(m0, UNIT_RADIUS, 0, 0) - xform(m0, 0, 0, 0)); half = v3(r, r, r); }
+            else half = v3(((std::fabs(m0.c[0].x) + std::fabs(m0.c[1].x)) + std::fabs(m0.c[2].x)) * UNIT_RADIUS,
+                           ((std::fabs(m0.c[0].y) + std::fabs(m0.c[1].y)) + std::fabs(m0.c[2].y)) * UNIT_RADIUS,
+                           ((std::fabs(m0.c[0].z) + std::fabs(m0.c[1].z)) + std::fabs(m0.c[2].z)) * UNIT_RADIUS);
+            const V3 lo = m0.t - half, hi = m0.t + half;                            // bounds when the collider's turn starts
+            if (std::isnan(lo.x) || std::isnan(hi.x)) continue;
+            for (uint32_t t = 0; t < n_triangles; t++) {                            // ascending triangle index
+                const MeshTri& tr = tris[t];
+                const V3 tlo = v3(smin(smin(tr.a.x, tr.b.x), tr.c.x), smin(smin(tr.a.y, tr.b.y), tr.c.y), smin(smin(tr.a.z, tr.b.z), tr.c.z));
+                const V3 thi = v3(smax(smax(tr.a.x, tr.b.x), tr.c.x), smax(smax(tr.a.y, tr.b.y), tr.c.y), smax(smax(tr.a.z, tr.b.z), tr.c.z));
+                if (!(tlo.x <= hi.x && lo.x <= thi.x && tlo.y <= hi.y && lo.y <= thi.y && tlo.z <= hi.z && lo.z <= thi.z)) continue;
+                const M4 m = compose_transform(c, T[e]);                            // where the previous triangle left the body
+                Hit h; h.point = v3(0, 0, 0); h.normal = v3(0, 0, 0); h.depth = 0;
+                const bool hit = c.colliderType == ICX_COLLIDER_SPHERE ? mesh_sphere_hit(m, tr, h) : mesh_box_hit(m, tr, h);
+                if (!hit) continue;
+                IcxTransform tB = tM; IcxPhysics pB = pM; IcxCollider cB = cM;
+                rigid_rigid_response(T[e], c, P[e], tB, cB, pB, h);
+                if (out && k < cap) {
+                    IcxMeshContact& mc = out[k];
+                    mc.entity = id ? id[e] : e; mc.row = e; mc.slot = s; mc.triangle = t;
+                    st3(mc.point, h.point); st3(mc.normal, h.normal); mc.depth = h.depth;
+                }
+                k++;
+            }
+        }
+    }
+    if (n_out) *n_out = k;
+    return 0;
+}

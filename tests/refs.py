@@ -156,6 +156,7 @@ REF_SIGS["icxref_tl_events_pop"] = (C.c_int, [_vp, C.c_uint16, C.c_int, _vp, _sz
 REF_SIGS.update({k.format(p="icxref"): v for k, v in _TL_SIGS.items()})
 ORACLE_SIGS.update({k.format(p="icxo"): v for k, v in _TL_SIGS.items()})
 ORACLE_SIGS["icxo_divergence_scan"] = (C.c_int, [_u32, _vp, _u32, _vp, _u32, _vp, _vp, _vp])
+ORACLE_SIGS["icxo_mesh_pass"] = (C.c_int, [_u32, _vp, _vp, _vp, _vp, _vp, _vp, _u32, _vp, _u32, _vp, _vp, _sz, C.POINTER(_sz)])
 ORACLE_SIGS["icxo_fork_age"] = (C.c_int, [_u32, _vp, _vp, C.c_uint16, C.POINTER(_u32), C.POINTER(C.c_int)])
 
 
@@ -201,6 +202,24 @@ def oracle_scan(live, rec, stride=0):
     flags, cnt, score = np.zeros(nw, np.uint8), np.zeros(nw, np.uint32), np.zeros(nw, np.float64)
     oracle().icxo_divergence_scan(live.n, abi.ptr(live.T), rec.n, abi.ptr(rec.T), stride, abi.ptr(flags), abi.ptr(cnt), abi.ptr(score))
     return flags, cnt, score
+
+
+def oracle_mesh_pass(s, vertices, triangles, material=None, cap=None):
+    """The static-mesh pass on a copy of `s` through the self-oracle (oracle/icx_oracle.cpp icxo_mesh_pass): (scene, contacts)."""
+    out = s.copy()
+    v = np.ascontiguousarray(vertices, np.float32).reshape(-1, 3)
+    t = np.ascontiguousarray(triangles, np.uint32).reshape(-1, 3)
+    m = None
+    if material is not None:
+        m = np.zeros(1, abi.mesh_material_dt)
+        m["staticFriction"], m["dynamicFriction"], m["restitution"] = material
+    cap = cap or max(16 * s.n, 1024)
+    hits = np.zeros(cap, abi.mesh_contact_dt)
+    k = C.c_size_t(0)
+    rc = oracle().icxo_mesh_pass(out.n, abi.ptr(out.ids), abi.ptr(out.T), abi.ptr(out.P), abi.ptr(out.hasP), abi.ptr(out.C),
+                                 abi.ptr(v), len(v), abi.ptr(t), len(t), abi.ptr(m), abi.ptr(hits), cap, C.byref(k))
+    assert rc == 0 and k.value <= cap, (rc, k.value)
+    return out, hits[:k.value]
 
 
 def oracle_fork_age(s, coherency):

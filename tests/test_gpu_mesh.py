@@ -1,0 +1,105 @@
+"""GPU: the static triangle-mesh pass (extension without a counterpart in the reference: ColliderType::mesh is commented out
+in source/physics/collider.h:18-29).  Checked against the SELF-ORACLE icxo_mesh_pass -- an independent CPU restatement of
+the definition in include/icx.h, brute force over all triangles: parity "unpinned" by construction -- bit for bit: the
+contacts (entity, slot, triangle, point, normal, depth) in the pass's order and the whole component state, after the pair
+loop of the same collision pass, which itself is checked against the pinned oracle."""
+import numpy as np
+import pytest
+
+from intercession_b200 import abi, scenes, world
+from intercession_b200.scenes import Scene
+import refs
+from util import assert_hits_equal, assert_state_equal, fields_diff
+
+pytestmark = pytest.mark.gpu
+DT = 1.0 / 45
+
+
+def mesh_scene(n, seed, rotate=True):
+    s = scenes.arena(n, seed=seed, walls=False, kinds=("sphere", "box", "aabb"))
+    rng = np.random.default_rng(seed)
+    if rotate:
+        q = rng.standard_normal((s.n, 4)).astype(np.float32)
+        q /= np.linalg.norm(q, axis=1, keepdims=True)
+        s.T["orientation"][:] = q.astype(np.float32)
+    s.P["velocity"][:] = rng.uniform(-2, 2, (s.n, 3)).astype(np.float32)
+    s.P["velocity"][:, 1] -= 3.0
+    lo, hi = s.T["origin"].min(0), s.T["origin"].max(0)
+    fv, ft = scenes.height_mesh(float((hi - lo).max()) + 6.0, 24, y=float(lo[1]) + 0.4, bump=0.25, seed=seed)       # cuts through the lowest bodies
+    tv, tt = scenes.torus_mesh(centre=tuple(0.5 * (lo + hi)), major=0.3 * float((hi - lo).max()), minor=0.9, n_major=40, n_minor=16)
+    verts = np.concatenate([fv, tv])
+    tris = np.concatenate([ft, tt + len(fv)]).astype(np.uint32)
+    return s, verts, tris
+
+
+def lockstep(s, verts, tris, material=None):
+    """Collision pass (pair loop + mesh pass) from the same post-integration state: everything bit-exact."""
+    with world.World(s.n) as w:
+        w.upload(s)
+        w.upload_mesh(verts, tris, material)
+        w.collision_engage()
+        got = w.download(s)
+        hits, mhits, us = w.contacts(), w.mesh_contacts(), w.mesh_kernel_us()
+    pairs_done = refs.procedures_tick(refs.oracle(), "icxo", s, euler=False)
+    assert_hits_equal(hits, pairs_done.hits)
+    exp, ehits = refs.oracle_mesh_pass(Scene({k: v for k, v in pairs_done.items() if k not in ("hits", "ints", "seconds")}), verts, tris, material)
+    assert len(mhits) == len(ehits), (len(mhits), len(ehits))
+    d = fields_diff(mhits, ehits)
+    assert not d, d[:4]
+    assert_state_equal(got, exp)
+    assert us > 0
+    return exp, ehits
+
+
+@pytest.mark.parametrize("seed", [1, 2])
+def test_mesh_pass_lockstep(built, seed):
+    s, verts, tris = mesh_scene(3000, seed)
+    exp, hits = lockstep(s, verts, tris)
+    kinds = s.C["colliders"]["colliderType"][hits["row"], 0]
+    assert (kinds == abi.COLLIDER_SPHERE).sum() > 20 and (kinds == abi.COLLIDER_BOX).sum() > 20
+    assert len(np.unique(hits["triangle"])) > 50
+    # some body met several triangles in one pass (the later ones saw it moved)
+    assert np.unique(hits["row"], return_counts=True)[1].max() >= 2
+    # every contact pushes its body away from the triangle's surface: after the pass nobody is deeper than it was reported
+    assert (hits["depth"] > 0).all() and np.isfinite(hits["point"]).all()
+
+
+def test_mesh_pass_skips_what_the_definition_skips(built):
+    s, verts, tris = mesh_scene(1500, 5)
+    s.hasP[100:400] = 0                                                             # no PhysicsComponent: not visited
+    s.C["colliders"]["collisionType"][400:700, 0] = abi.COLLISION_NOOP
+    s.C["colliders"]["isActive"][700:800, 0] = 0
+    s.P["mass"][800:900] = 0                                                        # infinite mass: the response returns at once, the contact is still reported
+    exp, hits = lockstep(s, verts, tris, material=(0.9, 0.2, 0.1))
+    rows = set(hits["row"].tolist())
+    assert not rows & set(range(100, 800)) and rows & set(range(800, 900))
+
+
+def test_mesh_free_run_against_oracle(built):
+    """Whole ticks with the mesh, device and oracle side by side from the drop: locked orientations keep the tick bit-exact
+    (no sin / cos), so the two stay identical while bodies land on the ground mesh and roll off the torus."""
+    s, verts, tris = mesh_scene(600, 9, rotate=False)
+    s.P["lockOrientation"][:] = 1
+    s.P["lockedOrientation"][:] = (1, 0, 0, 0)
+    s.P["angularVelocity"][:] = 0
+    cur, n_hits = s, 0
+    with world.World(s.n) as w:
+        w.upload(s)
+        w.upload_mesh(verts, tris)
+        for t in range(40):
+            w.step(DT)
+            got = w.download(s)
+            mh = w.mesh_contacts()
+            out = refs.procedures_tick(refs.oracle(), "icxo", cur, coherency=t)
+            cur, eh = refs.oracle_mesh_pass(Scene({k: v for k, v in out.items() if k not in ("hits", "ints", "seconds")}), verts, tris)
+            assert len(mh) == len(eh) and not fields_diff(mh, eh), t
+            assert_state_equal(got, cur, what=f"tick {t}")
+            n_hits += len(eh)
+        # the ground is a two-sided sheet: a body whose centre starts below it is pushed out downwards; everyone who started
+        # clearly above it is still above it
+        n_ground = 2 * 24 * 24
+        above = s.T["origin"][:, 1] > verts[:3 * n_ground, 1][: (24 + 1) ** 2].max() + 1.0
+        assert n_hits > 200 and above.sum() > 300 and (got.T["origin"][above, 1] > verts[:, 1].min() - 1.0).all()
+        w.remove_mesh()
+        w.step(DT)
+        assert len(w.mesh_contacts()) == 0
