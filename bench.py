@@ -315,6 +315,29 @@ def projectile_behaviors_bench(w, n, peak, reps=24):
             "timing": f"CUDA events per launch, mean of {reps}, L2 flushed (256 MB read pass) before each launch"}
 
 
+def mesh_pass_bench(w, s, peak, ticks=6):
+    """The static triangle-mesh pass (extension) on the headline scene: a torus of 18 432 triangles in the middle
+    of the arena and a ground sheet of 131 072 under it; mean device time of k_mesh_pass over a few ticks."""
+    from intercession_b200 import scenes
+    side = float(s["side"]) if "side" in s else 200.0
+    tv, tt = scenes.torus_mesh(centre=(0.0, 0.0, 0.0), major=0.25 * side, minor=0.05 * side, n_major=192, n_minor=48)
+    gv, gt = scenes.height_mesh(side, 256, y=-0.45 * side, bump=0.2, seed=3)
+    verts = np.concatenate([tv, gv]); tris = np.concatenate([tt, gt + len(tv)]).astype(np.uint32)
+    w.upload_mesh(verts, tris)
+    us, contacts = [], 0
+    for _ in range(ticks):
+        w.step(DT)
+        us.append(w.mesh_kernel_us())
+        contacts = len(w.mesh_contacts())
+    w.remove_mesh()
+    sec = float(np.mean(us[1:])) * 1e-6
+    nbytes = s.n * (5 * 16 + 2 * 16 + 4 + 16 + 16 + 16 + 4 + 96)     # state, constants, first_packet, lpos, mat0, lscale, damping, pk_d
+    return {"kernel": "k_mesh_pass", "entities": s.n, "triangles": int(len(tris)), "us": round(sec * 1e6, 2), "mesh_contacts_last_tick": contacts,
+            "alg_bytes": int(nbytes), "alg_GBps": round(nbytes / sec / 1e9, 1), "frac": round(nbytes / sec / 1e9 / peak, 4),
+            "timing": "CUDA events around the launch (icx_mesh_kernel_us), mean of %d ticks" % (ticks - 1),
+            "parity": "self-oracle (no mesh collider in the reference): tests/test_gpu_mesh.py, tests/test_mesh_oracle.py"}
+
+
 def timeslice_pipeline_bench(bodies, ticks, delay, rank, world_size, local_rank, barrier):
     """BASELINE.json configs[4] (reduced: no time travellers, no parallel cosmos): one timeslice per rank, each
     `delay` ticks behind its future neighbour; per wall tick and link ONE snapshot of 164 B per entity travels
@@ -698,12 +721,15 @@ def main():
     k_edit = max(1, s.n // 100)
     Te, _k3 = pinned_like(s.T[:k_edit])
     Pe, _k4 = pinned_like(s.P[:k_edit])
+    Tb, Pb = T.view(np.uint8).reshape(s.n, -1), P.view(np.uint8).reshape(s.n, -1)
+    Teb, Peb = Te.view(np.uint8).reshape(k_edit, -1), Pe.view(np.uint8).reshape(k_edit, -1)
+    edit_rows = [np.sort(rng.choice(s.n, size=k_edit, replace=False)).astype(np.uint32) for _ in range(2 + a.e2e_steps)]     # which rows: not the host's per-step work
     for it in range(2 + a.e2e_steps):
         if it == 2:
             barrier()
             t0 = time.perf_counter()
-        rows = np.sort(rng.choice(s.n, size=k_edit, replace=False)).astype(np.uint32)
-        Te[:] = T[rows]; Pe[:] = P[rows]                  # the host's edit: the rows as it last saw them (gathered like ComponentPools::to_device)
+        rows = edit_rows[it]
+        np.take(Tb, rows, axis=0, out=Teb); np.take(Pb, rows, axis=0, out=Peb)      # the host's edit: the rows as it last saw them (gathered like ComponentPools::to_device; as bytes: numpy's structured take is slow)
         w.update(rows, T=Te, P=Pe)
         w.step(DT)
         w.download_into(T=T, P=P)
@@ -720,6 +746,7 @@ def main():
                          "(tests/host/test_host_pools.cpp)"}
     tlk = timeline_kernels_bench(w, s.n, peak, local_rank) if (rank == 0 and not a.no_timeline) else None
     beh = projectile_behaviors_bench(w, s.n, peak) if (rank == 0 and not a.no_timeline) else None
+    mesh = mesh_pass_bench(w, s, peak) if (rank == 0 and not a.no_timeline) else None
     barrier()
     w.close()
 
@@ -774,6 +801,7 @@ def main():
                 "long_run": long_run,
                 "timeline_kernels": tlk,
                 "behaviors": beh,
+                "mesh_pass": mesh,
                 "worldline_batch": wlb,
                 "timeslice_pipeline": tsp,
                 "time_travel": tt,

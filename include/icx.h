@@ -291,7 +291,7 @@ ICX_API int icx_world_clone(IcxWorld* src, IcxWorld* dst, const uint8_t* has_fut
  * definition is this library's own and its checker is a CPU restatement of that definition
  * (oracle icxo_mesh_pass: self-oracle, parity unpinned).
  * A world may hold one mesh: world-space triangles, immutable, infinite mass.  After the pair loop of every collision pass
- * (icx_collision_engage / icx_step) each entity that has a PhysicsComponent meets the mesh: entities in row order, their
+ * (icx_collision_engage / icx_step) each entity that has a PhysicsComponent of finite mass (mass != 0) meets the mesh: entities in row order, their
  * active box / sphere colliders of collision type rigid in slot order, and for each collider the triangles whose bounds
  * overlap the collider's bounds (taken when the collider's turn starts) in ascending triangle index.  A hit (sphere -
  * triangle: closest point; box - triangle: 13-axis separating-axis test) is answered with the reference's

@@ -13,7 +13,7 @@ void launch_grid(const DeviceWorld& W, cudaStream_t st);      // 4 kernels: scan
 void launch_pairs(const DeviceWorld& W, cudaStream_t st);
 void launch_narrow(const DeviceWorld& W, int blocks, cudaStream_t st);
 int resolve_grid_blocks(int device, int phase);               // co-resident blocks of the persistent resolve kernels (0 = prepare, 1 = rounds)
-void launch_mesh_pass(const DeviceWorld& W, const DeviceMesh& M, cudaStream_t st);
+void launch_mesh_pass(const DeviceWorld& W, const DeviceMesh& M, int sms, cudaStream_t st);   // 2 kernels: select, pass
 cudaError_t launch_resolve(const DeviceWorld& W, double dt, int do_euler, int prepare_blocks, int blocks, cudaStream_t st);
 struct Mirror { uint32_t* ids; IcxTransform* T; IcxPhysics* P; IcxColliderComponent* C; uint8_t* hasP; };
 void launch_import_kernel(const DeviceWorld& W, Mirror M, const uint32_t* index, const uint32_t* ids, const IcxTransform* T,
@@ -69,7 +69,8 @@ struct IcxWorld {
     icx::DeviceBuffer pend_rows, pend_flag, pend_list, pend_count;
     bool pend_any = false;
     // static triangle mesh (extension, icx_mesh.cu): device arrays + the pass's contact list
-    icx::DeviceBuffer mesh_tri, mesh_cell_start, mesh_cell_tri, mesh_contacts, mesh_counter;
+    icx::DeviceBuffer mesh_tri, mesh_cell_start, mesh_cell_tri, mesh_contacts, mesh_counter, mesh_active;
+    int mesh_sms = 148;
     icx::DeviceMesh mesh = {};
     bool mesh_ran = false;              // a mesh pass ran in the last collision pass (its contacts are the ones to fetch)
     cudaEvent_t mesh_ev0 = nullptr, mesh_ev1 = nullptr;

@@ -15,7 +15,7 @@ int mfail(IcxWorld* w, int code, const std::string& msg) { if (w) w->error = msg
 
 void icx_mesh_release(IcxWorld* w)
 {
-    w->mesh_tri.release(); w->mesh_cell_start.release(); w->mesh_cell_tri.release(); w->mesh_contacts.release(); w->mesh_counter.release();
+    w->mesh_tri.release(); w->mesh_cell_start.release(); w->mesh_cell_tri.release(); w->mesh_contacts.release(); w->mesh_counter.release(); w->mesh_active.release();
     if (w->mesh_ev0) cudaEventDestroy(w->mesh_ev0);
     if (w->mesh_ev1) cudaEventDestroy(w->mesh_ev1);
     w->mesh_ev0 = w->mesh_ev1 = nullptr;
@@ -27,12 +27,12 @@ int icx_mesh_pass(IcxWorld* w)
     w->mesh_ran = false;
     if (!w->mesh.n_tri || !w->n_entities) return ICX_OK;
     cudaStream_t st = w->stream;
-    CKM(w, cudaMemsetAsync(w->mesh_counter.ptr, 0, 8, st));
+    CKM(w, cudaMemsetAsync(w->mesh_counter.ptr, 0, 16, st));
     CKM(w, cudaEventRecord(w->mesh_ev0, st));
-    launch_mesh_pass(w->W, w->mesh, st);
+    launch_mesh_pass(w->W, w->mesh, w->mesh_sms, st);
     CKM(w, cudaEventRecord(w->mesh_ev1, st));
     CKM(w, cudaGetLastError());
-    w->launches += 1;
+    w->launches += 2;
     w->mesh_ran = true;     // the contact list is sized for 4 contacts per entity; an overflow is reported by the fetch
     return ICX_OK;
 }
@@ -103,14 +103,16 @@ int icx_mesh_upload(IcxWorld* w, const float* vertices, uint32_t n_vertices, con
     }
     M.max_contacts = std::max<uint32_t>(4096u, w->cap_entities * 4u);
     CKM(w, w->mesh_contacts.ensure((size_t)M.max_contacts * sizeof(IcxMeshContact)));
-    CKM(w, w->mesh_counter.ensure(8));
-    CKM(w, cudaMemset(w->mesh_counter.ptr, 0, 8));
+    CKM(w, w->mesh_counter.ensure(16));
+    CKM(w, cudaMemset(w->mesh_counter.ptr, 0, 16));
+    CKM(w, w->mesh_active.ensure((size_t)std::max<uint32_t>(w->cap_entities, 1u) * 4));
+    cudaDeviceGetAttribute(&w->mesh_sms, cudaDevAttrMultiProcessorCount, w->device);
     if (!w->mesh_ev0) { CKM(w, cudaEventCreate(&w->mesh_ev0)); CKM(w, cudaEventCreate(&w->mesh_ev1)); }
     M.tri = (const float4*)w->mesh_tri.ptr; M.cell_start = (const uint32_t*)w->mesh_cell_start.ptr; M.cell_tri = (const uint32_t*)w->mesh_cell_tri.ptr;
     M.n_tri = n_triangles;
     M.staticFriction = material ? material->staticFriction : 0.45f; M.dynamicFriction = material ? material->dynamicFriction : 0.45f;
     M.restitution = material ? material->restitution : 0.70f;
-    M.contacts = (IcxMeshContact*)w->mesh_contacts.ptr; M.counter = (uint32_t*)w->mesh_counter.ptr;
+    M.contacts = (IcxMeshContact*)w->mesh_contacts.ptr; M.counter = (uint32_t*)w->mesh_counter.ptr; M.active = (uint32_t*)w->mesh_active.ptr;
     w->mesh = M; w->mesh_ran = false;
     return ICX_OK;
 }

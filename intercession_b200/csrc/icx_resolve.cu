@@ -1378,97 +1378,199 @@ __device__ __forceinline__ bool tri_bounds_overlap(const Tri& t, V3 lo, V3 hi)
     return tlo.x <= hi.x && lo.x <= thi.x && tlo.y <= hi.y && lo.y <= thi.y && tlo.z <= hi.z && lo.z <= thi.z;
 }
 
-__global__ void __launch_bounds__(128) k_mesh_pass(const __grid_constant__ DeviceWorld W, const __grid_constant__ DeviceMesh M)
+// the mesh as the other side of a response: immovable, identity transform, its material
+__device__ __forceinline__ Side mesh_side(const DeviceMesh& M)
+{
+    Side B;
+    B.origin = v3(0.0f, 0.0f, 0.0f); B.vel = B.origin; B.angvel = B.origin; B.acc = B.origin; B.angacc = B.origin;
+    B.mass = 0.0f; B.colAngDrag = 0.0f;
+    B.L = diag3(v3(1.0f, 1.0f, 1.0f)); B.base = B.origin; B.inv = B.L; B.inertia = B.origin;
+    B.staticFriction = M.staticFriction; B.dynamicFriction = M.dynamicFriction; B.restitution = M.restitution;
+    B.stiffness = 0.0f; B.damping = 0.0f; B.restLength = 0.0f; B.influenceOrientation = false;
+    return B;
+}
+__device__ __forceinline__ Tri mesh_tri(const DeviceMesh& M, uint32_t t) { Tri tr; tr.a = v3(M.tri[3 * t]); tr.b = v3(M.tri[3 * t + 1]); tr.c = v3(M.tri[3 * t + 2]); return tr; }
+__device__ __forceinline__ bool mesh_cells(const DeviceMesh& M, V3 lo, V3 hi, int* c0, int* c1)
+{
+    if (!(lo.x == lo.x && hi.x == hi.x && lo.y == lo.y && hi.y == hi.y && lo.z == lo.z && hi.z == hi.z)) return false;      // NaN state: nothing overlaps
+    const float l3[3] = {lo.x, lo.y, lo.z}, h3[3] = {hi.x, hi.y, hi.z};
+    for (int a = 0; a < 3; a++) {
+        const float f0 = floorf((l3[a] - M.lo[a]) * M.inv_cell), f1 = floorf((h3[a] - M.lo[a]) * M.inv_cell);
+        if (f1 < 0.0f || f0 > (float)(M.dim[a] - 1)) return false;
+        c0[a] = (int)fminf(fmaxf(f0, 0.0f), (float)(M.dim[a] - 1)); c1[a] = (int)fminf(fmaxf(f1, 0.0f), (float)(M.dim[a] - 1));
+    }
+    return true;
+}
+__device__ __forceinline__ void mesh_emit(const DeviceWorld& W, const DeviceMesh& M, uint32_t e, uint32_t bits, uint32_t t, const Hit& h)
+{
+    const uint32_t at = atomicAdd(&M.counter[0], 1u);
+    if (at >= M.max_contacts) { M.counter[1] = 1u; return; }
+    IcxMeshContact c;
+    c.entity = W.entity_id[e]; c.row = e; c.slot = (bits & PF_SLOT) ? 1u : 0u; c.triangle = t;
+    c.point[0] = h.point.x; c.point[1] = h.point.y; c.point[2] = h.point.z;
+    c.normal[0] = h.normal.x; c.normal[1] = h.normal.y; c.normal[2] = h.normal.z; c.depth = h.depth;
+    M.contacts[at] = c;
+}
+
+// Phase 1, one thread per entity: who can touch the mesh at all?  The packet bounds of this tick (post-integration, inflated by
+// the margin) moved with the body by what the pair loop displaced it -- a superset of the exact bounds -- against the occupied
+// grid cells.  Streams 70 B per entity; the few that pass go to phase 2.
+__global__ void __launch_bounds__(256) k_mesh_select(const __grid_constant__ DeviceWorld W, const __grid_constant__ DeviceMesh M)
 {
     const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= W.n_entities) return;
-    const float4 prm1 = W.prm1[e];
-    const uint32_t ef = __float_as_uint(prm1.w);
-    if (!(ef & EF_HAS_PHYSICS)) return;
+    if (!(__float_as_uint(W.prm1[e].w) & EF_HAS_PHYSICS)) return;
+    if (W.prm0[e].w == 0.0f) return;                                                // infinite mass: not visited (the response could not change it)
     const uint32_t fp = W.first_packet[e], npk = fp >> 30, p0 = fp & 0x3FFFFFFFu;
-    for (uint32_t k = 0; k < npk; k++) {
-        const uint32_t p = p0 + k;
-        const uint32_t bits = __float_as_uint(W.pk_lpos[p].w);
-        const int type = (int)(bits & PF_TYPE_MASK);
-        if (type != ICX_COLLIDER_BOX && type != ICX_COLLIDER_SPHERE) continue;
-        if (((bits >> PF_CTYPE_SHIFT) & 3u) != ICX_COLLISION_RIGID) continue;
-        // the collider as the pair loop left it
-        SideData sd;
-        sd.pos = W.in.pos[e]; sd.vel = W.in.vel[e]; sd.angvel = W.in.angvel[e]; sd.acc = W.in.acc[e]; sd.angacc = W.in.angacc[e];
-        sd.prm0 = W.prm0[e]; sd.prm1 = prm1; sd.pos0 = sd.pos; sd.slot = ICX_NONE; sd.ts = 0u; sd.id = 0u;
-        sd.mat0 = W.pk_mat0[p]; sd.lscale = W.pk_lscale[p]; sd.damping = W.pk_damping[p]; sd.minparam = 1.0f;
-        const float4* d = W.pk_d + (size_t)p * 6;
-#pragma unroll
-        for (int q = 0; q < 6; q++) sd.d[q] = d[q];
-        V3 base; Shape sh = shape_of(sd, type, base);
-        // bounds of the collider at the start of its turn
-        V3 half;
-        if (type == ICX_COLLIDER_SPHERE) { const float r = length(xform(sh.M, ICX_UNIT_RADIUS, 0.0f, 0.0f) - xform(sh.M, 0.0f, 0.0f, 0.0f)); half = v3(r, r, r); }
-        else half = v3(((fabsf(sh.M.c[0].x) + fabsf(sh.M.c[1].x)) + fabsf(sh.M.c[2].x)) * ICX_UNIT_RADIUS,
-                       ((fabsf(sh.M.c[0].y) + fabsf(sh.M.c[1].y)) + fabsf(sh.M.c[2].y)) * ICX_UNIT_RADIUS,
-                       ((fabsf(sh.M.c[0].z) + fabsf(sh.M.c[1].z)) + fabsf(sh.M.c[2].z)) * ICX_UNIT_RADIUS);
-        const V3 lo = sh.M.t - half, hi = sh.M.t + half;
-        if (!(lo.x == lo.x && hi.x == hi.x)) continue;                              // NaN state: nothing overlaps
-        int c0[3], c1[3]; bool outside = false;
-        const float l3[3] = {lo.x, lo.y, lo.z}, h3[3] = {hi.x, hi.y, hi.z};
-        for (int a = 0; a < 3; a++) {
-            const float f0 = floorf((l3[a] - M.lo[a]) * M.inv_cell), f1 = floorf((h3[a] - M.lo[a]) * M.inv_cell);
-            if (f1 < 0.0f || f0 > (float)(M.dim[a] - 1)) outside = true;
-            c0[a] = (int)fminf(fmaxf(f0, 0.0f), (float)(M.dim[a] - 1)); c1[a] = (int)fminf(fmaxf(f1, 0.0f), (float)(M.dim[a] - 1));
+    if (!npk) return;
+    const float4 pos = W.in.pos[e], q0 = W.pos0[e];
+    const V3 delta = v3(pos.x - q0.x, pos.y - q0.y, pos.z - q0.z);
+    const float slack = 1.0e-3f * (fabsf(delta.x) + fabsf(delta.y) + fabsf(delta.z)) + 1.0e-4f;
+    bool near = false;
+    for (uint32_t k = 0; k < npk && !near; k++) {
+        const float4 blo = W.pk_lo[p0 + k], bhi = W.pk_hi[p0 + k];
+        int c0[3], c1[3];
+        if (!mesh_cells(M, v3(blo.x + delta.x - slack, blo.y + delta.y - slack, blo.z + delta.z - slack),
+                        v3(bhi.x + delta.x + slack, bhi.y + delta.y + slack, bhi.z + delta.z + slack), c0, c1)) continue;
+        for (int cz = c0[2]; cz <= c1[2] && !near; cz++) for (int cy = c0[1]; cy <= c1[1] && !near; cy++) {
+            const uint32_t row = ((uint32_t)cz * (uint32_t)M.dim[1] + (uint32_t)cy) * (uint32_t)M.dim[0];
+            near = M.cell_start[row + (uint32_t)c1[0] + 1u] != M.cell_start[row + (uint32_t)c0[0]];      // cells of one row are contiguous in the CSR
         }
-        if (outside) continue;
-        Side A = side_of(sd, sh, base, bits);
+    }
+    if (near) M.active[atomicAdd(&M.counter[2], 1u)] = e;
+}
+
+// Phase 2, one WARP per selected entity.  Per collider: the lanes gather the triangles of the overlapped cells whose bounds
+// overlap the collider's (exact test), sort them ascending and drop duplicates in shared memory; then the ordered walk runs
+// 32 triangles at a time -- every lane tests ITS triangle against the current state, the lowest lane that hits is the next
+// contact of the sequential order (the misses before it saw the state they would have seen), all lanes apply its response
+// (same inputs, same result), and the lanes behind it test again.
+#define ICX_MESH_MAXC 256
+__global__ void __launch_bounds__(128) k_mesh_pass(const __grid_constant__ DeviceWorld W, const __grid_constant__ DeviceMesh M)
+{
+    __shared__ uint32_t s_list[4][2][ICX_MESH_MAXC];
+    const uint32_t FULL = 0xFFFFFFFFu, lane = threadIdx.x & 31u, wib = threadIdx.x >> 5;
+    const uint32_t n_act = min(*(volatile uint32_t*)&M.counter[2], W.n_entities);
+    uint32_t* raw = s_list[wib][0]; uint32_t* sorted = s_list[wib][1];
+    for (uint32_t ai = blockIdx.x * 4u + wib; ai < n_act; ai += gridDim.x * 4u) {
+        const uint32_t e = M.active[ai];
+        const float4 prm1 = W.prm1[e];
+        const uint32_t fp = W.first_packet[e], npk = fp >> 30, p0 = fp & 0x3FFFFFFFu;
+        // the entity as the pair loop left it; the second collider sees what the first one's contacts did
+        float4 pos = W.in.pos[e], vel = W.in.vel[e], angvel = W.in.angvel[e];
         bool touched = false;
-        uint32_t last = ICX_NONE;                                                   // ICX_NONE = none visited yet
-        for (;;) {
-            uint32_t next = ICX_NONE;
-            for (int cz = c0[2]; cz <= c1[2]; cz++) for (int cy = c0[1]; cy <= c1[1]; cy++) for (int cx = c0[0]; cx <= c1[0]; cx++) {
-                const uint32_t cell = ((uint32_t)cz * (uint32_t)M.dim[1] + (uint32_t)cy) * (uint32_t)M.dim[0] + (uint32_t)cx;
-                const uint32_t b = M.cell_start[cell], en = M.cell_start[cell + 1];
-                for (uint32_t i = b; i < en; i++) {
-                    const uint32_t t = M.cell_tri[i];
-                    if (last != ICX_NONE && t <= last) continue;
-                    if (t >= next) break;                                           // ascending per cell
-                    Tri tr; tr.a = v3(M.tri[3 * t]); tr.b = v3(M.tri[3 * t + 1]); tr.c = v3(M.tri[3 * t + 2]);
-                    if (tri_bounds_overlap(tr, lo, hi)) { next = t; break; }
+        for (uint32_t k = 0; k < npk; k++) {
+            const uint32_t p = p0 + k;
+            const uint32_t bits = __float_as_uint(W.pk_lpos[p].w);
+            const int type = (int)(bits & PF_TYPE_MASK);
+            if (type != ICX_COLLIDER_BOX && type != ICX_COLLIDER_SPHERE) continue;
+            if (((bits >> PF_CTYPE_SHIFT) & 3u) != ICX_COLLISION_RIGID) continue;
+            SideData sd;
+            sd.pos = pos; sd.vel = vel; sd.angvel = angvel; sd.acc = W.in.acc[e]; sd.angacc = W.in.angacc[e];
+            sd.prm0 = W.prm0[e]; sd.prm1 = prm1; sd.pos0 = sd.pos; sd.slot = ICX_NONE; sd.ts = 0u; sd.id = 0u;
+            sd.mat0 = W.pk_mat0[p]; sd.lscale = W.pk_lscale[p]; sd.damping = W.pk_damping[p]; sd.minparam = 1.0f;
+            const float4* d = W.pk_d + (size_t)p * 6;
+#pragma unroll
+            for (int q = 0; q < 6; q++) sd.d[q] = d[q];
+            V3 base; Shape sh = shape_of(sd, type, base);
+            V3 half;                                                                // bounds of the collider when its turn starts
+            if (type == ICX_COLLIDER_SPHERE) { const float r = length(xform(sh.M, ICX_UNIT_RADIUS, 0.0f, 0.0f) - xform(sh.M, 0.0f, 0.0f, 0.0f)); half = v3(r, r, r); }
+            else half = v3(((fabsf(sh.M.c[0].x) + fabsf(sh.M.c[1].x)) + fabsf(sh.M.c[2].x)) * ICX_UNIT_RADIUS,
+                           ((fabsf(sh.M.c[0].y) + fabsf(sh.M.c[1].y)) + fabsf(sh.M.c[2].y)) * ICX_UNIT_RADIUS,
+                           ((fabsf(sh.M.c[0].z) + fabsf(sh.M.c[1].z)) + fabsf(sh.M.c[2].z)) * ICX_UNIT_RADIUS);
+            const V3 lo = sh.M.t - half, hi = sh.M.t + half;
+            int c0[3], c1[3];
+            if (!mesh_cells(M, lo, hi, c0, c1)) continue;
+            Side A = side_of(sd, sh, base, bits);
+            const Side B0 = mesh_side(M);
+            // Candidates are staged ICX_MESH_MAXC at a time over windows of the triangle index range (normally ONE window: the
+            // whole range); a window that holds more is halved.  The bounds are fixed for the collider's turn, so the windows
+            // partition one ascending sequence.
+            uint32_t win_lo = 0u, span = M.n_tri;
+            while (win_lo < M.n_tri) {
+                const uint32_t win_hi = (span >= M.n_tri - win_lo) ? M.n_tri : win_lo + span;
+                // ---- gather (all lanes), exact bounds test, append through a ballot ----
+                uint32_t n_raw = 0;
+                for (int cz = c0[2]; cz <= c1[2]; cz++) for (int cy = c0[1]; cy <= c1[1]; cy++) {
+                    const uint32_t row = ((uint32_t)cz * (uint32_t)M.dim[1] + (uint32_t)cy) * (uint32_t)M.dim[0];
+                    const uint32_t b = M.cell_start[row + (uint32_t)c0[0]], en = M.cell_start[row + (uint32_t)c1[0] + 1u];
+                    for (uint32_t i0 = b; i0 < en; i0 += 32u) {
+                        const uint32_t i = i0 + lane;
+                        uint32_t t = ICX_NONE; bool want = false;
+                        if (i < en) { t = M.cell_tri[i]; want = t >= win_lo && t < win_hi && tri_bounds_overlap(mesh_tri(M, t), lo, hi); }
+                        const uint32_t m = __ballot_sync(FULL, want);
+                        const uint32_t at = n_raw + __popc(m & ((1u << lane) - 1u));
+                        if (want && at < ICX_MESH_MAXC) raw[at] = t;
+                        n_raw += __popc(m);
+                    }
                 }
+                if (n_raw > ICX_MESH_MAXC) {
+                    if (span > 1u) { span = (span + 1u) / 2u; __syncwarp(); continue; }
+                    n_raw = 1u;                                                     // one triangle registered in more cells than the staging holds: raw[0] is it
+                }
+                __syncwarp();
+                uint32_t n_c = 0;
+                if (n_raw) {
+                    // ---- sort ascending (rank by counting; equal values keep their order), then drop duplicates ----
+                    for (uint32_t i = lane; i < n_raw; i += 32u) {
+                        const uint32_t x = raw[i]; uint32_t rank = 0;
+                        for (uint32_t j = 0; j < n_raw; j++) { const uint32_t y = raw[j]; rank += (y < x || (y == x && j < i)) ? 1u : 0u; }
+                        sorted[rank] = x;
+                    }
+                    __syncwarp();
+                    for (uint32_t i0 = 0; i0 < n_raw; i0 += 32u) {
+                        const uint32_t i = i0 + lane;
+                        const bool keep = i < n_raw && (i == 0u || sorted[i] != sorted[i - 1u]);
+                        const uint32_t x = i < n_raw ? sorted[i] : 0u;
+                        const uint32_t m = __ballot_sync(FULL, keep);
+                        __syncwarp();
+                        if (keep) raw[n_c + __popc(m & ((1u << lane) - 1u))] = x;  // raw is free again: position <= i
+                        n_c += __popc(m);
+                        __syncwarp();
+                    }
+                }
+                // ---- the ordered walk, 32 candidates at a time ----
+                uint32_t at = 0;
+                while (at < n_c) {
+                    const uint32_t i = at + lane;
+                    Hit h; h.point = v3(0.0f, 0.0f, 0.0f); h.normal = v3(0.0f, 0.0f, 0.0f); h.depth = 0.0f;
+                    bool hit = false; uint32_t t = ICX_NONE;
+                    if (i < n_c) {
+                        t = raw[i];
+                        sh.M.t = A.base + (A.origin + v3(0.0f, 0.0f, 0.0f));
+                        const Tri tr = mesh_tri(M, t);
+                        hit = type == ICX_COLLIDER_SPHERE ? sphere_triangle_hit(sh.M, tr, h) : box_triangle_hit(sh.M, tr, h);
+                    }
+                    const uint32_t m = __ballot_sync(FULL, hit);
+                    if (!m) { at += 32u; continue; }
+                    const int f = __ffs(m) - 1;                                     // the next contact of the sequential order
+                    h.point.x = __shfl_sync(FULL, h.point.x, f); h.point.y = __shfl_sync(FULL, h.point.y, f); h.point.z = __shfl_sync(FULL, h.point.z, f);
+                    h.normal.x = __shfl_sync(FULL, h.normal.x, f); h.normal.y = __shfl_sync(FULL, h.normal.y, f); h.normal.z = __shfl_sync(FULL, h.normal.z, f);
+                    h.depth = __shfl_sync(FULL, h.depth, f); t = __shfl_sync(FULL, t, f);
+                    Side B = B0;
+                    rigid_rigid_response(A, B, h);                                  // every lane: same inputs, same result
+                    touched = true;
+                    if (lane == 0u) mesh_emit(W, M, e, bits, t, h);
+                    at += (uint32_t)f + 1u;
+                }
+                __syncwarp();
+                win_lo = win_hi;
+                span = span >= (M.n_tri >> 1) ? M.n_tri : span * 2u;
             }
-            if (next == ICX_NONE) break;
-            last = next;
-            Tri tr; tr.a = v3(M.tri[3 * next]); tr.b = v3(M.tri[3 * next + 1]); tr.c = v3(M.tri[3 * next + 2]);
-            sh.M.t = A.base + (A.origin + v3(0.0f, 0.0f, 0.0f));                    // the body where the previous triangle left it
-            Hit h; h.point = v3(0.0f, 0.0f, 0.0f); h.normal = v3(0.0f, 0.0f, 0.0f); h.depth = 0.0f;
-            const bool hit = type == ICX_COLLIDER_SPHERE ? sphere_triangle_hit(sh.M, tr, h) : box_triangle_hit(sh.M, tr, h);
-            if (!hit) continue;
-            Side B;                                                                 // the mesh: immovable, identity transform, its material
-            B.origin = v3(0.0f, 0.0f, 0.0f); B.vel = B.origin; B.angvel = B.origin; B.acc = B.origin; B.angacc = B.origin;
-            B.mass = 0.0f; B.colAngDrag = 0.0f;
-            B.L = diag3(v3(1.0f, 1.0f, 1.0f)); B.base = B.origin; B.inv = B.L; B.inertia = B.origin;
-            B.staticFriction = M.staticFriction; B.dynamicFriction = M.dynamicFriction; B.restitution = M.restitution;
-            B.stiffness = 0.0f; B.damping = 0.0f; B.restLength = 0.0f; B.influenceOrientation = false;
-            rigid_rigid_response(A, B, h);
-            touched = true;
-            const uint32_t at = atomicAdd(&M.counter[0], 1u);
-            if (at < M.max_contacts) {
-                IcxMeshContact c;
-                c.entity = W.entity_id[e]; c.row = e; c.slot = (bits & PF_SLOT) ? 1u : 0u; c.triangle = next;
-                c.point[0] = h.point.x; c.point[1] = h.point.y; c.point[2] = h.point.z;
-                c.normal[0] = h.normal.x; c.normal[1] = h.normal.y; c.normal[2] = h.normal.z; c.depth = h.depth;
-                M.contacts[at] = c;
-            } else M.counter[1] = 1u;
+            pos = make_float4(A.origin.x, A.origin.y, A.origin.z, 0.0f);
+            vel = make_float4(A.vel.x, A.vel.y, A.vel.z, 0.0f);
+            angvel = make_float4(A.angvel.x, A.angvel.y, A.angvel.z, 0.0f);
+            __syncwarp();
         }
-        if (touched) {
-            W.in.pos[e] = make_float4(A.origin.x, A.origin.y, A.origin.z, 0.0f);
-            W.in.vel[e] = make_float4(A.vel.x, A.vel.y, A.vel.z, 0.0f);
-            W.in.angvel[e] = make_float4(A.angvel.x, A.angvel.y, A.angvel.z, 0.0f);
-        }
+        if (touched && lane == 0u) { W.in.pos[e] = pos; W.in.vel[e] = vel; W.in.angvel[e] = angvel; }
     }
 }
 
-void launch_mesh_pass(const DeviceWorld& W, const DeviceMesh& M, cudaStream_t st)
+void launch_mesh_pass(const DeviceWorld& W, const DeviceMesh& M, int sms, cudaStream_t st)
 {
     if (!W.n_entities || !M.n_tri) return;
-    k_mesh_pass<<<(W.n_entities + 127) / 128, 128, 0, st>>>(W, M);
+    k_mesh_select<<<(W.n_entities + 255) / 256, 256, 0, st>>>(W, M);
+    k_mesh_pass<<<sms * 8, 128, 0, st>>>(W, M);
 }
 
 void launch_narrow(const DeviceWorld& W, int blocks, cudaStream_t st)

@@ -170,7 +170,8 @@ struct DeviceMesh {
     const float4* tri; const uint32_t* cell_start; const uint32_t* cell_tri;
     uint32_t n_tri; int dim[3]; float lo[3]; float inv_cell;
     float staticFriction, dynamicFriction, restitution;
-    IcxMeshContact* contacts; uint32_t max_contacts; uint32_t* counter;      // counter[0] contacts, counter[1] overflow
+    IcxMeshContact* contacts; uint32_t max_contacts; uint32_t* counter;      // counter[0] contacts, [1] overflow, [2] entities selected by phase 1
+    uint32_t* active;               // [n_entities] rows phase 1 selected
 };
 
 } // namespace icx

@@ -1130,6 +1130,7 @@ extern "C" int icxo_mesh_pass(uint32_t n, const IcxEntity* id, IcxTransform* T, 
     size_t k = 0;
     for (uint32_t e = 0; e < n; e++) {
         if (has_physics && !has_physics[e]) continue;
+        if (P[e].mass == 0.0f) continue;                                            // infinite mass: not visited
         for (uint32_t s = 0; s < ICX_COLLIDERS_PER_ENTITY; s++) {
             IcxCollider& c = C[e].colliders[s];
             if (!c.isActive) continue;

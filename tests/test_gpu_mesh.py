@@ -69,10 +69,26 @@ def test_mesh_pass_skips_what_the_definition_skips(built):
     s.hasP[100:400] = 0                                                             # no PhysicsComponent: not visited
     s.C["colliders"]["collisionType"][400:700, 0] = abi.COLLISION_NOOP
     s.C["colliders"]["isActive"][700:800, 0] = 0
-    s.P["mass"][800:900] = 0                                                        # infinite mass: the response returns at once, the contact is still reported
+    s.P["mass"][800:900] = 0                                                        # infinite mass: not visited
     exp, hits = lockstep(s, verts, tris, material=(0.9, 0.2, 0.1))
     rows = set(hits["row"].tolist())
-    assert not rows & set(range(100, 800)) and rows & set(range(800, 900))
+    assert not rows & set(range(100, 900)) and len(rows) > 50
+
+
+def test_mesh_body_over_many_triangles(built):
+    """A body whose bounds cover more triangles than one staging window holds (and triangles registered in many cells): the
+    windows partition one ascending sequence."""
+    s, verts, tris = mesh_scene(300, 7)
+    gv, gt = scenes.height_mesh(40.0, 64, y=float(s.T["origin"][:, 1].min()) + 0.3, bump=0.02, seed=1)       # 8 192 small triangles
+    big = np.array([[-30, -9, -30], [30, -9, -30], [0, -9, 40]], np.float32)                                 # + one huge triangle under everything
+    verts = np.concatenate([gv, big]); tris = np.concatenate([gt, np.array([[len(gv), len(gv) + 1, len(gv) + 2]])]).astype(np.uint32)
+    s.T["scale"][5] = (14.0, 1.0, 14.0)                                             # a slab over ~1 000 triangles
+    s.T["origin"][5, 1] = float(gv[:, 1].mean()) + 0.45
+    s.T["orientation"][5] = (1, 0, 0, 0)
+    s.P["mass"][5] = 1.0e6                                                          # the pair loop barely moves it
+    s.C["colliders"]["colliderType"][5, 0] = abi.COLLIDER_BOX
+    exp, hits = lockstep(s, verts, tris)
+    assert (hits["row"] == 5).sum() >= 3                                            # pushed clear by the first few; ~1 200 candidates were walked
 
 
 def test_mesh_free_run_against_oracle(built):
