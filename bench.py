@@ -336,10 +336,11 @@ def mesh_pass_bench(w, s, peak, ticks=6):
         contacts = len(w.mesh_contacts())
     w.remove_mesh()
     sec = float(np.mean(us[1:])) * 1e-6
-    nbytes = s.n * (5 * 16 + 2 * 16 + 4 + 16 + 16 + 16 + 4 + 96)     # state, constants, first_packet, lpos, mat0, lscale, damping, pk_d
-    return {"kernel": "k_mesh_pass", "entities": s.n, "triangles": int(len(tris)), "us": round(sec * 1e6, 2), "mesh_contacts_last_tick": contacts,
+    nbytes = s.n * (16 + 16 + 16 + 16 + 4 + 2 * 16)     # what the selection kernel streams per entity: prm1, prm0, origin, origin after integration, first_packet, packet bounds
+    return {"kernel": "k_mesh_select + k_mesh_pass", "entities": s.n, "triangles": int(len(tris)), "us": round(sec * 1e6, 2), "mesh_contacts_last_tick": contacts,
             "alg_bytes": int(nbytes), "alg_GBps": round(nbytes / sec / 1e9, 1), "frac": round(nbytes / sec / 1e9 / peak, 4),
-            "timing": "CUDA events around the launch (icx_mesh_kernel_us), mean of %d ticks" % (ticks - 1),
+            "bound": "latency of the ordered walk over the selected entities (k_mesh_select streams alg_bytes; k_mesh_pass runs one warp per selected entity)",
+            "timing": "CUDA events around the two launches (icx_mesh_kernel_us), mean of %d ticks" % (ticks - 1),
             "parity": "self-oracle (no mesh collider in the reference): tests/test_gpu_mesh.py, tests/test_mesh_oracle.py"}
 
 
