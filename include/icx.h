@@ -564,6 +564,15 @@ ICX_API int icx_timeline_event_push(IcxTimeline* tl, uint16_t coherency, const I
  * records are written, *n_out = how many were due.  mode as icx_replay (ICX_REPLAY_PARALLEL: behind the breakpoint). */
 ICX_API int icx_timeline_events_pop(IcxTimeline* tl, uint16_t now, int mode, IcxTimelineEvent* out, size_t cap, size_t* n_out);
 
+/* The components of ONE entity as the record of tick `coherency` holds them -- what the ENTITY_CREATED / JUMP_ARRIVAL
+ * handlers deserialise out of their message in the reference (server_network_dynamo.cpp:940-976: the arrival carries the
+ * traveller's serialised components; here the tick's ENTITY_UPDATE record already does).  id = the id the RECEIVING cosmos
+ * knows the entity by.  *found: bit 0 = Transform / Physics found, bit 1 = the record also carries its ColliderComponent (it
+ * does in the tick an entity is created: the row is new to the ring).  Call it after icx_timeline_events_pop and before the
+ * icx_replay that consumes the tick; then icx_entities_create.  Synchronous, one small copy. */
+ICX_API int icx_timeline_entity_fetch(IcxTimeline* tl, uint16_t coherency, IcxEntity id, IcxTransform* T, IcxPhysics* P,
+                                      uint8_t* has_physics, IcxColliderComponent* C, int* found);
+
 /* Snapshot transport between timeslices on different GPUs / processes (the future -> past ENTITY_UPDATE
  * stream, server_network_dynamo.cpp:642-679): pack the slot stamped `coherency` into / restore it from a
  * caller-owned DEVICE buffer, e.g. the buffer a ncclSend / ncclRecv moves:

@@ -198,6 +198,7 @@ SIGNATURES = {
     "icx_record_ex": (C.c_int, [_vp, _vp, C.c_uint16, _u32]),
     "icx_timeline_id_mismatches": (C.c_int, [_vp, C.POINTER(C.c_uint64)]),
     "icx_timeline_event_push": (C.c_int, [_vp, C.c_uint16, _vp, _u32]),
+    "icx_timeline_entity_fetch": (C.c_int, [_vp, C.c_uint16, _u32, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]),
     "icx_timeline_events_pop": (C.c_int, [_vp, C.c_uint16, C.c_int, _vp, _sz, _psz]),
     "icx_divergence_scan_enqueue": (C.c_int, [_vp, _vp, C.c_uint16, _u32]),
     "icx_divergence_scan_fetch": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp, C.c_int]),

@@ -60,6 +60,7 @@ struct IcxTimeline {
     // mirrored in pinned host memory; the slot's snapshot and its events are consumed independently
     struct EvBlock { uint32_t rows_unused, n_events, pad[2]; IcxTimelineEvent ev[ICX_TIMELINE_EVENTS_PER_TICK]; };
     EvBlock* d_ev = nullptr; EvBlock* h_ev = nullptr;       // [depth]
+    void* d_fetch = nullptr;            // staging of icx_timeline_entity_fetch (one recorded entity)
     std::vector<uint8_t> ev_valid, ev_behind, ev_pending;   // pending: the host mirror is being filled by the import's copy (slot_ev)
     std::vector<uint16_t> ev_stamp;
     std::vector<uint64_t> ev_seq;
@@ -462,7 +463,7 @@ void icx_timeline_destroy(IcxTimeline* tl)
     if (!tl) return;
     cudaSetDevice(tl->device);
     cudaDeviceSynchronize();
-    void* bufs[] = {tl->state, tl->ids, tl->seen, tl->d_delta_n, tl->d_mismatch, tl->delta, tl->d_score, tl->d_count, tl->d_ever, tl->d_age, tl->d_ev};
+    void* bufs[] = {tl->state, tl->ids, tl->seen, tl->d_delta_n, tl->d_mismatch, tl->delta, tl->d_score, tl->d_count, tl->d_ever, tl->d_age, tl->d_ev, tl->d_fetch};
     for (void* b : bufs) if (b) cudaFree(b);
     if (tl->h_ev) cudaFreeHost(tl->h_ev);
     for (cudaEvent_t e : tl->slot_ev) if (e) cudaEventDestroy(e);
@@ -804,6 +805,20 @@ int icx_fork_age(IcxWorld* w, uint32_t* n_promoted, int* resolution_needed)
 // Both are asynchronous on `stream` (cudaStream_t, NULL = the default stream): the export waits for the
 // record on the recording world's stream through an event, a replay / scan on another stream waits for the
 // import the same way -- no host synchronisation unless the number of collider rows is unknown to the host.
+// ---- one recorded entity out of a slot (the components an ENTITY_CREATED / JUMP_ARRIVAL handler needs, see include/icx.h) ----
+struct FetchOut { float4 v[TL_ARRAYS]; uint32_t found, has_row, pad[2]; IcxColliderComponent C; };
+__global__ void __launch_bounds__(256) k_entity_fetch(const float4* __restrict__ state, const uint32_t* __restrict__ ids, uint32_t n, uint32_t n_max,
+                                                      const DeltaRow* __restrict__ rows, const uint32_t* __restrict__ d_n, uint32_t cap, uint32_t id, FetchOut* out)
+{
+    if (threadIdx.x == 0) {
+        const uint32_t j = find_id(ids, n, id, ICX_NONE);
+        out->found = j != ICX_NONE ? 1u : 0u;
+        if (j != ICX_NONE) for (int k = 0; k < TL_ARRAYS; k++) out->v[k] = state[(size_t)k * n_max + j];
+    }
+    const uint32_t n_rows = rows ? min(*d_n, cap) : 0u;
+    for (uint32_t i = threadIdx.x; i < n_rows; i += blockDim.x) if (rows[i].id == id) { out->C = rows[i].C; out->has_row = 1u; }
+}
+
 // ---- event records ----
 // the events block of slot s belongs to the tick stamped `coherency`: a block left by an older tick is emptied
 static void ev_claim(IcxTimeline* tl, int s, uint16_t coherency)
@@ -854,6 +869,48 @@ int icx_timeline_events_pop(IcxTimeline* tl, uint16_t now, int mode, IcxTimeline
         for (uint32_t i = 0; i < std::min<uint32_t>(b.n_events, ICX_TIMELINE_EVENTS_PER_TICK); i++) { if (out && n < cap) out[n] = b.ev[i]; n++; }
     }
     if (n_out) *n_out = n;
+    return ICX_OK;
+}
+
+int icx_timeline_entity_fetch(IcxTimeline* tl, uint16_t coherency, IcxEntity id, IcxTransform* T, IcxPhysics* P, uint8_t* has_physics,
+                              IcxColliderComponent* C, int* found)
+{
+    if (!tl || !found) return ICX_E_INVALID;
+    *found = 0;
+    const int s = slot_of(tl, coherency);
+    if (!(tl->valid[s] && tl->stamp[s] == coherency)) return ICX_OK;                // no record of that tick (any more)
+    cudaSetDevice(tl->device);
+    if (!tl->d_fetch) TCK(cudaMalloc(&tl->d_fetch, sizeof(FetchOut)));
+    TCK(cudaEventSynchronize(tl->slot_ev[s]));
+    TCK(cudaMemset(tl->d_fetch, 0, sizeof(FetchOut)));
+    k_entity_fetch<<<1, 256>>>(slot_state(tl, s), slot_ids(tl, s), tl->count[s], tl->n_max,
+                               tl->delta_n[s] != 0 && tl->delta ? tl->delta + (size_t)s * tl->delta_cap : nullptr, tl->d_delta_n + s, tl->delta_cap, id, (FetchOut*)tl->d_fetch);
+    FetchOut h;
+    TCK(cudaMemcpy(&h, tl->d_fetch, sizeof(h), cudaMemcpyDeviceToHost));
+    if (!h.found) return ICX_OK;
+    *found = 1 | (h.has_row ? 2 : 0);
+    // the slot's SoA words back into component rows (the inverse of k_import; same mapping as k_export, icx_convert.cu)
+    const float4 pos = h.v[0], rot = h.v[1], vel = h.v[2], acc = h.v[3], av = h.v[4], aa = h.v[5], p0 = h.v[6], p1 = h.v[7], lp = h.v[8], lr = h.v[9];
+    uint32_t ef; std::memcpy(&ef, &p1.w, 4);
+    if (T) {
+        std::memset(T, 0, sizeof(*T));
+        T->origin[0] = pos.x; T->origin[1] = pos.y; T->origin[2] = pos.z;
+        T->orientation[0] = rot.x; T->orientation[1] = rot.y; T->orientation[2] = rot.z; T->orientation[3] = rot.w;
+        T->scale[0] = p0.x; T->scale[1] = p0.y; T->scale[2] = p0.z;
+    }
+    if (has_physics) *has_physics = (ef & EF_HAS_PHYSICS) ? 1 : 0;
+    if (P) {
+        std::memset(P, 0, sizeof(*P));
+        P->velocity[0] = vel.x; P->velocity[1] = vel.y; P->velocity[2] = vel.z;
+        P->acceleration[0] = acc.x; P->acceleration[1] = acc.y; P->acceleration[2] = acc.z;
+        P->angularVelocity[0] = av.x; P->angularVelocity[1] = av.y; P->angularVelocity[2] = av.z;
+        P->angularAcceleration[0] = aa.x; P->angularAcceleration[1] = aa.y; P->angularAcceleration[2] = aa.z;
+        P->linearDrag = p1.x; P->angularDrag = p1.y; P->collisionAngularDrag = p1.z; P->collisionLinearDrag = lp.w; P->mass = p0.w;
+        P->lockOrigin = (ef & EF_LOCK_ORIGIN) ? 1 : 0; P->lockOrientation = (ef & EF_LOCK_ORIENTATION) ? 1 : 0; P->isAsleep = (ef & EF_ASLEEP) ? 1 : 0;
+        P->lockedOrigin[0] = lp.x; P->lockedOrigin[1] = lp.y; P->lockedOrigin[2] = lp.z;
+        P->lockedOrientation[0] = lr.x; P->lockedOrientation[1] = lr.y; P->lockedOrientation[2] = lr.z; P->lockedOrientation[3] = lr.w;
+    }
+    if (C && h.has_row) *C = h.C;
     return ICX_OK;
 }
 

@@ -56,6 +56,22 @@ def insert_rows(scene, rows):
     return out
 
 
+def arrival_events(ids):
+    """What a timeslice pushes into its past when entities `ids` (as the PAST knows them: chain-link already incremented) arrive:
+    ENTITY_CREATED then JUMP_ARRIVAL per entity (_entity_created_handler, _jump_arrival_handler: server_network_dynamo.cpp:748-777,
+    :940-976).  The arrival's serialised components are not in the event: the tick's ENTITY_UPDATE record carries them."""
+    ids = np.asarray(ids, np.uint32)
+    ev = np.zeros(2 * len(ids), abi.event_dt)
+    ev["type"][0::2], ev["type"][1::2] = abi.EVENT_ENTITY_CREATED, abi.EVENT_JUMP_ARRIVAL
+    ev["entity"][0::2] = ids; ev["entity"][1::2] = ids
+    ev["source"][:] = abi.NULL_ENTITY
+    ev["payload"][0::2, 0] = 0xC1                                            # signature: Transform | Physics | Collider
+    ev["payload"][1::2, 0] = (ids >> 4) & 0xFFFFFF                           # tripId
+    ev["payload"][1::2, 1] = 1                                               # timesliceDelta
+    ev["payload"][1::2, 3] = 0xC1
+    return ev
+
+
 def traveller_row(scene, index, genesis, timeslice):
     """A copy of entity `index` arriving as a time traveller: chain-link 0, its own genesis id, merged state."""
     row = Scene({k: scene[k][index:index + 1].copy() for k in KEYS})
@@ -111,7 +127,40 @@ class DeviceBackend:
 
     # ---- networker phases ----
     def replay(self, k):
-        return k > 0 and self.w[k].replay(self.tl_in[k], self.coherency(k), abi.REPLAY_SERVER)
+        """Phase 2: the events of the future stream that have come due, then the ENTITY_UPDATE records.  ENTITY_CREATED: the entity
+        is created from the components the same tick's record holds, and the creation travels on into this timeslice's own past."""
+        if k == 0:
+            return False
+        c = self.coherency(k)
+        evs = self.tl_in[k].pop_events(c)
+        new = [int(e["entity"]) for e in evs if e["type"] == abi.EVENT_ENTITY_CREATED and not np.isin(e["entity"], self.scene[k].ids)]
+        if new:
+            rows = []
+            for ent in new:
+                row = self.tl_in[k].fetch_entity(c, ent)
+                assert row is not None and row.pop("have_collider"), "the record of the tick an entity is created in carries all its components"
+                rows.append(row)
+            self._create(k, rows)
+        return self.w[k].replay(self.tl_in[k], c, abi.REPLAY_SERVER)
+
+    def _past_ring(self, k):
+        """The ring this timeslice's pushes into the past go to (events ride with the tick's record)."""
+        if k + 1 >= self.n:
+            return None
+        return self.link[k][2] if self.devices[k] != self.devices[k + 1] else self.tl_in[k + 1]
+
+    def _create(self, k, rows):
+        """Cosmos::register_entity + components for the entities `rows` (1-row Scenes), and -- _entity_created_handler -- the
+        creation pushed on into the past."""
+        all_rows = rows[0]
+        for row in rows[1:]:
+            all_rows, _ = insert_row(all_rows, row)
+        self.scene[k] = insert_rows(self.scene[k], all_rows) if self.host_rows else Scene(ids=np.sort(np.concatenate([self.scene[k].ids, all_rows.ids])))
+        assert self.w[k].create_entities(all_rows) == len(rows)
+        assert np.array_equal(self.w[k].entity_ids(), self.scene[k].ids)
+        ring = self._past_ring(k)
+        if ring is not None:
+            ring.push_events(self.coherency(k), arrival_events(pipeline.past_ids(all_rows.ids)))
 
     def record_to_past(self, k):
         if k + 1 >= self.n:
@@ -141,13 +190,8 @@ class DeviceBackend:
 
     def arrive(self, k, rows):
         """Travellers arrive: icx_entities_create -- the timeslice's own entities stay on the device (the host keeps only the
-        row template: ids, hasP)."""
-        all_rows = rows[0]
-        for row in rows[1:]:
-            all_rows, _ = insert_row(all_rows, row)
-        self.scene[k] = insert_rows(self.scene[k], all_rows) if self.host_rows else Scene(ids=np.sort(np.concatenate([self.scene[k].ids, all_rows.ids])))
-        assert self.w[k].create_entities(all_rows) == len(rows)
-        assert np.array_equal(self.w[k].entity_ids(), self.scene[k].ids)
+        row template: ids, hasP) -- and the arrival is pushed into the past."""
+        self._create(k, rows)
 
     def has_future(self, k):
         """entity_has_timestream for every entity of timeslice k: the future neighbour pushes its entities at chain-link + 1."""
@@ -183,6 +227,7 @@ class DeviceBackend:
         c, target = self.coherency(k), self.coherency(k - 1)
         t1 = time.perf_counter()
         while c != target:
+            tl.pop_events(c, abi.REPLAY_PARALLEL)                           # (the parallel cosmos consumes the old history's events too; not acted on here)
             par.replay(tl, c, abi.REPLAY_PARALLEL)                          # pop_timestream_at_breakpoint: consumes old history
             par.record(tl, c, at_breakpoint=True)                           # push_timestream_at_breakpoint: new history
             par.step(DT)

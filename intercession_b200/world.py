@@ -366,6 +366,19 @@ class Timeline:
             raise RuntimeError("more event records due than the pop buffer holds")
         return out[:n.value]
 
+    def fetch_entity(self, coherency, entity):
+        """The recorded components of one entity of the tick stamped `coherency` as a 1-row Scene (None if the record does not
+        hold it); row.have_collider tells whether the record carried its ColliderComponent."""
+        from .scenes import Scene, _empty
+        row = _empty(1)
+        row["ids"] = np.array([entity], np.uint32)
+        found = C.c_int(0)
+        self._ck(self.lib.icx_timeline_entity_fetch(self.handle, coherency, int(entity), abi.ptr(row.T), abi.ptr(row.P), abi.ptr(row.hasP), abi.ptr(row.C), C.byref(found)))
+        if not (found.value & 1):
+            return None
+        row["have_collider"] = bool(found.value & 2)
+        return row
+
     def id_mismatches(self):
         v = C.c_uint64(0)
         self.lib.icx_timeline_id_mismatches(self.handle, C.byref(v))

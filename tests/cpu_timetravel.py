@@ -25,6 +25,7 @@ class CpuBackend:
         lib, prefix = (refs.ref(), "icxref") if (refs.ref() is not None and small) else (refs.oracle(), "icxo")
         self.containers = prefix
         self.tl_in = [None] + [refs.CpuTimeline(lib, prefix) for _ in range(1, self.n)]
+        self.stash = {}
 
     def close(self):
         for t in self.tl_in:
@@ -37,8 +38,25 @@ class CpuBackend:
     def replay(self, k):
         if k == 0:
             return False
+        evs = self.tl_in[k].pop_events(self.coh[k])
+        new = [int(e["entity"]) for e in evs if e["type"] == abi.EVENT_ENTITY_CREATED and not np.isin(e["entity"], self.scene[k].ids)]
+        if new:
+            self._create(k, [self.stash.pop((k, ent)) for ent in new])
         self.scene[k], n = self.tl_in[k].replay(self.scene[k], self.coh[k])
         return n > 0
+
+    def _create(self, k, rows):
+        """register_entity + the serialised components the arrival message carries (here: stashed beside the event), then the
+        creation pushed on into the past (_entity_created_handler / _jump_arrival_handler)."""
+        for row in rows:
+            self.scene[k], _ = timetravel.insert_row(self.scene[k], row)
+        if k + 1 < self.n:
+            ids = np.array([int(r.ids[0]) for r in rows], np.uint32)
+            past = pipeline.past_ids(ids)
+            self.tl_in[k + 1].push_events(self.coh[k], timetravel.arrival_events(past))
+            for row, pid in zip(rows, past):
+                r = row.copy(); r["ids"] = np.array([pid], np.uint32); r["tstate"][:] = abi.TS_MERGED; r["tcoh"][:] = 0
+                self.stash[(k + 1, int(pid))] = r
 
     def record_to_past(self, k):
         if k + 1 < self.n:
@@ -59,8 +77,7 @@ class CpuBackend:
         return self.scene[k].copy()                                         # extract mutates the future neighbour's scene in place
 
     def arrive(self, k, rows):
-        for row in rows:
-            self.scene[k], _ = timetravel.insert_row(self.scene[k], row)
+        self._create(k, rows)
 
     def has_future(self, k):
         return np.isin(self.scene[k].ids, pipeline.past_ids(self.scene[k - 1].ids)).astype(np.uint8)
@@ -74,6 +91,7 @@ class CpuBackend:
         ints = []
         target = self.coh[k - 1]
         while c != target:
+            tl.pop_events(c, mode=abi.REPLAY_PARALLEL)
             tl.replay(par, c, mode=abi.REPLAY_PARALLEL)
             tl.record(par, c, at_breakpoint=True, link_inc=False)
             out = refs.procedures_tick(refs.oracle(), "icxo", par, host=abi.NULL_TIMESLICE, coherency=c)

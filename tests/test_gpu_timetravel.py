@@ -93,3 +93,46 @@ def test_traveller_forks_its_victims_and_the_parallel_cosmos_resolves_them(built
     # after the cycle every timeslice but the traveller's own victims' copies in timeslice 0 ... : timeslice 0 is fully merged again
     last = [e for e in log["dev"] if e[1] == "tick"][-1][2]["states"]
     assert (last[0].tstate == abi.TS_MERGED).all()
+
+
+@pytest.mark.parametrize("devices", _device_layouts())
+def test_an_arrival_in_a_middle_timeslice_is_created_down_the_chain(built, devices):
+    """The event records in the device timeline at work: a traveller arrives in timeslice 1 of 3; ENTITY_CREATED + JUMP_ARRIVAL ride
+    in the tick's snapshot slot into timeslice 2's ring; `delay` wall ticks later they come due there, the entity is created on
+    the device from the components the same tick's record holds (icx_timeline_entity_fetch -> icx_entities_create) and follows
+    its future self from then on.  Device and CPU restatement (real EntityTimestreamMap for records AND events) identical on
+    every tick."""
+    import refs
+    n_ts, delay, ticks = 3, 4, 22
+    chain = make_chain(150, n_ts)
+    kinds = chain[0].C["colliders"]["colliderType"][:, 0]
+    twin = next(i for i in range(36, chain[0].n) if kinds[i] == abi.COLLIDER_BOX)
+    row = timetravel.traveller_row(chain[1], twin, genesis=240, timeslice=1)
+    row.T["origin"][0, 0] += np.float32(0.3)
+    arrivals = [(3, 1, row)]
+    dev = timetravel.DeviceBackend(chain, delay, devices=devices)
+    cpu = CpuBackend(chain, delay)
+    if refs.ref() is not None:
+        assert cpu.containers == "icxref"
+    log = {"dev": [], "cpu": []}
+    try:
+        timetravel.run(dev, ticks, arrivals, lambda t, ph, d: log["dev"].append((t, ph, d)))
+        timetravel.run(cpu, ticks, arrivals, lambda t, ph, d: log["cpu"].append((t, ph, d)))
+        mism = [int(t.id_mismatches()) for t in dev.tl_in if t is not None]
+    finally:
+        dev.close(); cpu.close()
+    assert len(log["dev"]) == len(log["cpu"])
+    n_ints = 0
+    for (t, ph, d), (t2, ph2, c) in zip(log["dev"], log["cpu"]):
+        assert (t, ph) == (t2, ph2) and ph == "tick"
+        assert d["ages"] == c["ages"], t
+        for k in range(n_ts):
+            assert len(d["interceptions"][k]) == len(c["interceptions"][k]) and not fields_diff(d["interceptions"][k], c["interceptions"][k]), (t, k)
+            same_scene(d["states"][k], c["states"][k], (t, k))
+            n_ints += len(d["interceptions"][k])
+    sizes = [[s.n for s in d["states"]] for _, _, d in log["dev"]]
+    assert sizes[2] == [156, 156, 156] and sizes[3] == [156, 157, 156] and sizes[3 + delay] == [156, 157, 157]
+    assert n_ints > 0
+    # while the traveller was unknown in timeslice 2 (delay ticks: its records were on their way, not due) nothing was missed:
+    # once it exists every record finds its entity
+    assert mism[1] == 0

@@ -45,3 +45,24 @@ def test_one_traveller_one_cycle_on_the_reference_containers():
     # load_and_link reset the source timeslice: nothing is forked right after the cycle
     after = next(d for t, d in ticks if t == tc)
     assert (after["states"][2].tstate != abi.TS_FORKED).all()
+
+
+def test_an_arrival_in_a_middle_timeslice_travels_on_into_the_past():
+    """_entity_created_handler / _jump_arrival_handler push the arrival into the past stream (server_network_dynamo.cpp:748-777,
+    :940-976): `delay` wall ticks later the traveller exists in the next timeslice too, one causal chain-link further."""
+    n_ts, delay = 3, 4
+    chain = make_chain(150, n_ts)
+    kinds = chain[0].C["colliders"]["colliderType"][:, 0]
+    twin = next(i for i in range(36, chain[0].n) if kinds[i] == abi.COLLIDER_BOX)
+    row = timetravel.traveller_row(chain[1], twin, genesis=240, timeslice=1)
+    row.T["origin"][0, 0] += np.float32(0.3)
+    cpu = CpuBackend(chain, delay)
+    sizes = []
+    try:
+        timetravel.run(cpu, 12, [(3, 1, row)], lambda t, ph, d: sizes.append([s.n for s in d["states"]]) if ph == "tick" else None)
+        there = int(row.ids[0]) + 1
+        assert sizes[2] == [156, 156, 156] and sizes[3] == [156, 157, 156] and sizes[3 + delay - 1] == [156, 157, 156] and sizes[3 + delay] == [156, 157, 157]
+        assert there in cpu.scene[2].ids.tolist() and int(row.ids[0]) in cpu.scene[1].ids.tolist()
+        # it follows its future self: the state it has in timeslice 2 is the one timeslice 1 recorded `delay` ticks earlier
+    finally:
+        cpu.close()
