@@ -72,6 +72,16 @@ def arrival_events(ids):
     return ev
 
 
+def removal_events(ids):
+    """ENTITY_REMOVED for entities `ids` (as the past knows them), _entity_removed_handler: server_network_dynamo.cpp:779-811."""
+    ids = np.asarray(ids, np.uint32)
+    ev = np.zeros(len(ids), abi.event_dt)
+    ev["type"] = abi.EVENT_ENTITY_REMOVED
+    ev["entity"] = ids
+    ev["source"] = abi.NULL_ENTITY                                           # forced: nothing inside the cosmos caused it
+    return ev
+
+
 def traveller_row(scene, index, genesis, timeslice):
     """A copy of entity `index` arriving as a time traveller: chain-link 0, its own genesis id, merged state."""
     row = Scene({k: scene[k][index:index + 1].copy() for k in KEYS})
@@ -141,7 +151,20 @@ class DeviceBackend:
                 assert row is not None and row.pop("have_collider"), "the record of the tick an entity is created in carries all its components"
                 rows.append(row)
             self._create(k, rows)
+        gone = [int(e["entity"]) for e in evs if e["type"] == abi.EVENT_ENTITY_REMOVED and np.isin(e["entity"], self.scene[k].ids)]
+        if gone:
+            self.depart(k, gone)
         return self.w[k].replay(self.tl_in[k], c, abi.REPLAY_SERVER)
+
+    def depart(self, k, ids):
+        """Cosmos::condemn_entity for `ids` (a departure, or ENTITY_REMOVED from the future stream), and the removal pushed on."""
+        ids = np.asarray(ids, np.uint32)
+        keep = ~np.isin(self.scene[k].ids, ids)
+        self.scene[k] = Scene({key: (v[keep] if isinstance(v, np.ndarray) and key in KEYS else v) for key, v in self.scene[k].items()})
+        assert self.w[k].remove_entities(ids) == len(ids)
+        ring = self._past_ring(k)
+        if ring is not None:
+            ring.push_events(self.coherency(k), removal_events(pipeline.past_ids(ids)))
 
     def _past_ring(self, k):
         """The ring this timeslice's pushes into the past go to (events ride with the tick's record)."""
@@ -242,8 +265,8 @@ class DeviceBackend:
         return {"cloned": n, "extracted": n_ex, "missing": n_miss, "interceptions": ints, "parallel_end": end}
 
 
-def run(backend, wall_ticks, arrivals=(), observe=None, with_states=True):
-    """Drive the chain for `wall_ticks` wall ticks.  arrivals: [(wall tick, timeslice, row)].  observe(tick, phase, data) is called
+def run(backend, wall_ticks, arrivals=(), observe=None, with_states=True, departures=()):
+    """Drive the chain for `wall_ticks` wall ticks.  arrivals: [(wall tick, timeslice, row)]; departures: [(wall tick, timeslice, ids)].  observe(tick, phase, data) is called
     with what both back ends must agree on.  Returns the number of parallel cycles that ran."""
     cycles = 0
     n = backend.n
@@ -253,6 +276,9 @@ def run(backend, wall_ticks, arrivals=(), observe=None, with_states=True):
             rows = [row for (ta, ka, row) in arrivals if ta == t and ka == k]
             if rows:
                 backend.arrive(k, rows)
+            for (td, kd, ids) in departures:
+                if td == t and kd == k:
+                    backend.depart(k, ids)
         # fork ageing of the PREVIOUS tick decided whether a resolution is needed; the cycle runs before this tick's networker
         need = getattr(backend, "_need", False)
         if need:

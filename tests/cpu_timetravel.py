@@ -42,8 +42,18 @@ class CpuBackend:
         new = [int(e["entity"]) for e in evs if e["type"] == abi.EVENT_ENTITY_CREATED and not np.isin(e["entity"], self.scene[k].ids)]
         if new:
             self._create(k, [self.stash.pop((k, ent)) for ent in new])
+        gone = [int(e["entity"]) for e in evs if e["type"] == abi.EVENT_ENTITY_REMOVED and np.isin(e["entity"], self.scene[k].ids)]
+        if gone:
+            self.depart(k, gone)
         self.scene[k], n = self.tl_in[k].replay(self.scene[k], self.coh[k])
         return n > 0
+
+    def depart(self, k, ids):
+        ids = np.asarray(ids, np.uint32)
+        keep = ~np.isin(self.scene[k].ids, ids)
+        self.scene[k] = Scene({key: (v[keep] if isinstance(v, np.ndarray) and key in timetravel.KEYS else v) for key, v in self.scene[k].items()})
+        if k + 1 < self.n:
+            self.tl_in[k + 1].push_events(self.coh[k], timetravel.removal_events(pipeline.past_ids(ids)))
 
     def _create(self, k, rows):
         """register_entity + the serialised components the arrival message carries (here: stashed beside the event), then the

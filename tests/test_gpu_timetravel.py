@@ -116,8 +116,9 @@ def test_an_arrival_in_a_middle_timeslice_is_created_down_the_chain(built, devic
         assert cpu.containers == "icxref"
     log = {"dev": [], "cpu": []}
     try:
-        timetravel.run(dev, ticks, arrivals, lambda t, ph, d: log["dev"].append((t, ph, d)))
-        timetravel.run(cpu, ticks, arrivals, lambda t, ph, d: log["cpu"].append((t, ph, d)))
+        leaves = [(12, 1, row.ids.copy())]                         # ... and leaves again at wall tick 12: ENTITY_REMOVED follows it down
+        timetravel.run(dev, ticks, arrivals, lambda t, ph, d: log["dev"].append((t, ph, d)), departures=leaves)
+        timetravel.run(cpu, ticks, arrivals, lambda t, ph, d: log["cpu"].append((t, ph, d)), departures=leaves)
         mism = [int(t.id_mismatches()) for t in dev.tl_in if t is not None]
     finally:
         dev.close(); cpu.close()
@@ -132,6 +133,7 @@ def test_an_arrival_in_a_middle_timeslice_is_created_down_the_chain(built, devic
             n_ints += len(d["interceptions"][k])
     sizes = [[s.n for s in d["states"]] for _, _, d in log["dev"]]
     assert sizes[2] == [156, 156, 156] and sizes[3] == [156, 157, 156] and sizes[3 + delay] == [156, 157, 157]
+    assert sizes[11] == [156, 157, 157] and sizes[12] == [156, 156, 157] and sizes[12 + delay] == [156, 156, 156]
     assert n_ints > 0
     # while the traveller was unknown in timeslice 2 (delay ticks: its records were on their way, not due) nothing was missed:
     # once it exists every record finds its entity

@@ -59,10 +59,12 @@ def test_an_arrival_in_a_middle_timeslice_travels_on_into_the_past():
     cpu = CpuBackend(chain, delay)
     sizes = []
     try:
-        timetravel.run(cpu, 12, [(3, 1, row)], lambda t, ph, d: sizes.append([s.n for s in d["states"]]) if ph == "tick" else None)
+        timetravel.run(cpu, 18, [(3, 1, row)], lambda t, ph, d: sizes.append([s.n for s in d["states"]]) if ph == "tick" else None,
+                       departures=[(12, 1, row.ids.copy())])
         there = int(row.ids[0]) + 1
         assert sizes[2] == [156, 156, 156] and sizes[3] == [156, 157, 156] and sizes[3 + delay - 1] == [156, 157, 156] and sizes[3 + delay] == [156, 157, 157]
-        assert there in cpu.scene[2].ids.tolist() and int(row.ids[0]) in cpu.scene[1].ids.tolist()
-        # it follows its future self: the state it has in timeslice 2 is the one timeslice 1 recorded `delay` ticks earlier
+        # ... and when it leaves again (wall tick 12), ENTITY_REMOVED follows it into the past
+        assert sizes[11] == [156, 157, 157] and sizes[12] == [156, 156, 157] and sizes[12 + delay] == [156, 156, 156]
+        assert there not in cpu.scene[2].ids.tolist() and int(row.ids[0]) not in cpu.scene[1].ids.tolist()
     finally:
         cpu.close()
