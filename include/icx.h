@@ -351,6 +351,11 @@ ICX_API int icx_entity_ids_fetch(IcxWorld* w, IcxEntity* out, size_t cap, size_t
  * reference registers them, :241-245: entity lifecycle is host-side).
  */
 ICX_API int icx_world_extract(IcxWorld* par, IcxWorld* dst, uint32_t* n_extracted, uint32_t* n_missing);
+/* The same with flags.  ICX_EXTRACT_REGISTER: ids absent from dst are registered there first, from the parallel world's rows, as
+ * the reference does (:241-245), and then extracted like the others (*n_missing = 0 afterwards unless dst is full:
+ * ICX_E_CAPACITY).  dst's row indices change when something was registered (icx_entity_ids_fetch). */
+#define ICX_EXTRACT_REGISTER 1u
+ICX_API int icx_world_extract_ex(IcxWorld* par, IcxWorld* dst, uint32_t flags, uint32_t* n_extracted, uint32_t* n_missing);
 
 /* Cosmos::get/set_coherency (cosmos.cpp:136-147) */
 ICX_API int icx_coherency_set(IcxWorld* w, uint16_t coherency);

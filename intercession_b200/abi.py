@@ -212,6 +212,7 @@ SIGNATURES = {
     "icx_timeline_slot_import": (C.c_int, [_vp, C.c_uint16, _u32, _vp, _sz, _vp]),
     "icx_world_clone": (C.c_int, [_vp, _vp, _vp, C.POINTER(_u32)]),
     "icx_world_extract": (C.c_int, [_vp, _vp, C.POINTER(_u32), C.POINTER(_u32)]),
+    "icx_world_extract_ex": (C.c_int, [_vp, _vp, _u32, C.POINTER(_u32), C.POINTER(_u32)]),
     "icx_mesh_upload": (C.c_int, [_vp, _vp, _u32, _vp, _u32, _vp]),
     "icx_mesh_contacts_fetch": (C.c_int, [_vp, _vp, _sz, _psz]),
     "icx_mesh_kernel_us": (C.c_int, [_vp, C.POINTER(C.c_float)]),

@@ -264,7 +264,43 @@ int icx_world_clone(IcxWorld* src, IcxWorld* dst, const uint8_t* has_future, uin
 
 int icx_world_extract(IcxWorld* par, IcxWorld* dst, uint32_t* n_extracted, uint32_t* n_missing)
 {
+    return icx_world_extract_ex(par, dst, 0u, n_extracted, n_missing);
+}
+
+int icx_world_extract_ex(IcxWorld* par, IcxWorld* dst, uint32_t flags, uint32_t* n_extracted, uint32_t* n_missing)
+{
     if (!par || !dst || par == dst) return ICX_E_INVALID;
+    if (flags & ICX_EXTRACT_REGISTER) {
+        // :241-245 "entity with non-null host from past does not already exist in future, registering it": the absent ones are
+        // created in dst first, from the parallel world's rows, {merged, 0} like Cosmos::register_entity leaves them; the loop
+        // below then finds every id
+        std::vector<uint32_t> have(dst->h_ids.begin(), dst->h_ids.begin() + dst->n_entities);
+        std::sort(have.begin(), have.end());
+        std::vector<uint32_t> rows;
+        for (uint32_t i = 0; i < par->n_entities; i++) {
+            const uint32_t id = par->h_ids[i], link = id & 0xFu;
+            if (link >= ICX_NULL_CHAINLINK || link == 0u || (id >> 28) == ICX_NULL_TIMESLICE) continue;
+            if (!std::binary_search(have.begin(), have.end(), id - 1u)) rows.push_back(i);
+        }
+        if (!rows.empty()) {
+            const size_t k = rows.size();
+            int rc = gather(par, rows, 1);
+            if (rc != ICX_OK) { dst->error = par->error; return rc; }
+            std::vector<uint32_t> ids(k); std::vector<IcxTransform> T(k); std::vector<IcxPhysics> P(k); std::vector<IcxColliderComponent> C(k);
+            std::vector<uint8_t> hp(k), ts(k, ICX_TS_MERGED); std::vector<uint16_t> tc(k, 0);
+            cudaSetDevice(par->device);
+            CKW(par, cudaMemcpy(ids.data(), par->cl_ids.ptr, k * 4, cudaMemcpyDeviceToHost));
+            CKW(par, cudaMemcpy(T.data(), par->cl_T.ptr, k * sizeof(IcxTransform), cudaMemcpyDeviceToHost));
+            CKW(par, cudaMemcpy(hp.data(), par->cl_hasP.ptr, k, cudaMemcpyDeviceToHost));
+            if (par->have_P) CKW(par, cudaMemcpy(P.data(), par->cl_P.ptr, k * sizeof(IcxPhysics), cudaMemcpyDeviceToHost));
+            if (par->have_C) CKW(par, cudaMemcpy(C.data(), par->cl_C.ptr, k * sizeof(IcxColliderComponent), cudaMemcpyDeviceToHost));
+            for (size_t i = 0; i < k; i++) ids[i] -= 1u;                            // chain-link - 1
+            uint32_t made = 0;
+            rc = icx_entities_create(dst, (uint32_t)k, ids.data(), T.data(), par->have_P ? P.data() : nullptr, hp.data(),
+                                     par->have_C ? C.data() : nullptr, ts.data(), tc.data(), &made);
+            if (rc != ICX_OK) return rc;
+        }
+    }
     if (n_extracted) *n_extracted = 0;
     if (n_missing) *n_missing = 0;
     if (par->have_C && !dst->have_C) return cfail(dst, ICX_E_STATE, "extract: destination has no collider components");

@@ -263,12 +263,15 @@ class World:
         dst.n = n.value
         return n.value
 
-    def extract_into(self, dst):
-        """Write this (parallel) world's temporal entities back into dst at chain-link - 1: (extracted, missing)."""
+    def extract_into(self, dst, register=False):
+        """Write this (parallel) world's temporal entities back into dst at chain-link - 1: (extracted, missing).
+        register: ids absent from dst are registered there first (parallel_cosmos_context.cpp:241-245)."""
         n, miss = C.c_uint32(0), C.c_uint32(0)
-        rc = self.lib.icx_world_extract(self.handle, dst.handle, C.byref(n), C.byref(miss))
+        rc = self.lib.icx_world_extract_ex(self.handle, dst.handle, 1 if register else 0, C.byref(n), C.byref(miss))
         if rc != abi.OK:
             raise IcxError(rc, self.lib.icx_last_error(dst.handle).decode())
+        if register:
+            dst.n = len(dst.entity_ids())
         return n.value, miss.value
 
     # ---- static triangle mesh (extension without a counterpart in the reference) ----

@@ -46,8 +46,9 @@ def load_and_link(src, src_coherency, has_future=None):
     return par, src_coherency
 
 
-def extract_entity_updates(par, dst, dst_coherency, dst_host_id):
-    """Mutates dst; returns (extracted, missing).
+def extract_entity_updates(par, dst, dst_coherency, dst_host_id, register=False):
+    """Mutates dst; returns (extracted, missing).  register=True: returns (dst with the absent entities registered, extracted,
+    registered) instead -- :241-245, Cosmos::register_entity leaves them {merged, 0} and the loop then treats them like the rest.
 
     :206-272 for every entity of the parallel cosmos:
       :212    localEntity = id with the chain-link decremented; link 15 -> ignored (:213-219),
@@ -58,6 +59,26 @@ def extract_entity_updates(par, dst, dst_coherency, dst_host_id):
       :255    if link(localEntity) > 0 the timestream state follows (stamped with dst's coherency)
       :268-271 timeslice 0 re-merges it
     """
+    if register:
+        import numpy as np
+        have = set(int(e) for e in dst.ids)
+        absent = [i for i in range(par.n) if (int(par.ids[i]) & 15) not in (0, NULL_CHAINLINK) and (int(par.ids[i]) >> 28) != NULL_TIMESLICE
+                  and int(par.ids[i]) - 1 not in have]
+        if absent:
+            keys = ("ids", "T", "P", "hasP", "C", "tstate", "tcoh")
+            ids = np.concatenate([dst.ids, par.ids[absent] - 1]).astype(np.uint32)
+            ascending = bool(np.all(np.diff(dst.ids.astype(np.int64)) > 0))
+            order = np.argsort(ids, kind="stable") if ascending else np.arange(len(ids))   # icx_entities_create: sorted in, else appended
+            grown = type(dst)({k: v for k, v in dst.items() if k not in keys})
+            for k in keys:
+                v = np.empty(dst.n + len(absent), dst[k].dtype)
+                v[:dst.n] = dst[k]
+                v[dst.n:] = {"ids": par.ids[absent] - 1, "tstate": TS_MERGED, "tcoh": 0}.get(k, par[k][absent] if k not in ("tstate", "tcoh") else 0)
+                grown[k] = v[order]
+            dst = grown
+        n_ex, n_miss = extract_entity_updates(par, dst, dst_coherency, dst_host_id)
+        assert n_miss == 0
+        return dst, n_ex, len(absent)
     where = {int(e): j for j, e in enumerate(dst.ids)}
     extracted = missing = 0
     for i in range(par.n):

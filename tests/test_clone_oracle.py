@@ -155,6 +155,24 @@ def test_extract_matches_the_reference_loop(seed, host):
     assert miss_o == reg_r == 0 and n_o == n_r > 50
     same_scene(a, b)
     assert (a.T["origin"] != dst.T["origin"]).any()
+    # a destination that lacks some of them: the reference registers exactly the ones the restatement registers (:241-245)
+    lack = rng.random(dst.n) < 0.15
+    small = dst.copy()
+    for k in ("ids", "T", "P", "hasP", "C", "tstate", "tcoh"):
+        small[k] = dst[k][~lack].copy()
+    grown, n_o2, reg_o = clone_oracle.extract_entity_updates(par, small.copy(), 88, host, register=True)
+    _, reg_r2 = refs.ref_extract(par, small.copy(), 88, host)
+    assert reg_o == reg_r2 > 0 and n_o2 == n_o and grown.n == small.n + reg_o
+    sub = np.isin(a.ids, grown.ids)                                             # (what nobody extracts -- non-temporal ids, ids created during the run -- stays lacking)
+    part = a.copy()
+    for k in ("ids", "T", "P", "hasP", "C", "tstate", "tcoh"):
+        part[k] = a[k][sub].copy()
+    assert np.array_equal(grown.ids, part.ids)                                  # registered + extracted = what the full destination became
+    for k in ("T", "P", "C"):                                                   # (a registered link-0 entity starts {merged, 0}; the full destination's kept its old state)
+        rows = grown.hasP.astype(bool) if k == "P" else np.ones(grown.n, bool)     # (no PhysicsComponent: the row's P bytes mean nothing)
+        assert not fields_diff(grown[k][rows], part[k][rows]), k
+    fresh = np.isin(grown.ids, small.ids, invert=True)
+    assert ((grown.tstate[fresh] == abi.TS_MERGED) | ((grown.ids[fresh] & 15) > 0) | (host == 0)).all()
 
 
 @needs_ref

@@ -98,3 +98,31 @@ def test_extract_counts_missing_and_rejects_link0(built):
         with pytest.raises(world.IcxError) as ei:
             par.extract_into(dst)
         assert ei.value.code == abi.E_INVALID
+
+
+def test_extract_registers_what_the_destination_lacks(built):
+    """parallel_cosmos_context.cpp:241-245: an entity of the past that does not exist in the future is registered there, then
+    extracted like the others.  On the device the destination's own rows stay where they are (icx_entities_create)."""
+    s, _ = past_scene(n=50, seed=2)
+    s.ids[:50] = (s.ids[:50] & ~np.uint32(15)) | 2
+    s.ids[50:] |= 15
+    assert np.all(np.diff(s.ids.astype(np.int64)) > 0)
+    full = s.copy()
+    full["ids"] = np.where((s.ids & 15) < 15, s.ids - 1, s.ids).astype(np.uint32)
+    full.T["origin"][:50] += np.float32(0.25)
+    keep = np.ones(s.n, bool); keep[[3, 10, 20, 30, 44]] = False
+    fut = scenes.Scene({k: (v[keep] if isinstance(v, np.ndarray) and k in ("ids", "T", "P", "hasP", "C", "tstate", "tcoh") else v) for k, v in full.items()})
+    for host in (1, 0):
+        with world.World(s.n, host_timeslice=abi.NULL_TIMESLICE) as par, world.World(s.n, host_timeslice=host) as dst:
+            par.upload(s); par.step(DT, 2)
+            dst.upload(fut); dst.set_coherency(par.coherency())
+            exp, n_ex, n_reg = clone_oracle.extract_entity_updates(par.download(s), fut.copy(), dst.coherency(), host, register=True)
+            assert (n_ex, n_reg) == (50, 5) and exp.n == s.n
+            assert par.extract_into(dst, register=True) == (50, 0)
+            assert np.array_equal(dst.entity_ids(), exp.ids)
+            same(dst.download(exp), exp)
+            # the registered entities are live: both worlds tick on identically from here
+            with world.World(s.n, host_timeslice=host) as fresh:
+                fresh.upload(exp); fresh.set_coherency(dst.coherency())
+                dst.step(DT, 3); fresh.step(DT, 3)
+                same(dst.download(exp), fresh.download(exp))
