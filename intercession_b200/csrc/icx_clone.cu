@@ -130,10 +130,20 @@ int icx_entities_create(IcxWorld* w, uint32_t count, const IcxEntity* entity, co
     if ((w->have_P && !P) || (w->have_C && !C)) return cfail(w, ICX_E_INVALID, "create: the world holds physics / collider components, the new rows need them too");
     const uint32_t n_old = w->n_entities;
     // an id that exists already is left alone (server_network_dynamo.cpp:431-437 "excessive creation ... ignoring")
-    std::unordered_map<uint32_t, uint32_t> have; have.reserve((size_t)n_old * 2 + count);
-    for (uint32_t j = 0; j < n_old; j++) have.emplace(w->h_ids[j], j);
+    const bool live_sorted = std::is_sorted(w->h_ids.begin(), w->h_ids.begin() + n_old);
     std::vector<uint32_t> take;                                                     // rows of the caller's arrays that are created
-    for (uint32_t i = 0; i < count; i++) if (have.emplace(entity[i], n_old + (uint32_t)take.size()).second) take.push_back(i);
+    if (live_sorted) {                                                              // (the usual case: one binary search per new id)
+        std::vector<uint32_t> seen;
+        for (uint32_t i = 0; i < count; i++) {
+            if (std::binary_search(w->h_ids.begin(), w->h_ids.begin() + n_old, entity[i])) continue;
+            if (std::find(seen.begin(), seen.end(), entity[i]) != seen.end()) continue;
+            seen.push_back(entity[i]); take.push_back(i);
+        }
+    } else {
+        std::unordered_map<uint32_t, uint32_t> have; have.reserve((size_t)n_old * 2 + count);
+        for (uint32_t j = 0; j < n_old; j++) have.emplace(w->h_ids[j], j);
+        for (uint32_t i = 0; i < count; i++) if (have.emplace(entity[i], n_old + (uint32_t)take.size()).second) take.push_back(i);
+    }
     const uint32_t n_app = (uint32_t)take.size();
     if (!n_app) return ICX_OK;
     if ((size_t)n_old + n_app > w->cap_entities) return cfail(w, ICX_E_CAPACITY, "create: max_entities too small");
@@ -160,9 +170,16 @@ int icx_entities_create(IcxWorld* w, uint32_t count, const IcxEntity* entity, co
     CKW(w, cudaStreamSynchronize(st));                                              // ts / hp are locals
     // new submission order: ascending ids when the live ones are (std::set<Entity>, ecs/i_synchro.h:48), else appended
     std::vector<uint32_t> order(n_old + n_app);
-    for (uint32_t i = 0; i < n_old + n_app; i++) order[i] = i;
-    if (std::is_sorted(w->h_ids.begin(), w->h_ids.begin() + n_old))
-        std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return w->h_ids[a] < w->h_ids[b]; });
+    if (live_sorted) {                                                              // merge: the few new rows (sorted among themselves) into the live run
+        std::vector<uint32_t> fresh(n_app);
+        for (uint32_t a = 0; a < n_app; a++) fresh[a] = n_old + a;
+        std::sort(fresh.begin(), fresh.end(), [&](uint32_t a, uint32_t b) { return w->h_ids[a] < w->h_ids[b]; });
+        uint32_t i = 0, a = 0, o = 0;
+        while (i < n_old || a < n_app) {
+            if (a == n_app || (i < n_old && w->h_ids[i] < w->h_ids[fresh[a]])) order[o++] = i++;
+            else order[o++] = fresh[a++];
+        }
+    } else for (uint32_t i = 0; i < n_old + n_app; i++) order[i] = i;
     const int rc = restructure(w, order);
     if (rc == ICX_OK && n_created) *n_created = n_app;
     return rc;

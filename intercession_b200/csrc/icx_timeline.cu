@@ -810,13 +810,13 @@ struct FetchOut { float4 v[TL_ARRAYS]; uint32_t found, has_row, pad[2]; IcxColli
 __global__ void __launch_bounds__(256) k_entity_fetch(const float4* __restrict__ state, const uint32_t* __restrict__ ids, uint32_t n, uint32_t n_max,
                                                       const DeltaRow* __restrict__ rows, const uint32_t* __restrict__ d_n, uint32_t cap, uint32_t id, FetchOut* out)
 {
-    if (threadIdx.x == 0) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
         const uint32_t j = find_id(ids, n, id, ICX_NONE);
         out->found = j != ICX_NONE ? 1u : 0u;
         if (j != ICX_NONE) for (int k = 0; k < TL_ARRAYS; k++) out->v[k] = state[(size_t)k * n_max + j];
     }
     const uint32_t n_rows = rows ? min(*d_n, cap) : 0u;
-    for (uint32_t i = threadIdx.x; i < n_rows; i += blockDim.x) if (rows[i].id == id) { out->C = rows[i].C; out->has_row = 1u; }
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_rows; i += gridDim.x * blockDim.x) if (rows[i].id == id) { out->C = rows[i].C; out->has_row = 1u; }
 }
 
 // ---- event records ----
@@ -883,7 +883,7 @@ int icx_timeline_entity_fetch(IcxTimeline* tl, uint16_t coherency, IcxEntity id,
     if (!tl->d_fetch) TCK(cudaMalloc(&tl->d_fetch, sizeof(FetchOut)));
     TCK(cudaEventSynchronize(tl->slot_ev[s]));
     TCK(cudaMemset(tl->d_fetch, 0, sizeof(FetchOut)));
-    k_entity_fetch<<<1, 256>>>(slot_state(tl, s), slot_ids(tl, s), tl->count[s], tl->n_max,
+    k_entity_fetch<<<tl->sms * 2, 256>>>(slot_state(tl, s), slot_ids(tl, s), tl->count[s], tl->n_max,
                                tl->delta_n[s] != 0 && tl->delta ? tl->delta + (size_t)s * tl->delta_cap : nullptr, tl->d_delta_n + s, tl->delta_cap, id, (FetchOut*)tl->d_fetch);
     FetchOut h;
     TCK(cudaMemcpy(&h, tl->d_fetch, sizeof(h), cudaMemcpyDeviceToHost));

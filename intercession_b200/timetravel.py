@@ -114,6 +114,7 @@ class DeviceBackend:
         self.tl_in = [None] + [world.Timeline(2 * delay + 4, cap, device=self.devices[k]) for k in range(1, self.n)]
         self.par = {}                                                       # device -> the parallel cosmos' world there
         self._pool = None
+        self.lifecycle_ticks = set()                                        # wall ticks in which entities were created / removed (bench)
         self.keep_parallel_end = host_rows
         self.link = {}
         if not host_rows:
@@ -135,6 +136,12 @@ class DeviceBackend:
     def coherency(self, k):
         return self.w[k].coherency()
 
+    def _has(self, k, entity):
+        """entity_exists: the ids of a timeslice are kept ascending (np.isin on a scalar builds a 2^28-entry table)."""
+        ids = self.scene[k].ids
+        j = int(np.searchsorted(ids, entity))
+        return j < len(ids) and ids[j] == entity
+
     # ---- networker phases ----
     def replay(self, k):
         """Phase 2: the events of the future stream that have come due, then the ENTITY_UPDATE records.  ENTITY_CREATED: the entity
@@ -143,7 +150,7 @@ class DeviceBackend:
             return False
         c = self.coherency(k)
         evs = self.tl_in[k].pop_events(c)
-        new = [int(e["entity"]) for e in evs if e["type"] == abi.EVENT_ENTITY_CREATED and not np.isin(e["entity"], self.scene[k].ids)]
+        new = [int(e["entity"]) for e in evs if e["type"] == abi.EVENT_ENTITY_CREATED and not self._has(k, e["entity"])]
         if new:
             rows = []
             for ent in new:
@@ -151,15 +158,16 @@ class DeviceBackend:
                 assert row is not None and row.pop("have_collider"), "the record of the tick an entity is created in carries all its components"
                 rows.append(row)
             self._create(k, rows)
-        gone = [int(e["entity"]) for e in evs if e["type"] == abi.EVENT_ENTITY_REMOVED and np.isin(e["entity"], self.scene[k].ids)]
+        gone = [int(e["entity"]) for e in evs if e["type"] == abi.EVENT_ENTITY_REMOVED and self._has(k, e["entity"])]
         if gone:
             self.depart(k, gone)
         return self.w[k].replay(self.tl_in[k], c, abi.REPLAY_SERVER)
 
     def depart(self, k, ids):
         """Cosmos::condemn_entity for `ids` (a departure, or ENTITY_REMOVED from the future stream), and the removal pushed on."""
+        self.lifecycle_ticks.add(getattr(self, "_tick", -1))
         ids = np.asarray(ids, np.uint32)
-        keep = ~np.isin(self.scene[k].ids, ids)
+        keep = ~np.isin(self.scene[k].ids, ids, kind="sort")
         self.scene[k] = Scene({key: (v[keep] if isinstance(v, np.ndarray) and key in KEYS else v) for key, v in self.scene[k].items()})
         assert self.w[k].remove_entities(ids) == len(ids)
         ring = self._past_ring(k)
@@ -175,6 +183,7 @@ class DeviceBackend:
     def _create(self, k, rows):
         """Cosmos::register_entity + components for the entities `rows` (1-row Scenes), and -- _entity_created_handler -- the
         creation pushed on into the past."""
+        self.lifecycle_ticks.add(getattr(self, "_tick", -1))
         all_rows = rows[0]
         for row in rows[1:]:
             all_rows, _ = insert_row(all_rows, row)
@@ -218,7 +227,7 @@ class DeviceBackend:
 
     def has_future(self, k):
         """entity_has_timestream for every entity of timeslice k: the future neighbour pushes its entities at chain-link + 1."""
-        return np.isin(self.scene[k].ids, pipeline.past_ids(self.scene[k - 1].ids)).astype(np.uint8)
+        return np.isin(self.scene[k].ids, pipeline.past_ids(self.scene[k - 1].ids), kind="sort").astype(np.uint8)
 
     def pmap(self, fn, ks):
         """One phase of a wall tick over the timeslices: concurrently (one host thread per timeslice; the C ABI calls release
@@ -272,6 +281,7 @@ def run(backend, wall_ticks, arrivals=(), observe=None, with_states=True, depart
     n = backend.n
     pmap = getattr(backend, "pmap", None) or (lambda fn, ks: [fn(k) for k in ks])
     for t in range(wall_ticks):
+        backend._tick = t
         for k in range(n):
             rows = [row for (ta, ka, row) in arrivals if ta == t and ka == k]
             if rows:

@@ -35,14 +35,19 @@ class CpuBackend:
     def coherency(self, k):
         return self.coh[k]
 
+    def _has(self, k, entity):
+        ids = self.scene[k].ids
+        j = int(np.searchsorted(ids, entity))
+        return j < len(ids) and ids[j] == entity
+
     def replay(self, k):
         if k == 0:
             return False
         evs = self.tl_in[k].pop_events(self.coh[k])
-        new = [int(e["entity"]) for e in evs if e["type"] == abi.EVENT_ENTITY_CREATED and not np.isin(e["entity"], self.scene[k].ids)]
+        new = [int(e["entity"]) for e in evs if e["type"] == abi.EVENT_ENTITY_CREATED and not self._has(k, e["entity"])]
         if new:
             self._create(k, [self.stash.pop((k, ent)) for ent in new])
-        gone = [int(e["entity"]) for e in evs if e["type"] == abi.EVENT_ENTITY_REMOVED and np.isin(e["entity"], self.scene[k].ids)]
+        gone = [int(e["entity"]) for e in evs if e["type"] == abi.EVENT_ENTITY_REMOVED and self._has(k, e["entity"])]
         if gone:
             self.depart(k, gone)
         self.scene[k], n = self.tl_in[k].replay(self.scene[k], self.coh[k])
@@ -50,7 +55,7 @@ class CpuBackend:
 
     def depart(self, k, ids):
         ids = np.asarray(ids, np.uint32)
-        keep = ~np.isin(self.scene[k].ids, ids)
+        keep = ~np.isin(self.scene[k].ids, ids, kind="sort")
         self.scene[k] = Scene({key: (v[keep] if isinstance(v, np.ndarray) and key in timetravel.KEYS else v) for key, v in self.scene[k].items()})
         if k + 1 < self.n:
             self.tl_in[k + 1].push_events(self.coh[k], timetravel.removal_events(pipeline.past_ids(ids)))
@@ -90,7 +95,7 @@ class CpuBackend:
         self._create(k, rows)
 
     def has_future(self, k):
-        return np.isin(self.scene[k].ids, pipeline.past_ids(self.scene[k - 1].ids)).astype(np.uint8)
+        return np.isin(self.scene[k].ids, pipeline.past_ids(self.scene[k - 1].ids), kind="sort").astype(np.uint8)
 
     def cycle_step(self, k):
         tl = self.tl_in[k]

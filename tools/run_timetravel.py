@@ -43,6 +43,12 @@ def timed(label, f):
 
 for wk in be.w:
     wk.create_entities = timed("arrive.create_entities", wk.create_entities)
+    wk.replay = timed("replay.icx_replay", wk.replay)
+for tk in be.tl_in:
+    if tk is not None:
+        tk.fetch_entity = timed("replay.fetch_entity", tk.fetch_entity)
+        tk.pop_events = timed("replay.pop_events", tk.pop_events)
+        tk.push_events = timed("push_events", tk.push_events)
 for name in ("replay", "record_to_past", "fork_age", "step", "arrive", "cycle_step"):
     f = getattr(be, name)
 
