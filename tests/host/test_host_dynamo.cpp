@@ -93,6 +93,32 @@ int main(int argc, char** argv)
         std::vector<ProjectileComponent> back;
         projectiles.fetch(back);
         std::printf("projectile life %.17g condemned %zu\n", back[0].currLifetime, projectiles.condemned().size());
+        // ---- event records + entity lifecycle through the C++ mirror: a second cosmos (the "past") receives ENTITY_CREATED for the
+        // biped at chain-link 1 in the same tick's record, creates it from the record's components, follows it, then removes it ----
+        {
+            PhysicsDynamo past(16, 1);
+            Entity pid[3]; TransformComponent pT[3]; PhysicsComponent pP[3]; ColliderComponent pC[3]; uint8_t hp[3] = {1, 1, 1};
+            for (int e = 0; e < 3; e++) { pid[e] = ids[e]; increment_causal_chain_link(pid[e]); pT[e] = T[e]; pP[e] = P[e]; pC[e] = C[e]; }
+            check(icx_bodies_upload(past.world(), 3, pid, pT, pP, hp, pC, nullptr, nullptr), past.world(), "upload past");
+            const uint16_t c = (uint16_t)ticks;
+            Entity born = ids[3]; increment_causal_chain_link(born);
+            IcxTimelineEvent ev{}; ev.type = ICX_EVENT_ENTITY_CREATED; ev.entity = born; ev.source = ICX_NULL_ENTITY; ev.payload[0] = 0xC1;
+            timeline.push_past_event(c, &ev, 1);
+            timeline.push_past_timestream(dynamo, c);                                   // the tick's record: all four entities at link + 1
+            int created = 0, followed = 0, removed = 0;
+            for (const IcxTimelineEvent& r : timeline.pop_future_events(c)) {
+                if (r.type != ICX_EVENT_ENTITY_CREATED) continue;
+                TransformComponent t; PhysicsComponent ph; ColliderComponent cc; bool has_p = false, has_c = false;
+                if (!timeline.recorded_entity(c, r.entity, t, ph, has_p, cc, &has_c)) continue;
+                if (!has_c) cc = C[3];          // its collider has not changed since the previous record: the ring carries the row only in the tick an entity is new to it
+                const uint8_t one = has_p ? 1 : 0;
+                created += (int)TimelineApi::create_entities(past, 1, &r.entity, &t, &ph, &one, &cc);
+                followed += std::memcmp(&t, &T[3], sizeof(t)) == 0 && std::memcmp(&ph, &P[3], sizeof(ph)) == 0 ? 1 : 0;
+            }
+            const bool applied = timeline.pop_future_timestream(past, c);
+            removed = (int)TimelineApi::remove_entities(past, 1, &born);
+            std::printf("lifecycle created %d record_matches %d replayed %d removed %d\n", created, followed, applied ? 1 : 0, removed);
+        }
     } catch (const std::exception& e) {
         std::printf("error: %s\n", e.what());
         return 2;

@@ -52,7 +52,10 @@ def test_host_mirror_reproduces_case_study(exe):
         elif w[0] == "projectile":                            # 299.99 + 1/60 > maxLifetime 300: condemned by the first update
             assert float(w[2]) == 299.99 + 1.0 / 60 and int(w[4]) == 1
             seen += 1
-    assert seen == 5
+        elif w[0] == "lifecycle":                             # ENTITY_CREATED record -> recorded components -> create on the device -> replay -> remove
+            assert [int(w[2]), int(w[4]), int(w[6]), int(w[8])] == [1, 1, 1, 1], line
+            seen += 1
+    assert seen == 6
 
 
 NCCL_SRC = os.path.join(ROOT, "tests", "host", "test_host_nccl.cpp")
