@@ -170,53 +170,83 @@ def cpu_reference(scene_name, n_sample, ticks, threads, seed_offset=0):
     return sum(done) / max(max(busy), 1e-9), max(busy), kind
 
 
-def worldline_batch_bench(n_worldlines, per, ticks, rank, world_size, local_rank, barrier):
+def worldline_batch_bench(n_worldlines, per, ticks, rank, world_size, local_rank, barrier, parts=0):
     """BASELINE.json configs[3]: independent world-line candidates x `per` bodies, sharded round-robin over
     the ranks (strong scaling, no data-path collective).  Per tick and rank: replay (parallel mode:
     consume) + physics tick + record + divergence scan against the shared base history; then ONE
-    gather of {flag, incongruent, score} per world-line (NCCL over NVLink when world_size > 1)."""
+    gather of {flag, incongruent, score} per world-line (NCCL over NVLink when world_size > 1).
+    A rank's share runs as `parts` worlds ticked concurrently by as many host threads on their own streams, each with 1 / parts
+    of the device for its persistent resolve kernels (icx_device_share_set): a small share is latency-bound on its dependency
+    rounds, and independent candidates need not wait for each other's.  parts = 0: one world per 2 048 world-lines or less."""
+    import threading
+
     import torch
     import torch.distributed as dist
     from intercession_b200 import abi, scenes, shard, world as icxworld
     mine = shard.worldlines_of_rank(n_worldlines, rank, world_size)
+    if parts <= 0:
+        parts = max(1, min(4, 2048 // max(len(mine), 1)))
+    parts = max(1, min(parts, len(mine)))
     full_local = scenes.worldline_batch(len(mine), per, seed=20261106, perturb=False)
     for k, wl in enumerate(mine):                 # candidate w perturbs body (w mod per), seed + 1 + w  (same as scenes.worldline_batch)
         r = np.random.default_rng(20261106 + 1 + int(wl))
         full_local.P["velocity"][k * per + (int(wl) % per)] += r.uniform(-2, 2, 3).astype(np.float32)
     base = full_local.base
     hist_depth = ticks + 2
-    wb = icxworld.World(base.n, host_timeslice=abi.NULL_TIMESLICE, device=local_rank)
-    tl_base = icxworld.Timeline(hist_depth, per, device=local_rank)
-    wb.upload(base)
-    for t in range(ticks):                        # the base history every candidate is compared with (replicated, read-only)
-        wb.step(DT)
-        wb.record(tl_base, t + 1, keep_link=True)
-    wb.close()
-    wc = icxworld.World(full_local.n, worldline_stride=per, host_timeslice=abi.NULL_TIMESLICE, device=local_rank)
-    tl_new = icxworld.Timeline(2, full_local.n, device=local_rank)
-    wc.upload(full_local)
+    keys = ("ids", "T", "P", "hasP", "C", "tstate", "tcoh")
+    bounds = [len(mine) * q // parts for q in range(parts + 1)]          # contiguous runs of this rank's candidates
+    part = []
+    for q in range(parts):
+        lo, hi = bounds[q] * per, bounds[q + 1] * per
+        sc = scenes.Scene({k: (v[lo:hi].copy() if k in keys else v) for k, v in full_local.items()})
+        wb = icxworld.World(base.n, host_timeslice=abi.NULL_TIMESLICE, device=local_rank)
+        tl_base = icxworld.Timeline(hist_depth, per, device=local_rank)
+        wb.upload(base)
+        for t in range(ticks):                    # the base history every candidate is compared with (replicated, read-only; one copy per
+            wb.step(DT)                           # part because the scan's accumulators live in the ring object)
+            wb.record(tl_base, t + 1, keep_link=True)
+        wb.close()
+        wc = icxworld.World(sc.n, worldline_stride=per, host_timeslice=abi.NULL_TIMESLICE, device=local_rank)
+        wc.share_device(parts)
+        tl_new = icxworld.Timeline(2, sc.n, device=local_rank)
+        wc.upload(sc)
+        part.append({"wc": wc, "tl_new": tl_new, "tl_base": tl_base, "n_wl": bounds[q + 1] - bounds[q], "dev_ms": 0.0, "scan_ms": []})
     dev = torch.device("cuda", local_rank) if world_size > 1 else None
     z = np.zeros(len(mine))
     shard.gather_results(z, z, z, n_worldlines, rank, world_size, device=dev)      # warm the communicator up (untimed)
+
+    def run_part(pt):
+        wc, tl_new, tl_base = pt["wc"], pt["tl_new"], pt["tl_base"]
+        tl_base.profile(True)
+        for t in range(ticks):
+            wc.replay(tl_new, t, mode=abi.REPLAY_PARALLEL)
+            wc.step(DT)
+            pt["dev_ms"] += wc.last_step_ms()
+            wc.record(tl_new, t + 1, at_breakpoint=False, keep_link=True)
+            wc.divergence_scan_enqueue(tl_base, t + 1, pt["n_wl"])     # verdicts stay on the device: no host round trip per tick
+            if t % 16 == 15 or t == ticks - 1:
+                pt["scan_ms"].append(tl_base.kernel_ms(2))
+        pt["out"] = tl_base.scan_fetch(pt["n_wl"])                       # the last tick's counts / scores + "ever flagged"
+
     barrier()
     t0 = time.perf_counter()
-    dev_ms = 0.0
-    tl_base.profile(True)
-    scan_ms = []
-    for t in range(ticks):
-        wc.replay(tl_new, t, mode=abi.REPLAY_PARALLEL)
-        wc.step(DT)
-        dev_ms += wc.last_step_ms()
-        wc.record(tl_new, t + 1, at_breakpoint=False, keep_link=True)
-        wc.divergence_scan_enqueue(tl_base, t + 1, len(mine))          # verdicts stay on the device: no host round trip per tick
-        if t % 16 == 15 or t == ticks - 1:
-            scan_ms.append(tl_base.kernel_ms(2))
-    flags, any_flag, cnt, score = tl_base.scan_fetch(len(mine))          # the last tick's counts / scores + "ever flagged"
+    if parts == 1:
+        run_part(part[0])
+    else:
+        ths = [threading.Thread(target=run_part, args=(pt,)) for pt in part]
+        [t.start() for t in ths]
+        [t.join() for t in ths]
+    any_flag = np.concatenate([pt["out"][1] for pt in part]); cnt = np.concatenate([pt["out"][2] for pt in part]); score = np.concatenate([pt["out"][3] for pt in part])
     gflags, gcnt, gscore = shard.gather_results(any_flag, cnt, score, n_worldlines, rank, world_size, device=dev)
     barrier()
     sec = time.perf_counter() - t0
-    st = wc.stats()
-    wc.close(); tl_new.close(); tl_base.close()
+    st = part[0]["wc"].stats()
+    n_dirty, n_contacts = sum(pt["wc"].stats().n_dirty for pt in part), sum(pt["wc"].stats().n_contacts for pt in part)
+    dev_ms = max(pt["dev_ms"] for pt in part)
+    scan_ms = [m for pt in part for m in pt["scan_ms"]]
+    scan_bodies = part[0]["n_wl"] * per
+    for pt in part:
+        pt["wc"].close(); pt["tl_new"].close(); pt["tl_base"].close()
     sec_t = torch.tensor([sec], dtype=torch.float64, device="cuda")
     if world_size > 1:
         dist.all_reduce(sec_t, op=dist.ReduceOp.MAX)
@@ -225,16 +255,17 @@ def worldline_batch_bench(n_worldlines, per, ticks, rank, world_size, local_rank
     return {"workload": f"config4: {n_worldlines} world-line candidates x {per} bodies, {ticks} ticks of replay + tick + record + divergence scan, "
                         f"sharded round-robin over {world_size} GPU(s), base history replicated",
             "scaling": "strong", "n_gpus": world_size, "ticks": ticks, "seconds": round(sec, 4),
+            "worlds_per_gpu": parts, "worldlines_per_world": part[0]["n_wl"],
             "worldline_ticks_per_s": n_worldlines * ticks / sec, "collider_steps_per_s": bodies * ticks / sec,
-            "physics_tick_ms_rank0": round(dev_ms / ticks, 4), "dirty_bodies_rank0": st.n_dirty, "contacts_rank0": st.n_contacts,
+            "physics_tick_ms_rank0": round(dev_ms / ticks, 4), "dirty_bodies_rank0": n_dirty, "contacts_rank0": n_contacts,
             "divergent_worldlines": int(gflags.sum()), "most_congruent": shard.most_congruent(gflags, gscore),
             "gather": {"collective": "all_gather_into_tensor (NCCL)" if world_size > 1 else "none (1 rank)",
                        "bytes_per_rank": 24 * ((n_worldlines + world_size - 1) // world_size)},
             "algorithmic_bytes_per_body_tick": {"record": 296, "scan": 26},
-            # k_divergence_scan over this rank's candidates: 16 B of live position per body from HBM (the tick and the record
+            # k_divergence_scan over one world's candidates: 16 B of live position per body from HBM (the tick and the record
             # ran in between, > L2); the 16 KB base record is shared by every world-line and stays in L2
-            "scan_kernel_rank0": {"us": round(float(np.mean(scan_ms)) * 1e3, 2), "bodies": int(full_local.n),
-                                  "alg_GBps": round(16.0 * full_local.n / (float(np.mean(scan_ms)) * 1e-3) / 1e9, 1),
+            "scan_kernel_rank0": {"us": round(float(np.mean(scan_ms)) * 1e3, 2), "bodies": int(scan_bodies),
+                                  "alg_GBps": round(16.0 * scan_bodies / (float(np.mean(scan_ms)) * 1e-3) / 1e9, 1),
                                   "timing": "CUDA events per launch (icx_timeline_kernel_ms), mean over the ticks"}}
 
 
@@ -609,6 +640,7 @@ def main():
     ap.add_argument("--no-timeline", action="store_true", help="skip the record / replay / scan kernel timings")
     ap.add_argument("--worldlines", type=int, default=4096, help="config-4 world-line candidates (0 = skip that section)")
     ap.add_argument("--worldline-bodies", type=int, default=1024)
+    ap.add_argument("--worldline-parts", type=int, default=0, help="worlds per GPU the rank's candidates are ticked as, concurrently (0 = one per 2 048 world-lines or less, at most 4)")
     ap.add_argument("--worldline-ticks", type=int, default=225, help="config 4 as written: 225 ticks against a 225-deep base history")
     ap.add_argument("--pipeline-bodies", type=int, default=100000, help="config-5 bodies per timeslice (0 = skip that section)")
     ap.add_argument("--pipeline-ticks", type=int, default=12)
@@ -765,7 +797,7 @@ def main():
 
     wlb = None
     if a.worldlines > 0:
-        wlb = worldline_batch_bench(a.worldlines, a.worldline_bodies, a.worldline_ticks, rank, world_size, local_rank, barrier)
+        wlb = worldline_batch_bench(a.worldlines, a.worldline_bodies, a.worldline_ticks, rank, world_size, local_rank, barrier, a.worldline_parts)
 
     tsp = None
     if a.pipeline_bodies > 0:

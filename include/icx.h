@@ -316,6 +316,13 @@ ICX_API int icx_mesh_contacts_fetch(IcxWorld* w, IcxMeshContact* out, size_t cap
 /* device time of the last mesh pass in microseconds (0 if none ran) */
 ICX_API int icx_mesh_kernel_us(IcxWorld* w, float* us);
 
+/* Several worlds on ONE device, ticked concurrently from different host threads (each world has its own stream): the two
+ * persistent cooperative kernels of the ordered resolve normally fill the device, so a second world's could only start when the
+ * first one's have finished.  With parts = k this world launches them over 1 / k of the co-resident blocks, and k such worlds
+ * overlap -- which pays when a world is small enough for its dependency rounds to be latency-bound (config 4 sharded over many
+ * GPUs: DESIGN.md 9).  Results do not depend on it.  parts = 1 restores the default. */
+ICX_API int icx_device_share_set(IcxWorld* w, uint32_t parts);
+
 /* Page-locked host memory for component storage that is handed to icx_bodies_upload / _update / _download every tick (the
  * copies then run at full PCIe rate and asynchronously; with pageable memory the driver stages them).  For hosts that do
  * not link the CUDA runtime themselves (icx_host::ComponentPools, host/component_pools.hpp, keeps its rows in it).

@@ -216,6 +216,7 @@ SIGNATURES = {
     "icx_mesh_upload": (C.c_int, [_vp, _vp, _u32, _vp, _u32, _vp]),
     "icx_mesh_contacts_fetch": (C.c_int, [_vp, _vp, _sz, _psz]),
     "icx_mesh_kernel_us": (C.c_int, [_vp, C.POINTER(C.c_float)]),
+    "icx_device_share_set": (C.c_int, [_vp, _u32]),
     "icx_host_alloc": (C.c_void_p, [_sz]),
     "icx_host_free": (None, [_vp]),
     "icx_entities_create": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.POINTER(_u32)]),

@@ -322,6 +322,16 @@ void icx_world_destroy(IcxWorld* w)
 
 const char* icx_last_error(const IcxWorld* w) { return w ? w->error.c_str() : "null world"; }
 
+int icx_device_share_set(IcxWorld* w, uint32_t parts)
+{
+    if (!w || parts == 0) return ICX_E_INVALID;
+    const int full_r = resolve_grid_blocks(w->device, 1), full_p = resolve_grid_blocks(w->device, 0);
+    if (full_r <= 0 || full_p <= 0) return fail(w, ICX_E_CUDA, "k_resolve cannot be made resident");
+    w->resolve_blocks = std::max(1, full_r / (int)parts);
+    w->prepare_blocks = std::max(1, full_p / (int)parts);
+    return ICX_OK;
+}
+
 void* icx_host_alloc(size_t bytes)
 {
     void* p = nullptr;

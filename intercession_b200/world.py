@@ -97,6 +97,10 @@ class World:
     def collision_engage(self):
         self._ck(self.lib.icx_collision_engage(self.handle))
 
+    def share_device(self, parts):
+        """This world's persistent kernels use 1 / parts of the device, so that `parts` worlds tick concurrently (icx_device_share_set)."""
+        self._ck(self.lib.icx_device_share_set(self.handle, parts))
+
     def sync(self):
         self._ck(self.lib.icx_sync(self.handle))
 
