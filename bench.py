@@ -177,15 +177,17 @@ def worldline_batch_bench(n_worldlines, per, ticks, rank, world_size, local_rank
     gather of {flag, incongruent, score} per world-line (NCCL over NVLink when world_size > 1).
     A rank's share runs as `parts` worlds ticked concurrently by as many host threads on their own streams, each with 1 / parts
     of the device for its persistent resolve kernels (icx_device_share_set): a small share is latency-bound on its dependency
-    rounds, and independent candidates need not wait for each other's.  parts = 0: one world per 2 048 world-lines or less."""
+    rounds, and independent candidates need not wait for each other's.  parts = 0: one world per 2 048 world-lines or less, at most 4,
+    and no more than the host has spare cores for (measured on one B200: 512 world-lines 0.151 s as one world, 0.140 s as four;
+    with 8 ranks on 16 cores the four threads per rank cost what they gain)."""
     import threading
 
     import torch
     import torch.distributed as dist
     from intercession_b200 import abi, scenes, shard, world as icxworld
     mine = shard.worldlines_of_rank(n_worldlines, rank, world_size)
-    if parts <= 0:
-        parts = max(1, min(4, 2048 // max(len(mine), 1)))
+    if parts <= 0:                                # (a host thread per world spins in its stream sync: no more worlds than spare cores)
+        parts = max(1, min(4, 2048 // max(len(mine), 1), (os.cpu_count() or 1) // (2 * world_size)))
     parts = max(1, min(parts, len(mine)))
     full_local = scenes.worldline_batch(len(mine), per, seed=20261106, perturb=False)
     for k, wl in enumerate(mine):                 # candidate w perturbs body (w mod per), seed + 1 + w  (same as scenes.worldline_batch)
