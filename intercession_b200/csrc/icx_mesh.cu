@@ -33,7 +33,7 @@ int icx_mesh_pass(IcxWorld* w)
     CKM(w, cudaEventRecord(w->mesh_ev1, st));
     CKM(w, cudaGetLastError());
     w->launches += 2;
-    w->mesh_ran = true;     // the contact list is sized for 4 contacts per entity; an overflow is reported by the fetch
+    w->mesh_ran = true;     // the contact list holds one contact per entity of capacity to start with; an overflow is reported by the fetch, which enlarges it
     return ICX_OK;
 }
 
@@ -101,7 +101,7 @@ int icx_mesh_upload(IcxWorld* w, const float* vertices, uint32_t n_vertices, con
         CKM(w, cudaMemcpy(w->mesh_cell_start.ptr, start.data(), start.size() * 4, cudaMemcpyHostToDevice));
         if (!list.empty()) CKM(w, cudaMemcpy(w->mesh_cell_tri.ptr, list.data(), list.size() * 4, cudaMemcpyHostToDevice));
     }
-    M.max_contacts = std::max<uint32_t>(4096u, w->cap_entities * 4u);
+    M.max_contacts = std::max<uint32_t>(4096u, w->cap_entities);           // grows when a pass overflows it (icx_mesh_contacts_fetch)
     CKM(w, w->mesh_contacts.ensure((size_t)M.max_contacts * sizeof(IcxMeshContact)));
     CKM(w, w->mesh_counter.ensure(16));
     CKM(w, cudaMemset(w->mesh_counter.ptr, 0, 16));
@@ -126,7 +126,14 @@ int icx_mesh_contacts_fetch(IcxWorld* w, IcxMeshContact* out, size_t cap, size_t
     uint32_t cnt[2] = {0, 0};
     CKM(w, cudaMemcpyAsync(cnt, w->mesh_counter.ptr, 8, cudaMemcpyDeviceToHost, w->stream));
     CKM(w, cudaStreamSynchronize(w->stream));
-    if (cnt[1] || cnt[0] > w->mesh.max_contacts) return mfail(w, ICX_E_CAPACITY, "mesh contacts exceeded 4 per entity of capacity; the list is incomplete");
+    if (cnt[1] || cnt[0] > w->mesh.max_contacts) {
+        // the pass itself is complete (states are right), its contact list is not: make room for the next pass and say so
+        const uint32_t want = std::max(cnt[0] + cnt[0] / 2u, w->mesh.max_contacts * 2u);
+        w->mesh_contacts.release();
+        CKM(w, w->mesh_contacts.ensure((size_t)want * sizeof(IcxMeshContact)));
+        w->mesh.contacts = (IcxMeshContact*)w->mesh_contacts.ptr; w->mesh.max_contacts = want;
+        return mfail(w, ICX_E_CAPACITY, "mesh contact list overflowed in this pass (the states are complete); it has been enlarged for the next one");
+    }
     if (n_out) *n_out = cnt[0];
     if (!out || !cnt[0]) return ICX_OK;
     std::vector<IcxMeshContact> all(cnt[0]);

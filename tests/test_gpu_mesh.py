@@ -91,6 +91,33 @@ def test_mesh_body_over_many_triangles(built):
     assert (hits["row"] == 5).sum() >= 3                                            # pushed clear by the first few; ~1 200 candidates were walked
 
 
+def test_mesh_contact_list_grows_after_an_overflow(built):
+    """More contacts in one pass than the list holds: the states are complete, the fetch says the list was not and enlarges it."""
+    s, _, _ = mesh_scene(3000, 4, rotate=False)
+    lo, hi = s.T["origin"].min(0), s.T["origin"].max(0)
+    span = float((hi - lo)[[0, 2]].max()) + 4
+    vs, ts_, nv = [], [], 0
+    for y in np.arange(float(lo[1]), float(hi[1]) + 0.5, 1.0):                      # sheets of small triangles through the whole arena:
+        v, tr = scenes.height_mesh(span, 64, y=float(y), bump=0.0,                  # every body sits in one
+                                   centre=(float(0.5 * (lo[0] + hi[0])), float(0.5 * (lo[2] + hi[2]))))
+        vs.append(v); ts_.append(tr + nv); nv += len(v)
+    verts, tris = np.concatenate(vs), np.concatenate(ts_).astype(np.uint32)
+    exp_pairs = refs.procedures_tick(refs.oracle(), "icxo", s, euler=False)
+    exp, ehits = refs.oracle_mesh_pass(Scene({k: v for k, v in exp_pairs.items() if k not in ("hits", "ints", "seconds")}), verts, tris)
+    assert len(ehits) > 4096
+    with world.World(s.n) as w:
+        w.upload(s); w.upload_mesh(verts, tris)
+        w.collision_engage()
+        assert_state_equal(w.download(s), exp)                                      # the pass itself was complete
+        with pytest.raises(world.IcxError) as ei:
+            w.mesh_contacts()
+        assert ei.value.code == abi.E_CAPACITY
+        w.upload(s)
+        w.collision_engage()
+        got = w.mesh_contacts()
+        assert len(got) == len(ehits) and not fields_diff(got, ehits)
+
+
 def test_mesh_free_run_against_oracle(built):
     """Whole ticks with the mesh, device and oracle side by side from the drop: locked orientations keep the tick bit-exact
     (no sin / cos), so the two stay identical while bodies land on the ground mesh and roll off the torus."""
