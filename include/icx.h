@@ -338,7 +338,7 @@ ICX_API void icx_host_free(void* p);
  * that everything derived from the row order is what icx_bodies_upload of the merged arrays would have built.  An id that
  * exists already is left alone (:431-437), removing an id that is not there does nothing.  The coherency is kept.
  * Row indices of entities behind an inserted / removed row change: host-side row tables must be refreshed
- * (icx_entity_ids_fetch).  Synchronous.
+ * (icx_entity_ids_fetch), and projectile rows (icx_projectiles_upload) are detached like after an upload.  Synchronous.
  */
 ICX_API int icx_entities_create(IcxWorld* w, uint32_t count, const IcxEntity* entity, const IcxTransform* T, const IcxPhysics* P,
                                 const uint8_t* has_physics, const IcxColliderComponent* C, const uint8_t* tstate, const uint16_t* tcoh,
