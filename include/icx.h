@@ -292,11 +292,12 @@ ICX_API int icx_world_clone(IcxWorld* src, IcxWorld* dst, const uint8_t* has_fut
  * (oracle icxo_mesh_pass: self-oracle, parity unpinned).
  * A world may hold one mesh: world-space triangles, immutable, infinite mass.  After the pair loop of every collision pass
  * (icx_collision_engage / icx_step) each entity that has a PhysicsComponent of finite mass (mass != 0) meets the mesh: entities in row order, their
- * active box / sphere colliders of collision type rigid in slot order, and for each collider the triangles whose bounds
+ * active box / sphere colliders of collision type rigid and ray colliders of collision type spring in slot order, and for each collider the triangles whose bounds
  * overlap the collider's bounds (taken when the collider's turn starts) in ascending triangle index.  A hit (sphere -
  * triangle: closest point; box - triangle: 13-axis separating-axis test) is answered with the reference's
  * rigid_rigid_response (collision_procedures.cpp:636-874) against an immovable body of the mesh's material, so later
- * triangles see the moved body.  Entities do not interact in this pass.  Contacts: icx_mesh_contacts_fetch, in that order.
+ * triangles see the moved body.  A ray (Moeller-Trumbore) only counts in front of what it has met so far this tick
+ * (Collider::minParametricValue, as ray_box_intersect keeps it) and is answered with spring_rigid_response (:876-1053).  Entities do not interact in this pass.  Contacts: icx_mesh_contacts_fetch, in that order.
  */
 typedef struct IcxMeshMaterial { float staticFriction, dynamicFriction, restitution; } IcxMeshMaterial;
 typedef struct IcxMeshContact {

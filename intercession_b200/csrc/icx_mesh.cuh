@@ -85,4 +85,35 @@ ICX_DI bool box_triangle_hit(const M4& M, const Tri& t, Hit& h)
     return true;
 }
 
+// Ray of the composite transform M (origin M * 0, end M * (0, 0, 1), collision_procedures.h:73-86) against one triangle:
+// Moeller-Trumbore.  A hit counts only in front of what the ray has already met (min_param, Collider::minParametricValue:
+// ray_box_intersect keeps the nearest hit the same way, collision_procedures.cpp:566-578).  normal = the triangle's normal on the
+// ray origin's side, depth = how far the ray's end lies behind the triangle's plane, point = where the ray pierces it.
+ICX_DI bool ray_triangle_hit(const M4& M, const Tri& t, float min_param, Hit& h, float& param)
+{
+    const V3 o = xform(M, 0.0f, 0.0f, 0.0f), end = xform(M, 0.0f, 0.0f, 1.0f);
+    const V3 d = end - o;
+    const V3 e1 = t.b - t.a, e2 = t.c - t.a;
+    const V3 pv = cross(d, e2);
+    const float det = dot(e1, pv);
+    if (!(fabsf(det) > 1.0e-12f)) return false;                                     // parallel to the plane, or a degenerate triangle
+    const float inv = 1.0f / det;
+    const V3 tv = o - t.a;
+    const float u = dot(tv, pv) * inv;
+    if (!(u >= 0.0f && u <= 1.0f)) return false;
+    const V3 qv = cross(tv, e1);
+    const float v = dot(d, qv) * inv;
+    if (!(v >= 0.0f && u + v <= 1.0f)) return false;
+    const float s = dot(e2, qv) * inv;
+    if (!(s >= 0.0f && s <= 1.0f)) return false;
+    if (s >= min_param) return false;
+    V3 n = normalize(cross(e1, e2));
+    if (dot(n, d) > 0.0f) n = -n;
+    param = s;
+    h.point = o + s * d;
+    h.normal = n;
+    h.depth = dot(n, h.point - end);
+    return true;
+}
+
 } // namespace icx

@@ -1457,32 +1457,39 @@ __global__ void __launch_bounds__(128) k_mesh_pass(const __grid_constant__ Devic
         const float4 prm1 = W.prm1[e];
         const uint32_t fp = W.first_packet[e], npk = fp >> 30, p0 = fp & 0x3FFFFFFFu;
         // the entity as the pair loop left it; the second collider sees what the first one's contacts did
-        float4 pos = W.in.pos[e], vel = W.in.vel[e], angvel = W.in.angvel[e];
+        float4 pos = W.in.pos[e], vel = W.in.vel[e], angvel = W.in.angvel[e], acc = W.in.acc[e], angacc = W.in.angacc[e];
         bool touched = false;
         for (uint32_t k = 0; k < npk; k++) {
             const uint32_t p = p0 + k;
             const uint32_t bits = __float_as_uint(W.pk_lpos[p].w);
             const int type = (int)(bits & PF_TYPE_MASK);
-            if (type != ICX_COLLIDER_BOX && type != ICX_COLLIDER_SPHERE) continue;
-            if (((bits >> PF_CTYPE_SHIFT) & 3u) != ICX_COLLISION_RIGID) continue;
+            const uint32_t ctype = (bits >> PF_CTYPE_SHIFT) & 3u;
+            const bool is_ray = type == ICX_COLLIDER_RAY;                            // a ray collider meets the mesh as a spring (the biped's legs), boxes and spheres as rigid bodies
+            if (is_ray ? ctype != ICX_COLLISION_SPRING : ((type != ICX_COLLIDER_BOX && type != ICX_COLLIDER_SPHERE) || ctype != ICX_COLLISION_RIGID)) continue;
             SideData sd;
-            sd.pos = pos; sd.vel = vel; sd.angvel = angvel; sd.acc = W.in.acc[e]; sd.angacc = W.in.angacc[e];
+            sd.pos = pos; sd.vel = vel; sd.angvel = angvel; sd.acc = acc; sd.angacc = angacc;
             sd.prm0 = W.prm0[e]; sd.prm1 = prm1; sd.pos0 = sd.pos; sd.slot = ICX_NONE; sd.ts = 0u; sd.id = 0u;
-            sd.mat0 = W.pk_mat0[p]; sd.lscale = W.pk_lscale[p]; sd.damping = W.pk_damping[p]; sd.minparam = 1.0f;
+            sd.mat0 = W.pk_mat0[p]; sd.lscale = W.pk_lscale[p]; sd.damping = W.pk_damping[p]; sd.minparam = W.pk_minparam[p];
             const float4* d = W.pk_d + (size_t)p * 6;
 #pragma unroll
             for (int q = 0; q < 6; q++) sd.d[q] = d[q];
             V3 base; Shape sh = shape_of(sd, type, base);
             V3 half;                                                                // bounds of the collider when its turn starts
-            if (type == ICX_COLLIDER_SPHERE) { const float r = length(xform(sh.M, ICX_UNIT_RADIUS, 0.0f, 0.0f) - xform(sh.M, 0.0f, 0.0f, 0.0f)); half = v3(r, r, r); }
+            V3 lo, hi;
+            if (is_ray) {
+                const V3 o = xform(sh.M, 0.0f, 0.0f, 0.0f), en = xform(sh.M, 0.0f, 0.0f, 1.0f);
+                lo = v3(smin(o.x, en.x), smin(o.y, en.y), smin(o.z, en.z)); hi = v3(smax(o.x, en.x), smax(o.y, en.y), smax(o.z, en.z));
+                half = v3(0.0f, 0.0f, 0.0f);
+            } else if (type == ICX_COLLIDER_SPHERE) { const float r = length(xform(sh.M, ICX_UNIT_RADIUS, 0.0f, 0.0f) - xform(sh.M, 0.0f, 0.0f, 0.0f)); half = v3(r, r, r); }
             else half = v3(((fabsf(sh.M.c[0].x) + fabsf(sh.M.c[1].x)) + fabsf(sh.M.c[2].x)) * ICX_UNIT_RADIUS,
                            ((fabsf(sh.M.c[0].y) + fabsf(sh.M.c[1].y)) + fabsf(sh.M.c[2].y)) * ICX_UNIT_RADIUS,
                            ((fabsf(sh.M.c[0].z) + fabsf(sh.M.c[1].z)) + fabsf(sh.M.c[2].z)) * ICX_UNIT_RADIUS);
-            const V3 lo = sh.M.t - half, hi = sh.M.t + half;
+            if (!is_ray) { lo = sh.M.t - half; hi = sh.M.t + half; }
             int c0[3], c1[3];
             if (!mesh_cells(M, lo, hi, c0, c1)) continue;
             Side A = side_of(sd, sh, base, bits);
             const Side B0 = mesh_side(M);
+            float min_param = sd.minparam;
             // Candidates are staged ICX_MESH_MAXC at a time over windows of the triangle index range (normally ONE window: the
             // whole range); a window that holds more is halved.  The bounds are fixed for the collider's turn, so the windows
             // partition one ascending sequence.
@@ -1534,21 +1541,24 @@ __global__ void __launch_bounds__(128) k_mesh_pass(const __grid_constant__ Devic
                 while (at < n_c) {
                     const uint32_t i = at + lane;
                     Hit h; h.point = v3(0.0f, 0.0f, 0.0f); h.normal = v3(0.0f, 0.0f, 0.0f); h.depth = 0.0f;
-                    bool hit = false; uint32_t t = ICX_NONE;
+                    bool hit = false; uint32_t t = ICX_NONE; float h_param = 0.0f;
                     if (i < n_c) {
                         t = raw[i];
                         sh.M.t = A.base + (A.origin + v3(0.0f, 0.0f, 0.0f));
                         const Tri tr = mesh_tri(M, t);
-                        hit = type == ICX_COLLIDER_SPHERE ? sphere_triangle_hit(sh.M, tr, h) : box_triangle_hit(sh.M, tr, h);
+                        float prm = 0.0f;
+                        hit = is_ray ? ray_triangle_hit(sh.M, tr, min_param, h, prm) : (type == ICX_COLLIDER_SPHERE ? sphere_triangle_hit(sh.M, tr, h) : box_triangle_hit(sh.M, tr, h));
+                        if (is_ray && hit) h_param = prm;
                     }
                     const uint32_t m = __ballot_sync(FULL, hit);
                     if (!m) { at += 32u; continue; }
                     const int f = __ffs(m) - 1;                                     // the next contact of the sequential order
                     h.point.x = __shfl_sync(FULL, h.point.x, f); h.point.y = __shfl_sync(FULL, h.point.y, f); h.point.z = __shfl_sync(FULL, h.point.z, f);
                     h.normal.x = __shfl_sync(FULL, h.normal.x, f); h.normal.y = __shfl_sync(FULL, h.normal.y, f); h.normal.z = __shfl_sync(FULL, h.normal.z, f);
-                    h.depth = __shfl_sync(FULL, h.depth, f); t = __shfl_sync(FULL, t, f);
+                    h.depth = __shfl_sync(FULL, h.depth, f); t = __shfl_sync(FULL, t, f); h_param = __shfl_sync(FULL, h_param, f);
                     Side B = B0;
-                    rigid_rigid_response(A, B, h);                                  // every lane: same inputs, same result
+                    if (is_ray) { min_param = h_param; spring_rigid_response(A, B, h); }   // the nearest hit so far; the spring pushes along the normal
+                    else rigid_rigid_response(A, B, h);                             // every lane: same inputs, same result
                     touched = true;
                     if (lane == 0u) mesh_emit(W, M, e, bits, t, h);
                     at += (uint32_t)f + 1u;
@@ -1560,9 +1570,12 @@ __global__ void __launch_bounds__(128) k_mesh_pass(const __grid_constant__ Devic
             pos = make_float4(A.origin.x, A.origin.y, A.origin.z, 0.0f);
             vel = make_float4(A.vel.x, A.vel.y, A.vel.z, 0.0f);
             angvel = make_float4(A.angvel.x, A.angvel.y, A.angvel.z, 0.0f);
+            acc = make_float4(A.acc.x, A.acc.y, A.acc.z, 0.0f);
+            angacc = make_float4(A.angacc.x, A.angacc.y, A.angacc.z, 0.0f);
+            if (is_ray && lane == 0u && min_param != sd.minparam) W.pk_minparam[p] = min_param;
             __syncwarp();
         }
-        if (touched && lane == 0u) { W.in.pos[e] = pos; W.in.vel[e] = vel; W.in.angvel[e] = angvel; }
+        if (touched && lane == 0u) { W.in.pos[e] = pos; W.in.vel[e] = vel; W.in.angvel[e] = angvel; W.in.acc[e] = acc; W.in.angacc[e] = angacc; }
     }
 }
 

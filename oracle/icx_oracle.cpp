@@ -1108,6 +1108,30 @@ bool mesh_box_hit(const M4& m, const MeshTri& t, Hit& h) {
     h.normal = bestN; h.depth = best; h.point = mesh_closest_point(centre, t);
     return true;
 }
+// ray (origin m * 0, end m * (0, 0, 1)) against one triangle, Moeller-Trumbore; only in front of what the ray has met so far
+bool mesh_ray_hit(const M4& m, const MeshTri& t, float minParam, Hit& h, float& param) {
+    const V3 o = xform(m, 0, 0, 0), end = xform(m, 0, 0, 1);
+    const V3 d = end - o;
+    const V3 e1 = t.b - t.a, e2 = t.c - t.a;
+    const V3 pv = cross(d, e2);
+    const float det = dot(e1, pv);
+    if (!(std::fabs(det) > 1.0e-12f)) return false;
+    const float inv = 1.0f / det;
+    const V3 tv = o - t.a;
+    const float u = dot(tv, pv) * inv;
+    if (!(u >= 0.0f && u <= 1.0f)) return false;
+    const V3 qv = cross(tv, e1);
+    const float v = dot(d, qv) * inv;
+    if (!(v >= 0.0f && u + v <= 1.0f)) return false;
+    const float s = dot(e2, qv) * inv;
+    if (!(s >= 0.0f && s <= 1.0f)) return false;
+    if (s >= minParam) return false;
+    V3 n = normalize(cross(e1, e2));
+    if (dot(n, d) > 0.0f) n = -n;
+    param = s;
+    h.point = o + s * d; h.normal = n; h.depth = dot(n, h.point - end);
+    return true;
+}
 } // namespace
 
 extern "C" int icxo_mesh_pass(uint32_t n, const IcxEntity* id, IcxTransform* T, IcxPhysics* P, const uint8_t* has_physics, IcxColliderComponent* C,
@@ -1134,15 +1158,21 @@ extern "C" int icxo_mesh_pass(uint32_t n, const IcxEntity* id, IcxTransform* T, 
         for (uint32_t s = 0; s < ICX_COLLIDERS_PER_ENTITY; s++) {
             IcxCollider& c = C[e].colliders[s];
             if (!c.isActive) continue;
-            if (c.colliderType != ICX_COLLIDER_BOX && c.colliderType != ICX_COLLIDER_SPHERE) continue;
-            if (c.collisionType != ICX_COLLISION_RIGID) continue;
+            const bool isRay = c.colliderType == ICX_COLLIDER_RAY;          // a ray meets the mesh as a spring (the biped's legs), boxes and spheres as rigid bodies
+            if (isRay ? c.collisionType != ICX_COLLISION_SPRING
+                      : ((c.colliderType != ICX_COLLIDER_BOX && c.colliderType != ICX_COLLIDER_SPHERE) || c.collisionType != ICX_COLLISION_RIGID)) continue;
             const M4 m0 = compose_transform(c, T[e]);
-            V3 half;
-            if (c.colliderType == ICX_COLLIDER_SPHERE) { const float r = length(xform(m0, UNIT_RADIUS, 0, 0) - xform(m0, 0, 0, 0)); half = v3(r, r, r); }
+            V3 half = v3(0, 0, 0);
+            if (isRay) {}
+            else if (c.colliderType == ICX_COLLIDER_SPHERE) { const float r = length(xform(m0, UNIT_RADIUS, 0, 0) - xform(m0, 0, 0, 0)); half = v3(r, r, r); }
             else half = v3(((std::fabs(m0.c[0].x) + std::fabs(m0.c[1].x)) + std::fabs(m0.c[2].x)) * UNIT_RADIUS,
                            ((std::fabs(m0.c[0].y) + std::fabs(m0.c[1].y)) + std::fabs(m0.c[2].y)) * UNIT_RADIUS,
                            ((std::fabs(m0.c[0].z) + std::fabs(m0.c[1].z)) + std::fabs(m0.c[2].z)) * UNIT_RADIUS);
-            const V3 lo = m0.t - half, hi = m0.t + half;                            // bounds when the collider's turn starts
+            V3 lo = m0.t - half, hi = m0.t + half;                                  // bounds when the collider's turn starts
+            if (isRay) {
+                const V3 o = xform(m0, 0, 0, 0), en = xform(m0, 0, 0, 1);
+                lo = v3(smin(o.x, en.x), smin(o.y, en.y), smin(o.z, en.z)); hi = v3(smax(o.x, en.x), smax(o.y, en.y), smax(o.z, en.z));
+            }
             if (std::isnan(lo.x) || std::isnan(hi.x)) continue;
             for (uint32_t t = 0; t < n_triangles; t++) {                            // ascending triangle index
                 const MeshTri& tr = tris[t];
@@ -1151,10 +1181,13 @@ extern "C" int icxo_mesh_pass(uint32_t n, const IcxEntity* id, IcxTransform* T, 
                 if (!(tlo.x <= hi.x && lo.x <= thi.x && tlo.y <= hi.y && lo.y <= thi.y && tlo.z <= hi.z && lo.z <= thi.z)) continue;
                 const M4 m = compose_transform(c, T[e]);                            // where the previous triangle left the body
                 Hit h; h.point = v3(0, 0, 0); h.normal = v3(0, 0, 0); h.depth = 0;
-                const bool hit = c.colliderType == ICX_COLLIDER_SPHERE ? mesh_sphere_hit(m, tr, h) : mesh_box_hit(m, tr, h);
+                float param = 0;
+                const bool hit = isRay ? mesh_ray_hit(m, tr, c.minParametricValue, h, param)
+                                       : (c.colliderType == ICX_COLLIDER_SPHERE ? mesh_sphere_hit(m, tr, h) : mesh_box_hit(m, tr, h));
                 if (!hit) continue;
                 IcxTransform tB = tM; IcxPhysics pB = pM; IcxCollider cB = cM;
-                rigid_rigid_response(T[e], c, P[e], tB, cB, pB, h);
+                if (isRay) { c.minParametricValue = param; spring_rigid_response(T[e], c, P[e], tB, cB, pB, h); }
+                else rigid_rigid_response(T[e], c, P[e], tB, cB, pB, h);
                 if (out && k < cap) {
                     IcxMeshContact& mc = out[k];
                     mc.entity = id ? id[e] : e; mc.row = e; mc.slot = s; mc.triangle = t;

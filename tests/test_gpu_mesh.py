@@ -91,6 +91,28 @@ def test_mesh_body_over_many_triangles(built):
     assert (hits["row"] == 5).sum() >= 3                                            # pushed clear by the first few; ~1 200 candidates were walked
 
 
+def test_mesh_pass_ray_spring_legs(built):
+    """Bipeds over mesh ground: a second collider slot with ray-spring legs (client_focal_entity.h:30-91) on 400 of the bodies.
+    The ray keeps its nearest hit (minParametricValue carries over from the pair loop) and answers it as a spring."""
+    s, verts, tris = mesh_scene(1500, 6)
+    h = np.float32(np.sqrt(0.5))
+    legs = np.arange(50, 450)
+    c = s.C["colliders"]
+    c["isActive"][legs, 1] = 1
+    c["colliderType"][legs, 1] = abi.COLLIDER_RAY
+    c["collisionType"][legs, 1] = abi.COLLISION_SPRING
+    c["localTransform"]["orientation"][legs, 1] = (h, h, 0, 0)
+    c["localTransform"]["scale"][legs, 1] = (1, 1, 2.0)
+    c["stiffness"][legs, 1], c["damping"][legs, 1], c["restLength"][legs, 1] = 2500, 400, 0.3
+    c["staticFriction"][legs, 1], c["dynamicFriction"][legs, 1] = 0, 0
+    c["inheritOrientation"][legs, 1], c["influenceOrientation"][legs, 1] = 0, 0
+    c["minParametricValue"][legs, 1] = 1.0
+    exp, hits = lockstep(s, verts, tris)
+    ray = hits[hits["slot"] == 1]
+    assert len(ray) > 10 and (ray["depth"] > 0).all()
+    assert (exp.C["colliders"]["minParametricValue"][legs, 1] < 1.0).sum() >= len(np.unique(ray["row"]))
+
+
 def test_mesh_contact_list_grows_after_an_overflow(built):
     """More contacts in one pass than the list holds: the states are complete, the fetch says the list was not and enlarges it."""
     s, _, _ = mesh_scene(3000, 4, rotate=False)

@@ -69,3 +69,31 @@ def test_triangles_are_met_in_ascending_order_and_later_ones_see_the_moved_body(
     assert hits["triangle"].tolist() == [0, 2]
     assert np.isclose(hits["depth"][0], 0.2) and np.isclose(hits["depth"][1], 0.1, atol=1e-6)      # 0.5 - (0.5 - 0.1): pushed to 0.5 by the first
     assert np.isclose(out.T["origin"][0, 1], 0.6, atol=1e-6)
+
+
+def test_ray_spring_on_a_flat_triangle():
+    """The biped's legs (a ray collider of collision type spring, client_focal_entity.h:30-91) over mesh ground."""
+    h = np.float32(np.sqrt(0.5))
+    s = one_body(abi.COLLIDER_BOX, (1.0, 2.0, -2.0))
+    c = s.C["colliders"]
+    c["isActive"][0, 1] = 1
+    c["colliderType"][0, 1] = abi.COLLIDER_RAY
+    c["collisionType"][0, 1] = abi.COLLISION_SPRING
+    c["localTransform"]["orientation"][0, 1] = (h, h, 0, 0)                   # +z of the ray -> -y of the body
+    c["localTransform"]["scale"][0, 1] = (1, 1, 3.0)                          # 3 long: the end is 1 below the floor
+    c["stiffness"][0, 1], c["damping"][0, 1], c["restLength"][0, 1] = 2500, 400, 0.1
+    c["inheritOrientation"][0, 1], c["influenceOrientation"][0, 1] = 0, 0
+    c["minParametricValue"][0, 1] = 1.0
+    out, hits = refs.oracle_mesh_pass(s, FLOOR_V, FLOOR_T)
+    ray = hits[hits["slot"] == 1]
+    assert len(ray) == 1                                                      # the second floor triangle lies no nearer: minParametricValue keeps the first
+    assert np.allclose(ray["normal"][0], (0, 1, 0), atol=2e-5) and np.isclose(ray["depth"][0], 1.0, atol=1e-5)
+    assert np.allclose(ray["point"][0], (1.0, -0.5, -2.0), atol=2e-5)          # spring_rigid_response moves the contact half the depth in (:926)
+    assert np.isclose(out.C["colliders"]["minParametricValue"][0, 1], 2.0 / 3.0, atol=1e-6)
+    assert out.P["acceleration"][0, 1] > 0                                    # the spring pushes the body up
+    # a ray that ends above the floor meets nothing; a hit behind an earlier one (minParametricValue) is not taken
+    c["localTransform"]["scale"][0, 1] = (1, 1, 1.5)
+    assert not (refs.oracle_mesh_pass(s, FLOOR_V, FLOOR_T)[1]["slot"] == 1).any()
+    c["localTransform"]["scale"][0, 1] = (1, 1, 3.0)
+    c["minParametricValue"][0, 1] = 0.5
+    assert not (refs.oracle_mesh_pass(s, FLOOR_V, FLOOR_T)[1]["slot"] == 1).any()
