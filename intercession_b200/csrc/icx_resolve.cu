@@ -49,6 +49,9 @@ __device__ __forceinline__ Cursor load_cursor(const DeviceWorld& W, uint32_t slo
 // entry.y = partner's entity index (24 bits) | quantised lower bound of the gap between the two shapes on the post-integration
 // state << 24 (ICX_GAP_UNIT margins per step; 0 = touching / unknown): see gap_of / cannot_meet
 #define ICX_NB_ENT_MASK 0x00FFFFFFu
+#ifndef ICX_GAPS_MIN_XPAIRS
+#define ICX_GAPS_MIN_XPAIRS 2048u   // extra pairs from which the flagged lists get their may_meet gaps (lists_extend_flagged)
+#endif
 #define ICX_GAP_UNIT 0.5f
 __device__ __forceinline__ bool cursor_head(const Cursor& c, uint32_t hw, uint32_t& k, uint32_t& entry, uint32_t& eo)
 {
@@ -835,6 +838,62 @@ __device__ __forceinline__ void lists_build(const DeviceWorld& W, uint32_t first
     for (uint32_t s = first + (tid >> 5); s < n_dirty; s += (nth >> 5)) if (slot_wanted(W, s, first, n_dirty, mode, always_from)) sort_lists_warp(W, s);
 }
 
+// The lists of the flagged slots among the listed ones [0, n_listed) -- the movers and the bodies their extra pairs name -- get
+// those extra pairs.  Their adjacency in the flat pair list is already there (sorted): the old entries are copied into a fresh pool
+// region, the extra pairs appended by a pass over the extra pairs alone, and the result sorted again.  No pass over the tick's pair
+// list, no gaps (0 = unknown: may_meet then decides on the bounds alone); the caller uses it while the extra pairs are few.
+template <typename Grid>
+__device__ __forceinline__ void lists_extend_flagged(const DeviceWorld& W, uint32_t n_listed, Grid& grid, uint32_t tid, uint32_t nth)
+{
+    const uint32_t FULL = 0xFFFFFFFFu, lane = tid & 31u;
+    const uint32_t n_x = min(*(volatile uint32_t*)&W.counters[CTR_XPAIRS], W.max_xpairs);
+    for (uint32_t s = tid; s < n_listed; s += nth) if (W.slot_flag[s]) { W.nbr_count[s * 2u] = 0u; W.nbr_count[s * 2u + 1u] = 0u; }
+    grid.sync();
+    for (int fill = 0; fill < 2; fill++) {
+        for (uint32_t i = tid; i < n_x; i += nth) {
+            const uint2 pr = W.xpairs[i];
+            const uint32_t pa = pr.x & ICX_NB_INDEX_MASK, pb = pr.y & ICX_NB_INDEX_MASK;
+            const bool ia = (pr.x & ICX_PAIR_A_IMMUT) != 0, ib = (pr.y & ICX_PAIR_B_IMMUT) != 0;
+            if (ia && ib) continue;
+            const uint32_t ea = W.pk_entity[pa], eb = W.pk_entity[pb];
+            const uint32_t sa = ia ? ICX_NONE : W.dirty_slot[ea], sb = ib ? ICX_NONE : W.dirty_slot[eb];
+            const bool wa = sa < n_listed && W.slot_flag[sa] != 0u, wb = sb < n_listed && W.slot_flag[sb] != 0u;
+            if (!wa && !wb) continue;
+            const uint32_t gapq = 0u;                                               // unknown: may_meet decides on the bounds alone
+            if (wa) list_visit(W, sa, ea, pa, pb, eb, ib, fill != 0, gapq);
+            if (wb) list_visit(W, sb, eb, pb, pa, ea, ia, fill != 0, gapq);
+        }
+        grid.sync();
+        if (fill) break;
+        for (uint32_t s = tid >> 5; s < n_listed; s += (nth >> 5)) {                // one warp per flagged slot: new region, old entries first
+            if (!W.slot_flag[s]) continue;
+            const uint4 old = W.slot_info[s];
+            if (old.z == ICX_NONE) continue;                                        // (the pool overflowed earlier: the tick is re-run)
+            const uint32_t n0 = old.y & 0xFFFFu, n1 = old.y >> 16;
+            const uint32_t c0 = n0 + W.nbr_count[s * 2u], c1 = n1 + W.nbr_count[s * 2u + 1u];
+            if (c0 == n0 && c1 == n1) continue;                                     // a mover whose walk found nothing new: its list stands
+            uint32_t off = ICX_NONE;
+            if (lane == 0u) {
+                if (c0 <= 0xFFFFu && c1 <= 0xFFFFu) { off = atomicAdd(&W.counters[CTR_POOL], c0 + c1); if (off + c0 + c1 > W.max_nbr) off = ICX_NONE; }
+                if (off == ICX_NONE) atomicOr(W.flags, RF_NEIGHBOR_OVERFLOW);
+            }
+            off = __shfl_sync(FULL, off, 0);
+            if (off != ICX_NONE) {
+                for (uint32_t i = lane; i < n0 + n1; i += 32u) {
+                    const uint2 en = W.nbr[old.z + i];
+                    W.nbr[off + (i < n0 ? i : c0 + (i - n0))] = en;
+                }
+            }
+            if (lane == 0u) {
+                W.slot_info[s] = make_uint4(old.x, off == ICX_NONE ? 0u : (c0 | (c1 << 16)), off, old.w);
+                W.nbr_fill[s * 2u] = n0; W.nbr_fill[s * 2u + 1u] = n1;              // the extra pairs go behind the old entries
+            }
+        }
+        grid.sync();
+    }
+    for (uint32_t s = tid >> 5; s < n_listed; s += (nth >> 5)) if (W.slot_flag[s]) sort_lists_warp(W, s);
+}
+
 // Put a dirty body back to its post-integration state (bit-identical recomputation from the tick input).
 static __device__ __noinline__ void restore_body(const DeviceWorld& W, uint32_t e, double dt, int do_euler)
 {
@@ -1193,6 +1252,7 @@ __device__ __forceinline__ void trace_mark(const DeviceWorld& W, uint32_t& n, ui
 // PHASE 0 = prepare (2 x 384 threads per SM), PHASE 1 = rounds (1 x 256 threads per SM, 251 registers) --
 // which also carries the whole loop for the rare restarts.
 #define ICX_MAX_ATTEMPTS 96u
+
 #ifndef ICX_LANE_MIN
 #define ICX_LANE_MIN 4u          // items per warp from which a round runs lane-parallel (break-even measured at ~4: the lane-parallel pass costs ~40 us flat, a warp-mode item ~19 us, a cursor walk ~9.5 us)
 #endif
@@ -1246,21 +1306,27 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
             if (n_mov != 0u) {                                  // (uniform) the lists of the movers and of the bodies their extra candidates name
                 for (uint32_t s = tid; s < n_dirty; s += nth) W.slot_flag[s] = 0u;      // again, now with those candidates and with the gaps may_meet prunes by
                 grid.sync();
-                for (uint32_t m = tid; m < n_mov; m += nth) { const uint32_t s = W.dirty_slot[W.mover_list[m]]; if (s < n_dirty) W.slot_flag[s] = 1u; }
+                for (uint32_t m = tid; m < n_mov; m += nth) { const uint32_t s = W.dirty_slot[W.mover_list[m]]; if (s < n_dirty) atomicMax(&W.slot_flag[s], 2u); }   // 2 = a mover: its list gets the gaps too
                 for (uint32_t i = tid; i < n_x; i += nth) {
                     const uint2 pr = W.xpairs[i];
-                    if (!(pr.x & ICX_PAIR_A_IMMUT)) { const uint32_t s = W.dirty_slot[W.pk_entity[pr.x & ICX_NB_INDEX_MASK]]; if (s < n_dirty) W.slot_flag[s] = 1u; }
-                    if (!(pr.y & ICX_PAIR_B_IMMUT)) { const uint32_t s = W.dirty_slot[W.pk_entity[pr.y & ICX_NB_INDEX_MASK]]; if (s < n_dirty) W.slot_flag[s] = 1u; }
+                    if (!(pr.x & ICX_PAIR_A_IMMUT)) { const uint32_t s = W.dirty_slot[W.pk_entity[pr.x & ICX_NB_INDEX_MASK]]; if (s < n_dirty) atomicMax(&W.slot_flag[s], 1u); }
+                    if (!(pr.y & ICX_PAIR_B_IMMUT)) { const uint32_t s = W.dirty_slot[W.pk_entity[pr.y & ICX_NB_INDEX_MASK]]; if (s < n_dirty) atomicMax(&W.slot_flag[s], 1u); }
                 }
                 grid.sync();
-                lists_build(W, 0u, n_dirty, grid, tid, nth, LISTS_FLAGGED, done);      // (+ plain lists of the bodies the last pass marked: slots >= done)
+                // Many extra pairs (a pile): the flagged lists are built again from the pair list, with the gap of every two-sided
+                // pair measured once.  A handful (the sparse case, every tick of it): the extra pairs are appended to the lists that
+                // exist and the gaps are left out -- measuring them would put ~100 us of cold-code latency on the critical path.
+                const bool rebuild = n_x >= ICX_GAPS_MIN_XPAIRS;                    // (uniform)
+                if (rebuild) lists_build(W, 0u, n_dirty, grid, tid, nth, LISTS_FLAGGED, done);      // (+ plain lists of the bodies the last pass marked: slots >= done)
+                else lists_extend_flagged(W, done, grid, tid, nth);            // (those bodies get their lists -- extra pairs included -- with the attempt's)
                 grid.sync();
                 // ... and the clean bodies a mover can reach through them are replayed in order too
+                const uint32_t listed = rebuild ? n_dirty : done;
                 for (uint32_t m = (tid >> 5); m < n_mov; m += (nth >> 5)) {
                     const uint32_t sl = W.dirty_slot[W.mover_list[m]];
-                    if (sl < n_dirty) predict_body_warp(W, sl, true);
+                    if (sl < listed) predict_body_warp(W, sl, true);
                 }
-                done = n_dirty;
+                done = listed;
                 grid.sync();
             }
         }
