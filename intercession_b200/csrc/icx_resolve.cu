@@ -49,6 +49,9 @@ __device__ __forceinline__ Cursor load_cursor(const DeviceWorld& W, uint32_t slo
 // entry.y = partner's entity index (24 bits) | quantised lower bound of the gap between the two shapes on the post-integration
 // state << 24 (ICX_GAP_UNIT margins per step; 0 = touching / unknown): see gap_of / cannot_meet
 #define ICX_NB_ENT_MASK 0x00FFFFFFu
+#ifndef ICX_SWEEP_MIN_SHARE
+#define ICX_SWEEP_MIN_SHARE 50u     // another list + prediction sweep only if more than 1 / this of the dirty bodies are new
+#endif
 #ifndef ICX_GAPS_MIN_XPAIRS
 #define ICX_GAPS_MIN_XPAIRS 2048u   // extra pairs from which the flagged lists get their may_meet gaps (lists_extend_flagged)
 #endif
@@ -1288,7 +1291,7 @@ __device__ __forceinline__ void resolve_body(const DeviceWorld& W, double dt, in
             const uint32_t changed = sweep ? ctr[CTR_PUSHED] : 1u;
             grid.sync();                                        // every thread has read the counters before thread 0 resets one
             // another pass only if it matters: many new bodies to list, or many pushes handed on (uniform)
-            if (sweep && (n_dirty - done) * 50u < n_dirty && changed * 100u < n_dirty) break;
+            if (sweep && (n_dirty - done) * ICX_SWEEP_MIN_SHARE < n_dirty && changed * 100u < n_dirty) break;
             if (tid == 0) { ctr[CTR_PUSHED] = 0u; __threadfence(); }
             lists_build(W, done, n_dirty, grid, tid, nth, LISTS_PLAIN, 0u);
             if (tid == 0) trace_mark(W, tn, 0x60000u | min(n_dirty - done, 0xFFFFu));
