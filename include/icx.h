@@ -296,7 +296,8 @@ ICX_API int icx_world_clone(IcxWorld* src, IcxWorld* dst, const uint8_t* has_fut
  * overlap the collider's bounds (taken when the collider's turn starts) in ascending triangle index.  A hit (sphere -
  * triangle: closest point; box - triangle: 13-axis separating-axis test) is answered with the reference's
  * rigid_rigid_response (collision_procedures.cpp:636-874) against an immovable body of the mesh's material, so later
- * triangles see the moved body.  A ray (Moeller-Trumbore) only counts in front of what it has met so far this tick
+ * triangles see the moved body.  (The mesh belongs to the world it was uploaded to: icx_world_clone copies entities, not the
+ * mesh -- a parallel cosmos that should meet it gets its own icx_mesh_upload.)  A ray (Moeller-Trumbore) only counts in front of what it has met so far this tick
  * (Collider::minParametricValue, as ray_box_intersect keeps it) and is answered with spring_rigid_response (:876-1053).  Entities do not interact in this pass.  Contacts: icx_mesh_contacts_fetch, in that order.
  */
 typedef struct IcxMeshMaterial { float staticFriction, dynamicFriction, restitution; } IcxMeshMaterial;
